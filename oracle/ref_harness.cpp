@@ -1,0 +1,182 @@
+// oracle/ref_harness.cpp — TEST INFRASTRUCTURE ONLY (not product code).
+//
+// A small C-ABI driver over the reference's PUBLIC ggml API (ggml.h, ggml-backend.h, ggml-alloc.h)
+// so that Python tests / bench.py can run one GGML_OP_MUL_MAT or GGML_OP_MUL_MAT_ID graph on any
+// registered ggml backend device: the reference's ggml-cpu variants (the oracle and the timed CPU
+// baseline) or our own libggml-b200.so loaded through ggml_backend_load() (the drop-in check).
+// It mirrors what tests/test-backend-ops.cpp does per test case (build 1-op graph, allocate on the
+// backend, ggml_backend_tensor_set inputs, ggml_backend_graph_compute, ggml_backend_tensor_get).
+//
+// Compiled against the reference's headers where they lie (/root/reference/ggml/include) and linked
+// to oracle/_ref/libggml.so + libggml-base.so; output oracle/_ref/libref_harness.so.
+
+#include "ggml.h"
+#include "ggml-alloc.h"
+#include "ggml-backend.h"
+
+#include <chrono>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace {
+
+struct graph_run {
+    ggml_context *        ctx   = nullptr;
+    ggml_backend_t        be    = nullptr;
+    ggml_backend_buffer_t buf   = nullptr;
+    ggml_cgraph *         graph = nullptr;
+    ~graph_run() {
+        if (buf) ggml_backend_buffer_free(buf);
+        if (be) ggml_backend_free(be);
+        if (ctx) ggml_free(ctx);
+    }
+};
+
+std::vector<ggml_backend_reg_t> g_regs;
+
+ggml_backend_t open_backend(int reg_index, int dev_index, int n_threads) {
+    if (reg_index < 0 || reg_index >= (int) g_regs.size()) return nullptr;
+    ggml_backend_reg_t reg = g_regs[reg_index];
+    if (dev_index < 0 || dev_index >= (int) ggml_backend_reg_dev_count(reg)) return nullptr;
+    ggml_backend_dev_t dev = ggml_backend_reg_dev_get(reg, dev_index);
+    ggml_backend_t be = ggml_backend_dev_init(dev, nullptr);
+    if (!be) return nullptr;
+    if (n_threads > 0) {
+        auto set_n = (ggml_backend_set_n_threads_t) ggml_backend_reg_get_proc_address(reg, "ggml_backend_set_n_threads");
+        if (set_n) set_n(be, n_threads);
+    }
+    return be;
+}
+
+bool make_ctx(graph_run & g) {
+    ggml_init_params ip = { ggml_tensor_overhead() * 64 + ggml_graph_overhead(), nullptr, true };
+    g.ctx = ggml_init(ip);
+    return g.ctx != nullptr;
+}
+
+bool finish(graph_run & g, ggml_tensor * out) {
+    g.graph = ggml_new_graph(g.ctx);
+    ggml_build_forward_expand(g.graph, out);
+    g.buf = ggml_backend_alloc_ctx_tensors(g.ctx, g.be);
+    return g.buf != nullptr;
+}
+
+double time_graph(graph_run & g, double seconds, int * runs_out) {
+    // warm-up once, then repeat for >= `seconds` (tests/test-backend-ops.cpp:1499-1515 pattern)
+    ggml_backend_graph_compute(g.be, g.graph);
+    ggml_backend_synchronize(g.be);
+    int runs = 0;
+    auto t0 = std::chrono::steady_clock::now();
+    double el = 0;
+    do {
+        ggml_backend_graph_compute(g.be, g.graph);
+        ggml_backend_synchronize(g.be);
+        runs++;
+        el = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    } while (el < seconds);
+    if (runs_out) *runs_out = runs;
+    return el / runs * 1e6;
+}
+
+} // namespace
+
+extern "C" {
+
+// load a backend shared library (a ggml-cpu variant or libggml-b200.so); returns a handle >= 0, or -1
+int refh_load_backend(const char * path) {
+    ggml_backend_reg_t reg = ggml_backend_load(path);
+    if (!reg) return -1;
+    g_regs.push_back(reg);
+    return (int) g_regs.size() - 1;
+}
+
+const char * refh_reg_name(int reg) { return reg >= 0 && reg < (int) g_regs.size() ? ggml_backend_reg_name(g_regs[reg]) : ""; }
+int refh_reg_dev_count(int reg) { return reg >= 0 && reg < (int) g_regs.size() ? (int) ggml_backend_reg_dev_count(g_regs[reg]) : 0; }
+const char * refh_dev_description(int reg, int dev) {
+    if (reg < 0 || reg >= (int) g_regs.size() || dev < 0 || dev >= (int) ggml_backend_reg_dev_count(g_regs[reg])) return "";
+    return ggml_backend_dev_description(ggml_backend_reg_dev_get(g_regs[reg], dev));
+}
+
+// dst[M, N, ne12, ne13] = MUL_MAT(W[K, M, ne02, ne03] (type), X[K, N, ne12, ne13] f32); contiguous tensors.
+// seconds > 0: also time it, *us_per_run receives the mean. returns 0 on success.
+int refh_mul_mat(int reg, int dev, int n_threads, int type, int64_t M, int64_t K, int64_t N,
+                 int64_t ne02, int64_t ne03, int64_t ne12, int64_t ne13,
+                 const void * W, const float * X, float * dst, double seconds, double * us_per_run) {
+    graph_run g;
+    g.be = open_backend(reg, dev, n_threads);
+    if (!g.be || !make_ctx(g)) return 1;
+    ggml_tensor * w = ggml_new_tensor_4d(g.ctx, (ggml_type) type, K, M, ne02, ne03);
+    ggml_tensor * x = ggml_new_tensor_4d(g.ctx, GGML_TYPE_F32, K, N, ne12, ne13);
+    ggml_tensor * o = ggml_mul_mat(g.ctx, w, x);
+    if (!ggml_backend_supports_op(g.be, o)) return 2;
+    if (!finish(g, o)) return 3;
+    ggml_backend_tensor_set(w, W, 0, ggml_nbytes(w));
+    ggml_backend_tensor_set(x, X, 0, ggml_nbytes(x));
+    if (ggml_backend_graph_compute(g.be, g.graph) != GGML_STATUS_SUCCESS) return 4;
+    ggml_backend_synchronize(g.be);
+    if (dst) ggml_backend_tensor_get(o, dst, 0, ggml_nbytes(o));
+    if (seconds > 0 && us_per_run) *us_per_run = time_graph(g, seconds, nullptr);
+    return 0;
+}
+
+// dst[M, n_used, n_tok] = MUL_MAT_ID(as[K, M, n_as] (type), b[K, ne11, n_tok] f32, ids[n_used, n_tok] i32)
+int refh_mul_mat_id(int reg, int dev, int n_threads, int type, int64_t M, int64_t K, int64_t n_as,
+                    int64_t n_used, int64_t ne11, int64_t n_tok,
+                    const void * W, const float * B, const int32_t * ids, float * dst,
+                    double seconds, double * us_per_run) {
+    graph_run g;
+    g.be = open_backend(reg, dev, n_threads);
+    if (!g.be || !make_ctx(g)) return 1;
+    ggml_tensor * w = ggml_new_tensor_3d(g.ctx, (ggml_type) type, K, M, n_as);
+    ggml_tensor * b = ggml_new_tensor_3d(g.ctx, GGML_TYPE_F32, K, ne11, n_tok);
+    ggml_tensor * i = ggml_new_tensor_2d(g.ctx, GGML_TYPE_I32, n_used, n_tok);
+    ggml_tensor * o = ggml_mul_mat_id(g.ctx, w, b, i);
+    if (!ggml_backend_supports_op(g.be, o)) return 2;
+    if (!finish(g, o)) return 3;
+    ggml_backend_tensor_set(w, W, 0, ggml_nbytes(w));
+    ggml_backend_tensor_set(b, B, 0, ggml_nbytes(b));
+    ggml_backend_tensor_set(i, ids, 0, ggml_nbytes(i));
+    if (ggml_backend_graph_compute(g.be, g.graph) != GGML_STATUS_SUCCESS) return 4;
+    ggml_backend_synchronize(g.be);
+    if (dst) ggml_backend_tensor_get(o, dst, 0, ggml_nbytes(o));
+    if (seconds > 0 && us_per_run) *us_per_run = time_graph(g, seconds, nullptr);
+    return 0;
+}
+
+// A stack of `n_mats` independent MUL_MATs in ONE graph (distinct weight tensors, one shared or per-op
+// activation), the CPU-baseline counterpart of bench.py's layer-stack step. Ms/Ks give each matrix' shape.
+// Weights: W_all is the concatenation of the matrices' bytes. Returns us per graph run in *us_per_run.
+int refh_mul_mat_stack(int reg, int dev, int n_threads, int type, int n_mats, const int64_t * Ms, const int64_t * Ks,
+                       int64_t N, const void * W_all, const float * X_all, double seconds, double * us_per_run, int * runs) {
+    graph_run g;
+    g.be = open_backend(reg, dev, n_threads);
+    if (!g.be) return 1;
+    ggml_init_params ip = { ggml_tensor_overhead() * (size_t) (4 * n_mats + 16) + ggml_graph_overhead_custom(4 * n_mats + 16, false), nullptr, true };
+    g.ctx = ggml_init(ip);
+    if (!g.ctx) return 1;
+    std::vector<ggml_tensor *> ws(n_mats), xs(n_mats), os(n_mats);
+    g.graph = ggml_new_graph_custom(g.ctx, 4 * n_mats + 16, false);
+    for (int i = 0; i < n_mats; i++) {
+        ws[i] = ggml_new_tensor_2d(g.ctx, (ggml_type) type, Ks[i], Ms[i]);
+        xs[i] = ggml_new_tensor_2d(g.ctx, GGML_TYPE_F32, Ks[i], N);
+        os[i] = ggml_mul_mat(g.ctx, ws[i], xs[i]);
+        ggml_build_forward_expand(g.graph, os[i]);
+    }
+    g.buf = ggml_backend_alloc_ctx_tensors(g.ctx, g.be);
+    if (!g.buf) return 3;
+    const char *  wp = (const char *) W_all;
+    const float * xp = X_all;
+    for (int i = 0; i < n_mats; i++) {
+        ggml_backend_tensor_set(ws[i], wp, 0, ggml_nbytes(ws[i]));
+        ggml_backend_tensor_set(xs[i], xp, 0, ggml_nbytes(xs[i]));
+        wp += ggml_nbytes(ws[i]);
+        xp += Ks[i] * N;
+    }
+    *us_per_run = time_graph(g, seconds, runs);
+    return 0;
+}
+
+} // extern "C"
