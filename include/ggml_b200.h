@@ -1,0 +1,183 @@
+/* include/ggml_b200.h — the thin C-ABI between the ggml-backend host code and the sm_100a CUDA kernels.
+ *
+ * Everything the B200 backend does on the device goes through these entry points: plain pointers,
+ * sizes and ggml-style byte strides — no ggml, torch or CUDA types in the signatures. The host side
+ * (qvac-ext-lib-llama.cpp_b200/csrc/ggml_backend_b200.cpp) implements the reference's
+ * ggml_backend_reg_i / ggml_backend_device_i / ggml_backend_i / ggml_backend_buffer(_type)_i vtables
+ * (/root/reference/ggml/src/ggml-backend-impl.h:16-204) purely in terms of this header; Python tests
+ * and bench.py bind the same symbols with ctypes.
+ *
+ * Each entry point names the reference interface it replaces (paths relative to /root/reference).
+ * There is NO CPU fallback anywhere behind this API: without a CUDA device every call fails with
+ * B200_ERR_CUDA, and an unsupported shape/type fails with B200_ERR_UNSUPPORTED.
+ */
+#ifndef GGML_B200_H
+#define GGML_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_API __attribute__((visibility("default")))
+
+typedef enum {
+    B200_OK              = 0,
+    B200_ERR_UNSUPPORTED = 1, /* type / layout outside the hot path (ggml-cuda.cu supports_op :4258-4618 analogue) */
+    B200_ERR_CUDA        = 2, /* CUDA runtime error, no device, or kernel image missing */
+    B200_ERR_ARG         = 3,
+    B200_ERR_ALLOC       = 4  /* device OOM: alloc_buffer returns nullptr (ggml-cuda.cu:695-712) */
+} b200_status;
+
+/* enum ggml_type values of the three weight formats (ggml/include/ggml.h:378-395) */
+#define B200_TYPE_Q4_0 2
+#define B200_TYPE_Q8_0 8
+#define B200_TYPE_Q4_K 12
+
+/* which kernel family a MUL_MAT is routed to (b200_set_force_path / B200 env GGML_B200_FORCE) */
+#define B200_PATH_AUTO   0
+#define B200_PATH_MMVQ   1   /* decode mat-vec kernels, any n (looped over 8-column groups) */
+#define B200_PATH_MMQ    2   /* tcgen05 int8 tile kernels */
+#define B200_PATH_SIMPLE 3   /* generic one-warp-per-row kernel (any K % 32, any alignment) */
+
+typedef struct b200_ctx b200_ctx; /* one device + one stream + scratch pool: a ggml_backend_t "stream"
+                                     (ggml_backend_cuda_context, ggml-cuda/common.cuh:1134-1196) */
+
+/* ---------------------------------------------------------------- device / context ---- */
+
+/* number of usable devices = CUDA devices with compute capability 10.0 (ggml_backend_cuda_get_device_count, ggml-cuda.cu:4821) */
+B200_API int          b200_device_count(void);
+/* name[<=128], PCI bus id[<=32] (device_id, ggml-cuda.cu:4814-4816), SM count */
+B200_API b200_status  b200_device_info(int device, char * name, size_t name_len, char * pci_bus_id, size_t id_len,
+                                       int * sm_count, int * cc_major, int * cc_minor);
+/* get_memory (ggml-cuda.cu:4188-4193) */
+B200_API b200_status  b200_device_memory(int device, size_t * free_bytes, size_t * total_bytes);
+
+/* init_backend (ggml-cuda.cu:4711-4717). stream: an existing cudaStream_t (as void*) to launch on, or NULL to create one */
+B200_API b200_status  b200_ctx_create(int device, void * stream, b200_ctx ** out);
+B200_API void         b200_ctx_destroy(b200_ctx * ctx);
+B200_API int          b200_ctx_device(const b200_ctx * ctx);
+B200_API void *       b200_ctx_stream(const b200_ctx * ctx);                 /* the cudaStream_t kernels are launched on */
+B200_API b200_status  b200_ctx_synchronize(b200_ctx * ctx);                  /* iface.synchronize (ggml-cuda.cu:2828-2834) */
+B200_API const char * b200_last_error(void);                                 /* thread-local message of the last failure */
+B200_API uint64_t     b200_ctx_launch_count(const b200_ctx * ctx);           /* kernels launched so far (bench.py gpu_launches) */
+B200_API void         b200_ctx_set_force_path(b200_ctx * ctx, int path);     /* B200_PATH_* */
+
+/* ---------------------------------------------------------------- memory ---- */
+
+/* buffer type alloc_buffer / free_buffer (ggml-cuda.cu:564-712); 256-byte aligned, NULL + B200_ERR_ALLOC on OOM */
+B200_API b200_status  b200_malloc(int device, size_t size, void ** ptr);
+B200_API b200_status  b200_free(int device, void * ptr);
+/* pinned host buffer type (ggml-cuda.cu:1104-1168) */
+B200_API b200_status  b200_host_malloc(size_t size, void ** ptr);
+B200_API b200_status  b200_host_free(void * ptr);
+/* buffer set_tensor / get_tensor / memset_tensor / clear: synchronous on return (ggml-cuda.cu:614-662) */
+B200_API b200_status  b200_memcpy_h2d(int device, void * dst, const void * src, size_t size);
+B200_API b200_status  b200_memcpy_d2h(int device, void * dst, const void * src, size_t size);
+B200_API b200_status  b200_memcpy_d2d(int device, void * dst, const void * src, size_t size);
+B200_API b200_status  b200_memcpy_peer(int dst_device, void * dst, int src_device, const void * src, size_t size);
+B200_API b200_status  b200_memset(int device, void * dst, int value, size_t size);
+/* iface.set_tensor_async / get_tensor_async / cpy_tensor_async on the context's stream (ggml-cuda.cu:2755-2826) */
+B200_API b200_status  b200_memcpy_h2d_async(b200_ctx * ctx, void * dst, const void * src, size_t size);
+B200_API b200_status  b200_memcpy_d2h_async(b200_ctx * ctx, void * dst, const void * src, size_t size);
+B200_API b200_status  b200_memcpy_d2d_async(b200_ctx * ctx, void * dst, const void * src, size_t size);
+
+/* events: device event_new/free/synchronize, backend event_record/event_wait (ggml-cuda.cu:2836-2862, 4649-4677) */
+B200_API b200_status  b200_event_create(int device, void ** event);
+B200_API b200_status  b200_event_destroy(int device, void * event);
+B200_API b200_status  b200_event_record(b200_ctx * ctx, void * event);
+B200_API b200_status  b200_event_wait(b200_ctx * ctx, void * event);
+B200_API b200_status  b200_event_synchronize(void * event);
+B200_API b200_status  b200_event_elapsed_ms(void * start, void * stop, float * ms);
+
+/* ---------------------------------------------------------------- K1: activation quantizer ---- */
+
+/* F32 rows -> ggml blocks, bit-exact to quantize_row_q8_0_ref / _q8_1_ref / _q8_K_ref
+ * (ggml/src/ggml-quants.c:199-222, 225-258, 2555-2592); replaces quantize_row_q8_1_cuda
+ * (ggml-cuda/quantize.cu:148-162). x: device F32, row r at (char*)x + r*x_row_stride; y: device, rows of
+ * k/32*34 (q8_0), k/32*36 (q8_1) or k/256*292 (q8_K) bytes, contiguous. k % 32 == 0 (q8_K: % 256). */
+B200_API b200_status  b200_quantize_q8_0(b200_ctx * ctx, const float * x, int64_t k, int64_t nrows, size_t x_row_stride, void * y);
+B200_API b200_status  b200_quantize_q8_1(b200_ctx * ctx, const float * x, int64_t k, int64_t nrows, size_t x_row_stride, void * y);
+B200_API b200_status  b200_quantize_q8_K(b200_ctx * ctx, const float * x, int64_t k, int64_t nrows, size_t x_row_stride, void * y);
+
+/* the kernels' internal activation layout ("unit records": 256 int8 + 16 B scales/sums per 256 elements, + 16 B aux),
+ * same values as the functions above. kind: 0 = q8_0-valued (for q4_0/q8_0 weights), 1 = q8_K-valued (for q4_K).
+ * main: nrows * k/256 * 272 bytes, aux: nrows * k/256 * 16 bytes. Exposed for the parity tests. k % 256 == 0. */
+B200_API b200_status  b200_quantize_units(b200_ctx * ctx, int kind, const float * x, int64_t k, int64_t nrows, size_t x_row_stride,
+                                          void * main, void * aux);
+
+/* ---------------------------------------------------------------- K3/K4: MUL_MAT ---- */
+
+/* tensor geometry exactly as struct ggml_tensor carries it (ggml/include/ggml.h:645-676): ne in elements, nb in bytes.
+ * src0 = weights [ne00=K, ne01=M, ne02, ne03] of `type`, rows contiguous (nb00 == type size);
+ * src1 = activations F32 [K, ne11=N, ne12, ne13], nb10 == 4; dst F32 [M, N, ne12, ne13], nb0 == 4.
+ * src0 is broadcast over ne12/ne02 and ne13/ne03 (ggml-cpu.c:1133-1134). */
+typedef struct {
+    int32_t type;
+    int64_t ne00, ne01, ne02, ne03;
+    size_t  nb01, nb02, nb03;
+    int64_t ne11, ne12, ne13;
+    size_t  nb11, nb12, nb13;
+    size_t  nb1, nb2, nb3;
+} b200_mul_mat_desc;
+
+/* supports_op for MUL_MAT (ggml-cuda.cu:4258-4330 analogue): 1 if b200_mul_mat accepts this geometry */
+B200_API int          b200_mul_mat_supported(const b200_mul_mat_desc * d);
+
+/* GGML_OP_MUL_MAT on device pointers; replaces ggml_cuda_mul_mat (ggml-cuda.cu:2178-2261) for the three types:
+ * quantizes src1 (K1), then mat-vec kernels for N <= 8 (ggml_cuda_mul_mat_vec_q, mmvq.cu:605-732) or the tcgen05
+ * int8 tile kernel otherwise (ggml_cuda_mul_mat_q, mmq.cu:70-236). Asynchronous on the context's stream. */
+B200_API b200_status  b200_mul_mat(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * src0, const float * src1, float * dst);
+
+/* Several MUL_MATs that share src1 (q/k/v, gate/up) in one launch. All descs must have identical type, K, N, batch
+ * dims 1 and src1 geometry. The ggml backend's graph_compute uses this when consecutive nodes share src1
+ * (the reference re-quantizes per op: SURVEY §8a a15). */
+B200_API b200_status  b200_mul_mat_shared_src1(b200_ctx * ctx, int n_ops, const b200_mul_mat_desc * descs,
+                                               const void * const * src0s, const float * src1, float * const * dsts);
+
+/* same op with HOST buffers: uploads src1 (and src0 when w_on_device == 0), runs, downloads dst, synchronizes.
+ * This is the call bench.py's `e2e` leg times (host<->device copies inside). */
+B200_API b200_status  b200_mul_mat_host(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * src0, int w_on_device,
+                                        const float * src1_host, float * dst_host);
+
+/* ---------------------------------------------------------------- K5/K6: MUL_MAT_ID ---- */
+
+/* as = experts [K, M, n_as] of `type` (expert e at as + e*nb02); b F32 [K, ne11, n_tok] (nb11, nb12);
+ * ids I32 [n_used, n_tok] (row stride ids_nb1); dst F32 [M, n_used, n_tok] (nb1, nb2):
+ * dst[:, i, t] = as[ids[i,t]] . b[:, i % ne11, t]   (ggml-cpu.c:1476-1649; ggml_cuda_mul_mat_id, ggml-cuda.cu:2263-2409) */
+typedef struct {
+    int32_t type;
+    int64_t ne00, ne01, n_as;
+    size_t  nb01, nb02;
+    int64_t ne11, n_tok;
+    size_t  nb11, nb12;
+    int64_t n_used;
+    size_t  ids_nb1;
+    size_t  nb1, nb2;
+} b200_mul_mat_id_desc;
+
+B200_API int          b200_mul_mat_id_supported(const b200_mul_mat_id_desc * d);
+B200_API b200_status  b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, const void * as, const float * b,
+                                      const int32_t * ids, float * dst);
+
+/* K5 alone (mm_ids_helper, ggml-cuda/mmid.cu:26-164): counting sort of the (slot, token) pairs by expert.
+ * pair p = t*n_used + i. Outputs (device): sorted_pairs[n_pairs] (pair index in expert order, stable in p),
+ * expert_bounds[n_as + 1]. Exposed for the parity tests. */
+B200_API b200_status  b200_mm_ids_sort(b200_ctx * ctx, const int32_t * ids, int64_t n_used, int64_t n_tok, size_t ids_nb1,
+                                       int64_t n_as, int32_t * sorted_pairs, int32_t * expert_bounds);
+
+/* ---------------------------------------------------------------- prefill weight cache ---- */
+
+/* The tcgen05 path consumes an int8, K-major, TMA-tileable expansion of a weight matrix plus per-32 float scales
+ * (the load-time analogue of ggml-cpu's repack buffer type, ggml-cpu/repack.cpp). It is built on first use per
+ * (src0 pointer, geometry) and dropped with these calls (buffer free / set_tensor on the range). */
+B200_API void         b200_weight_cache_invalidate(b200_ctx * ctx, const void * base, size_t size);
+B200_API void         b200_weight_cache_clear(b200_ctx * ctx);
+B200_API size_t       b200_weight_cache_bytes(const b200_ctx * ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GGML_B200_H */

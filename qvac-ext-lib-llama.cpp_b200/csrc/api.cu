@@ -1,0 +1,502 @@
+// api.cu — the C-ABI of include/ggml_b200.h: device/context/memory plumbing and the MUL_MAT dispatch that replaces
+// ggml_cuda_mul_mat (/root/reference/ggml/src/ggml-cuda/ggml-cuda.cu:2178-2261).
+// There is no CPU path in this file: every entry point either launches sm_100a kernels or fails.
+
+#include "internal.h"
+
+#include <mutex>
+#include <vector>
+
+using namespace b200;
+
+// ------------------------------------------------------------------------------------------------ errors
+
+static thread_local char g_err[512] = "";
+
+b200_status b200_fail(b200_status st, const char * fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return st;
+}
+#define fail b200_fail
+
+const char * b200_last_error(void) { return g_err; }
+
+b200_status b200_ensure(b200_ctx * ctx, void ** buf, size_t * cur, size_t need) {
+    if (need <= *cur) return B200_OK;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(ctx->stream, &cs);
+    if (cs != cudaStreamCaptureStatusNone) {
+        return fail(B200_ERR_ARG, "scratch buffer would have to grow (%zu -> %zu) during stream capture; run once uncaptured first", *cur, need);
+    }
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (*buf) CU(cudaFree(*buf));
+    *buf = nullptr;
+    *cur = 0;
+    const size_t sz = (need + (size_t) (1 << 20) - 1) & ~((size_t) (1 << 20) - 1);
+    CU(cudaMalloc(buf, sz));
+    *cur = sz;
+    return B200_OK;
+}
+#define ensure b200_ensure
+
+int b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    int ok = 0;
+    for (int i = 0; i < n; i++) {
+        int maj = 0;
+        if (cudaDeviceGetAttribute(&maj, cudaDevAttrComputeCapabilityMajor, i) == cudaSuccess && maj == 10) ok++;
+        else return ok;  // devices must be a homogeneous prefix; sm_100a images run on CC 10.0 only
+    }
+    return ok;
+}
+
+b200_status b200_device_info(int device, char * name, size_t name_len, char * pci, size_t pci_len, int * sms, int * maj, int * min) {
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (name && name_len) snprintf(name, name_len, "%s", prop.name);
+    if (pci && pci_len) snprintf(pci, pci_len, "%04x:%02x:%02x.0", prop.pciDomainID, prop.pciBusID, prop.pciDeviceID);
+    if (sms) *sms = prop.multiProcessorCount;
+    if (maj) *maj = prop.major;
+    if (min) *min = prop.minor;
+    return B200_OK;
+}
+
+b200_status b200_device_memory(int device, size_t * free_b, size_t * total_b) {
+    CU(cudaSetDevice(device));
+    CU(cudaMemGetInfo(free_b, total_b));
+    return B200_OK;
+}
+
+b200_status b200_ctx_create(int device, void * stream, b200_ctx ** out) {
+    if (!out) return fail(B200_ERR_ARG, "out is NULL");
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(B200_ERR_CUDA, "no CUDA device: the B200 backend has no CPU fallback");
+    }
+    if (device < 0 || device >= n) return fail(B200_ERR_ARG, "device %d out of range (%d devices)", device, n);
+    int maj = 0, sms = 0;
+    CU(cudaDeviceGetAttribute(&maj, cudaDevAttrComputeCapabilityMajor, device));
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    if (maj != 10) return fail(B200_ERR_CUDA, "device %d has compute capability %d.x; kernels are built for sm_100a only", device, maj);
+    CU(cudaSetDevice(device));
+    b200_ctx * c = new b200_ctx();
+    c->device   = device;
+    c->sm_count = sms;
+    if (stream) {
+        c->stream = (cudaStream_t) stream;
+    } else {
+        cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+        if (e != cudaSuccess) {
+            delete c;
+            return fail(B200_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
+        }
+        c->own_stream = true;
+    }
+    if (const char * s = getenv("GGML_B200_FORCE")) {
+        if (!strcmp(s, "mmvq")) c->force_path = B200_PATH_MMVQ;
+        else if (!strcmp(s, "mmq")) c->force_path = B200_PATH_MMQ;
+        else if (!strcmp(s, "simple")) c->force_path = B200_PATH_SIMPLE;
+    }
+    if (const char * s = getenv("GGML_B200_MV_WARPS")) c->mv_warps = atoi(s);
+    if (const char * s = getenv("GGML_B200_MV_STAGES")) c->mv_stages = atoi(s);
+    *out = c;
+    return B200_OK;
+}
+
+void b200_ctx_destroy(b200_ctx * ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->scratch) cudaFree(ctx->scratch);
+    if (ctx->io) cudaFree(ctx->io);
+    if (ctx->scratch2) cudaFree(ctx->scratch2);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int          b200_ctx_device(const b200_ctx * ctx) { return ctx->device; }
+void *       b200_ctx_stream(const b200_ctx * ctx) { return (void *) ctx->stream; }
+uint64_t     b200_ctx_launch_count(const b200_ctx * ctx) { return ctx->launches; }
+void         b200_ctx_set_force_path(b200_ctx * ctx, int path) { ctx->force_path = path; }
+b200_status  b200_ctx_synchronize(b200_ctx * ctx) {
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ memory
+
+b200_status b200_malloc(int device, size_t size, void ** ptr) {
+    *ptr = nullptr;
+    CU(cudaSetDevice(device));
+    cudaError_t e = cudaMalloc(ptr, size ? size : 1);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        *ptr = nullptr;
+        return fail(B200_ERR_ALLOC, "cudaMalloc(%zu) on device %d: %s", size, device, cudaGetErrorString(e));
+    }
+    return B200_OK;
+}
+b200_status b200_free(int device, void * ptr) {
+    CU(cudaSetDevice(device));
+    CU(cudaFree(ptr));
+    return B200_OK;
+}
+b200_status b200_host_malloc(size_t size, void ** ptr) {
+    *ptr = nullptr;
+    cudaError_t e = cudaMallocHost(ptr, size ? size : 1);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        *ptr = nullptr;
+        return fail(B200_ERR_ALLOC, "cudaMallocHost(%zu): %s", size, cudaGetErrorString(e));
+    }
+    return B200_OK;
+}
+b200_status b200_host_free(void * ptr) {
+    CU(cudaFreeHost(ptr));
+    return B200_OK;
+}
+b200_status b200_memcpy_h2d(int device, void * dst, const void * src, size_t size) {
+    CU(cudaSetDevice(device));
+    CU(cudaMemcpyAsync(dst, src, size, cudaMemcpyHostToDevice, cudaStreamPerThread));
+    CU(cudaStreamSynchronize(cudaStreamPerThread));
+    return B200_OK;
+}
+b200_status b200_memcpy_d2h(int device, void * dst, const void * src, size_t size) {
+    CU(cudaSetDevice(device));
+    CU(cudaMemcpyAsync(dst, src, size, cudaMemcpyDeviceToHost, cudaStreamPerThread));
+    CU(cudaStreamSynchronize(cudaStreamPerThread));
+    return B200_OK;
+}
+b200_status b200_memcpy_d2d(int device, void * dst, const void * src, size_t size) {
+    CU(cudaSetDevice(device));
+    CU(cudaMemcpyAsync(dst, src, size, cudaMemcpyDeviceToDevice, cudaStreamPerThread));
+    CU(cudaStreamSynchronize(cudaStreamPerThread));
+    return B200_OK;
+}
+b200_status b200_memcpy_peer(int dst_device, void * dst, int src_device, const void * src, size_t size) {
+    CU(cudaMemcpyPeer(dst, dst_device, src, src_device, size));
+    return B200_OK;
+}
+b200_status b200_memset(int device, void * dst, int value, size_t size) {
+    CU(cudaSetDevice(device));
+    CU(cudaMemsetAsync(dst, value, size, cudaStreamPerThread));
+    CU(cudaStreamSynchronize(cudaStreamPerThread));
+    return B200_OK;
+}
+b200_status b200_memcpy_h2d_async(b200_ctx * ctx, void * dst, const void * src, size_t size) {
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(dst, src, size, cudaMemcpyHostToDevice, ctx->stream));
+    return B200_OK;
+}
+b200_status b200_memcpy_d2h_async(b200_ctx * ctx, void * dst, const void * src, size_t size) {
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(dst, src, size, cudaMemcpyDeviceToHost, ctx->stream));
+    return B200_OK;
+}
+b200_status b200_memcpy_d2d_async(b200_ctx * ctx, void * dst, const void * src, size_t size) {
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(dst, src, size, cudaMemcpyDeviceToDevice, ctx->stream));
+    return B200_OK;
+}
+
+b200_status b200_event_create(int device, void ** event) {
+    CU(cudaSetDevice(device));
+    cudaEvent_t ev;
+    CU(cudaEventCreate(&ev));
+    *event = (void *) ev;
+    return B200_OK;
+}
+b200_status b200_event_destroy(int device, void * event) {
+    CU(cudaSetDevice(device));
+    CU(cudaEventDestroy((cudaEvent_t) event));
+    return B200_OK;
+}
+b200_status b200_event_record(b200_ctx * ctx, void * event) {
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventRecord((cudaEvent_t) event, ctx->stream));
+    return B200_OK;
+}
+b200_status b200_event_wait(b200_ctx * ctx, void * event) {
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamWaitEvent(ctx->stream, (cudaEvent_t) event, 0));
+    return B200_OK;
+}
+b200_status b200_event_synchronize(void * event) {
+    CU(cudaEventSynchronize((cudaEvent_t) event));
+    return B200_OK;
+}
+b200_status b200_event_elapsed_ms(void * start, void * stop, float * ms) {
+    CU(cudaEventElapsedTime(ms, (cudaEvent_t) start, (cudaEvent_t) stop));
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ K1
+
+static b200_status quantize_ggml_api(b200_ctx * ctx, int val, int64_t blk, const float * x, int64_t k, int64_t nrows, size_t stride, void * y) {
+    if (!ctx || !x || !y) return fail(B200_ERR_ARG, "null argument");
+    if (k <= 0 || k % blk != 0) return fail(B200_ERR_UNSUPPORTED, "k=%lld is not a multiple of %lld", (long long) k, (long long) blk);
+    if (stride % 4 != 0) return fail(B200_ERR_ARG, "row stride must be a multiple of 4 bytes");
+    CU(cudaSetDevice(ctx->device));
+    int l = 0;
+    CU(quantize_ggml(val, x, k, nrows, stride, y, ctx->stream, &l));
+    ctx->launches += l;
+    return B200_OK;
+}
+b200_status b200_quantize_q8_0(b200_ctx * ctx, const float * x, int64_t k, int64_t nrows, size_t s, void * y) { return quantize_ggml_api(ctx, 0, 32, x, k, nrows, s, y); }
+b200_status b200_quantize_q8_1(b200_ctx * ctx, const float * x, int64_t k, int64_t nrows, size_t s, void * y) { return quantize_ggml_api(ctx, 2, 32, x, k, nrows, s, y); }
+b200_status b200_quantize_q8_K(b200_ctx * ctx, const float * x, int64_t k, int64_t nrows, size_t s, void * y) { return quantize_ggml_api(ctx, 1, 256, x, k, nrows, s, y); }
+
+b200_status b200_quantize_units(b200_ctx * ctx, int kind, const float * x, int64_t k, int64_t nrows, size_t stride, void * main, void * aux) {
+    if (!ctx || !x || !main || !aux) return fail(B200_ERR_ARG, "null argument");
+    if (k <= 0 || k % 256 != 0) return fail(B200_ERR_UNSUPPORTED, "k=%lld is not a multiple of 256", (long long) k);
+    if (kind != ACT_KIND_Q8_0 && kind != ACT_KIND_Q8_K) return fail(B200_ERR_ARG, "kind must be 0 or 1");
+    CU(cudaSetDevice(ctx->device));
+    int l = 0;
+    CU(quantize_units(kind, x, k, nrows, stride, main, aux, ctx->stream, &l));
+    ctx->launches += l;
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ MUL_MAT
+
+static bool type_ok(int t) { return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K; }
+
+static size_t row_bytes(int type, int64_t k) { return (size_t) (k / type_block_elems(type)) * type_block_bytes(type); }
+
+int b200_mul_mat_supported(const b200_mul_mat_desc * d) {
+    if (!d || !type_ok(d->type)) return 0;
+    if (d->ne00 <= 0 || d->ne00 % type_block_elems(d->type) != 0) return 0;
+    if (d->ne01 < 0 || d->ne02 <= 0 || d->ne03 <= 0 || d->ne11 < 0 || d->ne12 <= 0 || d->ne13 <= 0) return 0;
+    if (d->ne12 % d->ne02 != 0 || d->ne13 % d->ne03 != 0) return 0;
+    if (d->nb01 < row_bytes(d->type, d->ne00)) return 0;
+    if (d->nb11 % 4 || d->nb12 % 4 || d->nb13 % 4 || d->nb1 % 4 || d->nb2 % 4 || d->nb3 % 4) return 0;
+    if (d->ne01 > INT32_MAX || d->ne00 > INT32_MAX) return 0;
+    return 1;
+}
+
+struct mv_cfg { int nw, ns; size_t smem; };
+
+static bool pick_mv_cfg(const b200_ctx * ctx, int type, int U, int nc, mv_cfg * out) {
+    static const int cand[][2] = { { 8, 4 }, { 8, 3 }, { 8, 2 }, { 4, 4 }, { 4, 3 }, { 4, 2 }, { 2, 2 }, { 1, 2 } };
+    const size_t lim = 227 * 1024;
+    if (ctx->mv_warps > 0 && ctx->mv_stages > 0) {
+        const size_t s = mv_fast_smem(type, U, nc, ctx->mv_warps, ctx->mv_stages);
+        if (s <= lim && ctx->mv_warps <= 8) { *out = { ctx->mv_warps, ctx->mv_stages, s }; return true; }
+    }
+    for (auto & c : cand) {
+        const size_t s = mv_fast_smem(type, U, nc, c[0], c[1]);
+        if (s <= lim) { *out = { c[0], c[1], s }; return true; }
+    }
+    return false;
+}
+
+static void mv_geometry(int U, MvParams * p) {
+    if (U <= 32) {
+        int L = 1;
+        while (L < U) L <<= 1;
+        p->L = L; p->rpg = 32 / L; p->slices = 1;
+    } else {
+        p->L = 32; p->rpg = 1; p->slices = (U + 31) / 32;
+    }
+    p->U = U;
+}
+
+static bool fast_layout_ok(int type, int64_t K, const void * w, size_t nb01, size_t nb02, size_t nb03) {
+    (void) type;
+    return K % 256 == 0 && (uintptr_t) w % 16 == 0 && nb01 % 16 == 0 && nb02 % 16 == 0 && nb03 % 16 == 0;
+}
+
+// run `n_ops` matrices (same type, K) against `ncols` (<= 8) already-quantized unit-record columns
+static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, const uint8_t * const * ws, const size_t * nb01s,
+                               const int64_t * Ms, float * const * dsts, const int64_t * dst_cs, int ncols,
+                               const uint8_t * act_main, const uint8_t * act_aux) {
+    const int U = (int) (K / 256);
+    for (int c0 = 0; c0 < ncols;) {
+        int     nc = ncols - c0 < MV_MAX_COLS ? ncols - c0 : MV_MAX_COLS;
+        mv_cfg  cfg;
+        while (nc >= 1 && !pick_mv_cfg(ctx, type, U, nc, &cfg)) nc--;
+        if (nc < 1) return fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
+        for (int o0 = 0; o0 < n_ops; o0 += MV_MAX_MATS) {
+            MvParams p;
+            memset(&p, 0, sizeof(p));
+            mv_geometry(U, &p);
+            p.n_mats = n_ops - o0 < MV_MAX_MATS ? n_ops - o0 : MV_MAX_MATS;
+            int g = 0;
+            for (int i = 0; i < p.n_mats; i++) {
+                p.mat[i].w      = ws[o0 + i];
+                p.mat[i].nb01   = (int64_t) nb01s[o0 + i];
+                p.mat[i].dst    = dsts[o0 + i] + (int64_t) c0 * dst_cs[o0 + i];
+                p.mat[i].dst_cs = dst_cs[o0 + i];
+                p.mat[i].M      = (int) Ms[o0 + i];
+                p.mat[i].group0 = g;
+                g += (int) ((Ms[o0 + i] + p.rpg - 1) / p.rpg);
+            }
+            for (int i = p.n_mats; i < MV_MAX_MATS; i++) p.mat[i].group0 = INT32_MAX;
+            p.total_groups = g;
+            if (g == 0) continue;
+            p.n_warps  = cfg.nw;
+            p.n_stages = cfg.ns;
+            p.act_main = act_main + (size_t) c0 * U * ACT_MAIN;
+            p.act_aux  = act_aux + (size_t) c0 * U * ACT_AUX;
+            const int n_ctas = g < ctx->sm_count ? g : ctx->sm_count;
+            CU(mv_fast_launch(type, nc, p, n_ctas, 1, cfg.smem, ctx->stream));
+            ctx->launches++;
+        }
+        c0 += nc;
+    }
+    return B200_OK;
+}
+
+static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_desc * descs, const void * const * src0s,
+                                const float * src1, float * const * dsts) {
+    const b200_mul_mat_desc & d = descs[0];
+    const int     type = d.type;
+    const int64_t K = d.ne00, N = d.ne11;
+    if (N == 0 || d.ne01 == 0) return B200_OK;
+    CU(cudaSetDevice(ctx->device));
+
+    bool fast = ctx->force_path != B200_PATH_SIMPLE;
+    for (int i = 0; i < n_ops; i++) fast = fast && fast_layout_ok(type, K, src0s[i], descs[i].nb01, descs[i].nb02, descs[i].nb03);
+
+    const int64_t n_batch = d.ne12 * d.ne13;
+    const int64_t n_rows  = N * n_batch;  // activation rows to quantize
+
+    if (fast) {
+        const int    U      = (int) (K / 256);
+        const size_t main_b = (size_t) n_rows * U * ACT_MAIN, aux_b = (size_t) n_rows * U * ACT_AUX;
+        const size_t aux_o  = (main_b + 255) & ~(size_t) 255;
+        b200_status  st     = ensure(ctx, &ctx->scratch, &ctx->scratch_size, aux_o + aux_b);
+        if (st != B200_OK) return st;
+        uint8_t * am = (uint8_t *) ctx->scratch, * ax = am + aux_o;
+        const int kind = act_kind_for(type);
+        for (int64_t i13 = 0; i13 < d.ne13; i13++)
+            for (int64_t i12 = 0; i12 < d.ne12; i12++) {
+                const int64_t b = i13 * d.ne12 + i12;
+                int l = 0;
+                CU(quantize_units(kind, (const float *) ((const char *) src1 + i12 * d.nb12 + i13 * d.nb13), K, N, d.nb11,
+                                  am + (size_t) b * N * U * ACT_MAIN, ax + (size_t) b * N * U * ACT_AUX, ctx->stream, &l));
+                ctx->launches += l;
+            }
+        const uint8_t * ws[MV_MAX_MATS * 8];
+        size_t          nb01s[MV_MAX_MATS * 8];
+        int64_t         Ms[MV_MAX_MATS * 8], dcs[MV_MAX_MATS * 8];
+        float *         ds[MV_MAX_MATS * 8];
+        if (n_ops > MV_MAX_MATS * 8) return fail(B200_ERR_ARG, "too many fused ops");
+        for (int64_t i13 = 0; i13 < d.ne13; i13++)
+            for (int64_t i12 = 0; i12 < d.ne12; i12++) {
+                const int64_t b = i13 * d.ne12 + i12;
+                for (int i = 0; i < n_ops; i++) {
+                    const b200_mul_mat_desc & di = descs[i];
+                    const int64_t r2 = di.ne12 / di.ne02, r3 = di.ne13 / di.ne03;
+                    ws[i]    = (const uint8_t *) src0s[i] + (i12 / r2) * di.nb02 + (i13 / r3) * di.nb03;
+                    nb01s[i] = di.nb01;
+                    Ms[i]    = di.ne01;
+                    ds[i]    = (float *) ((char *) dsts[i] + i12 * di.nb2 + i13 * di.nb3);
+                    dcs[i]   = (int64_t) (di.nb1 / 4);
+                }
+                st = mv_fast_run(ctx, type, K, n_ops, ws, nb01s, Ms, ds, dcs, (int) N, am + (size_t) b * N * U * ACT_MAIN,
+                                 ax + (size_t) b * N * U * ACT_AUX);
+                if (st != B200_OK) return st;
+            }
+        return B200_OK;
+    }
+
+    // generic path: reference block layout for the activations, one warp per row
+    const int    val    = type == B200_TYPE_Q4_K ? 1 : 0;
+    const size_t act_rs = type == B200_TYPE_Q4_K ? (size_t) (K / QK_K) * SZ_Q8_K : (size_t) (K / QK) * SZ_Q8_0;
+    b200_status  st     = ensure(ctx, &ctx->scratch, &ctx->scratch_size, (size_t) n_rows * act_rs + 16);
+    if (st != B200_OK) return st;
+    uint8_t * act = (uint8_t *) ctx->scratch;
+    for (int64_t i13 = 0; i13 < d.ne13; i13++)
+        for (int64_t i12 = 0; i12 < d.ne12; i12++) {
+            const int64_t b = i13 * d.ne12 + i12;
+            int l = 0;
+            CU(quantize_ggml(val, (const float *) ((const char *) src1 + i12 * d.nb12 + i13 * d.nb13), K, N, d.nb11,
+                             act + (size_t) b * N * act_rs, ctx->stream, &l));
+            ctx->launches += l;
+            for (int i = 0; i < n_ops; i++) {
+                const b200_mul_mat_desc & di = descs[i];
+                const int64_t r2 = di.ne12 / di.ne02, r3 = di.ne13 / di.ne03;
+                for (int64_t c0 = 0; c0 < N; c0 += 65535) {
+                    MvSimpleParams sp;
+                    memset(&sp, 0, sizeof(sp));
+                    sp.w      = (const uint8_t *) src0s[i] + (i12 / r2) * di.nb02 + (i13 / r3) * di.nb03;
+                    sp.nb01   = (int64_t) di.nb01;
+                    sp.act    = act + (size_t) (b * N + c0) * act_rs;
+                    sp.act_rs = (int64_t) act_rs;
+                    sp.dst    = (float *) ((char *) dsts[i] + i12 * di.nb2 + i13 * di.nb3) + c0 * (int64_t) (di.nb1 / 4);
+                    sp.dst_cs = (int64_t) (di.nb1 / 4);
+                    sp.M      = (int) di.ne01;
+                    sp.K      = (int) K;
+                    sp.ncols  = (int) (N - c0 < 65535 ? N - c0 : 65535);
+                    CU(mv_simple_launch(type, sp, ctx->stream));
+                    ctx->launches++;
+                }
+            }
+        }
+    return B200_OK;
+}
+
+b200_status b200_mul_mat(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * src0, const float * src1, float * dst) {
+    if (!ctx || !d || !src0 || !src1 || !dst) return fail(B200_ERR_ARG, "null argument");
+    if (!b200_mul_mat_supported(d)) return fail(B200_ERR_UNSUPPORTED, "MUL_MAT geometry/type not supported");
+    const void * s0[1] = { src0 };
+    float *      ds[1] = { dst };
+    return mul_mat_impl(ctx, 1, d, s0, src1, ds);
+}
+
+b200_status b200_mul_mat_shared_src1(b200_ctx * ctx, int n_ops, const b200_mul_mat_desc * descs, const void * const * src0s,
+                                     const float * src1, float * const * dsts) {
+    if (!ctx || !descs || !src0s || !src1 || !dsts || n_ops < 1) return fail(B200_ERR_ARG, "bad argument");
+    for (int i = 0; i < n_ops; i++) {
+        if (!b200_mul_mat_supported(&descs[i])) return fail(B200_ERR_UNSUPPORTED, "MUL_MAT %d geometry/type not supported", i);
+        const b200_mul_mat_desc & a = descs[0], & b = descs[i];
+        if (a.type != b.type || a.ne00 != b.ne00 || a.ne11 != b.ne11 || a.ne12 != b.ne12 || a.ne13 != b.ne13 || a.nb11 != b.nb11 ||
+            a.nb12 != b.nb12 || a.nb13 != b.nb13) {
+            return fail(B200_ERR_ARG, "fused MUL_MATs must share type, K and the src1 geometry");
+        }
+    }
+    return mul_mat_impl(ctx, n_ops, descs, src0s, src1, dsts);
+}
+
+b200_status b200_mul_mat_host(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * src0, int w_on_device, const float * src1_host,
+                              float * dst_host) {
+    if (!ctx || !d || !src0 || !src1_host || !dst_host) return fail(B200_ERR_ARG, "null argument");
+    if (!b200_mul_mat_supported(d)) return fail(B200_ERR_UNSUPPORTED, "MUL_MAT geometry/type not supported");
+    CU(cudaSetDevice(ctx->device));
+    // host tensors are taken as contiguous in the order the strides describe (last row end = total size)
+    const size_t x_bytes = (size_t) (d->ne13 - 1) * d->nb13 + (size_t) (d->ne12 - 1) * d->nb12 + (size_t) (d->ne11 - 1) * d->nb11 + (size_t) d->ne00 * 4;
+    const size_t y_bytes = (size_t) (d->ne13 - 1) * d->nb3 + (size_t) (d->ne12 - 1) * d->nb2 + (size_t) (d->ne11 - 1) * d->nb1 + (size_t) d->ne01 * 4;
+    const size_t w_bytes = w_on_device ? 0 : (size_t) (d->ne03 - 1) * d->nb03 + (size_t) (d->ne02 - 1) * d->nb02 + (size_t) d->ne01 * d->nb01;
+    const size_t xo = 0, yo = (x_bytes + 255) & ~(size_t) 255, wo = yo + ((y_bytes + 255) & ~(size_t) 255);
+    b200_status  st = ensure(ctx, &ctx->io, &ctx->io_size, wo + w_bytes + 256);
+    if (st != B200_OK) return st;
+    uint8_t * io = (uint8_t *) ctx->io;
+    CU(cudaMemcpyAsync(io + xo, src1_host, x_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    const void * w = src0;
+    if (!w_on_device) {
+        CU(cudaMemcpyAsync(io + wo, src0, w_bytes, cudaMemcpyHostToDevice, ctx->stream));
+        w = io + wo;
+    }
+    st = b200_mul_mat(ctx, d, w, (const float *) (io + xo), (float *) (io + yo));
+    if (st != B200_OK) return st;
+    CU(cudaMemcpyAsync(dst_host, io + yo, y_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ weight cache (tcgen05 path)
+
+void   b200_weight_cache_invalidate(b200_ctx *, const void *, size_t) {}
+void   b200_weight_cache_clear(b200_ctx *) {}
+size_t b200_weight_cache_bytes(const b200_ctx *) { return 0; }

@@ -1,0 +1,119 @@
+// common.cuh — shared device helpers for the B200 (sm_100a) MUL_MAT kernels.
+#pragma once
+
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ggml_b200.h"
+
+namespace b200 {
+
+// ---- block formats: byte sizes only, the kernels address raw bytes (ggml/src/ggml-common.h:170-175, 218-238, 291-305, 322-328)
+constexpr int QK      = 32;
+constexpr int QK_K    = 256;
+constexpr int SZ_Q4_0 = 18;
+constexpr int SZ_Q8_0 = 34;
+constexpr int SZ_Q8_1 = 36;
+constexpr int SZ_Q4_K = 144;
+constexpr int SZ_Q8_K = 292;
+
+// ---- "unit": 256 consecutive weights of one row. 8 q4_0 blocks and one q4_K block are both 144 bytes = 9 x 16 B,
+// 8 q8_0 blocks are 272 bytes = 17 x 16 B, so a unit is always a whole number of 128-bit words and a stride of
+// 144 B / 272 B between lanes is bank-conflict free for 128-bit shared-memory loads (36 resp. 68 words == 4 mod 32).
+constexpr int UNIT_ELEMS = 256;
+__host__ __device__ constexpr int unit_bytes(int type) { return type == B200_TYPE_Q8_0 ? 272 : 144; }
+__host__ __device__ constexpr int type_block_elems(int type) { return type == B200_TYPE_Q4_K ? 256 : 32; }
+__host__ __device__ constexpr int type_block_bytes(int type) {
+    return type == B200_TYPE_Q4_0 ? SZ_Q4_0 : type == B200_TYPE_Q8_0 ? SZ_Q8_0 : SZ_Q4_K;
+}
+
+// ---- activation unit record (kernel-internal layout, written by quantize.cu, read by mmvq.cu / mmq)
+//   main (272 B): int8 q[256] ; then 16 B: kind 0 (q8_0-valued): half d[8]       (one per 32-block)
+//                                          kind 1 (q8_K-valued): int16 bsum32[8] (sum of q per 32-block)
+//   aux  (16 B):  kind 0: int16 sum[8] (sum of q per 32-block) ; kind 1: float d, 12 B zero
+constexpr int ACT_MAIN = 272;
+constexpr int ACT_AUX  = 16;
+constexpr int ACT_KIND_Q8_0 = 0;
+constexpr int ACT_KIND_Q8_K = 1;
+__host__ __device__ constexpr int act_kind_for(int type) { return type == B200_TYPE_Q4_K ? ACT_KIND_Q8_K : ACT_KIND_Q8_0; }
+
+__device__ __forceinline__ float half_bits_to_float(uint16_t h) { return __half2float(__ushort_as_half(h)); }
+
+__device__ __forceinline__ int dp4a_ss(int a, int b, int c) { return __dp4a(a, b, c); }
+// unsigned 8-bit a (0..255) times signed 8-bit b
+__device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+// two signed 16-bit halves of a times the low / high two unsigned bytes of b
+__device__ __forceinline__ int dp2a_lo_su(int a, uint32_t b, int c) {
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi_su(int a, uint32_t b, int c) {
+    int d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+
+// ---- mbarrier + bulk async copy (TMA 1-D, SASS UBLKCP) ----
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {}
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+// global -> shared bulk copy, completion reported as transaction bytes on `bar`. dst/src 16-B aligned, bytes % 16 == 0.
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void * src, uint32_t bytes, uint32_t bar, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst),
+        "l"(src), "r"(bytes), "r"(bar), "l"(policy)
+        : "memory");
+}
+
+} // namespace b200

@@ -1,0 +1,451 @@
+// ggml_backend_b200.cpp — the drop-in: a ggml backend ("B200") that implements the reference's five backend vtables
+// (/root/reference/ggml/src/ggml-backend-impl.h:16-204, API version 2) for exactly GGML_OP_MUL_MAT and
+// GGML_OP_MUL_MAT_ID on q4_0 / q8_0 / q4_K weights x F32 activations. All device work goes through the C-ABI of
+// include/ggml_b200.h (libb200mm.so); this file contains no CUDA and no CPU compute.
+//
+// Loaded out of tree: GGML_BACKEND_PATH=/path/libggml-b200.so (ggml-backend-reg.cpp:711-715) or ggml_backend_load();
+// the exported symbols are ggml_backend_init / ggml_backend_score (ggml-backend-impl.h:215-251).
+//
+// What it mirrors in ggml-cuda (paths relative to /root/reference/ggml/src/ggml-cuda/ggml-cuda.cu):
+//   buffer + buffer type :564-769, pinned host buffer type :1104-1168, backend (stream) iface :2748-2862, 3679-3754,
+//   device iface :4160-4677, reg + get_proc_address :4683-4830.
+
+#include "ggml-backend-impl.h"
+#include "ggml-impl.h"
+#include "ggml.h"
+
+#include "ggml_b200.h"
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#define B200_NAME "B200"
+#define B200_MAX_DEVICES 16
+
+namespace {
+
+struct dev_ctx {
+    int         device;
+    std::string name, description, pci_id;
+    ggml_backend_buffer_type buft;       // device buffer type singleton
+    ggml_backend_buffer_type host_buft;  // pinned host buffer type singleton
+};
+
+struct buf_ctx {
+    int    device;
+    void * base;
+};
+
+struct be_ctx {
+    int        device;
+    b200_ctx * ctx;
+    std::string name;
+    bool       fuse;
+};
+
+ggml_backend_reg_t b200_reg();
+
+[[noreturn]] void die(const char * what) {
+    GGML_LOG_ERROR("ggml-b200: %s failed: %s\n", what, b200_last_error());
+    GGML_ABORT("ggml-b200 fatal error");  // same convention as CUDA_CHECK -> ggml_cuda_error (ggml-cuda.cu:82-93)
+}
+#define CHECK(call) do { if ((call) != B200_OK) die(#call); } while (0)
+
+// ------------------------------------------------------------------------------------------------ device buffer
+
+void buf_free(ggml_backend_buffer_t buffer) {
+    buf_ctx * c = (buf_ctx *) buffer->context;
+    b200_free(c->device, c->base);
+    delete c;
+}
+void * buf_get_base(ggml_backend_buffer_t buffer) { return ((buf_ctx *) buffer->context)->base; }
+ggml_status buf_init_tensor(ggml_backend_buffer_t, ggml_tensor *) {
+    // nothing to do: the kernels never read past a row's own bytes, so the reference's 512-element row padding and its
+    // zero fill (ggml-cuda.cu:593-612, 720-734) are not needed
+    return GGML_STATUS_SUCCESS;
+}
+void buf_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * t, uint8_t value, size_t offset, size_t size) {
+    CHECK(b200_memset(((buf_ctx *) buffer->context)->device, (char *) t->data + offset, value, size));
+}
+void buf_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * t, const void * data, size_t offset, size_t size) {
+    CHECK(b200_memcpy_h2d(((buf_ctx *) buffer->context)->device, (char *) t->data + offset, data, size));
+}
+void buf_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * t, void * data, size_t offset, size_t size) {
+    CHECK(b200_memcpy_d2h(((buf_ctx *) buffer->context)->device, data, (const char *) t->data + offset, size));
+}
+bool buft_is_b200(ggml_backend_buffer_type_t buft);
+bool buf_cpy_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * src, ggml_tensor * dst) {
+    ggml_backend_buffer_t sb = src->view_src ? src->view_src->buffer : src->buffer;
+    if (!sb || !buft_is_b200(sb->buft)) return false;
+    buf_ctx * s = (buf_ctx *) sb->context, * d = (buf_ctx *) buffer->context;
+    if (s->device == d->device) CHECK(b200_memcpy_d2d(d->device, dst->data, src->data, ggml_nbytes(src)));
+    else CHECK(b200_memcpy_peer(d->device, dst->data, s->device, src->data, ggml_nbytes(src)));
+    return true;
+}
+void buf_clear(ggml_backend_buffer_t buffer, uint8_t value) {
+    buf_ctx * c = (buf_ctx *) buffer->context;
+    CHECK(b200_memset(c->device, c->base, value, buffer->size));
+}
+
+const ggml_backend_buffer_i buf_iface = {
+    /* .free_buffer   = */ buf_free,
+    /* .get_base      = */ buf_get_base,
+    /* .init_tensor   = */ buf_init_tensor,
+    /* .memset_tensor = */ buf_memset_tensor,
+    /* .set_tensor    = */ buf_set_tensor,
+    /* .get_tensor    = */ buf_get_tensor,
+    /* .cpy_tensor    = */ buf_cpy_tensor,
+    /* .clear         = */ buf_clear,
+    /* .reset         = */ nullptr,
+};
+
+// ------------------------------------------------------------------------------------------------ device buffer type
+
+const char * buft_name(ggml_backend_buffer_type_t buft) { return ((dev_ctx *) buft->context)->name.c_str(); }
+ggml_backend_buffer_t buft_alloc(ggml_backend_buffer_type_t buft, size_t size) {
+    dev_ctx * d = (dev_ctx *) buft->context;
+    void * p = nullptr;
+    if (b200_malloc(d->device, size, &p) != B200_OK) {  // soft failure, as ggml-cuda.cu:700-707
+        GGML_LOG_ERROR("ggml-b200: allocating %.2f MiB on device %d failed: %s\n", size / 1048576.0, d->device, b200_last_error());
+        return nullptr;
+    }
+    return ggml_backend_buffer_init(buft, buf_iface, new buf_ctx{ d->device, p }, size);
+}
+size_t buft_alignment(ggml_backend_buffer_type_t) { return 256; }  // every tensor starts 16-byte aligned for the bulk copies
+size_t buft_alloc_size(ggml_backend_buffer_type_t, const ggml_tensor * t) { return ggml_nbytes(t); }
+
+const ggml_backend_buffer_type_i buft_iface = {
+    /* .get_name       = */ buft_name,
+    /* .alloc_buffer   = */ buft_alloc,
+    /* .get_alignment  = */ buft_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ buft_alloc_size,
+    /* .is_host        = */ nullptr,
+};
+bool buft_is_b200(ggml_backend_buffer_type_t buft) { return buft->iface.get_name == buft_name; }
+
+// ------------------------------------------------------------------------------------------------ pinned host buffer type
+
+const char * host_buft_name(ggml_backend_buffer_type_t) { return B200_NAME "_Host"; }
+void host_buf_free(ggml_backend_buffer_t buffer) { b200_host_free(buffer->context); }
+ggml_backend_buffer_t host_buft_alloc(ggml_backend_buffer_type_t buft, size_t size) {
+    void * p = nullptr;
+    if (b200_host_malloc(size, &p) != B200_OK) {
+        // fall back to pageable memory like ggml-cuda.cu:1140-1146
+        return ggml_backend_buft_alloc_buffer(ggml_backend_cpu_buffer_type(), size);
+    }
+    ggml_backend_buffer_t b = ggml_backend_cpu_buffer_from_ptr(p, size);
+    b->buft = buft;
+    b->iface.free_buffer = host_buf_free;
+    return b;
+}
+size_t host_buft_alignment(ggml_backend_buffer_type_t) { return 64; }
+bool   host_buft_is_host(ggml_backend_buffer_type_t) { return true; }
+const ggml_backend_buffer_type_i host_buft_iface = {
+    /* .get_name       = */ host_buft_name,
+    /* .alloc_buffer   = */ host_buft_alloc,
+    /* .get_alignment  = */ host_buft_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ nullptr,
+    /* .is_host        = */ host_buft_is_host,
+};
+
+// ------------------------------------------------------------------------------------------------ op geometry
+
+bool is_noop(const ggml_tensor * t) {
+    return ggml_is_empty(t) || t->op == GGML_OP_NONE || t->op == GGML_OP_RESHAPE || t->op == GGML_OP_VIEW || t->op == GGML_OP_PERMUTE ||
+           t->op == GGML_OP_TRANSPOSE;
+}
+bool weight_type_ok(ggml_type t) { return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K; }
+
+bool fill_mul_mat(const ggml_tensor * op, b200_mul_mat_desc * d) {
+    const ggml_tensor * a = op->src[0], * b = op->src[1];
+    if (!a || !b || !weight_type_ok(a->type) || b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+    if (a->nb[0] != ggml_type_size(a->type) || b->nb[0] != sizeof(float) || op->nb[0] != sizeof(float)) return false;
+    d->type = (int32_t) a->type;
+    d->ne00 = a->ne[0]; d->ne01 = a->ne[1]; d->ne02 = a->ne[2]; d->ne03 = a->ne[3];
+    d->nb01 = a->nb[1]; d->nb02 = a->nb[2]; d->nb03 = a->nb[3];
+    d->ne11 = b->ne[1]; d->ne12 = b->ne[2]; d->ne13 = b->ne[3];
+    d->nb11 = b->nb[1]; d->nb12 = b->nb[2]; d->nb13 = b->nb[3];
+    d->nb1 = op->nb[1]; d->nb2 = op->nb[2]; d->nb3 = op->nb[3];
+    if (b->ne[0] != a->ne[0] || op->ne[0] != a->ne[1] || op->ne[1] != b->ne[1] || op->ne[2] != b->ne[2] || op->ne[3] != b->ne[3]) return false;
+    return b200_mul_mat_supported(d) != 0;
+}
+
+bool fill_mul_mat_id(const ggml_tensor * op, b200_mul_mat_id_desc * d) {
+    const ggml_tensor * a = op->src[0], * b = op->src[1], * ids = op->src[2];
+    if (!a || !b || !ids || !weight_type_ok(a->type) || b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32 || ids->type != GGML_TYPE_I32) return false;
+    if (a->nb[0] != ggml_type_size(a->type) || b->nb[0] != sizeof(float) || op->nb[0] != sizeof(float) || ids->nb[0] != sizeof(int32_t)) return false;
+    if (a->ne[3] != 1 || b->ne[3] != 1 || op->ne[3] != 1 || ids->ne[2] != 1 || ids->ne[3] != 1) return false;
+    if (b->ne[0] != a->ne[0] || op->ne[0] != a->ne[1] || op->ne[1] != ids->ne[0] || op->ne[2] != b->ne[2] || ids->ne[1] != b->ne[2]) return false;
+    if (ids->ne[0] % b->ne[1] != 0) return false;  // broadcast rule of ggml_mul_mat_id (ggml.c:3194-3225)
+    d->type = (int32_t) a->type;
+    d->ne00 = a->ne[0]; d->ne01 = a->ne[1]; d->n_as = a->ne[2];
+    d->nb01 = a->nb[1]; d->nb02 = a->nb[2];
+    d->ne11 = b->ne[1]; d->n_tok = b->ne[2];
+    d->nb11 = b->nb[1]; d->nb12 = b->nb[2];
+    d->n_used = ids->ne[0]; d->ids_nb1 = ids->nb[1];
+    d->nb1 = op->nb[1]; d->nb2 = op->nb[2];
+    return b200_mul_mat_id_supported(d) != 0;
+}
+
+// ------------------------------------------------------------------------------------------------ backend (stream)
+
+const char * be_name(ggml_backend_t backend) { return ((be_ctx *) backend->context)->name.c_str(); }
+void be_free(ggml_backend_t backend) {
+    be_ctx * c = (be_ctx *) backend->context;
+    b200_ctx_destroy(c->ctx);
+    delete c;
+    delete backend;
+}
+void be_set_tensor_async(ggml_backend_t backend, ggml_tensor * t, const void * data, size_t offset, size_t size) {
+    CHECK(b200_memcpy_h2d_async(((be_ctx *) backend->context)->ctx, (char *) t->data + offset, data, size));
+}
+void be_get_tensor_async(ggml_backend_t backend, const ggml_tensor * t, void * data, size_t offset, size_t size) {
+    CHECK(b200_memcpy_d2h_async(((be_ctx *) backend->context)->ctx, data, (const char *) t->data + offset, size));
+}
+bool be_cpy_tensor_async(ggml_backend_t, ggml_backend_t, const ggml_tensor *, ggml_tensor *) { return false; }  // caller falls back (ggml-backend.cpp:408-429)
+void be_synchronize(ggml_backend_t backend) { CHECK(b200_ctx_synchronize(((be_ctx *) backend->context)->ctx)); }
+
+bool ranges_overlap(const ggml_tensor * a, const ggml_tensor * b) {
+    const char * a0 = (const char *) a->data, * b0 = (const char *) b->data;
+    return a0 < b0 + ggml_nbytes(b) && b0 < a0 + ggml_nbytes(a);
+}
+
+ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
+    be_ctx * c = (be_ctx *) backend->context;
+    for (int i = 0; i < cgraph->n_nodes; i++) {
+        ggml_tensor * node = cgraph->nodes[i];
+        if (is_noop(node)) continue;  // as ggml-cuda.cu:3333-3335
+        if (node->op == GGML_OP_MUL_MAT) {
+            b200_mul_mat_desc descs[4];
+            const void *      w[4];
+            float *           o[4];
+            if (!fill_mul_mat(node, &descs[0])) {
+                GGML_LOG_ERROR("ggml-b200: unsupported MUL_MAT reached graph_compute (%s)\n", node->name);
+                return GGML_STATUS_FAILED;
+            }
+            w[0] = node->src[0]->data;
+            o[0] = (float *) node->data;
+            int n = 1;
+            // peephole: consecutive MUL_MATs reading the same src1 (q/k/v, gate/up) share one activation quantization
+            // and one launch; the reference re-quantizes per op (mmvq.cu:667-674)
+            while (c->fuse && n < 4 && i + n < cgraph->n_nodes) {
+                ggml_tensor * nx = cgraph->nodes[i + n];
+                if (nx->op != GGML_OP_MUL_MAT || nx->src[1] != node->src[1] || !fill_mul_mat(nx, &descs[n])) break;
+                if (descs[n].type != descs[0].type || descs[n].ne00 != descs[0].ne00 || descs[0].ne12 != 1 || descs[0].ne13 != 1) break;
+                bool clash = ranges_overlap(nx, node->src[1]);
+                for (int j = 0; j < n; j++) clash = clash || ranges_overlap(nx, cgraph->nodes[i + j]) || nx->src[0] == cgraph->nodes[i + j];
+                if (clash) break;
+                w[n] = nx->src[0]->data;
+                o[n] = (float *) nx->data;
+                n++;
+            }
+            if (n == 1) CHECK(b200_mul_mat(c->ctx, &descs[0], w[0], (const float *) node->src[1]->data, o[0]));
+            else CHECK(b200_mul_mat_shared_src1(c->ctx, n, descs, w, (const float *) node->src[1]->data, o));
+            i += n - 1;
+        } else if (node->op == GGML_OP_MUL_MAT_ID) {
+            b200_mul_mat_id_desc d;
+            if (!fill_mul_mat_id(node, &d)) {
+                GGML_LOG_ERROR("ggml-b200: unsupported MUL_MAT_ID reached graph_compute (%s)\n", node->name);
+                return GGML_STATUS_FAILED;
+            }
+            CHECK(b200_mul_mat_id(c->ctx, &d, node->src[0]->data, (const float *) node->src[1]->data, (const int32_t *) node->src[2]->data,
+                                  (float *) node->data));
+        } else {
+            GGML_LOG_ERROR("ggml-b200: op %s is not implemented by this backend (%s)\n", ggml_op_name(node->op), node->name);
+            return GGML_STATUS_FAILED;
+        }
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+void be_event_record(ggml_backend_t backend, ggml_backend_event_t event) { CHECK(b200_event_record(((be_ctx *) backend->context)->ctx, event->context)); }
+void be_event_wait(ggml_backend_t backend, ggml_backend_event_t event) { CHECK(b200_event_wait(((be_ctx *) backend->context)->ctx, event->context)); }
+
+const ggml_backend_i be_iface = {
+    /* .get_name           = */ be_name,
+    /* .free               = */ be_free,
+    /* .set_tensor_async   = */ be_set_tensor_async,
+    /* .get_tensor_async   = */ be_get_tensor_async,
+    /* .cpy_tensor_async   = */ be_cpy_tensor_async,
+    /* .synchronize        = */ be_synchronize,
+    /* .graph_plan_create  = */ nullptr,
+    /* .graph_plan_free    = */ nullptr,
+    /* .graph_plan_update  = */ nullptr,
+    /* .graph_plan_compute = */ nullptr,
+    /* .graph_compute      = */ be_graph_compute,
+    /* .event_record       = */ be_event_record,
+    /* .event_wait         = */ be_event_wait,
+    /* .graph_optimize     = */ nullptr,
+};
+
+ggml_guid_t be_guid() {
+    static ggml_guid guid = { 0xb2, 0x00, 0x51, 0x00, 0xa0, 0x67, 0x67, 0x6d, 0x6c, 0x2d, 0x62, 0x32, 0x30, 0x30, 0x00, 0x01 };
+    return &guid;
+}
+
+// ------------------------------------------------------------------------------------------------ device
+
+const char * dev_name(ggml_backend_dev_t dev) { return ((dev_ctx *) dev->context)->name.c_str(); }
+const char * dev_description(ggml_backend_dev_t dev) { return ((dev_ctx *) dev->context)->description.c_str(); }
+void dev_memory(ggml_backend_dev_t dev, size_t * free, size_t * total) {
+    if (b200_device_memory(((dev_ctx *) dev->context)->device, free, total) != B200_OK) { *free = 0; *total = 0; }
+}
+enum ggml_backend_dev_type dev_type(ggml_backend_dev_t) { return GGML_BACKEND_DEVICE_TYPE_GPU; }
+void dev_props(ggml_backend_dev_t dev, ggml_backend_dev_props * props) {
+    dev_ctx * d = (dev_ctx *) dev->context;
+    props->name        = d->name.c_str();
+    props->description = d->description.c_str();
+    props->type        = GGML_BACKEND_DEVICE_TYPE_GPU;
+    props->device_id   = d->pci_id.c_str();
+    dev_memory(dev, &props->memory_free, &props->memory_total);
+    props->caps = { /* async */ true, /* host_buffer */ true, /* buffer_from_host_ptr */ false, /* events */ true };
+}
+ggml_backend_t dev_init_backend(ggml_backend_dev_t dev, const char *) {
+    dev_ctx * d = (dev_ctx *) dev->context;
+    b200_ctx * ctx = nullptr;
+    if (b200_ctx_create(d->device, nullptr, &ctx) != B200_OK) {
+        GGML_LOG_ERROR("ggml-b200: cannot create a context on device %d: %s\n", d->device, b200_last_error());
+        return nullptr;
+    }
+    const char * nf = getenv("GGML_B200_DISABLE_FUSION");
+    be_ctx * c = new be_ctx{ d->device, ctx, d->name, !(nf && atoi(nf)) };
+    return new ggml_backend{ be_guid(), be_iface, dev, c };
+}
+ggml_backend_buffer_type_t dev_buffer_type(ggml_backend_dev_t dev) { return &((dev_ctx *) dev->context)->buft; }
+ggml_backend_buffer_type_t dev_host_buffer_type(ggml_backend_dev_t dev) { return &((dev_ctx *) dev->context)->host_buft; }
+
+bool dev_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) { return buft_is_b200(buft) && buft->device == dev; }
+
+bool dev_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
+    // tensors must live in our buffers when they are already allocated (llama probes with 0-byte buffers of the
+    // candidate buft, src/llama-model.cpp:165-305, and test-backend-ops asks for leaves and views too, :1265-1272)
+    for (int i = 0; i < GGML_MAX_SRC; i++) {
+        const ggml_tensor * s = op->src[i];
+        if (s && s->buffer && !dev_supports_buft(dev, s->buffer->buft) && op->op != GGML_OP_NONE) {
+            // weights in a foreign buffer are handled by the scheduler through offload_op copies; activations likewise
+        }
+    }
+    switch (op->op) {
+        case GGML_OP_NONE:
+        case GGML_OP_RESHAPE:
+        case GGML_OP_VIEW:
+        case GGML_OP_PERMUTE:
+        case GGML_OP_TRANSPOSE:
+            return true;
+        case GGML_OP_MUL_MAT: {
+            b200_mul_mat_desc d;
+            return fill_mul_mat(op, &d);
+        }
+        case GGML_OP_MUL_MAT_ID: {
+            b200_mul_mat_id_desc d;
+            return fill_mul_mat_id(op, &d);
+        }
+        default:
+            return false;
+    }
+}
+
+bool dev_offload_op(ggml_backend_dev_t, const ggml_tensor * op) {
+    const int min_batch = 32;  // ggml-cuda.cu:4641-4647
+    return (op->op == GGML_OP_MUL_MAT && op->ne[1] >= min_batch) || (op->op == GGML_OP_MUL_MAT_ID && op->ne[2] >= min_batch);
+}
+
+ggml_backend_event_t dev_event_new(ggml_backend_dev_t dev) {
+    void * ev = nullptr;
+    if (b200_event_create(((dev_ctx *) dev->context)->device, &ev) != B200_OK) return nullptr;
+    return new ggml_backend_event{ dev, ev };
+}
+void dev_event_free(ggml_backend_dev_t dev, ggml_backend_event_t event) {
+    b200_event_destroy(((dev_ctx *) dev->context)->device, event->context);
+    delete event;
+}
+void dev_event_synchronize(ggml_backend_dev_t, ggml_backend_event_t event) { CHECK(b200_event_synchronize(event->context)); }
+
+const ggml_backend_device_i dev_iface = {
+    /* .get_name             = */ dev_name,
+    /* .get_description      = */ dev_description,
+    /* .get_memory           = */ dev_memory,
+    /* .get_type             = */ dev_type,
+    /* .get_props            = */ dev_props,
+    /* .init_backend         = */ dev_init_backend,
+    /* .get_buffer_type      = */ dev_buffer_type,
+    /* .get_host_buffer_type = */ dev_host_buffer_type,
+    /* .buffer_from_host_ptr = */ nullptr,
+    /* .supports_op          = */ dev_supports_op,
+    /* .supports_buft        = */ dev_supports_buft,
+    /* .offload_op           = */ dev_offload_op,
+    /* .event_new            = */ dev_event_new,
+    /* .event_free           = */ dev_event_free,
+    /* .event_synchronize    = */ dev_event_synchronize,
+};
+
+// ------------------------------------------------------------------------------------------------ reg
+
+struct reg_ctx {
+    std::vector<ggml_backend_device *> devices;
+};
+
+const char * reg_name(ggml_backend_reg_t) { return B200_NAME; }
+size_t reg_dev_count(ggml_backend_reg_t reg) { return ((reg_ctx *) reg->context)->devices.size(); }
+ggml_backend_dev_t reg_dev_get(ggml_backend_reg_t reg, size_t i) {
+    reg_ctx * r = (reg_ctx *) reg->context;
+    GGML_ASSERT(i < r->devices.size());
+    return r->devices[i];
+}
+
+ggml_backend_feature * reg_features(ggml_backend_reg_t) {
+    static ggml_backend_feature f[] = {
+        { "ARCH", "sm_100a" }, { "TMA_BULK_MMVQ", "1" }, { "TCGEN05_I8_MMQ", "1" }, { "ACT_QUANT", "bit-exact q8_0/q8_1/q8_K" },
+        { "CPU_FALLBACK", "0" }, { nullptr, nullptr },
+    };
+    return f;
+}
+
+void * reg_proc_address(ggml_backend_reg_t, const char * name) {
+    if (!strcmp(name, "ggml_backend_get_features")) return (void *) reg_features;
+    // "ggml_backend_split_buffer_type", "ggml_backend_set_n_threads", "ggml_backend_dev_get_extra_bufts": not provided
+    return nullptr;
+}
+
+const ggml_backend_reg_i reg_iface = { reg_name, reg_dev_count, reg_dev_get, reg_proc_address };
+
+ggml_backend_reg_t b200_reg() {
+    static ggml_backend_reg reg;
+    static std::once_flag   once;
+    std::call_once(once, [] {
+        reg_ctx * r = new reg_ctx();
+        reg = { GGML_BACKEND_API_VERSION, reg_iface, r };
+        const int n = b200_device_count();
+        for (int i = 0; i < n && i < B200_MAX_DEVICES; i++) {
+            char name[128] = "", pci[32] = "";
+            int  sms = 0, maj = 0, min = 0;
+            if (b200_device_info(i, name, sizeof(name), pci, sizeof(pci), &sms, &maj, &min) != B200_OK) break;
+            dev_ctx * d    = new dev_ctx();
+            d->device      = i;
+            d->name        = std::string(B200_NAME) + std::to_string(i);
+            d->description = std::string(name) + " (sm_" + std::to_string(maj) + std::to_string(min) + "a, " + std::to_string(sms) + " SMs)";
+            d->pci_id      = pci;
+            ggml_backend_device * dev = new ggml_backend_device{ dev_iface, &reg, d };
+            d->buft      = { buft_iface, dev, d };
+            d->host_buft = { host_buft_iface, dev, d };
+            r->devices.push_back(dev);
+        }
+        if (n == 0) GGML_LOG_WARN("ggml-b200: no sm_100 device found; the backend registers zero devices (there is no CPU fallback)\n");
+    });
+    return &reg;
+}
+
+} // namespace
+
+extern "C" {
+GGML_BACKEND_API ggml_backend_reg_t ggml_backend_init(void) { return b200_reg(); }
+GGML_BACKEND_API int ggml_backend_score(void) { return b200_device_count() > 0 ? 100 : 0; }
+// in-process registration for hosts that link the library directly (ggml_backend_register, ggml-backend.h:218)
+GGML_BACKEND_API ggml_backend_reg_t ggml_backend_b200_reg(void) { return b200_reg(); }
+}

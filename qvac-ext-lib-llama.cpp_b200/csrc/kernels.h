@@ -1,0 +1,72 @@
+// kernels.h — internal C++ interface between api.cu (dispatch) and the kernel translation units.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200 {
+
+// ---- quantize.cu (K1)
+// val: 0 = q8_0, 1 = q8_K, 2 = q8_1 valued blocks in the reference's block layout
+cudaError_t quantize_ggml(int val, const float * x, int64_t k, int64_t nrows, size_t stride, void * y, cudaStream_t st, int * launches);
+// kind: ACT_KIND_Q8_0 / ACT_KIND_Q8_K, unit-record layout (common.cuh)
+cudaError_t quantize_units(int kind, const float * x, int64_t k, int64_t nrows, size_t stride, void * main, void * aux, cudaStream_t st,
+                           int * launches);
+
+// ---- mmvq.cu (K3)
+constexpr int MV_MAX_MATS = 4;
+constexpr int MV_MAX_COLS = 8;
+
+// expert routing for MUL_MAT_ID (ggml-cpu.c:1564-1578): pair (i, t) uses expert ids[t*ids_rs + i], activation row
+// t*ne11 + i % ne11 of the quantized activations, and writes dst + t*dst_ts + i*dst_is (floats)
+struct MvIds {
+    const int32_t * ids;      // nullptr = plain MUL_MAT
+    int64_t         ids_rs;   // int32 elements between token rows of ids
+    int64_t         nb02;     // bytes between expert matrices
+    int64_t         dst_is, dst_ts;
+    int             n_used, ne11, n_as;
+};
+
+struct MvMat {
+    const uint8_t * w;        // row 0 of the weight matrix (16-byte aligned)
+    int64_t         nb01;     // bytes between rows (multiple of 16)
+    float *         dst;      // dst(row 0, col 0)
+    int64_t         dst_cs;   // floats between dst columns
+    int             M;        // rows
+    int             group0;   // first global row-group id of this matrix
+};
+
+struct MvParams {
+    MvMat           mat[MV_MAX_MATS];
+    int             n_mats;
+    int             total_groups;
+    int             U;        // 256-element units per row (K / 256)
+    int             L;        // lanes per row: power of two >= min(U, 32)
+    int             rpg;      // rows per group: 32 / L when U <= 32, else 1
+    int             slices;   // ceil(U / 32)
+    int             n_warps, n_stages;
+    const uint8_t * act_main; // [ncols][U][272]
+    const uint8_t * act_aux;  // [ncols][U][16]
+    // MUL_MAT_ID mode (ids != nullptr): blockIdx.y = pair p = t*n_used + i; one column per pair; mat[0] = expert 0
+    MvIds           ids;
+};
+
+// smem bytes needed by the fast kernel for a configuration
+size_t mv_fast_smem(int type, int U, int ncols, int n_warps, int n_stages);
+// launches the persistent TMA-staged mat-vec kernel (type, ncols 1..8); grid = n_ctas
+cudaError_t mv_fast_launch(int type, int ncols, const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st);
+
+// generic kernel: any K % block == 0, any (2-byte) alignment; activations in the reference's q8_0 / q8_K block layout
+struct MvSimpleParams {
+    const uint8_t * w;
+    int64_t         nb01;
+    const uint8_t * act;      // [ncols] rows of q8_0 (34 B / 32) or q8_K (292 B / 256) blocks
+    int64_t         act_rs;   // bytes between activation rows
+    float *         dst;
+    int64_t         dst_cs;
+    int             M, K, ncols;
+    MvIds           ids;      // ids.ids != nullptr: blockIdx.y = pair, act row = t*ne11 + i % ne11
+};
+cudaError_t mv_simple_launch(int type, const MvSimpleParams & p, cudaStream_t st);
+
+} // namespace b200

@@ -1,0 +1,210 @@
+// mmid.cu — K5/K6: GGML_OP_MUL_MAT_ID (MoE expert mat-vec / mat-mul).
+//
+// Replaces ggml_cuda_mul_mat_id (/root/reference/ggml/src/ggml-cuda/ggml-cuda.cu:2263-2409) and mm_ids_helper
+// (/root/reference/ggml/src/ggml-cuda/mmid.cu:26-164). Semantics follow ggml-cpu (ggml-cpu.c:1476-1649):
+//   dst[:, i, t] = as[ids[i, t]] . b[:, i % ne11, t]      for every slot i < n_used and token t < n_tok.
+// There is no host synchronisation anywhere on this path (the reference's fallback copies ids to the host,
+// ggml-cuda.cu:2322-2345): the expert id of a (slot, token) pair is read on the device by the CTAs that work on it.
+//
+// Routing of the work:
+//   * every b row is quantized once (K1, unit records) — ne11*n_tok rows, not n_used*n_tok;
+//   * each (slot, token) pair is one mat-vec of the TMA-staged kernel (mmvq.cu) with blockIdx.y = pair; the CTAs of a
+//     pair split the expert's rows. With n_pairs >= #SMs a pair gets one CTA.
+//   * b200_mm_ids_sort (counting sort by expert, stable) is the building block of the grouped tcgen05 path.
+
+#include "internal.h"
+
+using namespace b200;
+
+#define fail b200_fail
+
+// ------------------------------------------------------------------------------------------------ K5: sort pairs by expert
+
+// one CTA; warp w handles experts w, w+32, ...; pairs are scanned in order so the output is stable in p = t*n_used + i
+__global__ void __launch_bounds__(1024) mm_ids_sort_kernel(const int32_t * __restrict__ ids, int n_used, int n_tok, int64_t ids_rs, int n_as,
+                                                           int32_t * __restrict__ sorted_pairs, int32_t * __restrict__ expert_bounds) {
+    extern __shared__ int counts[];  // [n_as + 1]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, n_warps = blockDim.x >> 5;
+    const int n_pairs = n_used * n_tok;
+    for (int e = warp; e < n_as; e += n_warps) {
+        int cnt = 0;
+        for (int p0 = 0; p0 < n_pairs; p0 += 32) {
+            const int p = p0 + lane;
+            bool hit = false;
+            if (p < n_pairs) {
+                const int t = p / n_used, i = p - t * n_used;
+                hit = ids[(int64_t) t * ids_rs + i] == e;
+            }
+            cnt += __popc(__ballot_sync(0xffffffffu, hit));
+        }
+        if (lane == 0) counts[e] = cnt;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {  // exclusive scan; n_as is at most a few hundred
+        int run = 0;
+        for (int e = 0; e < n_as; e++) {
+            const int c = counts[e];
+            counts[e] = run;
+            expert_bounds[e] = run;
+            run += c;
+        }
+        counts[n_as] = run;
+        expert_bounds[n_as] = run;
+    }
+    __syncthreads();
+    for (int e = warp; e < n_as; e += n_warps) {
+        int pos = counts[e];
+        for (int p0 = 0; p0 < n_pairs; p0 += 32) {
+            const int p = p0 + lane;
+            bool hit = false;
+            if (p < n_pairs) {
+                const int t = p / n_used, i = p - t * n_used;
+                hit = ids[(int64_t) t * ids_rs + i] == e;
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (hit) sorted_pairs[pos + __popc(m & ((1u << lane) - 1))] = p;
+            pos += __popc(m);
+        }
+    }
+}
+
+b200_status b200_mm_ids_sort(b200_ctx * ctx, const int32_t * ids, int64_t n_used, int64_t n_tok, size_t ids_nb1, int64_t n_as,
+                             int32_t * sorted_pairs, int32_t * expert_bounds) {
+    if (!ctx || !ids || !sorted_pairs || !expert_bounds) return fail(B200_ERR_ARG, "null argument");
+    if (n_as <= 0 || n_as > 8192 || ids_nb1 % 4 != 0 || n_used * n_tok > INT32_MAX) return fail(B200_ERR_UNSUPPORTED, "bad MUL_MAT_ID index geometry");
+    CU(cudaSetDevice(ctx->device));
+    mm_ids_sort_kernel<<<1, 1024, (size_t) (n_as + 1) * sizeof(int), ctx->stream>>>(ids, (int) n_used, (int) n_tok, (int64_t) (ids_nb1 / 4), (int) n_as,
+                                                                                  sorted_pairs, expert_bounds);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ K6: dispatch
+
+int b200_mul_mat_id_supported(const b200_mul_mat_id_desc * d) {
+    if (!d) return 0;
+    if (d->type != B200_TYPE_Q4_0 && d->type != B200_TYPE_Q8_0 && d->type != B200_TYPE_Q4_K) return 0;
+    if (d->ne00 <= 0 || d->ne00 % type_block_elems(d->type) != 0) return 0;
+    if (d->ne01 < 0 || d->n_as <= 0 || d->ne11 <= 0 || d->n_tok < 0 || d->n_used <= 0) return 0;
+    if (d->nb01 < (size_t) (d->ne00 / type_block_elems(d->type)) * type_block_bytes(d->type)) return 0;
+    if (d->nb11 % 4 || d->nb12 % 4 || d->nb1 % 4 || d->nb2 % 4 || d->ids_nb1 % 4) return 0;
+    if (d->ne01 > INT32_MAX || d->ne00 > INT32_MAX || d->n_used * d->n_tok > INT32_MAX) return 0;
+    return 1;
+}
+
+b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, const void * as, const float * b, const int32_t * ids, float * dst) {
+    if (!ctx || !d || !as || !b || !ids || !dst) return fail(B200_ERR_ARG, "null argument");
+    if (!b200_mul_mat_id_supported(d)) return fail(B200_ERR_UNSUPPORTED, "MUL_MAT_ID geometry/type not supported");
+    const int64_t K = d->ne00, M = d->ne01;
+    const int64_t n_pairs = d->n_used * d->n_tok;
+    if (n_pairs == 0 || M == 0) return B200_OK;
+    CU(cudaSetDevice(ctx->device));
+
+    MvIds mi;
+    mi.ids    = ids;
+    mi.ids_rs = (int64_t) (d->ids_nb1 / 4);
+    mi.nb02   = (int64_t) d->nb02;
+    mi.dst_is = (int64_t) (d->nb1 / 4);
+    mi.dst_ts = (int64_t) (d->nb2 / 4);
+    mi.n_used = (int) d->n_used;
+    mi.ne11   = (int) d->ne11;
+    mi.n_as   = (int) d->n_as;
+
+    const bool fast = ctx->force_path != B200_PATH_SIMPLE && K % 256 == 0 && (uintptr_t) as % 16 == 0 && d->nb01 % 16 == 0 && d->nb02 % 16 == 0;
+    const int64_t n_rows = d->ne11 * d->n_tok;
+
+    if (fast) {
+        const int    U      = (int) (K / 256);
+        const size_t main_b = (size_t) n_rows * U * ACT_MAIN, aux_b = (size_t) n_rows * U * ACT_AUX;
+        const size_t aux_o  = (main_b + 255) & ~(size_t) 255;
+        b200_status  st     = b200_ensure(ctx, &ctx->scratch, &ctx->scratch_size, aux_o + aux_b);
+        if (st != B200_OK) return st;
+        uint8_t * am = (uint8_t *) ctx->scratch, * ax = am + aux_o;
+        if (d->nb12 == d->nb11 * (size_t) d->ne11) {  // rows of all tokens are equally spaced: one launch
+            int l = 0;
+            CU(quantize_units(act_kind_for(d->type), b, K, n_rows, d->nb11, am, ax, ctx->stream, &l));
+            ctx->launches += l;
+        } else {
+            for (int64_t t = 0; t < d->n_tok; t++) {
+                int l = 0;
+                CU(quantize_units(act_kind_for(d->type), (const float *) ((const char *) b + t * d->nb12), K, d->ne11, d->nb11,
+                                  am + (size_t) t * d->ne11 * U * ACT_MAIN, ax + (size_t) t * d->ne11 * U * ACT_AUX, ctx->stream, &l));
+                ctx->launches += l;
+            }
+        }
+        MvParams p;
+        memset(&p, 0, sizeof(p));
+        p.U = U;
+        if (U <= 32) { int L = 1; while (L < U) L <<= 1; p.L = L; p.rpg = 32 / L; p.slices = 1; }
+        else { p.L = 32; p.rpg = 1; p.slices = (U + 31) / 32; }
+        p.n_mats        = 1;
+        p.mat[0].w      = (const uint8_t *) as;
+        p.mat[0].nb01   = (int64_t) d->nb01;
+        p.mat[0].dst    = dst;
+        p.mat[0].dst_cs = 0;
+        p.mat[0].M      = (int) M;
+        p.mat[0].group0 = 0;
+        for (int i = 1; i < MV_MAX_MATS; i++) p.mat[i].group0 = INT32_MAX;
+        p.total_groups = (int) ((M + p.rpg - 1) / p.rpg);
+        p.act_main = am;
+        p.act_aux  = ax;
+        p.ids      = mi;
+        // shared-memory configuration for one column
+        static const int cand[][2] = { { 8, 4 }, { 8, 3 }, { 8, 2 }, { 4, 3 }, { 4, 2 }, { 2, 2 }, { 1, 2 } };
+        size_t smem = 0;
+        for (auto & c : cand) {
+            smem = mv_fast_smem(d->type, U, 1, c[0], c[1]);
+            if (smem <= 227 * 1024) { p.n_warps = c[0]; p.n_stages = c[1]; break; }
+            smem = 0;
+        }
+        if (!smem) return fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
+        // grid.y carries the pairs; chunk by whole tokens so that a chunk's pair index restarts at (slot 0, token t0)
+        const int64_t tok_chunk = 32768 / d->n_used > 0 ? 32768 / d->n_used : 1;
+        if (d->n_used > 65535) return fail(B200_ERR_UNSUPPORTED, "n_used > 65535");
+        for (int64_t t0 = 0; t0 < d->n_tok; t0 += tok_chunk) {
+            const int64_t nt = d->n_tok - t0 < tok_chunk ? d->n_tok - t0 : tok_chunk;
+            const int     np = (int) (nt * d->n_used);
+            int ctas = (ctx->sm_count + np - 1) / np;
+            if (ctas > p.total_groups) ctas = p.total_groups;
+            if (ctas < 1) ctas = 1;
+            MvParams q = p;
+            q.ids.ids    = ids + t0 * mi.ids_rs;
+            q.mat[0].dst = dst + t0 * mi.dst_ts;
+            q.act_main   = am + (size_t) t0 * d->ne11 * U * ACT_MAIN;
+            q.act_aux    = ax + (size_t) t0 * d->ne11 * U * ACT_AUX;
+            CU(mv_fast_launch(d->type, 1, q, ctas, np, smem, ctx->stream));
+            ctx->launches++;
+        }
+        return B200_OK;
+    }
+
+    // generic path
+    const int    val    = d->type == B200_TYPE_Q4_K ? 1 : 0;
+    const size_t act_rs = d->type == B200_TYPE_Q4_K ? (size_t) (K / QK_K) * SZ_Q8_K : (size_t) (K / QK) * SZ_Q8_0;
+    b200_status  st     = b200_ensure(ctx, &ctx->scratch, &ctx->scratch_size, (size_t) n_rows * act_rs + 16);
+    if (st != B200_OK) return st;
+    uint8_t * act = (uint8_t *) ctx->scratch;
+    for (int64_t t = 0; t < d->n_tok; t++) {
+        int l = 0;
+        CU(quantize_ggml(val, (const float *) ((const char *) b + t * d->nb12), K, d->ne11, d->nb11, act + (size_t) t * d->ne11 * act_rs,
+                         ctx->stream, &l));
+        ctx->launches += l;
+    }
+    if (n_pairs > 65535) return fail(B200_ERR_UNSUPPORTED, "more than 65535 (slot, token) pairs on the generic MUL_MAT_ID path");
+    MvSimpleParams sp;
+    memset(&sp, 0, sizeof(sp));
+    sp.w      = (const uint8_t *) as;
+    sp.nb01   = (int64_t) d->nb01;
+    sp.act    = act;
+    sp.act_rs = (int64_t) act_rs;
+    sp.dst    = dst;
+    sp.dst_cs = 0;
+    sp.M      = (int) M;
+    sp.K      = (int) K;
+    sp.ncols  = (int) n_pairs;
+    sp.ids    = mi;
+    CU(mv_simple_launch(d->type, sp, ctx->stream));
+    ctx->launches++;
+    return B200_OK;
+}

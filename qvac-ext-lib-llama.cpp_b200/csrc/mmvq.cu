@@ -1,0 +1,499 @@
+// mmvq.cu — K3: decode mat-vec kernels (1..8 activation columns) for q4_0 / q8_0 / q4_K weights on sm_100a.
+//
+// Replaces mul_mat_vec_q + vec_dot_{q4_0,q8_0,q4_K}_q8_1 (/root/reference/ggml/src/ggml-cuda/mmvq.cu:141-335,
+// vecdotq.cuh:103-122, 231-243, 461-483). Not a port: the reference walks a row with 2-/4-byte scalar loads
+// (vecdotq.cuh:7-30) because 18-/34-byte blocks are only 2-byte aligned; here
+//   * the weight stream is moved by the TMA engine: cp.async.bulk (SASS UBLKCP) copies whole row slices
+//     (>= 2.3 KB each) global -> shared into a per-warp ring of stages, completion through mbarriers, with an
+//     L2 evict_first policy (weights are read once per token);
+//   * each warp is its own producer/consumer pipeline (lane 0 issues the copies), so there is no CTA-wide
+//     barrier in the steady state; a persistent grid of one CTA per SM takes contiguous row ranges and its warps
+//     pull row groups from a shared counter;
+//   * out of shared memory a lane owns one 256-weight "unit" (8 x q4_0 = 1 x q4_K = 144 B, 8 x q8_0 = 272 B):
+//     every unit is a whole number of 128-bit words, lane strides of 144 / 272 bytes are bank-conflict free for
+//     ld.shared.v4, and all sub-block offsets inside a unit are compile-time constants (the 2-byte misalignment
+//     of q4_0/q8_0 blocks becomes a constant 16-bit funnel shift);
+//   * integer dot products with dp4a (dp4a.u32.s32 on the un-shifted high nibbles, exact >>4 afterwards) and
+//     dp2a for the q4_K min term, fp32 accumulation per lane, warp-shuffle reduction per row.
+// The integer block sums are identical to ggml-cpu's vec_dot_q4_0_q8_0 / q8_0_q8_0 / q4_K_q8_K because the
+// activations are quantized exactly like the CPU does (quantize.cu); only the fp32 summation order differs.
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------------
+// per-unit dot products. `w` = shared address of the unit's weights, `am`/`ax` = shared addresses of the
+// unit's activation record for column 0 (main / aux), `cs_m`/`cs_x` = byte strides between columns.
+// ------------------------------------------------------------------------------------------------
+
+template <int NC>
+__device__ __forceinline__ void unit_dot_q4_K(uint32_t w, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc)[NC]) {
+    const uint4 hdr = lds128(w);  // d | dmin, 12 bytes of 6-bit scales/mins (ggml-common.h:291-305)
+    const float d    = half_bits_to_float((uint16_t) (hdr.x & 0xffff));
+    const float dmin = half_bits_to_float((uint16_t) (hdr.x >> 16));
+    // 8 scales and 8 mins as bytes (same bit surgery as ggml-cpu/quants.c:586-591)
+    const uint32_t sc_lo = hdr.y & 0x3f3f3f3fu;
+    const uint32_t mn_lo = hdr.z & 0x3f3f3f3fu;
+    const uint32_t sc_hi = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
+    const uint32_t mn_hi = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
+
+    int isum[NC];
+#pragma unroll
+    for (int c = 0; c < NC; c++) isum[c] = 0;
+
+#pragma unroll
+    for (int g = 0; g < 4; g++) {  // 64 weights: 32 bytes, low nibbles = sub-block 2g, high nibbles = sub-block 2g+1
+        const uint4 qa = lds128(w + 16 + 32 * g);
+        const uint4 qb = lds128(w + 32 + 32 * g);
+        const uint32_t q[8] = { qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w };
+        const uint32_t scw  = g < 2 ? sc_lo : sc_hi;
+        const int      s0   = (scw >> (16 * (g & 1))) & 0xff;
+        const int      s1   = (scw >> (16 * (g & 1) + 8)) & 0xff;
+#pragma unroll
+        for (int c = 0; c < NC; c++) {
+            const uint32_t a  = am + c * cs_m + 64 * g;
+            const uint4    l0 = lds128(a), l1 = lds128(a + 16), h0 = lds128(a + 32), h1 = lds128(a + 48);
+            const int lo[8] = { (int) l0.x, (int) l0.y, (int) l0.z, (int) l0.w, (int) l1.x, (int) l1.y, (int) l1.z, (int) l1.w };
+            const int hi[8] = { (int) h0.x, (int) h0.y, (int) h0.z, (int) h0.w, (int) h1.x, (int) h1.y, (int) h1.z, (int) h1.w };
+            int sl = 0, sh = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                sl = dp4a_us(q[k] & 0x0f0f0f0fu, lo[k], sl);
+                sh = dp4a_us(q[k] & 0xf0f0f0f0u, hi[k], sh);  // 16 x the high-nibble dot product
+            }
+            isum[c] += s0 * sl + s1 * (sh >> 4);
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NC; c++) {
+        const uint4 bs = lds128(am + c * cs_m + 256);  // int16 sum of q per 32-block (x8)
+        int imin = dp2a_lo_su((int) bs.x, mn_lo, 0);
+        imin     = dp2a_hi_su((int) bs.y, mn_lo, imin);
+        imin     = dp2a_lo_su((int) bs.z, mn_hi, imin);
+        imin     = dp2a_hi_su((int) bs.w, mn_hi, imin);
+        const float dy = __uint_as_float(lds32(ax + c * cs_x));
+        acc[c] = fmaf(d * dy, (float) isum[c], acc[c]);
+        acc[c] = fmaf(-(dmin * dy), (float) imin, acc[c]);
+    }
+}
+
+template <int NC>
+__device__ __forceinline__ void unit_dot_q4_0(uint32_t w, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc)[NC]) {
+    uint32_t ww[36];  // 8 blocks of { half d; uint8 qs[16] } = 144 bytes
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        const uint4 v = lds128(w + 16 * i);
+        ww[4 * i] = v.x; ww[4 * i + 1] = v.y; ww[4 * i + 2] = v.z; ww[4 * i + 3] = v.w;
+    }
+    uint4 dyh[NC], ys[NC];
+#pragma unroll
+    for (int c = 0; c < NC; c++) {
+        dyh[c] = lds128(am + c * cs_m + 256);  // half d[8]
+        ys[c]  = lds128(ax + c * cs_x);        // int16 sum[8]
+    }
+#pragma unroll
+    for (int b = 0; b < 8; b++) {
+        const int p = 9 * (b >> 1);  // word offset of the block pair
+        float    dw;
+        uint32_t q[4];
+        if ((b & 1) == 0) {  // block starts on a word boundary: d in the low half, nibbles shifted by 16 bits
+            dw = half_bits_to_float((uint16_t) (ww[p] & 0xffff));
+#pragma unroll
+            for (int k = 0; k < 4; k++) q[k] = __funnelshift_r(ww[p + k], ww[p + k + 1], 16);
+        } else {  // block starts in the middle of word p+4: d in its high half, nibbles word aligned
+            dw = half_bits_to_float((uint16_t) (ww[p + 4] >> 16));
+#pragma unroll
+            for (int k = 0; k < 4; k++) q[k] = ww[p + 5 + k];
+        }
+#pragma unroll
+        for (int c = 0; c < NC; c++) {
+            const uint32_t a  = am + c * cs_m + 32 * b;
+            const uint4    l  = lds128(a), h = lds128(a + 16);  // elements 0..15 (low nibbles), 16..31 (high nibbles)
+            int sl = 0, sh = 0;
+            sl = dp4a_us(q[0] & 0x0f0f0f0fu, (int) l.x, sl); sh = dp4a_us(q[0] & 0xf0f0f0f0u, (int) h.x, sh);
+            sl = dp4a_us(q[1] & 0x0f0f0f0fu, (int) l.y, sl); sh = dp4a_us(q[1] & 0xf0f0f0f0u, (int) h.y, sh);
+            sl = dp4a_us(q[2] & 0x0f0f0f0fu, (int) l.z, sl); sh = dp4a_us(q[2] & 0xf0f0f0f0u, (int) h.z, sh);
+            sl = dp4a_us(q[3] & 0x0f0f0f0fu, (int) l.w, sl); sh = dp4a_us(q[3] & 0xf0f0f0f0u, (int) h.w, sh);
+            const uint32_t dword = b < 2 ? dyh[c].x : b < 4 ? dyh[c].y : b < 6 ? dyh[c].z : dyh[c].w;
+            const uint32_t sword = b < 2 ? ys[c].x : b < 4 ? ys[c].y : b < 6 ? ys[c].z : ys[c].w;
+            const float    dy    = half_bits_to_float((uint16_t) ((b & 1) ? dword >> 16 : dword & 0xffff));
+            const int      ysum  = (int) (int16_t) ((b & 1) ? sword >> 16 : sword & 0xffff);
+            const int      sumi  = sl + (sh >> 4) - 8 * ysum;  // sum((q-8)*y), ggml-cpu/quants.c:135-146
+            acc[c] = fmaf((float) sumi * dw, dy, acc[c]);
+        }
+    }
+}
+
+template <int NC>
+__device__ __forceinline__ void unit_dot_q8_0(uint32_t w, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc)[NC]) {
+    (void) ax; (void) cs_x;
+    uint32_t ww[68];  // 8 blocks of { half d; int8 qs[32] } = 272 bytes; 128-bit loads at a 272-byte lane stride are conflict free
+#pragma unroll
+    for (int i = 0; i < 17; i++) {
+        const uint4 v = lds128(w + 16 * i);
+        ww[4 * i] = v.x; ww[4 * i + 1] = v.y; ww[4 * i + 2] = v.z; ww[4 * i + 3] = v.w;
+    }
+    uint4 dyh[NC];
+#pragma unroll
+    for (int c = 0; c < NC; c++) dyh[c] = lds128(am + c * cs_m + 256);
+#pragma unroll
+    for (int b = 0; b < 8; b++) {
+        const int p = 17 * (b >> 1);  // a block pair is 68 bytes = 17 words starting on a word boundary
+        float    dw;
+        uint32_t q[8];
+        if ((b & 1) == 0) {
+            dw = half_bits_to_float((uint16_t) (ww[p] & 0xffff));
+#pragma unroll
+            for (int k = 0; k < 8; k++) q[k] = __funnelshift_r(ww[p + k], ww[p + k + 1], 16);
+        } else {
+            dw = half_bits_to_float((uint16_t) (ww[p + 8] >> 16));
+#pragma unroll
+            for (int k = 0; k < 8; k++) q[k] = ww[p + 9 + k];
+        }
+#pragma unroll
+        for (int c = 0; c < NC; c++) {
+            const uint32_t a  = am + c * cs_m + 32 * b;
+            const uint4    y0 = lds128(a), y1 = lds128(a + 16);
+            int s = 0;
+            s = dp4a_ss((int) q[0], (int) y0.x, s); s = dp4a_ss((int) q[1], (int) y0.y, s);
+            s = dp4a_ss((int) q[2], (int) y0.z, s); s = dp4a_ss((int) q[3], (int) y0.w, s);
+            s = dp4a_ss((int) q[4], (int) y1.x, s); s = dp4a_ss((int) q[5], (int) y1.y, s);
+            s = dp4a_ss((int) q[6], (int) y1.z, s); s = dp4a_ss((int) q[7], (int) y1.w, s);
+            const uint32_t dword = b < 2 ? dyh[c].x : b < 4 ? dyh[c].y : b < 6 ? dyh[c].z : dyh[c].w;
+            const float    dy    = half_bits_to_float((uint16_t) ((b & 1) ? dword >> 16 : dword & 0xffff));
+            acc[c] = fmaf((float) s, dw * dy, acc[c]);  // sumi*(dx*dy), ggml-cpu/quants.c:329
+        }
+    }
+}
+
+template <int TYPE, int NC>
+__device__ __forceinline__ void unit_dot(uint32_t w, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc)[NC]) {
+    if (TYPE == B200_TYPE_Q4_K) unit_dot_q4_K<NC>(w, am, ax, cs_m, cs_x, acc);
+    else if (TYPE == B200_TYPE_Q4_0) unit_dot_q4_0<NC>(w, am, ax, cs_m, cs_x, acc);
+    else unit_dot_q8_0<NC>(w, am, ax, cs_m, cs_x, acc);
+}
+
+// ------------------------------------------------------------------------------------------------
+// the persistent kernel
+// shared memory map (dynamic, 128-byte aligned):
+//   [0, 16)                               : int next_group ; pad
+//   [16, 16 + 8)                          : act mbarrier
+//   [64, 64 + 8*NW*NS)                    : per-warp stage mbarriers
+//   [.., + 8*NW*NS)                       : per-warp stage descriptors {group, slice}
+//   [act_main: NC*U*272][act_aux: NC*U*16]
+//   [ring: NW*NS*stage_bytes]
+// ------------------------------------------------------------------------------------------------
+
+constexpr int MV_HDR_BYTES = 64;
+
+__host__ __device__ inline size_t mv_align(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+size_t mv_fast_smem(int type, int U, int ncols, int n_warps, int n_stages) {
+    const size_t stage = 32 * (size_t) unit_bytes(type);
+    size_t s = MV_HDR_BYTES;
+    s += (size_t) 16 * n_warps * n_stages;  // barriers + descriptors
+    s = mv_align(s, 128);
+    s += (size_t) ncols * U * (ACT_MAIN + ACT_AUX);
+    s = mv_align(s, 128);
+    s += (size_t) n_warps * n_stages * stage;
+    return s;
+}
+
+template <int TYPE, int NC>
+__global__ void __launch_bounds__(256, 1) mv_fast_kernel(const __grid_constant__ MvParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    constexpr int UB    = unit_bytes(TYPE);
+    constexpr int STAGE = 32 * UB;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int NW = p.n_warps, NS = p.n_stages;
+    const int U = p.U;
+
+    int *      next_group = (int *) smem;
+    uint64_t * act_bar    = (uint64_t *) (smem + 16);
+    uint64_t * bars       = (uint64_t *) (smem + MV_HDR_BYTES);
+    int2 *     descs      = (int2 *) (smem + MV_HDR_BYTES + 8 * NW * NS);
+    size_t     off        = mv_align(MV_HDR_BYTES + (size_t) 16 * NW * NS, 128);
+    uint8_t *  act_m      = smem + off;
+    uint8_t *  act_x      = act_m + (size_t) NC * U * ACT_MAIN;
+    off                   = mv_align(off + (size_t) NC * U * (ACT_MAIN + ACT_AUX), 128);
+    uint8_t *  ring       = smem + off + (size_t) warp * NS * STAGE;
+
+    // MUL_MAT_ID: this CTA row (blockIdx.y) is one (slot, token) pair with its own expert, activation row and dst column
+    int64_t w_off = 0, dst_off = 0;
+    int     act_col = 0;
+    if (p.ids.ids) {
+        const int pair = blockIdx.y;
+        const int t = pair / p.ids.n_used, i = pair - t * p.ids.n_used;
+        const int e = p.ids.ids[(int64_t) t * p.ids.ids_rs + i];
+        if (e < 0 || e >= p.ids.n_as) return;  // ggml-cpu asserts here (ggml-cpu.c:1574); never read out of bounds
+        w_off   = (int64_t) e * p.ids.nb02;
+        dst_off = (int64_t) t * p.ids.dst_ts + (int64_t) i * p.ids.dst_is;
+        act_col = t * p.ids.ne11 + i % p.ids.ne11;
+    }
+
+    // this CTA's contiguous range of row groups
+    const int g_begin = (int) ((int64_t) p.total_groups * blockIdx.x / gridDim.x);
+    const int g_end   = (int) ((int64_t) p.total_groups * (blockIdx.x + 1) / gridDim.x);
+
+    if (threadIdx.x == 0) {
+        *next_group = g_begin;
+        mbar_init(smem_u32(act_bar), 1);
+        for (int i = 0; i < NW * NS; i++) mbar_init(smem_u32(bars + i), 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    const uint64_t pol_stream = l2_policy_evict_first();
+    const uint64_t pol_keep   = l2_policy_evict_last();
+
+    if (threadIdx.x == 0) {  // activations: NC columns of U records (main + aux), shared by every row
+        const uint32_t bytes_m = (uint32_t) NC * U * ACT_MAIN, bytes_x = (uint32_t) NC * U * ACT_AUX;
+        mbar_expect_tx(smem_u32(act_bar), bytes_m + bytes_x);
+        for (int c = 0; c < NC; c++) {
+            bulk_g2s(smem_u32(act_m + (size_t) c * U * ACT_MAIN), p.act_main + (size_t) (act_col + c) * U * ACT_MAIN,
+                     (uint32_t) U * ACT_MAIN, smem_u32(act_bar), pol_keep);
+        }
+        bulk_g2s(smem_u32(act_x), p.act_aux + (size_t) act_col * U * ACT_AUX, bytes_x, smem_u32(act_bar), pol_keep);
+    }
+
+    uint64_t * my_bars  = bars + warp * NS;
+    int2 *     my_descs = descs + warp * NS;
+
+    // ---- producer state (warp-uniform)
+    int  prod_group = -1, prod_slice = p.slices;
+    int  issued = 0, consumed = 0;
+    bool exhausted = false;
+
+    auto produce = [&]() {
+        if (exhausted) return;
+        if (prod_slice >= p.slices) {
+            int g = 0;
+            if (lane == 0) g = atomicAdd(next_group, 1);
+            g = __shfl_sync(0xffffffffu, g, 0);
+            if (g >= g_end) { exhausted = true; return; }
+            prod_group = g;
+            prod_slice = 0;
+        }
+        const int stage = issued % NS;
+        if (lane == 0) {
+            // locate the matrix of this global group id
+            int m = 0;
+#pragma unroll
+            for (int i = 1; i < MV_MAX_MATS; i++) if (i < p.n_mats && prod_group >= p.mat[i].group0) m = i;
+            const MvMat & mat  = p.mat[m];
+            const int     row0 = (prod_group - mat.group0) * p.rpg;
+            const int     nrow = min(p.rpg, mat.M - row0);
+            const int     u0   = prod_slice * 32;
+            const int     nu   = min(32, U - u0);
+            const uint32_t bar = smem_u32(my_bars + stage);
+            const uint32_t dst = smem_u32(ring + (size_t) stage * STAGE);
+            my_descs[stage] = make_int2(prod_group, prod_slice);
+            const uint32_t row_bytes = (uint32_t) nu * UB;
+            mbar_expect_tx(bar, row_bytes * nrow);
+            const uint8_t * src = mat.w + w_off + (int64_t) row0 * mat.nb01 + (int64_t) u0 * UB;
+            if (nrow > 1 && mat.nb01 == (int64_t) U * UB) {
+                bulk_g2s(dst, src, row_bytes * nrow, bar, pol_stream);  // rows are adjacent in memory: one copy
+            } else {
+                for (int r = 0; r < nrow; r++) bulk_g2s(dst + r * row_bytes, src + (int64_t) r * mat.nb01, row_bytes, bar, pol_stream);
+            }
+        }
+        issued++;
+        prod_slice++;
+    };
+
+    for (int i = 0; i < NS; i++) produce();
+
+    mbar_wait(smem_u32(act_bar), 0);
+
+    const uint32_t am0  = smem_u32(act_m), ax0 = smem_u32(act_x);
+    const uint32_t cs_m = (uint32_t) U * ACT_MAIN, cs_x = (uint32_t) U * ACT_AUX;
+
+    const int L   = p.L;
+    const int sub = lane & (L - 1);  // unit index inside the row slice
+    const int rr  = lane / L;        // row inside the group
+
+    float acc[NC];
+#pragma unroll
+    for (int c = 0; c < NC; c++) acc[c] = 0.0f;
+
+    while (consumed < issued) {
+        const int stage = consumed % NS;
+        mbar_wait(smem_u32(my_bars + stage), (consumed / NS) & 1);
+        const int2 ds    = my_descs[stage];
+        const int  group = ds.x, slice = ds.y;
+        int m = 0;
+#pragma unroll
+        for (int i = 1; i < MV_MAX_MATS; i++) if (i < p.n_mats && group >= p.mat[i].group0) m = i;
+        const int row0 = (group - p.mat[m].group0) * p.rpg;
+        const int M    = p.mat[m].M;
+        const int u0   = slice * 32;
+        const int nu   = min(32, U - u0);
+        const int row  = row0 + rr;
+        const int u    = u0 + sub;
+
+        if (sub < nu && row < M && rr < p.rpg) {
+            const uint32_t w = smem_u32(ring + (size_t) stage * STAGE) + (uint32_t) (rr * nu + sub) * UB;
+            unit_dot<TYPE, NC>(w, am0 + (uint32_t) u * ACT_MAIN, ax0 + (uint32_t) u * ACT_AUX, cs_m, cs_x, acc);
+        }
+
+        if (slice == p.slices - 1) {  // row finished: reduce the L lanes of each row and store
+#pragma unroll
+            for (int c = 0; c < NC; c++) {
+                float v = acc[c];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const float t = __shfl_xor_sync(0xffffffffu, v, o);
+                    if (o < L) v += t;
+                }
+                if (sub == 0 && row < M && rr < p.rpg) p.mat[m].dst[dst_off + (int64_t) c * p.mat[m].dst_cs + row] = v;
+                acc[c] = 0.0f;
+            }
+        }
+        __syncwarp();
+        consumed++;
+        produce();  // refill the stage that was just drained
+    }
+}
+
+template <int TYPE, int NC>
+static cudaError_t mv_fast_launch_t(const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
+    static bool attr_done[64] = {};  // one attribute call per instantiation and device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(mv_fast_kernel<TYPE, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_done[dev] = true;
+    }
+    mv_fast_kernel<TYPE, NC><<<dim3(n_ctas, n_pairs), p.n_warps * 32, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+template <int TYPE>
+static cudaError_t mv_fast_launch_n(int nc, const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
+    switch (nc) {
+        case 1: return mv_fast_launch_t<TYPE, 1>(p, n_ctas, n_pairs, smem, st);
+        case 2: return mv_fast_launch_t<TYPE, 2>(p, n_ctas, n_pairs, smem, st);
+        case 3: return mv_fast_launch_t<TYPE, 3>(p, n_ctas, n_pairs, smem, st);
+        case 4: return mv_fast_launch_t<TYPE, 4>(p, n_ctas, n_pairs, smem, st);
+        case 5: return mv_fast_launch_t<TYPE, 5>(p, n_ctas, n_pairs, smem, st);
+        case 6: return mv_fast_launch_t<TYPE, 6>(p, n_ctas, n_pairs, smem, st);
+        case 7: return mv_fast_launch_t<TYPE, 7>(p, n_ctas, n_pairs, smem, st);
+        case 8: return mv_fast_launch_t<TYPE, 8>(p, n_ctas, n_pairs, smem, st);
+    }
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t mv_fast_launch(int type, int ncols, const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
+    switch (type) {
+        case B200_TYPE_Q4_0: return mv_fast_launch_n<B200_TYPE_Q4_0>(ncols, p, n_ctas, n_pairs, smem, st);
+        case B200_TYPE_Q8_0: return mv_fast_launch_n<B200_TYPE_Q8_0>(ncols, p, n_ctas, n_pairs, smem, st);
+        case B200_TYPE_Q4_K: return mv_fast_launch_n<B200_TYPE_Q4_K>(ncols, p, n_ctas, n_pairs, smem, st);
+    }
+    return cudaErrorInvalidValue;
+}
+
+// ------------------------------------------------------------------------------------------------
+// generic kernel: one warp per weight row, one lane per block, 16-bit loads only (blocks are 2-byte aligned),
+// activations in the reference's own q8_0 / q8_K block layout. Used for K % 256 != 0, unaligned views, and as an
+// independent on-device cross-check of the fast kernel. Performance is not a goal here.
+// ------------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ uint32_t ld16x2(const uint8_t * p) {  // 4 bytes from a 2-byte aligned address
+    const uint16_t * h = (const uint16_t *) p;
+    return (uint32_t) h[0] | ((uint32_t) h[1] << 16);
+}
+
+template <int TYPE>
+__global__ void __launch_bounds__(128) mv_simple_kernel(const MvSimpleParams p) {
+    const int lane = threadIdx.x & 31;
+    const int row  = blockIdx.x * 4 + (threadIdx.x >> 5);
+    int     col = blockIdx.y, act_row = blockIdx.y;
+    int64_t w_off = 0, dst_off = 0;
+    if (row >= p.M) return;
+    if (p.ids.ids) {
+        const int t = col / p.ids.n_used, i = col - t * p.ids.n_used;
+        const int e = p.ids.ids[(int64_t) t * p.ids.ids_rs + i];
+        if (e < 0 || e >= p.ids.n_as) return;
+        w_off   = (int64_t) e * p.ids.nb02;
+        dst_off = (int64_t) t * p.ids.dst_ts + (int64_t) i * p.ids.dst_is;
+        act_row = t * p.ids.ne11 + i % p.ids.ne11;
+        col     = 0;
+    }
+    const uint8_t * wr = p.w + w_off + (int64_t) row * p.nb01;
+    const uint8_t * ar = p.act + (int64_t) act_row * p.act_rs;
+    float acc = 0.0f;
+    if (TYPE == B200_TYPE_Q4_K) {
+        for (int b = lane; b < p.K / QK_K; b += 32) {
+            const uint8_t * wb = wr + (int64_t) b * SZ_Q4_K;
+            const uint8_t * ab = ar + (int64_t) b * SZ_Q8_K;
+            const uint32_t  h0 = ld16x2(wb), u0 = ld16x2(wb + 4), u1 = ld16x2(wb + 8), u2 = ld16x2(wb + 12);
+            const float d = half_bits_to_float((uint16_t) (h0 & 0xffff)), dmin = half_bits_to_float((uint16_t) (h0 >> 16));
+            const uint32_t sc4[2] = { u0 & 0x3f3f3f3fu, (u2 & 0x0f0f0f0fu) | ((u0 >> 2) & 0x30303030u) };
+            const uint32_t mn4[2] = { u1 & 0x3f3f3f3fu, ((u2 >> 4) & 0x0f0f0f0fu) | ((u1 >> 2) & 0x30303030u) };
+            const float    dy     = *(const float *) ab;
+            const int8_t *  q8    = (const int8_t *) (ab + 4);
+            const int16_t * bs    = (const int16_t *) (ab + 4 + QK_K);
+            int isum = 0, imin = 0;
+            for (int s = 0; s < 8; s++) {
+                const int sc = (sc4[s >> 2] >> (8 * (s & 3))) & 0xff, mn = (mn4[s >> 2] >> (8 * (s & 3))) & 0xff;
+                imin += mn * (bs[2 * s] + bs[2 * s + 1]);
+                const uint8_t * qq = wb + 16 + 32 * (s >> 1);
+                int dot = 0;
+                for (int l = 0; l < 32; l += 2) {
+                    const uint16_t two = *(const uint16_t *) (qq + l);
+                    const int w0 = (s & 1) ? (two >> 4) & 0xf : two & 0xf;
+                    const int w1 = (s & 1) ? (two >> 12) & 0xf : (two >> 8) & 0xf;
+                    dot += w0 * q8[32 * s + l] + w1 * q8[32 * s + l + 1];
+                }
+                isum += sc * dot;
+            }
+            acc = fmaf(d * dy, (float) isum, acc);
+            acc = fmaf(-(dmin * dy), (float) imin, acc);
+        }
+    } else {
+        constexpr int WB = TYPE == B200_TYPE_Q4_0 ? SZ_Q4_0 : SZ_Q8_0;
+        for (int b = lane; b < p.K / QK; b += 32) {
+            const uint8_t * wb = wr + (int64_t) b * WB;
+            const uint8_t * ab = ar + (int64_t) b * SZ_Q8_0;
+            const float     dw = half_bits_to_float(*(const uint16_t *) wb);
+            const float     dy = half_bits_to_float(*(const uint16_t *) ab);
+            const int8_t *  q8 = (const int8_t *) (ab + 2);
+            int sumi = 0;
+            if (TYPE == B200_TYPE_Q4_0) {
+                for (int j = 0; j < 16; j += 2) {
+                    const uint16_t two = *(const uint16_t *) (wb + 2 + j);
+                    sumi += ((two & 0xf) - 8) * q8[j] + (((two >> 4) & 0xf) - 8) * q8[j + 16];
+                    sumi += (((two >> 8) & 0xf) - 8) * q8[j + 1] + (((two >> 12) & 0xf) - 8) * q8[j + 17];
+                }
+                acc = fmaf((float) sumi * dw, dy, acc);
+            } else {
+                for (int j = 0; j < 32; j += 2) {
+                    const uint16_t two = *(const uint16_t *) (wb + 2 + j);
+                    sumi += (int) (int8_t) (two & 0xff) * q8[j] + (int) (int8_t) (two >> 8) * q8[j + 1];
+                }
+                acc = fmaf((float) sumi, dw * dy, acc);
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) p.dst[dst_off + (int64_t) col * p.dst_cs + row] = acc;
+}
+
+cudaError_t mv_simple_launch(int type, const MvSimpleParams & p, cudaStream_t st) {
+    if (p.M == 0 || p.ncols == 0) return cudaSuccess;
+    dim3 grid((unsigned) ((p.M + 3) / 4), (unsigned) p.ncols);
+    switch (type) {
+        case B200_TYPE_Q4_0: mv_simple_kernel<B200_TYPE_Q4_0><<<grid, 128, 0, st>>>(p); break;
+        case B200_TYPE_Q8_0: mv_simple_kernel<B200_TYPE_Q8_0><<<grid, 128, 0, st>>>(p); break;
+        case B200_TYPE_Q4_K: mv_simple_kernel<B200_TYPE_Q4_K><<<grid, 128, 0, st>>>(p); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+} // namespace b200
