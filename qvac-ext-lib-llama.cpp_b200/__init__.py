@@ -1,0 +1,249 @@
+"""ggml-b200 — Python view of the C-ABI in include/ggml_b200.h (ctypes), for tests and bench.py.
+
+The product is the pair of shared libraries next to this file:
+  libb200mm.so     sm_100a CUDA kernels + C-ABI           (csrc/*.cu)
+  libggml-b200.so  the ggml backend over that C-ABI        (csrc/ggml_backend_b200.cpp)
+PyTorch is used only as a device-memory allocator and stream provider. Nothing in this package computes on the CPU and
+nothing here imports oracle/: if the CUDA library is missing or there is no sm_100 device, calls raise.
+
+The directory name contains '-' and '.', so import it through `b200_pkg.load()` at the repository root.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "libb200mm.so"
+BACKEND_PATH = HERE / "libggml-b200.so"
+
+Q4_0, Q8_0, Q4_K = 2, 8, 12
+TYPE_NAMES = {Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K"}
+BLOCK = {Q4_0: (32, 18), Q8_0: (32, 34), Q4_K: (256, 144)}
+PATH_AUTO, PATH_MMVQ, PATH_MMQ, PATH_SIMPLE = 0, 1, 2, 3
+
+EXPORTS = [
+    "b200_device_count", "b200_device_info", "b200_device_memory", "b200_ctx_create", "b200_ctx_destroy", "b200_ctx_device",
+    "b200_ctx_stream", "b200_ctx_synchronize", "b200_last_error", "b200_ctx_launch_count", "b200_ctx_set_force_path",
+    "b200_malloc", "b200_free", "b200_host_malloc", "b200_host_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_memcpy_d2d",
+    "b200_memcpy_peer", "b200_memset", "b200_memcpy_h2d_async", "b200_memcpy_d2h_async", "b200_memcpy_d2d_async",
+    "b200_event_create", "b200_event_destroy", "b200_event_record", "b200_event_wait", "b200_event_synchronize",
+    "b200_event_elapsed_ms", "b200_quantize_q8_0", "b200_quantize_q8_1", "b200_quantize_q8_K", "b200_quantize_units",
+    "b200_mul_mat_supported", "b200_mul_mat", "b200_mul_mat_shared_src1", "b200_mul_mat_host", "b200_mul_mat_id_supported",
+    "b200_mul_mat_id", "b200_mm_ids_sort", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
+]
+
+
+def row_size(t: int, k: int) -> int:
+    e, b = BLOCK[t]
+    if k % e:
+        raise ValueError(f"K={k} is not a multiple of the {TYPE_NAMES[t]} block size {e}")
+    return k // e * b
+
+
+class MulMatDesc(C.Structure):
+    _fields_ = [("type", C.c_int32),
+                ("ne00", C.c_int64), ("ne01", C.c_int64), ("ne02", C.c_int64), ("ne03", C.c_int64),
+                ("nb01", C.c_size_t), ("nb02", C.c_size_t), ("nb03", C.c_size_t),
+                ("ne11", C.c_int64), ("ne12", C.c_int64), ("ne13", C.c_int64),
+                ("nb11", C.c_size_t), ("nb12", C.c_size_t), ("nb13", C.c_size_t),
+                ("nb1", C.c_size_t), ("nb2", C.c_size_t), ("nb3", C.c_size_t)]
+
+    @classmethod
+    def contiguous(cls, t, M, K, N, ne02=1, ne03=1, ne12=None, ne13=None):
+        ne12 = ne02 if ne12 is None else ne12
+        ne13 = ne03 if ne13 is None else ne13
+        rb = row_size(t, K)
+        return cls(t, K, M, ne02, ne03, rb, rb * M, rb * M * ne02, N, ne12, ne13, 4 * K, 4 * K * N, 4 * K * N * ne12,
+                   4 * M, 4 * M * N, 4 * M * N * ne12)
+
+
+class MulMatIdDesc(C.Structure):
+    _fields_ = [("type", C.c_int32),
+                ("ne00", C.c_int64), ("ne01", C.c_int64), ("n_as", C.c_int64),
+                ("nb01", C.c_size_t), ("nb02", C.c_size_t),
+                ("ne11", C.c_int64), ("n_tok", C.c_int64),
+                ("nb11", C.c_size_t), ("nb12", C.c_size_t),
+                ("n_used", C.c_int64), ("ids_nb1", C.c_size_t),
+                ("nb1", C.c_size_t), ("nb2", C.c_size_t)]
+
+    @classmethod
+    def contiguous(cls, t, M, K, n_as, n_used, ne11, n_tok):
+        rb = row_size(t, K)
+        return cls(t, K, M, n_as, rb, rb * M, ne11, n_tok, 4 * K, 4 * K * ne11, n_used, 4 * n_used, 4 * M, 4 * M * n_used)
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """the C-ABI library; raises if it has not been built (no fallback of any kind)"""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise B200Error(f"{LIB_PATH} is missing: run __graft_entry__.build() (make -C {HERE / 'csrc'})")
+        L = C.CDLL(str(LIB_PATH))
+        vp, i64, sz, ci = C.c_void_p, C.c_int64, C.c_size_t, C.c_int
+        L.b200_device_count.restype = ci
+        L.b200_last_error.restype = C.c_char_p
+        L.b200_ctx_create.argtypes = [ci, vp, C.POINTER(vp)]
+        L.b200_ctx_destroy.argtypes = [vp]
+        L.b200_ctx_destroy.restype = None
+        L.b200_ctx_stream.argtypes = [vp]
+        L.b200_ctx_stream.restype = vp
+        L.b200_ctx_synchronize.argtypes = [vp]
+        L.b200_ctx_launch_count.argtypes = [vp]
+        L.b200_ctx_launch_count.restype = C.c_uint64
+        L.b200_ctx_set_force_path.argtypes = [vp, ci]
+        L.b200_ctx_set_force_path.restype = None
+        L.b200_device_info.argtypes = [ci, C.c_char_p, sz, C.c_char_p, sz, C.POINTER(ci), C.POINTER(ci), C.POINTER(ci)]
+        L.b200_host_malloc.argtypes = [sz, C.POINTER(vp)]
+        L.b200_host_free.argtypes = [vp]
+        for n in ("b200_quantize_q8_0", "b200_quantize_q8_1", "b200_quantize_q8_K"):
+            getattr(L, n).argtypes = [vp, vp, i64, i64, sz, vp]
+        L.b200_quantize_units.argtypes = [vp, ci, vp, i64, i64, sz, vp, vp]
+        L.b200_mul_mat_supported.argtypes = [C.POINTER(MulMatDesc)]
+        L.b200_mul_mat.argtypes = [vp, C.POINTER(MulMatDesc), vp, vp, vp]
+        L.b200_mul_mat_shared_src1.argtypes = [vp, ci, C.POINTER(MulMatDesc), C.POINTER(vp), vp, C.POINTER(vp)]
+        L.b200_mul_mat_host.argtypes = [vp, C.POINTER(MulMatDesc), vp, ci, vp, vp]
+        L.b200_mul_mat_id_supported.argtypes = [C.POINTER(MulMatIdDesc)]
+        L.b200_mul_mat_id.argtypes = [vp, C.POINTER(MulMatIdDesc), vp, vp, vp, vp]
+        L.b200_mm_ids_sort.argtypes = [vp, vp, i64, i64, sz, i64, vp, vp]
+        _lib = L
+    return _lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        raise B200Error(f"{what} failed (status {rc}): {lib().b200_last_error().decode(errors='replace')}")
+
+
+class Context:
+    """one device + one stream (a ggml_backend_t). By default launches on torch's current stream so torch events see it."""
+
+    def __init__(self, device: int = 0, use_torch_stream: bool = True):
+        import torch
+        if not torch.cuda.is_available():
+            raise B200Error("no CUDA device: ggml-b200 has no CPU fallback")
+        self.torch = torch
+        self.device = device
+        torch.cuda.set_device(device)
+        stream = torch.cuda.current_stream(device).cuda_stream if use_torch_stream else None
+        h = C.c_void_p()
+        check(lib().b200_ctx_create(device, C.c_void_p(stream) if stream else None, C.byref(h)), "b200_ctx_create")
+        self.h = h
+
+    def close(self):
+        if self.h:
+            lib().b200_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sync(self):
+        check(lib().b200_ctx_synchronize(self.h), "synchronize")
+
+    @property
+    def launches(self) -> int:
+        return int(lib().b200_ctx_launch_count(self.h))
+
+    def force_path(self, p: int):
+        lib().b200_ctx_set_force_path(self.h, p)
+
+    # ---- K1
+    def quantize(self, name: str, x):
+        """x: float32 cuda tensor [rows, k] (last dim contiguous) -> uint8 tensor [rows, row_bytes] in the reference block layout"""
+        torch = self.torch
+        sz = {"q8_0": (32, 34), "q8_1": (32, 36), "q8_K": (256, 292)}[name]
+        rows, k = x.shape
+        y = torch.empty((rows, k // sz[0] * sz[1]), dtype=torch.uint8, device=x.device)
+        f = getattr(lib(), f"b200_quantize_{name}")
+        check(f(self.h, x.data_ptr(), k, rows, x.stride(0) * 4, y.data_ptr()), f"b200_quantize_{name}")
+        return y
+
+    def quantize_units(self, kind: int, x):
+        torch = self.torch
+        rows, k = x.shape
+        u = k // 256
+        main = torch.empty((rows, u, 272), dtype=torch.uint8, device=x.device)
+        aux = torch.empty((rows, u, 16), dtype=torch.uint8, device=x.device)
+        check(lib().b200_quantize_units(self.h, kind, x.data_ptr(), k, rows, x.stride(0) * 4, main.data_ptr(), aux.data_ptr()),
+              "b200_quantize_units")
+        return main, aux
+
+    # ---- K3/K4
+    def mul_mat(self, t: int, W, X, out=None, desc: MulMatDesc | None = None):
+        """W: uint8 cuda tensor holding ggml blocks [M, row_bytes] (or [ne03, ne02, M, row_bytes]);
+        X: float32 [N, K] (or [ne13, ne12, N, K]); returns float32 [N, M] (or [ne13, ne12, N, M])"""
+        torch = self.torch
+        K = X.shape[-1]
+        if desc is None:
+            if X.dim() == 2:
+                M = W.numel() // row_size(t, K)
+                desc = MulMatDesc.contiguous(t, M, K, X.shape[0])
+                oshape = (X.shape[0], M)
+            else:
+                ne03, ne02, M = W.shape[0], W.shape[1], W.shape[2]
+                ne13, ne12, N = X.shape[0], X.shape[1], X.shape[2]
+                desc = MulMatDesc.contiguous(t, M, K, N, ne02, ne03, ne12, ne13)
+                oshape = (ne13, ne12, N, M)
+        else:
+            oshape = (desc.ne13, desc.ne12, desc.ne11, desc.ne01)
+        if out is None:
+            out = torch.empty(oshape, dtype=torch.float32, device=X.device)
+        check(lib().b200_mul_mat(self.h, C.byref(desc), W.data_ptr(), X.data_ptr(), out.data_ptr()), "b200_mul_mat")
+        return out
+
+    def mul_mat_shared(self, t: int, Ws, X, outs=None):
+        torch = self.torch
+        N, K = X.shape
+        n = len(Ws)
+        descs = (MulMatDesc * n)()
+        Ms = []
+        for i, W in enumerate(Ws):
+            M = W.numel() // row_size(t, K)
+            Ms.append(M)
+            descs[i] = MulMatDesc.contiguous(t, M, K, N)
+        if outs is None:
+            outs = [torch.empty((N, M), dtype=torch.float32, device=X.device) for M in Ms]
+        wp = (C.c_void_p * n)(*[W.data_ptr() for W in Ws])
+        op = (C.c_void_p * n)(*[o.data_ptr() for o in outs])
+        check(lib().b200_mul_mat_shared_src1(self.h, n, descs, wp, X.data_ptr(), op), "b200_mul_mat_shared_src1")
+        return outs
+
+    def mul_mat_host(self, desc: MulMatDesc, W_dev_ptr: int, x_host_ptr: int, y_host_ptr: int, w_on_device: bool = True):
+        check(lib().b200_mul_mat_host(self.h, C.byref(desc), W_dev_ptr, 1 if w_on_device else 0, x_host_ptr, y_host_ptr), "b200_mul_mat_host")
+
+    # ---- K5/K6
+    def mul_mat_id(self, t: int, W, B, ids, out=None):
+        """W uint8 [n_as, M, row_bytes]; B float32 [n_tok, ne11, K]; ids int32 [n_tok, n_used] -> float32 [n_tok, n_used, M]"""
+        torch = self.torch
+        n_tok, ne11, K = B.shape
+        n_as, M = W.shape[0], W.shape[1]
+        n_used = ids.shape[1]
+        desc = MulMatIdDesc.contiguous(t, M, K, n_as, n_used, ne11, n_tok)
+        if out is None:
+            out = torch.empty((n_tok, n_used, M), dtype=torch.float32, device=B.device)
+        check(lib().b200_mul_mat_id(self.h, C.byref(desc), W.data_ptr(), B.data_ptr(), ids.data_ptr(), out.data_ptr()), "b200_mul_mat_id")
+        return out
+
+    def mm_ids_sort(self, ids, n_as: int):
+        torch = self.torch
+        n_tok, n_used = ids.shape
+        sp = torch.empty(n_tok * n_used, dtype=torch.int32, device=ids.device)
+        eb = torch.empty(n_as + 1, dtype=torch.int32, device=ids.device)
+        check(lib().b200_mm_ids_sort(self.h, ids.data_ptr(), n_used, n_tok, 4 * n_used, n_as, sp.data_ptr(), eb.data_ptr()), "b200_mm_ids_sort")
+        return sp, eb
+
+
+def device_count() -> int:
+    return int(lib().b200_device_count())

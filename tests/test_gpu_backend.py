@@ -1,0 +1,66 @@
+"""GPU drop-in tests (pytest -m gpu): the ggml backend library loaded through the reference's own registry
+(ggml_backend_load -> ggml_backend_init) and driven through the reference's public API, plus the reference's
+conformance harness tests/test-backend-ops.cpp (compiled into oracle/_ref) pointed at it with GGML_BACKEND_PATH."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle.pyoracle import Q4_0, Q4_K, Q8_0, REF_DIR, have_ref
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def b200(pkg, harness):
+    if not pkg.BACKEND_PATH.exists():
+        pytest.fail("libggml-b200.so missing: build it with __graft_entry__.build()")
+    return harness.load(pkg.BACKEND_PATH)
+
+
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
+@pytest.mark.parametrize("M,K,N", [(64, 256, 1), (128, 1024, 4), (96, 4096, 1), (50, 512, 33)])
+def test_backend_mul_mat_matches_ggml_cpu(harness, refq, oracle, b200, t, M, K, N):
+    rng = np.random.default_rng(M + K + N + t)
+    W = refq.quantize_weights(t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    got, _ = harness.mul_mat(b200, t, W, X)
+    ref, _ = harness.mul_mat(harness.cpu("x64"), t, W, X, n_threads=4)
+    assert oracle.nmse(ref, got) <= 5e-4
+    assert oracle.nmse(ref, got) <= 1e-10
+
+
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
+def test_backend_mul_mat_id_matches_ggml_cpu(harness, refq, oracle, b200, t):
+    rng = np.random.default_rng(t)
+    n_as, M, K, n_used, n_tok = 8, 64, 512, 2, 7
+    W = refq.quantize_weights(t, rng.uniform(-1, 1, (n_as * M, K)).astype(np.float32)).reshape(n_as, M, -1)
+    B = rng.uniform(-1, 1, (n_tok, 1, K)).astype(np.float32)
+    ids = np.stack([rng.permutation(n_as)[:n_used] for _ in range(n_tok)]).astype(np.int32)
+    got, _ = harness.mul_mat_id(b200, t, W, B, ids)
+    ref, _ = harness.mul_mat_id(harness.cpu("x64"), t, W, B, ids, n_threads=4)
+    assert oracle.nmse(ref, got) <= 1e-10
+
+
+def run_tbo(pkg, *args, timeout=900):
+    env = dict(os.environ, GGML_BACKEND_PATH=str(pkg.BACKEND_PATH))
+    p = subprocess.run([str(REF_DIR / "test-backend-ops"), *args], env=env, capture_output=True, text=True, timeout=timeout)
+    return p.returncode, re.sub(r"\x1b\[[0-9;]*m", "", p.stdout + p.stderr)
+
+
+@pytest.mark.parametrize("op", ["MUL_MAT", "MUL_MAT_ID"])
+def test_reference_conformance_harness(pkg, op):
+    """test-backend-ops test -b B2000 -o <op>: every case the backend claims through supports_op must pass the reference's
+    own NMSE check against ggml-cpu; cases outside the hot path (f16/f32/other quants) are reported 'not supported'."""
+    if not have_ref() or not (REF_DIR / "test-backend-ops").exists():
+        pytest.skip("oracle/_ref/test-backend-ops not built")
+    rc, out = run_tbo(pkg, "test", "-b", "B2000", "-o", op)
+    tail = "\n".join(out.splitlines()[-25:])
+    assert "Backend B2000: OK" in out or re.search(r"\d+/\d+ tests passed", out), tail
+    m = re.search(r"(\d+)/(\d+) tests passed", out)
+    assert m, tail
+    assert m.group(1) == m.group(2), tail
+    assert int(m.group(2)) > 50, tail   # it really ran our quantized cases
+    assert rc == 0, tail

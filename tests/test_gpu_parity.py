@@ -1,0 +1,272 @@
+"""GPU parity tests (pytest -m gpu): every call goes through the C-ABI (libb200mm.so via ctypes); the oracle is only the checker.
+Bar: activation quantizer bit-exact; MUL_MAT / MUL_MAT_ID NMSE <= 5e-4 against ggml-cpu semantics
+(tests/test-backend-ops.cpp:3569-3571, 3697-3699 in the reference) — in practice ~1e-13 because the integer block sums are identical."""
+import glob
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from oracle.pyoracle import Q4_0, Q4_K, Q8_0, TYPE_NAMES, have_ref
+
+pytestmark = pytest.mark.gpu
+GOLD = Path(__file__).resolve().parent / "golden"
+NMSE_MAX = 5e-4          # the reference's own threshold
+NMSE_TIGHT = 1e-10       # what identical integer sums + fp32 reordering actually give
+
+
+def cu(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def quantize_weights(oracle, t, w):
+    if have_ref():
+        from oracle.pyoracle import RefQuant
+        return RefQuant().quantize_weights(t, w)
+    if t == Q4_K:
+        pytest.skip("q4_K weights need oracle/_ref")
+    return oracle.quantize("q4_0" if t == Q4_0 else "q8_0", w)
+
+
+def mask_q8k(a):
+    a = a.copy().reshape(a.shape[0], -1, 292)
+    zero = (a[:, :, :4].view(np.float32)[:, :, 0] == 0)
+    a[zero, 260:] = 0
+    return a
+
+
+# ---------------------------------------------------------------- K1
+
+def test_act_quant_golden_bit_exact(ctx):
+    g = np.load(GOLD / "act_quant.npz")
+    x = cu(g["x"])
+    for name in ("q8_0", "q8_1", "q8_K"):
+        got = ctx.quantize(name, x).cpu().numpy()
+        ref = g[name]
+        if name == "q8_K":
+            got, ref = mask_q8k(got), mask_q8k(ref)
+        assert np.array_equal(got, ref), name
+
+
+@pytest.mark.parametrize("k", [32, 96, 256, 4096, 14336])
+def test_act_quant_vs_oracle(ctx, oracle, k):
+    rng = np.random.default_rng(k)
+    x = (rng.standard_normal((9, k)) * rng.choice([1e-4, 1.0, 300.0], (9, 1))).astype(np.float32)
+    x[0, :32] = 0
+    for name in ("q8_0", "q8_1") + (("q8_K",) if k % 256 == 0 else ()):
+        got = ctx.quantize(name, cu(x)).cpu().numpy()
+        ref = oracle.quantize(name, x)
+        if name == "q8_K":
+            got, ref = mask_q8k(got), mask_q8k(ref)
+        assert np.array_equal(got, ref), (name, k)
+
+
+def test_act_quant_strided_rows(ctx, oracle):
+    import torch
+    rng = np.random.default_rng(5)
+    big = rng.uniform(-1, 1, (6, 1024 + 36)).astype(np.float32)
+    xb = cu(big)
+    view = xb[:, 4:4 + 1024]                       # row stride 1060 floats, base offset 16 B... and
+    got = ctx.quantize("q8_0", view).cpu().numpy()
+    assert np.array_equal(got, oracle.quantize("q8_0", big[:, 4:4 + 1024]))
+    view = xb[:, 1:1 + 1024]                       # only 4-byte aligned: scalar-load path
+    got = ctx.quantize("q8_K", view).cpu().numpy()
+    assert np.array_equal(mask_q8k(got), mask_q8k(oracle.quantize("q8_K", big[:, 1:1 + 1024])))
+
+
+def test_unit_records_hold_the_same_values(ctx, oracle):
+    rng = np.random.default_rng(11)
+    x = rng.uniform(-2, 2, (5, 1024)).astype(np.float32)
+    # kind 0: q8_0 values
+    main, aux = ctx.quantize_units(0, cu(x))
+    main, aux = main.cpu().numpy(), aux.cpu().numpy()
+    ref = oracle.quantize("q8_0", x).reshape(5, -1, 34)
+    q = main[:, :, :256].reshape(5, -1, 32)
+    assert np.array_equal(q, ref[:, :, 2:])
+    assert np.array_equal(main[:, :, 256:].reshape(5, -1, 2), ref[:, :, :2])
+    sums = aux.view(np.int16).reshape(5, -1)
+    assert np.array_equal(sums, ref[:, :, 2:].view(np.int8).astype(np.int32).sum(-1).astype(np.int16))
+    # kind 1: q8_K values
+    main, aux = ctx.quantize_units(1, cu(x))
+    main, aux = main.cpu().numpy(), aux.cpu().numpy()
+    ref = oracle.quantize("q8_K", x).reshape(5, -1, 292)
+    assert np.array_equal(main[:, :, :256], ref[:, :, 4:260])
+    assert np.array_equal(aux[:, :, :4], ref[:, :, :4])
+    bs16 = ref[:, :, 260:].view(np.int16).astype(np.int32).reshape(5, -1, 8, 2).sum(-1).astype(np.int16)
+    assert np.array_equal(main[:, :, 256:].view(np.int16), bs16)
+
+
+# ---------------------------------------------------------------- K3 on golden fixtures
+
+@pytest.mark.parametrize("f", sorted(glob.glob(str(GOLD / "mul_mat_q*_*x*.npz"))))
+def test_mul_mat_golden(ctx, oracle, f):
+    g = np.load(f)
+    t = int(g["type"])
+    got = ctx.mul_mat(t, cu(g["W"]), cu(g["X"])).cpu().numpy()
+    assert oracle.nmse(g["out"], got) <= NMSE_TIGHT
+
+
+def test_mul_mat_bcast_golden(ctx, oracle):
+    g = np.load(GOLD / "mul_mat_q4_K_bcast.npz")
+    W = g["W"].reshape(1, 2, -1, g["W"].shape[-1])
+    got = ctx.mul_mat(int(g["type"]), cu(W), cu(g["X"])).cpu().numpy()
+    assert oracle.nmse(g["out"], got) <= NMSE_TIGHT
+
+
+@pytest.mark.parametrize("f", sorted(glob.glob(str(GOLD / "mul_mat_id_*.npz"))))
+def test_mul_mat_id_golden(ctx, oracle, f):
+    g = np.load(f)
+    got = ctx.mul_mat_id(int(g["type"]), cu(g["W"]), cu(g["B"]), cu(g["ids"])).cpu().numpy()
+    assert oracle.nmse(g["out"], got) <= NMSE_TIGHT
+
+
+# ---------------------------------------------------------------- K3 against the oracle, seeded
+
+SHAPES = [  # (M, K): K/256 = 1, 2, 3 (L=4, one idle lane group), 16 (two rows per warp), 24 (idle lanes), 56 (two slices)
+    (67, 256), (130, 512), (33, 768), (96, 4096), (40, 6144), (24, 14336),
+]
+
+
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
+@pytest.mark.parametrize("M,K", SHAPES)
+@pytest.mark.parametrize("N", [1, 2, 5, 8])
+def test_mul_mat_vs_oracle(ctx, oracle, t, M, K, N):
+    if K >= 4096 and N in (2, 5):
+        pytest.skip("covered by the smaller K")
+    rng = np.random.default_rng(M * 131 + K + N + t)
+    W = quantize_weights(oracle, t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    got = ctx.mul_mat(t, cu(W), cu(X)).cpu().numpy()
+    assert oracle.nmse(oracle.mul_mat(t, W, X), got) <= NMSE_TIGHT
+
+
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
+@pytest.mark.parametrize("N", [9, 17, 64])
+def test_mul_mat_more_than_8_columns(ctx, oracle, t, N):
+    rng = np.random.default_rng(N + t)
+    M, K = 100, 1024
+    W = quantize_weights(oracle, t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    got = ctx.mul_mat(t, cu(W), cu(X)).cpu().numpy()
+    assert oracle.nmse(oracle.mul_mat(t, W, X), got) <= NMSE_TIGHT
+
+
+@pytest.mark.parametrize("t,K", [(Q4_0, 32), (Q4_0, 96), (Q8_0, 160), (Q8_0, 1056), (Q4_0, 4128)])
+def test_generic_kernel_for_k_not_multiple_of_256(ctx, oracle, t, K):
+    rng = np.random.default_rng(K)
+    M, N = 37, 3
+    W = quantize_weights(oracle, t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    got = ctx.mul_mat(t, cu(W), cu(X)).cpu().numpy()
+    assert oracle.nmse(oracle.mul_mat(t, W, X), got) <= NMSE_TIGHT
+
+
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
+def test_fast_and_generic_kernels_agree(ctx, pkg, oracle, t):
+    """two independent CUDA implementations of the same integer arithmetic"""
+    rng = np.random.default_rng(3 + t)
+    M, K, N = 200, 2048, 4
+    W = quantize_weights(oracle, t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    a = ctx.mul_mat(t, cu(W), cu(X)).cpu().numpy()
+    ctx.force_path(pkg.PATH_SIMPLE)
+    try:
+        b = ctx.mul_mat(t, cu(W), cu(X)).cpu().numpy()
+    finally:
+        ctx.force_path(pkg.PATH_AUTO)
+    assert oracle.nmse(a, b) <= NMSE_TIGHT
+    assert oracle.nmse(oracle.mul_mat(t, W, X), b) <= NMSE_TIGHT
+
+
+def test_empty_and_degenerate(ctx, pkg, oracle):
+    import torch
+    W = quantize_weights(oracle, Q4_0, np.ones((4, 256), dtype=np.float32))
+    X = torch.zeros((0, 256), dtype=torch.float32, device="cuda")
+    out = ctx.mul_mat(Q4_0, cu(W), X)
+    assert out.shape == (0, 4)
+    # all-zero activations and all-zero weights give exact zeros
+    Z = quantize_weights(oracle, Q4_0, np.zeros((4, 256), dtype=np.float32))
+    assert float(ctx.mul_mat(Q4_0, cu(Z), cu(np.ones((2, 256), dtype=np.float32))).abs().max()) == 0.0
+    assert float(ctx.mul_mat(Q4_0, cu(W), cu(np.zeros((2, 256), dtype=np.float32))).abs().max()) == 0.0
+
+
+def test_strided_weight_view(ctx, pkg, oracle):
+    """src0 as a view: rows taken out of a wider tensor (nb01 > row size), as the reference's k_v cases do"""
+    rng = np.random.default_rng(77)
+    M, K, KV, N = 20, 512, 1024, 2
+    Wfull = quantize_weights(oracle, Q8_0, rng.uniform(-1, 1, (M, KV)).astype(np.float32))   # rows of KV
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    rb, rbv = pkg.row_size(Q8_0, K), pkg.row_size(Q8_0, KV)
+    d = pkg.MulMatDesc.contiguous(Q8_0, M, K, N)
+    d.nb01, d.nb02, d.nb03 = rbv, rbv * M, rbv * M
+    got = ctx.mul_mat(Q8_0, cu(Wfull), cu(X), desc=d).cpu().numpy()[0, 0]
+    ref = oracle.mul_mat(Q8_0, np.ascontiguousarray(Wfull[:, :rb]), X)
+    assert oracle.nmse(ref, got) <= NMSE_TIGHT
+
+
+@pytest.mark.parametrize("t", [Q4_0, Q4_K])
+def test_shared_src1_fusion(ctx, oracle, t):
+    rng = np.random.default_rng(9)
+    K, N = 1024, 2
+    Ws = [quantize_weights(oracle, t, rng.uniform(-1, 1, (M, K)).astype(np.float32)) for M in (64, 16, 16, 200, 8)]
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    outs = ctx.mul_mat_shared(t, [cu(W) for W in Ws], cu(X))
+    for W, o in zip(Ws, outs):
+        assert oracle.nmse(oracle.mul_mat(t, W, X), o.cpu().numpy()) <= NMSE_TIGHT
+
+
+# ---------------------------------------------------------------- K5/K6
+
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
+@pytest.mark.parametrize("n_as,n_used,bcast,n_tok", [(4, 1, 1, 1), (8, 2, 1, 1), (8, 4, 0, 5), (4, 2, 1, 17), (8, 2, 0, 32)])
+def test_mul_mat_id_vs_oracle(ctx, oracle, t, n_as, n_used, bcast, n_tok):
+    """the shapes of the reference's own cases (tests/test-backend-ops.cpp:7394-7407: m=512, k=256), scaled down in m"""
+    rng = np.random.default_rng(n_as * 7 + n_used + n_tok + t)
+    M, K = 96, 256
+    W = quantize_weights(oracle, t, rng.uniform(-1, 1, (n_as * M, K)).astype(np.float32)).reshape(n_as, M, -1)
+    B = rng.uniform(-1, 1, (n_tok, 1 if bcast else n_used, K)).astype(np.float32)
+    ids = np.stack([rng.permutation(n_as)[:n_used] for _ in range(n_tok)]).astype(np.int32)
+    got = ctx.mul_mat_id(t, cu(W), cu(B), cu(ids)).cpu().numpy()
+    assert oracle.nmse(oracle.mul_mat_id(t, W, B, ids), got) <= NMSE_TIGHT
+
+
+def test_mm_ids_sort(ctx):
+    rng = np.random.default_rng(4)
+    for n_as, n_used, n_tok in ((8, 2, 1), (8, 2, 64), (128, 8, 33), (4, 4, 129)):
+        ids = np.stack([rng.permutation(n_as)[:n_used] for _ in range(n_tok)]).astype(np.int32)
+        sp, eb = ctx.mm_ids_sort(cu(ids), n_as)
+        sp, eb = sp.cpu().numpy(), eb.cpu().numpy()
+        flat = ids.reshape(-1)
+        order = np.argsort(flat, kind="stable")
+        assert np.array_equal(sp, order.astype(np.int32))
+        assert np.array_equal(eb, np.concatenate([[0], np.cumsum(np.bincount(flat, minlength=n_as))]).astype(np.int32))
+
+
+# ---------------------------------------------------------------- full-size properties (sizes the oracle cannot run in seconds)
+
+@pytest.mark.parametrize("t", [Q4_0, Q4_K, Q8_0])
+def test_full_size_properties(ctx, pkg, oracle, t):
+    """Llama-3-8B FFN shape 14336x4096: (1) a random sample of rows equals the oracle, (2) column c of an 8-column call is
+    bit-identical to the 1-column call on that column, (3) the generic kernel agrees on the whole output."""
+    import torch
+    rng = np.random.default_rng(31 + t)
+    M, K, N = 14336, 4096, 8
+    # quantize a slab with the reference quantizer and tile it (quantizing 58M weights on the host takes too long)
+    slab = quantize_weights(oracle, t, rng.uniform(-1, 1, (512, K)).astype(np.float32))
+    perm = rng.permutation(M) % 512
+    W = np.ascontiguousarray(slab[perm])
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    Wd, Xd = cu(W), cu(X)
+    full = ctx.mul_mat(t, Wd, Xd)
+    rows = rng.choice(M, 64, replace=False)
+    ref = oracle.mul_mat(t, np.ascontiguousarray(W[rows]), X)
+    assert oracle.nmse(ref, full[:, rows].cpu().numpy()) <= NMSE_TIGHT
+    one = ctx.mul_mat(t, Wd, Xd[3:4].contiguous())
+    assert torch.equal(one[0], full[3])
+    ctx.force_path(pkg.PATH_SIMPLE)
+    try:
+        gen = ctx.mul_mat(t, Wd, Xd)
+    finally:
+        ctx.force_path(pkg.PATH_AUTO)
+    assert oracle.nmse(gen.cpu().numpy(), full.cpu().numpy()) <= NMSE_TIGHT
