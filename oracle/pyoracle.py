@@ -142,7 +142,7 @@ class RefQuant:
         p = REF_DIR / "libggml-base.so"
         if not p.exists():
             raise FileNotFoundError(f"{p} missing — run `make -C oracle ref` where /root/reference exists")
-        L = self.lib = C.CDLL(str(p), mode=C.RTLD_GLOBAL)
+        L = self.lib = C.CDLL(str(p))
         for n in ("q8_0", "q8_1", "q8_K", "q4_0", "q4_K"):
             f = getattr(L, f"quantize_row_{n}_ref")
             f.restype = None
@@ -193,8 +193,7 @@ class RefHarness:
         for n in ("libggml-base.so", "libggml.so", "libref_harness.so"):
             if not (REF_DIR / n).exists():
                 raise FileNotFoundError(f"{REF_DIR / n} missing — run `make -C oracle ref` where /root/reference exists")
-        C.CDLL(str(REF_DIR / "libggml-base.so"), mode=C.RTLD_GLOBAL)
-        C.CDLL(str(REF_DIR / "libggml.so"), mode=C.RTLD_GLOBAL)
+        # RTLD_LOCAL: libref_harness.so finds both through DT_NEEDED + rpath; nothing of ggml's goes into the global scope
         L = self.lib = C.CDLL(str(REF_DIR / "libref_harness.so"))
         L.refh_load_backend.restype = C.c_int
         L.refh_load_backend.argtypes = [C.c_char_p]
