@@ -171,11 +171,14 @@ B200_API b200_status  b200_mm_ids_sort(b200_ctx * ctx, const int32_t * ids, int6
 /* ---------------------------------------------------------------- prefill weight cache ---- */
 
 /* The tcgen05 path consumes an int8, K-major, TMA-tileable expansion of a weight matrix plus per-32 float scales
- * (the load-time analogue of ggml-cpu's repack buffer type, ggml-cpu/repack.cpp). It is built on first use per
- * (src0 pointer, geometry) and dropped with these calls (buffer free / set_tensor on the range). */
-B200_API void         b200_weight_cache_invalidate(b200_ctx * ctx, const void * base, size_t size);
-B200_API void         b200_weight_cache_clear(b200_ctx * ctx);
-B200_API size_t       b200_weight_cache_bytes(const b200_ctx * ctx);
+ * (the load-time analogue of ggml-cpu's repack buffer type, ggml-cpu/repack.cpp). By default it is rebuilt on every
+ * call in scratch memory. A caller that owns the weight memory and reports every write to it (the ggml backend's
+ * buffer: set_tensor / memset_tensor / clear / cpy_tensor / free_buffer) may switch a context to keep one expansion
+ * per weight matrix (keyed by device + src0 pointer) and must then invalidate overwritten or freed ranges. */
+B200_API void         b200_ctx_set_weight_cache(b200_ctx * ctx, int enable);
+B200_API void         b200_weight_cache_invalidate(int device, const void * base, size_t size);
+B200_API void         b200_weight_cache_clear(int device);
+B200_API size_t       b200_weight_cache_bytes(void);
 
 #ifdef __cplusplus
 }

@@ -209,7 +209,7 @@ class RefHarness:
         L.refh_mul_mat_id.argtypes = [C.c_int] * 4 + [C.c_int64] * 6 + [C.c_void_p] * 4 + [C.c_double, C.POINTER(C.c_double)]
         L.refh_mul_mat_stack.restype = C.c_int
         L.refh_mul_mat_stack.argtypes = [C.c_int] * 5 + [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
-                                                        C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_int)]
+                                                        C.c_double, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         self._loaded = {}
 
     @classmethod
@@ -287,13 +287,14 @@ class RefHarness:
         return out, (us.value if seconds > 0 else None)
 
     def mul_mat_stack(self, reg: int, t: int, shapes, N: int, W_all: np.ndarray, X_all: np.ndarray, n_threads=0,
-                      dev=0, seconds=1.0):
+                      dev=0, seconds=1.0, reps=1):
+        """times the stack of MUL_MATs as ONE graph holding `reps` repetitions of it; returns (us per repetition, repetitions run)"""
         Ms = np.array([s[0] for s in shapes], dtype=np.int64)
         Ks = np.array([s[1] for s in shapes], dtype=np.int64)
         us = C.c_double(0)
         runs = C.c_int(0)
         rc = self.lib.refh_mul_mat_stack(reg, dev, n_threads, t, len(shapes), _ptr(Ms), _ptr(Ks), N,
-                                         _ptr(W_all), _ptr(X_all), seconds, C.byref(us), C.byref(runs))
+                                         _ptr(W_all), _ptr(X_all), seconds, int(reps), C.byref(us), C.byref(runs))
         if rc:
             raise RuntimeError(f"refh_mul_mat_stack rc={rc}")
         return us.value, runs.value

@@ -23,19 +23,41 @@
 
 namespace {
 
+typedef ggml_threadpool_t (*threadpool_new_t)(struct ggml_threadpool_params *);
+typedef void (*threadpool_free_t)(ggml_threadpool_t);
+typedef void (*set_threadpool_t)(ggml_backend_t, ggml_threadpool_t);
+
 struct graph_run {
     ggml_context *        ctx   = nullptr;
     ggml_backend_t        be    = nullptr;
     ggml_backend_buffer_t buf   = nullptr;
     ggml_cgraph *         graph = nullptr;
+    ggml_threadpool_t     tp    = nullptr;
+    threadpool_free_t     tp_free = nullptr;
     ~graph_run() {
         if (buf) ggml_backend_buffer_free(buf);
         if (be) ggml_backend_free(be);
+        if (tp && tp_free) tp_free(tp);
         if (ctx) ggml_free(ctx);
     }
 };
 
 std::vector<ggml_backend_reg_t> g_regs;
+
+// A persistent thread pool for the CPU backend, attached the way llama.cpp's own tools do (common/common.cpp,
+// tools/llama-bench): without one, ggml-cpu creates and joins its worker threads inside every graph_compute.
+void attach_threadpool(graph_run & g, int reg_index, int n_threads) {
+    if (n_threads <= 1 || reg_index < 0 || reg_index >= (int) g_regs.size() || !g.be) return;
+    ggml_backend_reg_t reg = g_regs[reg_index];
+    auto tp_new  = (threadpool_new_t) ggml_backend_reg_get_proc_address(reg, "ggml_threadpool_new");
+    auto tp_free = (threadpool_free_t) ggml_backend_reg_get_proc_address(reg, "ggml_threadpool_free");
+    auto tp_set  = (set_threadpool_t) ggml_backend_reg_get_proc_address(reg, "ggml_backend_cpu_set_threadpool");
+    if (!tp_new || !tp_free || !tp_set) return;
+    ggml_threadpool_params tpp = ggml_threadpool_params_default(n_threads);
+    g.tp = tp_new(&tpp);
+    g.tp_free = tp_free;
+    if (g.tp) tp_set(g.be, g.tp);
+}
 
 ggml_backend_t open_backend(int reg_index, int dev_index, int n_threads) {
     if (reg_index < 0 || reg_index >= (int) g_regs.size()) return nullptr;
@@ -108,6 +130,7 @@ int refh_mul_mat(int reg, int dev, int n_threads, int type, int64_t M, int64_t K
     graph_run g;
     g.be = open_backend(reg, dev, n_threads);
     if (!g.be || !make_ctx(g)) return 1;
+    if (seconds > 0) attach_threadpool(g, reg, n_threads);
     ggml_tensor * w = ggml_new_tensor_4d(g.ctx, (ggml_type) type, K, M, ne02, ne03);
     ggml_tensor * x = ggml_new_tensor_4d(g.ctx, GGML_TYPE_F32, K, N, ne12, ne13);
     ggml_tensor * o = ggml_mul_mat(g.ctx, w, x);
@@ -130,6 +153,7 @@ int refh_mul_mat_id(int reg, int dev, int n_threads, int type, int64_t M, int64_
     graph_run g;
     g.be = open_backend(reg, dev, n_threads);
     if (!g.be || !make_ctx(g)) return 1;
+    if (seconds > 0) attach_threadpool(g, reg, n_threads);
     ggml_tensor * w = ggml_new_tensor_3d(g.ctx, (ggml_type) type, K, M, n_as);
     ggml_tensor * b = ggml_new_tensor_3d(g.ctx, GGML_TYPE_F32, K, ne11, n_tok);
     ggml_tensor * i = ggml_new_tensor_2d(g.ctx, GGML_TYPE_I32, n_used, n_tok);
@@ -149,22 +173,31 @@ int refh_mul_mat_id(int reg, int dev, int n_threads, int type, int64_t M, int64_
 // A stack of `n_mats` independent MUL_MATs in ONE graph (distinct weight tensors, one shared or per-op
 // activation), the CPU-baseline counterpart of bench.py's layer-stack step. Ms/Ks give each matrix' shape.
 // Weights: W_all is the concatenation of the matrices' bytes. Returns us per graph run in *us_per_run.
+// `reps` repeats the whole stack inside the graph (fresh result tensors over the same inputs), as eval_perf duplicates its
+// node (tests/test-backend-ops.cpp:1449-1515), so that one graph_compute is long against the thread pool's wake-up cost;
+// *us_per_run is per repetition.
 int refh_mul_mat_stack(int reg, int dev, int n_threads, int type, int n_mats, const int64_t * Ms, const int64_t * Ks,
-                       int64_t N, const void * W_all, const float * X_all, double seconds, double * us_per_run, int * runs) {
+                       int64_t N, const void * W_all, const float * X_all, double seconds, int reps, double * us_per_run, int * runs) {
+    if (reps < 1) reps = 1;
     graph_run g;
     g.be = open_backend(reg, dev, n_threads);
     if (!g.be) return 1;
-    ggml_init_params ip = { ggml_tensor_overhead() * (size_t) (4 * n_mats + 16) + ggml_graph_overhead_custom(4 * n_mats + 16, false), nullptr, true };
+    attach_threadpool(g, reg, n_threads);
+    const size_t n_nodes = (size_t) (2 + reps) * n_mats + 16;
+    ggml_init_params ip = { ggml_tensor_overhead() * n_nodes + ggml_graph_overhead_custom(n_nodes, false), nullptr, true };
     g.ctx = ggml_init(ip);
     if (!g.ctx) return 1;
     std::vector<ggml_tensor *> ws(n_mats), xs(n_mats), os(n_mats);
-    g.graph = ggml_new_graph_custom(g.ctx, 4 * n_mats + 16, false);
+    g.graph = ggml_new_graph_custom(g.ctx, n_nodes, false);
     for (int i = 0; i < n_mats; i++) {
         ws[i] = ggml_new_tensor_2d(g.ctx, (ggml_type) type, Ks[i], Ms[i]);
         xs[i] = ggml_new_tensor_2d(g.ctx, GGML_TYPE_F32, Ks[i], N);
-        os[i] = ggml_mul_mat(g.ctx, ws[i], xs[i]);
-        ggml_build_forward_expand(g.graph, os[i]);
     }
+    for (int r = 0; r < reps; r++)
+        for (int i = 0; i < n_mats; i++) {
+            os[i] = ggml_mul_mat(g.ctx, ws[i], xs[i]);
+            ggml_build_forward_expand(g.graph, os[i]);
+        }
     g.buf = ggml_backend_alloc_ctx_tensors(g.ctx, g.be);
     if (!g.buf) return 3;
     const char *  wp = (const char *) W_all;
@@ -175,7 +208,8 @@ int refh_mul_mat_stack(int reg, int dev, int n_threads, int type, int n_mats, co
         wp += ggml_nbytes(ws[i]);
         xp += Ks[i] * N;
     }
-    *us_per_run = time_graph(g, seconds, runs);
+    *us_per_run = time_graph(g, seconds, runs) / reps;
+    if (runs) *runs *= reps;
     return 0;
 }
 

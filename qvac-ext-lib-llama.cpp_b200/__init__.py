@@ -31,7 +31,7 @@ EXPORTS = [
     "b200_event_create", "b200_event_destroy", "b200_event_record", "b200_event_wait", "b200_event_synchronize",
     "b200_event_elapsed_ms", "b200_quantize_q8_0", "b200_quantize_q8_1", "b200_quantize_q8_K", "b200_quantize_units",
     "b200_mul_mat_supported", "b200_mul_mat", "b200_mul_mat_shared_src1", "b200_mul_mat_host", "b200_mul_mat_id_supported",
-    "b200_mul_mat_id", "b200_mm_ids_sort", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
+    "b200_mul_mat_id", "b200_mm_ids_sort", "b200_ctx_set_weight_cache", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
 ]
 
 
@@ -114,6 +114,16 @@ def lib() -> C.CDLL:
         L.b200_mul_mat_id_supported.argtypes = [C.POINTER(MulMatIdDesc)]
         L.b200_mul_mat_id.argtypes = [vp, C.POINTER(MulMatIdDesc), vp, vp, vp, vp]
         L.b200_mm_ids_sort.argtypes = [vp, vp, i64, i64, sz, i64, vp, vp]
+        for n in ("b200_memcpy_h2d_async", "b200_memcpy_d2h_async", "b200_memcpy_d2d_async"):
+            getattr(L, n).argtypes = [vp, vp, vp, sz]
+        L.b200_ctx_set_weight_cache.argtypes = [vp, ci]
+        L.b200_ctx_set_weight_cache.restype = None
+        L.b200_weight_cache_invalidate.argtypes = [ci, vp, sz]
+        L.b200_weight_cache_invalidate.restype = None
+        L.b200_weight_cache_clear.argtypes = [ci]
+        L.b200_weight_cache_clear.restype = None
+        L.b200_weight_cache_bytes.argtypes = []
+        L.b200_weight_cache_bytes.restype = sz
         _lib = L
     return _lib
 
@@ -133,7 +143,9 @@ class Context:
         self.torch = torch
         self.device = device
         torch.cuda.set_device(device)
-        stream = torch.cuda.current_stream(device).cuda_stream if use_torch_stream else None
+        # torch's default stream has handle 0, which the C-ABI reads as "create a stream": name the legacy default stream
+        # explicitly (cudaStreamLegacy == 1) so that torch's copies and .cpu() reads stay ordered with our launches
+        stream = (torch.cuda.current_stream(device).cuda_stream or 1) if use_torch_stream else None
         h = C.c_void_p()
         check(lib().b200_ctx_create(device, C.c_void_p(stream) if stream else None, C.byref(h)), "b200_ctx_create")
         self.h = h
@@ -158,6 +170,20 @@ class Context:
 
     def force_path(self, p: int):
         lib().b200_ctx_set_force_path(self.h, p)
+
+    def weight_cache(self, enable: bool):
+        """keep int8 expansions of weight matrices across calls; the caller must invalidate ranges it overwrites or frees"""
+        lib().b200_ctx_set_weight_cache(self.h, 1 if enable else 0)
+
+    def weight_cache_clear(self):
+        lib().b200_weight_cache_clear(self.device)
+
+    # ---- iface.set_tensor_async / get_tensor_async on the context's stream
+    def h2d_async(self, dst_dev_ptr: int, src_host_ptr: int, nbytes: int):
+        check(lib().b200_memcpy_h2d_async(self.h, dst_dev_ptr, src_host_ptr, nbytes), "b200_memcpy_h2d_async")
+
+    def d2h_async(self, dst_host_ptr: int, src_dev_ptr: int, nbytes: int):
+        check(lib().b200_memcpy_d2h_async(self.h, dst_host_ptr, src_dev_ptr, nbytes), "b200_memcpy_d2h_async")
 
     # ---- K1
     def quantize(self, name: str, x):

@@ -108,6 +108,10 @@ b200_status b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     }
     if (const char * s = getenv("GGML_B200_MV_WARPS")) c->mv_warps = atoi(s);
     if (const char * s = getenv("GGML_B200_MV_STAGES")) c->mv_stages = atoi(s);
+    if (const char * s = getenv("GGML_B200_PDL")) c->pdl = atoi(s) != 0;
+    if (const char * s = getenv("GGML_B200_MMQ_MIN")) c->mmq_min_cols = atoi(s);
+    if (const char * s = getenv("GGML_B200_WEIGHT_CACHE")) c->weight_cache = atoi(s) != 0;
+    if (const char * s = getenv("GGML_B200_FUSE_QUANT")) c->fuse_quant = atoi(s) != 0;
     *out = c;
     return B200_OK;
 }
@@ -127,6 +131,7 @@ int          b200_ctx_device(const b200_ctx * ctx) { return ctx->device; }
 void *       b200_ctx_stream(const b200_ctx * ctx) { return (void *) ctx->stream; }
 uint64_t     b200_ctx_launch_count(const b200_ctx * ctx) { return ctx->launches; }
 void         b200_ctx_set_force_path(b200_ctx * ctx, int path) { ctx->force_path = path; }
+void         b200_ctx_set_weight_cache(b200_ctx * ctx, int enable) { ctx->weight_cache = enable != 0; }
 b200_status  b200_ctx_synchronize(b200_ctx * ctx) {
     CU(cudaSetDevice(ctx->device));
     CU(cudaStreamSynchronize(ctx->stream));
@@ -286,16 +291,28 @@ int b200_mul_mat_supported(const b200_mul_mat_desc * d) {
 
 struct mv_cfg { int nw, ns; size_t smem; };
 
+// Two CTAs of <= 113 KB fit one SM (228 KB, 1 KB reserved per CTA): with that budget the next mat-vec kernel of the stream
+// becomes co-resident (programmatic dependent launch) and streams its first stages while this one computes. Configurations
+// beyond it get the SM to themselves.
+static const size_t MV_SMEM_CORESIDENT = 113 * 1024;
+static const size_t MV_SMEM_MAX        = 227 * 1024;
+
 static bool pick_mv_cfg(const b200_ctx * ctx, int type, int U, int nc, mv_cfg * out) {
-    static const int cand[][2] = { { 8, 4 }, { 8, 3 }, { 8, 2 }, { 4, 4 }, { 4, 3 }, { 4, 2 }, { 2, 2 }, { 1, 2 } };
-    const size_t lim = 227 * 1024;
-    if (ctx->mv_warps > 0 && ctx->mv_stages > 0) {
+    if (ctx->mv_warps > 0 && ctx->mv_stages > 0 && ctx->mv_warps <= MV_MAX_CONS) {
         const size_t s = mv_fast_smem(type, U, nc, ctx->mv_warps, ctx->mv_stages);
-        if (s <= lim && ctx->mv_warps <= 8) { *out = { ctx->mv_warps, ctx->mv_stages, s }; return true; }
+        if (s <= MV_SMEM_MAX) { *out = { ctx->mv_warps, ctx->mv_stages, s }; return true; }
     }
-    for (auto & c : cand) {
+    static const int small[][2] = { { 8, 3 }, { 8, 2 } };
+    if (nc <= 4) {  // the <= 4 column instantiations are compiled for two CTAs per SM (<= 112 registers)
+        for (auto & c : small) {
+            const size_t s = mv_fast_smem(type, U, nc, c[0], c[1]);
+            if (s <= MV_SMEM_CORESIDENT) { *out = { c[0], c[1], s }; return true; }
+        }
+    }
+    static const int big[][2] = { { 8, 4 }, { 8, 3 }, { 8, 2 }, { 6, 2 }, { 4, 2 }, { 2, 2 }, { 1, 2 } };
+    for (auto & c : big) {
         const size_t s = mv_fast_smem(type, U, nc, c[0], c[1]);
-        if (s <= lim) { *out = { c[0], c[1], s }; return true; }
+        if (s <= MV_SMEM_MAX) { *out = { c[0], c[1], s }; return true; }
     }
     return false;
 }
@@ -316,10 +333,14 @@ static bool fast_layout_ok(int type, int64_t K, const void * w, size_t nb01, siz
     return K % 256 == 0 && (uintptr_t) w % 16 == 0 && nb01 % 16 == 0 && nb02 % 16 == 0 && nb03 % 16 == 0;
 }
 
-// run `n_ops` matrices (same type, K) against `ncols` (<= 8) already-quantized unit-record columns
+// the mat-vec kernel quantizes src1 itself (no K1 launch, no scratch round trip) while the per-CTA redundancy is small
+static bool mv_fuse_quant(const b200_ctx * ctx, int U, int64_t ncols) { return ctx->fuse_quant && ncols <= MV_MAX_COLS && ncols * U <= 64; }
+
+// run `n_ops` matrices (same type, K) against `ncols` activation columns: either F32 columns x (+ c*x_cs bytes), quantized
+// inside the kernel, or already-quantized unit-record columns (act_main / act_aux)
 static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, const uint8_t * const * ws, const size_t * nb01s,
                                const int64_t * Ms, float * const * dsts, const int64_t * dst_cs, int ncols,
-                               const uint8_t * act_main, const uint8_t * act_aux) {
+                               const float * x, size_t x_cs, const uint8_t * act_main, const uint8_t * act_aux) {
     const int U = (int) (K / 256);
     for (int c0 = 0; c0 < ncols;) {
         int     nc = ncols - c0 < MV_MAX_COLS ? ncols - c0 : MV_MAX_COLS;
@@ -344,10 +365,18 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
             for (int i = p.n_mats; i < MV_MAX_MATS; i++) p.mat[i].group0 = INT32_MAX;
             p.total_groups = g;
             if (g == 0) continue;
-            p.n_warps  = cfg.nw;
+            p.n_cons   = cfg.nw;
             p.n_stages = cfg.ns;
-            p.act_main = act_main + (size_t) c0 * U * ACT_MAIN;
-            p.act_aux  = act_aux + (size_t) c0 * U * ACT_AUX;
+            p.pdl      = ctx->pdl;
+            if (x) {
+                p.fuse_quant = 1;
+                p.x          = (const float *) ((const char *) x + (size_t) c0 * x_cs);
+                p.x_cs       = (int64_t) x_cs;
+                p.x_vec      = (uintptr_t) p.x % 16 == 0 && x_cs % 16 == 0;
+            } else {
+                p.act_main = act_main + (size_t) c0 * U * ACT_MAIN;
+                p.act_aux  = act_aux + (size_t) c0 * U * ACT_AUX;
+            }
             const int n_ctas = g < ctx->sm_count ? g : ctx->sm_count;
             CU(mv_fast_launch(type, nc, p, n_ctas, 1, cfg.smem, ctx->stream));
             ctx->launches++;
@@ -365,6 +394,25 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
     if (N == 0 || d.ne01 == 0) return B200_OK;
     CU(cudaSetDevice(ctx->device));
 
+    // more columns than the mat-vec kernels hold in registers: the tcgen05 int8 tile kernel (K4)
+    const int64_t mmq_min = ctx->mmq_min_cols > 0 ? ctx->mmq_min_cols : (ctx->weight_cache ? 9 : 33);
+    bool mmq = ctx->force_path == B200_PATH_MMQ || (ctx->force_path == B200_PATH_AUTO && N >= mmq_min);
+    for (int i = 0; i < n_ops && mmq; i++) mmq = b200_mmq_usable(type, K, src0s[i], descs[i].nb01);
+    if (mmq) {
+        for (int i = 0; i < n_ops; i++) {
+            const b200_mul_mat_desc & di = descs[i];
+            const int64_t r2 = di.ne12 / di.ne02, r3 = di.ne13 / di.ne03;
+            for (int64_t i13 = 0; i13 < di.ne13; i13++)
+                for (int64_t i12 = 0; i12 < di.ne12; i12++) {
+                    b200_status st = b200_mmq_run(ctx, type, (const uint8_t *) src0s[i] + (i12 / r2) * di.nb02 + (i13 / r3) * di.nb03, di.nb01,
+                                                  di.ne01, K, (const float *) ((const char *) src1 + i12 * di.nb12 + i13 * di.nb13), di.nb11, N,
+                                                  (float *) ((char *) dsts[i] + i12 * di.nb2 + i13 * di.nb3), (int64_t) (di.nb1 / 4));
+                    if (st != B200_OK) return st;
+                }
+        }
+        return B200_OK;
+    }
+
     bool fast = ctx->force_path != B200_PATH_SIMPLE;
     for (int i = 0; i < n_ops; i++) fast = fast && fast_layout_ok(type, K, src0s[i], descs[i].nb01, descs[i].nb02, descs[i].nb03);
 
@@ -372,21 +420,26 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
     const int64_t n_rows  = N * n_batch;  // activation rows to quantize
 
     if (fast) {
-        const int    U      = (int) (K / 256);
-        const size_t main_b = (size_t) n_rows * U * ACT_MAIN, aux_b = (size_t) n_rows * U * ACT_AUX;
-        const size_t aux_o  = (main_b + 255) & ~(size_t) 255;
-        b200_status  st     = ensure(ctx, &ctx->scratch, &ctx->scratch_size, aux_o + aux_b);
-        if (st != B200_OK) return st;
-        uint8_t * am = (uint8_t *) ctx->scratch, * ax = am + aux_o;
-        const int kind = act_kind_for(type);
-        for (int64_t i13 = 0; i13 < d.ne13; i13++)
-            for (int64_t i12 = 0; i12 < d.ne12; i12++) {
-                const int64_t b = i13 * d.ne12 + i12;
-                int l = 0;
-                CU(quantize_units(kind, (const float *) ((const char *) src1 + i12 * d.nb12 + i13 * d.nb13), K, N, d.nb11,
-                                  am + (size_t) b * N * U * ACT_MAIN, ax + (size_t) b * N * U * ACT_AUX, ctx->stream, &l));
-                ctx->launches += l;
-            }
+        const int  U    = (int) (K / 256);
+        const bool fuse = mv_fuse_quant(ctx, U, N);
+        uint8_t * am = nullptr, * ax = nullptr;
+        if (!fuse) {
+            const size_t main_b = (size_t) n_rows * U * ACT_MAIN, aux_b = (size_t) n_rows * U * ACT_AUX;
+            const size_t aux_o  = (main_b + 255) & ~(size_t) 255;
+            b200_status  st     = ensure(ctx, &ctx->scratch, &ctx->scratch_size, aux_o + aux_b);
+            if (st != B200_OK) return st;
+            am = (uint8_t *) ctx->scratch;
+            ax = am + aux_o;
+            const int kind = act_kind_for(type);
+            for (int64_t i13 = 0; i13 < d.ne13; i13++)
+                for (int64_t i12 = 0; i12 < d.ne12; i12++) {
+                    const int64_t b = i13 * d.ne12 + i12;
+                    int l = 0;
+                    CU(quantize_units(kind, (const float *) ((const char *) src1 + i12 * d.nb12 + i13 * d.nb13), K, N, d.nb11,
+                                      am + (size_t) b * N * U * ACT_MAIN, ax + (size_t) b * N * U * ACT_AUX, ctx->stream, &l));
+                    ctx->launches += l;
+                }
+        }
         const uint8_t * ws[MV_MAX_MATS * 8];
         size_t          nb01s[MV_MAX_MATS * 8];
         int64_t         Ms[MV_MAX_MATS * 8], dcs[MV_MAX_MATS * 8];
@@ -404,8 +457,9 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
                     ds[i]    = (float *) ((char *) dsts[i] + i12 * di.nb2 + i13 * di.nb3);
                     dcs[i]   = (int64_t) (di.nb1 / 4);
                 }
-                st = mv_fast_run(ctx, type, K, n_ops, ws, nb01s, Ms, ds, dcs, (int) N, am + (size_t) b * N * U * ACT_MAIN,
-                                 ax + (size_t) b * N * U * ACT_AUX);
+                b200_status st = mv_fast_run(ctx, type, K, n_ops, ws, nb01s, Ms, ds, dcs, (int) N,
+                                             fuse ? (const float *) ((const char *) src1 + i12 * d.nb12 + i13 * d.nb13) : nullptr, d.nb11,
+                                             fuse ? nullptr : am + (size_t) b * N * U * ACT_MAIN, fuse ? nullptr : ax + (size_t) b * N * U * ACT_AUX);
                 if (st != B200_OK) return st;
             }
         return B200_OK;
@@ -495,8 +549,3 @@ b200_status b200_mul_mat_host(b200_ctx * ctx, const b200_mul_mat_desc * d, const
     return B200_OK;
 }
 
-// ------------------------------------------------------------------------------------------------ weight cache (tcgen05 path)
-
-void   b200_weight_cache_invalidate(b200_ctx *, const void *, size_t) {}
-void   b200_weight_cache_clear(b200_ctx *) {}
-size_t b200_weight_cache_bytes(const b200_ctx *) { return 0; }

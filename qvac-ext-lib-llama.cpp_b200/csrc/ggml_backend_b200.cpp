@@ -57,8 +57,15 @@ ggml_backend_reg_t b200_reg();
 
 // ------------------------------------------------------------------------------------------------ device buffer
 
+// every host-side write into a buffer (and its release) is reported to the prefill weight cache, which keeps int8
+// expansions keyed by weight pointer: the whole tensor range is dropped, so chunked uploads (src/llama-model-loader.cpp
+// :1072-1090) and per-expert matrices inside a 3-D tensor are covered
+void drop_cached(ggml_backend_buffer_t buffer, const ggml_tensor * t) {
+    if (t && t->data && ggml_is_quantized(t->type)) b200_weight_cache_invalidate(((buf_ctx *) buffer->context)->device, t->data, ggml_nbytes(t));
+}
 void buf_free(ggml_backend_buffer_t buffer) {
     buf_ctx * c = (buf_ctx *) buffer->context;
+    b200_weight_cache_invalidate(c->device, c->base, buffer->size);
     b200_free(c->device, c->base);
     delete c;
 }
@@ -69,9 +76,11 @@ ggml_status buf_init_tensor(ggml_backend_buffer_t, ggml_tensor *) {
     return GGML_STATUS_SUCCESS;
 }
 void buf_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * t, uint8_t value, size_t offset, size_t size) {
+    drop_cached(buffer, t);
     CHECK(b200_memset(((buf_ctx *) buffer->context)->device, (char *) t->data + offset, value, size));
 }
 void buf_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * t, const void * data, size_t offset, size_t size) {
+    drop_cached(buffer, t);
     CHECK(b200_memcpy_h2d(((buf_ctx *) buffer->context)->device, (char *) t->data + offset, data, size));
 }
 void buf_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * t, void * data, size_t offset, size_t size) {
@@ -82,12 +91,14 @@ bool buf_cpy_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * src, ggml_
     ggml_backend_buffer_t sb = src->view_src ? src->view_src->buffer : src->buffer;
     if (!sb || !buft_is_b200(sb->buft)) return false;
     buf_ctx * s = (buf_ctx *) sb->context, * d = (buf_ctx *) buffer->context;
+    drop_cached(buffer, dst);
     if (s->device == d->device) CHECK(b200_memcpy_d2d(d->device, dst->data, src->data, ggml_nbytes(src)));
     else CHECK(b200_memcpy_peer(d->device, dst->data, s->device, src->data, ggml_nbytes(src)));
     return true;
 }
 void buf_clear(ggml_backend_buffer_t buffer, uint8_t value) {
     buf_ctx * c = (buf_ctx *) buffer->context;
+    b200_weight_cache_invalidate(c->device, c->base, buffer->size);
     CHECK(b200_memset(c->device, c->base, value, buffer->size));
 }
 
@@ -203,6 +214,7 @@ void be_free(ggml_backend_t backend) {
     delete backend;
 }
 void be_set_tensor_async(ggml_backend_t backend, ggml_tensor * t, const void * data, size_t offset, size_t size) {
+    if (t->data && ggml_is_quantized(t->type)) b200_weight_cache_invalidate(((be_ctx *) backend->context)->device, t->data, ggml_nbytes(t));
     CHECK(b200_memcpy_h2d_async(((be_ctx *) backend->context)->ctx, (char *) t->data + offset, data, size));
 }
 void be_get_tensor_async(ggml_backend_t backend, const ggml_tensor * t, void * data, size_t offset, size_t size) {
@@ -313,6 +325,10 @@ ggml_backend_t dev_init_backend(ggml_backend_dev_t dev, const char *) {
         GGML_LOG_ERROR("ggml-b200: cannot create a context on device %d: %s\n", d->device, b200_last_error());
         return nullptr;
     }
+    // this backend owns its buffers and reports every write to them (drop_cached), so the int8 expansion of a weight
+    // matrix used by the tcgen05 prefill kernel is built once and kept (GGML_B200_WEIGHT_CACHE=0 rebuilds it per call)
+    const char * wc = getenv("GGML_B200_WEIGHT_CACHE");
+    b200_ctx_set_weight_cache(ctx, !(wc && !atoi(wc)));
     const char * nf = getenv("GGML_B200_DISABLE_FUSION");
     be_ctx * c = new be_ctx{ d->device, ctx, d->name, !(nf && atoi(nf)) };
     return new ggml_backend{ be_guid(), be_iface, dev, c };

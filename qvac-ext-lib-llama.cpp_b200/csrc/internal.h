@@ -38,7 +38,16 @@ struct b200_ctx {
     void *       scratch2      = nullptr;
     size_t       scratch2_size = 0;
     int          mv_warps = 0, mv_stages = 0;  // 0 = auto; GGML_B200_MV_WARPS / GGML_B200_MV_STAGES
+    int          pdl        = 1;               // programmatic dependent launch of the mat-vec kernels; GGML_B200_PDL=0 disables
+    int          weight_cache = 0;             // keep the int8 expansion of a weight matrix across calls (owner must invalidate)
+    int          mmq_min_cols = 0;             // 0 = auto; GGML_B200_MMQ_MIN
+    int          fuse_quant = 1;               // quantize src1 inside the mat-vec kernel when small; GGML_B200_FUSE_QUANT=0 disables
 };
 
 // grow-only device buffer owned by the context (fails instead of reallocating while the stream is being captured)
 b200_status b200_ensure(b200_ctx * ctx, void ** buf, size_t * cur, size_t need);
+
+// mmq.cu: the tcgen05 int8 tile kernel
+bool        b200_mmq_usable(int type, int64_t K, const void * w, size_t nb01);
+b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, int64_t M, int64_t K, const float * x, size_t x_rs, int64_t N,
+                         float * dst, int64_t ldc);

@@ -16,6 +16,7 @@ cudaError_t quantize_units(int kind, const float * x, int64_t k, int64_t nrows, 
 // ---- mmvq.cu (K3)
 constexpr int MV_MAX_MATS = 4;
 constexpr int MV_MAX_COLS = 8;
+constexpr int MV_MAX_CONS = 8;   // consumer warps per CTA (+ 1 producer warp)
 
 // expert routing for MUL_MAT_ID (ggml-cpu.c:1564-1578): pair (i, t) uses expert ids[t*ids_rs + i], activation row
 // t*ne11 + i % ne11 of the quantized activations, and writes dst + t*dst_ts + i*dst_is (floats)
@@ -24,6 +25,7 @@ struct MvIds {
     int64_t         ids_rs;   // int32 elements between token rows of ids
     int64_t         nb02;     // bytes between expert matrices
     int64_t         dst_is, dst_ts;
+    int64_t         x_is, x_ts;   // bytes between b rows (nb11) / tokens (nb12) of the F32 activations (fused quantization)
     int             n_used, ne11, n_as;
 };
 
@@ -44,15 +46,20 @@ struct MvParams {
     int             L;        // lanes per row: power of two >= min(U, 32)
     int             rpg;      // rows per group: 32 / L when U <= 32, else 1
     int             slices;   // ceil(U / 32)
-    int             n_warps, n_stages;
-    const uint8_t * act_main; // [ncols][U][272]
-    const uint8_t * act_aux;  // [ncols][U][16]
+    int             n_cons, n_stages; // consumer warps (<= MV_MAX_CONS), ring stages per consumer warp
+    int             fuse_quant;       // 1: quantize src1 inside the kernel (x, x_cs); 0: load act_main / act_aux
+    int             x_vec;            // x rows are 16-byte aligned
+    int             pdl;              // launch with programmatic stream serialization
+    const float *   x;                // F32 activations, column c at (char*)x + c*x_cs
+    int64_t         x_cs;
+    const uint8_t * act_main;         // [ncols][U][272]
+    const uint8_t * act_aux;          // [ncols][U][16]
     // MUL_MAT_ID mode (ids != nullptr): blockIdx.y = pair p = t*n_used + i; one column per pair; mat[0] = expert 0
     MvIds           ids;
 };
 
 // smem bytes needed by the fast kernel for a configuration
-size_t mv_fast_smem(int type, int U, int ncols, int n_warps, int n_stages);
+size_t mv_fast_smem(int type, int U, int ncols, int n_cons, int n_stages);
 // launches the persistent TMA-staged mat-vec kernel (type, ncols 1..8); grid = n_ctas
 cudaError_t mv_fast_launch(int type, int ncols, const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st);
 

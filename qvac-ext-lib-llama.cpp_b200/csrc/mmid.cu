@@ -115,24 +115,31 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
     const int64_t n_rows = d->ne11 * d->n_tok;
 
     if (fast) {
-        const int    U      = (int) (K / 256);
-        const size_t main_b = (size_t) n_rows * U * ACT_MAIN, aux_b = (size_t) n_rows * U * ACT_AUX;
-        const size_t aux_o  = (main_b + 255) & ~(size_t) 255;
-        b200_status  st     = b200_ensure(ctx, &ctx->scratch, &ctx->scratch_size, aux_o + aux_b);
-        if (st != B200_OK) return st;
-        uint8_t * am = (uint8_t *) ctx->scratch, * ax = am + aux_o;
-        if (d->nb12 == d->nb11 * (size_t) d->ne11) {  // rows of all tokens are equally spaced: one launch
-            int l = 0;
-            CU(quantize_units(act_kind_for(d->type), b, K, n_rows, d->nb11, am, ax, ctx->stream, &l));
-            ctx->launches += l;
-        } else {
-            for (int64_t t = 0; t < d->n_tok; t++) {
+        const int  U    = (int) (K / 256);
+        const bool fuse = ctx->fuse_quant && U <= 64;  // every pair's CTAs quantize that pair's activation row themselves
+        uint8_t * am = nullptr, * ax = nullptr;
+        if (!fuse) {
+            const size_t main_b = (size_t) n_rows * U * ACT_MAIN, aux_b = (size_t) n_rows * U * ACT_AUX;
+            const size_t aux_o  = (main_b + 255) & ~(size_t) 255;
+            b200_status  st     = b200_ensure(ctx, &ctx->scratch, &ctx->scratch_size, aux_o + aux_b);
+            if (st != B200_OK) return st;
+            am = (uint8_t *) ctx->scratch;
+            ax = am + aux_o;
+            if (d->nb12 == d->nb11 * (size_t) d->ne11) {  // rows of all tokens are equally spaced: one launch
                 int l = 0;
-                CU(quantize_units(act_kind_for(d->type), (const float *) ((const char *) b + t * d->nb12), K, d->ne11, d->nb11,
-                                  am + (size_t) t * d->ne11 * U * ACT_MAIN, ax + (size_t) t * d->ne11 * U * ACT_AUX, ctx->stream, &l));
+                CU(quantize_units(act_kind_for(d->type), b, K, n_rows, d->nb11, am, ax, ctx->stream, &l));
                 ctx->launches += l;
+            } else {
+                for (int64_t t = 0; t < d->n_tok; t++) {
+                    int l = 0;
+                    CU(quantize_units(act_kind_for(d->type), (const float *) ((const char *) b + t * d->nb12), K, d->ne11, d->nb11,
+                                      am + (size_t) t * d->ne11 * U * ACT_MAIN, ax + (size_t) t * d->ne11 * U * ACT_AUX, ctx->stream, &l));
+                    ctx->launches += l;
+                }
             }
         }
+        mi.x_is = (int64_t) d->nb11;
+        mi.x_ts = (int64_t) d->nb12;
         MvParams p;
         memset(&p, 0, sizeof(p));
         p.U = U;
@@ -147,15 +154,16 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
         p.mat[0].group0 = 0;
         for (int i = 1; i < MV_MAX_MATS; i++) p.mat[i].group0 = INT32_MAX;
         p.total_groups = (int) ((M + p.rpg - 1) / p.rpg);
-        p.act_main = am;
-        p.act_aux  = ax;
-        p.ids      = mi;
+        p.pdl          = ctx->pdl;
+        p.fuse_quant   = fuse ? 1 : 0;
+        p.x_vec        = (uintptr_t) b % 16 == 0 && d->nb11 % 16 == 0 && d->nb12 % 16 == 0;
+        p.ids          = mi;
         // shared-memory configuration for one column
-        static const int cand[][2] = { { 8, 4 }, { 8, 3 }, { 8, 2 }, { 4, 3 }, { 4, 2 }, { 2, 2 }, { 1, 2 } };
+        static const int cand[][2] = { { 8, 3 }, { 8, 2 }, { 4, 3 }, { 4, 2 }, { 2, 2 }, { 1, 2 } };
         size_t smem = 0;
         for (auto & c : cand) {
             smem = mv_fast_smem(d->type, U, 1, c[0], c[1]);
-            if (smem <= 227 * 1024) { p.n_warps = c[0]; p.n_stages = c[1]; break; }
+            if (smem <= 227 * 1024) { p.n_cons = c[0]; p.n_stages = c[1]; break; }
             smem = 0;
         }
         if (!smem) return fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
@@ -171,8 +179,12 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
             MvParams q = p;
             q.ids.ids    = ids + t0 * mi.ids_rs;
             q.mat[0].dst = dst + t0 * mi.dst_ts;
-            q.act_main   = am + (size_t) t0 * d->ne11 * U * ACT_MAIN;
-            q.act_aux    = ax + (size_t) t0 * d->ne11 * U * ACT_AUX;
+            if (fuse) {
+                q.x = (const float *) ((const char *) b + t0 * d->nb12);
+            } else {
+                q.act_main = am + (size_t) t0 * d->ne11 * U * ACT_MAIN;
+                q.act_aux  = ax + (size_t) t0 * d->ne11 * U * ACT_AUX;
+            }
             CU(mv_fast_launch(d->type, 1, q, ctas, np, smem, ctx->stream));
             ctx->launches++;
         }

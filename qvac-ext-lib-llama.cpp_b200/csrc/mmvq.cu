@@ -18,7 +18,7 @@
 // The integer block sums are identical to ggml-cpu's vec_dot_q4_0_q8_0 / q8_0_q8_0 / q4_K_q8_K because the
 // activations are quantized exactly like the CPU does (quantize.cu); only the fp32 summation order differs.
 
-#include "common.cuh"
+#include "quant_core.cuh"
 #include "kernels.h"
 
 namespace b200 {
@@ -176,53 +176,89 @@ __device__ __forceinline__ void unit_dot(uint32_t w, uint32_t am, uint32_t ax, u
 }
 
 // ------------------------------------------------------------------------------------------------
-// the persistent kernel
+// the persistent, warp-specialised kernel
+//
+// CTA = n_cons consumer warps + 1 producer warp; grid = one CTA per SM (x pairs for MUL_MAT_ID). A CTA owns a contiguous
+// range of row groups; consumer warp w takes groups w, w + n_cons, ... of that range, each group in `slices` stages
+// (a stage = up to 32 units: rpg rows x U units when U <= 32, else a 32-unit slice of one row).
+//   producer warp : lane w is the producer of consumer warp w. It polls the consumer's "empty" mbarriers and issues
+//                   cp.async.bulk copies (L2 evict_first) into that consumer's ring; completion arrives on "full".
+//                   Weights never depend on an earlier kernel of the stream, so the producer starts immediately.
+//   consumer warps: griddepcontrol.wait (programmatic dependent launch: the previous kernel of the stream has completed
+//                   and its writes are visible) -> quantize the activations straight from the F32 src1 into shared
+//                   memory (fused K1, same arithmetic as quantize.cu) or bulk-load pre-quantized unit records ->
+//                   wait full / unit dot products / warp-shuffle row reduction / store / arrive empty.
+// griddepcontrol.launch_dependents is executed at kernel start and the default configuration keeps shared memory
+// <= 113 KB and registers <= 112, so the NEXT mat-vec kernel of the stream becomes co-resident on every SM and streams
+// its first stages while this one is still computing: HBM stays busy across kernel boundaries (a 4096x4096 q4 matrix
+// is 1.4 us of HBM time - shorter than a launch + drain).
+//
 // shared memory map (dynamic, 128-byte aligned):
-//   [0, 16)                               : int next_group ; pad
-//   [16, 16 + 8)                          : act mbarrier
-//   [64, 64 + 8*NW*NS)                    : per-warp stage mbarriers
-//   [.., + 8*NW*NS)                       : per-warp stage descriptors {group, slice}
+//   [0, 8)                      : act mbarrier (pre-quantized activation loads)
+//   [64, 64 + 8*NWC*NS)         : full barriers ; then 8*NWC*NS empty barriers
 //   [act_main: NC*U*272][act_aux: NC*U*16]
-//   [ring: NW*NS*stage_bytes]
+//   [ring: NWC*NS*stage_bytes]
 // ------------------------------------------------------------------------------------------------
 
 constexpr int MV_HDR_BYTES = 64;
 
 __host__ __device__ inline size_t mv_align(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-size_t mv_fast_smem(int type, int U, int ncols, int n_warps, int n_stages) {
-    const size_t stage = 32 * (size_t) unit_bytes(type);
+size_t mv_fast_smem(int type, int U, int ncols, int n_cons, int n_stages) {
+    const size_t stage = 32 * (size_t) unit_bytes(type);  // a stage always has room for 32 units
     size_t s = MV_HDR_BYTES;
-    s += (size_t) 16 * n_warps * n_stages;  // barriers + descriptors
+    s += (size_t) 16 * n_cons * n_stages;  // full + empty barriers
     s = mv_align(s, 128);
     s += (size_t) ncols * U * (ACT_MAIN + ACT_AUX);
     s = mv_align(s, 128);
-    s += (size_t) n_warps * n_stages * stage;
+    s += (size_t) n_cons * n_stages * stage;
     return s;
 }
 
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void bar_sync_named(int id, int n_threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n_threads) : "memory"); }
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
+__device__ __forceinline__ int mv_find_mat(const MvParams & p, int group) {
+    int m = 0;
+#pragma unroll
+    for (int i = 1; i < MV_MAX_MATS; i++) if (i < p.n_mats && group >= p.mat[i].group0) m = i;
+    return m;
+}
+
 template <int TYPE, int NC>
-__global__ void __launch_bounds__(256, 1) mv_fast_kernel(const __grid_constant__ MvParams p) {
+__global__ void __launch_bounds__(32 * (MV_MAX_CONS + 1), NC <= 4 ? 2 : 1) mv_fast_kernel(const __grid_constant__ MvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int UB    = unit_bytes(TYPE);
     constexpr int STAGE = 32 * UB;
+    constexpr int KIND  = act_kind_for(TYPE);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int NW = p.n_warps, NS = p.n_stages;
+    const int NWC = p.n_cons, NS = p.n_stages;
     const int U = p.U;
 
-    int *      next_group = (int *) smem;
-    uint64_t * act_bar    = (uint64_t *) (smem + 16);
-    uint64_t * bars       = (uint64_t *) (smem + MV_HDR_BYTES);
-    int2 *     descs      = (int2 *) (smem + MV_HDR_BYTES + 8 * NW * NS);
-    size_t     off        = mv_align(MV_HDR_BYTES + (size_t) 16 * NW * NS, 128);
-    uint8_t *  act_m      = smem + off;
-    uint8_t *  act_x      = act_m + (size_t) NC * U * ACT_MAIN;
-    off                   = mv_align(off + (size_t) NC * U * (ACT_MAIN + ACT_AUX), 128);
-    uint8_t *  ring       = smem + off + (size_t) warp * NS * STAGE;
+    uint64_t * act_bar = (uint64_t *) smem;
+    uint64_t * full    = (uint64_t *) (smem + MV_HDR_BYTES);
+    uint64_t * empty   = full + NWC * NS;
+    size_t     off     = mv_align(MV_HDR_BYTES + (size_t) 16 * NWC * NS, 128);
+    uint8_t *  act_m   = smem + off;
+    uint8_t *  act_x   = act_m + (size_t) NC * U * ACT_MAIN;
+    off                = mv_align(off + (size_t) NC * U * (ACT_MAIN + ACT_AUX), 128);
+    uint8_t *  ring0   = smem + off;
 
     // MUL_MAT_ID: this CTA row (blockIdx.y) is one (slot, token) pair with its own expert, activation row and dst column
-    int64_t w_off = 0, dst_off = 0;
+    int64_t w_off = 0, dst_off = 0, x_off = 0;
     int     act_col = 0;
     if (p.ids.ids) {
         const int pair = blockIdx.y;
@@ -232,6 +268,7 @@ __global__ void __launch_bounds__(256, 1) mv_fast_kernel(const __grid_constant__
         w_off   = (int64_t) e * p.ids.nb02;
         dst_off = (int64_t) t * p.ids.dst_ts + (int64_t) i * p.ids.dst_is;
         act_col = t * p.ids.ne11 + i % p.ids.ne11;
+        x_off   = (int64_t) t * p.ids.x_ts + (int64_t) (i % p.ids.ne11) * p.ids.x_is;
     }
 
     // this CTA's contiguous range of row groups
@@ -239,77 +276,94 @@ __global__ void __launch_bounds__(256, 1) mv_fast_kernel(const __grid_constant__
     const int g_end   = (int) ((int64_t) p.total_groups * (blockIdx.x + 1) / gridDim.x);
 
     if (threadIdx.x == 0) {
-        *next_group = g_begin;
         mbar_init(smem_u32(act_bar), 1);
-        for (int i = 0; i < NW * NS; i++) mbar_init(smem_u32(bars + i), 1);
+        for (int i = 0; i < NWC * NS; i++) {
+            mbar_init(smem_u32(full + i), 1);
+            mbar_init(smem_u32(empty + i), 1);
+        }
         fence_mbar_init();
     }
     __syncthreads();
+    griddep_launch_dependents();
 
-    const uint64_t pol_stream = l2_policy_evict_first();
-    const uint64_t pol_keep   = l2_policy_evict_last();
-
-    if (threadIdx.x == 0) {  // activations: NC columns of U records (main + aux), shared by every row
-        const uint32_t bytes_m = (uint32_t) NC * U * ACT_MAIN, bytes_x = (uint32_t) NC * U * ACT_AUX;
-        mbar_expect_tx(smem_u32(act_bar), bytes_m + bytes_x);
-        for (int c = 0; c < NC; c++) {
-            bulk_g2s(smem_u32(act_m + (size_t) c * U * ACT_MAIN), p.act_main + (size_t) (act_col + c) * U * ACT_MAIN,
-                     (uint32_t) U * ACT_MAIN, smem_u32(act_bar), pol_keep);
-        }
-        bulk_g2s(smem_u32(act_x), p.act_aux + (size_t) act_col * U * ACT_AUX, bytes_x, smem_u32(act_bar), pol_keep);
-    }
-
-    uint64_t * my_bars  = bars + warp * NS;
-    int2 *     my_descs = descs + warp * NS;
-
-    // ---- producer state (warp-uniform)
-    int  prod_group = -1, prod_slice = p.slices;
-    int  issued = 0, consumed = 0;
-    bool exhausted = false;
-
-    auto produce = [&]() {
-        if (exhausted) return;
-        if (prod_slice >= p.slices) {
-            int g = 0;
-            if (lane == 0) g = atomicAdd(next_group, 1);
-            g = __shfl_sync(0xffffffffu, g, 0);
-            if (g >= g_end) { exhausted = true; return; }
-            prod_group = g;
-            prod_slice = 0;
-        }
-        const int stage = issued % NS;
-        if (lane == 0) {
-            // locate the matrix of this global group id
-            int m = 0;
-#pragma unroll
-            for (int i = 1; i < MV_MAX_MATS; i++) if (i < p.n_mats && prod_group >= p.mat[i].group0) m = i;
-            const MvMat & mat  = p.mat[m];
-            const int     row0 = (prod_group - mat.group0) * p.rpg;
-            const int     nrow = min(p.rpg, mat.M - row0);
-            const int     u0   = prod_slice * 32;
-            const int     nu   = min(32, U - u0);
-            const uint32_t bar = smem_u32(my_bars + stage);
-            const uint32_t dst = smem_u32(ring + (size_t) stage * STAGE);
-            my_descs[stage] = make_int2(prod_group, prod_slice);
-            const uint32_t row_bytes = (uint32_t) nu * UB;
-            mbar_expect_tx(bar, row_bytes * nrow);
-            const uint8_t * src = mat.w + w_off + (int64_t) row0 * mat.nb01 + (int64_t) u0 * UB;
-            if (nrow > 1 && mat.nb01 == (int64_t) U * UB) {
-                bulk_g2s(dst, src, row_bytes * nrow, bar, pol_stream);  // rows are adjacent in memory: one copy
-            } else {
-                for (int r = 0; r < nrow; r++) bulk_g2s(dst + r * row_bytes, src + (int64_t) r * mat.nb01, row_bytes, bar, pol_stream);
+    if (warp == NWC) {
+        // ================================================================ producer warp: lane w feeds consumer warp w
+        const int w = lane;
+        int my_total = 0;
+        if (w < NWC && g_end - g_begin > w) my_total = ((g_end - g_begin - w + NWC - 1) / NWC) * p.slices;
+        const uint64_t pol_stream = l2_policy_evict_first();
+        uint8_t * ring = ring0 + (size_t) w * NS * STAGE;
+        int issued = 0, stage = 0, j = 0, slice = 0;
+        uint32_t phase = 1;  // parity of the "previous" phase of a fresh barrier: the first NS waits fall through
+        while (__any_sync(0xffffffffu, issued < my_total)) {
+            bool can = issued < my_total;
+            if (can) can = mbar_test_wait(smem_u32(empty + w * NS + stage), phase);
+            if (can) {
+                const int     group = g_begin + w + j * NWC;
+                const MvMat & mat   = p.mat[mv_find_mat(p, group)];
+                const int     row0  = (group - mat.group0) * p.rpg;
+                const int     nrow  = min(p.rpg, mat.M - row0);
+                const int     u0    = slice * 32;
+                const int     nu    = min(32, U - u0);
+                const uint32_t bar  = smem_u32(full + w * NS + stage);
+                const uint32_t dst  = smem_u32(ring + (size_t) stage * STAGE);
+                const uint32_t row_bytes = (uint32_t) nu * UB;
+                mbar_expect_tx(bar, row_bytes * nrow);
+                const uint8_t * src = mat.w + w_off + (int64_t) row0 * mat.nb01 + (int64_t) u0 * UB;
+                if (nrow > 1 && mat.nb01 == (int64_t) U * UB) {
+                    bulk_g2s(dst, src, row_bytes * nrow, bar, pol_stream);  // rows are adjacent in memory: one copy
+                } else {
+                    for (int r = 0; r < nrow; r++) bulk_g2s(dst + r * row_bytes, src + (int64_t) r * mat.nb01, row_bytes, bar, pol_stream);
+                }
+                issued++;
+                if (++stage == NS) { stage = 0; phase ^= 1; }
+                if (++slice == p.slices) { slice = 0; j++; }
             }
         }
-        issued++;
-        prod_slice++;
-    };
+        return;
+    }
+    if (warp > NWC) return;
 
-    for (int i = 0; i < NS; i++) produce();
+    // ==================================================================== consumer warps
+    const int w = warp;
+    int my_total = 0;
+    if (g_end - g_begin > w) my_total = ((g_end - g_begin - w + NWC - 1) / NWC) * p.slices;
 
-    mbar_wait(smem_u32(act_bar), 0);
+    griddep_wait();  // everything below reads src1 / writes dst, which earlier kernels of the stream may produce / still read
+
+    if (p.fuse_quant) {
+        // fused K1: unit (c, u) of the activations, F32 global -> unit record in shared memory
+        const int n_tasks = NC * U;
+        for (int t = w; t < n_tasks; t += NWC) {
+            const int c = t / U, u = t - c * U;
+            const float * xr = (const float *) ((const char *) p.x + x_off + (int64_t) c * p.x_cs) + (int64_t) u * UNIT_ELEMS + lane * 8;
+            float v[8];
+            if (p.x_vec) {
+                const float4 a = __ldg((const float4 *) xr);
+                const float4 b = __ldg((const float4 *) xr + 1);
+                v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+                v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; i++) v[i] = __ldg(xr + i);
+            }
+            quant_unit_store<KIND>(v, lane, act_m + (size_t) t * ACT_MAIN, act_x + (size_t) t * ACT_AUX);
+        }
+        bar_sync_named(1, NWC * 32);
+    } else {
+        if (w == 0 && lane == 0) {  // pre-quantized activations: NC columns of U records (main + aux)
+            const uint64_t pol_keep = l2_policy_evict_last();
+            const uint32_t bytes_m = (uint32_t) NC * U * ACT_MAIN, bytes_x = (uint32_t) NC * U * ACT_AUX;
+            mbar_expect_tx(smem_u32(act_bar), bytes_m + bytes_x);
+            bulk_g2s(smem_u32(act_m), p.act_main + (size_t) act_col * U * ACT_MAIN, bytes_m, smem_u32(act_bar), pol_keep);
+            bulk_g2s(smem_u32(act_x), p.act_aux + (size_t) act_col * U * ACT_AUX, bytes_x, smem_u32(act_bar), pol_keep);
+        }
+        mbar_wait(smem_u32(act_bar), 0);
+    }
 
     const uint32_t am0  = smem_u32(act_m), ax0 = smem_u32(act_x);
     const uint32_t cs_m = (uint32_t) U * ACT_MAIN, cs_x = (uint32_t) U * ACT_AUX;
+    const uint32_t ring = smem_u32(ring0 + (size_t) w * NS * STAGE);
 
     const int L   = p.L;
     const int sub = lane & (L - 1);  // unit index inside the row slice
@@ -319,25 +373,26 @@ __global__ void __launch_bounds__(256, 1) mv_fast_kernel(const __grid_constant__
 #pragma unroll
     for (int c = 0; c < NC; c++) acc[c] = 0.0f;
 
-    while (consumed < issued) {
-        const int stage = consumed % NS;
-        mbar_wait(smem_u32(my_bars + stage), (consumed / NS) & 1);
-        const int2 ds    = my_descs[stage];
-        const int  group = ds.x, slice = ds.y;
-        int m = 0;
-#pragma unroll
-        for (int i = 1; i < MV_MAX_MATS; i++) if (i < p.n_mats && group >= p.mat[i].group0) m = i;
-        const int row0 = (group - p.mat[m].group0) * p.rpg;
-        const int M    = p.mat[m].M;
-        const int u0   = slice * 32;
-        const int nu   = min(32, U - u0);
-        const int row  = row0 + rr;
-        const int u    = u0 + sub;
+    int stage = 0, j = 0, slice = 0;
+    uint32_t phase = 0;
+    for (int q = 0; q < my_total; q++) {
+        mbar_wait(smem_u32(full + w * NS + stage), phase);
+        const int group = g_begin + w + j * NWC;
+        const int m     = mv_find_mat(p, group);
+        const int row0  = (group - p.mat[m].group0) * p.rpg;
+        const int M     = p.mat[m].M;
+        const int u0    = slice * 32;
+        const int nu    = min(32, U - u0);
+        const int row   = row0 + rr;
+        const int u     = u0 + sub;
+        const bool mine = sub < nu && row < M && rr < p.rpg;
 
-        if (sub < nu && row < M && rr < p.rpg) {
-            const uint32_t w = smem_u32(ring + (size_t) stage * STAGE) + (uint32_t) (rr * nu + sub) * UB;
-            unit_dot<TYPE, NC>(w, am0 + (uint32_t) u * ACT_MAIN, ax0 + (uint32_t) u * ACT_AUX, cs_m, cs_x, acc);
+        if (mine) {
+            const uint32_t wp = ring + (uint32_t) stage * STAGE + (uint32_t) (rr * nu + sub) * UB;
+            unit_dot<TYPE, NC>(wp, am0 + (uint32_t) u * ACT_MAIN, ax0 + (uint32_t) u * ACT_AUX, cs_m, cs_x, acc);
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(empty + w * NS + stage));  // the stage's bytes are in registers: hand it back
 
         if (slice == p.slices - 1) {  // row finished: reduce the L lanes of each row and store
 #pragma unroll
@@ -352,9 +407,8 @@ __global__ void __launch_bounds__(256, 1) mv_fast_kernel(const __grid_constant__
                 acc[c] = 0.0f;
             }
         }
-        __syncwarp();
-        consumed++;
-        produce();  // refill the stage that was just drained
+        if (++stage == NS) { stage = 0; phase ^= 1; }
+        if (++slice == p.slices) { slice = 0; j++; }
     }
 }
 
@@ -368,8 +422,17 @@ static cudaError_t mv_fast_launch_t(const MvParams & p, int n_ctas, int n_pairs,
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
-    mv_fast_kernel<TYPE, NC><<<dim3(n_ctas, n_pairs), p.n_warps * 32, smem, st>>>(p);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim          = dim3(n_ctas, n_pairs);
+    cfg.blockDim         = dim3(32 * (p.n_cons + 1));
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream           = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs    = attr;
+    cfg.numAttrs = p.pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, mv_fast_kernel<TYPE, NC>, p);
 }
 
 template <int TYPE>

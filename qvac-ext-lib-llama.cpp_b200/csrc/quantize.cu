@@ -10,23 +10,13 @@
 //   LAYOUT_GGML  — the reference's block structs (what the C-ABI quantizers return and the parity tests memcmp)
 //   LAYOUT_UNITS — the kernels' internal unit records (common.cuh), 16-byte aligned for 128-bit shared loads.
 
-#include "common.cuh"
+#include "quant_core.cuh"
 #include "kernels.h"
 
 namespace b200 {
 
 enum { VAL_Q8_0 = 0, VAL_Q8_K = 1, VAL_Q8_1 = 2 };
 enum { LAYOUT_GGML = 0, LAYOUT_UNITS = 1 };
-
-__device__ __forceinline__ int nearest_int_rne(float v) {
-    // round-half-even through the 1.5*2^23 magic add (ggml-quants.c:444-449)
-    const float t = __fadd_rn(v, 12582912.f);
-    return (__float_as_int(t) & 0x007fffff) - 0x00400000;
-}
-
-__device__ __forceinline__ uint32_t pack4(int a, int b, int c, int d) {
-    return (uint32_t) (a & 0xff) | ((uint32_t) (b & 0xff) << 8) | ((uint32_t) (c & 0xff) << 16) | ((uint32_t) (d & 0xff) << 24);
-}
 
 template <int VAL, int LAYOUT>
 __global__ void __launch_bounds__(128) quantize_rows_kernel(const float * __restrict__ x, int64_t k, int64_t nrows, size_t x_row_stride,
@@ -58,96 +48,48 @@ __global__ void __launch_bounds__(128) quantize_rows_kernel(const float * __rest
         for (int i = 0; i < 8; i++) v[i] = 0.0f;
     }
 
-    int q[8];
-
     if (VAL == VAL_Q8_0 || VAL == VAL_Q8_1) {
-        float amax = 0.0f;
-#pragma unroll
-        for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
-        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-        const float d  = __fdiv_rn(amax, 127.0f);
-        const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-        int sum = 0;
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-            q[i] = (int) roundf(__fmul_rn(v[i], id));
-            sum += q[i];
-        }
-        sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-        sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-        const uint16_t dh = __half_as_ushort(__float2half_rn(d));
-        const uint32_t w0 = pack4(q[0], q[1], q[2], q[3]);
-        const uint32_t w1 = pack4(q[4], q[5], q[6], q[7]);
+        const Q80Lane  r  = quant_lane_q8_0(v);
+        const uint16_t dh = __half_as_ushort(__float2half_rn(r.d));
         if (!active) {
             return;
         }
         const int blk = lane >> 2, sub = lane & 3;
         if (LAYOUT == LAYOUT_UNITS) {
             uint8_t * m = y_main + (row * units + unit) * ACT_MAIN;
-            *(uint2 *) (m + lane * 8) = make_uint2(w0, w1);
+            *(uint2 *) (m + lane * 8) = make_uint2(r.w0, r.w1);
             if (sub == 0) {
                 *(uint16_t *) (m + 256 + 2 * blk) = dh;
-                *(int16_t *) (y_aux + (row * units + unit) * ACT_AUX + 2 * blk) = (int16_t) sum;
+                *(int16_t *) (y_aux + (row * units + unit) * ACT_AUX + 2 * blk) = (int16_t) r.sum;
             }
         } else if (VAL == VAL_Q8_0) {
             uint8_t * b = y_main + row * (size_t) (k / QK * SZ_Q8_0) + (unit * 8 + blk) * SZ_Q8_0;
             if (sub == 0) *(uint16_t *) b = dh;
             uint16_t * qs = (uint16_t *) (b + 2 + sub * 8);  // only 2-byte aligned
-            qs[0] = (uint16_t) w0; qs[1] = (uint16_t) (w0 >> 16);
-            qs[2] = (uint16_t) w1; qs[3] = (uint16_t) (w1 >> 16);
+            qs[0] = (uint16_t) r.w0; qs[1] = (uint16_t) (r.w0 >> 16);
+            qs[2] = (uint16_t) r.w1; qs[3] = (uint16_t) (r.w1 >> 16);
         } else {
             uint8_t * b = y_main + row * (size_t) (k / QK * SZ_Q8_1) + (unit * 8 + blk) * SZ_Q8_1;
             if (sub == 0) {
-                const uint16_t sh = __half_as_ushort(__float2half_rn(__fmul_rn((float) sum, d)));
+                const uint16_t sh = __half_as_ushort(__float2half_rn(__fmul_rn((float) r.sum, r.d)));
                 *(uint32_t *) b = (uint32_t) dh | ((uint32_t) sh << 16);
             }
             uint32_t * qs = (uint32_t *) (b + 4 + sub * 8);
-            qs[0] = w0; qs[1] = w1;
+            qs[0] = r.w0; qs[1] = r.w1;
         }
     } else {  // VAL_Q8_K: the warp is one 256-element super-block (k % 256 == 0 checked on the host)
-        float amax = 0.0f, vmax = 0.0f;
-        int   idx  = lane * 8;
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-            const float a = fabsf(v[i]);
-            if (a > amax) { amax = a; vmax = v[i]; idx = lane * 8 + i; }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const float oa = __shfl_xor_sync(0xffffffffu, amax, o);
-            const float ov = __shfl_xor_sync(0xffffffffu, vmax, o);
-            const int   oi = __shfl_xor_sync(0xffffffffu, idx, o);
-            if (oa > amax || (oa == amax && oi < idx)) { amax = oa; vmax = ov; idx = oi; }  // first max wins (ggml-quants.c:2564-2569)
-        }
-        float d = 0.0f;
-        if (amax != 0.0f) {
-            const float iscale = __fdiv_rn(-127.f, vmax);
-#pragma unroll
-            for (int i = 0; i < 8; i++) q[i] = min(127, nearest_int_rne(__fmul_rn(iscale, v[i])));
-            d = __fdiv_rn(1.0f, iscale);
-        } else {
-#pragma unroll
-            for (int i = 0; i < 8; i++) q[i] = 0;
-        }
-        int s8 = 0;
-#pragma unroll
-        for (int i = 0; i < 8; i++) s8 += q[i];
-        const int s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);
-        const int s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);
-        const uint32_t w0 = pack4(q[0], q[1], q[2], q[3]);
-        const uint32_t w1 = pack4(q[4], q[5], q[6], q[7]);
+        const Q8KLane r = quant_lane_q8_K(v, lane);
         if (LAYOUT == LAYOUT_UNITS) {
             uint8_t * m = y_main + (row * units + unit) * ACT_MAIN;
-            *(uint2 *) (m + lane * 8) = make_uint2(w0, w1);
-            if ((lane & 3) == 0) *(int16_t *) (m + 256 + 2 * (lane >> 2)) = (int16_t) s32;
-            if (lane == 0) *(float4 *) (y_aux + (row * units + unit) * ACT_AUX) = make_float4(d, 0.f, 0.f, 0.f);
+            *(uint2 *) (m + lane * 8) = make_uint2(r.w0, r.w1);
+            if ((lane & 3) == 0) *(int16_t *) (m + 256 + 2 * (lane >> 2)) = (int16_t) r.s32;
+            if (lane == 0) *(float4 *) (y_aux + (row * units + unit) * ACT_AUX) = make_float4(r.d, 0.f, 0.f, 0.f);
         } else {
             uint8_t * b = y_main + row * (size_t) (k / QK_K * SZ_Q8_K) + unit * SZ_Q8_K;
-            if (lane == 0) *(float *) b = d;
+            if (lane == 0) *(float *) b = r.d;
             uint32_t * qs = (uint32_t *) (b + 4 + lane * 8);
-            qs[0] = w0; qs[1] = w1;
-            if ((lane & 1) == 0) *(int16_t *) (b + 4 + QK_K + 2 * (lane >> 1)) = (int16_t) s16;
+            qs[0] = r.w0; qs[1] = r.w1;
+            if ((lane & 1) == 0) *(int16_t *) (b + 4 + QK_K + 2 * (lane >> 1)) = (int16_t) r.s16;
         }
     }
 }

@@ -270,3 +270,104 @@ def test_full_size_properties(ctx, pkg, oracle, t):
     finally:
         ctx.force_path(pkg.PATH_AUTO)
     assert oracle.nmse(gen.cpu().numpy(), full.cpu().numpy()) <= NMSE_TIGHT
+
+
+# ---------------------------------------------------------------- K2/K4: the tcgen05 int8 tile kernel
+
+MMQ_SHAPES = [  # (M, K, N): full tiles, M / N / K tails (K % 128 != 0 -> TMA zero fill), one-block K, one column
+    (128, 128, 128), (200, 256, 64), (130, 4096, 33), (512, 1024, 512), (64, 32, 16), (96, 96, 130), (257, 2048, 1), (300, 14336, 40),
+]
+
+
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
+@pytest.mark.parametrize("M,K,N", MMQ_SHAPES)
+def test_mmq_vs_oracle(ctx, pkg, oracle, t, M, K, N):
+    if t == Q4_K and K % 256:
+        pytest.skip("q4_K needs K % 256 == 0")
+    rng = np.random.default_rng(M + 3 * K + 7 * N + t)
+    W = quantize_weights(oracle, t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = (rng.standard_normal((N, K)) * rng.choice([0.01, 1.0, 30.0], (N, 1))).astype(np.float32)
+    ctx.force_path(pkg.PATH_MMQ)
+    try:
+        got = ctx.mul_mat(t, cu(W), cu(X)).cpu().numpy()
+    finally:
+        ctx.force_path(pkg.PATH_AUTO)
+    assert oracle.nmse(oracle.mul_mat(t, W, X), got) <= NMSE_TIGHT
+
+
+@pytest.mark.parametrize("t", [Q4_0, Q4_K])
+def test_mmq_and_matvec_kernels_agree(ctx, pkg, oracle, t):
+    """tensor-core tiles and dp4a mat-vec form the same integer block sums; only the fp32 summation order differs"""
+    rng = np.random.default_rng(17 + t)
+    M, K, N = 384, 4096, 8
+    W = quantize_weights(oracle, t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    a = ctx.mul_mat(t, cu(W), cu(X)).cpu().numpy()
+    ctx.force_path(pkg.PATH_MMQ)
+    try:
+        b = ctx.mul_mat(t, cu(W), cu(X)).cpu().numpy()
+    finally:
+        ctx.force_path(pkg.PATH_AUTO)
+    assert oracle.nmse(a, b) <= NMSE_TIGHT
+
+
+def test_mmq_batched_broadcast(ctx, pkg, oracle):
+    rng = np.random.default_rng(23)
+    M, K, N = 70, 512, 20
+    W = quantize_weights(oracle, Q8_0, rng.uniform(-1, 1, (2 * M, K)).astype(np.float32)).reshape(1, 2, M, -1)
+    X = rng.uniform(-1, 1, (1, 4, N, K)).astype(np.float32)
+    ctx.force_path(pkg.PATH_MMQ)
+    try:
+        got = ctx.mul_mat(Q8_0, cu(W), cu(X)).cpu().numpy()
+    finally:
+        ctx.force_path(pkg.PATH_AUTO)
+    ref = oracle.mul_mat(Q8_0, W, X, ne02=2, ne03=1)
+    assert oracle.nmse(ref, got) <= NMSE_TIGHT
+
+
+def test_mmq_weight_cache(ctx, pkg, oracle):
+    """a context that keeps int8 expansions must be told about overwritten weights (what the ggml buffer does on set_tensor)"""
+    import torch
+    rng = np.random.default_rng(29)
+    M, K, N = 256, 1024, 48
+    W1 = quantize_weights(oracle, Q4_0, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    W2 = quantize_weights(oracle, Q4_0, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    Wd, Xd = cu(W1), cu(X)
+    ctx.weight_cache(True)
+    try:
+        a = ctx.mul_mat(Q4_0, Wd, Xd).cpu().numpy()
+        assert pkg.lib().b200_weight_cache_bytes() > 0
+        a2 = ctx.mul_mat(Q4_0, Wd, Xd).cpu().numpy()        # served from the cache
+        assert np.array_equal(a, a2)
+        Wd.copy_(torch.from_numpy(W2))
+        pkg.lib().b200_weight_cache_invalidate(0, Wd.data_ptr(), Wd.numel())
+        b = ctx.mul_mat(Q4_0, Wd, Xd).cpu().numpy()
+    finally:
+        ctx.weight_cache(False)
+        ctx.weight_cache_clear()
+    assert pkg.lib().b200_weight_cache_bytes() == 0
+    assert oracle.nmse(oracle.mul_mat(Q4_0, W1, X), a) <= NMSE_TIGHT
+    assert oracle.nmse(oracle.mul_mat(Q4_0, W2, X), b) <= NMSE_TIGHT
+
+
+@pytest.mark.parametrize("t", [Q4_0, Q4_K, Q8_0])
+def test_mmq_full_size_properties(ctx, pkg, oracle, t):
+    """Llama-3-8B prefill shape 14336x4096, n=512: sampled rows equal the oracle; columns equal the mat-vec kernels' result"""
+    rng = np.random.default_rng(37 + t)
+    M, K, N = 14336, 4096, 512
+    slab = quantize_weights(oracle, t, rng.uniform(-1, 1, (512, K)).astype(np.float32))
+    W = np.ascontiguousarray(slab[rng.permutation(M) % 512])
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    Wd, Xd = cu(W), cu(X)
+    full = ctx.mul_mat(t, Wd, Xd)                      # n = 512 -> tile kernel
+    rows = rng.choice(M, 48, replace=False)
+    cols = rng.choice(N, 24, replace=False)
+    ref = oracle.mul_mat(t, np.ascontiguousarray(W[rows]), X[cols])
+    assert oracle.nmse(ref, full[cols][:, rows].cpu().numpy()) <= NMSE_TIGHT
+    ctx.force_path(pkg.PATH_MMVQ)
+    try:
+        mv = ctx.mul_mat(t, Wd, Xd[100:108].contiguous())
+    finally:
+        ctx.force_path(pkg.PATH_AUTO)
+    assert oracle.nmse(mv.cpu().numpy(), full[100:108].cpu().numpy()) <= NMSE_TIGHT
