@@ -159,7 +159,7 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
         p.x_vec        = (uintptr_t) b % 16 == 0 && d->nb11 % 16 == 0 && d->nb12 % 16 == 0;
         p.ids          = mi;
         // shared-memory configuration for one column
-        static const int cand[][2] = { { 8, 3 }, { 8, 2 }, { 4, 3 }, { 4, 2 }, { 2, 2 }, { 1, 2 } };
+        static const int cand[][2] = { { 16, 2 }, { 8, 3 }, { 8, 2 }, { 4, 3 }, { 4, 2 }, { 2, 2 }, { 1, 2 } };
         size_t smem = 0;
         for (auto & c : cand) {
             smem = mv_fast_smem(d->type, U, 1, c[0], c[1]);

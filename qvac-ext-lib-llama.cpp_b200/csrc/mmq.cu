@@ -7,7 +7,7 @@
 // (/root/reference/ggml/src/ggml-cuda/mmq.cu:70-236, mmq.cuh:3287-3536, 277-336, 637-697, 1840-1947, 796-931, 965-1091,
 // 3006-3053, quantize.cu:50-147). Not a port: the reference keeps 16x8 mma.sync fragments in registers and re-loads
 // tiles synchronously (4 __syncthreads per 256-K step, mmq.cuh:3241-3275); here one thread issues 128xBNx32 MMAs, the
-// copy engine feeds a 4-stage ring, and 16 epilogue warps do nothing but rescale.
+// copy engine feeds a 4-stage ring, and 8 epilogue warps do nothing but rescale (double-buffered TMEM drain, packed fp32 math).
 //
 // Arithmetic is the CPU reference's (ggml-cpu vec_dot_q4_0_q8_0 / q8_0_q8_0 / q4_K_q8_K): activations are quantized
 // exactly like quantize_row_q8_0_ref / q8_K_ref, every 32-element block's integer dot product is formed exactly
@@ -22,8 +22,8 @@
 //   activations : int8 [N][K] K-major + float scales [K/32][N]   (quantize_tiles_kernel, bit-exact values)
 // Tiling: CTA tile 128 (M) x 128 (N); K in stages of 128 (4 blocks of 32); TMEM: 4 slots of 128 columns, one slot per
 // 32-block, recycled as soon as the epilogue has pulled it into registers.
-// Warp roles (640 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 4..19 epilogue
-// (warp % 4 = TMEM lane quadrant = 32 weight rows, (warp - 4) / 4 = group of 32 activation columns).
+// Warp roles (384 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 4..11 epilogue
+// (warp % 4 = TMEM lane quadrant = 32 weight rows, (warp - 4) / 4 = half of the tile's 128 activation columns).
 
 #include "internal.h"
 #include "quant_core.cuh"
@@ -42,7 +42,7 @@ namespace {
 
 constexpr int BM = 128, BN = 128, BKB = 4;        // CTA tile; 32-blocks per stage
 constexpr int STAGES = 4, SLOTS = 4;
-constexpr int EPI_WARPS = 16, FIRST_EPI_WARP = 4;
+constexpr int EPI_WARPS = 8, FIRST_EPI_WARP = 4;   // 2 warps per TMEM lane quadrant, 64 accumulator columns per thread
 constexpr int MMQ_THREADS = 32 * (FIRST_EPI_WARP + EPI_WARPS);
 constexpr int A_BYTES = BM * 128, B_BYTES = BN * 128, S_BYTES = BKB * 128 * 4;
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES + 4 * S_BYTES;  // A, B, sW, sA, mW, aS
@@ -251,63 +251,85 @@ mmq_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
         }
     } else if (warp >= FIRST_EPI_WARP) {
         // ================================================================ epilogue: TMEM -> registers, scale, accumulate, store
-        const int quad = warp & 3, cg = (warp - FIRST_EPI_WARP) >> 2;
+        // A thread owns one weight row (TMEM lane) and 64 of the tile's 128 columns, drained as chunks of 32 columns.
+        // The tcgen05.ld of chunk i+1 is in flight while chunk i is converted and scaled (I2FP + FMUL2 + FFMA2).
+        const int quad = warp & 3, half = (warp - FIRST_EPI_WARP) >> 2;
         const int row_in_tile = quad * 32 + lane;
-        const uint32_t t_lane = tmem_base + ((uint32_t) (quad * 32) << 16) + cg * 32;
+        const uint32_t t_lane = tmem_base + ((uint32_t) (quad * 32) << 16) + half * 64;
         int stage = 0, slot = 0; uint32_t phase = 0, tphase = 0;
         for (int t = blockIdx.x; t < n_tiles_total; t += gridDim.x) {
             const int m0 = (t / p.n_tiles) * BM, n0 = (t % p.n_tiles) * BN;
-            float acc[32];
+            float2 acc[32];
 #pragma unroll
-            for (int j = 0; j < 32; j++) acc[j] = 0.0f;
-            for (int ks = 0; ks < k_stages; ks++) {
-                mbar_wait(smem_u32(full + stage), phase);  // the scales of this stage have landed
-                const uint8_t * st = smem + stage * STAGE_BYTES + A_BYTES + B_BYTES;
-#pragma unroll 1
-                for (int kb = 0; kb < BKB; kb++) {
+            for (int j = 0; j < 32; j++) acc[j] = make_float2(0.0f, 0.0f);
+            const int n_chunks = k_stages * BKB * 2;
+            uint32_t ca[32], cb[32];
+            // chunk 0
+            mbar_wait(smem_u32(tfull + slot), tphase);
+            tc_fence_after();
+            tmem_ld_32x32(t_lane + slot * BN, ca);
+            tc_wait_ld_regs(ca);
+
+            auto math = [&](const uint32_t (&c)[32], int kb, int h, uint32_t st) {
+                const float sw = __uint_as_float(lds32(st + 4 * (kb * 128 + row_in_tile)));
+                const float2 sw2 = make_float2(sw, sw);
+                const uint32_t sa = st + S_BYTES + 4 * (kb * 128 + half * 64 + h * 32);
+                float2 mw2 = make_float2(0.0f, 0.0f);
+                if (HAS_MIN) {
+                    const float mw = -__uint_as_float(lds32(st + 2 * S_BYTES + 4 * (kb * 128 + row_in_tile)));
+                    mw2 = make_float2(mw, mw);
+                }
+#pragma unroll
+                for (int j4 = 0; j4 < 8; j4++) {
+                    const uint4 a = lds128(sa + 16 * j4);
+                    const float2 p0 = fmul2(make_float2(__uint_as_float(a.x), __uint_as_float(a.y)), sw2);
+                    const float2 p1 = fmul2(make_float2(__uint_as_float(a.z), __uint_as_float(a.w)), sw2);
+                    float2 & r0 = acc[h * 16 + 2 * j4], & r1 = acc[h * 16 + 2 * j4 + 1];
+                    r0 = ffma2(p0, make_float2((float) (int) c[4 * j4 + 0], (float) (int) c[4 * j4 + 1]), r0);
+                    r1 = ffma2(p1, make_float2((float) (int) c[4 * j4 + 2], (float) (int) c[4 * j4 + 3]), r1);
+                    if (HAS_MIN) {
+                        const uint4 b = lds128(sa + 2 * S_BYTES + 16 * j4);
+                        r0 = ffma2(mw2, make_float2(__uint_as_float(b.x), __uint_as_float(b.y)), r0);
+                        r1 = ffma2(mw2, make_float2(__uint_as_float(b.z), __uint_as_float(b.w)), r1);
+                    }
+                }
+            };
+
+            // chunks are processed in pairs (h = 0, 1 of one 32-block) so that the two register buffers alternate statically
+            for (int ck = 0; ck < n_chunks; ck += 2) {
+                const int kb = (ck >> 1) & (BKB - 1);
+                if (kb == 0) mbar_wait(smem_u32(full + stage), phase);  // the scales of this stage have landed
+                const uint32_t st = smem_u32(smem + stage * STAGE_BYTES + A_BYTES + B_BYTES);
+                // second half of this 32-block in flight while the first is scaled
+                tmem_ld_32x32(t_lane + slot * BN + 32, cb);
+                math(ca, kb, 0, st);
+                tc_wait_ld_regs(cb);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(tempty + slot));  // both halves are in registers: the next MMA may overwrite the slot
+                if (++slot == SLOTS) { slot = 0; tphase ^= 1; }
+                // first half of the next 32-block in flight while the second half of this one is scaled
+                const bool more = ck + 2 < n_chunks;
+                if (more) {
                     mbar_wait(smem_u32(tfull + slot), tphase);
                     tc_fence_after();
-                    uint32_t c[32];
-                    tmem_ld_32x32(t_lane + slot * BN, c);
-                    tc_wait_ld();
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(smem_u32(tempty + slot));  // the slot is in registers: the next MMA may overwrite it
-                    const float   sw = ((const float *) st)[kb * 128 + row_in_tile];
-                    const float4 * sa = (const float4 *) (st + S_BYTES) + (kb * 128 + cg * 32) / 4;
-                    float mw = 0.0f;
-                    const float4 * as = nullptr;
-                    if (HAS_MIN) {
-                        mw = ((const float *) (st + 2 * S_BYTES))[kb * 128 + row_in_tile];
-                        as = (const float4 *) (st + 3 * S_BYTES) + (kb * 128 + cg * 32) / 4;
-                    }
-#pragma unroll
-                    for (int j4 = 0; j4 < 8; j4++) {
-                        const float4 a = sa[j4];
-                        acc[4 * j4 + 0] = fmaf(sw * a.x, (float) (int) c[4 * j4 + 0], acc[4 * j4 + 0]);
-                        acc[4 * j4 + 1] = fmaf(sw * a.y, (float) (int) c[4 * j4 + 1], acc[4 * j4 + 1]);
-                        acc[4 * j4 + 2] = fmaf(sw * a.z, (float) (int) c[4 * j4 + 2], acc[4 * j4 + 2]);
-                        acc[4 * j4 + 3] = fmaf(sw * a.w, (float) (int) c[4 * j4 + 3], acc[4 * j4 + 3]);
-                        if (HAS_MIN) {
-                            const float4 b = as[j4];
-                            acc[4 * j4 + 0] = fmaf(-mw, b.x, acc[4 * j4 + 0]);
-                            acc[4 * j4 + 1] = fmaf(-mw, b.y, acc[4 * j4 + 1]);
-                            acc[4 * j4 + 2] = fmaf(-mw, b.z, acc[4 * j4 + 2]);
-                            acc[4 * j4 + 3] = fmaf(-mw, b.w, acc[4 * j4 + 3]);
-                        }
-                    }
-                    if (++slot == SLOTS) { slot = 0; tphase ^= 1; }
+                    tmem_ld_32x32(t_lane + slot * BN, ca);
                 }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(empty + stage));  // done with this stage's scales
-                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                math(cb, kb, 1, st);
+                if (more) tc_wait_ld_regs(ca);
+                if (kb == BKB - 1) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(smem_u32(empty + stage));  // done with this stage's scales
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
             }
             const int m = m0 + row_in_tile;
             if (m < p.M) {
 #pragma unroll
                 for (int j = 0; j < 32; j++) {
-                    const int n = n0 + cg * 32 + j;
-                    if (n < p.N) p.dst[(int64_t) n * p.ldc + m] = acc[j];
+                    const int n = n0 + half * 64 + 2 * j;
+                    if (n < p.N) p.dst[(int64_t) n * p.ldc + m] = acc[j].x;
+                    if (n + 1 < p.N) p.dst[(int64_t) (n + 1) * p.ldc + m] = acc[j].y;
                 }
             }
         }

@@ -21,6 +21,8 @@
 #include "quant_core.cuh"
 #include "kernels.h"
 
+#include <type_traits>
+
 namespace b200 {
 
 // ------------------------------------------------------------------------------------------------
@@ -28,9 +30,18 @@ namespace b200 {
 // unit's activation record for column 0 (main / aux), `cs_m`/`cs_x` = byte strides between columns.
 // ------------------------------------------------------------------------------------------------
 
+// compile-time loop helper so that every shared-memory offset below is an immediate
+template <int I, int N, typename F>
+__device__ __forceinline__ void static_for(F && f) {
+    if constexpr (I < N) {
+        f(std::integral_constant<int, I>{});
+        static_for<I + 1, N>(f);
+    }
+}
+
 template <int NC>
 __device__ __forceinline__ void unit_dot_q4_K(uint32_t w, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc)[NC]) {
-    const uint4 hdr = lds128(w);  // d | dmin, 12 bytes of 6-bit scales/mins (ggml-common.h:291-305)
+    const uint4 hdr = lds128o<0>(w);  // d | dmin, 12 bytes of 6-bit scales/mins (ggml-common.h:291-305)
     const float d    = half_bits_to_float((uint16_t) (hdr.x & 0xffff));
     const float dmin = half_bits_to_float((uint16_t) (hdr.x >> 16));
     // 8 scales and 8 mins as bytes (same bit surgery as ggml-cpu/quants.c:586-591)
@@ -39,22 +50,26 @@ __device__ __forceinline__ void unit_dot_q4_K(uint32_t w, uint32_t am, uint32_t 
     const uint32_t sc_hi = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
     const uint32_t mn_hi = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
 
-    int isum[NC];
+    int      isum[NC];
+    uint32_t ac[NC];
 #pragma unroll
-    for (int c = 0; c < NC; c++) isum[c] = 0;
+    for (int c = 0; c < NC; c++) {
+        isum[c] = 0;
+        ac[c]   = am + c * cs_m;
+    }
 
-#pragma unroll
-    for (int g = 0; g < 4; g++) {  // 64 weights: 32 bytes, low nibbles = sub-block 2g, high nibbles = sub-block 2g+1
-        const uint4 qa = lds128(w + 16 + 32 * g);
-        const uint4 qb = lds128(w + 32 + 32 * g);
+    static_for<0, 4>([&](auto gi) {  // 64 weights: 32 bytes, low nibbles = sub-block 2g, high nibbles = sub-block 2g+1
+        constexpr int g = decltype(gi)::value;
+        const uint4 qa = lds128o<16 + 32 * g>(w);
+        const uint4 qb = lds128o<32 + 32 * g>(w);
         const uint32_t q[8] = { qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w };
         const uint32_t scw  = g < 2 ? sc_lo : sc_hi;
         const int      s0   = (scw >> (16 * (g & 1))) & 0xff;
         const int      s1   = (scw >> (16 * (g & 1) + 8)) & 0xff;
 #pragma unroll
         for (int c = 0; c < NC; c++) {
-            const uint32_t a  = am + c * cs_m + 64 * g;
-            const uint4    l0 = lds128(a), l1 = lds128(a + 16), h0 = lds128(a + 32), h1 = lds128(a + 48);
+            const uint4 l0 = lds128o<64 * g>(ac[c]), l1 = lds128o<64 * g + 16>(ac[c]), h0 = lds128o<64 * g + 32>(ac[c]),
+                        h1 = lds128o<64 * g + 48>(ac[c]);
             const int lo[8] = { (int) l0.x, (int) l0.y, (int) l0.z, (int) l0.w, (int) l1.x, (int) l1.y, (int) l1.z, (int) l1.w };
             const int hi[8] = { (int) h0.x, (int) h0.y, (int) h0.z, (int) h0.w, (int) h1.x, (int) h1.y, (int) h1.z, (int) h1.w };
             int sl = 0, sh = 0;
@@ -65,10 +80,10 @@ __device__ __forceinline__ void unit_dot_q4_K(uint32_t w, uint32_t am, uint32_t 
             }
             isum[c] += s0 * sl + s1 * (sh >> 4);
         }
-    }
+    });
 #pragma unroll
     for (int c = 0; c < NC; c++) {
-        const uint4 bs = lds128(am + c * cs_m + 256);  // int16 sum of q per 32-block (x8)
+        const uint4 bs = lds128o<256>(ac[c]);  // int16 sum of q per 32-block (x8)
         int imin = dp2a_lo_su((int) bs.x, mn_lo, 0);
         imin     = dp2a_hi_su((int) bs.y, mn_lo, imin);
         imin     = dp2a_lo_su((int) bs.z, mn_hi, imin);
@@ -82,20 +97,22 @@ __device__ __forceinline__ void unit_dot_q4_K(uint32_t w, uint32_t am, uint32_t 
 template <int NC>
 __device__ __forceinline__ void unit_dot_q4_0(uint32_t w, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc)[NC]) {
     uint32_t ww[36];  // 8 blocks of { half d; uint8 qs[16] } = 144 bytes
-#pragma unroll
-    for (int i = 0; i < 9; i++) {
-        const uint4 v = lds128(w + 16 * i);
+    static_for<0, 9>([&](auto ii) {
+        constexpr int i = decltype(ii)::value;
+        const uint4 v = lds128o<16 * i>(w);
         ww[4 * i] = v.x; ww[4 * i + 1] = v.y; ww[4 * i + 2] = v.z; ww[4 * i + 3] = v.w;
-    }
-    uint4 dyh[NC], ys[NC];
+    });
+    uint4    dyh[NC], ys[NC];
+    uint32_t ac[NC];
 #pragma unroll
     for (int c = 0; c < NC; c++) {
-        dyh[c] = lds128(am + c * cs_m + 256);  // half d[8]
-        ys[c]  = lds128(ax + c * cs_x);        // int16 sum[8]
+        ac[c]  = am + c * cs_m;
+        dyh[c] = lds128o<256>(ac[c]);      // half d[8]
+        ys[c]  = lds128(ax + c * cs_x);    // int16 sum[8]
     }
-#pragma unroll
-    for (int b = 0; b < 8; b++) {
-        const int p = 9 * (b >> 1);  // word offset of the block pair
+    static_for<0, 8>([&](auto bi) {
+        constexpr int b = decltype(bi)::value;
+        constexpr int p = 9 * (b >> 1);  // word offset of the block pair
         float    dw;
         uint32_t q[4];
         if ((b & 1) == 0) {  // block starts on a word boundary: d in the low half, nibbles shifted by 16 bits
@@ -109,8 +126,7 @@ __device__ __forceinline__ void unit_dot_q4_0(uint32_t w, uint32_t am, uint32_t 
         }
 #pragma unroll
         for (int c = 0; c < NC; c++) {
-            const uint32_t a  = am + c * cs_m + 32 * b;
-            const uint4    l  = lds128(a), h = lds128(a + 16);  // elements 0..15 (low nibbles), 16..31 (high nibbles)
+            const uint4 l = lds128o<32 * b>(ac[c]), h = lds128o<32 * b + 16>(ac[c]);  // elements 0..15 (low nibbles), 16..31 (high nibbles)
             int sl = 0, sh = 0;
             sl = dp4a_us(q[0] & 0x0f0f0f0fu, (int) l.x, sl); sh = dp4a_us(q[0] & 0xf0f0f0f0u, (int) h.x, sh);
             sl = dp4a_us(q[1] & 0x0f0f0f0fu, (int) l.y, sl); sh = dp4a_us(q[1] & 0xf0f0f0f0u, (int) h.y, sh);
@@ -123,24 +139,28 @@ __device__ __forceinline__ void unit_dot_q4_0(uint32_t w, uint32_t am, uint32_t 
             const int      sumi  = sl + (sh >> 4) - 8 * ysum;  // sum((q-8)*y), ggml-cpu/quants.c:135-146
             acc[c] = fmaf((float) sumi * dw, dy, acc[c]);
         }
-    }
+    });
 }
 
 template <int NC>
 __device__ __forceinline__ void unit_dot_q8_0(uint32_t w, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc)[NC]) {
     (void) ax; (void) cs_x;
     uint32_t ww[68];  // 8 blocks of { half d; int8 qs[32] } = 272 bytes; 128-bit loads at a 272-byte lane stride are conflict free
-#pragma unroll
-    for (int i = 0; i < 17; i++) {
-        const uint4 v = lds128(w + 16 * i);
+    static_for<0, 17>([&](auto ii) {
+        constexpr int i = decltype(ii)::value;
+        const uint4 v = lds128o<16 * i>(w);
         ww[4 * i] = v.x; ww[4 * i + 1] = v.y; ww[4 * i + 2] = v.z; ww[4 * i + 3] = v.w;
+    });
+    uint4    dyh[NC];
+    uint32_t ac[NC];
+#pragma unroll
+    for (int c = 0; c < NC; c++) {
+        ac[c]  = am + c * cs_m;
+        dyh[c] = lds128o<256>(ac[c]);
     }
-    uint4 dyh[NC];
-#pragma unroll
-    for (int c = 0; c < NC; c++) dyh[c] = lds128(am + c * cs_m + 256);
-#pragma unroll
-    for (int b = 0; b < 8; b++) {
-        const int p = 17 * (b >> 1);  // a block pair is 68 bytes = 17 words starting on a word boundary
+    static_for<0, 8>([&](auto bi) {
+        constexpr int b = decltype(bi)::value;
+        constexpr int p = 17 * (b >> 1);  // a block pair is 68 bytes = 17 words starting on a word boundary
         float    dw;
         uint32_t q[8];
         if ((b & 1) == 0) {
@@ -154,8 +174,7 @@ __device__ __forceinline__ void unit_dot_q8_0(uint32_t w, uint32_t am, uint32_t 
         }
 #pragma unroll
         for (int c = 0; c < NC; c++) {
-            const uint32_t a  = am + c * cs_m + 32 * b;
-            const uint4    y0 = lds128(a), y1 = lds128(a + 16);
+            const uint4 y0 = lds128o<32 * b>(ac[c]), y1 = lds128o<32 * b + 16>(ac[c]);
             int s = 0;
             s = dp4a_ss((int) q[0], (int) y0.x, s); s = dp4a_ss((int) q[1], (int) y0.y, s);
             s = dp4a_ss((int) q[2], (int) y0.z, s); s = dp4a_ss((int) q[3], (int) y0.w, s);
@@ -165,7 +184,7 @@ __device__ __forceinline__ void unit_dot_q8_0(uint32_t w, uint32_t am, uint32_t 
             const float    dy    = half_bits_to_float((uint16_t) ((b & 1) ? dword >> 16 : dword & 0xffff));
             acc[c] = fmaf((float) s, dw * dy, acc[c]);  // sumi*(dx*dy), ggml-cpu/quants.c:329
         }
-    }
+    });
 }
 
 template <int TYPE, int NC>
@@ -237,8 +256,11 @@ __device__ __forceinline__ int mv_find_mat(const MvParams & p, int group) {
     return m;
 }
 
-template <int TYPE, int NC>
-__global__ void __launch_bounds__(32 * (MV_MAX_CONS + 1), NC <= 4 ? 2 : 1) mv_fast_kernel(const __grid_constant__ MvParams p) {
+// WIDE: up to 16 consumer warps and the SM to itself (<= 120 registers); otherwise up to 8 consumer warps and, for <= 4
+// columns, two CTAs per SM (<= 112 registers) so that consecutive kernels of the stream overlap
+template <int TYPE, int NC, bool WIDE>
+__global__ void __launch_bounds__(WIDE ? 32 * (MV_MAX_CONS + 1) : 32 * 9, (!WIDE && NC <= 4) ? 2 : 1)
+mv_fast_kernel(const __grid_constant__ MvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int UB    = unit_bytes(TYPE);
     constexpr int STAGE = 32 * UB;
@@ -332,22 +354,33 @@ __global__ void __launch_bounds__(32 * (MV_MAX_CONS + 1), NC <= 4 ? 2 : 1) mv_fa
     griddep_wait();  // everything below reads src1 / writes dst, which earlier kernels of the stream may produce / still read
 
     if (p.fuse_quant) {
-        // fused K1: unit (c, u) of the activations, F32 global -> unit record in shared memory
+        // fused K1: unit (c, u) of the activations, F32 global -> unit record in shared memory. Up to 4 units per warp are
+        // loaded before the first is quantized, so the L2 round trips overlap instead of chaining
         const int n_tasks = NC * U;
-        for (int t = w; t < n_tasks; t += NWC) {
-            const int c = t / U, u = t - c * U;
-            const float * xr = (const float *) ((const char *) p.x + x_off + (int64_t) c * p.x_cs) + (int64_t) u * UNIT_ELEMS + lane * 8;
-            float v[8];
-            if (p.x_vec) {
-                const float4 a = __ldg((const float4 *) xr);
-                const float4 b = __ldg((const float4 *) xr + 1);
-                v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
-                v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
-            } else {
+        for (int t0 = w; t0 < n_tasks; t0 += 4 * NWC) {
+            float v[4][8];
 #pragma unroll
-                for (int i = 0; i < 8; i++) v[i] = __ldg(xr + i);
+            for (int b = 0; b < 4; b++) {
+                const int t = t0 + b * NWC;
+                if (t < n_tasks) {
+                    const int c = t / U, u = t - c * U;
+                    const float * xr = (const float *) ((const char *) p.x + x_off + (int64_t) c * p.x_cs) + (int64_t) u * UNIT_ELEMS + lane * 8;
+                    if (p.x_vec) {
+                        const float4 a = __ldg((const float4 *) xr);
+                        const float4 bb = __ldg((const float4 *) xr + 1);
+                        v[b][0] = a.x; v[b][1] = a.y; v[b][2] = a.z; v[b][3] = a.w;
+                        v[b][4] = bb.x; v[b][5] = bb.y; v[b][6] = bb.z; v[b][7] = bb.w;
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 8; i++) v[b][i] = __ldg(xr + i);
+                    }
+                }
             }
-            quant_unit_store<KIND>(v, lane, act_m + (size_t) t * ACT_MAIN, act_x + (size_t) t * ACT_AUX);
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                const int t = t0 + b * NWC;
+                if (t < n_tasks) quant_unit_store<KIND>(v[b], lane, act_m + (size_t) t * ACT_MAIN, act_x + (size_t) t * ACT_AUX);
+            }
         }
         bar_sync_named(1, NWC * 32);
     } else {
@@ -412,13 +445,13 @@ __global__ void __launch_bounds__(32 * (MV_MAX_CONS + 1), NC <= 4 ? 2 : 1) mv_fa
     }
 }
 
-template <int TYPE, int NC>
-static cudaError_t mv_fast_launch_t(const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
+template <int TYPE, int NC, bool WIDE>
+static cudaError_t mv_fast_launch_w(const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
     static bool attr_done[64] = {};  // one attribute call per instantiation and device
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(mv_fast_kernel<TYPE, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(mv_fast_kernel<TYPE, NC, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
@@ -432,7 +465,16 @@ static cudaError_t mv_fast_launch_t(const MvParams & p, int n_ctas, int n_pairs,
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs    = attr;
     cfg.numAttrs = p.pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, mv_fast_kernel<TYPE, NC>, p);
+    return cudaLaunchKernelEx(&cfg, mv_fast_kernel<TYPE, NC, WIDE>, p);
+}
+
+template <int TYPE, int NC>
+static cudaError_t mv_fast_launch_t(const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
+    if (p.n_cons > 8) {
+        if constexpr (NC <= MV_WIDE_MAX_COLS) return mv_fast_launch_w<TYPE, NC, true>(p, n_ctas, n_pairs, smem, st);
+        else return cudaErrorInvalidValue;
+    }
+    return mv_fast_launch_w<TYPE, NC, false>(p, n_ctas, n_pairs, smem, st);
 }
 
 template <int TYPE>
