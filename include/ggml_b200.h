@@ -168,6 +168,26 @@ B200_API b200_status  b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc
 B200_API b200_status  b200_mm_ids_sort(b200_ctx * ctx, const int32_t * ids, int64_t n_used, int64_t n_tok, size_t ids_nb1,
                                        int64_t n_as, int32_t * sorted_pairs, int32_t * expert_bounds);
 
+/* ---------------------------------------------------------------- row-split tensor parallelism ---- */
+
+/* Weight rows split over n_ranks GPUs of one box (ggml_backend_split_buffer_type + ggml_cuda_op_mul_mat,
+ * ggml-cuda.cu:807-1102, 1447-1765): each rank holds rows [lo, hi) of every split matrix, src1 is replicated, and every rank
+ * needs the whole dst. Instead of the reference's cudaMemcpy2DPeerAsync per device (:1721-1734) the kernels store each
+ * result into the dst of every rank (peer memory over NVLink/NVSwitch) and exchange one flag per rank and op: the
+ * all-gather is part of the MUL_MAT launch. While a context is in this mode, every MUL_MAT / MUL_MAT_ID it runs must have
+ *   - desc.ne01 = the rank's row count, src0 = the rank's rows, dst = address of (row lo, column 0) inside the rank's FULL dst,
+ *     nb1 = the full dst's column stride;
+ *   - dst inside a region that exists on every rank such that  peer address = local address + dst_delta[r]  (symmetric
+ *     allocation; single-process hosts enable peer access, one-process-per-GPU hosts map the peers' allocations);
+ *   - the same sequence of calls on every rank (the flag protocol counts ops).
+ * sync_words[r]: rank r's 16 zero-initialised uint32 words (also peer-mapped). */
+typedef struct {
+    int32_t n_ranks, rank;
+    int64_t dst_delta[8];
+    void *  sync_words[8];
+} b200_row_split;
+B200_API b200_status  b200_ctx_set_row_split(b200_ctx * ctx, const b200_row_split * rs);   /* rs == NULL or n_ranks <= 1: off */
+
 /* ---------------------------------------------------------------- prefill weight cache ---- */
 
 /* The tcgen05 path consumes an int8, K-major, TMA-tileable expansion of a weight matrix plus per-32 float scales

@@ -31,7 +31,7 @@ EXPORTS = [
     "b200_event_create", "b200_event_destroy", "b200_event_record", "b200_event_wait", "b200_event_synchronize",
     "b200_event_elapsed_ms", "b200_quantize_q8_0", "b200_quantize_q8_1", "b200_quantize_q8_K", "b200_quantize_units",
     "b200_mul_mat_supported", "b200_mul_mat", "b200_mul_mat_shared_src1", "b200_mul_mat_host", "b200_mul_mat_id_supported",
-    "b200_mul_mat_id", "b200_mm_ids_sort", "b200_ctx_set_weight_cache", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
+    "b200_mul_mat_id", "b200_mm_ids_sort", "b200_ctx_set_row_split", "b200_ctx_set_weight_cache", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
 ]
 
 
@@ -72,6 +72,10 @@ class MulMatIdDesc(C.Structure):
     def contiguous(cls, t, M, K, n_as, n_used, ne11, n_tok):
         rb = row_size(t, K)
         return cls(t, K, M, n_as, rb, rb * M, ne11, n_tok, 4 * K, 4 * K * ne11, n_used, 4 * n_used, 4 * M, 4 * M * n_used)
+
+
+class RowSplit(C.Structure):
+    _fields_ = [("n_ranks", C.c_int32), ("rank", C.c_int32), ("dst_delta", C.c_int64 * 8), ("sync_words", C.c_void_p * 8)]
 
 
 class B200Error(RuntimeError):
@@ -116,6 +120,7 @@ def lib() -> C.CDLL:
         L.b200_mm_ids_sort.argtypes = [vp, vp, i64, i64, sz, i64, vp, vp]
         for n in ("b200_memcpy_h2d_async", "b200_memcpy_d2h_async", "b200_memcpy_d2d_async"):
             getattr(L, n).argtypes = [vp, vp, vp, sz]
+        L.b200_ctx_set_row_split.argtypes = [vp, C.POINTER(RowSplit)]
         L.b200_ctx_set_weight_cache.argtypes = [vp, ci]
         L.b200_ctx_set_weight_cache.restype = None
         L.b200_weight_cache_invalidate.argtypes = [ci, vp, sz]
@@ -170,6 +175,19 @@ class Context:
 
     def force_path(self, p: int):
         lib().b200_ctx_set_force_path(self.h, p)
+
+    def row_split(self, rank: int, dst_ptrs, sync_ptrs):
+        """fused all-gather mode: dst_ptrs[r] / sync_ptrs[r] = base address of the symmetric dst region / sync words on rank r"""
+        n = len(dst_ptrs)
+        if n <= 1:
+            check(lib().b200_ctx_set_row_split(self.h, None), "b200_ctx_set_row_split")
+            return
+        rs = RowSplit()
+        rs.n_ranks, rs.rank = n, rank
+        for r in range(n):
+            rs.dst_delta[r] = int(dst_ptrs[r]) - int(dst_ptrs[rank])
+            rs.sync_words[r] = int(sync_ptrs[r])
+        check(lib().b200_ctx_set_row_split(self.h, C.byref(rs)), "b200_ctx_set_row_split")
 
     def weight_cache(self, enable: bool):
         """keep int8 expansions of weight matrices across calls; the caller must invalidate ranges it overwrites or frees"""
@@ -229,7 +247,9 @@ class Context:
         check(lib().b200_mul_mat(self.h, C.byref(desc), W.data_ptr(), X.data_ptr(), out.data_ptr()), "b200_mul_mat")
         return out
 
-    def mul_mat_shared(self, t: int, Ws, X, outs=None):
+    def mul_mat_shared(self, t: int, Ws, X, outs=None, dst_strides=None):
+        """several weight matrices against one X in one launch; dst_strides[i] = bytes between dst columns of output i
+        (default: contiguous [N, M_i])"""
         torch = self.torch
         N, K = X.shape
         n = len(Ws)
@@ -239,6 +259,9 @@ class Context:
             M = W.numel() // row_size(t, K)
             Ms.append(M)
             descs[i] = MulMatDesc.contiguous(t, M, K, N)
+            if dst_strides is not None:
+                descs[i].nb1 = dst_strides[i]
+                descs[i].nb2 = descs[i].nb3 = dst_strides[i] * N
         if outs is None:
             outs = [torch.empty((N, M), dtype=torch.float32, device=X.device) for M in Ms]
         wp = (C.c_void_p * n)(*[W.data_ptr() for W in Ws])

@@ -138,6 +138,25 @@ b200_status  b200_ctx_synchronize(b200_ctx * ctx) {
     return B200_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ row split
+
+b200_status b200_ctx_set_row_split(b200_ctx * ctx, const b200_row_split * rs) {
+    if (!ctx) return fail(B200_ERR_ARG, "null context");
+    ctx->split = SplitParams{};
+    if (!rs || rs->n_ranks <= 1) return B200_OK;
+    if (rs->n_ranks > SPLIT_MAX_RANKS || rs->rank < 0 || rs->rank >= rs->n_ranks || !rs->sync_words[rs->rank])
+        return fail(B200_ERR_ARG, "bad row-split description (n_ranks=%d rank=%d)", rs->n_ranks, rs->rank);
+    ctx->split.n_ranks = rs->n_ranks;
+    ctx->split.rank    = rs->rank;
+    for (int r = 0; r < rs->n_ranks; r++) {
+        if (!rs->sync_words[r]) return fail(B200_ERR_ARG, "row split: rank %d has no sync words", r);
+        ctx->split.dst_delta[r] = rs->dst_delta[r];
+        ctx->split.sync_peer[r] = (uint32_t *) rs->sync_words[r];
+    }
+    ctx->split.sync_local = (uint32_t *) rs->sync_words[rs->rank];
+    return B200_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ memory
 
 b200_status b200_malloc(int device, size_t size, void ** ptr) {
@@ -373,6 +392,7 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
             p.n_cons   = cfg.nw;
             p.n_stages = cfg.ns;
             p.pdl      = ctx->pdl;
+            p.split    = ctx->split;
             if (x) {
                 p.fuse_quant = 1;
                 p.x          = (const float *) ((const char *) x + (size_t) c0 * x_cs);

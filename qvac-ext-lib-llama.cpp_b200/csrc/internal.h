@@ -41,6 +41,7 @@ struct b200_ctx {
     int          pdl        = 1;               // programmatic dependent launch of the mat-vec kernels; GGML_B200_PDL=0 disables
     int          weight_cache = 0;             // keep the int8 expansion of a weight matrix across calls (owner must invalidate)
     int          mmq_min_cols = 0;             // 0 = auto; GGML_B200_MMQ_MIN
+    b200::SplitParams split = {};              // row-split all-gather fused into the kernels (b200_ctx_set_row_split)
     int          fuse_quant = 1;               // quantize src1 inside the mat-vec kernel when small; GGML_B200_FUSE_QUANT=0 disables
 };
 

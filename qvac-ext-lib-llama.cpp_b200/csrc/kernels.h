@@ -30,6 +30,53 @@ struct MvIds {
     int             n_used, ne11, n_as;
 };
 
+// Row-split tensor parallelism: this rank computes a slice of dst's rows and the epilogue stores every value
+// into the dst of ALL ranks (peer memory over NVLink / NVSwitch) - the all-gather is fused into the kernel. Completion:
+// the last CTA to finish bumps the local epoch, writes it into every peer's flag slot for this rank (st.release.sys) and
+// waits until every peer's flag has reached the same epoch (ld.acquire.sys); kernel completion therefore means "dst is
+// complete on this rank". Epoch and CTA counter live in device memory, so CUDA-graph replays keep counting.
+constexpr int SPLIT_MAX_RANKS = 8;
+struct SplitParams {
+    int        n_ranks;                       // 0 / 1 = off
+    int        rank;
+    int64_t    dst_delta[SPLIT_MAX_RANKS];    // bytes from a local dst address to the same element on rank r (0 for own rank)
+    uint32_t * sync_local;                    // [0..7] flags written by the peers, [8] epoch, [9] CTA counter
+    uint32_t * sync_peer[SPLIT_MAX_RANKS];    // rank r's sync words
+};
+
+__device__ __forceinline__ void split_store(const SplitParams & sp, float * addr, float v) {
+    if (sp.n_ranks <= 1) {
+        *addr = v;
+    } else {
+        for (int r = 0; r < sp.n_ranks; r++) *(float *) ((char *) addr + sp.dst_delta[r]) = v;
+    }
+}
+
+// called by ONE warp of every CTA after all of the CTA's stores are done and fenced (__threadfence_system + CTA barrier)
+__device__ __forceinline__ void split_complete(const SplitParams & sp, unsigned n_ctas) {
+    const int lane = threadIdx.x & 31;
+    unsigned last = 0;
+    if (lane == 0) last = atomicAdd(&sp.sync_local[9], 1u) == n_ctas - 1 ? 1u : 0u;
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (!last) return;
+    __threadfence_system();
+    uint32_t e = 0;
+    if (lane == 0) {
+        e = sp.sync_local[8] + 1;
+        sp.sync_local[8] = e;
+        sp.sync_local[9] = 0;
+    }
+    e = __shfl_sync(0xffffffffu, e, 0);
+    if (lane < sp.n_ranks && lane != sp.rank) {
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sp.sync_peer[lane] + sp.rank), "r"(e) : "memory");
+        uint32_t v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(sp.sync_local + lane) : "memory");
+        } while ((int32_t) (v - e) < 0);
+    }
+    __syncwarp();
+}
+
 struct MvMat {
     const uint8_t * w;        // row 0 of the weight matrix (16-byte aligned)
     int64_t         nb01;     // bytes between rows (multiple of 16)
@@ -57,6 +104,7 @@ struct MvParams {
     const uint8_t * act_aux;          // [ncols][U][16]
     // MUL_MAT_ID mode (ids != nullptr): blockIdx.y = pair p = t*n_used + i; one column per pair; mat[0] = expert 0
     MvIds           ids;
+    SplitParams     split;
 };
 
 // smem bytes needed by the fast kernel for a configuration

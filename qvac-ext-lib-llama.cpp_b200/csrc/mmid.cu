@@ -155,6 +155,7 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
         for (int i = 1; i < MV_MAX_MATS; i++) p.mat[i].group0 = INT32_MAX;
         p.total_groups = (int) ((M + p.rpg - 1) / p.rpg);
         p.pdl          = ctx->pdl;
+        p.split        = ctx->split;
         p.fuse_quant   = fuse ? 1 : 0;
         p.x_vec        = (uintptr_t) b % 16 == 0 && d->nb11 % 16 == 0 && d->nb12 % 16 == 0;
         p.ids          = mi;

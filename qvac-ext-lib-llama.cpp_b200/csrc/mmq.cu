@@ -161,6 +161,7 @@ __global__ void __launch_bounds__(128) quantize_tiles_kernel(const float * __res
 // ------------------------------------------------------------------------------------------------ the GEMM (K4)
 
 struct MmqParams {
+    SplitParams split;
     float * dst;
     int64_t ldc;  // floats between dst columns (tokens)
     int     M, N, K;
@@ -328,15 +329,17 @@ mmq_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
 #pragma unroll
                 for (int j = 0; j < 32; j++) {
                     const int n = n0 + half * 64 + 2 * j;
-                    if (n < p.N) p.dst[(int64_t) n * p.ldc + m] = acc[j].x;
-                    if (n + 1 < p.N) p.dst[(int64_t) (n + 1) * p.ldc + m] = acc[j].y;
+                    if (n < p.N) split_store(p.split, p.dst + (int64_t) n * p.ldc + m, acc[j].x);
+                    if (n + 1 < p.N) split_store(p.split, p.dst + (int64_t) (n + 1) * p.ldc + m, acc[j].y);
                 }
             }
         }
     }
 
+    if (p.split.n_ranks > 1) __threadfence_system();
     tc_fence_before();
     __syncthreads();
+    if (p.split.n_ranks > 1 && warp == 0) split_complete(p.split, gridDim.x);
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc<512>(tmem_base);
@@ -553,6 +556,7 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
     }
 
     MmqParams p;
+    p.split = ctx->split;
     p.dst = dst; p.ldc = ldc; p.M = (int) M; p.N = (int) N; p.K = (int) K;
     p.m_tiles = (int) ((M + BM - 1) / BM);
     p.n_tiles = (int) ((N + BN - 1) / BN);

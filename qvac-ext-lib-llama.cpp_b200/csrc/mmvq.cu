@@ -286,7 +286,10 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
         const int pair = blockIdx.y;
         const int t = pair / p.ids.n_used, i = pair - t * p.ids.n_used;
         const int e = p.ids.ids[(int64_t) t * p.ids.ids_rs + i];
-        if (e < 0 || e >= p.ids.n_as) return;  // ggml-cpu asserts here (ggml-cpu.c:1574); never read out of bounds
+        if (e < 0 || e >= p.ids.n_as) {  // ggml-cpu asserts here (ggml-cpu.c:1574); never read out of bounds
+            if (p.split.n_ranks > 1 && warp == 0) split_complete(p.split, gridDim.x * gridDim.y);
+            return;
+        }
         w_off   = (int64_t) e * p.ids.nb02;
         dst_off = (int64_t) t * p.ids.dst_ts + (int64_t) i * p.ids.dst_is;
         act_col = t * p.ids.ne11 + i % p.ids.ne11;
@@ -436,12 +439,17 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
                     const float t = __shfl_xor_sync(0xffffffffu, v, o);
                     if (o < L) v += t;
                 }
-                if (sub == 0 && row < M && rr < p.rpg) p.mat[m].dst[dst_off + (int64_t) c * p.mat[m].dst_cs + row] = v;
+                if (sub == 0 && row < M && rr < p.rpg) split_store(p.split, p.mat[m].dst + dst_off + (int64_t) c * p.mat[m].dst_cs + row, v);
                 acc[c] = 0.0f;
             }
         }
         if (++stage == NS) { stage = 0; phase ^= 1; }
         if (++slice == p.slices) { slice = 0; j++; }
+    }
+    if (p.split.n_ranks > 1) {  // fused all-gather: this CTA's slice is on its way to every rank; the last CTA exchanges flags
+        __threadfence_system();
+        bar_sync_named(1, NWC * 32);
+        if (w == 0) split_complete(p.split, gridDim.x * gridDim.y);
     }
 }
 
