@@ -200,6 +200,23 @@ B200_API void         b200_weight_cache_invalidate(int device, const void * base
 B200_API void         b200_weight_cache_clear(int device);
 B200_API size_t       b200_weight_cache_bytes(void);
 
+/* Cross-kernel weight prefetch for decode. A token step is a dependent chain of short mat-vec kernels; at every kernel
+ * boundary HBM idles for the launch / dependency / drain latency (~3 us, as long as a 4096x4096 q4 matrix takes to stream).
+ * With prefetch on, a context remembers which launch followed each weight tensor the last time (decode replays the same
+ * graph every token: ggml_backend_sched, ggml-backend.cpp:1439-1560) and lets every mat-vec kernel pull the first
+ * `kb_per_cta` KB per SM of the predicted next kernel's weights into L2 once its own copies are in flight. Results are
+ * unaffected; a wrong prediction only costs the prefetch traffic. Predictions hold raw device pointers: they are dropped
+ * whenever b200_free is called, and a caller that frees weight memory by other means must switch prefetch off (0) first. */
+B200_API void         b200_ctx_set_prefetch(b200_ctx * ctx, int kb_per_cta);
+
+/* Debug: device-side timeline of the mat-vec launches of a context (how profiles/ explains kernel-boundary latency without a
+ * profiler attached). n_slots > 0 allocates n_slots x sm_count x 8 uint64; launch number L of the context (see
+ * b200_ctx_launch_count) records into slot L % n_slots, CTA b at [slot][b][0..7] = %globaltimer ns of: CTA start, first weight
+ * copy issued, last weight copy issued, consumers past the stream dependency, activations quantized, first stage landed,
+ * consumer warp 0 done; [7] = SM id. n_slots = 0 frees it. b200_ctx_trace_read synchronizes the stream and copies it out. */
+B200_API b200_status  b200_ctx_trace(b200_ctx * ctx, int n_slots);
+B200_API b200_status  b200_ctx_trace_read(b200_ctx * ctx, void * host, size_t bytes);
+
 #ifdef __cplusplus
 }
 #endif

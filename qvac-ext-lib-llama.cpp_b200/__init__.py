@@ -31,7 +31,7 @@ EXPORTS = [
     "b200_event_create", "b200_event_destroy", "b200_event_record", "b200_event_wait", "b200_event_synchronize",
     "b200_event_elapsed_ms", "b200_quantize_q8_0", "b200_quantize_q8_1", "b200_quantize_q8_K", "b200_quantize_units",
     "b200_mul_mat_supported", "b200_mul_mat", "b200_mul_mat_shared_src1", "b200_mul_mat_host", "b200_mul_mat_id_supported",
-    "b200_mul_mat_id", "b200_mm_ids_sort", "b200_ctx_set_row_split", "b200_ctx_set_weight_cache", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
+    "b200_mul_mat_id", "b200_mm_ids_sort", "b200_ctx_set_row_split", "b200_ctx_set_weight_cache", "b200_ctx_set_prefetch", "b200_ctx_trace", "b200_ctx_trace_read", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
 ]
 
 
@@ -76,6 +76,28 @@ class MulMatIdDesc(C.Structure):
 
 class RowSplit(C.Structure):
     _fields_ = [("n_ranks", C.c_int32), ("rank", C.c_int32), ("dst_delta", C.c_int64 * 8), ("sync_words", C.c_void_p * 8)]
+
+
+ROW_SPLIT_ROUNDING = 128   # rows: the tensor-core kernel's tile height (the reference rounds to its mmq_y, ggml-cuda.cu:773-784)
+
+
+def row_split_bounds(nrows: int, n_ranks: int, rank: int, tensor_split=None, rounding: int = ROW_SPLIT_ROUNDING):
+    """[row_low, row_high) of `rank`'s slice of a row-split weight tensor. Same rule as the reference's get_row_split
+    (ggml-cuda.cu:786-799): tensor_split holds the CUMULATIVE start fraction of every device (llama.cpp normalises
+    --tensor-split into that form, ggml-cuda.cu:941-967), boundaries are rounded down to `rounding`, the last device takes the rest.
+    The slices of ranks 0..n-1 are disjoint, ordered and cover [0, nrows); a slice may be empty."""
+    if tensor_split is None:
+        tensor_split = [r / n_ranks for r in range(n_ranks)]
+    if len(tensor_split) != n_ranks or tensor_split[0] != 0 or any(b < a for a, b in zip(tensor_split, tensor_split[1:])):
+        raise ValueError("tensor_split must hold n_ranks non-decreasing cumulative fractions starting at 0")
+    lo = 0 if rank == 0 else int(nrows * tensor_split[rank])
+    lo -= lo % rounding
+    if rank == n_ranks - 1:
+        hi = nrows
+    else:
+        hi = int(nrows * tensor_split[rank + 1])
+        hi -= hi % rounding
+    return lo, hi
 
 
 class B200Error(RuntimeError):
@@ -123,6 +145,10 @@ def lib() -> C.CDLL:
         L.b200_ctx_set_row_split.argtypes = [vp, C.POINTER(RowSplit)]
         L.b200_ctx_set_weight_cache.argtypes = [vp, ci]
         L.b200_ctx_set_weight_cache.restype = None
+        L.b200_ctx_set_prefetch.argtypes = [vp, ci]
+        L.b200_ctx_set_prefetch.restype = None
+        L.b200_ctx_trace.argtypes = [vp, ci]
+        L.b200_ctx_trace_read.argtypes = [vp, vp, C.c_size_t]
         L.b200_weight_cache_invalidate.argtypes = [ci, vp, sz]
         L.b200_weight_cache_invalidate.restype = None
         L.b200_weight_cache_clear.argtypes = [ci]
@@ -192,6 +218,22 @@ class Context:
     def weight_cache(self, enable: bool):
         """keep int8 expansions of weight matrices across calls; the caller must invalidate ranges it overwrites or frees"""
         lib().b200_ctx_set_weight_cache(self.h, 1 if enable else 0)
+
+    def prefetch(self, kb_per_cta=32):
+        """cross-kernel weight prefetch for decode (b200_ctx_set_prefetch); 0 switches it off"""
+        lib().b200_ctx_set_prefetch(self.h, int(kb_per_cta))
+
+    def trace(self, n_slots: int):
+        """debug timeline of the mat-vec launches (b200_ctx_trace); 0 = off"""
+        check(lib().b200_ctx_trace(self.h, int(n_slots)), "b200_ctx_trace")
+        self._trace_slots = int(n_slots)
+
+    def trace_read(self, sm_count: int = 148):
+        """-> uint64 array [n_slots, sm_count, 8]"""
+        import numpy as np
+        a = np.zeros((self._trace_slots, sm_count, 8), dtype=np.uint64)
+        check(lib().b200_ctx_trace_read(self.h, a.ctypes.data, a.nbytes), "b200_ctx_trace_read")
+        return a
 
     def weight_cache_clear(self):
         lib().b200_weight_cache_clear(self.device)

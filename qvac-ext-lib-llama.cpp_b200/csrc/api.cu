@@ -4,6 +4,8 @@
 
 #include "internal.h"
 
+#include <atomic>
+
 #include <mutex>
 #include <vector>
 
@@ -112,6 +114,8 @@ b200_status b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     if (const char * s = getenv("GGML_B200_MMQ_MIN")) c->mmq_min_cols = atoi(s);
     if (const char * s = getenv("GGML_B200_WEIGHT_CACHE")) c->weight_cache = atoi(s) != 0;
     if (const char * s = getenv("GGML_B200_FUSE_QUANT")) c->fuse_quant = atoi(s) != 0;
+    if (const char * s = getenv("GGML_B200_PREFETCH_KB")) c->prefetch_kb = atoi(s);
+    if (const char * s = getenv("GGML_B200_DBG")) c->dbg = atoi(s);
     *out = c;
     return B200_OK;
 }
@@ -123,6 +127,7 @@ void b200_ctx_destroy(b200_ctx * ctx) {
     if (ctx->scratch) cudaFree(ctx->scratch);
     if (ctx->io) cudaFree(ctx->io);
     if (ctx->scratch2) cudaFree(ctx->scratch2);
+    if (ctx->trace) cudaFree(ctx->trace);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -132,6 +137,35 @@ void *       b200_ctx_stream(const b200_ctx * ctx) { return (void *) ctx->stream
 uint64_t     b200_ctx_launch_count(const b200_ctx * ctx) { return ctx->launches; }
 void         b200_ctx_set_force_path(b200_ctx * ctx, int path) { ctx->force_path = path; }
 void         b200_ctx_set_weight_cache(b200_ctx * ctx, int enable) { ctx->weight_cache = enable != 0; }
+b200_status  b200_ctx_trace(b200_ctx * ctx, int n_slots) {
+    CU(cudaSetDevice(ctx->device));
+    if (ctx->trace) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        CU(cudaFree(ctx->trace));
+        ctx->trace = nullptr;
+        ctx->trace_slots = 0;
+    }
+    if (n_slots <= 0) return B200_OK;
+    const size_t bytes = (size_t) n_slots * ctx->sm_count * 64;
+    CU(cudaMalloc((void **) &ctx->trace, bytes));
+    CU(cudaMemset(ctx->trace, 0, bytes));
+    ctx->trace_slots = n_slots;
+    return B200_OK;
+}
+b200_status  b200_ctx_trace_read(b200_ctx * ctx, void * host, size_t bytes) {
+    if (!ctx->trace) return fail(B200_ERR_ARG, "trace is off");
+    const size_t have = (size_t) ctx->trace_slots * ctx->sm_count * 64;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaMemcpy(host, ctx->trace, bytes < have ? bytes : have, cudaMemcpyDeviceToHost));
+    return B200_OK;
+}
+void         b200_ctx_set_prefetch(b200_ctx * ctx, int kb_per_cta) {
+    if (getenv("GGML_B200_PREFETCH_KB")) return;  // the environment knob wins (experiments)
+    ctx->prefetch_kb = kb_per_cta < 0 ? 0 : kb_per_cta;
+    ctx->next_of.clear();
+    ctx->last_key = nullptr;
+}
 b200_status  b200_ctx_synchronize(b200_ctx * ctx) {
     CU(cudaSetDevice(ctx->device));
     CU(cudaStreamSynchronize(ctx->stream));
@@ -170,7 +204,12 @@ b200_status b200_malloc(int device, size_t size, void ** ptr) {
     }
     return B200_OK;
 }
+static std::atomic<uint64_t> g_mem_gen{ 1 };
+uint64_t b200_mem_generation() { return g_mem_gen.load(std::memory_order_relaxed); }
+void     b200_mem_generation_bump() { g_mem_gen.fetch_add(1, std::memory_order_relaxed); }
+
 b200_status b200_free(int device, void * ptr) {
+    b200_mem_generation_bump();  // learned next-kernel predictions may point into this allocation
     CU(cudaSetDevice(device));
     CU(cudaFree(ptr));
     return B200_OK;
@@ -403,6 +442,34 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
                 p.act_aux  = act_aux + (size_t) c0 * U * ACT_AUX;
             }
             const int n_ctas = g < ctx->sm_count ? g : ctx->sm_count;
+            if (ctx->prefetch_kb > 0) {
+                if (ctx->mem_gen != b200_mem_generation()) {  // an allocation went away: forget what was learned
+                    ctx->next_of.clear();
+                    ctx->last_key = nullptr;
+                    ctx->mem_gen  = b200_mem_generation();
+                }
+                const void * key = p.mat[0].w;
+                auto it = ctx->next_of.find(key);
+                if (it != ctx->next_of.end()) p.next = it->second;
+                if (ctx->last_key) {  // this launch is what followed `last_key`
+                    if (ctx->next_of.size() > 65536) ctx->next_of.clear();
+                    MvNext & nx = ctx->next_of[ctx->last_key];
+                    memset(&nx, 0, sizeof(nx));
+                    for (int i = 0; i < p.n_mats; i++) {
+                        nx.w[i] = p.mat[i].w; nx.nb01[i] = p.mat[i].nb01; nx.M[i] = p.mat[i].M; nx.group0[i] = p.mat[i].group0;
+                    }
+                    nx.n_mats         = p.n_mats;
+                    nx.total_groups   = p.total_groups;
+                    nx.n_ctas         = n_ctas;
+                    nx.rpg            = p.rpg;
+                    nx.row_bytes      = U * unit_bytes(type);
+                    const int64_t gb  = (int64_t) p.rpg * nx.row_bytes;
+                    nx.groups_per_cta = (int) (((int64_t) ctx->prefetch_kb * 1024 + gb - 1) / gb);
+                }
+                ctx->last_key = key;
+            }
+            p.dbg = ctx->dbg;
+            if (ctx->trace) p.trace = ctx->trace + (size_t) (ctx->launches % ctx->trace_slots) * ctx->sm_count * 8;
             CU(mv_fast_launch(type, nc, p, n_ctas, 1, cfg.smem, ctx->stream));
             ctx->launches++;
         }

@@ -128,5 +128,9 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void * src, uint32_
         "l"(src), "r"(bytes), "r"(bar), "l"(policy)
         : "memory");
 }
+// asynchronous prefetch of [src, src + bytes) into L2 (no destination, no completion); src 16-B aligned, bytes % 16 == 0
+__device__ __forceinline__ void bulk_prefetch_l2(const void * src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 
 } // namespace b200

@@ -329,6 +329,9 @@ ggml_backend_t dev_init_backend(ggml_backend_dev_t dev, const char *) {
     // matrix used by the tcgen05 prefill kernel is built once and kept (GGML_B200_WEIGHT_CACHE=0 rebuilds it per call)
     const char * wc = getenv("GGML_B200_WEIGHT_CACHE");
     b200_ctx_set_weight_cache(ctx, !(wc && !atoi(wc)));
+    // every src0 this backend sees lives in a buffer it allocated with b200_malloc and frees with b200_free (which drops the
+    // learned next-kernel predictions), so the decode weight prefetch is safe to leave on
+    b200_ctx_set_prefetch(ctx, 32);
     const char * nf = getenv("GGML_B200_DISABLE_FUSION");
     be_ctx * c = new be_ctx{ d->device, ctx, d->name, !(nf && atoi(nf)) };
     return new ggml_backend{ be_guid(), be_iface, dev, c };

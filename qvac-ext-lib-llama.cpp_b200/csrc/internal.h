@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <unordered_map>
 
 b200_status b200_fail(b200_status st, const char * fmt, ...);
 
@@ -43,7 +44,21 @@ struct b200_ctx {
     int          mmq_min_cols = 0;             // 0 = auto; GGML_B200_MMQ_MIN
     b200::SplitParams split = {};              // row-split all-gather fused into the kernels (b200_ctx_set_row_split)
     int          fuse_quant = 1;               // quantize src1 inside the mat-vec kernel when small; GGML_B200_FUSE_QUANT=0 disables
+    // cross-kernel weight prefetch (kernels.h MvNext): the launch that followed a weight tensor last time is assumed to follow
+    // it again (decode repeats the same graph every token). Keyed by the first weight pointer of a launch.
+    int          prefetch_kb = 0;              // per-CTA prefetch depth in KB; 0 = off (b200_ctx_set_prefetch / GGML_B200_PREFETCH_KB)
+    std::unordered_map<const void *, b200::MvNext> next_of;
+    const void * last_key   = nullptr;
+    uint64_t     mem_gen    = 0;               // generation of the device allocations the predictions were learned under
+    // debug timeline of the mat-vec launches (b200_ctx_trace): slot = launch counter % trace_slots, sm_count CTAs x 8 u64 each
+    unsigned long long * trace = nullptr;
+    int          trace_slots = 0;
+    int          dbg = 0;                      // GGML_B200_DBG: experiment switches handed to the kernels
 };
+
+// bumped whenever device memory the library may hold predictions / caches for is freed or rewritten
+uint64_t b200_mem_generation();
+void     b200_mem_generation_bump();
 
 // grow-only device buffer owned by the context (fails instead of reallocating while the stream is being captured)
 b200_status b200_ensure(b200_ctx * ctx, void ** buf, size_t * cur, size_t need);

@@ -70,9 +70,16 @@ __device__ __forceinline__ void split_complete(const SplitParams & sp, unsigned 
     if (lane < sp.n_ranks && lane != sp.rank) {
         asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sp.sync_peer[lane] + sp.rank), "r"(e) : "memory");
         uint32_t v;
-        do {
+        uint64_t t0 = 0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (unsigned spins = 1;; spins++) {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(sp.sync_local + lane) : "memory");
-        } while ((int32_t) (v - e) < 0);
+            if ((int32_t) (v - e) >= 0) break;
+            if ((spins & 0xfff) == 0) {  // a peer that never arrives (crashed rank, mismatched launch sequence) must not hang the GPU
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 5000000000ull) __trap();
+            }
+        }
     }
     __syncwarp();
 }
@@ -84,6 +91,25 @@ struct MvMat {
     int64_t         dst_cs;   // floats between dst columns
     int             M;        // rows
     int             group0;   // first global row-group id of this matrix
+};
+
+// Cross-kernel weight prefetch. A decode step is a dependent chain of small mat-vec kernels: every kernel boundary costs
+// ~3 us of launch / dependency / drain latency during which HBM would idle. Weights never depend on earlier kernels, so the
+// producer warp of THIS kernel, once its own copies are issued, pulls the head of the NEXT kernel's weight stream (the first
+// `groups_per_cta` row groups of every CTA's range - what that kernel's rings will ask for first) into L2 with
+// cp.async.bulk.prefetch.L2. The next kernel is predicted by the context (api.cu: the launch that followed these weights
+// last time); a wrong prediction costs only the prefetch traffic.
+struct MvNext {
+    const uint8_t * w[MV_MAX_MATS];
+    int64_t         nb01[MV_MAX_MATS];
+    int             M[MV_MAX_MATS];
+    int             group0[MV_MAX_MATS];
+    int             n_mats;           // 0 = no prediction
+    int             total_groups;
+    int             n_ctas;           // grid of the predicted launch
+    int             rpg;
+    int             row_bytes;        // U * unit_bytes
+    int             groups_per_cta;   // prefetch depth
 };
 
 struct MvParams {
@@ -105,6 +131,12 @@ struct MvParams {
     // MUL_MAT_ID mode (ids != nullptr): blockIdx.y = pair p = t*n_used + i; one column per pair; mat[0] = expert 0
     MvIds           ids;
     SplitParams     split;
+    MvNext          next;
+    // debug timeline (b200_ctx_trace): 8 x u64 per CTA at trace + blockIdx.x*8: globaltimer ns of [0] CTA start, [1] first and
+    // [2] last weight copy issued, [3] consumer warp 0 past griddepcontrol.wait, [4] activations quantized, [5] first stage
+    // landed, [6] consumer warp 0 done, [7] SM id. nullptr = off.
+    unsigned long long * trace;
+    int             dbg;      // experiment switches (GGML_B200_DBG)
 };
 
 // smem bytes needed by the fast kernel for a configuration

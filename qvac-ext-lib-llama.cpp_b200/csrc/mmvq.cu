@@ -249,6 +249,13 @@ __device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
     return ok != 0;
 }
 
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define MV_TRACE(i) do { if (p.trace && lane == 0) p.trace[(size_t) blockIdx.x * 8 + (i)] = global_ns(); } while (0)
+
 __device__ __forceinline__ int mv_find_mat(const MvParams & p, int group) {
     int m = 0;
 #pragma unroll
@@ -258,8 +265,11 @@ __device__ __forceinline__ int mv_find_mat(const MvParams & p, int group) {
 
 // WIDE: up to 16 consumer warps and the SM to itself (<= 120 registers); otherwise up to 8 consumer warps and, for <= 4
 // columns, two CTAs per SM (<= 112 registers) so that consecutive kernels of the stream overlap
-template <int TYPE, int NC, bool WIDE>
-__global__ void __launch_bounds__(WIDE ? 32 * (MV_MAX_CONS + 1) : 32 * 9, (!WIDE && NC <= 4) ? 2 : 1)
+// WCLASS (CTA shapes): 0 = up to 8 consumer warps, two CTAs per SM for <= 4 columns; 1 = up to 16 consumer warps, the SM to
+// itself; 2 = up to 11 consumer warps and two CTAs per SM (<= 80 registers): consecutive kernels of a stream co-reside
+constexpr int mv_class_warps(int c) { return c == 1 ? MV_MAX_CONS + 1 : c == 2 ? 12 : 9; }
+template <int TYPE, int NC, int WCLASS>
+__global__ void __launch_bounds__(32 * mv_class_warps(WCLASS), (WCLASS == 2 || (WCLASS == 0 && NC <= 4)) ? 2 : 1)
 mv_fast_kernel(const __grid_constant__ MvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int UB    = unit_bytes(TYPE);
@@ -300,49 +310,89 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
     const int g_begin = (int) ((int64_t) p.total_groups * blockIdx.x / gridDim.x);
     const int g_end   = (int) ((int64_t) p.total_groups * (blockIdx.x + 1) / gridDim.x);
 
-    if (threadIdx.x == 0) {
-        mbar_init(smem_u32(act_bar), 1);
-        for (int i = 0; i < NWC * NS; i++) {
-            mbar_init(smem_u32(full + i), 1);
-            mbar_init(smem_u32(empty + i), 1);
+    // barrier set-up by the producer warp: lane w initialises the ring barriers of consumer warp w and starts copying at once;
+    // the consumers only have to see them before their first wait (CTA barrier 0: the producer arrives, the consumers sync)
+    if (warp == NWC) {
+        if (lane == 0) mbar_init(smem_u32(act_bar), 1);
+        if (lane < NWC) {
+            for (int i = 0; i < NS; i++) {
+                mbar_init(smem_u32(full + lane * NS + i), 1);
+                mbar_init(smem_u32(empty + lane * NS + i), 1);
+            }
         }
         fence_mbar_init();
+        __syncwarp();
+        asm volatile("bar.arrive 0, %0;" ::"r"(blockDim.x) : "memory");
+    } else {
+        asm volatile("bar.sync 0, %0;" ::"r"(blockDim.x) : "memory");
     }
-    __syncthreads();
     griddep_launch_dependents();
+    if (p.trace && threadIdx.x == 0) {
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        p.trace[(size_t) blockIdx.x * 8 + 0] = global_ns();
+        (void) smid;
+    }
 
+    const uint64_t pol_stream = l2_policy_evict_first();
+    // one stage of consumer warp w_: row group j_ of the warp's list, 32-unit slice slice_ -> ring stage stage_
+    auto issue = [&](int w_, int stage_, int j_, int slice_) {
+        const int     group = g_begin + w_ + j_ * NWC;
+        const MvMat & mat   = p.mat[mv_find_mat(p, group)];
+        const int     row0  = (group - mat.group0) * p.rpg;
+        const int     nrow  = min(p.rpg, mat.M - row0);
+        const int     u0    = slice_ * 32;
+        const int     nu    = min(32, U - u0);
+        const uint32_t bar  = smem_u32(full + w_ * NS + stage_);
+        const uint32_t dst  = smem_u32(ring0 + ((size_t) w_ * NS + stage_) * STAGE);
+        const uint32_t row_bytes = (uint32_t) nu * UB;
+        mbar_expect_tx(bar, row_bytes * nrow);
+        const uint8_t * src = mat.w + w_off + (int64_t) row0 * mat.nb01 + (int64_t) u0 * UB;
+        if (nrow > 1 && mat.nb01 == (int64_t) U * UB) {
+            bulk_g2s(dst, src, row_bytes * nrow, bar, pol_stream);  // rows are adjacent in memory: one copy
+        } else {
+            for (int r = 0; r < nrow; r++) bulk_g2s(dst + r * row_bytes, src + (int64_t) r * mat.nb01, row_bytes, bar, pol_stream);
+        }
+    };
     if (warp == NWC) {
         // ================================================================ producer warp: lane w feeds consumer warp w
         const int w = lane;
         int my_total = 0;
         if (w < NWC && g_end - g_begin > w) my_total = ((g_end - g_begin - w + NWC - 1) / NWC) * p.slices;
-        const uint64_t pol_stream = l2_policy_evict_first();
-        uint8_t * ring = ring0 + (size_t) w * NS * STAGE;
         int issued = 0, stage = 0, j = 0, slice = 0;
         uint32_t phase = 1;  // parity of the "previous" phase of a fresh barrier: the first NS waits fall through
         while (__any_sync(0xffffffffu, issued < my_total)) {
             bool can = issued < my_total;
             if (can) can = mbar_test_wait(smem_u32(empty + w * NS + stage), phase);
             if (can) {
-                const int     group = g_begin + w + j * NWC;
-                const MvMat & mat   = p.mat[mv_find_mat(p, group)];
-                const int     row0  = (group - mat.group0) * p.rpg;
-                const int     nrow  = min(p.rpg, mat.M - row0);
-                const int     u0    = slice * 32;
-                const int     nu    = min(32, U - u0);
-                const uint32_t bar  = smem_u32(full + w * NS + stage);
-                const uint32_t dst  = smem_u32(ring + (size_t) stage * STAGE);
-                const uint32_t row_bytes = (uint32_t) nu * UB;
-                mbar_expect_tx(bar, row_bytes * nrow);
-                const uint8_t * src = mat.w + w_off + (int64_t) row0 * mat.nb01 + (int64_t) u0 * UB;
-                if (nrow > 1 && mat.nb01 == (int64_t) U * UB) {
-                    bulk_g2s(dst, src, row_bytes * nrow, bar, pol_stream);  // rows are adjacent in memory: one copy
-                } else {
-                    for (int r = 0; r < nrow; r++) bulk_g2s(dst + r * row_bytes, src + (int64_t) r * mat.nb01, row_bytes, bar, pol_stream);
-                }
+                if (p.trace && w == 0 && issued == 0) p.trace[(size_t) blockIdx.x * 8 + 1] = global_ns();
+                issue(w, stage, j, slice);
+                if (p.trace && w == 0 && issued == 0) p.trace[(size_t) blockIdx.x * 8 + 2] = global_ns();
                 issued++;
                 if (++stage == NS) { stage = 0; phase ^= 1; }
                 if (++slice == p.slices) { slice = 0; j++; }
+            }
+        }
+        // every copy of this kernel is in flight: keep HBM busy across the kernel boundary with the head of the predicted
+        // next kernel's weight stream (see MvNext)
+        if (p.next.n_mats > 0) {
+            const MvNext & nx = p.next;
+            for (int b = blockIdx.x; b < nx.n_ctas; b += gridDim.x) {
+                const int nb = (int) ((int64_t) nx.total_groups * b / nx.n_ctas);
+                const int ne = min((int) ((int64_t) nx.total_groups * (b + 1) / nx.n_ctas), nb + nx.groups_per_cta);
+                for (int g = nb + lane; g < ne; g += 32) {
+                    int m = 0;
+#pragma unroll
+                    for (int i = 1; i < MV_MAX_MATS; i++) if (i < nx.n_mats && g >= nx.group0[i]) m = i;
+                    const int row0 = (g - nx.group0[m]) * nx.rpg;
+                    const int nrow = min(nx.rpg, nx.M[m] - row0);
+                    const uint8_t * src = nx.w[m] + (int64_t) row0 * nx.nb01[m];
+                    if (nx.nb01[m] == (int64_t) nx.row_bytes) {
+                        bulk_prefetch_l2(src, (uint32_t) (nrow * nx.row_bytes));
+                    } else {
+                        for (int r = 0; r < nrow; r++) bulk_prefetch_l2(src + (int64_t) r * nx.nb01[m], (uint32_t) nx.row_bytes);
+                    }
+                }
             }
         }
         return;
@@ -356,6 +406,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
 
     griddep_wait();  // everything below reads src1 / writes dst, which earlier kernels of the stream may produce / still read
 
+    if (w == 0) MV_TRACE(3);
     if (p.fuse_quant) {
         // fused K1: unit (c, u) of the activations, F32 global -> unit record in shared memory. Up to 4 units per warp are
         // loaded before the first is quantized, so the L2 round trips overlap instead of chaining
@@ -379,6 +430,10 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
                     }
                 }
             }
+            if (p.trace && w == 0 && t0 == w) {  // the first batch's loads have returned
+                asm volatile("" : "+f"(v[0][0]), "+f"(v[0][7]));
+                MV_TRACE(7);
+            }
 #pragma unroll
             for (int b = 0; b < 4; b++) {
                 const int t = t0 + b * NWC;
@@ -397,6 +452,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
         mbar_wait(smem_u32(act_bar), 0);
     }
 
+    if (w == 0) MV_TRACE(4);
     const uint32_t am0  = smem_u32(act_m), ax0 = smem_u32(act_x);
     const uint32_t cs_m = (uint32_t) U * ACT_MAIN, cs_x = (uint32_t) U * ACT_AUX;
     const uint32_t ring = smem_u32(ring0 + (size_t) w * NS * STAGE);
@@ -413,6 +469,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
     uint32_t phase = 0;
     for (int q = 0; q < my_total; q++) {
         mbar_wait(smem_u32(full + w * NS + stage), phase);
+        if (w == 0 && q == 0) MV_TRACE(5);
         const int group = g_begin + w + j * NWC;
         const int m     = mv_find_mat(p, group);
         const int row0  = (group - p.mat[m].group0) * p.rpg;
@@ -446,6 +503,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
         if (++stage == NS) { stage = 0; phase ^= 1; }
         if (++slice == p.slices) { slice = 0; j++; }
     }
+    if (w == 0) MV_TRACE(6);
     if (p.split.n_ranks > 1) {  // fused all-gather: this CTA's slice is on its way to every rank; the last CTA exchanges flags
         __threadfence_system();
         bar_sync_named(1, NWC * 32);
@@ -453,13 +511,17 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
     }
 }
 
-template <int TYPE, int NC, bool WIDE>
+template <int TYPE, int NC, int WIDE>
 static cudaError_t mv_fast_launch_w(const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
     static bool attr_done[64] = {};  // one attribute call per instantiation and device
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_done[dev]) {
         cudaError_t e = cudaFuncSetAttribute(mv_fast_kernel<TYPE, NC, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        // always the largest shared-memory carve-out: a CTA of the NEXT kernel can only become co-resident if the SM does not
+        // have to be reconfigured between the two launches
+        e = cudaFuncSetAttribute(mv_fast_kernel<TYPE, NC, WIDE>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
@@ -479,10 +541,12 @@ static cudaError_t mv_fast_launch_w(const MvParams & p, int n_ctas, int n_pairs,
 template <int TYPE, int NC>
 static cudaError_t mv_fast_launch_t(const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
     if (p.n_cons > 8) {
-        if constexpr (NC <= MV_WIDE_MAX_COLS) return mv_fast_launch_w<TYPE, NC, true>(p, n_ctas, n_pairs, smem, st);
-        else return cudaErrorInvalidValue;
+        if constexpr (NC <= MV_WIDE_MAX_COLS) {
+            if (p.n_cons <= 11) return mv_fast_launch_w<TYPE, NC, 2>(p, n_ctas, n_pairs, smem, st);
+            return mv_fast_launch_w<TYPE, NC, 1>(p, n_ctas, n_pairs, smem, st);
+        } else return cudaErrorInvalidValue;
     }
-    return mv_fast_launch_w<TYPE, NC, false>(p, n_ctas, n_pairs, smem, st);
+    return mv_fast_launch_w<TYPE, NC, 0>(p, n_ctas, n_pairs, smem, st);
 }
 
 template <int TYPE>

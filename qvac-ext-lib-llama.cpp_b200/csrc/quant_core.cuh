@@ -36,17 +36,15 @@ __device__ __forceinline__ Q80Lane quant_lane_q8_0(const float (&v)[8]) {
     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
     const float d  = __fdiv_rn(amax, 127.0f);
     const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-    int q[8], sum = 0;
+    int q[8];
 #pragma unroll
-    for (int i = 0; i < 8; i++) {
-        q[i] = (int) roundf(__fmul_rn(v[i], id));
-        sum += q[i];
-    }
-    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-    sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+    for (int i = 0; i < 8; i++) q[i] = (int) roundf(__fmul_rn(v[i], id));
     Q80Lane r;
     r.w0  = pack4(q[0], q[1], q[2], q[3]);
     r.w1  = pack4(q[4], q[5], q[6], q[7]);
+    int sum = __dp4a((int) r.w0, 0x01010101, __dp4a((int) r.w1, 0x01010101, 0));  // sum of the 8 signed bytes
+    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+    sum += __shfl_xor_sync(0xffffffffu, sum, 2);
     r.d   = d;
     r.sum = sum;
     return r;
@@ -60,23 +58,24 @@ struct Q8KLane {
     int      s16, s32;
 };
 __device__ __forceinline__ Q8KLane quant_lane_q8_K(const float (&v)[8], int lane) {
-    float amax = 0.0f, vmax = 0.0f;
-    int   idx  = lane * 8;
+    // max |v| of the super-block and the FIRST element that attains it (ggml-quants.c:2564-2569: `if (ax > amax)` keeps the
+    // earliest). |v| >= 0, so the fp32 bit patterns order like unsigned integers and one REDUX gives the warp maximum; a second
+    // one gives the smallest index among the elements equal to it.
+    float amax_l = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 8; i++) {
-        const float a = fabsf(v[i]);
-        if (a > amax) { amax = a; vmax = v[i]; idx = lane * 8 + i; }
-    }
+    for (int i = 0; i < 8; i++) amax_l = fmaxf(amax_l, fabsf(v[i]));
+    const uint32_t amax_b = __reduce_max_sync(0xffffffffu, __float_as_uint(amax_l));
+    uint32_t idx_l = 0xffffffffu;
+    float    cand  = 0.0f;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const float oa = __shfl_xor_sync(0xffffffffu, amax, o);
-        const float ov = __shfl_xor_sync(0xffffffffu, vmax, o);
-        const int   oi = __shfl_xor_sync(0xffffffffu, idx, o);
-        if (oa > amax || (oa == amax && oi < idx)) { amax = oa; vmax = ov; idx = oi; }  // first max wins (ggml-quants.c:2564-2569)
+    for (int i = 7; i >= 0; i--) {
+        if (__float_as_uint(fabsf(v[i])) == amax_b) { idx_l = (uint32_t) (lane * 8 + i); cand = v[i]; }
     }
+    const uint32_t idx  = __reduce_min_sync(0xffffffffu, idx_l);
+    const float    vmax = __shfl_sync(0xffffffffu, cand, (int) (idx >> 3) & 31);
     int   q[8];
     float d = 0.0f;
-    if (amax != 0.0f) {
+    if (amax_b != 0u) {
         const float iscale = __fdiv_rn(-127.f, vmax);
 #pragma unroll
         for (int i = 0; i < 8; i++) q[i] = min(127, nearest_int_rne(__fmul_rn(iscale, v[i])));
@@ -85,14 +84,12 @@ __device__ __forceinline__ Q8KLane quant_lane_q8_K(const float (&v)[8], int lane
 #pragma unroll
         for (int i = 0; i < 8; i++) q[i] = 0;
     }
-    int s8 = 0;
-#pragma unroll
-    for (int i = 0; i < 8; i++) s8 += q[i];
     Q8KLane r;
+    r.w0 = pack4(q[0], q[1], q[2], q[3]);
+    r.w1 = pack4(q[4], q[5], q[6], q[7]);
+    const int s8 = __dp4a((int) r.w0, 0x01010101, __dp4a((int) r.w1, 0x01010101, 0));  // sum of the 8 signed bytes
     r.s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);
     r.s32 = r.s16 + __shfl_xor_sync(0xffffffffu, r.s16, 2);
-    r.w0  = pack4(q[0], q[1], q[2], q[3]);
-    r.w1  = pack4(q[4], q[5], q[6], q[7]);
     r.d   = d;
     return r;
 }

@@ -216,6 +216,32 @@ def test_shared_src1_fusion(ctx, oracle, t):
         assert oracle.nmse(oracle.mul_mat(t, W, X), o.cpu().numpy()) <= NMSE_TIGHT
 
 
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
+def test_decode_weight_prefetch_changes_nothing(pkg, oracle, t):
+    """b200_ctx_set_prefetch: a repeating chain of mat-vecs (what a decode step is) with the next kernel's weights pulled into
+    L2 by the current one. Same bits as without it; a chain that changes under the predictor (wrong predictions) too."""
+    rng = np.random.default_rng(41 + t)
+    shapes = [(96, 4096), (200, 1024), (64, 14336), (33, 512)]
+    Ws = [cu(quantize_weights(oracle, t, rng.uniform(-1, 1, (M, K)).astype(np.float32))) for (M, K) in shapes]
+    Xs = [cu(rng.uniform(-1, 1, (1, K)).astype(np.float32)) for (_, K) in shapes]
+    c = pkg.Context(0)
+    try:
+        base = [c.mul_mat(t, W, X).cpu().numpy() for W, X in zip(Ws, Xs)]
+        c.prefetch(128)
+        for order in ([0, 1, 2, 3], [0, 1, 2, 3], [3, 1, 0, 2], [0, 0, 2, 2], [0, 1, 2, 3]):
+            for i in order:
+                got = c.mul_mat(t, Ws[i], Xs[i]).cpu().numpy()
+                assert np.array_equal(got, base[i])
+        fused = c.mul_mat_shared(t, [Ws[1], Ws[1]], Xs[1])          # a fused launch as predecessor and successor
+        again = c.mul_mat_shared(t, [Ws[1], Ws[1]], Xs[1])
+        assert np.array_equal(fused[0].cpu().numpy(), base[1]) and np.array_equal(again[1].cpu().numpy(), base[1])
+        c.prefetch(0)
+        assert np.array_equal(c.mul_mat(t, Ws[2], Xs[2]).cpu().numpy(), base[2])
+    finally:
+        c.close()
+    assert oracle.nmse(oracle.mul_mat(t, Ws[0].cpu().numpy(), Xs[0].cpu().numpy()), base[0]) <= NMSE_TIGHT
+
+
 # ---------------------------------------------------------------- K5/K6
 
 @pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
