@@ -52,11 +52,17 @@ __device__ __forceinline__ void split_store(const SplitParams & sp, float * addr
     }
 }
 
-// called by ONE warp of every CTA after all of the CTA's stores are done and fenced (__threadfence_system + CTA barrier)
+// called by ONE warp of every CTA after a CTA barrier that follows all of the CTA's stores. One system-scope fence per CTA
+// (not per thread: thousands of concurrent membar.sys were the dominant cost of the exchange): the barrier orders the other
+// threads' peer stores before lane 0's fence, the fence is cumulative, so they are visible system-wide before the counter and,
+// through the last CTA's fence + release store, before the flag.
 __device__ __forceinline__ void split_complete(const SplitParams & sp, unsigned n_ctas) {
     const int lane = threadIdx.x & 31;
     unsigned last = 0;
-    if (lane == 0) last = atomicAdd(&sp.sync_local[9], 1u) == n_ctas - 1 ? 1u : 0u;
+    if (lane == 0) {
+        __threadfence_system();
+        last = atomicAdd(&sp.sync_local[9], 1u) == n_ctas - 1 ? 1u : 0u;
+    }
     last = __shfl_sync(0xffffffffu, last, 0);
     if (!last) return;
     __threadfence_system();

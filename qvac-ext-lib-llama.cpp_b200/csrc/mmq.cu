@@ -7,7 +7,7 @@
 // (/root/reference/ggml/src/ggml-cuda/mmq.cu:70-236, mmq.cuh:3287-3536, 277-336, 637-697, 1840-1947, 796-931, 965-1091,
 // 3006-3053, quantize.cu:50-147). Not a port: the reference keeps 16x8 mma.sync fragments in registers and re-loads
 // tiles synchronously (4 __syncthreads per 256-K step, mmq.cuh:3241-3275); here one thread issues 128xBNx32 MMAs, the
-// copy engine feeds a 4-stage ring, and 8 epilogue warps do nothing but rescale (double-buffered TMEM drain, packed fp32 math).
+// copy engine feeds a 4-stage ring, and 16 epilogue warps do nothing but rescale (double-buffered TMEM drain, packed fp32 math).
 //
 // Arithmetic is the CPU reference's (ggml-cpu vec_dot_q4_0_q8_0 / q8_0_q8_0 / q4_K_q8_K): activations are quantized
 // exactly like quantize_row_q8_0_ref / q8_K_ref, every 32-element block's integer dot product is formed exactly
@@ -22,8 +22,8 @@
 //   activations : int8 [N][K] K-major + float scales [K/32][N]   (quantize_tiles_kernel, bit-exact values)
 // Tiling: CTA tile 128 (M) x 128 (N); K in stages of 128 (4 blocks of 32); TMEM: 4 slots of 128 columns, one slot per
 // 32-block, recycled as soon as the epilogue has pulled it into registers.
-// Warp roles (384 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 4..11 epilogue
-// (warp % 4 = TMEM lane quadrant = 32 weight rows, (warp - 4) / 4 = half of the tile's 128 activation columns).
+// Warp roles (640 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 4..19 epilogue
+// (warp % 4 = TMEM lane quadrant = 32 weight rows, (warp - 4) / 4 = quarter of the tile's 128 activation columns).
 
 #include "internal.h"
 #include "quant_core.cuh"
@@ -42,7 +42,8 @@ namespace {
 
 constexpr int BM = 128, BN = 128, BKB = 4;        // CTA tile; 32-blocks per stage
 constexpr int STAGES = 4, SLOTS = 4;
-constexpr int EPI_WARPS = 8, FIRST_EPI_WARP = 4;   // 2 warps per TMEM lane quadrant, 64 accumulator columns per thread
+constexpr int EPI_WARPS = 16, FIRST_EPI_WARP = 4;  // 4 warps per TMEM lane quadrant, 32 accumulator columns per thread: the
+                                                   // epilogue is latency bound (TMEM round trips, LDS), so warps beat registers
 constexpr int MMQ_THREADS = 32 * (FIRST_EPI_WARP + EPI_WARPS);
 constexpr int A_BYTES = BM * 128, B_BYTES = BN * 128, S_BYTES = BKB * 128 * 4;
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES + 4 * S_BYTES;  // A, B, sW, sA, mW, aS
@@ -118,7 +119,7 @@ __global__ void __launch_bounds__(256) expand_weights_kernel(const uint8_t * __r
 template <int KIND>
 __global__ void __launch_bounds__(128) quantize_tiles_kernel(const float * __restrict__ x, int64_t K, int64_t N, size_t x_rs,
                                                              int8_t * __restrict__ q, float * __restrict__ sA, float * __restrict__ aS,
-                                                             int64_t Np, int vec_ok) {
+                                                             int64_t Np, int vec_ok, int16_t * __restrict__ bs = nullptr) {
     const int     lane  = threadIdx.x & 31;
     const int64_t unit  = (int64_t) blockIdx.x * 4 + (threadIdx.x >> 5);
     const int64_t n     = blockIdx.y;
@@ -153,7 +154,8 @@ __global__ void __launch_bounds__(128) quantize_tiles_kernel(const float * __res
         *(uint2 *) (q + n * K + e0) = make_uint2(r.w0, r.w1);
         if ((lane & 3) == 0) {
             sA[kb * Np + n] = r.d;
-            aS[kb * Np + n] = r.d * (float) r.s32;
+            if (bs) bs[(n * units + unit) * 8 + (lane >> 2)] = (int16_t) r.s32;  // q8_K bsums per 32 (the CPU sums its 16-wide pairs)
+            else aS[kb * Np + n] = r.d * (float) r.s32;
         }
     }
 }
@@ -252,29 +254,24 @@ mmq_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
         }
     } else if (warp >= FIRST_EPI_WARP) {
         // ================================================================ epilogue: TMEM -> registers, scale, accumulate, store
-        // A thread owns one weight row (TMEM lane) and 64 of the tile's 128 columns, drained as chunks of 32 columns.
-        // The tcgen05.ld of chunk i+1 is in flight while chunk i is converted and scaled (I2FP + FMUL2 + FFMA2).
-        const int quad = warp & 3, half = (warp - FIRST_EPI_WARP) >> 2;
+        // A thread owns one weight row (TMEM lane) and 32 of the tile's 128 columns: per 32-block one tcgen05.ld.32x32b.x32, then
+        // I2FP + FMUL2 + FFMA2 on the 32 values.
+        const int quad = warp & 3, part = (warp - FIRST_EPI_WARP) >> 2;
         const int row_in_tile = quad * 32 + lane;
-        const uint32_t t_lane = tmem_base + ((uint32_t) (quad * 32) << 16) + half * 64;
+        const uint32_t t_lane = tmem_base + ((uint32_t) (quad * 32) << 16) + part * 32;
         int stage = 0, slot = 0; uint32_t phase = 0, tphase = 0;
         for (int t = blockIdx.x; t < n_tiles_total; t += gridDim.x) {
             const int m0 = (t / p.n_tiles) * BM, n0 = (t % p.n_tiles) * BN;
-            float2 acc[32];
+            float2 acc[16];
 #pragma unroll
-            for (int j = 0; j < 32; j++) acc[j] = make_float2(0.0f, 0.0f);
-            const int n_chunks = k_stages * BKB * 2;
-            uint32_t ca[32], cb[32];
-            // chunk 0
-            mbar_wait(smem_u32(tfull + slot), tphase);
-            tc_fence_after();
-            tmem_ld_32x32(t_lane + slot * BN, ca);
-            tc_wait_ld_regs(ca);
+            for (int j = 0; j < 16; j++) acc[j] = make_float2(0.0f, 0.0f);
+            const int n_blocks = k_stages * BKB;
+            uint32_t c[32];
 
-            auto math = [&](const uint32_t (&c)[32], int kb, int h, uint32_t st) {
+            auto math = [&](const uint32_t (&c)[32], int kb, uint32_t st) {
                 const float sw = __uint_as_float(lds32(st + 4 * (kb * 128 + row_in_tile)));
                 const float2 sw2 = make_float2(sw, sw);
-                const uint32_t sa = st + S_BYTES + 4 * (kb * 128 + half * 64 + h * 32);
+                const uint32_t sa = st + S_BYTES + 4 * (kb * 128 + part * 32);
                 float2 mw2 = make_float2(0.0f, 0.0f);
                 if (HAS_MIN) {
                     const float mw = -__uint_as_float(lds32(st + 2 * S_BYTES + 4 * (kb * 128 + row_in_tile)));
@@ -285,7 +282,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
                     const uint4 a = lds128(sa + 16 * j4);
                     const float2 p0 = fmul2(make_float2(__uint_as_float(a.x), __uint_as_float(a.y)), sw2);
                     const float2 p1 = fmul2(make_float2(__uint_as_float(a.z), __uint_as_float(a.w)), sw2);
-                    float2 & r0 = acc[h * 16 + 2 * j4], & r1 = acc[h * 16 + 2 * j4 + 1];
+                    float2 & r0 = acc[2 * j4], & r1 = acc[2 * j4 + 1];
                     r0 = ffma2(p0, make_float2((float) (int) c[4 * j4 + 0], (float) (int) c[4 * j4 + 1]), r0);
                     r1 = ffma2(p1, make_float2((float) (int) c[4 * j4 + 2], (float) (int) c[4 * j4 + 3]), r1);
                     if (HAS_MIN) {
@@ -295,29 +292,20 @@ mmq_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
                     }
                 }
             };
-
-            // chunks are processed in pairs (h = 0, 1 of one 32-block) so that the two register buffers alternate statically
-            for (int ck = 0; ck < n_chunks; ck += 2) {
-                const int kb = (ck >> 1) & (BKB - 1);
+            // four warps per scheduler hide the TMEM round trip of one another: a single register buffer per thread is enough
+            for (int blk = 0; blk < n_blocks; blk++) {
+                const int kb = blk & (BKB - 1);
+                mbar_wait(smem_u32(tfull + slot), tphase);
+                tc_fence_after();
+                tmem_ld_32x32(t_lane + slot * BN, c);
                 if (kb == 0) mbar_wait(smem_u32(full + stage), phase);  // the scales of this stage have landed
                 const uint32_t st = smem_u32(smem + stage * STAGE_BYTES + A_BYTES + B_BYTES);
-                // second half of this 32-block in flight while the first is scaled
-                tmem_ld_32x32(t_lane + slot * BN + 32, cb);
-                math(ca, kb, 0, st);
-                tc_wait_ld_regs(cb);
+                tc_wait_ld_regs(c);
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(tempty + slot));  // both halves are in registers: the next MMA may overwrite the slot
+                if (lane == 0) mbar_arrive(smem_u32(tempty + slot));  // the block is in registers: the next MMA may overwrite the slot
                 if (++slot == SLOTS) { slot = 0; tphase ^= 1; }
-                // first half of the next 32-block in flight while the second half of this one is scaled
-                const bool more = ck + 2 < n_chunks;
-                if (more) {
-                    mbar_wait(smem_u32(tfull + slot), tphase);
-                    tc_fence_after();
-                    tmem_ld_32x32(t_lane + slot * BN, ca);
-                }
-                math(cb, kb, 1, st);
-                if (more) tc_wait_ld_regs(ca);
+                math(c, kb, st);
                 if (kb == BKB - 1) {
                     __syncwarp();
                     if (lane == 0) mbar_arrive(smem_u32(empty + stage));  // done with this stage's scales
@@ -327,8 +315,8 @@ mmq_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
             const int m = m0 + row_in_tile;
             if (m < p.M) {
 #pragma unroll
-                for (int j = 0; j < 32; j++) {
-                    const int n = n0 + half * 64 + 2 * j;
+                for (int j = 0; j < 16; j++) {
+                    const int n = n0 + part * 32 + 2 * j;
                     if (n < p.N) split_store(p.split, p.dst + (int64_t) n * p.ldc + m, acc[j].x);
                     if (n + 1 < p.N) split_store(p.split, p.dst + (int64_t) (n + 1) * p.ldc + m, acc[j].y);
                 }
@@ -336,7 +324,259 @@ mmq_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
         }
     }
 
-    if (p.split.n_ranks > 1) __threadfence_system();
+    tc_fence_before();
+    __syncthreads();
+    if (p.split.n_ranks > 1 && warp == 0) split_complete(p.split, gridDim.x);
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem_base);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ q4_K: exact integer scale folding
+//
+// q4_K's sub-block scales are 6-bit integers under one fp16 d per 256-weight super-block, and q8_K activations carry one scale
+// per 256 elements, so the per-32 rescale can move into the integer domain:  sc = 8*a + b  (a, b in 0..7)  gives
+//     sum_j sc_j * sum_{k in j} q_k * y_k  =  8 * sum_k (q_k * a_j(k)) * y_k  +  sum_k (q_k * b_j(k)) * y_k
+// with q*a and q*b <= 105, i.e. two int8 weight planes. Per super-block the tensor core accumulates 8 + 8 UTCIMMAs (K = 256) into
+// two int32 TMEM accumulators and the CUDA cores touch each output once per 256 instead of once per 32 elements:
+//     dst[n][m] = sum_sb  dA[sb][n] * ( d[sb][m] * (8 * Ca + Cb)  -  dmin[sb][m] * sum_kb m_kb[m] * bsum_kb[n] )
+// where the min term is an 8-term integer dot product (dp2a: int16 block sums x 6-bit mins) per output and super-block
+// - the same integers ggml-cpu's vec_dot_q4_K_q8_K forms (ggml-cpu/quants.c:560-640), so parity stays in the 1e-13 class.
+
+// one thread per 32-block: plane a = q * (sc >> 3), plane b = q * (sc & 7) (packed bytes: no carries, products <= 105)
+__global__ void __launch_bounds__(256) expand_q4k_planes_kernel(const uint8_t * __restrict__ w, int64_t nb01, int64_t M, int64_t K,
+                                                                int8_t * __restrict__ qa, int8_t * __restrict__ qb, float * __restrict__ dw,
+                                                                float * __restrict__ dm, uint8_t * __restrict__ mb, int64_t Mp) {
+    const int64_t KB  = K / 32;
+    const int64_t idx = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= M * KB) return;
+    const int64_t row = idx / KB, kb = idx - row * KB;
+    const uint8_t * b = w + row * nb01 + (kb >> 3) * SZ_Q4_K;
+    const int j = (int) (kb & 7);
+    const uint32_t hdr = *(const uint32_t *) b;
+    const float d = half_bits_to_float((uint16_t) (hdr & 0xffff)), dmin = half_bits_to_float((uint16_t) (hdr >> 16));
+    const uint8_t * s = b + 4;
+    int scv, mv;  // get_scale_min_k4 (ggml-quants.c:703-711)
+    if (j < 4) {
+        scv = s[j] & 63;
+        mv  = s[j + 4] & 63;
+    } else {
+        scv = (s[j + 4] & 0xF) | ((s[j - 4] >> 6) << 4);
+        mv  = (s[j + 4] >> 4) | ((s[j] >> 6) << 4);
+    }
+    const uint4 * qs = (const uint4 *) (b + 16 + 32 * (j >> 1));
+    const uint4 v0 = qs[0], v1 = qs[1];
+    const uint32_t x[8] = { v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w };
+    const int sh = (j & 1) ? 4 : 0;
+    const uint32_t fa = (uint32_t) (scv >> 3), fb = (uint32_t) (scv & 7);
+    uint32_t oa[8], ob[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const uint32_t q = (x[i] >> sh) & 0x0f0f0f0fu;
+        oa[i] = q * fa;
+        ob[i] = q * fb;
+    }
+    uint4 * da = (uint4 *) (qa + row * K + kb * 32);
+    uint4 * db = (uint4 *) (qb + row * K + kb * 32);
+    da[0] = make_uint4(oa[0], oa[1], oa[2], oa[3]); da[1] = make_uint4(oa[4], oa[5], oa[6], oa[7]);
+    db[0] = make_uint4(ob[0], ob[1], ob[2], ob[3]); db[1] = make_uint4(ob[4], ob[5], ob[6], ob[7]);
+    if (j == 0) {
+        dw[(kb >> 3) * Mp + row] = d;
+        dm[(kb >> 3) * Mp + row] = dmin;
+    }
+    uint8_t * mrow = mb + (row * (K / 256) + (kb >> 3)) * 16;  // 8 mins (+ 8 bytes of padding: TMA boxes are >= 16 bytes wide)
+    mrow[j]     = (uint8_t) mv;
+    mrow[8 + j] = 0;
+}
+
+constexpr int KQ_OSTAGES = 4, KQ_SSTAGES = 3, KQ_SLOTS = 2;   // operand ring (half super-blocks), scale ring (super-blocks), TMEM slots
+constexpr int KQ_O_BYTES = 3 * BM * 128;                       // plane a, plane b, activations: 128 rows x 128 K-bytes each
+constexpr int KQ_S_BYTES = 3 * 128 * 4 + 2 * 128 * 16;         // dW[128], dmin[128], dA[128], mins[128][16 B], bsums[128][8 x int16]
+constexpr int KQ_SMEM    = 1024 + KQ_OSTAGES * KQ_O_BYTES + KQ_SSTAGES * KQ_S_BYTES + 256;
+
+__global__ void __launch_bounds__(MMQ_THREADS, 1)
+mmq_q4k_kernel(const __grid_constant__ CUtensorMap map_wa, const __grid_constant__ CUtensorMap map_wb, const __grid_constant__ CUtensorMap map_b,
+               const __grid_constant__ CUtensorMap map_mb, const __grid_constant__ CUtensorMap map_bs, const __grid_constant__ CUtensorMap map_dw,
+               const __grid_constant__ CUtensorMap map_dm, const __grid_constant__ CUtensorMap map_da, const MmqParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *  smem   = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
+    uint8_t *  sring  = smem + KQ_OSTAGES * KQ_O_BYTES;
+    uint64_t * bars   = (uint64_t *) (sring + KQ_SSTAGES * KQ_S_BYTES);
+    uint64_t * ofull  = bars;                      // [OSTAGES] TMA -> MMA
+    uint64_t * oempty = ofull + KQ_OSTAGES;        // [OSTAGES] MMA commit -> TMA
+    uint64_t * sfull  = oempty + KQ_OSTAGES;       // [SSTAGES] TMA -> epilogue
+    uint64_t * sempty = sfull + KQ_SSTAGES;        // [SSTAGES] epilogue warps -> TMA
+    uint64_t * tfull  = sempty + KQ_SSTAGES;       // [SLOTS]   MMA commit -> epilogue
+    uint64_t * tempty = tfull + KQ_SLOTS;          // [SLOTS]   epilogue warps -> MMA
+    uint32_t * tmem_slot = (uint32_t *) (tempty + KQ_SLOTS);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_tiles_total = p.m_tiles * p.n_tiles;
+    const int n_sb = p.K / 256;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < KQ_OSTAGES; i++) { mbar_init(smem_u32(ofull + i), 1); mbar_init(smem_u32(oempty + i), 1); }
+        for (int i = 0; i < KQ_SSTAGES; i++) { mbar_init(smem_u32(sfull + i), 1); mbar_init(smem_u32(sempty + i), EPI_WARPS); }
+        for (int i = 0; i < KQ_SLOTS; i++) { mbar_init(smem_u32(tfull + i), 1); mbar_init(smem_u32(tempty + i), EPI_WARPS); }
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc<512>(smem_u32(tmem_slot));
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================================================================ TMA producer
+        if (lane == 0) {
+            tma_prefetch_desc(&map_wa); tma_prefetch_desc(&map_wb); tma_prefetch_desc(&map_b);
+            int os = 0, ss = 0; uint32_t ophase = 1, sphase = 1;
+            for (int t = blockIdx.x; t < n_tiles_total; t += gridDim.x) {
+                const int m0 = (t / p.n_tiles) * BM, n0 = (t % p.n_tiles) * BN;
+                for (int sb = 0; sb < n_sb; sb++) {
+                    mbar_wait(smem_u32(sempty + ss), sphase);
+                    {
+                        const uint32_t bar = smem_u32(sfull + ss);
+                        const uint32_t st  = smem_u32(sring + ss * KQ_S_BYTES);
+                        mbar_expect_tx(bar, KQ_S_BYTES);
+                        tma_load_2d(st, &map_dw, m0, sb, bar);
+                        tma_load_2d(st + 512, &map_dm, m0, sb, bar);
+                        tma_load_2d(st + 1024, &map_da, n0, sb, bar);
+                        tma_load_2d(st + 1536, &map_mb, sb * 16, m0, bar);
+                        tma_load_2d(st + 1536 + 2048, &map_bs, sb * 8, n0, bar);
+                    }
+                    if (++ss == KQ_SSTAGES) { ss = 0; sphase ^= 1; }
+                    for (int h = 0; h < 2; h++) {
+                        mbar_wait(smem_u32(oempty + os), ophase);
+                        const uint32_t bar = smem_u32(ofull + os);
+                        const uint32_t st  = smem_u32(smem + os * KQ_O_BYTES);
+                        mbar_expect_tx(bar, KQ_O_BYTES);
+                        tma_load_2d(st, &map_wa, sb * 256 + h * 128, m0, bar);
+                        tma_load_2d(st + BM * 128, &map_wb, sb * 256 + h * 128, m0, bar);
+                        tma_load_2d(st + 2 * BM * 128, &map_b, sb * 256 + h * 128, n0, bar);
+                        if (++os == KQ_OSTAGES) { os = 0; ophase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================================================================ MMA issuer: 8 + 8 UTCIMMAs (128 x 128 x 32) per super-block
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_i8(BM, BN);
+            int os = 0, slot = 0; uint32_t ophase = 0, tphase = 1;
+            for (int t = blockIdx.x; t < n_tiles_total; t += gridDim.x) {
+                for (int sb = 0; sb < n_sb; sb++) {
+                    mbar_wait(smem_u32(tempty + slot), tphase);
+                    tc_fence_after();
+                    const uint32_t d_a = tmem_base + slot * 2 * BN, d_b = d_a + BN;
+                    for (int h = 0; h < 2; h++) {
+                        mbar_wait(smem_u32(ofull + os), ophase);
+                        tc_fence_after();
+                        const uint32_t a0 = smem_u32(smem + os * KQ_O_BYTES), a1 = a0 + BM * 128, b0 = a1 + BM * 128;
+#pragma unroll
+                        for (int kb = 0; kb < 4; kb++) {
+                            const uint32_t accumulate = (h | kb) != 0;
+                            const uint64_t db = umma_desc_sw128(b0 + kb * 32);
+                            umma_i8(d_a, umma_desc_sw128(a0 + kb * 32), db, idesc, accumulate);
+                            umma_i8(d_b, umma_desc_sw128(a1 + kb * 32), db, idesc, accumulate);
+                        }
+                        umma_commit(smem_u32(oempty + os));  // the operands of this stage have been read
+                        if (++os == KQ_OSTAGES) { os = 0; ophase ^= 1; }
+                    }
+                    umma_commit(smem_u32(tfull + slot));
+                    if (++slot == KQ_SLOTS) { slot = 0; tphase ^= 1; }
+                }
+            }
+        }
+    } else if (warp >= FIRST_EPI_WARP) {
+        // ================================================================ epilogue: one pass per super-block
+        const int quad = warp & 3, part = (warp - FIRST_EPI_WARP) >> 2;
+        const int row_in_tile = quad * 32 + lane;
+        const uint32_t t_lane = tmem_base + ((uint32_t) (quad * 32) << 16) + part * 32;
+        int ss = 0, slot = 0; uint32_t sphase = 0, tphase = 0;
+        for (int t = blockIdx.x; t < n_tiles_total; t += gridDim.x) {
+            const int m0 = (t / p.n_tiles) * BM, n0 = (t % p.n_tiles) * BN;
+            float2 acc[16];
+#pragma unroll
+            for (int j = 0; j < 16; j++) acc[j] = make_float2(0.0f, 0.0f);
+            for (int sb = 0; sb < n_sb; sb++) {
+                mbar_wait(smem_u32(tfull + slot), tphase);
+                tc_fence_after();
+                uint32_t ca[16], cb[16];
+                const uint32_t t_a = t_lane + slot * 2 * BN, t_b = t_a + BN;
+                tmem_ld_32x16(t_a, ca);
+                tmem_ld_32x16(t_b, cb);
+                mbar_wait(smem_u32(sfull + ss), sphase);  // the scales of this super-block have landed
+                const uint32_t st = smem_u32(sring + ss * KQ_S_BYTES);
+                const float dw = __uint_as_float(lds32(st + 4 * row_in_tile));
+                const float2 dw2 = make_float2(dw, dw);
+                const uint32_t da = st + 1024 + 4 * (part * 32);
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    tc_wait_ld_regs2(ca, cb);
+                    float2 v[8];
+#pragma unroll
+                    for (int j = 0; j < 8; j++)
+                        v[j] = make_float2((float) (int) ((ca[2 * j] << 3) + cb[2 * j]), (float) (int) ((ca[2 * j + 1] << 3) + cb[2 * j + 1]));
+                    if (h == 0) {  // second half of the columns in flight while the first is scaled
+                        tmem_ld_32x16(t_a + 16, ca);
+                        tmem_ld_32x16(t_b + 16, cb);
+                    } else {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(smem_u32(tempty + slot));  // both accumulators are in registers
+                    }
+#pragma unroll
+                    for (int j4 = 0; j4 < 4; j4++) {
+                        const uint4 a = lds128(da + 64 * h + 16 * j4);
+                        const float2 s0 = fmul2(make_float2(__uint_as_float(a.x), __uint_as_float(a.y)), dw2);
+                        const float2 s1 = fmul2(make_float2(__uint_as_float(a.z), __uint_as_float(a.w)), dw2);
+                        acc[8 * h + 2 * j4]     = ffma2(s0, v[2 * j4], acc[8 * h + 2 * j4]);
+                        acc[8 * h + 2 * j4 + 1] = ffma2(s1, v[2 * j4 + 1], acc[8 * h + 2 * j4 + 1]);
+                    }
+                }
+                if (++slot == KQ_SLOTS) { slot = 0; tphase ^= 1; }
+                // mins: acc -= dmin[row] * dA[col] * sum_kb m_kb[row] * bsum_kb[col]   (integer dot, ggml-cpu/quants.c:618-626)
+                {
+                    const float dm = -__uint_as_float(lds32(st + 512 + 4 * row_in_tile));
+                    const float2 dm2 = make_float2(dm, dm);
+                    const uint2 mm = lds64(st + 1536 + 16 * row_in_tile);
+                    const uint32_t bs = st + 1536 + 2048 + 16 * (part * 32);
+#pragma unroll
+                    for (int j4 = 0; j4 < 8; j4++) {
+                        const uint4 a = lds128(da + 16 * j4);
+                        int iv[4];
+#pragma unroll
+                        for (int c = 0; c < 4; c++) {
+                            const uint4 b = lds128(bs + 16 * (4 * j4 + c));
+                            int i = dp2a_lo_su((int) b.x, mm.x, 0);
+                            i     = dp2a_hi_su((int) b.y, mm.x, i);
+                            i     = dp2a_lo_su((int) b.z, mm.y, i);
+                            iv[c] = dp2a_hi_su((int) b.w, mm.y, i);
+                        }
+                        const float2 s0 = fmul2(make_float2(__uint_as_float(a.x), __uint_as_float(a.y)), dm2);
+                        const float2 s1 = fmul2(make_float2(__uint_as_float(a.z), __uint_as_float(a.w)), dm2);
+                        acc[2 * j4]     = ffma2(s0, make_float2((float) iv[0], (float) iv[1]), acc[2 * j4]);
+                        acc[2 * j4 + 1] = ffma2(s1, make_float2((float) iv[2], (float) iv[3]), acc[2 * j4 + 1]);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(sempty + ss));  // done with this super-block's scales
+                if (++ss == KQ_SSTAGES) { ss = 0; sphase ^= 1; }
+            }
+            const int m = m0 + row_in_tile;
+            if (m < p.M) {
+#pragma unroll
+                for (int j = 0; j < 16; j++) {
+                    const int n = n0 + part * 32 + 2 * j;
+                    if (n < p.N) split_store(p.split, p.dst + (int64_t) n * p.ldc + m, acc[j].x);
+                    if (n + 1 < p.N) split_store(p.split, p.dst + (int64_t) (n + 1) * p.ldc + m, acc[j].y);
+                }
+            }
+        }
+    }
+
     tc_fence_before();
     __syncthreads();
     if (p.split.n_ranks > 1 && warp == 0) split_complete(p.split, gridDim.x);
@@ -387,6 +627,9 @@ struct WEntry {  // expanded form of one weight matrix
     uint8_t * buf = nullptr;  // [q: M*K int8][sc: KB*Mp float][mn: KB*Mp float]
     size_t    bytes = 0;
     CUtensorMap map_q, map_sc, map_mn;
+    bool        planes = false;   // q4_K scale-folded form: [qa][qb][d: SB*Mp float][dmin: SB*Mp float][mins: M*SB*16 bytes];
+                                  // map_sc = dmin, map_mn = mins
+    CUtensorMap map_qb, map_dw;
 };
 
 struct WKey {
@@ -399,9 +642,19 @@ std::mutex                 g_wmutex;
 std::map<WKey, WEntry *>   g_wcache;
 size_t                     g_wbytes = 0;
 
+bool q4k_planes_enabled() {
+    static const bool on = [] { const char * s = getenv("GGML_B200_MMQ_Q4K_PLANES"); return !(s && atoi(s) == 0); }();
+    return on;
+}
+
 size_t wentry_bytes(int type, int64_t M, int64_t K, int64_t Mp) {
     const size_t qb = ((size_t) M * K + 255) & ~(size_t) 255;
     const size_t sb = (((size_t) (K / 32) * Mp * 4) + 255) & ~(size_t) 255;
+    if (type == B200_TYPE_Q4_K && K % 256 == 0 && q4k_planes_enabled()) {
+        const size_t db = (((size_t) (K / 256) * Mp * 4) + 255) & ~(size_t) 255;
+        const size_t mb = (((size_t) M * (K / 256) * 16) + 255) & ~(size_t) 255;
+        return 2 * qb + 2 * db + mb;
+    }
     return qb + sb * (type == B200_TYPE_Q4_K ? 2 : 1);
 }
 
@@ -415,6 +668,25 @@ b200_status wentry_fill(b200_ctx * ctx, WEntry * e, const void * src, uint8_t * 
     e->buf = buf;
     const int64_t total = M * KB;
     const unsigned grid = (unsigned) ((total + 255) / 256);
+    if (e->type == B200_TYPE_Q4_K && K % 256 == 0 && q4k_planes_enabled()) {
+        const size_t db = (((size_t) (K / 256) * e->Mp * 4) + 255) & ~(size_t) 255;
+        int8_t * qa = (int8_t *) buf, * qbp = (int8_t *) (buf + qb);
+        float *   dw = (float *) (buf + 2 * qb);
+        float *   dm = (float *) (buf + 2 * qb + db);
+        uint8_t * mb = buf + 2 * qb + 2 * db;
+        expand_q4k_planes_kernel<<<grid, 256, 0, ctx->stream>>>((const uint8_t *) src, (int64_t) e->nb01, M, K, qa, qbp, dw, dm, mb, e->Mp);
+        CU(cudaGetLastError());
+        ctx->launches++;
+        e->planes = true;
+        if (!make_map(&e->map_q, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, qa, (uint64_t) K, (uint64_t) M, (uint64_t) K, 128, BM, true) ||
+            !make_map(&e->map_qb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, qbp, (uint64_t) K, (uint64_t) M, (uint64_t) K, 128, BM, true) ||
+            !make_map(&e->map_dw, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dw, (uint64_t) M, (uint64_t) (K / 256), (uint64_t) e->Mp * 4, 128, 1, false) ||
+            !make_map(&e->map_sc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dm, (uint64_t) M, (uint64_t) (K / 256), (uint64_t) e->Mp * 4, 128, 1, false) ||
+            !make_map(&e->map_mn, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, mb, (uint64_t) (K / 256) * 16, (uint64_t) M, (uint64_t) (K / 256) * 16, 16, BM, false)) {
+            return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the q4_K planes (M=%lld K=%lld)", (long long) M, (long long) K);
+        }
+        return B200_OK;
+    }
     switch (e->type) {
         case B200_TYPE_Q4_0: expand_weights_kernel<B200_TYPE_Q4_0><<<grid, 256, 0, ctx->stream>>>((const uint8_t *) src, (int64_t) e->nb01, M, K, q, sc, mn, e->Mp); break;
         case B200_TYPE_Q8_0: expand_weights_kernel<B200_TYPE_Q8_0><<<grid, 256, 0, ctx->stream>>>((const uint8_t *) src, (int64_t) e->nb01, M, K, q, sc, mn, e->Mp); break;
@@ -535,6 +807,7 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
     int8_t * xq = (int8_t *) s2;
     float *  sA = (float *) (s2 + aq);
     float *  aS = has_min ? (float *) (s2 + aq + as) : sA;
+    int16_t * bsums = (int16_t *) aS;  // q4_K planes: int16 block sums [N][K/256][8] instead of the float products (N*K/16 <= as bytes)
     {
         const int64_t units  = (K + 255) / 256;
         const int     vec_ok = ((uintptr_t) x % 16 == 0) && (x_rs % 16 == 0);
@@ -542,7 +815,8 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
             const int64_t nr = N - r0 < 65535 ? N - r0 : 65535;
             dim3 grid((unsigned) ((units + 3) / 4), (unsigned) nr);
             const float * xs = (const float *) ((const char *) x + r0 * x_rs);
-            if (has_min) quantize_tiles_kernel<ACT_KIND_Q8_K><<<grid, 128, 0, ctx->stream>>>(xs, K, nr, x_rs, xq + r0 * K, sA + r0, aS + r0, Np, vec_ok);
+            if (has_min) quantize_tiles_kernel<ACT_KIND_Q8_K><<<grid, 128, 0, ctx->stream>>>(xs, K, nr, x_rs, xq + r0 * K, sA + r0, aS + r0, Np, vec_ok,
+                                                                                               e->planes ? bsums + r0 * (K / 256) * 8 : nullptr);
             else         quantize_tiles_kernel<ACT_KIND_Q8_0><<<grid, 128, 0, ctx->stream>>>(xs, K, nr, x_rs, xq + r0 * K, sA + r0, aS + r0, Np, vec_ok);
             ctx->launches++;
         }
@@ -562,6 +836,22 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
     p.n_tiles = (int) ((N + BN - 1) / BN);
     const int tiles = p.m_tiles * p.n_tiles;
     const int grid  = tiles < ctx->sm_count ? tiles : ctx->sm_count;
+    if (e->planes) {  // q4_K with the sub-block scales folded into two int8 planes
+        CUtensorMap map_bs, map_da;
+        if (!make_map(&map_bs, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, bsums, (uint64_t) (K / 256) * 8, (uint64_t) N, (uint64_t) (K / 256) * 16, 8, BN, false) ||
+            !make_map(&map_da, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, sA, (uint64_t) N, (uint64_t) (K / 256), (uint64_t) Np * 4 * 8, 128, 1, false)) {
+            return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the q8_K scale tiles (N=%lld K=%lld)", (long long) N, (long long) K);
+        }
+        static bool kattr_done[64] = {};
+        if (ctx->device < 64 && !kattr_done[ctx->device]) {
+            CU(cudaFuncSetAttribute(mmq_q4k_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KQ_SMEM));
+            kattr_done[ctx->device] = true;
+        }
+        mmq_q4k_kernel<<<grid, MMQ_THREADS, KQ_SMEM, ctx->stream>>>(e->map_q, e->map_qb, map_b, e->map_mn, map_bs, e->map_dw, e->map_sc, map_da, p);
+        CU(cudaGetLastError());
+        ctx->launches++;
+        return B200_OK;
+    }
     static bool attr_done[2][64] = {};
     if (ctx->device < 64 && !attr_done[has_min][ctx->device]) {
         if (has_min) CU(cudaFuncSetAttribute(mmq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MMQ_SMEM));

@@ -505,7 +505,6 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
     }
     if (w == 0) MV_TRACE(6);
     if (p.split.n_ranks > 1) {  // fused all-gather: this CTA's slice is on its way to every rank; the last CTA exchanges flags
-        __threadfence_system();
         bar_sync_named(1, NWC * 32);
         if (w == 0) split_complete(p.split, gridDim.x * gridDim.y);
     }
