@@ -1,0 +1,174 @@
+"""Row-split tensor parallelism: the host-side partition rule on CPU, the slice/gather layout with two gloo ranks,
+and - on a GPU - the fused exchange epilogue of the kernels with a second destination on the same device."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from oracle.pyoracle import Q4_0, Q4_K, Q8_0
+
+
+# ---------------------------------------------------------------- the partition rule (reference: get_row_split, ggml-cuda.cu:786-799)
+
+def ref_row_split(nrows, tensor_split, dev, n_dev, rounding):
+    """literal restatement of the reference function for the checker"""
+    lo = 0 if dev == 0 else int(nrows * tensor_split[dev])
+    lo -= lo % rounding
+    if dev == n_dev - 1:
+        hi = nrows
+    else:
+        hi = int(nrows * tensor_split[dev + 1])
+        hi -= hi % rounding
+    return lo, hi
+
+
+@pytest.mark.parametrize("nrows", [1, 64, 127, 128, 1000, 4096, 14336, 128256])
+@pytest.mark.parametrize("n", [1, 2, 4, 8])
+def test_bounds_cover_disjoint_ordered(pkg, nrows, n):
+    prev = 0
+    for r in range(n):
+        lo, hi = pkg.row_split_bounds(nrows, n, r)
+        assert lo == prev and hi >= lo
+        if r < n - 1:
+            assert hi % pkg.ROW_SPLIT_ROUNDING == 0
+        prev = hi
+    assert prev == nrows
+
+
+def test_bounds_follow_the_reference_rule(pkg):
+    rng = np.random.default_rng(5)
+    for _ in range(200):
+        n = int(rng.integers(1, 9))
+        w = rng.uniform(0.0, 1.0, n)
+        if w.sum() == 0:
+            continue
+        cum = np.concatenate([[0.0], np.cumsum(w / w.sum())[:-1]]).tolist()   # llama.cpp's normalised cumulative form
+        nrows = int(rng.integers(1, 200000))
+        rounding = int(rng.choice([1, 32, 64, 128]))
+        for r in range(n):
+            assert pkg.row_split_bounds(nrows, n, r, cum, rounding) == ref_row_split(nrows, cum, r, n, rounding)
+
+
+def test_bounds_reject_bad_splits(pkg):
+    with pytest.raises(ValueError):
+        pkg.row_split_bounds(100, 2, 0, [0.1, 0.5])
+    with pytest.raises(ValueError):
+        pkg.row_split_bounds(100, 3, 0, [0.0, 0.7, 0.5])
+
+
+# ---------------------------------------------------------------- two ranks over gloo: slices + all-gather == the whole product
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _gloo_worker(rank, world, port, t, M, K, N, split, q):
+    import sys
+    from pathlib import Path
+    sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+    import torch
+    import torch.distributed as dist
+    import b200_pkg
+    from oracle.pyoracle import Oracle
+    pkg = b200_pkg.load()
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        oracle = Oracle()
+        rng = np.random.default_rng(11)                      # same seed on every rank: replicated weights / activations
+        Wf = rng.uniform(-1, 1, (M, K)).astype(np.float32)
+        X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+        W = oracle.quantize("q4_0" if t == Q4_0 else "q8_0", Wf)
+        lo, hi = pkg.row_split_bounds(M, world, rank, split, 32)
+        mine = oracle.mul_mat(t, np.ascontiguousarray(W[lo:hi]), X) if hi > lo else np.zeros((N, 0), np.float32)   # this rank's dst rows
+        # the layout the fused all-gather produces: every rank's slice at columns [lo, hi) of a full [N, M] dst
+        sizes = [pkg.row_split_bounds(M, world, r, split, 32) for r in range(world)]
+        parts = [torch.zeros((N, h - l), dtype=torch.float32) for (l, h) in sizes]
+        # gloo's all_gather wants equal shapes: pad to the widest slice
+        wmax = max(h - l for (l, h) in sizes)
+        padded = torch.zeros((N, wmax), dtype=torch.float32)
+        padded[:, :hi - lo] = torch.from_numpy(np.ascontiguousarray(mine))
+        gathered = [torch.zeros((N, wmax), dtype=torch.float32) for _ in range(world)]
+        dist.all_gather(gathered, padded)
+        for r, (l, h) in enumerate(sizes):
+            parts[r] = gathered[r][:, :h - l]
+        full = torch.cat(parts, dim=1).numpy()
+        whole = oracle.mul_mat(t, W, X)
+        q.put((rank, bool(np.array_equal(full, whole)), (lo, hi)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("split", [None, [0.0, 0.75], [0.0, 0.0]])
+def test_two_rank_slices_gather_to_the_whole_product(split):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    M, K, N = 200, 256, 3
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, Q8_0, M, K, N, split, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for (_, ok, _) in res), res
+    bounds = dict((r, b) for (r, _, b) in res)
+    assert bounds[0][1] == bounds[1][0] and bounds[0][0] == 0 and bounds[1][1] == M
+
+
+# ---------------------------------------------------------------- GPU: the fused exchange epilogue
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("t,N", [(Q4_K, 1), (Q4_0, 2), (Q8_0, 1), (Q4_K, 40), (Q8_0, 64)])
+def test_fused_exchange_writes_every_destination(pkg, oracle, t, N):
+    """rank 0 of a 2-rank split whose 'peer' dst is a second buffer on the same GPU and whose peer flag is already at the far
+    epoch (nothing spins): the kernel must store every value into both destinations, bump its epoch, reset its CTA counter and
+    publish the epoch into the peer's flag slot. Mat-vec (N <= 8) and tensor-core (N > 8) kernels."""
+    import torch
+    from oracle.pyoracle import RefQuant, have_ref
+
+    def cu(a):
+        return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+    def quantize_weights(oracle, t, w):
+        if have_ref():
+            return RefQuant().quantize_weights(t, w)
+        if t == Q4_K:
+            pytest.skip("q4_K weights need oracle/_ref")
+        return oracle.quantize("q4_0" if t == Q4_0 else "q8_0", w)
+
+    NMSE_TIGHT = 1e-10
+    rng = np.random.default_rng(23 + t + N)
+    M, K = 384, 1024
+    W = quantize_weights(oracle, t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    c = pkg.Context(0)
+    try:
+        ref = c.mul_mat(t, cu(W), cu(X)).cpu().numpy()
+        pool = torch.zeros(2 * N * M + 64, dtype=torch.float32, device="cuda")      # [dst of rank 0][dst of the 'peer'][sync words x2]
+        sync = pool[2 * N * M:].view(torch.int32)
+        sync[1] = 0x7FFFFFF0                                                     # rank 1's flag in rank 0's words: already there
+        torch.cuda.synchronize()
+        base = pool.data_ptr()
+        peer = base + 4 * N * M
+        s0, s1 = base + 8 * N * M, base + 8 * N * M + 128
+        c.row_split(0, [base, peer], [s0, s1])
+        out = pool[:N * M].view(N, M)
+        for rep in range(3):
+            c.mul_mat(t, cu(W), cu(X), out=out)
+            torch.cuda.synchronize()
+            assert np.array_equal(out.cpu().numpy(), ref)
+            assert np.array_equal(pool[N * M:2 * N * M].view(N, M).cpu().numpy(), ref)
+            words = pool[2 * N * M:].view(torch.int32).cpu().numpy()
+            assert words[8] == rep + 1 and words[9] == 0          # epoch, CTA counter
+            assert words[32 + 0] == rep + 1                        # published into the peer's slot for rank 0
+        c.row_split(0, [base], [s0])                               # one rank: off
+        assert np.array_equal(c.mul_mat(t, cu(W), cu(X)).cpu().numpy(), ref)
+    finally:
+        c.close()
+    assert oracle.nmse(oracle.mul_mat(t, W, X), ref) <= NMSE_TIGHT
