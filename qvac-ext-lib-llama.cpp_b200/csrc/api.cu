@@ -116,6 +116,8 @@ b200_status b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     if (const char * s = getenv("GGML_B200_FUSE_QUANT")) c->fuse_quant = atoi(s) != 0;
     if (const char * s = getenv("GGML_B200_PREFETCH_KB")) c->prefetch_kb = atoi(s);
     if (const char * s = getenv("GGML_B200_DBG")) c->dbg = atoi(s);
+    if (const char * s = getenv("GGML_B200_MMA_MIN")) c->mma_min_cols = atoi(s);
+    if (const char * s = getenv("GGML_B200_MMA_WARPS")) c->mma_warps = atoi(s);
     *out = c;
     return B200_OK;
 }
@@ -407,6 +409,15 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
     const int U = (int) (K / 256);
     for (int c0 = 0; c0 < ncols;) {
         int     nc = ncols - c0 < MV_MAX_COLS ? ncols - c0 : MV_MAX_COLS;
+        if (!x && ctx->mma_min_cols > 0 && nc >= ctx->mma_min_cols && mv_mma_usable(type)) {  // 3..8 columns: tensor-core mat-vec (mvmma.cu)
+            float * ds[MV_MAX_MATS * 8];
+            for (int i = 0; i < n_ops; i++) ds[i] = dsts[i] + (int64_t) c0 * dst_cs[i];
+            b200_status st = b200_mv_mma_run(ctx, type, K, n_ops, ws, nb01s, Ms, ds, dst_cs, nc, act_main + (size_t) c0 * U * ACT_MAIN,
+                                             act_aux + (size_t) c0 * U * ACT_AUX);
+            if (st != B200_OK) return st;
+            c0 += nc;
+            continue;
+        }
         mv_cfg  cfg;
         while (nc >= 1 && !pick_mv_cfg(ctx, type, U, nc, &cfg)) nc--;
         if (nc < 1) return fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
@@ -513,7 +524,8 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
 
     if (fast) {
         const int  U    = (int) (K / 256);
-        const bool fuse = mv_fuse_quant(ctx, U, N);
+        const bool mma  = ctx->mma_min_cols > 0 && N >= ctx->mma_min_cols && mv_mma_usable(type);  // the IMMA kernel reads pre-quantized columns
+        const bool fuse = !mma && mv_fuse_quant(ctx, U, N);
         uint8_t * am = nullptr, * ax = nullptr;
         if (!fuse) {
             const size_t main_b = (size_t) n_rows * U * ACT_MAIN, aux_b = (size_t) n_rows * U * ACT_AUX;

@@ -54,6 +54,8 @@ struct b200_ctx {
     unsigned long long * trace = nullptr;
     int          trace_slots = 0;
     int          dbg = 0;                      // GGML_B200_DBG: experiment switches handed to the kernels
+    int          mma_min_cols = 3;             // columns from which the IMMA mat-vec kernel (mvmma.cu) replaces the dp4a one; GGML_B200_MMA_MIN
+    int          mma_warps = 0;                // 0 = auto (8); GGML_B200_MMA_WARPS
 };
 
 // bumped whenever device memory the library may hold predictions / caches for is freed or rewritten
@@ -62,6 +64,11 @@ void     b200_mem_generation_bump();
 
 // grow-only device buffer owned by the context (fails instead of reallocating while the stream is being captured)
 b200_status b200_ensure(b200_ctx * ctx, void ** buf, size_t * cur, size_t need);
+
+// mvmma.cu: the IMMA mat-vec kernel for 3..8 columns (q4_0, q4_K)
+namespace b200 { bool mv_mma_usable(int type); }
+b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, const uint8_t * const * ws, const size_t * nb01s, const int64_t * Ms,
+                            float * const * dsts, const int64_t * dst_cs, int ncols, const uint8_t * act_main, const uint8_t * act_aux);
 
 // mmq.cu: the tcgen05 int8 tile kernel
 bool        b200_mmq_usable(int type, int64_t K, const void * w, size_t nb01);

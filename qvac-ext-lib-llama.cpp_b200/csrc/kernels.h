@@ -17,7 +17,7 @@ cudaError_t quantize_units(int kind, const float * x, int64_t k, int64_t nrows, 
 constexpr int MV_MAX_MATS = 4;
 constexpr int MV_MAX_COLS = 8;
 constexpr int MV_MAX_CONS = 16;  // consumer warps per CTA (+ 1 producer warp); more than 8 only up to MV_WIDE_MAX_COLS columns
-constexpr int MV_WIDE_MAX_COLS = 2;
+constexpr int MV_WIDE_MAX_COLS = 4;
 
 // expert routing for MUL_MAT_ID (ggml-cpu.c:1564-1578): pair (i, t) uses expert ids[t*ids_rs + i], activation row
 // t*ne11 + i % ne11 of the quantized activations, and writes dst + t*dst_ts + i*dst_is (floats)

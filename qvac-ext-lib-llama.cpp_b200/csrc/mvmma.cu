@@ -1,0 +1,391 @@
+// mvmma.cu — K3b: batched decode (3..8 activation columns) on the warp-level int8 tensor-core path.
+//
+// The dp4a mat-vec kernel (mmvq.cu) spends ~100 instructions per 256 weights and column: beyond 2 columns it is instruction
+// bound (n = 4: 2.1 TB/s, n = 8: 1.2 TB/s). Here one mma.sync.m16n8k32 (SASS IMMA.16832) forms 16 weight rows x 8 columns x 32
+// weights at once, A fragments unpacked from the 4-bit stream in registers (one 32-bit shared load holds the nibbles of both
+// k-halves a lane needs), so the instruction count per weight byte is independent of the column count and the kernel stays HBM
+// bound. Replaces mul_mat_vec_q for ncols_dst 3..8 (/root/reference/ggml/src/ggml-cuda/mmvq.cu:141-335) and is the building block
+// for small MUL_MAT_ID batches.
+//
+// Geometry: a CTA owns a contiguous range of 16-row tiles. A tile's K range is streamed in chunks of NWC units (a unit = 256
+// weights = 144 B of q4_0 / q4_K); one 3-D TMA box [units][16 rows][144 B] per chunk lands so that consumer warp w finds "its"
+// unit as a dense [16][144 B] sub-tile (36-word row pitch: the 8 rows x 4 words a fragment load touches hit 32 distinct banks).
+// Warp w multiplies unit w of every chunk for all 16 rows; the NWC partial 16x8 results of a tile are summed in a fixed order
+// through shared memory (bit-reproducible run to run). One producer warp issues the TMA loads through a ring of stages.
+// Integer arithmetic is the CPU reference's: per 32-block integer dot products, 6-bit scales / block scales applied exactly as
+// vec_dot_q4_K_q8_K / vec_dot_q4_0_q8_0 do (ggml-cpu/quants.c), activations quantized bit-exactly by quantize.cu.
+
+#include "internal.h"
+#include "tc.cuh"
+
+#include <cuda.h>
+
+using namespace b200;
+
+namespace b200 {
+
+struct MmaMvParams {
+    MvMat           mat[MV_MAX_MATS];   // group0 = first global tile id of the matrix
+    int             n_mats, total_tiles;
+    int             U, ncols, n_cons, n_stages, pdl;
+    const uint8_t * act_main;           // [ncols][U][272]
+    const uint8_t * act_aux;            // [ncols][U][16]
+    SplitParams     split;
+};
+
+namespace {
+
+constexpr int MMA_ROWS = 16;
+constexpr int MMA_RT   = 2;   // 16-row tiles a warp accumulates before the CTA-wide reduction (one barrier per 64 rows)
+
+__device__ __forceinline__ void mma_u8s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
+                 : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0), "r"(0), "r"(0), "r"(0));
+}
+
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const void * tmap, int c0, int c1, int c2, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+        "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+        : "memory");
+}
+
+// ---- one unit (256 weights) of 16 rows against 8 columns. wt = shared address of the [16][144 B] sub-tile, am / ax = shared
+// addresses of the unit's activation records of column 0 (column stride cs_m / cs_x bytes). acc: (g, 2t) (g, 2t+1) (g+8, 2t) (g+8, 2t+1)
+
+__device__ __forceinline__ void unit_mma_q4_K(uint32_t wt, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, int g, int t, float (&acc)[4]) {
+    const uint32_t r0 = wt + g * 144, r1 = r0 + 8 * 144;
+    const uint4 h0 = lds128(r0), h1 = lds128(r1);  // d | dmin, 12 bytes of 6-bit scales / mins (ggml-common.h:291-305)
+    // 8 scales and 8 mins as bytes (ggml-cpu/quants.c:586-591)
+    const uint32_t sc0[2] = { h0.y & 0x3f3f3f3fu, (h0.w & 0x0f0f0f0fu) | ((h0.y >> 2) & 0x30303030u) };
+    const uint32_t mn0[2] = { h0.z & 0x3f3f3f3fu, ((h0.w >> 4) & 0x0f0f0f0fu) | ((h0.z >> 2) & 0x30303030u) };
+    const uint32_t sc1[2] = { h1.y & 0x3f3f3f3fu, (h1.w & 0x0f0f0f0fu) | ((h1.y >> 2) & 0x30303030u) };
+    const uint32_t mn1[2] = { h1.z & 0x3f3f3f3fu, ((h1.w >> 4) & 0x0f0f0f0fu) | ((h1.z >> 2) & 0x30303030u) };
+    const uint32_t bcol = am + g * cs_m + 4 * t;  // B fragments: column g, k bytes 4t.. and 16 + 4t..
+    int isum[4] = { 0, 0, 0, 0 };
+#pragma unroll
+    for (int i = 0; i < 4; i++) {  // 64 weights: low nibbles = sub-block 2i, high nibbles = sub-block 2i + 1
+        const uint32_t wa = lds32(r0 + 16 + 32 * i + 4 * t), wb = lds32(r0 + 32 + 32 * i + 4 * t);
+        const uint32_t wc = lds32(r1 + 16 + 32 * i + 4 * t), wd = lds32(r1 + 32 + 32 * i + 4 * t);
+#pragma unroll
+        for (int hn = 0; hn < 2; hn++) {
+            const int j = 2 * i + hn;
+            const uint32_t b0 = lds32(bcol + 32 * j), b1 = lds32(bcol + 32 * j + 16);
+            int c[4];
+            mma_u8s8(c, (wa >> (4 * hn)) & 0x0f0f0f0fu, (wc >> (4 * hn)) & 0x0f0f0f0fu, (wb >> (4 * hn)) & 0x0f0f0f0fu,
+                     (wd >> (4 * hn)) & 0x0f0f0f0fu, b0, b1);
+            const int s0 = (int) ((sc0[j >> 2] >> (8 * (j & 3))) & 0xff), s1 = (int) ((sc1[j >> 2] >> (8 * (j & 3))) & 0xff);
+            isum[0] += s0 * c[0]; isum[1] += s0 * c[1];
+            isum[2] += s1 * c[2]; isum[3] += s1 * c[3];
+        }
+    }
+    // min term: sum_j m_j * bsum_j per (row, column) - int16 block sums at +256 of the column's record
+    const uint4 bs0 = lds128(am + (2 * t) * cs_m + 256), bs1 = lds128(am + (2 * t + 1) * cs_m + 256);
+    auto mdot = [](const uint4 & bs, const uint32_t (&mn)[2]) {
+        int v = dp2a_lo_su((int) bs.x, mn[0], 0);
+        v     = dp2a_hi_su((int) bs.y, mn[0], v);
+        v     = dp2a_lo_su((int) bs.z, mn[1], v);
+        return dp2a_hi_su((int) bs.w, mn[1], v);
+    };
+    const float dy0 = __uint_as_float(lds32(ax + (2 * t) * cs_x)), dy1 = __uint_as_float(lds32(ax + (2 * t + 1) * cs_x));
+    const float d0 = half_bits_to_float((uint16_t) (h0.x & 0xffff)), m0 = half_bits_to_float((uint16_t) (h0.x >> 16));
+    const float d1 = half_bits_to_float((uint16_t) (h1.x & 0xffff)), m1 = half_bits_to_float((uint16_t) (h1.x >> 16));
+    acc[0] = fmaf(d0 * dy0, (float) isum[0], acc[0]); acc[0] = fmaf(-(m0 * dy0), (float) mdot(bs0, mn0), acc[0]);
+    acc[1] = fmaf(d0 * dy1, (float) isum[1], acc[1]); acc[1] = fmaf(-(m0 * dy1), (float) mdot(bs1, mn0), acc[1]);
+    acc[2] = fmaf(d1 * dy0, (float) isum[2], acc[2]); acc[2] = fmaf(-(m1 * dy0), (float) mdot(bs0, mn1), acc[2]);
+    acc[3] = fmaf(d1 * dy1, (float) isum[3], acc[3]); acc[3] = fmaf(-(m1 * dy1), (float) mdot(bs1, mn1), acc[3]);
+}
+
+// q4_0: 8 blocks of { half d; uint8 qs[16] } = 144 B per unit; element k = low nibble of qs[k], k + 16 = high nibble (one word
+// holds both k-halves of a fragment). Blocks are 18 bytes: even blocks start on a word boundary (qs is shifted by 16 bits), odd
+// blocks have qs word aligned. sum((q - 8) * y) = sum(q * y) - 8 * sum(y)  (ggml-cpu/quants.c:135-146)
+__device__ __forceinline__ void unit_mma_q4_0(uint32_t wt, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, int g, int t, float (&acc)[4]) {
+    const uint32_t r0 = wt + g * 144, r1 = r0 + 8 * 144;
+    const uint32_t bcol = am + g * cs_m + 4 * t;
+    // activation block scales (fp16 x 8 at +256 of the record) and block sums (int16 x 8 in the aux record) of columns 2t, 2t+1
+    const uint4 dy0 = lds128(am + (2 * t) * cs_m + 256), dy1 = lds128(am + (2 * t + 1) * cs_m + 256);
+    const uint4 ys0 = lds128(ax + (2 * t) * cs_x), ys1 = lds128(ax + (2 * t + 1) * cs_x);
+#pragma unroll
+    for (int bp = 0; bp < 4; bp++) {  // block pair = 36 bytes = 9 words
+        const uint32_t p0 = r0 + 36 * bp, p1 = r1 + 36 * bp;
+        // even block: d in the low half of word 0, qs word t = bytes 2 + 4t .. 5 + 4t = funnel(word t, word t + 1) >> 16
+        const uint32_t e0a = lds32(p0 + 4 * t), e0b = lds32(p0 + 4 * t + 4), e1a = lds32(p1 + 4 * t), e1b = lds32(p1 + 4 * t + 4);
+        const uint32_t hd0 = lds32(p0), hd1 = lds32(p1), od0 = lds32(p0 + 16), od1 = lds32(p1 + 16);  // d of the even / odd block
+        const uint32_t o0 = lds32(p0 + 20 + 4 * t), o1 = lds32(p1 + 20 + 4 * t);                         // odd block: qs word aligned
+#pragma unroll
+        for (int ob = 0; ob < 2; ob++) {
+            const int b = 2 * bp + ob;
+            const uint32_t q0 = ob ? o0 : __funnelshift_r(e0a, e0b, 16), q1 = ob ? o1 : __funnelshift_r(e1a, e1b, 16);
+            const float dw0 = half_bits_to_float((uint16_t) (ob ? od0 >> 16 : hd0 & 0xffff));
+            const float dw1 = half_bits_to_float((uint16_t) (ob ? od1 >> 16 : hd1 & 0xffff));
+            const uint32_t b0 = lds32(bcol + 32 * b), b1 = lds32(bcol + 32 * b + 16);
+            int c[4];
+            mma_u8s8(c, q0 & 0x0f0f0f0fu, q1 & 0x0f0f0f0fu, (q0 >> 4) & 0x0f0f0f0fu, (q1 >> 4) & 0x0f0f0f0fu, b0, b1);
+            const uint32_t dwd0 = b < 2 ? dy0.x : b < 4 ? dy0.y : b < 6 ? dy0.z : dy0.w, dwd1 = b < 2 ? dy1.x : b < 4 ? dy1.y : b < 6 ? dy1.z : dy1.w;
+            const uint32_t swd0 = b < 2 ? ys0.x : b < 4 ? ys0.y : b < 6 ? ys0.z : ys0.w, swd1 = b < 2 ? ys1.x : b < 4 ? ys1.y : b < 6 ? ys1.z : ys1.w;
+            const float y0 = half_bits_to_float((uint16_t) ((b & 1) ? dwd0 >> 16 : dwd0 & 0xffff));
+            const float y1 = half_bits_to_float((uint16_t) ((b & 1) ? dwd1 >> 16 : dwd1 & 0xffff));
+            const int   s0 = (int) (int16_t) ((b & 1) ? swd0 >> 16 : swd0 & 0xffff), s1 = (int) (int16_t) ((b & 1) ? swd1 >> 16 : swd1 & 0xffff);
+            acc[0] = fmaf((float) (c[0] - 8 * s0) * dw0, y0, acc[0]);
+            acc[1] = fmaf((float) (c[1] - 8 * s1) * dw0, y1, acc[1]);
+            acc[2] = fmaf((float) (c[2] - 8 * s0) * dw1, y0, acc[2]);
+            acc[3] = fmaf((float) (c[3] - 8 * s1) * dw1, y1, acc[3]);
+        }
+    }
+}
+
+template <int TYPE>
+__device__ __forceinline__ void unit_mma(uint32_t wt, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, int g, int t, float (&acc)[4]) {
+    if (TYPE == B200_TYPE_Q4_K) unit_mma_q4_K(wt, am, ax, cs_m, cs_x, g, t, acc);
+    else unit_mma_q4_0(wt, am, ax, cs_m, cs_x, g, t, acc);
+}
+
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void bar_named(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+struct MmaMaps {
+    CUtensorMap m[MV_MAX_MATS];
+};
+
+// shared memory: [0,8) act barrier | full[NS] empty[NS] | act: 8 columns x U x (272 + 16) | red: 2 x NWC x MMA_RT x 128 floats | ring
+template <int TYPE>
+__global__ void __launch_bounds__(32 * 17, 1)
+mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaMvParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    constexpr int UB = unit_bytes(TYPE);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int NWC = p.n_cons, NS = p.n_stages, U = p.U;
+    const int stage_bytes = NWC * MMA_ROWS * UB;
+    const int n_chunks = (U + NWC - 1) / NWC;
+
+    uint64_t * act_bar = (uint64_t *) smem;
+    uint64_t * full    = (uint64_t *) (smem + 64);
+    uint64_t * empty   = full + NS;
+    size_t     off     = (64 + 16 * (size_t) NS + 127) / 128 * 128;
+    uint8_t *  act_m   = smem + off;
+    const uint32_t cs_m = (uint32_t) U * ACT_MAIN + 16;  // +4 words: the 8 columns of a B-fragment load fall into 8 different bank groups
+    const uint32_t cs_x = (uint32_t) U * ACT_AUX;
+    uint8_t *  act_x   = act_m + (size_t) 8 * cs_m;
+    off                = (off + (size_t) 8 * (cs_m + cs_x) + 127) / 128 * 128;
+    float *    red     = (float *) (smem + off);
+    off                = (off + (size_t) 2 * NWC * MMA_RT * 128 * 4 + 1023) / 1024 * 1024;
+    uint8_t *  ring    = smem + off;
+
+    const int t_begin = (int) ((int64_t) p.total_tiles * blockIdx.x / gridDim.x);
+    const int t_end   = (int) ((int64_t) p.total_tiles * (blockIdx.x + 1) / gridDim.x);
+
+    if (threadIdx.x == 0) {
+        mbar_init(smem_u32(act_bar), 1);
+        for (int i = 0; i < NS; i++) {
+            mbar_init(smem_u32(full + i), 1);
+            mbar_init(smem_u32(empty + i), NWC);
+        }
+        fence_mbar_init();
+    }
+    __syncthreads();
+    pdl_launch_dependents();
+
+    if (warp == NWC) {
+        // ================================================================ producer: one 3-D box per (tile, chunk)
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 1;
+            for (int tile = t_begin; tile < t_end; tile++) {
+                int m = 0;
+#pragma unroll
+                for (int i = 1; i < MV_MAX_MATS; i++) if (i < p.n_mats && tile >= p.mat[i].group0) m = i;
+                const int row0 = (tile - p.mat[m].group0) * MMA_ROWS;
+                for (int ch = 0; ch < n_chunks; ch++) {
+                    mbar_wait(smem_u32(empty + stage), phase);
+                    const uint32_t bar = smem_u32(full + stage);
+                    mbar_expect_tx(bar, (uint32_t) stage_bytes);  // out-of-range rows / units are zero filled and still counted
+                    tma_load_3d(smem_u32(ring + (size_t) stage * stage_bytes), &maps.m[m], 0, row0, ch * NWC, bar);
+                    if (++stage == NS) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        return;
+    }
+    if (warp > NWC) return;
+
+    // ==================================================================== consumers
+    const int w = warp, g = lane >> 2, t = lane & 3;
+    pdl_wait();  // the activation records are written by the quantizer launch before this one
+    // activations: ncols columns of U records (one bulk copy per column: the shared column stride is padded); columns ncols..7
+    // are zero (the MMA always multiplies 8)
+    for (int i = threadIdx.x; i < (8 - p.ncols) * (int) (cs_m / 16); i += NWC * 32)
+        ((uint4 *) (act_m + (size_t) p.ncols * cs_m))[i] = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x; i < (8 - p.ncols) * (int) (cs_x / 16); i += NWC * 32)
+        ((uint4 *) (act_x + (size_t) p.ncols * cs_x))[i] = make_uint4(0, 0, 0, 0);
+    if (w == 0 && lane == 0) {
+        const uint64_t pol_keep = l2_policy_evict_last();
+        const uint32_t bytes_m = (uint32_t) U * ACT_MAIN, bytes_x = (uint32_t) p.ncols * U * ACT_AUX;
+        mbar_expect_tx(smem_u32(act_bar), (uint32_t) p.ncols * bytes_m + bytes_x);
+        for (int c = 0; c < p.ncols; c++)
+            bulk_g2s(smem_u32(act_m + (size_t) c * cs_m), p.act_main + (size_t) c * bytes_m, bytes_m, smem_u32(act_bar), pol_keep);
+        bulk_g2s(smem_u32(act_x), p.act_aux, bytes_x, smem_u32(act_bar), pol_keep);
+    }
+    mbar_wait(smem_u32(act_bar), 0);
+    bar_named(1, NWC * 32);  // the zero fill of the unused columns is visible
+
+    const uint32_t am0 = smem_u32(act_m), ax0 = smem_u32(act_x);
+    int stage = 0; uint32_t phase = 0;
+    int parity = 0;
+    for (int tile0 = t_begin; tile0 < t_end; tile0 += MMA_RT) {
+        const int nt = min(MMA_RT, t_end - tile0);
+        float acc[MMA_RT][4];
+#pragma unroll
+        for (int r = 0; r < MMA_RT; r++) { acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.0f; }
+#pragma unroll
+        for (int r = 0; r < MMA_RT; r++) {
+            if (r < nt) {
+                for (int ch = 0; ch < n_chunks; ch++) {
+                    mbar_wait(smem_u32(full + stage), phase);
+                    const int u = ch * NWC + w;
+                    if (u < U) {
+                        const uint32_t wt = smem_u32(ring + (size_t) stage * stage_bytes) + (uint32_t) w * MMA_ROWS * UB;
+                        unit_mma<TYPE>(wt, am0 + (uint32_t) u * ACT_MAIN, ax0 + (uint32_t) u * ACT_AUX, cs_m, cs_x, g, t, acc[r]);
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(smem_u32(empty + stage));
+                    if (++stage == NS) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        // fixed-order sum of the NWC partial results: red[parity][w][tile r][(row, col)]
+        float * rp = red + (size_t) parity * NWC * MMA_RT * 128;
+#pragma unroll
+        for (int r = 0; r < MMA_RT; r++) {
+            float * q = rp + (w * MMA_RT + r) * 128;
+            q[g * 8 + 2 * t]           = acc[r][0];
+            q[g * 8 + 2 * t + 1]       = acc[r][1];
+            q[(g + 8) * 8 + 2 * t]     = acc[r][2];
+            q[(g + 8) * 8 + 2 * t + 1] = acc[r][3];
+        }
+        bar_named(1, NWC * 32);
+        for (int o = threadIdx.x; o < nt * 128; o += NWC * 32) {
+            const int r = o >> 7, e = o & 127;
+            float v = 0.0f;
+            for (int i = 0; i < NWC; i++) v += rp[(i * MMA_RT + r) * 128 + e];
+            const int tile = tile0 + r;
+            int m = 0;
+#pragma unroll
+            for (int i = 1; i < MV_MAX_MATS; i++) if (i < p.n_mats && tile >= p.mat[i].group0) m = i;
+            const int row = (tile - p.mat[m].group0) * MMA_ROWS + (e >> 3), c = e & 7;
+            if (row < p.mat[m].M && c < p.ncols) split_store(p.split, p.mat[m].dst + (int64_t) c * p.mat[m].dst_cs + row, v);
+        }
+        parity ^= 1;
+    }
+    if (p.split.n_ranks > 1) {
+        bar_named(1, NWC * 32);
+        if (w == 0) split_complete(p.split, gridDim.x * gridDim.y);
+    }
+}
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                    const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+encode_tiled_fn mma_get_encode() {
+    static encode_tiled_fn fn = [] {
+        void * ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess && qres == cudaDriverEntryPointSuccess)
+            return (encode_tiled_fn) ptr;
+        return (encode_tiled_fn) nullptr;
+    }();
+    return fn;
+}
+
+} // namespace
+
+size_t mv_mma_smem(int type, int U, int n_cons, int n_stages) {
+    size_t off = (64 + 16 * (size_t) n_stages + 127) / 128 * 128;
+    off = (off + (size_t) 8 * ((size_t) U * (ACT_MAIN + ACT_AUX) + 16) + 127) / 128 * 128;
+    off = (off + (size_t) 2 * n_cons * MMA_RT * 128 * 4 + 1023) / 1024 * 1024;
+    return off + (size_t) n_stages * n_cons * MMA_ROWS * unit_bytes(type) + 1024;
+}
+
+bool mv_mma_usable(int type) { return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0) && mma_get_encode() != nullptr; }
+
+} // namespace b200
+
+// host: n_ops matrices (same type, K) against `ncols` pre-quantized activation columns
+b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, const uint8_t * const * ws, const size_t * nb01s, const int64_t * Ms,
+                            float * const * dsts, const int64_t * dst_cs, int ncols, const uint8_t * act_main, const uint8_t * act_aux) {
+    const int U  = (int) (K / 256);
+    const int UB = unit_bytes(type);
+    // consumer warps: as many as leave room for >= 3 ring stages next to the 8 activation columns (K = 14336: 129 KB of them)
+    int n_cons = 0, n_stages = 0;
+    static const int cand[] = { 16, 12, 8, 6, 4 };
+    for (int nc : cand) {
+        if (ctx->mma_warps > 0 && nc != ctx->mma_warps) continue;
+        for (int ns = 6; ns >= 2 && !n_cons; ns--) {
+            if (ns < 3 && nc > 4) continue;
+            if (mv_mma_smem(type, U, nc, ns) <= 227 * 1024) { n_cons = nc; n_stages = ns; }
+        }
+        if (n_cons) break;
+    }
+    if (!n_cons && ctx->mma_warps > 0 && mv_mma_smem(type, U, ctx->mma_warps, 2) <= 227 * 1024) { n_cons = ctx->mma_warps; n_stages = 2; }
+    if (n_cons == 0) return b200_fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
+    const size_t smem = mv_mma_smem(type, U, n_cons, n_stages);
+    encode_tiled_fn enc = mma_get_encode();
+    for (int o0 = 0; o0 < n_ops; o0 += MV_MAX_MATS) {
+        MmaMvParams p;
+        MmaMaps     maps;
+        memset(&p, 0, sizeof(p));
+        memset(&maps, 0, sizeof(maps));
+        p.n_mats = n_ops - o0 < MV_MAX_MATS ? n_ops - o0 : MV_MAX_MATS;
+        int tiles = 0;
+        for (int i = 0; i < p.n_mats; i++) {
+            p.mat[i].w      = ws[o0 + i];
+            p.mat[i].nb01   = (int64_t) nb01s[o0 + i];
+            p.mat[i].dst    = dsts[o0 + i];
+            p.mat[i].dst_cs = dst_cs[o0 + i];
+            p.mat[i].M      = (int) Ms[o0 + i];
+            p.mat[i].group0 = tiles;
+            tiles += (int) ((Ms[o0 + i] + MMA_ROWS - 1) / MMA_ROWS);
+            // 3-D view of the row-major block stream: [unit][row][unit bytes] - a box lands as NWC dense [16][144 B] sub-tiles. (A 2-D
+            // box with long rows is no faster and needs an odd unit count to stay bank-conflict free: measured 2441 vs 2612 GB/s.)
+            cuuint64_t dims[3]    = { (cuuint64_t) (UB / 4), (cuuint64_t) Ms[o0 + i], (cuuint64_t) U };
+            cuuint64_t strides[2] = { (cuuint64_t) nb01s[o0 + i], (cuuint64_t) UB };
+            cuuint32_t box[3]     = { (cuuint32_t) (UB / 4), MMA_ROWS, (cuuint32_t) n_cons };
+            cuuint32_t estr[3]    = { 1, 1, 1 };
+            const CUresult cr = enc(&maps.m[i], CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, (void *) ws[o0 + i], dims, strides, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (cr != CUDA_SUCCESS) {
+                return b200_fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the weight stream (M=%lld K=%lld nb01=%zu)", (long long) Ms[o0 + i],
+                                 (long long) K, nb01s[o0 + i]);
+            }
+        }
+        for (int i = p.n_mats; i < MV_MAX_MATS; i++) p.mat[i].group0 = INT32_MAX;
+        if (tiles == 0) continue;
+        p.total_tiles = tiles;
+        p.U = U; p.ncols = ncols; p.n_cons = n_cons; p.n_stages = n_stages; p.pdl = ctx->pdl;
+        p.act_main = act_main; p.act_aux = act_aux;
+        p.split = ctx->split;
+        const int grid = tiles < ctx->sm_count ? tiles : ctx->sm_count;
+        static bool attr_done[2][64] = {};
+        const int ti = type == B200_TYPE_Q4_K ? 0 : 1;
+        if (ctx->device < 64 && !attr_done[ti][ctx->device]) {
+            if (ti == 0) CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            else         CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q4_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            attr_done[ti][ctx->device] = true;
+        }
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim          = dim3(grid);
+        cfg.blockDim         = dim3(32 * (n_cons + 1));
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream           = ctx->stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs    = attr;
+        cfg.numAttrs = p.pdl ? 1 : 0;
+        if (ti == 0) CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_K>, maps, p));
+        else         CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_0>, maps, p));
+        ctx->launches++;
+    }
+    return B200_OK;
+}
