@@ -118,6 +118,7 @@ b200_status b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     if (const char * s = getenv("GGML_B200_DBG")) c->dbg = atoi(s);
     if (const char * s = getenv("GGML_B200_MMA_MIN")) c->mma_min_cols = atoi(s);
     if (const char * s = getenv("GGML_B200_MMA_WARPS")) c->mma_warps = atoi(s);
+    if (const char * s = getenv("GGML_B200_MOE_GROUP_MIN")) c->moe_group_min = atoi(s);
     *out = c;
     return B200_OK;
 }

@@ -55,7 +55,9 @@ struct b200_ctx {
     int          trace_slots = 0;
     int          dbg = 0;                      // GGML_B200_DBG: experiment switches handed to the kernels
     int          mma_min_cols = 3;             // columns from which the IMMA mat-vec kernel (mvmma.cu) replaces the dp4a one; GGML_B200_MMA_MIN
-    int          mma_warps = 0;                // 0 = auto (8); GGML_B200_MMA_WARPS
+    int          mma_warps = 0;                // 0 = auto; GGML_B200_MMA_WARPS
+    int          moe_group_min = 2;            // MUL_MAT_ID: group by expert (tensor-core mat-vec) from this many pairs per expert on
+                                               // average; 0 = never; GGML_B200_MOE_GROUP_MIN
 };
 
 // bumped whenever device memory the library may hold predictions / caches for is freed or rewritten
@@ -69,6 +71,10 @@ b200_status b200_ensure(b200_ctx * ctx, void ** buf, size_t * cur, size_t need);
 namespace b200 { bool mv_mma_usable(int type); }
 b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, const uint8_t * const * ws, const size_t * nb01s, const int64_t * Ms,
                             float * const * dsts, const int64_t * dst_cs, int ncols, const uint8_t * act_main, const uint8_t * act_aux);
+
+b200_status b200_mv_mma_run_ids(b200_ctx * ctx, int type, int64_t K, const uint8_t * as, size_t nb01, size_t nb02, int64_t M, int64_t n_as,
+                                float * dst, const b200::MvIds & ids, const int32_t * sp, const int32_t * eb, const uint8_t * act_main,
+                                const uint8_t * act_aux);
 
 // mmq.cu: the tcgen05 int8 tile kernel
 bool        b200_mmq_usable(int type, int64_t K, const void * w, size_t nb01);

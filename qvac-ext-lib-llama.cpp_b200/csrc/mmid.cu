@@ -116,7 +116,11 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
 
     if (fast) {
         const int  U    = (int) (K / 256);
-        const bool fuse = ctx->fuse_quant && U <= 64;  // every pair's CTAs quantize that pair's activation row themselves
+        // enough pairs per expert: sort the pairs by expert and let every expert multiply its tokens 8 columns at a time on the
+        // tensor-core mat-vec kernel (mvmma.cu) - an expert's weights are then read once per 8 tokens instead of once per token
+        const bool grouped = ctx->moe_group_min > 0 && n_pairs >= (int64_t) ctx->moe_group_min * d->n_as && n_pairs >= 8 && mv_mma_usable(d->type) &&
+                             d->nb12 == d->nb11 * (size_t) d->ne11;
+        const bool fuse = !grouped && ctx->fuse_quant && U <= 64;  // every pair's CTAs quantize that pair's activation row themselves
         uint8_t * am = nullptr, * ax = nullptr;
         if (!fuse) {
             const size_t main_b = (size_t) n_rows * U * ACT_MAIN, aux_b = (size_t) n_rows * U * ACT_AUX;
@@ -140,6 +144,15 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
         }
         mi.x_is = (int64_t) d->nb11;
         mi.x_ts = (int64_t) d->nb12;
+        if (grouped) {
+            b200_status st = b200_ensure(ctx, &ctx->scratch2, &ctx->scratch2_size, (size_t) (((n_pairs + 63) & ~(int64_t) 63) + d->n_as + 1) * 4 + 256);
+            if (st != B200_OK) return st;
+            int32_t * sp = (int32_t *) ctx->scratch2;
+            int32_t * eb = sp + ((n_pairs + 63) & ~(int64_t) 63);
+            st = b200_mm_ids_sort(ctx, ids, d->n_used, d->n_tok, d->ids_nb1, d->n_as, sp, eb);
+            if (st != B200_OK) return st;
+            return b200_mv_mma_run_ids(ctx, d->type, K, (const uint8_t *) as, d->nb01, d->nb02, M, d->n_as, dst, mi, sp, eb, am, ax);
+        }
         MvParams p;
         memset(&p, 0, sizeof(p));
         p.U = U;

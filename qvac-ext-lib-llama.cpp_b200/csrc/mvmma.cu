@@ -31,6 +31,11 @@ struct MmaMvParams {
     const uint8_t * act_main;           // [ncols][U][272]
     const uint8_t * act_aux;            // [ncols][U][16]
     SplitParams     split;
+    // MUL_MAT_ID mode (sp != nullptr): blockIdx.y = expert e; its (slot, token) pairs sp[eb[e] .. eb[e+1]) are the columns, 8 at a
+    // time; pair p = t * n_used + i reads activation row t * ne11 + i % ne11 and writes dst + t * dst_ts + i * dst_is
+    const int32_t * sp;                 // pairs sorted by expert (b200_mm_ids_sort)
+    const int32_t * eb;                 // [n_as + 1] first sorted position of every expert
+    MvIds           ids;
 };
 
 namespace {
@@ -48,6 +53,13 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const void * tmap, int
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
         "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+        : "memory");
+}
+
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const void * tmap, int c0, int c1, int c2, int c3, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];" ::"r"(dst),
+        "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar)
         : "memory");
 }
 
@@ -176,6 +188,21 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
     const int t_begin = (int) ((int64_t) p.total_tiles * blockIdx.x / gridDim.x);
     const int t_end   = (int) ((int64_t) p.total_tiles * (blockIdx.x + 1) / gridDim.x);
 
+    // MUL_MAT_ID: this CTA row works for expert e on the pairs routed to it (the sort ran earlier on the stream)
+    const bool by_expert = p.sp != nullptr;
+    int e = 0, pair0 = 0, n_pairs = p.ncols;
+    if (by_expert) {
+        pdl_wait();
+        e       = blockIdx.y;
+        pair0   = p.eb[e];
+        n_pairs = p.eb[e + 1] - pair0;
+        if (n_pairs <= 0 || t_begin >= t_end) {
+            if (p.split.n_ranks > 1 && warp == 0) split_complete(p.split, gridDim.x * gridDim.y);
+            return;
+        }
+    }
+    const int n_passes = (n_pairs + 7) / 8;  // the weight stream is read once per 8 columns
+
     if (threadIdx.x == 0) {
         mbar_init(smem_u32(act_bar), 1);
         for (int i = 0; i < NS; i++) {
@@ -188,20 +215,24 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
     pdl_launch_dependents();
 
     if (warp == NWC) {
-        // ================================================================ producer: one 3-D box per (tile, chunk)
+        // ================================================================ producer: one TMA box per (pass, tile, chunk)
         if (lane == 0) {
             int stage = 0; uint32_t phase = 1;
-            for (int tile = t_begin; tile < t_end; tile++) {
-                int m = 0;
+            for (int pass = 0; pass < n_passes; pass++) {
+                for (int tile = t_begin; tile < t_end; tile++) {
+                    int m = 0;
 #pragma unroll
-                for (int i = 1; i < MV_MAX_MATS; i++) if (i < p.n_mats && tile >= p.mat[i].group0) m = i;
-                const int row0 = (tile - p.mat[m].group0) * MMA_ROWS;
-                for (int ch = 0; ch < n_chunks; ch++) {
-                    mbar_wait(smem_u32(empty + stage), phase);
-                    const uint32_t bar = smem_u32(full + stage);
-                    mbar_expect_tx(bar, (uint32_t) stage_bytes);  // out-of-range rows / units are zero filled and still counted
-                    tma_load_3d(smem_u32(ring + (size_t) stage * stage_bytes), &maps.m[m], 0, row0, ch * NWC, bar);
-                    if (++stage == NS) { stage = 0; phase ^= 1; }
+                    for (int i = 1; i < MV_MAX_MATS; i++) if (i < p.n_mats && tile >= p.mat[i].group0) m = i;
+                    const int row0 = (tile - p.mat[m].group0) * MMA_ROWS;
+                    for (int ch = 0; ch < n_chunks; ch++) {
+                        mbar_wait(smem_u32(empty + stage), phase);
+                        const uint32_t bar = smem_u32(full + stage);
+                        mbar_expect_tx(bar, (uint32_t) stage_bytes);  // out-of-range rows / units are zero filled and still counted
+                        const uint32_t dst = smem_u32(ring + (size_t) stage * stage_bytes);
+                        if (by_expert) tma_load_4d(dst, &maps.m[0], 0, row0, ch * NWC, e, bar);
+                        else tma_load_3d(dst, &maps.m[m], 0, row0, ch * NWC, bar);
+                        if (++stage == NS) { stage = 0; phase ^= 1; }
+                    }
                 }
             }
         }
@@ -211,74 +242,90 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
 
     // ==================================================================== consumers
     const int w = warp, g = lane >> 2, t = lane & 3;
-    pdl_wait();  // the activation records are written by the quantizer launch before this one
-    // activations: ncols columns of U records (one bulk copy per column: the shared column stride is padded); columns ncols..7
-    // are zero (the MMA always multiplies 8)
-    for (int i = threadIdx.x; i < (8 - p.ncols) * (int) (cs_m / 16); i += NWC * 32)
-        ((uint4 *) (act_m + (size_t) p.ncols * cs_m))[i] = make_uint4(0, 0, 0, 0);
-    for (int i = threadIdx.x; i < (8 - p.ncols) * (int) (cs_x / 16); i += NWC * 32)
-        ((uint4 *) (act_x + (size_t) p.ncols * cs_x))[i] = make_uint4(0, 0, 0, 0);
-    if (w == 0 && lane == 0) {
-        const uint64_t pol_keep = l2_policy_evict_last();
-        const uint32_t bytes_m = (uint32_t) U * ACT_MAIN, bytes_x = (uint32_t) p.ncols * U * ACT_AUX;
-        mbar_expect_tx(smem_u32(act_bar), (uint32_t) p.ncols * bytes_m + bytes_x);
-        for (int c = 0; c < p.ncols; c++)
-            bulk_g2s(smem_u32(act_m + (size_t) c * cs_m), p.act_main + (size_t) c * bytes_m, bytes_m, smem_u32(act_bar), pol_keep);
-        bulk_g2s(smem_u32(act_x), p.act_aux, bytes_x, smem_u32(act_bar), pol_keep);
-    }
-    mbar_wait(smem_u32(act_bar), 0);
-    bar_named(1, NWC * 32);  // the zero fill of the unused columns is visible
-
+    if (!by_expert) pdl_wait();  // the activation records are written by the quantizer launch before this one
     const uint32_t am0 = smem_u32(act_m), ax0 = smem_u32(act_x);
     int stage = 0; uint32_t phase = 0;
     int parity = 0;
-    for (int tile0 = t_begin; tile0 < t_end; tile0 += MMA_RT) {
-        const int nt = min(MMA_RT, t_end - tile0);
-        float acc[MMA_RT][4];
-#pragma unroll
-        for (int r = 0; r < MMA_RT; r++) { acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.0f; }
-#pragma unroll
-        for (int r = 0; r < MMA_RT; r++) {
-            if (r < nt) {
-                for (int ch = 0; ch < n_chunks; ch++) {
-                    mbar_wait(smem_u32(full + stage), phase);
-                    const int u = ch * NWC + w;
-                    if (u < U) {
-                        const uint32_t wt = smem_u32(ring + (size_t) stage * stage_bytes) + (uint32_t) w * MMA_ROWS * UB;
-                        unit_mma<TYPE>(wt, am0 + (uint32_t) u * ACT_MAIN, ax0 + (uint32_t) u * ACT_AUX, cs_m, cs_x, g, t, acc[r]);
-                    }
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(smem_u32(empty + stage));
-                    if (++stage == NS) { stage = 0; phase ^= 1; }
+    for (int pass = 0; pass < n_passes; pass++) {
+        const int nc = min(8, n_pairs - 8 * pass);
+        // activations: nc columns of U records (one bulk copy per column: the shared column stride is padded); columns nc..7 are
+        // zero (the MMA always multiplies 8). The previous pass's readers are behind its last reduction barrier.
+        for (int i = threadIdx.x; i < (8 - nc) * (int) (cs_m / 16); i += NWC * 32) ((uint4 *) (act_m + (size_t) nc * cs_m))[i] = make_uint4(0, 0, 0, 0);
+        for (int i = threadIdx.x; i < (8 - nc) * (int) (cs_x / 16); i += NWC * 32) ((uint4 *) (act_x + (size_t) nc * cs_x))[i] = make_uint4(0, 0, 0, 0);
+        if (w == 0 && lane == 0) {
+            const uint64_t pol_keep = l2_policy_evict_last();
+            const uint32_t bytes_m = (uint32_t) U * ACT_MAIN, bytes_x = (uint32_t) U * ACT_AUX;
+            mbar_expect_tx(smem_u32(act_bar), (uint32_t) nc * (bytes_m + bytes_x));
+            for (int c = 0; c < nc; c++) {
+                int64_t arow = c;
+                if (by_expert) {
+                    const int pr = p.sp[pair0 + 8 * pass + c];
+                    const int tk = pr / p.ids.n_used, sl = pr - tk * p.ids.n_used;
+                    arow = (int64_t) tk * p.ids.ne11 + sl % p.ids.ne11;
                 }
+                bulk_g2s(smem_u32(act_m + (size_t) c * cs_m), p.act_main + (size_t) arow * bytes_m, bytes_m, smem_u32(act_bar), pol_keep);
+                bulk_g2s(smem_u32(act_x + (size_t) c * cs_x), p.act_aux + (size_t) arow * bytes_x, bytes_x, smem_u32(act_bar), pol_keep);
             }
         }
-        // fixed-order sum of the NWC partial results: red[parity][w][tile r][(row, col)]
-        float * rp = red + (size_t) parity * NWC * MMA_RT * 128;
+        mbar_wait(smem_u32(act_bar), (uint32_t) (pass & 1));
+        bar_named(1, NWC * 32);  // the zero fill of the unused columns is visible
+
+        for (int tile0 = t_begin; tile0 < t_end; tile0 += MMA_RT) {
+            const int nt = min(MMA_RT, t_end - tile0);
+            float acc[MMA_RT][4];
 #pragma unroll
-        for (int r = 0; r < MMA_RT; r++) {
-            float * q = rp + (w * MMA_RT + r) * 128;
-            q[g * 8 + 2 * t]           = acc[r][0];
-            q[g * 8 + 2 * t + 1]       = acc[r][1];
-            q[(g + 8) * 8 + 2 * t]     = acc[r][2];
-            q[(g + 8) * 8 + 2 * t + 1] = acc[r][3];
-        }
-        bar_named(1, NWC * 32);
-        for (int o = threadIdx.x; o < nt * 128; o += NWC * 32) {
-            const int r = o >> 7, e = o & 127;
-            float v = 0.0f;
-            for (int i = 0; i < NWC; i++) v += rp[(i * MMA_RT + r) * 128 + e];
-            const int tile = tile0 + r;
-            int m = 0;
+            for (int r = 0; r < MMA_RT; r++) { acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.0f; }
 #pragma unroll
-            for (int i = 1; i < MV_MAX_MATS; i++) if (i < p.n_mats && tile >= p.mat[i].group0) m = i;
-            const int row = (tile - p.mat[m].group0) * MMA_ROWS + (e >> 3), c = e & 7;
-            if (row < p.mat[m].M && c < p.ncols) split_store(p.split, p.mat[m].dst + (int64_t) c * p.mat[m].dst_cs + row, v);
+            for (int r = 0; r < MMA_RT; r++) {
+                if (r < nt) {
+                    for (int ch = 0; ch < n_chunks; ch++) {
+                        mbar_wait(smem_u32(full + stage), phase);
+                        const int u = ch * NWC + w;
+                        if (u < U) {
+                            const uint32_t wt = smem_u32(ring + (size_t) stage * stage_bytes) + (uint32_t) w * MMA_ROWS * UB;
+                            unit_mma<TYPE>(wt, am0 + (uint32_t) u * ACT_MAIN, ax0 + (uint32_t) u * ACT_AUX, cs_m, cs_x, g, t, acc[r]);
+                        }
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(smem_u32(empty + stage));
+                        if (++stage == NS) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+            // fixed-order sum of the NWC partial results: red[parity][w][tile r][(row, col)]
+            float * rp = red + (size_t) parity * NWC * MMA_RT * 128;
+#pragma unroll
+            for (int r = 0; r < MMA_RT; r++) {
+                float * q = rp + (w * MMA_RT + r) * 128;
+                q[g * 8 + 2 * t]           = acc[r][0];
+                q[g * 8 + 2 * t + 1]       = acc[r][1];
+                q[(g + 8) * 8 + 2 * t]     = acc[r][2];
+                q[(g + 8) * 8 + 2 * t + 1] = acc[r][3];
+            }
+            bar_named(1, NWC * 32);
+            for (int o = threadIdx.x; o < nt * 128; o += NWC * 32) {
+                const int r = o >> 7, el = o & 127;
+                float v = 0.0f;
+                for (int i = 0; i < NWC; i++) v += rp[(i * MMA_RT + r) * 128 + el];
+                const int tile = tile0 + r;
+                int m = 0;
+#pragma unroll
+                for (int i = 1; i < MV_MAX_MATS; i++) if (i < p.n_mats && tile >= p.mat[i].group0) m = i;
+                const int row = (tile - p.mat[m].group0) * MMA_ROWS + (el >> 3), c = el & 7;
+                if (row < p.mat[m].M && c < nc) {
+                    int64_t col_off = (int64_t) c * p.mat[m].dst_cs;
+                    if (by_expert) {
+                        const int pr = p.sp[pair0 + 8 * pass + c];
+                        const int tk = pr / p.ids.n_used, sl = pr - tk * p.ids.n_used;
+                        col_off = (int64_t) tk * p.ids.dst_ts + (int64_t) sl * p.ids.dst_is;
+                    }
+                    split_store(p.split, p.mat[m].dst + col_off + row, v);
+                }
+            }
+            parity ^= 1;
         }
-        parity ^= 1;
+        bar_named(1, NWC * 32);  // every warp is done with this pass's activation columns
     }
     if (p.split.n_ranks > 1) {
-        bar_named(1, NWC * 32);
         if (w == 0) split_complete(p.split, gridDim.x * gridDim.y);
     }
 }
@@ -387,5 +434,75 @@ b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, cons
         else         CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_0>, maps, p));
         ctx->launches++;
     }
+    return B200_OK;
+}
+
+// host: MUL_MAT_ID grouped by expert. as = [n_as] expert matrices (nb02 apart), activations pre-quantized ([ne11 * n_tok] rows of
+// unit records), sp / eb = the device arrays b200_mm_ids_sort produced for these ids.
+b200_status b200_mv_mma_run_ids(b200_ctx * ctx, int type, int64_t K, const uint8_t * as, size_t nb01, size_t nb02, int64_t M, int64_t n_as,
+                                float * dst, const MvIds & ids, const int32_t * sp, const int32_t * eb, const uint8_t * act_main,
+                                const uint8_t * act_aux) {
+    const int U  = (int) (K / 256);
+    const int UB = unit_bytes(type);
+    int n_cons = 0, n_stages = 0;
+    static const int cand[] = { 16, 12, 8, 6, 4 };
+    for (int nc : cand) {
+        for (int ns = 6; ns >= 2 && !n_cons; ns--) {
+            if (ns < 3 && nc > 4) continue;
+            if (mv_mma_smem(type, U, nc, ns) <= 227 * 1024) { n_cons = nc; n_stages = ns; }
+        }
+        if (n_cons) break;
+    }
+    if (n_cons == 0) return b200_fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
+    const size_t smem = mv_mma_smem(type, U, n_cons, n_stages);
+    MmaMvParams p;
+    MmaMaps     maps;
+    memset(&p, 0, sizeof(p));
+    memset(&maps, 0, sizeof(maps));
+    cuuint64_t dims[4]    = { (cuuint64_t) (UB / 4), (cuuint64_t) M, (cuuint64_t) U, (cuuint64_t) n_as };
+    cuuint64_t strides[3] = { (cuuint64_t) nb01, (cuuint64_t) UB, (cuuint64_t) nb02 };
+    cuuint32_t box[4]     = { (cuuint32_t) (UB / 4), MMA_ROWS, (cuuint32_t) n_cons, 1 };
+    cuuint32_t estr[4]    = { 1, 1, 1, 1 };
+    if (mma_get_encode()(&maps.m[0], CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, (void *) as, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+        return b200_fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the expert weight stream (M=%lld K=%lld n_as=%lld)", (long long) M,
+                         (long long) K, (long long) n_as);
+    }
+    p.n_mats        = 1;
+    p.mat[0].w      = as;
+    p.mat[0].nb01   = (int64_t) nb01;
+    p.mat[0].dst    = dst;
+    p.mat[0].dst_cs = 0;
+    p.mat[0].M      = (int) M;
+    p.mat[0].group0 = 0;
+    for (int i = 1; i < MV_MAX_MATS; i++) p.mat[i].group0 = INT32_MAX;
+    p.total_tiles = (int) ((M + MMA_ROWS - 1) / MMA_ROWS);
+    p.U = U; p.ncols = 0; p.n_cons = n_cons; p.n_stages = n_stages; p.pdl = ctx->pdl;
+    p.act_main = act_main; p.act_aux = act_aux;
+    p.split = ctx->split;
+    p.sp = sp; p.eb = eb; p.ids = ids;
+    int per_expert = (int) (ctx->sm_count / n_as);
+    if (per_expert < 1) per_expert = 1;
+    if (per_expert > p.total_tiles) per_expert = p.total_tiles;
+    static bool attr_done[2][64] = {};
+    const int ti = type == B200_TYPE_Q4_K ? 0 : 1;
+    if (ctx->device < 64 && !attr_done[ti][ctx->device]) {
+        if (ti == 0) CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        else         CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q4_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_done[ti][ctx->device] = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim          = dim3(per_expert, (unsigned) n_as);
+    cfg.blockDim         = dim3(32 * (n_cons + 1));
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream           = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs    = attr;
+    cfg.numAttrs = p.pdl ? 1 : 0;
+    if (ti == 0) CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_K>, maps, p));
+    else         CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_0>, maps, p));
+    ctx->launches++;
     return B200_OK;
 }
