@@ -187,6 +187,12 @@ typedef struct {
     void *  sync_words[8];
 } b200_row_split;
 B200_API b200_status  b200_ctx_set_row_split(b200_ctx * ctx, const b200_row_split * rs);   /* rs == NULL or n_ranks <= 1: off */
+/* Deferred mode: a decode mat-vec kernel publishes its epoch to the peers and returns without waiting for theirs; the wait moves into
+ * the prologue of the next kernel of the context (behind its weight prefetch) and into every entry point that reads results or
+ * synchronizes (memcpy, event record, synchronize run b200_ctx_row_split_wait first). A caller that lets anything else consume a
+ * dst on the stream must call b200_ctx_row_split_wait itself before that. */
+B200_API b200_status  b200_ctx_set_row_split_deferred(b200_ctx * ctx, int enable);
+B200_API b200_status  b200_ctx_row_split_wait(b200_ctx * ctx);
 
 /* ---------------------------------------------------------------- prefill weight cache ---- */
 

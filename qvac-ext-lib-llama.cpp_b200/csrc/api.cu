@@ -170,6 +170,7 @@ void         b200_ctx_set_prefetch(b200_ctx * ctx, int kb_per_cta) {
     ctx->last_key = nullptr;
 }
 b200_status  b200_ctx_synchronize(b200_ctx * ctx) {
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
     CU(cudaSetDevice(ctx->device));
     CU(cudaStreamSynchronize(ctx->stream));
     return B200_OK;
@@ -179,6 +180,7 @@ b200_status  b200_ctx_synchronize(b200_ctx * ctx) {
 
 b200_status b200_ctx_set_row_split(b200_ctx * ctx, const b200_row_split * rs) {
     if (!ctx) return fail(B200_ERR_ARG, "null context");
+    if (b200_status st = b200_split_flush(ctx)) return st;
     ctx->split = SplitParams{};
     if (!rs || rs->n_ranks <= 1) return B200_OK;
     if (rs->n_ranks > SPLIT_MAX_RANKS || rs->rank < 0 || rs->rank >= rs->n_ranks || !rs->sync_words[rs->rank])
@@ -192,6 +194,29 @@ b200_status b200_ctx_set_row_split(b200_ctx * ctx, const b200_row_split * rs) {
     }
     ctx->split.sync_local = (uint32_t *) rs->sync_words[rs->rank];
     return B200_OK;
+}
+
+__global__ void split_wait_kernel(const SplitParams sp) { split_wait(sp); }
+
+b200_status b200_split_flush(b200_ctx * ctx) {
+    if (!ctx->split_pending || ctx->split.n_ranks <= 1) return B200_OK;
+    CU(cudaSetDevice(ctx->device));
+    split_wait_kernel<<<1, 32, 0, ctx->stream>>>(ctx->split);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    ctx->split_pending = 0;
+    return B200_OK;
+}
+
+b200_status b200_ctx_set_row_split_deferred(b200_ctx * ctx, int enable) {
+    if (!ctx) return fail(B200_ERR_ARG, "null context");
+    b200_status st = b200_split_flush(ctx);
+    ctx->split_deferred = enable != 0;
+    return st;
+}
+b200_status b200_ctx_row_split_wait(b200_ctx * ctx) {
+    if (!ctx) return fail(B200_ERR_ARG, "null context");
+    return b200_split_flush(ctx);
 }
 
 // ------------------------------------------------------------------------------------------------ memory
@@ -260,16 +285,19 @@ b200_status b200_memset(int device, void * dst, int value, size_t size) {
     return B200_OK;
 }
 b200_status b200_memcpy_h2d_async(b200_ctx * ctx, void * dst, const void * src, size_t size) {
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
     CU(cudaSetDevice(ctx->device));
     CU(cudaMemcpyAsync(dst, src, size, cudaMemcpyHostToDevice, ctx->stream));
     return B200_OK;
 }
 b200_status b200_memcpy_d2h_async(b200_ctx * ctx, void * dst, const void * src, size_t size) {
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
     CU(cudaSetDevice(ctx->device));
     CU(cudaMemcpyAsync(dst, src, size, cudaMemcpyDeviceToHost, ctx->stream));
     return B200_OK;
 }
 b200_status b200_memcpy_d2d_async(b200_ctx * ctx, void * dst, const void * src, size_t size) {
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
     CU(cudaSetDevice(ctx->device));
     CU(cudaMemcpyAsync(dst, src, size, cudaMemcpyDeviceToDevice, ctx->stream));
     return B200_OK;
@@ -288,6 +316,7 @@ b200_status b200_event_destroy(int device, void * event) {
     return B200_OK;
 }
 b200_status b200_event_record(b200_ctx * ctx, void * event) {
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
     CU(cudaSetDevice(ctx->device));
     CU(cudaEventRecord((cudaEvent_t) event, ctx->stream));
     return B200_OK;
@@ -313,6 +342,7 @@ static b200_status quantize_ggml_api(b200_ctx * ctx, int val, int64_t blk, const
     if (k <= 0 || k % blk != 0) return fail(B200_ERR_UNSUPPORTED, "k=%lld is not a multiple of %lld", (long long) k, (long long) blk);
     if (stride % 4 != 0) return fail(B200_ERR_ARG, "row stride must be a multiple of 4 bytes");
     CU(cudaSetDevice(ctx->device));
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
     int l = 0;
     CU(quantize_ggml(val, x, k, nrows, stride, y, ctx->stream, &l));
     ctx->launches += l;
@@ -327,6 +357,7 @@ b200_status b200_quantize_units(b200_ctx * ctx, int kind, const float * x, int64
     if (k <= 0 || k % 256 != 0) return fail(B200_ERR_UNSUPPORTED, "k=%lld is not a multiple of 256", (long long) k);
     if (kind != ACT_KIND_Q8_0 && kind != ACT_KIND_Q8_K) return fail(B200_ERR_ARG, "kind must be 0 or 1");
     CU(cudaSetDevice(ctx->device));
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
     int l = 0;
     CU(quantize_units(kind, x, k, nrows, stride, main, aux, ctx->stream, &l));
     ctx->launches += l;
@@ -444,6 +475,14 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
             p.n_stages = cfg.ns;
             p.pdl      = ctx->pdl;
             p.split    = ctx->split;
+            if (ctx->split.n_ranks > 1) {
+                if (ctx->split_deferred && x) {  // src1 is read inside the kernel, behind its split_wait prologue
+                    p.split.deferred   = 1;
+                    ctx->split_pending = 1;
+                } else if (b200_status st = b200_split_flush(ctx)) {
+                    return st;
+                }
+            }
             if (x) {
                 p.fuse_quant = 1;
                 p.x          = (const float *) ((const char *) x + (size_t) c0 * x_cs);
@@ -503,6 +542,7 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
     bool mmq = ctx->force_path == B200_PATH_MMQ || (ctx->force_path == B200_PATH_AUTO && N >= mmq_min);
     for (int i = 0; i < n_ops && mmq; i++) mmq = b200_mmq_usable(type, K, src0s[i], descs[i].nb01);
     if (mmq) {
+        if (b200_status fst = b200_split_flush(ctx)) return fst;
         for (int i = 0; i < n_ops; i++) {
             const b200_mul_mat_desc & di = descs[i];
             const int64_t r2 = di.ne12 / di.ne02, r3 = di.ne13 / di.ne03;
@@ -529,6 +569,7 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
         const bool fuse = !mma && mv_fuse_quant(ctx, U, N);
         uint8_t * am = nullptr, * ax = nullptr;
         if (!fuse) {
+            if (b200_status fst = b200_split_flush(ctx)) return fst;  // the quantizer launch reads src1 without a split_wait prologue
             const size_t main_b = (size_t) n_rows * U * ACT_MAIN, aux_b = (size_t) n_rows * U * ACT_AUX;
             const size_t aux_o  = (main_b + 255) & ~(size_t) 255;
             b200_status  st     = ensure(ctx, &ctx->scratch, &ctx->scratch_size, aux_o + aux_b);
@@ -570,6 +611,7 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
         return B200_OK;
     }
 
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
     // generic path: reference block layout for the activations, one warp per row
     const int    val    = type == B200_TYPE_Q4_K ? 1 : 0;
     const size_t act_rs = type == B200_TYPE_Q4_K ? (size_t) (K / QK_K) * SZ_Q8_K : (size_t) (K / QK) * SZ_Q8_0;

@@ -43,6 +43,8 @@ struct b200_ctx {
     int          weight_cache = 0;             // keep the int8 expansion of a weight matrix across calls (owner must invalidate)
     int          mmq_min_cols = 0;             // 0 = auto; GGML_B200_MMQ_MIN
     b200::SplitParams split = {};              // row-split all-gather fused into the kernels (b200_ctx_set_row_split)
+    int          split_deferred = 0;           // mat-vec kernels publish their epoch and let the NEXT launch wait (b200_ctx_set_row_split_deferred)
+    int          split_pending  = 0;           // a deferred kernel was launched and nothing has waited for the peers since
     int          fuse_quant = 1;               // quantize src1 inside the mat-vec kernel when small; GGML_B200_FUSE_QUANT=0 disables
     // cross-kernel weight prefetch (kernels.h MvNext): the launch that followed a weight tensor last time is assumed to follow
     // it again (decode repeats the same graph every token). Keyed by the first weight pointer of a launch.
@@ -63,6 +65,10 @@ struct b200_ctx {
 // bumped whenever device memory the library may hold predictions / caches for is freed or rewritten
 uint64_t b200_mem_generation();
 void     b200_mem_generation_bump();
+
+// row split, deferred mode: enqueue the wait for the peers (a one-warp kernel) if a deferred kernel is outstanding. Every entry
+// point that reads a dst, synchronizes, or launches a kernel without a split_wait prologue calls this first.
+b200_status b200_split_flush(b200_ctx * ctx);
 
 // grow-only device buffer owned by the context (fails instead of reallocating while the stream is being captured)
 b200_status b200_ensure(b200_ctx * ctx, void ** buf, size_t * cur, size_t need);

@@ -42,7 +42,30 @@ struct SplitParams {
     int64_t    dst_delta[SPLIT_MAX_RANKS];    // bytes from a local dst address to the same element on rank r (0 for own rank)
     uint32_t * sync_local;                    // [0..7] flags written by the peers, [8] epoch, [9] CTA counter
     uint32_t * sync_peer[SPLIT_MAX_RANKS];    // rank r's sync words
+    int        deferred;                      // 1: publish the epoch but do not wait for the peers here - the next kernel of the
+                                              // stream (split_wait in its prologue) or b200_ctx_row_split_wait does
 };
+
+// waits until every peer has published the epoch this rank is at (all of their slices of every earlier dst have arrived).
+// Called by one warp after the stream dependency is resolved (the local epoch is final then).
+__device__ __forceinline__ void split_wait(const SplitParams & sp) {
+    const int lane = threadIdx.x & 31;
+    if (lane < sp.n_ranks && lane != sp.rank) {
+        uint32_t e, v;
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(e) : "l"(sp.sync_local + 8) : "memory");
+        uint64_t t0 = 0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (unsigned spins = 1;; spins++) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(sp.sync_local + lane) : "memory");
+            if ((int32_t) (v - e) >= 0) break;
+            if ((spins & 0xfff) == 0) {
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 5000000000ull) __trap();
+            }
+        }
+    }
+    __syncwarp();
+}
 
 __device__ __forceinline__ void split_store(const SplitParams & sp, float * addr, float v) {
     if (sp.n_ranks <= 1) {
@@ -52,20 +75,21 @@ __device__ __forceinline__ void split_store(const SplitParams & sp, float * addr
     }
 }
 
-// called by ONE warp of every CTA after a CTA barrier that follows all of the CTA's stores. One system-scope fence per CTA
-// (not per thread: thousands of concurrent membar.sys were the dominant cost of the exchange): the barrier orders the other
-// threads' peer stores before lane 0's fence, the fence is cumulative, so they are visible system-wide before the counter and,
-// through the last CTA's fence + release store, before the flag.
+// called by ONE warp of every CTA after a CTA barrier that follows all of the CTA's stores. membar.sys is expensive (microseconds,
+// and worse when thousands run concurrently), so there is exactly ONE per kernel: every CTA orders its stores before the counter
+// with a device-scope fence (the CTA barrier orders the other threads' stores before lane 0's fence; fences are cumulative), and
+// the last CTA - which has observed every other CTA's counter increment - issues the system-scope fence before the release store
+// of the flag: everything that happens-before that fence is visible to the peers before the flag.
 __device__ __forceinline__ void split_complete(const SplitParams & sp, unsigned n_ctas) {
     const int lane = threadIdx.x & 31;
     unsigned last = 0;
     if (lane == 0) {
-        __threadfence_system();
+        __threadfence();  // device scope: orders this CTA's (peer) stores before the counter; the last CTA's system fence is cumulative
         last = atomicAdd(&sp.sync_local[9], 1u) == n_ctas - 1 ? 1u : 0u;
     }
     last = __shfl_sync(0xffffffffu, last, 0);
     if (!last) return;
-    __threadfence_system();
+    __threadfence();  // acquire side of the counter; the release.sys store below carries the (single) system-scope fence
     uint32_t e = 0;
     if (lane == 0) {
         e = sp.sync_local[8] + 1;
@@ -78,7 +102,7 @@ __device__ __forceinline__ void split_complete(const SplitParams & sp, unsigned 
         uint32_t v;
         uint64_t t0 = 0, t1;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-        for (unsigned spins = 1;; spins++) {
+        for (unsigned spins = 1; !sp.deferred; spins++) {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(sp.sync_local + lane) : "memory");
             if ((int32_t) (v - e) >= 0) break;
             if ((spins & 0xfff) == 0) {  // a peer that never arrives (crashed rank, mismatched launch sequence) must not hang the GPU

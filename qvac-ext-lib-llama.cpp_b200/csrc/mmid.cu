@@ -73,6 +73,7 @@ b200_status b200_mm_ids_sort(b200_ctx * ctx, const int32_t * ids, int64_t n_used
     if (!ctx || !ids || !sorted_pairs || !expert_bounds) return fail(B200_ERR_ARG, "null argument");
     if (n_as <= 0 || n_as > 8192 || ids_nb1 % 4 != 0 || n_used * n_tok > INT32_MAX) return fail(B200_ERR_UNSUPPORTED, "bad MUL_MAT_ID index geometry");
     CU(cudaSetDevice(ctx->device));
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
     mm_ids_sort_kernel<<<1, 1024, (size_t) (n_as + 1) * sizeof(int), ctx->stream>>>(ids, (int) n_used, (int) n_tok, (int64_t) (ids_nb1 / 4), (int) n_as,
                                                                                   sorted_pairs, expert_bounds);
     CU(cudaGetLastError());
@@ -100,6 +101,7 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
     const int64_t n_pairs = d->n_used * d->n_tok;
     if (n_pairs == 0 || M == 0) return B200_OK;
     CU(cudaSetDevice(ctx->device));
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
 
     MvIds mi;
     mi.ids    = ids;

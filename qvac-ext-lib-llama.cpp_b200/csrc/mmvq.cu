@@ -407,6 +407,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
     griddep_wait();  // everything below reads src1 / writes dst, which earlier kernels of the stream may produce / still read
 
     if (w == 0) MV_TRACE(3);
+    if (p.split.n_ranks > 1 && p.split.deferred) split_wait(p.split);  // src1 may derive from a dst whose remote slices are still in flight
     if (p.fuse_quant) {
         // fused K1: unit (c, u) of the activations, F32 global -> unit record in shared memory. Up to 4 units per warp are
         // loaded before the first is quantized, so the L2 round trips overlap instead of chaining

@@ -21,6 +21,8 @@ def main():
     ap.add_argument("--prefetch-kb", type=int, default=0)
     ap.add_argument("--ncols", type=int, default=1)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--split-selftest", action="store_true", help="row-split epilogue against this same GPU (peer flag pre-armed): local cost of the exchange")
+    ap.add_argument("--deferred", action="store_true")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     import torch
@@ -36,6 +38,13 @@ def main():
         ctx = pkg.Context(0)
         if args.prefetch_kb > 0:
             ctx.prefetch(args.prefetch_kb)
+        if args.split_selftest:
+            sync = torch.zeros(64, dtype=torch.int32, device=device)
+            sync[1] = 0x7FFFFFF0
+            torch.cuda.synchronize()
+            dummy = torch.zeros(16, dtype=torch.float32, device=device)
+            ctx.row_split(0, [dummy.data_ptr(), dummy.data_ptr()], [sync.data_ptr(), sync.data_ptr() + 128])
+            ctx.row_split_deferred(args.deferred)
         ops = bench.build_stack(torch, m, args.type, args.ncols, 1, 0, device)
         groups = bench.group_ops(ops)
 

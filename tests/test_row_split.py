@@ -124,8 +124,9 @@ def test_two_rank_slices_gather_to_the_whole_product(split):
 # ---------------------------------------------------------------- GPU: the fused exchange epilogue
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("t,N", [(Q4_K, 1), (Q4_0, 2), (Q8_0, 1), (Q4_K, 40), (Q8_0, 64)])
-def test_fused_exchange_writes_every_destination(pkg, oracle, t, N):
+@pytest.mark.parametrize("deferred", [False, True])
+@pytest.mark.parametrize("t,N", [(Q4_K, 1), (Q4_0, 2), (Q8_0, 1), (Q4_K, 5), (Q4_K, 40), (Q8_0, 64)])
+def test_fused_exchange_writes_every_destination(pkg, oracle, t, N, deferred):
     """rank 0 of a 2-rank split whose 'peer' dst is a second buffer on the same GPU and whose peer flag is already at the far
     epoch (nothing spins): the kernel must store every value into both destinations, bump its epoch, reset its CTA counter and
     publish the epoch into the peer's flag slot. Mat-vec (N <= 8) and tensor-core (N > 8) kernels."""
@@ -158,9 +159,11 @@ def test_fused_exchange_writes_every_destination(pkg, oracle, t, N):
         peer = base + 4 * N * M
         s0, s1 = base + 8 * N * M, base + 8 * N * M + 128
         c.row_split(0, [base, peer], [s0, s1])
+        c.row_split_deferred(deferred)       # deferred: the wait for the peers is a separate step (next kernel / row_split_wait)
         out = pool[:N * M].view(N, M)
         for rep in range(3):
             c.mul_mat(t, cu(W), cu(X), out=out)
+            c.row_split_wait()
             torch.cuda.synchronize()
             assert np.array_equal(out.cpu().numpy(), ref)
             assert np.array_equal(pool[N * M:2 * N * M].view(N, M).cpu().numpy(), ref)
