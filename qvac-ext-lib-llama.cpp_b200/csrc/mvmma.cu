@@ -49,6 +49,12 @@ __device__ __forceinline__ void mma_u8s8(int (&c)[4], uint32_t a0, uint32_t a1, 
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0), "r"(0), "r"(0), "r"(0));
 }
 
+__device__ __forceinline__ void mma_s8s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
+                 : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0), "r"(0), "r"(0), "r"(0));
+}
+
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const void * tmap, int c0, int c1, int c2, uint32_t bar) {
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
@@ -147,9 +153,52 @@ __device__ __forceinline__ void unit_mma_q4_0(uint32_t wt, uint32_t am, uint32_t
     }
 }
 
+// q8_0: 8 blocks of { half d; int8 qs[32] } = 272 B per unit; a block pair is 68 bytes = 17 words: the even block's qs is shifted
+// by 16 bits against the word grid, the odd block's is word aligned. sumi * (d_w * d_y) per block (ggml-cpu/quants.c:329)
+__device__ __forceinline__ void unit_mma_q8_0(uint32_t wt, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, int g, int t, float (&acc)[4]) {
+    (void) ax; (void) cs_x;
+    const uint32_t r0 = wt + g * 272, r1 = r0 + 8 * 272;
+    const uint32_t bcol = am + g * cs_m + 4 * t;
+    const uint4 dy0 = lds128(am + (2 * t) * cs_m + 256), dy1 = lds128(am + (2 * t + 1) * cs_m + 256);
+#pragma unroll
+    for (int bp = 0; bp < 4; bp++) {
+        const uint32_t p0 = r0 + 68 * bp, p1 = r1 + 68 * bp;
+#pragma unroll
+        for (int ob = 0; ob < 2; ob++) {
+            const int b = 2 * bp + ob;
+            uint32_t a0, a1, a2, a3;
+            float dw0, dw1;
+            if (ob == 0) {  // qs word k = bytes 2 + 4k .. 5 + 4k of the pair = funnel(word k, word k + 1) >> 16
+                const uint32_t x0 = lds32(p0 + 4 * t), x1 = lds32(p0 + 4 * t + 4), x2 = lds32(p0 + 16 + 4 * t), x3 = lds32(p0 + 20 + 4 * t);
+                const uint32_t y0 = lds32(p1 + 4 * t), y1 = lds32(p1 + 4 * t + 4), y2 = lds32(p1 + 16 + 4 * t), y3 = lds32(p1 + 20 + 4 * t);
+                a0 = __funnelshift_r(x0, x1, 16); a2 = __funnelshift_r(x2, x3, 16);
+                a1 = __funnelshift_r(y0, y1, 16); a3 = __funnelshift_r(y2, y3, 16);
+                dw0 = half_bits_to_float((uint16_t) (lds32(p0) & 0xffff));
+                dw1 = half_bits_to_float((uint16_t) (lds32(p1) & 0xffff));
+            } else {        // odd block at +34: d in the high half of word 8, qs from word 9 on
+                a0 = lds32(p0 + 36 + 4 * t); a2 = lds32(p0 + 52 + 4 * t);
+                a1 = lds32(p1 + 36 + 4 * t); a3 = lds32(p1 + 52 + 4 * t);
+                dw0 = half_bits_to_float((uint16_t) (lds32(p0 + 32) >> 16));
+                dw1 = half_bits_to_float((uint16_t) (lds32(p1 + 32) >> 16));
+            }
+            const uint32_t b0 = lds32(bcol + 32 * b), b1 = lds32(bcol + 32 * b + 16);
+            int c[4];
+            mma_s8s8(c, a0, a1, a2, a3, b0, b1);
+            const uint32_t dwd0 = b < 2 ? dy0.x : b < 4 ? dy0.y : b < 6 ? dy0.z : dy0.w, dwd1 = b < 2 ? dy1.x : b < 4 ? dy1.y : b < 6 ? dy1.z : dy1.w;
+            const float y0f = half_bits_to_float((uint16_t) ((b & 1) ? dwd0 >> 16 : dwd0 & 0xffff));
+            const float y1f = half_bits_to_float((uint16_t) ((b & 1) ? dwd1 >> 16 : dwd1 & 0xffff));
+            acc[0] = fmaf((float) c[0], dw0 * y0f, acc[0]);
+            acc[1] = fmaf((float) c[1], dw0 * y1f, acc[1]);
+            acc[2] = fmaf((float) c[2], dw1 * y0f, acc[2]);
+            acc[3] = fmaf((float) c[3], dw1 * y1f, acc[3]);
+        }
+    }
+}
+
 template <int TYPE>
 __device__ __forceinline__ void unit_mma(uint32_t wt, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, int g, int t, float (&acc)[4]) {
     if (TYPE == B200_TYPE_Q4_K) unit_mma_q4_K(wt, am, ax, cs_m, cs_x, g, t, acc);
+    else if (TYPE == B200_TYPE_Q8_0) unit_mma_q8_0(wt, am, ax, cs_m, cs_x, g, t, acc);
     else unit_mma_q4_0(wt, am, ax, cs_m, cs_x, g, t, acc);
 }
 
@@ -353,9 +402,23 @@ size_t mv_mma_smem(int type, int U, int n_cons, int n_stages) {
     return off + (size_t) n_stages * n_cons * MMA_ROWS * unit_bytes(type) + 1024;
 }
 
-bool mv_mma_usable(int type) { return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0) && mma_get_encode() != nullptr; }
+bool mv_mma_usable(int type) {
+    return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0) && mma_get_encode() != nullptr;
+}
 
 } // namespace b200
+
+static b200_status mma_set_attr(b200_ctx * ctx, int type) {
+    static bool done[3][64] = {};
+    const int ti = type == B200_TYPE_Q4_K ? 0 : type == B200_TYPE_Q4_0 ? 1 : 2;
+    if (ctx->device < 64 && !done[ti][ctx->device]) {
+        if (ti == 0)      CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        else if (ti == 1) CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q4_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        else              CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q8_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        done[ti][ctx->device] = true;
+    }
+    return B200_OK;
+}
 
 // host: n_ops matrices (same type, K) against `ncols` pre-quantized activation columns
 b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, const uint8_t * const * ws, const size_t * nb01s, const int64_t * Ms,
@@ -413,13 +476,7 @@ b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, cons
         p.act_main = act_main; p.act_aux = act_aux;
         p.split = ctx->split;
         const int grid = tiles < ctx->sm_count ? tiles : ctx->sm_count;
-        static bool attr_done[2][64] = {};
-        const int ti = type == B200_TYPE_Q4_K ? 0 : 1;
-        if (ctx->device < 64 && !attr_done[ti][ctx->device]) {
-            if (ti == 0) CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-            else         CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q4_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-            attr_done[ti][ctx->device] = true;
-        }
+        if (b200_status ast = mma_set_attr(ctx, type)) return ast;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim          = dim3(grid);
         cfg.blockDim         = dim3(32 * (n_cons + 1));
@@ -430,8 +487,9 @@ b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, cons
         attr[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs    = attr;
         cfg.numAttrs = p.pdl ? 1 : 0;
-        if (ti == 0) CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_K>, maps, p));
-        else         CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_0>, maps, p));
+        if (type == B200_TYPE_Q4_K)      CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_K>, maps, p));
+        else if (type == B200_TYPE_Q8_0) CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q8_0>, maps, p));
+        else                             CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_0>, maps, p));
         ctx->launches++;
     }
     return B200_OK;
@@ -484,13 +542,7 @@ b200_status b200_mv_mma_run_ids(b200_ctx * ctx, int type, int64_t K, const uint8
     int per_expert = (int) (ctx->sm_count / n_as);
     if (per_expert < 1) per_expert = 1;
     if (per_expert > p.total_tiles) per_expert = p.total_tiles;
-    static bool attr_done[2][64] = {};
-    const int ti = type == B200_TYPE_Q4_K ? 0 : 1;
-    if (ctx->device < 64 && !attr_done[ti][ctx->device]) {
-        if (ti == 0) CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        else         CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q4_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_done[ti][ctx->device] = true;
-    }
+    if (b200_status ast = mma_set_attr(ctx, type)) return ast;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim          = dim3(per_expert, (unsigned) n_as);
     cfg.blockDim         = dim3(32 * (n_cons + 1));
@@ -501,8 +553,9 @@ b200_status b200_mv_mma_run_ids(b200_ctx * ctx, int type, int64_t K, const uint8
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs    = attr;
     cfg.numAttrs = p.pdl ? 1 : 0;
-    if (ti == 0) CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_K>, maps, p));
-    else         CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_0>, maps, p));
+    if (type == B200_TYPE_Q4_K)      CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_K>, maps, p));
+    else if (type == B200_TYPE_Q8_0) CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q8_0>, maps, p));
+    else                             CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_0>, maps, p));
     ctx->launches++;
     return B200_OK;
 }
