@@ -206,6 +206,13 @@ B200_API void         b200_weight_cache_invalidate(int device, const void * base
 B200_API void         b200_weight_cache_clear(int device);
 B200_API size_t       b200_weight_cache_bytes(void);
 
+/* Prefill arithmetic (more than 8 activation columns). enable = 1 (default; env GGML_B200_MMQ_F16): tcgen05 kind::f16 GEMM on
+ * fp16 operands that carry the block scales (weights: dequantize_row_<type> rounded to fp16; activations: the bit-exact
+ * q8_0 / q8_K quantization, dequantized, times a per-row power of two, rounded to fp16) with one fp32 accumulation over K:
+ * NMSE against the CPU reference about 1e-7. enable = 0: tcgen05 kind::i8 with an exact int32 sum per 32-block scaled in
+ * fp32 (the arithmetic of ggml_cuda_mul_mat_q, ggml-cuda/mmq.cu:70-236), about three times slower. */
+B200_API void         b200_ctx_set_mmq_f16(b200_ctx * ctx, int enable);
+
 /* Cross-kernel weight prefetch for decode. A token step is a dependent chain of short mat-vec kernels; at every kernel
  * boundary HBM idles for the launch / dependency / drain latency (~3 us, as long as a 4096x4096 q4 matrix takes to stream).
  * With prefetch on, a context remembers which launch followed each weight tensor the last time (decode replays the same

@@ -31,7 +31,7 @@ EXPORTS = [
     "b200_event_create", "b200_event_destroy", "b200_event_record", "b200_event_wait", "b200_event_synchronize",
     "b200_event_elapsed_ms", "b200_quantize_q8_0", "b200_quantize_q8_1", "b200_quantize_q8_K", "b200_quantize_units",
     "b200_mul_mat_supported", "b200_mul_mat", "b200_mul_mat_shared_src1", "b200_mul_mat_host", "b200_mul_mat_id_supported",
-    "b200_mul_mat_id", "b200_mm_ids_sort", "b200_ctx_set_row_split", "b200_ctx_set_row_split_deferred", "b200_ctx_row_split_wait", "b200_ctx_set_weight_cache", "b200_ctx_set_prefetch", "b200_ctx_trace", "b200_ctx_trace_read", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
+    "b200_mul_mat_id", "b200_mm_ids_sort", "b200_ctx_set_row_split", "b200_ctx_set_row_split_deferred", "b200_ctx_row_split_wait", "b200_ctx_set_weight_cache", "b200_ctx_set_mmq_f16", "b200_ctx_set_prefetch", "b200_ctx_trace", "b200_ctx_trace_read", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
 ]
 
 
@@ -145,6 +145,8 @@ def lib() -> C.CDLL:
         L.b200_ctx_set_row_split.argtypes = [vp, C.POINTER(RowSplit)]
         L.b200_ctx_set_weight_cache.argtypes = [vp, ci]
         L.b200_ctx_set_weight_cache.restype = None
+        L.b200_ctx_set_mmq_f16.argtypes = [vp, ci]
+        L.b200_ctx_set_mmq_f16.restype = None
         L.b200_ctx_set_row_split_deferred.argtypes = [vp, ci]
         L.b200_ctx_row_split_wait.argtypes = [vp]
         L.b200_ctx_set_prefetch.argtypes = [vp, ci]
@@ -227,6 +229,10 @@ class Context:
     def weight_cache(self, enable: bool):
         """keep int8 expansions of weight matrices across calls; the caller must invalidate ranges it overwrites or frees"""
         lib().b200_ctx_set_weight_cache(self.h, 1 if enable else 0)
+
+    def mmq_f16(self, enable: bool):
+        """prefill arithmetic: True = kind::f16 GEMM on scale-carrying fp16 operands (default), False = exact per-block kind::i8"""
+        lib().b200_ctx_set_mmq_f16(self.h, 1 if enable else 0)
 
     def prefetch(self, kb_per_cta=32):
         """cross-kernel weight prefetch for decode (b200_ctx_set_prefetch); 0 switches it off"""

@@ -119,6 +119,7 @@ b200_status b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     if (const char * s = getenv("GGML_B200_MMA_MIN")) c->mma_min_cols = atoi(s);
     if (const char * s = getenv("GGML_B200_MMA_WARPS")) c->mma_warps = atoi(s);
     if (const char * s = getenv("GGML_B200_MOE_GROUP_MIN")) c->moe_group_min = atoi(s);
+    if (const char * s = getenv("GGML_B200_MMQ_F16")) c->mmq_f16 = atoi(s) != 0;
     *out = c;
     return B200_OK;
 }
@@ -130,6 +131,7 @@ void b200_ctx_destroy(b200_ctx * ctx) {
     if (ctx->scratch) cudaFree(ctx->scratch);
     if (ctx->io) cudaFree(ctx->io);
     if (ctx->scratch2) cudaFree(ctx->scratch2);
+    if (ctx->scratch3) cudaFree(ctx->scratch3);
     if (ctx->trace) cudaFree(ctx->trace);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -140,6 +142,7 @@ void *       b200_ctx_stream(const b200_ctx * ctx) { return (void *) ctx->stream
 uint64_t     b200_ctx_launch_count(const b200_ctx * ctx) { return ctx->launches; }
 void         b200_ctx_set_force_path(b200_ctx * ctx, int path) { ctx->force_path = path; }
 void         b200_ctx_set_weight_cache(b200_ctx * ctx, int enable) { ctx->weight_cache = enable != 0; }
+void         b200_ctx_set_mmq_f16(b200_ctx * ctx, int enable) { ctx->mmq_f16 = enable != 0; }
 b200_status  b200_ctx_trace(b200_ctx * ctx, int n_slots) {
     CU(cudaSetDevice(ctx->device));
     if (ctx->trace) {
@@ -582,7 +585,7 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
                     const int64_t b = i13 * d.ne12 + i12;
                     int l = 0;
                     CU(quantize_units(kind, (const float *) ((const char *) src1 + i12 * d.nb12 + i13 * d.nb13), K, N, d.nb11,
-                                      am + (size_t) b * N * U * ACT_MAIN, ax + (size_t) b * N * U * ACT_AUX, ctx->stream, &l));
+                                      am + (size_t) b * N * U * ACT_MAIN, ax + (size_t) b * N * U * ACT_AUX, ctx->stream, &l, ctx->pdl));
                     ctx->launches += l;
                 }
         }

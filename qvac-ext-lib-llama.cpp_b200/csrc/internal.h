@@ -38,6 +38,8 @@ struct b200_ctx {
     // second scratch: MoE index tables, tcgen05 activation tiles
     void *       scratch2      = nullptr;
     size_t       scratch2_size = 0;
+    void *       scratch3      = nullptr;      // stream-K workspace of the fp16 prefill GEMM: flags + partial accumulators
+    size_t       scratch3_size = 0;
     int          mv_warps = 0, mv_stages = 0;  // 0 = auto; GGML_B200_MV_WARPS / GGML_B200_MV_STAGES
     int          pdl        = 1;               // programmatic dependent launch of the mat-vec kernels; GGML_B200_PDL=0 disables
     int          weight_cache = 0;             // keep the int8 expansion of a weight matrix across calls (owner must invalidate)
@@ -58,6 +60,7 @@ struct b200_ctx {
     int          dbg = 0;                      // GGML_B200_DBG: experiment switches handed to the kernels
     int          mma_min_cols = 3;             // columns from which the IMMA mat-vec kernel (mvmma.cu) replaces the dp4a one; GGML_B200_MMA_MIN
     int          mma_warps = 0;                // 0 = auto; GGML_B200_MMA_WARPS
+    int          mmq_f16 = 1;                  // prefill GEMM on kind::f16 with the block scales folded into fp16 operands (mmf16.cuh); 0: kind::i8
     int          moe_group_min = 2;            // MUL_MAT_ID: group by expert (tensor-core mat-vec) from this many pairs per expert on
                                                // average; 0 = never; GGML_B200_MOE_GROUP_MIN
 };

@@ -1,0 +1,560 @@
+// mmf16.cuh — K5: prefill GEMM on tcgen05.mma kind::f16 (SASS UTCHMMA) with ONE fp32 accumulation over the whole K in TMEM.
+// Included by mmq.cu (inside its anonymous namespace: shares make_map and the weight cache).
+//
+// Why a second tensor-core path: the kind::i8 kernels of mmq.cu keep the reference's per-32-block structure (an int32 dot
+// product per block, scaled in fp32 by the epilogue warps). That epilogue costs M*N*K/32 I2F + FMUL + FFMA and is what bounds
+// them (profiles/r01_pass7_mmq_q4k_full.md: imma pipe 26 %). Here the block scales are folded into the OPERANDS instead:
+//   A[m][k] = fp16( dequantize_row_<type>(W)[m][k] )                     (ggml-quants.c:307-325, 359-372, 1352-1374)
+//   B[n][k] = fp16( 2^-e[n] * d_a[n][k/32|k/256] * q_a[n][k] )           (q_a, d_a: bit-exact quantize_row_q8_0_ref / q8_K_ref)
+//   dst[n][m] = 2^e[n] * sum_k A[m][k] * B[n][k]                         (fp32 accumulation in TMEM)
+// which is the same sum the CPU reference forms (vec_dot_q4_0_q8_0 / q8_0_q8_0 / q4_K_q8_K factor the block scales out of it),
+// with two roundings to 11 significant bits per product (relative 2^-12 each) in place of exact integer block sums: NMSE
+// against the oracle is about 1e-7 (tests/test_gpu_parity.py states the bound), north_star allows 5e-4. The per-row power of
+// two 2^e[n] brings every activation row's largest magnitude into [2^14, 2^15): no fp16 overflow or subnormals whatever the
+// activation range, and a power of two commutes with the rounding. GGML_B200_MMQ_F16=0 (b200_ctx_set_mmq_f16) selects the
+// exact-block-sum kind::i8 kernels instead.
+//
+// Tiling: CTA tile 128 (M) x BN (N, 256 or 128), K in stages of 64 halfs (= one 128-byte swizzle row), four UTCHMMA
+// 128 x BN x 16 per stage, 2 TMEM accumulator slots of BN columns (the epilogue of one work item overlaps the main loop of the next).
+// Scheduling is stream-K: the launch's tiles x K-stages are cut into gridDim.x equal contiguous spans (one persistent CTA per SM),
+// so every SM is busy for the same time whatever the tile count (wk/wv of Llama-3-8B at n = 512 are 16 tiles). A tile cut by a
+// span boundary is finished deterministically: the CTAs holding its later K-ranges start their span with it, park the partial
+// accumulator in a workspace and raise a flag; the CTA holding the K-range that begins at 0 reaches it last, waits for the flags
+// and adds the partials in ascending K order before it stores the tile (no atomics: results do not depend on timing).
+// Warp roles (384 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 4..11 epilogue.
+// Tried and dropped: clusters of two CTAs sharing the activation tile by TMA multicast (same speed: the SM's ingest, not the
+// L2 read rate, is what a 128 x 256 tile is short of - profiles/README.md).
+
+#include <cuda_fp16.h>
+
+constexpr int F_BM = 128, F_BK = 64;
+constexpr int F_EPI_WARPS = 8, F_FIRST_EPI = 4;
+constexpr int F_THREADS = 32 * (F_FIRST_EPI + F_EPI_WARPS);
+constexpr int F_A_BYTES = F_BM * 128;
+__host__ __device__ constexpr int f_b_bytes(int bn) { return bn * 128; }
+__host__ __device__ constexpr int f_stages(int bn) { return bn == 256 ? 4 : 6; }
+__host__ __device__ constexpr int f_smem(int bn) { return 1024 + f_stages(bn) * (F_A_BYTES + f_b_bytes(bn)) + 256; }
+
+// ---- instruction descriptor for kind::f16: D = f32 ([4,6) = 1), A and B fp16 ([7,10) = [10,13) = 0), both K-major
+__host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N) { return (1u << 4) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (M >> 4) << 24); }
+
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_l2_2d(const void * tmap, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(tmap), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void st_release_gpu(unsigned * p, unsigned v) { asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned * p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long mmf_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *(const uint32_t *) &h;
+}
+
+// ------------------------------------------------------------------------------------------------ weights -> fp16 [M][K]
+
+// one thread per 32-element block: the values dequantize_row_q4_0 / q8_0 / q4_K produce (fp32), rounded to fp16
+template <int TYPE>
+__global__ void __launch_bounds__(256) expand_f16_kernel(const uint8_t * __restrict__ w, int64_t nb01, int64_t M, int64_t K, __half * __restrict__ h) {
+    const int64_t KB  = K / 32;
+    const int64_t idx = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= M * KB) return;
+    const int64_t row = idx / KB, kb = idx - row * KB;
+    const uint8_t * wr = w + row * nb01;
+    float v[32];
+    if (TYPE == B200_TYPE_Q4_0) {
+        const uint8_t * b = wr + kb * SZ_Q4_0;
+        const float d = half_bits_to_float(*(const uint16_t *) b);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t x = ld16x2(b + 2 + 4 * i);
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                v[4 * i + j]      = (float) ((int) ((x >> (8 * j)) & 0xf) - 8) * d;
+                v[16 + 4 * i + j] = (float) ((int) ((x >> (8 * j + 4)) & 0xf) - 8) * d;
+            }
+        }
+    } else if (TYPE == B200_TYPE_Q8_0) {
+        const uint8_t * b = wr + kb * SZ_Q8_0;
+        const float d = half_bits_to_float(*(const uint16_t *) b);
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const uint32_t x = ld16x2(b + 2 + 4 * i);
+#pragma unroll
+            for (int j = 0; j < 4; j++) v[4 * i + j] = (float) (int) (int8_t) (x >> (8 * j)) * d;
+        }
+    } else {
+        const uint8_t * b = wr + (kb >> 3) * SZ_Q4_K;
+        const int j = (int) (kb & 7);
+        const uint32_t hdr = *(const uint32_t *) b;
+        const float d = half_bits_to_float((uint16_t) (hdr & 0xffff)), dmin = half_bits_to_float((uint16_t) (hdr >> 16));
+        const uint8_t * s = b + 4;
+        int scv, mv;
+        if (j < 4) {
+            scv = s[j] & 63;
+            mv  = s[j + 4] & 63;
+        } else {
+            scv = (s[j + 4] & 0xF) | ((s[j - 4] >> 6) << 4);
+            mv  = (s[j + 4] >> 4) | ((s[j] >> 6) << 4);
+        }
+        const float d1 = __fmul_rn(d, (float) scv), m1 = __fmul_rn(dmin, (float) mv);  // dequantize_row_q4_K: y = d1 * q - m1
+        const uint4 * qs = (const uint4 *) (b + 16 + 32 * (j >> 1));
+        const uint4 a = qs[0], c = qs[1];
+        const uint32_t x[8] = { a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w };
+        const int sh = (j & 1) ? 4 : 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+#pragma unroll
+            for (int l = 0; l < 4; l++) v[4 * i + l] = __fsub_rn(__fmul_rn(d1, (float) ((x[i] >> (8 * l + sh)) & 0xf)), m1);
+        }
+    }
+    uint4 * dst = (uint4 *) (h + row * K + kb * 32);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        dst[i] = make_uint4(pack_h2(v[8 * i], v[8 * i + 1]), pack_h2(v[8 * i + 2], v[8 * i + 3]), pack_h2(v[8 * i + 4], v[8 * i + 5]),
+                            pack_h2(v[8 * i + 6], v[8 * i + 7]));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ activations -> fp16 [N][K]
+
+// one CTA per activation row: (1) the row's largest magnitude -> the power of two that normalises it, (2) per 256-element unit
+// the bit-exact q8_0 / q8_K quantization, dequantized (q * d), pre-scaled and rounded to fp16. rs[n] = 2^e[n] for the epilogue.
+// UPW > 0: a warp keeps its UPW units of the row in registers between the two steps (rows of up to 2048 * UPW floats: one
+// trip to memory); UPW = 0: any row length, the row is read twice.
+template <int KIND, int UPW>
+__global__ void __launch_bounds__(256) act_f16_kernel(const float * __restrict__ x, int64_t K, size_t x_rs, __half * __restrict__ h,
+                                                      float * __restrict__ rs, int vec_ok) {
+    __shared__ float s_amax[8];
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // the GEMM's set-up may start; it waits for this grid before it reads h
+    asm volatile("griddepcontrol.wait;" ::: "memory");               // x is the previous kernel's output; h / rs are still read by the previous GEMM
+    const int     lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t n     = blockIdx.x;
+    const int64_t units = (K + UNIT_ELEMS - 1) / UNIT_ELEMS;
+    const float * xr = (const float *) ((const char *) x + n * x_rs);
+    constexpr int NV = UPW > 0 ? UPW : 1;
+
+    auto load = [&](int64_t unit, float (&v)[8]) -> bool {
+        const int64_t e0 = unit * UNIT_ELEMS + lane * 8;
+        if (unit >= units || e0 >= K) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = 0.0f;
+            return false;
+        }
+        if (vec_ok) {
+            const float4 a = __ldg((const float4 *) (xr + e0));
+            const float4 b = __ldg((const float4 *) (xr + e0) + 1);
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+            v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = __ldg(xr + e0 + i);
+        }
+        return true;
+    };
+
+    float keep[NV][8];
+    bool  act[NV];
+    float amax = 0.0f;
+    if (UPW > 0) {
+#pragma unroll
+        for (int i = 0; i < NV; i++) {
+            act[i] = load(warp + 8 * i, keep[i]);
+#pragma unroll
+            for (int j = 0; j < 8; j++) amax = fmaxf(amax, fabsf(keep[i][j]));  // NaN-ignoring, like the quantizers' own amax
+        }
+    } else {
+        for (int64_t u = warp; u < units; u += 8) {
+            load(u, keep[0]);
+#pragma unroll
+            for (int j = 0; j < 8; j++) amax = fmaxf(amax, fabsf(keep[0][j]));
+        }
+    }
+    amax = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(amax)));
+    if (lane == 0) s_amax[warp] = amax;
+    __syncthreads();
+    amax = s_amax[0];
+#pragma unroll
+    for (int i = 1; i < 8; i++) amax = fmaxf(amax, s_amax[i]);
+    // 2^e with amax * 2^-e in [2^14, 2^15); e clamped so that both powers stay normal floats
+    int e = (int) ((__float_as_uint(amax) >> 23) & 0xff) - 127 - 14;
+    if (amax == 0.0f || !(amax < INFINITY)) e = 0;
+    e = max(-100, min(100, e));
+    const float pre = __uint_as_float((uint32_t) (127 - e) << 23);
+    if (threadIdx.x == 0) rs[n] = __uint_as_float((uint32_t) (127 + e) << 23);
+
+    auto emit = [&](int64_t u, const float (&v)[8], bool active) {
+        uint32_t w0, w1;
+        float    d;
+        if (KIND == ACT_KIND_Q8_0) {
+            const Q80Lane r = quant_lane_q8_0(v);
+            w0 = r.w0; w1 = r.w1;
+            d  = __half2float(__float2half_rn(r.d));  // the dot product reads the stored fp16 scale
+        } else {
+            const Q8KLane r = quant_lane_q8_K(v, lane);
+            w0 = r.w0; w1 = r.w1;
+            d  = r.d;
+        }
+        if (!active) return;
+        float f[8];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            f[i]     = __fmul_rn(__fmul_rn((float) (int) (int8_t) (w0 >> (8 * i)), d), pre);
+            f[4 + i] = __fmul_rn(__fmul_rn((float) (int) (int8_t) (w1 >> (8 * i)), d), pre);
+        }
+        *(uint4 *) (h + n * K + u * UNIT_ELEMS + lane * 8) = make_uint4(pack_h2(f[0], f[1]), pack_h2(f[2], f[3]), pack_h2(f[4], f[5]), pack_h2(f[6], f[7]));
+    };
+    if (UPW > 0) {
+#pragma unroll
+        for (int i = 0; i < NV; i++) {
+            if (warp + 8 * i < units) emit(warp + 8 * i, keep[i], act[i]);  // warp-uniform
+        }
+    } else {
+        for (int64_t u = warp; u < units; u += 8) {
+            const bool active = load(u, keep[0]);
+            emit(u, keep[0], active);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ the GEMM (K5)
+
+struct MmfParams {
+    SplitParams   split;
+    float *       dst;
+    int64_t       ldc;  // floats between dst columns (tokens)
+    const float * rs;   // [N] 2^e[n]
+    int           M, N, K;
+    int           n_tiles, k_stages;
+    long long     units;   // tiles x k_stages
+    float *       ws;      // [gridDim.x][BN][128] partial accumulators of cut tiles
+    unsigned *    flags;   // [gridDim.x] 1 = CTA c's partial is in ws (reset by its reader)
+    unsigned long long * trace;  // debug timeline (b200_ctx_trace): 8 x u64 per CTA
+    int           pf;      // L2 prefetch distance of the weight tiles in stages (0 = off)
+    int           early_a;      // the weight tiles may be requested before the stream dependency resolves
+    int           whole_tiles;  // spans end on tile boundaries (no cut tiles; GGML_B200_MMF_STREAMK=0)
+};
+
+#define MMF_TRACE(i) do { if (p.trace) p.trace[(size_t) blockIdx.x * 8 + (i)] = mmf_ns(); } while (0)
+
+template <int BN>
+__global__ void __launch_bounds__(F_THREADS, 1)
+mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const MmfParams p) {
+    constexpr int STAGES = f_stages(BN), SLOTS = 2;
+    constexpr int B_BYTES = f_b_bytes(BN), STAGE_BYTES = F_A_BYTES + B_BYTES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t * smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
+    uint64_t * bars      = (uint64_t *) (smem + STAGES * STAGE_BYTES);
+    uint64_t * full      = bars;               // [STAGES]  TMA -> MMA
+    uint64_t * empty     = bars + STAGES;      // [STAGES]  MMA commit -> TMA
+    uint64_t * tfull     = bars + 2 * STAGES;  // [SLOTS]   MMA commit -> epilogue
+    uint64_t * tempty    = tfull + SLOTS;      // [SLOTS]   epilogue warps -> MMA
+    uint32_t * tmem_slot = (uint32_t *) (tempty + SLOTS);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int KS = p.k_stages;
+    // this CTA's span of the launch's tile-major (tile, K-stage) units
+    const long long u_begin = p.whole_tiles ? (p.units / KS * blockIdx.x / gridDim.x) * KS : p.units * blockIdx.x / gridDim.x;
+    const long long u_end   = p.whole_tiles ? (p.units / KS * (blockIdx.x + 1) / gridDim.x) * KS : p.units * (blockIdx.x + 1) / gridDim.x;
+
+    if (threadIdx.x == 0) {
+        MMF_TRACE(0);
+        for (int i = 0; i < STAGES; i++) {
+            mbar_init(smem_u32(full + i), 1);
+            mbar_init(smem_u32(empty + i), 1);
+        }
+        for (int i = 0; i < SLOTS; i++) {
+            mbar_init(smem_u32(tfull + i), 1);
+            mbar_init(smem_u32(tempty + i), F_EPI_WARPS);
+        }
+        fence_mbar_init();
+        tma_prefetch_desc(&map_a);
+        tma_prefetch_desc(&map_b);
+    }
+    if (warp == 1) tmem_alloc<SLOTS * BN>(smem_u32(tmem_slot));
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (threadIdx.x == 0) MMF_TRACE(1);
+
+    // one (tile, K-stage) unit after the other of this CTA's span
+    struct Cursor {
+        long long u;
+        int       ks, k1, m0, n0;
+    };
+    auto open_item = [&](Cursor & c) {
+        const int tile = (int) (c.u / KS);
+        c.ks = (int) (c.u - (long long) tile * KS);
+        c.k1 = (int) min((long long) KS, c.ks + (u_end - c.u));
+        c.m0 = (tile / p.n_tiles) * F_BM;
+        c.n0 = (tile % p.n_tiles) * BN;
+    };
+    auto step = [&](Cursor & c) {
+        c.u++;
+        if (++c.ks == c.k1 && c.u < u_end) open_item(c);
+    };
+
+    if (warp == 0) {
+        // ================================================================ TMA producer
+        if (lane == 0) {
+            Cursor c;
+            c.u = u_begin;
+            if (c.u < u_end) open_item(c);
+            // the weights do not depend on the stream: the first ring of weight tiles is requested before the dependency resolves
+            if (!p.early_a) asm volatile("griddepcontrol.wait;" ::: "memory");  // the fp16 weights were written on this stream just now
+            Cursor ca = c;
+            int npre = 0;
+            for (; npre < STAGES && ca.u < u_end; npre++, step(ca)) {
+                const uint32_t bar = smem_u32(full + npre);
+                mbar_expect_tx(bar, STAGE_BYTES);
+                tma_load_2d(smem_u32(smem + npre * STAGE_BYTES), &map_a, ca.ks * F_BK, ca.m0, bar);
+            }
+            MMF_TRACE(2);
+            if (p.early_a) asm volatile("griddepcontrol.wait;" ::: "memory");  // the activations are the previous kernel's output
+            for (int i = 0; i < npre; i++, step(c)) {
+                tma_load_2d(smem_u32(smem + i * STAGE_BYTES) + F_A_BYTES, &map_b, c.ks * F_BK, c.n0, smem_u32(full + i));
+            }
+            int stage = npre == STAGES ? 0 : npre; uint32_t phase = npre == STAGES ? 0 : 1;
+            for (; c.u < u_end; step(c)) {
+                if (p.pf > 0 && c.ks + p.pf < c.k1) tma_prefetch_l2_2d(&map_a, (c.ks + p.pf) * F_BK, c.m0);
+                mbar_wait(smem_u32(empty + stage), phase);
+                const uint32_t bar = smem_u32(full + stage);
+                const uint32_t st  = smem_u32(smem + stage * STAGE_BYTES);
+                mbar_expect_tx(bar, STAGE_BYTES);
+                tma_load_2d(st, &map_a, c.ks * F_BK, c.m0, bar);
+                tma_load_2d(st + F_A_BYTES, &map_b, c.ks * F_BK, c.n0, bar);
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        // ================================================================ MMA issuer: four UTCHMMA (128 x BN x 16) per stage
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_f16(F_BM, BN);
+            int stage = 0, slot = 0; uint32_t phase = 0, tphase = 1;
+            bool first = true;
+            for (long long u = u_begin; u < u_end;) {
+                const int tile = (int) (u / KS), k0 = (int) (u - (long long) tile * KS);
+                const int k1 = (int) min((long long) KS, k0 + (u_end - u));
+                mbar_wait(smem_u32(tempty + slot), tphase);  // the epilogue has drained this accumulator
+                tc_fence_after();
+                for (int ks = k0; ks < k1; ks++) {
+                    mbar_wait(smem_u32(full + stage), phase);
+                    tc_fence_after();
+                    if (first && ks == k0) MMF_TRACE(3);
+                    if (first && ks == k0 + (k1 - k0) / 2) MMF_TRACE(4);
+                    const uint32_t a0 = smem_u32(smem + stage * STAGE_BYTES), b0 = a0 + F_A_BYTES;
+#pragma unroll
+                    for (int k = 0; k < F_BK / 16; k++) {
+                        umma_f16(tmem_base + slot * BN, umma_desc_sw128(a0 + k * 32), umma_desc_sw128(b0 + k * 32), idesc, (uint32_t) ((ks - k0) | k));
+                    }
+                    umma_commit(smem_u32(empty + stage));
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(smem_u32(tfull + slot));
+                if (first) { MMF_TRACE(5); first = false; }
+                if (++slot == SLOTS) { slot = 0; tphase ^= 1; }
+                u += k1 - k0;
+            }
+        }
+    } else if (warp >= F_FIRST_EPI) {
+        // ================================================================ epilogue: TMEM -> registers -> (partials) -> * 2^e[n] -> dst
+        // a thread owns one weight row (TMEM lane); the two warps of a lane quadrant take half of the tile's columns each
+        const int quad = warp & 3, half = (warp - F_FIRST_EPI) >> 2;
+        const int row  = quad * 32 + lane;
+        int slot = 0; uint32_t tphase = 0;
+        bool first = true;
+        asm volatile("griddepcontrol.wait;" ::: "memory");  // rs, the workspace flags and dst belong to earlier kernels until here
+        for (long long u = u_begin; u < u_end;) {
+            const int tile = (int) (u / KS), k0 = (int) (u - (long long) tile * KS);
+            const int k1 = (int) min((long long) KS, k0 + (u_end - u));
+            const int m0 = (tile / p.n_tiles) * F_BM, n0 = (tile % p.n_tiles) * BN;
+            const int m  = m0 + row;
+            mbar_wait(smem_u32(tfull + slot), tphase);
+            tc_fence_after();
+            if (first && warp == F_FIRST_EPI && lane == 0) MMF_TRACE(6);
+            const uint32_t t_lane = tmem_base + ((uint32_t) (quad * 32) << 16) + slot * BN + half * (BN / 2);
+            if (k0 > 0) {
+                // a later K-range of a cut tile: park the accumulator for the CTA that holds the range starting at 0
+                float * wsp = p.ws + ((size_t) blockIdx.x * BN + half * (BN / 2)) * F_BM + row;
+#pragma unroll 1
+                for (int c0 = 0; c0 < BN / 2; c0 += 32) {
+                    uint32_t c[32];
+                    tmem_ld_32x32(t_lane + c0, c);
+                    tc_wait_ld_regs(c);
+#pragma unroll
+                    for (int j = 0; j < 32; j++) __stcg(wsp + (size_t) (c0 + j) * F_BM, __uint_as_float(c[j]));
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(tempty + slot));
+                __threadfence();
+                asm volatile("bar.sync 1, %0;" ::"n"(32 * F_EPI_WARPS) : "memory");
+                if (warp == F_FIRST_EPI && lane == 0) st_release_gpu(p.flags + blockIdx.x, 1u);
+            } else {
+                // the K-range starting at 0: the tile is this CTA's to store; the CTAs after this one hold the rest of a cut tile
+                int n_parts = 0;
+                if (k1 < KS) {
+                    const long long tile_end = (long long) (tile + 1) * KS;
+                    while (blockIdx.x + 1 + n_parts < gridDim.x && p.units * (blockIdx.x + 1 + n_parts) / gridDim.x < tile_end) n_parts++;
+                    if (lane == 0) {
+                        for (int q = 1; q <= n_parts; q++) {
+                            long long spins = 0;
+                            while (ld_acquire_gpu(p.flags + blockIdx.x + q) == 0u) {
+                                if (++spins > (1ll << 24)) { printf("mmf_kernel: CTA %d timed out waiting for the partial of CTA %d\n", blockIdx.x, blockIdx.x + q); __trap(); }
+                            }
+                        }
+                    }
+                    __syncwarp();
+                }
+#pragma unroll 1
+                for (int c0 = 0; c0 < BN / 2; c0 += 32) {
+                    uint32_t c[32];
+                    tmem_ld_32x32(t_lane + c0, c);
+                    tc_wait_ld_regs(c);
+                    for (int q = 1; q <= n_parts; q++) {  // ascending K
+                        const float * wsp = p.ws + ((size_t) (blockIdx.x + q) * BN + half * (BN / 2) + c0) * F_BM + row;
+#pragma unroll
+                        for (int j = 0; j < 32; j++) c[j] = __float_as_uint(__uint_as_float(c[j]) + __ldcg(wsp + (size_t) j * F_BM));
+                    }
+                    const int   nb  = n0 + half * (BN / 2) + c0;
+                    const float rsv = nb + lane < p.N ? __ldg(p.rs + nb + lane) : 0.0f;
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; j++) v[j] = __uint_as_float(c[j]) * __shfl_sync(0xffffffffu, rsv, j);
+                    if (m < p.M) split_store_cols32(p.split, p.dst + (int64_t) nb * p.ldc + m, p.ldc, v, p.N - nb);
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(tempty + slot));
+                if (n_parts > 0) {  // every epilogue warp has seen the flags: lower them for the next launch
+                    asm volatile("bar.sync 1, %0;" ::"n"(32 * F_EPI_WARPS) : "memory");
+                    if (warp == F_FIRST_EPI && lane < n_parts) p.flags[blockIdx.x + 1 + lane] = 0u;
+                    if (warp == F_FIRST_EPI && lane == 0) for (int q = 33; q <= n_parts; q++) p.flags[blockIdx.x + q] = 0u;
+                }
+            }
+            if (first && warp == F_FIRST_EPI && lane == 0) { MMF_TRACE(7); first = false; }
+            if (++slot == SLOTS) { slot = 0; tphase ^= 1; }
+            u += k1 - k0;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (p.split.n_ranks > 1 && warp == 0) split_complete(p.split, gridDim.x);
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<SLOTS * BN>(tmem_base);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+
+int mmf_env(const char * name, int dflt) {
+    const char * s = getenv(name);
+    return s && *s ? atoi(s) : dflt;
+}
+
+template <int BN>
+b200_status mmf_launch(b200_ctx * ctx, const CUtensorMap & map_a, const CUtensorMap & map_b, MmfParams & p, int m_tiles) {
+    static bool attr_done[64] = {};
+    if (ctx->device < 64 && !attr_done[ctx->device]) {
+        CU(cudaFuncSetAttribute(mmf_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, f_smem(BN)));
+        attr_done[ctx->device] = true;
+    }
+    static const int env_sk = mmf_env("GGML_B200_MMF_STREAMK", 1), env_min = mmf_env("GGML_B200_MMF_MIN_SPAN", 4);
+    const int tiles = m_tiles * p.n_tiles;
+    p.units = (long long) tiles * p.k_stages;
+    int grid;
+    if (env_sk) {  // equal spans of at least env_min stages
+        const long long g = p.units / (env_min > 0 ? env_min : 1);
+        grid = (int) (g < 1 ? 1 : g < ctx->sm_count ? g : ctx->sm_count);
+    } else {       // whole tiles only
+        grid = tiles < ctx->sm_count ? tiles : ctx->sm_count;
+    }
+    p.whole_tiles = !env_sk;
+    // workspace: [flags: 4 KB][grid][BN][128] floats
+    const size_t need = 4096 + (size_t) ctx->sm_count * 256 * F_BM * 4;
+    if (ctx->scratch3_size < need) {
+        b200_status st = b200_ensure(ctx, &ctx->scratch3, &ctx->scratch3_size, need);
+        if (st != B200_OK) return st;
+        CU(cudaMemsetAsync(ctx->scratch3, 0, 4096, ctx->stream));
+    }
+    p.flags = (unsigned *) ctx->scratch3;
+    p.ws    = (float *) ((uint8_t *) ctx->scratch3 + 4096);
+    p.trace = ctx->trace ? ctx->trace + (size_t) (ctx->launches % ctx->trace_slots) * ctx->sm_count * 8 : nullptr;
+    cudaLaunchConfig_t  cfg = {};
+    cudaLaunchAttribute attr[1];
+    attr[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.gridDim          = dim3((unsigned) grid);
+    cfg.blockDim         = dim3(F_THREADS);
+    cfg.dynamicSmemBytes = f_smem(BN);
+    cfg.stream           = ctx->stream;
+    cfg.attrs            = attr;
+    cfg.numAttrs         = ctx->pdl ? 1 : 0;
+    CU(cudaLaunchKernelEx(&cfg, mmf_kernel<BN>, map_a, map_b, p));
+    ctx->launches++;
+    return B200_OK;
+}
+
+// dst[n*ldc + m] = sum_k W[m][k] * X[n][k]: e holds the fp16 weights, h / rs are scratch for the fp16 activations and 2^e[n]
+b200_status mmf_run(b200_ctx * ctx, WEntry * e, bool settled, const float * x, size_t x_rs, int64_t N, __half * h, float * rs, float * dst, int64_t ldc) {
+    const int64_t M = e->M, K = e->K;
+    const int     vec_ok = ((uintptr_t) x % 16 == 0) && (x_rs % 16 == 0);
+    for (int64_t r0 = 0; r0 < N; r0 += 1 << 30) {
+        const int64_t nr = N - r0 < (1 << 30) ? N - r0 : (1 << 30);
+        const float * xs = (const float *) ((const char *) x + r0 * x_rs);
+        cudaLaunchConfig_t  cfg = {};
+        cudaLaunchAttribute attr[1];
+        attr[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.gridDim  = dim3((unsigned) nr);
+        cfg.blockDim = dim3(256);
+        cfg.stream   = ctx->stream;
+        cfg.attrs    = attr;
+        cfg.numAttrs = ctx->pdl ? 1 : 0;
+        const int64_t units = (K + 255) / 256;
+        const bool    k8    = e->type == B200_TYPE_Q4_K;
+#define ACT_LAUNCH(UPW) (k8 ? cudaLaunchKernelEx(&cfg, act_f16_kernel<ACT_KIND_Q8_K, UPW>, xs, K, x_rs, h + r0 * K, rs + r0, vec_ok) \
+                            : cudaLaunchKernelEx(&cfg, act_f16_kernel<ACT_KIND_Q8_0, UPW>, xs, K, x_rs, h + r0 * K, rs + r0, vec_ok))
+        if (units <= 16)      CU(ACT_LAUNCH(2));
+        else if (units <= 32) CU(ACT_LAUNCH(4));
+        else if (units <= 64) CU(ACT_LAUNCH(8));
+        else                  CU(ACT_LAUNCH(0));
+#undef ACT_LAUNCH
+        ctx->launches++;
+    }
+
+    static const int env_bn = mmf_env("GGML_B200_MMF_BN", 0), env_pf = mmf_env("GGML_B200_MMF_PF", 0);
+    const int m_tiles = (int) ((M + F_BM - 1) / F_BM);
+    const int bn = env_bn ? env_bn : (N <= 128 ? 128 : 256);
+    MmfParams p;
+    p.split = ctx->split;
+    p.dst = dst; p.ldc = ldc; p.rs = rs; p.M = (int) M; p.N = (int) N; p.K = (int) K;
+    p.n_tiles  = (int) ((N + bn - 1) / bn);
+    p.k_stages = (int) ((K + F_BK - 1) / F_BK);
+    p.pf       = env_pf;
+    p.early_a  = settled;
+    CUtensorMap map_b;
+    if (!make_map(&map_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, h, (uint64_t) K, (uint64_t) N, (uint64_t) K * 2, F_BK, (uint32_t) bn, true)) {
+        return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the fp16 activations (N=%lld K=%lld)", (long long) N, (long long) K);
+    }
+    return bn == 256 ? mmf_launch<256>(ctx, e->map_q, map_b, p, m_tiles) : mmf_launch<128>(ctx, e->map_q, map_b, p, m_tiles);
+}

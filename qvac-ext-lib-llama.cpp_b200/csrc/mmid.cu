@@ -133,13 +133,13 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
             ax = am + aux_o;
             if (d->nb12 == d->nb11 * (size_t) d->ne11) {  // rows of all tokens are equally spaced: one launch
                 int l = 0;
-                CU(quantize_units(act_kind_for(d->type), b, K, n_rows, d->nb11, am, ax, ctx->stream, &l));
+                CU(quantize_units(act_kind_for(d->type), b, K, n_rows, d->nb11, am, ax, ctx->stream, &l, ctx->pdl));
                 ctx->launches += l;
             } else {
                 for (int64_t t = 0; t < d->n_tok; t++) {
                     int l = 0;
                     CU(quantize_units(act_kind_for(d->type), (const float *) ((const char *) b + t * d->nb12), K, d->ne11, d->nb11,
-                                      am + (size_t) t * d->ne11 * U * ACT_MAIN, ax + (size_t) t * d->ne11 * U * ACT_AUX, ctx->stream, &l));
+                                      am + (size_t) t * d->ne11 * U * ACT_MAIN, ax + (size_t) t * d->ne11 * U * ACT_AUX, ctx->stream, &l, ctx->pdl));
                     ctx->launches += l;
                 }
             }

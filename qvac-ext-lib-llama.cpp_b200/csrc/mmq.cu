@@ -314,12 +314,11 @@ mmq_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
             }
             const int m = m0 + row_in_tile;
             if (m < p.M) {
+                float v[32];
 #pragma unroll
-                for (int j = 0; j < 16; j++) {
-                    const int n = n0 + part * 32 + 2 * j;
-                    if (n < p.N) split_store(p.split, p.dst + (int64_t) n * p.ldc + m, acc[j].x);
-                    if (n + 1 < p.N) split_store(p.split, p.dst + (int64_t) (n + 1) * p.ldc + m, acc[j].y);
-                }
+                for (int j = 0; j < 16; j++) { v[2 * j] = acc[j].x; v[2 * j + 1] = acc[j].y; }
+                const int nb = n0 + part * 32;
+                split_store_cols32(p.split, p.dst + (int64_t) nb * p.ldc + m, p.ldc, v, p.N - nb);
             }
         }
     }
@@ -567,12 +566,11 @@ mmq_q4k_kernel(const __grid_constant__ CUtensorMap map_wa, const __grid_constant
             }
             const int m = m0 + row_in_tile;
             if (m < p.M) {
+                float v[32];
 #pragma unroll
-                for (int j = 0; j < 16; j++) {
-                    const int n = n0 + part * 32 + 2 * j;
-                    if (n < p.N) split_store(p.split, p.dst + (int64_t) n * p.ldc + m, acc[j].x);
-                    if (n + 1 < p.N) split_store(p.split, p.dst + (int64_t) (n + 1) * p.ldc + m, acc[j].y);
-                }
+                for (int j = 0; j < 16; j++) { v[2 * j] = acc[j].x; v[2 * j + 1] = acc[j].y; }
+                const int nb = n0 + part * 32;
+                split_store_cols32(p.split, p.dst + (int64_t) nb * p.ldc + m, p.ldc, v, p.N - nb);
             }
         }
     }
@@ -630,7 +628,11 @@ struct WEntry {  // expanded form of one weight matrix
     bool        planes = false;   // q4_K scale-folded form: [qa][qb][d: SB*Mp float][dmin: SB*Mp float][mins: M*SB*16 bytes];
                                   // map_sc = dmin, map_mn = mins
     CUtensorMap map_qb, map_dw;
+    bool        f16 = false;      // fp16 [M][K] for the kind::f16 kernel (mmf16.cuh): map_q only
+    bool        settled = false;  // the expansion kernel is known to have finished (set after a stream synchronize)
 };
+
+#include "mmf16.cuh"
 
 struct WKey {
     int          device;
@@ -647,7 +649,8 @@ bool q4k_planes_enabled() {
     return on;
 }
 
-size_t wentry_bytes(int type, int64_t M, int64_t K, int64_t Mp) {
+size_t wentry_bytes(int type, int64_t M, int64_t K, int64_t Mp, bool f16) {
+    if (f16) return ((size_t) M * K * 2 + 255) & ~(size_t) 255;
     const size_t qb = ((size_t) M * K + 255) & ~(size_t) 255;
     const size_t sb = (((size_t) (K / 32) * Mp * 4) + 255) & ~(size_t) 255;
     if (type == B200_TYPE_Q4_K && K % 256 == 0 && q4k_planes_enabled()) {
@@ -668,6 +671,20 @@ b200_status wentry_fill(b200_ctx * ctx, WEntry * e, const void * src, uint8_t * 
     e->buf = buf;
     const int64_t total = M * KB;
     const unsigned grid = (unsigned) ((total + 255) / 256);
+    if (e->f16) {
+        __half * h = (__half *) buf;
+        switch (e->type) {
+            case B200_TYPE_Q4_0: expand_f16_kernel<B200_TYPE_Q4_0><<<grid, 256, 0, ctx->stream>>>((const uint8_t *) src, (int64_t) e->nb01, M, K, h); break;
+            case B200_TYPE_Q8_0: expand_f16_kernel<B200_TYPE_Q8_0><<<grid, 256, 0, ctx->stream>>>((const uint8_t *) src, (int64_t) e->nb01, M, K, h); break;
+            default:             expand_f16_kernel<B200_TYPE_Q4_K><<<grid, 256, 0, ctx->stream>>>((const uint8_t *) src, (int64_t) e->nb01, M, K, h); break;
+        }
+        CU(cudaGetLastError());
+        ctx->launches++;
+        if (!make_map(&e->map_q, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, h, (uint64_t) K, (uint64_t) M, (uint64_t) K * 2, F_BK, F_BM, true)) {
+            return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the fp16 weights (M=%lld K=%lld)", (long long) M, (long long) K);
+        }
+        return B200_OK;
+    }
     if (e->type == B200_TYPE_Q4_K && K % 256 == 0 && q4k_planes_enabled()) {
         const size_t db = (((size_t) (K / 256) * e->Mp * 4) + 255) & ~(size_t) 255;
         int8_t * qa = (int8_t *) buf, * qbp = (int8_t *) (buf + qb);
@@ -750,7 +767,11 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
     // ---- activations: int8 [N][K] + scales [KB][Np] (+ sums) in scratch2
     const size_t aq = ((size_t) N * K + 255) & ~(size_t) 255;
     const size_t as = (((size_t) KB * Np * 4) + 255) & ~(size_t) 255;
-    size_t need = aq + as * (has_min ? 2 : 1);
+    const bool   f16 = ctx->mmq_f16 != 0;
+    const size_t hb  = ((size_t) N * K * 2 + 255) & ~(size_t) 255;   // fp16 activations [N][K] + 2^e[n]
+    const size_t rb  = ((size_t) N * 4 + 255) & ~(size_t) 255;
+    const size_t act_bytes = f16 ? hb + rb : aq + as * (has_min ? 2 : 1);
+    size_t need = act_bytes;
     // ---- weights: cached or transient (transient copies live behind the activations in scratch2)
     WEntry * e = nullptr;
     WEntry   tmp;
@@ -758,12 +779,13 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
     if (ctx->weight_cache) {
         std::lock_guard<std::mutex> lock(g_wmutex);
         auto it = g_wcache.find(WKey{ ctx->device, w });
-        if (it != g_wcache.end() && it->second->type == type && it->second->M == M && it->second->K == K && it->second->nb01 == nb01) {
+        if (it != g_wcache.end() && it->second->type == type && it->second->M == M && it->second->K == K && it->second->nb01 == nb01 &&
+            it->second->f16 == f16) {
             e = it->second;
             cached = true;
         }
     }
-    const size_t wb = wentry_bytes(type, M, K, Mp);
+    const size_t wb = wentry_bytes(type, M, K, Mp, f16);
     if (!e && !ctx->weight_cache) need += wb;
     b200_status st = b200_ensure(ctx, &ctx->scratch2, &ctx->scratch2_size, need);
     if (st != B200_OK) return st;
@@ -771,7 +793,7 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
 
     if (!e) {
         WEntry * ne = ctx->weight_cache ? new WEntry() : &tmp;
-        ne->type = type; ne->M = M; ne->K = K; ne->Mp = Mp; ne->nb01 = nb01; ne->bytes = wb;
+        ne->type = type; ne->M = M; ne->K = K; ne->Mp = Mp; ne->nb01 = nb01; ne->bytes = wb; ne->f16 = f16;
         uint8_t * buf = nullptr;
         if (ctx->weight_cache) {
             cudaError_t ce = cudaMalloc((void **) &buf, wb);
@@ -781,7 +803,7 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
                 return fail(B200_ERR_ALLOC, "weight cache: cudaMalloc(%zu): %s", wb, cudaGetErrorString(ce));
             }
         } else {
-            buf = s2 + aq + as * (has_min ? 2 : 1);
+            buf = s2 + act_bytes;
         }
         st = wentry_fill(ctx, ne, w, buf);
         if (st != B200_OK) {
@@ -789,6 +811,14 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
             return st;
         }
         if (ctx->weight_cache) {
+            // filling the cache is a load-time step: wait for it once, so that later launches may read the expansion ahead of
+            // their stream dependency (not possible while the stream is being captured: such an entry stays unsettled)
+            cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+            cudaStreamIsCapturing(ctx->stream, &cs);
+            if (cs == cudaStreamCaptureStatusNone) {
+                CU(cudaStreamSynchronize(ctx->stream));
+                ne->settled = true;
+            }
             std::lock_guard<std::mutex> lock(g_wmutex);
             auto it = g_wcache.find(WKey{ ctx->device, w });
             if (it != g_wcache.end()) {  // geometry changed under the same address: replace
@@ -803,6 +833,7 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
         e = ne;
     }
     (void) cached;
+    if (f16) return mmf_run(ctx, e, cached && e->settled, x, x_rs, N, (__half *) s2, (float *) (s2 + hb), dst, ldc);
 
     int8_t * xq = (int8_t *) s2;
     float *  sA = (float *) (s2 + aq);

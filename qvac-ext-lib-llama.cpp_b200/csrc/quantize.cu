@@ -21,6 +21,10 @@ enum { LAYOUT_GGML = 0, LAYOUT_UNITS = 1 };
 template <int VAL, int LAYOUT>
 __global__ void __launch_bounds__(128) quantize_rows_kernel(const float * __restrict__ x, int64_t k, int64_t nrows, size_t x_row_stride,
                                                             uint8_t * __restrict__ y_main, uint8_t * __restrict__ y_aux, int vec_ok) {
+    // programmatic dependent launch (no-ops without the launch attribute): let the consumer of the records start its weight
+    // prologue now; wait for the producer of x - and for the previous reader of the record scratch - before touching memory
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int     lane  = threadIdx.x & 31;
     const int64_t unit  = (int64_t) blockIdx.x * 4 + (threadIdx.x >> 5);
     const int64_t row   = blockIdx.y;
@@ -95,7 +99,7 @@ __global__ void __launch_bounds__(128) quantize_rows_kernel(const float * __rest
 }
 
 template <int VAL, int LAYOUT>
-static cudaError_t launch(const float * x, int64_t k, int64_t nrows, size_t stride, void * y_main, void * y_aux, cudaStream_t st) {
+static cudaError_t launch(const float * x, int64_t k, int64_t nrows, size_t stride, void * y_main, void * y_aux, cudaStream_t st, int pdl = 0) {
     if (nrows == 0 || k == 0) return cudaSuccess;
     const int64_t units  = (k + UNIT_ELEMS - 1) / UNIT_ELEMS;
     const int     vec_ok = ((uintptr_t) x % 16 == 0) && (stride % 16 == 0);
@@ -108,9 +112,19 @@ static cudaError_t launch(const float * x, int64_t k, int64_t nrows, size_t stri
         else if (VAL == VAL_Q8_0)   { main_row = k / QK * SZ_Q8_0; }
         else if (VAL == VAL_Q8_1)   { main_row = k / QK * SZ_Q8_1; }
         else                        { main_row = k / QK_K * SZ_Q8_K; }
-        quantize_rows_kernel<VAL, LAYOUT><<<grid, 128, 0, st>>>((const float *) ((const char *) x + r0 * stride), k, nr, stride,
-                                                                (uint8_t *) y_main + r0 * main_row,
-                                                                y_aux ? (uint8_t *) y_aux + r0 * aux_row : nullptr, vec_ok);
+        cudaLaunchConfig_t  cfg = {};
+        cudaLaunchAttribute attr[1];
+        attr[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.gridDim  = grid;
+        cfg.blockDim = dim3(128);
+        cfg.stream   = st;
+        cfg.attrs    = attr;
+        cfg.numAttrs = pdl ? 1 : 0;
+        const cudaError_t e = cudaLaunchKernelEx(&cfg, quantize_rows_kernel<VAL, LAYOUT>, (const float *) ((const char *) x + r0 * stride), k,
+                                                 nr, stride, (uint8_t *) y_main + r0 * main_row,
+                                                 y_aux ? (uint8_t *) y_aux + r0 * aux_row : (uint8_t *) nullptr, vec_ok);
+        if (e != cudaSuccess) return e;
     }
     return cudaGetLastError();
 }
@@ -127,11 +141,11 @@ cudaError_t quantize_ggml(int val, const float * x, int64_t k, int64_t nrows, si
 }
 
 cudaError_t quantize_units(int kind, const float * x, int64_t k, int64_t nrows, size_t stride, void * main, void * aux, cudaStream_t st,
-                           int * launches) {
+                           int * launches, int pdl) {
     const int n = (int) ((nrows + 65534) / 65535);
     if (launches) *launches += n;
-    if (kind == ACT_KIND_Q8_0) return launch<VAL_Q8_0, LAYOUT_UNITS>(x, k, nrows, stride, main, aux, st);
-    return launch<VAL_Q8_K, LAYOUT_UNITS>(x, k, nrows, stride, main, aux, st);
+    if (kind == ACT_KIND_Q8_0) return launch<VAL_Q8_0, LAYOUT_UNITS>(x, k, nrows, stride, main, aux, st, pdl);
+    return launch<VAL_Q8_K, LAYOUT_UNITS>(x, k, nrows, stride, main, aux, st, pdl);
 }
 
 } // namespace b200

@@ -29,7 +29,7 @@ def test_backend_mul_mat_matches_ggml_cpu(harness, refq, oracle, b200, t, M, K, 
     got, _ = harness.mul_mat(b200, t, W, X)
     ref, _ = harness.mul_mat(harness.cpu("x64"), t, W, X, n_threads=4)
     assert oracle.nmse(ref, got) <= 5e-4
-    assert oracle.nmse(ref, got) <= 1e-10
+    assert oracle.nmse(ref, got) <= (1e-10 if N <= 8 else 1e-6)   # more than 8 columns: fp16-operand prefill GEMM
 
 
 @pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])

@@ -13,6 +13,7 @@ pytestmark = pytest.mark.gpu
 GOLD = Path(__file__).resolve().parent / "golden"
 NMSE_MAX = 5e-4          # the reference's own threshold
 NMSE_TIGHT = 1e-10       # what identical integer sums + fp32 reordering actually give
+NMSE_F16 = 1e-6          # prefill on kind::f16 (default): operands rounded to 11 significant bits, fp32 accumulation; measured 1.2e-7
 
 
 def cu(a):
@@ -143,13 +144,13 @@ def test_mul_mat_vs_oracle(ctx, oracle, t, M, K, N):
 
 @pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
 @pytest.mark.parametrize("N", [9, 17, 64])
-def test_mul_mat_more_than_8_columns(ctx, oracle, t, N):
+def test_mul_mat_more_than_8_columns(ctx, oracle, t, N, mmq_bound):
     rng = np.random.default_rng(N + t)
     M, K = 100, 1024
     W = quantize_weights(oracle, t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
     X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
     got = ctx.mul_mat(t, cu(W), cu(X)).cpu().numpy()
-    assert oracle.nmse(oracle.mul_mat(t, W, X), got) <= NMSE_TIGHT
+    assert oracle.nmse(oracle.mul_mat(t, W, X), got) <= mmq_bound
 
 
 @pytest.mark.parametrize("t,K", [(Q4_0, 32), (Q4_0, 96), (Q8_0, 160), (Q8_0, 1056), (Q4_0, 4128)])
@@ -368,7 +369,7 @@ MMQ_SHAPES = [  # (M, K, N): full tiles, M / N / K tails (K % 128 != 0 -> TMA ze
 
 @pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
 @pytest.mark.parametrize("M,K,N", MMQ_SHAPES)
-def test_mmq_vs_oracle(ctx, pkg, oracle, t, M, K, N):
+def test_mmq_vs_oracle(ctx, pkg, oracle, t, M, K, N, mmq_bound):
     if t == Q4_K and K % 256:
         pytest.skip("q4_K needs K % 256 == 0")
     rng = np.random.default_rng(M + 3 * K + 7 * N + t)
@@ -379,11 +380,11 @@ def test_mmq_vs_oracle(ctx, pkg, oracle, t, M, K, N):
         got = ctx.mul_mat(t, cu(W), cu(X)).cpu().numpy()
     finally:
         ctx.force_path(pkg.PATH_AUTO)
-    assert oracle.nmse(oracle.mul_mat(t, W, X), got) <= NMSE_TIGHT
+    assert oracle.nmse(oracle.mul_mat(t, W, X), got) <= mmq_bound
 
 
 @pytest.mark.parametrize("t", [Q4_0, Q4_K])
-def test_mmq_and_matvec_kernels_agree(ctx, pkg, oracle, t):
+def test_mmq_and_matvec_kernels_agree(ctx, pkg, oracle, t, mmq_bound):
     """tensor-core tiles and dp4a mat-vec form the same integer block sums; only the fp32 summation order differs"""
     rng = np.random.default_rng(17 + t)
     M, K, N = 384, 4096, 8
@@ -395,10 +396,10 @@ def test_mmq_and_matvec_kernels_agree(ctx, pkg, oracle, t):
         b = ctx.mul_mat(t, cu(W), cu(X)).cpu().numpy()
     finally:
         ctx.force_path(pkg.PATH_AUTO)
-    assert oracle.nmse(a, b) <= NMSE_TIGHT
+    assert oracle.nmse(a, b) <= mmq_bound
 
 
-def test_mmq_batched_broadcast(ctx, pkg, oracle):
+def test_mmq_batched_broadcast(ctx, pkg, oracle, mmq_bound):
     rng = np.random.default_rng(23)
     M, K, N = 70, 512, 20
     W = quantize_weights(oracle, Q8_0, rng.uniform(-1, 1, (2 * M, K)).astype(np.float32)).reshape(1, 2, M, -1)
@@ -409,10 +410,10 @@ def test_mmq_batched_broadcast(ctx, pkg, oracle):
     finally:
         ctx.force_path(pkg.PATH_AUTO)
     ref = oracle.mul_mat(Q8_0, W, X, ne02=2, ne03=1)
-    assert oracle.nmse(ref, got) <= NMSE_TIGHT
+    assert oracle.nmse(ref, got) <= mmq_bound
 
 
-def test_mmq_weight_cache(ctx, pkg, oracle):
+def test_mmq_weight_cache(ctx, pkg, oracle, mmq_bound):
     """a context that keeps int8 expansions must be told about overwritten weights (what the ggml buffer does on set_tensor)"""
     import torch
     rng = np.random.default_rng(29)
@@ -434,12 +435,20 @@ def test_mmq_weight_cache(ctx, pkg, oracle):
         ctx.weight_cache(False)
         ctx.weight_cache_clear()
     assert pkg.lib().b200_weight_cache_bytes() == 0
-    assert oracle.nmse(oracle.mul_mat(Q4_0, W1, X), a) <= NMSE_TIGHT
-    assert oracle.nmse(oracle.mul_mat(Q4_0, W2, X), b) <= NMSE_TIGHT
+    assert oracle.nmse(oracle.mul_mat(Q4_0, W1, X), a) <= mmq_bound
+    assert oracle.nmse(oracle.mul_mat(Q4_0, W2, X), b) <= mmq_bound
+
+
+@pytest.fixture(params=["f16", "i8"])
+def mmq_bound(request, ctx):
+    """both prefill arithmetics (b200_ctx_set_mmq_f16): scale-carrying fp16 operands (default) and exact per-block int8"""
+    ctx.mmq_f16(request.param == "f16")
+    yield NMSE_F16 if request.param == "f16" else NMSE_TIGHT
+    ctx.mmq_f16(True)
 
 
 @pytest.mark.parametrize("t", [Q4_0, Q4_K, Q8_0])
-def test_mmq_full_size_properties(ctx, pkg, oracle, t):
+def test_mmq_full_size_properties(ctx, pkg, oracle, t, mmq_bound):
     """Llama-3-8B prefill shape 14336x4096, n=512: sampled rows equal the oracle; columns equal the mat-vec kernels' result"""
     rng = np.random.default_rng(37 + t)
     M, K, N = 14336, 4096, 512
@@ -451,10 +460,10 @@ def test_mmq_full_size_properties(ctx, pkg, oracle, t):
     rows = rng.choice(M, 48, replace=False)
     cols = rng.choice(N, 24, replace=False)
     ref = oracle.mul_mat(t, np.ascontiguousarray(W[rows]), X[cols])
-    assert oracle.nmse(ref, full[cols][:, rows].cpu().numpy()) <= NMSE_TIGHT
+    assert oracle.nmse(ref, full[cols][:, rows].cpu().numpy()) <= mmq_bound
     ctx.force_path(pkg.PATH_MMVQ)
     try:
         mv = ctx.mul_mat(t, Wd, Xd[100:108].contiguous())
     finally:
         ctx.force_path(pkg.PATH_AUTO)
-    assert oracle.nmse(mv.cpu().numpy(), full[100:108].cpu().numpy()) <= NMSE_TIGHT
+    assert oracle.nmse(mv.cpu().numpy(), full[100:108].cpu().numpy()) <= mmq_bound

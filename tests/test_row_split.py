@@ -174,4 +174,4 @@ def test_fused_exchange_writes_every_destination(pkg, oracle, t, N, deferred):
         assert np.array_equal(c.mul_mat(t, cu(W), cu(X)).cpu().numpy(), ref)
     finally:
         c.close()
-    assert oracle.nmse(oracle.mul_mat(t, W, X), ref) <= NMSE_TIGHT
+    assert oracle.nmse(oracle.mul_mat(t, W, X), ref) <= (NMSE_TIGHT if N <= 8 else 1e-6)   # N > 8: fp16-operand prefill GEMM
