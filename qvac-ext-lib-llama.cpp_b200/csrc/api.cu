@@ -553,7 +553,8 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
                 for (int64_t i12 = 0; i12 < di.ne12; i12++) {
                     b200_status st = b200_mmq_run(ctx, type, (const uint8_t *) src0s[i] + (i12 / r2) * di.nb02 + (i13 / r3) * di.nb03, di.nb01,
                                                   di.ne01, K, (const float *) ((const char *) src1 + i12 * di.nb12 + i13 * di.nb13), di.nb11, N,
-                                                  (float *) ((char *) dsts[i] + i12 * di.nb2 + i13 * di.nb3), (int64_t) (di.nb1 / 4));
+                                                  (float *) ((char *) dsts[i] + i12 * di.nb2 + i13 * di.nb3), (int64_t) (di.nb1 / 4),
+                                                  /* act_shared = */ i > 0 && di.ne12 == 1 && di.ne13 == 1);
                     if (st != B200_OK) return st;
                 }
         }

@@ -60,6 +60,8 @@ struct b200_ctx {
     int          dbg = 0;                      // GGML_B200_DBG: experiment switches handed to the kernels
     int          mma_min_cols = 3;             // columns from which the IMMA mat-vec kernel (mvmma.cu) replaces the dp4a one; GGML_B200_MMA_MIN
     int          mma_warps = 0;                // 0 = auto; GGML_B200_MMA_WARPS
+    // the fp16 activation operand last built in scratch2 (kind::f16 prefill): valid for further matrices of the same shared-src1 group
+    const void * act_x = nullptr; size_t act_rs = 0; int64_t act_N = 0, act_K = 0; const void * act_buf = nullptr; int act_kind = -1;
     int          mmq_f16 = 1;                  // prefill GEMM on kind::f16 with the block scales folded into fp16 operands (mmf16.cuh); 0: kind::i8
     int          moe_group_min = 2;            // MUL_MAT_ID: group by expert (tensor-core mat-vec) from this many pairs per expert on
                                                // average; 0 = never; GGML_B200_MOE_GROUP_MIN
@@ -87,5 +89,7 @@ b200_status b200_mv_mma_run_ids(b200_ctx * ctx, int type, int64_t K, const uint8
 
 // mmq.cu: the tcgen05 int8 tile kernel
 bool        b200_mmq_usable(int type, int64_t K, const void * w, size_t nb01);
+// act_shared: this call belongs to a group of MUL_MATs that read the same src1 (b200_mul_mat_shared_src1) and is not the group's first:
+// the fp16 activation operand built by the previous call of the group is still in scratch and is used as it is
 b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, int64_t M, int64_t K, const float * x, size_t x_rs, int64_t N,
-                         float * dst, int64_t ldc);
+                         float * dst, int64_t ldc, bool act_shared = false);

@@ -44,6 +44,11 @@ struct SplitParams {
     uint32_t * sync_peer[SPLIT_MAX_RANKS];    // rank r's sync words
     int        deferred;                      // 1: publish the epoch but do not wait for the peers here - the next kernel of the
                                               // stream (split_wait in its prologue) or b200_ctx_row_split_wait does
+    // ---- flagged-payload exchange for the decode mat-vec kernels (b200_ctx_set_row_split_ll; see ll_store / ll_receive below)
+    int          ll;                          // 1: this launch exchanges its rows as 8-byte {value, epoch} records
+    char *       ll_stage[SPLIT_MAX_RANKS];   // rank r's staging area: two halves (epoch parity) of ll_half bytes
+    const char * ll_base;                     // local address of the symmetric dst region the staging area mirrors (8 bytes per float)
+    uint64_t     ll_half;
 };
 
 // waits until every peer has published the epoch this rank is at (all of their slices of every earlier dst have arrived).
@@ -133,6 +138,70 @@ __device__ __forceinline__ void split_complete(const SplitParams & sp, unsigned 
     __syncwarp();
 }
 
+// ---- flagged-payload ("LL") exchange. The flag protocol above needs a system-scope release per kernel, which alone costs ~3 us
+// on this machine and leaves 8-GPU decode at ~11 us of exchange per launch. Here a value and the launch's
+// epoch travel in ONE aligned 8-byte store into a staging area on every peer (8-byte stores are single-copy atomic: no fence,
+// no flag, no counter on the data path), and every rank's threads poll their share of the staging records of the rows the
+// OTHER ranks own and copy the values into the local dst: kernel completion still means "the whole dst is here". The staging area
+// has two halves used by odd / even epochs: a rank can be at most one launch ahead of a peer (it cannot finish launch L + 1
+// before every peer has sent its rows of L + 1, i.e. has finished L), so records of launch L are never overwritten before they
+// are read. Epochs are counted in device memory (sync word 8, bumped by the last CTA of every launch of either protocol), so
+// CUDA-graph replays keep counting and all ranks agree as long as they run the same launch sequence.
+struct SplitGeom {
+    int lo[4][SPLIT_MAX_RANKS + 1];           // per matrix of a launch: first row of every rank's slice; [n_ranks] = rows of the full matrix
+};
+
+__device__ __forceinline__ uint32_t ll_epoch(const SplitParams & sp) {  // after the stream dependency is resolved
+    uint32_t e;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(e) : "l"(sp.sync_local + 8) : "memory");
+    return e + 1;
+}
+
+__device__ __forceinline__ void ll_store(const SplitParams & sp, uint32_t ep, float * addr, float v) {
+    *addr = v;
+    const uint64_t off = (uint64_t) ((const char *) addr - sp.ll_base) * 2 + (uint64_t) (ep & 1) * sp.ll_half;
+    const uint64_t rec = (uint64_t) __float_as_uint(v) | ((uint64_t) ep << 32);
+    for (int r = 0; r < sp.n_ranks; r++) {
+        if (r != sp.rank) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(sp.ll_stage[r] + off), "l"(rec) : "memory");
+    }
+}
+
+// thread `tid` of `T` receiving threads of the launch: polls the records of every T-th element the peers own and stores the values
+template <typename MAT>
+__device__ __forceinline__ void ll_receive(const SplitParams & sp, uint32_t ep, const SplitGeom & g, const MAT * mat, int n_mats, int ncols, int tid, int T) {
+    const char * stage = sp.ll_stage[sp.rank] + (uint64_t) (ep & 1) * sp.ll_half;
+    int done = 0;
+    for (int i = 0; i < n_mats; i++) {
+        const int lo = g.lo[i][sp.rank], own = g.lo[i][sp.rank + 1] - lo, remote = g.lo[i][sp.n_ranks] - own;
+        const int total = remote * ncols;
+        for (int e = ((tid - done) % T + T) % T; e < total; e += T) {
+            const int c = e / remote, j = e - c * remote;
+            float * a = mat[i].dst + (int64_t) c * mat[i].dst_cs + ((j < lo ? j : j + own) - lo);
+            const char * rp = stage + (uint64_t) ((const char *) a - sp.ll_base) * 2;
+            uint64_t rec, t0 = 0, t1;
+            for (unsigned spins = 1;; spins++) {
+                asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(rec) : "l"(rp) : "memory");
+                if ((uint32_t) (rec >> 32) == ep) break;
+                if ((spins & 0x3ff) == 0) {  // a peer that never sends (crashed rank, mismatched launch sequence) must not hang the GPU
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                    if (t0 == 0) t0 = t1;
+                    if (t1 - t0 > 5000000000ull) __trap();
+                }
+            }
+            *a = __uint_as_float((uint32_t) rec);
+        }
+        done += total;
+    }
+}
+
+// one thread per CTA, after the CTA's receiving threads are done: the last CTA of the launch publishes the epoch for the next one
+__device__ __forceinline__ void ll_finish(const SplitParams & sp, uint32_t ep, unsigned n_ctas) {
+    if (atomicAdd(&sp.sync_local[9], 1u) == n_ctas - 1) {
+        sp.sync_local[9] = 0;
+        sp.sync_local[8] = ep;
+    }
+}
+
 struct MvMat {
     const uint8_t * w;        // row 0 of the weight matrix (16-byte aligned)
     int64_t         nb01;     // bytes between rows (multiple of 16)
@@ -180,6 +249,7 @@ struct MvParams {
     // MUL_MAT_ID mode (ids != nullptr): blockIdx.y = pair p = t*n_used + i; one column per pair; mat[0] = expert 0
     MvIds           ids;
     SplitParams     split;
+    SplitGeom       geom;     // split.ll: who owns which rows of mat[i]
     MvNext          next;
     // debug timeline (b200_ctx_trace): 8 x u64 per CTA at trace + blockIdx.x*8: globaltimer ns of [0] CTA start, [1] first and
     // [2] last weight copy issued, [3] consumer warp 0 past griddepcontrol.wait, [4] activations quantized, [5] first stage

@@ -17,15 +17,17 @@
 // Tiling: CTA tile 128 (M) x BN (N, 256 or 128), K in stages of 64 halfs (= one 128-byte swizzle row), four UTCHMMA
 // 128 x BN x 16 per stage, 2 TMEM accumulator slots of BN columns (the epilogue of one work item overlaps the main loop of the next).
 // Scheduling is stream-K: the launch's tiles x K-stages are cut into gridDim.x equal contiguous spans (one persistent CTA per SM),
-// so every SM is busy for the same time whatever the tile count (wk/wv of Llama-3-8B at n = 512 are 16 tiles). A tile cut by a
-// span boundary is finished deterministically: the CTAs holding its later K-ranges start their span with it, park the partial
-// accumulator in a workspace and raise a flag; the CTA holding the K-range that begins at 0 reaches it last, waits for the flags
-// and adds the partials in ascending K order before it stores the tile (no atomics: results do not depend on timing).
+// so every SM is busy for the same time whatever the tile count (wk/wv of Llama-3-8B at n = 512 are 16 tiles). A tile cut by
+// span boundaries is finished deterministically in two phases: every CTA parks the partial accumulator of its part in a
+// workspace and bumps a counter; at the end of its span each of the P CTAs that share the tile waits for the P parts and sums
+// all of them in ascending K order for ITS 1/P of the tile's columns, scales and stores that share (no atomics on data: results
+// do not depend on timing; the fix-up of a tile cut P ways runs on P SMs - a single owner summing P x 128 KB took 28 us on wk).
 // Warp roles (384 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 4..11 epilogue.
 // Tried and dropped: clusters of two CTAs sharing the activation tile by TMA multicast (same speed: the SM's ingest, not the
 // L2 read rate, is what a 128 x 256 tile is short of - profiles/README.md).
 
 #include <cuda_fp16.h>
+#include <type_traits>
 
 constexpr int F_BM = 128, F_BK = 64;
 constexpr int F_EPI_WARPS = 8, F_FIRST_EPI = 4;
@@ -57,7 +59,7 @@ __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned * p) {
 }
 __device__ __forceinline__ unsigned long long mmf_ns() {
     unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) :: "memory");
     return t;
 }
 
@@ -242,8 +244,8 @@ struct MmfParams {
     int           M, N, K;
     int           n_tiles, k_stages;
     long long     units;   // tiles x k_stages
-    float *       ws;      // [gridDim.x][BN][128] partial accumulators of cut tiles
-    unsigned *    flags;   // [gridDim.x] 1 = CTA c's partial is in ws (reset by its reader)
+    float *       ws;      // [gridDim.x][2][BN][128] partial accumulators of cut tiles (slot 1: the K-range that starts at 0)
+    unsigned *    flags;   // [h] parts of the cut tile headed by CTA h that are parked; [512 + h] CTAs that have summed their share of it
     unsigned long long * trace;  // debug timeline (b200_ctx_trace): 8 x u64 per CTA
     int           pf;      // L2 prefetch distance of the weight tiles in stages (0 = off)
     int           early_a;      // the weight tiles may be requested before the stream dependency resolves
@@ -358,7 +360,6 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
                     mbar_wait(smem_u32(full + stage), phase);
                     tc_fence_after();
                     if (first && ks == k0) MMF_TRACE(3);
-                    if (first && ks == k0 + (k1 - k0) / 2) MMF_TRACE(4);
                     const uint32_t a0 = smem_u32(smem + stage * STAGE_BYTES), b0 = a0 + F_A_BYTES;
 #pragma unroll
                     for (int k = 0; k < F_BK / 16; k++) {
@@ -374,13 +375,16 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
             }
         }
     } else if (warp >= F_FIRST_EPI) {
-        // ================================================================ epilogue: TMEM -> registers -> (partials) -> * 2^e[n] -> dst
+        // ================================================================ epilogue: TMEM -> registers -> * 2^e[n] -> dst, or -> workspace
         // a thread owns one weight row (TMEM lane); the two warps of a lane quadrant take half of the tile's columns each
         const int quad = warp & 3, half = (warp - F_FIRST_EPI) >> 2;
         const int row  = quad * 32 + lane;
+        const int te   = (warp - F_FIRST_EPI) * 32 + lane;  // 0 .. 255
+        const long long G = gridDim.x;
         int slot = 0; uint32_t tphase = 0;
         bool first = true;
-        asm volatile("griddepcontrol.wait;" ::: "memory");  // rs, the workspace flags and dst belong to earlier kernels until here
+        int  cut_tile[2], n_cut = 0;  // the (at most two) tiles of this span that other CTAs share: finished in phase 2
+        asm volatile("griddepcontrol.wait;" ::: "memory");  // rs, the workspace, its counters and dst belong to earlier kernels until here
         for (long long u = u_begin; u < u_end;) {
             const int tile = (int) (u / KS), k0 = (int) (u - (long long) tile * KS);
             const int k1 = (int) min((long long) KS, k0 + (u_end - u));
@@ -390,9 +394,10 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
             tc_fence_after();
             if (first && warp == F_FIRST_EPI && lane == 0) MMF_TRACE(6);
             const uint32_t t_lane = tmem_base + ((uint32_t) (quad * 32) << 16) + slot * BN + half * (BN / 2);
-            if (k0 > 0) {
-                // a later K-range of a cut tile: park the accumulator for the CTA that holds the range starting at 0
-                float * wsp = p.ws + ((size_t) blockIdx.x * BN + half * (BN / 2)) * F_BM + row;
+            if (k0 > 0 || k1 < KS) {
+                // part of a tile that is cut by span boundaries: park the accumulator (slot 1 of this CTA for the K-range that starts
+                // at 0, slot 0 otherwise - a later range is always the first item of its CTA) and count it on the tile's head CTA
+                float * wsp = p.ws + (((size_t) (2 * blockIdx.x + (k0 == 0 ? 1 : 0)) * BN + half * (BN / 2)) * F_BM + row);
 #pragma unroll 1
                 for (int c0 = 0; c0 < BN / 2; c0 += 32) {
                     uint32_t c[32];
@@ -406,33 +411,17 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
                 if (lane == 0) mbar_arrive(smem_u32(tempty + slot));
                 __threadfence();
                 asm volatile("bar.sync 1, %0;" ::"n"(32 * F_EPI_WARPS) : "memory");
-                if (warp == F_FIRST_EPI && lane == 0) st_release_gpu(p.flags + blockIdx.x, 1u);
-            } else {
-                // the K-range starting at 0: the tile is this CTA's to store; the CTAs after this one hold the rest of a cut tile
-                int n_parts = 0;
-                if (k1 < KS) {
-                    const long long tile_end = (long long) (tile + 1) * KS;
-                    while (blockIdx.x + 1 + n_parts < gridDim.x && p.units * (blockIdx.x + 1 + n_parts) / gridDim.x < tile_end) n_parts++;
-                    if (lane == 0) {
-                        for (int q = 1; q <= n_parts; q++) {
-                            long long spins = 0;
-                            while (ld_acquire_gpu(p.flags + blockIdx.x + q) == 0u) {
-                                if (++spins > (1ll << 24)) { printf("mmf_kernel: CTA %d timed out waiting for the partial of CTA %d\n", blockIdx.x, blockIdx.x + q); __trap(); }
-                            }
-                        }
-                    }
-                    __syncwarp();
+                if (warp == F_FIRST_EPI && lane == 0) {
+                    const int h = (int) ((((long long) tile * KS + 1) * G + p.units - 1) / p.units) - 1;  // the CTA whose span holds the tile's first stage
+                    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.flags + h) : "memory");
                 }
+                cut_tile[n_cut++] = tile;
+            } else {
 #pragma unroll 1
                 for (int c0 = 0; c0 < BN / 2; c0 += 32) {
                     uint32_t c[32];
                     tmem_ld_32x32(t_lane + c0, c);
                     tc_wait_ld_regs(c);
-                    for (int q = 1; q <= n_parts; q++) {  // ascending K
-                        const float * wsp = p.ws + ((size_t) (blockIdx.x + q) * BN + half * (BN / 2) + c0) * F_BM + row;
-#pragma unroll
-                        for (int j = 0; j < 32; j++) c[j] = __float_as_uint(__uint_as_float(c[j]) + __ldcg(wsp + (size_t) j * F_BM));
-                    }
                     const int   nb  = n0 + half * (BN / 2) + c0;
                     const float rsv = nb + lane < p.N ? __ldg(p.rs + nb + lane) : 0.0f;
                     float v[32];
@@ -443,20 +432,97 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(smem_u32(tempty + slot));
-                if (n_parts > 0) {  // every epilogue warp has seen the flags: lower them for the next launch
-                    asm volatile("bar.sync 1, %0;" ::"n"(32 * F_EPI_WARPS) : "memory");
-                    if (warp == F_FIRST_EPI && lane < n_parts) p.flags[blockIdx.x + 1 + lane] = 0u;
-                    if (warp == F_FIRST_EPI && lane == 0) for (int q = 33; q <= n_parts; q++) p.flags[blockIdx.x + q] = 0u;
-                }
             }
-            if (first && warp == F_FIRST_EPI && lane == 0) { MMF_TRACE(7); first = false; }
+            if (first) first = false;
             if (++slot == SLOTS) { slot = 0; tphase ^= 1; }
             u += k1 - k0;
         }
+        // ---- phase 2: every CTA that holds a part of a cut tile sums ALL of the tile's parts (ascending K: fixed order, no atomics on
+        // data) for its own share of the tile's columns and stores that share - the fix-up of a tile cut P ways runs on P SMs
+        for (int r = 0; r < n_cut; r++) {
+            const int tile = cut_tile[r];
+            const int m0 = (tile / p.n_tiles) * F_BM, n0 = (tile % p.n_tiles) * BN;
+            const int h  = (int) ((((long long) tile * KS + 1) * G + p.units - 1) / p.units) - 1;
+            const int l  = (int) ((((long long) (tile + 1) * KS) * G + p.units - 1) / p.units) - 1;
+            const int P  = l - h + 1, me = (int) blockIdx.x - h;
+            if (lane == 0) {
+                long long spins = 0;
+                while (ld_acquire_gpu(p.flags + h) < (unsigned) P) {
+                    if (++spins > (1ll << 24)) { printf("mmf_kernel: CTA %d timed out waiting for the parts of tile %d\n", blockIdx.x, tile); __trap(); }
+                }
+            }
+            __syncwarp();
+            const int c_lo = BN * me / P, c_hi = BN * (me + 1) / P;
+            const int n_pos = (c_hi - c_lo) * 32;  // positions of 4 consecutive rows (16 bytes) of one column
+            const bool vec = p.split.n_ranks <= 1 && (p.ldc & 3) == 0 && ((uintptr_t) p.dst & 15) == 0;
+            const size_t slot_floats = (size_t) BN * F_BM;
+            // a thread keeps NP positions x JB parts in flight: the sums are L2-latency bound otherwise (2 loads per round trip
+            // made this phase 20 us). Few parts: many positions at once; many parts: many parts at once.
+            auto reduce = [&](auto np_c, auto jb_c) {
+                constexpr int NP = decltype(np_c)::value, JB = decltype(jb_c)::value;
+                for (int pos0 = te; pos0 < n_pos; pos0 += NP * 32 * F_EPI_WARPS) {
+                    float4        acc[NP];
+                    const float * src[NP];
+#pragma unroll
+                    for (int i = 0; i < NP; i++) {
+                        const int pos = min(pos0 + i * 32 * F_EPI_WARPS, n_pos - 1);  // out-of-range lanes repeat the last position (not stored)
+                        src[i] = p.ws + ((size_t) (c_lo + (pos >> 5)) * F_BM + 4 * (pos & 31));
+                        acc[i] = __ldcg((const float4 *) (src[i] + (size_t) (2 * h + 1) * slot_floats));  // the range that starts at 0: the head's slot 1
+                    }
+                    for (int j0 = 1; j0 < P; j0 += JB) {  // ascending K
+                        float4 v[JB][NP];
+#pragma unroll
+                        for (int j = 0; j < JB; j++) {
+                            const int jj = min(j0 + j, P - 1);
+#pragma unroll
+                            for (int i = 0; i < NP; i++) v[j][i] = __ldcg((const float4 *) (src[i] + (size_t) (2 * (h + jj)) * slot_floats));
+                        }
+#pragma unroll
+                        for (int j = 0; j < JB; j++) {
+                            if (j0 + j < P) {
+#pragma unroll
+                                for (int i = 0; i < NP; i++) { acc[i].x += v[j][i].x; acc[i].y += v[j][i].y; acc[i].z += v[j][i].z; acc[i].w += v[j][i].w; }
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < NP; i++) {
+                        const int pos = pos0 + i * 32 * F_EPI_WARPS;
+                        if (pos >= n_pos) continue;
+                        const int n = n0 + c_lo + (pos >> 5), m = m0 + 4 * (pos & 31);
+                        if (n >= p.N || m >= p.M) continue;
+                        const float rsv = __ldg(p.rs + n);
+                        float4 a = acc[i];
+                        a.x *= rsv; a.y *= rsv; a.z *= rsv; a.w *= rsv;
+                        float * d = p.dst + (int64_t) n * p.ldc + m;
+                        if (vec && m + 3 < p.M) {
+                            *(float4 *) d = a;
+                        } else {
+                            split_store(p.split, d, a.x);
+                            if (m + 1 < p.M) split_store(p.split, d + 1, a.y);
+                            if (m + 2 < p.M) split_store(p.split, d + 2, a.z);
+                            if (m + 3 < p.M) split_store(p.split, d + 3, a.w);
+                        }
+                    }
+                }
+            };
+            if (P <= 3) reduce(std::integral_constant<int, 8>{}, std::integral_constant<int, 2>{});
+            else        reduce(std::integral_constant<int, 4>{}, std::integral_constant<int, 4>{});
+            // the last of the P readers lowers the counters for the next launch
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * F_EPI_WARPS) : "memory");
+            if (warp == F_FIRST_EPI && lane == 0) {
+                if (atomicAdd(p.flags + 512 + h, 1u) == (unsigned) (P - 1)) {
+                    p.flags[h]       = 0u;
+                    p.flags[512 + h] = 0u;
+                }
+            }
+        }
+        if (warp == F_FIRST_EPI && lane == 0) MMF_TRACE(7);
     }
 
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) MMF_TRACE(4);  // every role of this CTA is through its span
     if (p.split.n_ranks > 1 && warp == 0) split_complete(p.split, gridDim.x);
     if (warp == 1) {
         tc_fence_after();
@@ -478,19 +544,20 @@ b200_status mmf_launch(b200_ctx * ctx, const CUtensorMap & map_a, const CUtensor
         CU(cudaFuncSetAttribute(mmf_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, f_smem(BN)));
         attr_done[ctx->device] = true;
     }
-    static const int env_sk = mmf_env("GGML_B200_MMF_STREAMK", 1), env_min = mmf_env("GGML_B200_MMF_MIN_SPAN", 4);
+    static const int env_sk = mmf_env("GGML_B200_MMF_STREAMK", 1), env_min = mmf_env("GGML_B200_MMF_MIN_SPAN", 8);
     const int tiles = m_tiles * p.n_tiles;
     p.units = (long long) tiles * p.k_stages;
     int grid;
     if (env_sk) {  // equal spans of at least env_min stages
         const long long g = p.units / (env_min > 0 ? env_min : 1);
         grid = (int) (g < 1 ? 1 : g < ctx->sm_count ? g : ctx->sm_count);
+        if (grid > 512) grid = 512;  // the counters of the cut tiles are indexed by CTA
     } else {       // whole tiles only
         grid = tiles < ctx->sm_count ? tiles : ctx->sm_count;
     }
     p.whole_tiles = !env_sk;
-    // workspace: [flags: 4 KB][grid][BN][128] floats
-    const size_t need = 4096 + (size_t) ctx->sm_count * 256 * F_BM * 4;
+    // workspace: [counters: 4 KB (parts parked per head CTA, readers done per head CTA)][2 slots per CTA][BN][128] floats
+    const size_t need = 4096 + (size_t) 2 * ctx->sm_count * 256 * F_BM * 4;
     if (ctx->scratch3_size < need) {
         b200_status st = b200_ensure(ctx, &ctx->scratch3, &ctx->scratch3_size, need);
         if (st != B200_OK) return st;
@@ -515,10 +582,12 @@ b200_status mmf_launch(b200_ctx * ctx, const CUtensorMap & map_a, const CUtensor
 }
 
 // dst[n*ldc + m] = sum_k W[m][k] * X[n][k]: e holds the fp16 weights, h / rs are scratch for the fp16 activations and 2^e[n]
-b200_status mmf_run(b200_ctx * ctx, WEntry * e, bool settled, const float * x, size_t x_rs, int64_t N, __half * h, float * rs, float * dst, int64_t ldc) {
+// have_act: h / rs already hold this src1 (an earlier matrix of the same shared-src1 group built them): no quantizer launch
+b200_status mmf_run(b200_ctx * ctx, WEntry * e, bool settled, const float * x, size_t x_rs, int64_t N, __half * h, float * rs, float * dst, int64_t ldc,
+                    bool have_act) {
     const int64_t M = e->M, K = e->K;
     const int     vec_ok = ((uintptr_t) x % 16 == 0) && (x_rs % 16 == 0);
-    for (int64_t r0 = 0; r0 < N; r0 += 1 << 30) {
+    for (int64_t r0 = 0; r0 < N && !have_act; r0 += 1 << 30) {
         const int64_t nr = N - r0 < (1 << 30) ? N - r0 : (1 << 30);
         const float * xs = (const float *) ((const char *) x + r0 * x_rs);
         cudaLaunchConfig_t  cfg = {};

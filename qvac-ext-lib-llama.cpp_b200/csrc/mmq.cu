@@ -757,7 +757,7 @@ bool b200_mmq_usable(int type, int64_t K, const void * w, size_t nb01) {
 
 // dst[n*ldc + m] = sum_k W[m][k] * X[n][k] for one weight matrix and N activation rows
 b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, int64_t M, int64_t K, const float * x, size_t x_rs, int64_t N,
-                         float * dst, int64_t ldc) {
+                         float * dst, int64_t ldc, bool act_shared) {
     if (M <= 0 || N <= 0) return B200_OK;
     if (M > INT32_MAX - BM || N > INT32_MAX - BN || K > INT32_MAX - 128) return fail(B200_ERR_UNSUPPORTED, "MMQ shape too large");
     const int64_t KB = K / 32;
@@ -833,7 +833,14 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
         e = ne;
     }
     (void) cached;
-    if (f16) return mmf_run(ctx, e, cached && e->settled, x, x_rs, N, (__half *) s2, (float *) (s2 + hb), dst, ldc);
+    if (f16) {
+        const int kind = type == B200_TYPE_Q4_K ? ACT_KIND_Q8_K : ACT_KIND_Q8_0;
+        const bool have_act = act_shared && ctx->act_x == x && ctx->act_rs == x_rs && ctx->act_N == N && ctx->act_K == K && ctx->act_buf == s2 &&
+                              ctx->act_kind == kind;
+        ctx->act_x = x; ctx->act_rs = x_rs; ctx->act_N = N; ctx->act_K = K; ctx->act_buf = s2; ctx->act_kind = kind;
+        return mmf_run(ctx, e, cached && e->settled, x, x_rs, N, (__half *) s2, (float *) (s2 + hb), dst, ldc, have_act);
+    }
+    ctx->act_x = nullptr;
 
     int8_t * xq = (int8_t *) s2;
     float *  sA = (float *) (s2 + aq);

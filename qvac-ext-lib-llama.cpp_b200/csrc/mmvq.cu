@@ -407,7 +407,9 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
     griddep_wait();  // everything below reads src1 / writes dst, which earlier kernels of the stream may produce / still read
 
     if (w == 0) MV_TRACE(3);
-    if (p.split.n_ranks > 1 && p.split.deferred) split_wait(p.split);  // src1 may derive from a dst whose remote slices are still in flight
+    const bool     ll = p.split.n_ranks > 1 && p.split.ll;
+    const uint32_t ep = ll ? ll_epoch(p.split) : 0u;
+    if (p.split.n_ranks > 1 && p.split.deferred && !ll) split_wait(p.split);  // src1 may derive from a dst whose remote slices are still in flight
     if (p.fuse_quant) {
         // fused K1: unit (c, u) of the activations, F32 global -> unit record in shared memory. Up to 4 units per warp are
         // loaded before the first is quantized, so the L2 round trips overlap instead of chaining
@@ -497,7 +499,11 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
                     const float t = __shfl_xor_sync(0xffffffffu, v, o);
                     if (o < L) v += t;
                 }
-                if (sub == 0 && row < M && rr < p.rpg) split_store(p.split, p.mat[m].dst + dst_off + (int64_t) c * p.mat[m].dst_cs + row, v);
+                if (sub == 0 && row < M && rr < p.rpg) {
+                    float * a = p.mat[m].dst + dst_off + (int64_t) c * p.mat[m].dst_cs + row;
+                    if (ll) ll_store(p.split, ep, a, v);
+                    else split_store(p.split, a, v);
+                }
                 acc[c] = 0.0f;
             }
         }
@@ -505,7 +511,11 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
         if (++slice == p.slices) { slice = 0; j++; }
     }
     if (w == 0) MV_TRACE(6);
-    if (p.split.n_ranks > 1) {  // fused all-gather: this CTA's slice is on its way to every rank; the last CTA exchanges flags
+    if (ll) {  // flagged-payload exchange: this CTA's rows are on their way to every rank; collect this CTA's share of the peers' rows
+        ll_receive(p.split, ep, p.geom, p.mat, p.n_mats, NC, (int) blockIdx.x * NWC * 32 + w * 32 + lane, (int) gridDim.x * NWC * 32);
+        bar_sync_named(1, NWC * 32);
+        if (w == 0 && lane == 0) ll_finish(p.split, ep, gridDim.x);
+    } else if (p.split.n_ranks > 1) {  // fused all-gather: this CTA's slice is on its way to every rank; the last CTA exchanges flags
         bar_sync_named(1, NWC * 32);
         if (w == 0) split_complete(p.split, gridDim.x * gridDim.y);
     }

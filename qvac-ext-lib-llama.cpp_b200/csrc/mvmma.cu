@@ -31,6 +31,7 @@ struct MmaMvParams {
     const uint8_t * act_main;           // [ncols][U][272]
     const uint8_t * act_aux;            // [ncols][U][16]
     SplitParams     split;
+    SplitGeom       geom;               // split.ll: who owns which rows of mat[i]
     // MUL_MAT_ID mode (sp != nullptr): blockIdx.y = expert e; its (slot, token) pairs sp[eb[e] .. eb[e+1]) are the columns, 8 at a
     // time; pair p = t * n_used + i reads activation row t * ne11 + i % ne11 and writes dst + t * dst_ts + i * dst_is
     const int32_t * sp;                 // pairs sorted by expert (b200_mm_ids_sort)
@@ -292,6 +293,8 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
     // ==================================================================== consumers
     const int w = warp, g = lane >> 2, t = lane & 3;
     if (!by_expert) pdl_wait();  // the activation records are written by the quantizer launch before this one
+    const bool     ll = p.split.n_ranks > 1 && p.split.ll && !by_expert;
+    const uint32_t ep = ll ? ll_epoch(p.split) : 0u;
     const uint32_t am0 = smem_u32(act_m), ax0 = smem_u32(act_x);
     int stage = 0; uint32_t phase = 0;
     int parity = 0;
@@ -367,14 +370,19 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
                         const int tk = pr / p.ids.n_used, sl = pr - tk * p.ids.n_used;
                         col_off = (int64_t) tk * p.ids.dst_ts + (int64_t) sl * p.ids.dst_is;
                     }
-                    split_store(p.split, p.mat[m].dst + col_off + row, v);
+                    if (ll) ll_store(p.split, ep, p.mat[m].dst + col_off + row, v);
+                    else split_store(p.split, p.mat[m].dst + col_off + row, v);
                 }
             }
             parity ^= 1;
         }
         bar_named(1, NWC * 32);  // every warp is done with this pass's activation columns
     }
-    if (p.split.n_ranks > 1) {
+    if (ll) {
+        ll_receive(p.split, ep, p.geom, p.mat, p.n_mats, p.ncols, (int) blockIdx.x * NWC * 32 + w * 32 + lane, (int) gridDim.x * NWC * 32);
+        bar_named(1, NWC * 32);
+        if (w == 0 && lane == 0) ll_finish(p.split, ep, gridDim.x);
+    } else if (p.split.n_ranks > 1) {
         if (w == 0) split_complete(p.split, gridDim.x * gridDim.y);
     }
 }

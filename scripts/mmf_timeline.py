@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """mmf_timeline.py — device-side timeline of the prefill GEMM launches of one Llama-3-8B layer (b200_ctx_trace, no profiler):
 per launch the spread over CTAs of CTA start / set-up done + dependency resolved / first TMA issued / first stage landed /
-middle stage landed / last MMA of the first work item issued / its accumulator complete / its epilogue done, in us."""
+CTA done (every role through its span) / last MMA of the first work item issued / its accumulator complete / its epilogue done, in us."""
 import argparse
 import sys
 from pathlib import Path
@@ -58,7 +58,7 @@ def main():
     starts = np.array([tr[s, :, 0][tr[s, :, 0] > 0].min() for s in used])
     order = [used[i] for i in np.argsort(starts)]
     t0 = starts.min()
-    lines = [f"{'launch':<10}{'ctas':>5} | {'start':>13} | {'dep ok':>13} | {'tma 0':>13} | {'stage 0':>13} | {'mid stage':>13} | {'last mma':>13} | {'acc full':>13} | {'epi done':>13}"]
+    lines = [f"{'launch':<10}{'ctas':>5} | {'start':>13} | {'dep ok':>13} | {'tma 0':>13} | {'stage 0':>13} | {'cta done':>13} | {'last mma':>13} | {'acc full':>13} | {'epi done':>13}"]
     for k, s in enumerate(order):
         live = tr[s, :, 0] > 0
         cols = []
