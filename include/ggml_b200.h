@@ -187,6 +187,24 @@ typedef struct {
     void *  sync_words[8];
 } b200_row_split;
 B200_API b200_status  b200_ctx_set_row_split(b200_ctx * ctx, const b200_row_split * rs);   /* rs == NULL or n_ranks <= 1: off */
+/* Flagged-payload exchange for the decode mat-vec kernels (at most 8 activation columns, plain MUL_MAT). Instead of peer stores
+ * into dst followed by a system-scope release and a flag round trip, every result travels as ONE aligned 8-byte {value, epoch}
+ * store into a staging area on each peer, and every rank's kernel polls the staging records of the rows the other ranks own and
+ * copies them into its dst: no fence, no flag and no counter on the data path. Call after b200_ctx_set_row_split (which clears it).
+ *   stage[r]      rank r's staging area, peer-mapped like the sync words: 4 * region_bytes bytes, zero-initialised
+ *   dst_base      local address of the symmetric dst region (every dst of a split MUL_MAT lies in [dst_base, dst_base + region_bytes))
+ *   tensor_split  cumulative start fraction of every rank, rounding: the get_row_split rule (ggml-cuda.cu:786-799) that produced the
+ *                 ranks' slices; with nb1 / 4 = rows of the full matrix the kernels derive who owns which rows from it. A MUL_MAT
+ *                 whose ne01 does not match the rule, or whose dst lies outside the region, uses the flag protocol.
+ * ll == NULL switches it off. */
+typedef struct {
+    void *       stage[8];
+    const void * dst_base;
+    uint64_t     region_bytes;
+    double       tensor_split[8];
+    int32_t      rounding;
+} b200_row_split_ll;
+B200_API b200_status  b200_ctx_set_row_split_ll(b200_ctx * ctx, const b200_row_split_ll * ll);
 /* Deferred mode: a decode mat-vec kernel publishes its epoch to the peers and returns without waiting for theirs; the wait moves into
  * the prologue of the next kernel of the context (behind its weight prefetch) and into every entry point that reads results or
  * synchronizes (memcpy, event record, synchronize run b200_ctx_row_split_wait first). A caller that lets anything else consume a

@@ -31,7 +31,7 @@ EXPORTS = [
     "b200_event_create", "b200_event_destroy", "b200_event_record", "b200_event_wait", "b200_event_synchronize",
     "b200_event_elapsed_ms", "b200_quantize_q8_0", "b200_quantize_q8_1", "b200_quantize_q8_K", "b200_quantize_units",
     "b200_mul_mat_supported", "b200_mul_mat", "b200_mul_mat_shared_src1", "b200_mul_mat_host", "b200_mul_mat_id_supported",
-    "b200_mul_mat_id", "b200_mm_ids_sort", "b200_ctx_set_row_split", "b200_ctx_set_row_split_deferred", "b200_ctx_row_split_wait", "b200_ctx_set_weight_cache", "b200_ctx_set_mmq_f16", "b200_ctx_set_prefetch", "b200_ctx_trace", "b200_ctx_trace_read", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
+    "b200_mul_mat_id", "b200_mm_ids_sort", "b200_ctx_set_row_split", "b200_ctx_set_row_split_ll", "b200_ctx_set_row_split_deferred", "b200_ctx_row_split_wait", "b200_ctx_set_weight_cache", "b200_ctx_set_mmq_f16", "b200_ctx_set_prefetch", "b200_ctx_trace", "b200_ctx_trace_read", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
 ]
 
 
@@ -76,6 +76,11 @@ class MulMatIdDesc(C.Structure):
 
 class RowSplit(C.Structure):
     _fields_ = [("n_ranks", C.c_int32), ("rank", C.c_int32), ("dst_delta", C.c_int64 * 8), ("sync_words", C.c_void_p * 8)]
+
+
+class RowSplitLL(C.Structure):
+    _fields_ = [("stage", C.c_void_p * 8), ("dst_base", C.c_void_p), ("region_bytes", C.c_uint64), ("tensor_split", C.c_double * 8),
+                ("rounding", C.c_int32)]
 
 
 ROW_SPLIT_ROUNDING = 128   # rows: the tensor-core kernel's tile height (the reference rounds to its mmq_y, ggml-cuda.cu:773-784)
@@ -145,6 +150,8 @@ def lib() -> C.CDLL:
         L.b200_ctx_set_row_split.argtypes = [vp, C.POINTER(RowSplit)]
         L.b200_ctx_set_weight_cache.argtypes = [vp, ci]
         L.b200_ctx_set_weight_cache.restype = None
+        L.b200_ctx_set_row_split_ll.argtypes = [vp, vp]
+        L.b200_ctx_set_row_split_ll.restype = ci
         L.b200_ctx_set_mmq_f16.argtypes = [vp, ci]
         L.b200_ctx_set_mmq_f16.restype = None
         L.b200_ctx_set_row_split_deferred.argtypes = [vp, ci]
@@ -218,6 +225,20 @@ class Context:
             rs.dst_delta[r] = int(dst_ptrs[r]) - int(dst_ptrs[rank])
             rs.sync_words[r] = int(sync_ptrs[r])
         check(lib().b200_ctx_set_row_split(self.h, C.byref(rs)), "b200_ctx_set_row_split")
+
+    def row_split_ll(self, stage_ptrs, dst_base: int, region_bytes: int, tensor_split=None, rounding: int = ROW_SPLIT_ROUNDING):
+        """flagged-payload exchange for the decode mat-vec kernels (b200_ctx_set_row_split_ll): stage_ptrs[r] = rank r's staging area
+        (4 * region_bytes bytes, zeroed, peer-mapped), dst_base / region_bytes = the local symmetric dst region. None switches it off."""
+        if stage_ptrs is None:
+            check(lib().b200_ctx_set_row_split_ll(self.h, None), "b200_ctx_set_row_split_ll")
+            return
+        n = len(stage_ptrs)
+        ll = RowSplitLL()
+        for r in range(n):
+            ll.stage[r] = int(stage_ptrs[r])
+            ll.tensor_split[r] = (r / n) if tensor_split is None else float(tensor_split[r])
+        ll.dst_base, ll.region_bytes, ll.rounding = int(dst_base), int(region_bytes), int(rounding)
+        check(lib().b200_ctx_set_row_split_ll(self.h, C.byref(ll)), "b200_ctx_set_row_split_ll")
 
     def row_split_deferred(self, enable: bool = True):
         """decode kernels publish their slice and let the next launch (or row_split_wait) wait for the peers"""

@@ -185,6 +185,7 @@ b200_status b200_ctx_set_row_split(b200_ctx * ctx, const b200_row_split * rs) {
     if (!ctx) return fail(B200_ERR_ARG, "null context");
     if (b200_status st = b200_split_flush(ctx)) return st;
     ctx->split = SplitParams{};
+    ctx->ll_on = 0;
     if (!rs || rs->n_ranks <= 1) return B200_OK;
     if (rs->n_ranks > SPLIT_MAX_RANKS || rs->rank < 0 || rs->rank >= rs->n_ranks || !rs->sync_words[rs->rank])
         return fail(B200_ERR_ARG, "bad row-split description (n_ranks=%d rank=%d)", rs->n_ranks, rs->rank);
@@ -197,6 +198,50 @@ b200_status b200_ctx_set_row_split(b200_ctx * ctx, const b200_row_split * rs) {
     }
     ctx->split.sync_local = (uint32_t *) rs->sync_words[rs->rank];
     return B200_OK;
+}
+
+b200_status b200_ctx_set_row_split_ll(b200_ctx * ctx, const b200_row_split_ll * ll) {
+    if (!ctx) return fail(B200_ERR_ARG, "null context");
+    if (b200_status st = b200_split_flush(ctx)) return st;
+    ctx->ll_on = 0;
+    if (!ll) return B200_OK;
+    const int n = ctx->split.n_ranks;
+    if (n <= 1) return fail(B200_ERR_ARG, "b200_ctx_set_row_split_ll: call b200_ctx_set_row_split first");
+    if (!ll->dst_base || ll->region_bytes == 0 || ll->region_bytes % 8 || (uintptr_t) ll->dst_base % 8 || ll->rounding < 1 || ll->tensor_split[0] != 0.0)
+        return fail(B200_ERR_ARG, "b200_ctx_set_row_split_ll: bad region / split description");
+    for (int r = 0; r < n; r++) {
+        if (!ll->stage[r] || (uintptr_t) ll->stage[r] % 8) return fail(B200_ERR_ARG, "b200_ctx_set_row_split_ll: rank %d has no (aligned) staging area", r);
+        if (r > 0 && ll->tensor_split[r] < ll->tensor_split[r - 1]) return fail(B200_ERR_ARG, "b200_ctx_set_row_split_ll: tensor_split must not decrease");
+        ctx->split.ll_stage[r]  = (char *) ll->stage[r];
+        ctx->ll_tensor_split[r] = ll->tensor_split[r];
+    }
+    ctx->split.ll_base = (const char *) ll->dst_base;
+    ctx->split.ll_half = 2 * ll->region_bytes;
+    ctx->ll_region     = ll->region_bytes;
+    ctx->ll_rounding   = ll->rounding;
+    ctx->ll_on         = 1;
+    return B200_OK;
+}
+
+bool b200_split_ll_geom(const b200_ctx * ctx, int n_mats, const int64_t * Ms, float * const * dsts, const int64_t * dst_cs, int ncols, SplitGeom * g) {
+    const SplitParams & sp = ctx->split;
+    if (sp.n_ranks <= 1 || !ctx->ll_on || ctx->split_deferred || n_mats > 4) return false;
+    for (int i = 0; i < n_mats; i++) {
+        const int64_t Mf = dst_cs[i];
+        if (Mf < Ms[i] || Mf > INT32_MAX) return false;
+        for (int r = 0; r < sp.n_ranks; r++) {  // get_row_split (ggml-cuda.cu:786-799): cumulative fractions, rounded down, the last rank takes the rest
+            int64_t lo = r == 0 ? 0 : (int64_t) ((double) Mf * ctx->ll_tensor_split[r]);
+            lo -= lo % ctx->ll_rounding;
+            g->lo[i][r] = (int) lo;
+        }
+        g->lo[i][sp.n_ranks] = (int) Mf;
+        for (int r = sp.n_ranks + 1; r <= SPLIT_MAX_RANKS; r++) g->lo[i][r] = (int) Mf;
+        const int lo = g->lo[i][sp.rank], hi = g->lo[i][sp.rank + 1];
+        if (hi - lo != Ms[i]) return false;
+        const char * first = (const char *) (dsts[i] - lo), * last = (const char *) (dsts[i] - lo + (int64_t) (ncols - 1) * dst_cs[i] + Mf);
+        if (first < sp.ll_base || last > sp.ll_base + ctx->ll_region) return false;
+    }
+    return true;
 }
 
 __global__ void split_wait_kernel(const SplitParams sp) { split_wait(sp); }
@@ -478,7 +523,9 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
             p.n_stages = cfg.ns;
             p.pdl      = ctx->pdl;
             p.split    = ctx->split;
-            if (ctx->split.n_ranks > 1) {
+            if (b200_split_ll_geom(ctx, p.n_mats, Ms + o0, dsts + o0, dst_cs + o0, c0 + nc, &p.geom)) {
+                p.split.ll = 1;  // flagged-payload exchange: no flag round trip, nothing to flush
+            } else if (ctx->split.n_ranks > 1) {
                 if (ctx->split_deferred && x) {  // src1 is read inside the kernel, behind its split_wait prologue
                     p.split.deferred   = 1;
                     ctx->split_pending = 1;

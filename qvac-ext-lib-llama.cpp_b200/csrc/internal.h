@@ -45,6 +45,10 @@ struct b200_ctx {
     int          weight_cache = 0;             // keep the int8 expansion of a weight matrix across calls (owner must invalidate)
     int          mmq_min_cols = 0;             // 0 = auto; GGML_B200_MMQ_MIN
     b200::SplitParams split = {};              // row-split all-gather fused into the kernels (b200_ctx_set_row_split)
+    int          ll_on = 0;                    // flagged-payload exchange configured (b200_ctx_set_row_split_ll)
+    double       ll_tensor_split[8] = {};
+    int          ll_rounding = 1;
+    uint64_t     ll_region = 0;
     int          split_deferred = 0;           // mat-vec kernels publish their epoch and let the NEXT launch wait (b200_ctx_set_row_split_deferred)
     int          split_pending  = 0;           // a deferred kernel was launched and nothing has waited for the peers since
     int          fuse_quant = 1;               // quantize src1 inside the mat-vec kernel when small; GGML_B200_FUSE_QUANT=0 disables
@@ -74,6 +78,11 @@ void     b200_mem_generation_bump();
 // row split, deferred mode: enqueue the wait for the peers (a one-warp kernel) if a deferred kernel is outstanding. Every entry
 // point that reads a dst, synchronizes, or launches a kernel without a split_wait prologue calls this first.
 b200_status b200_split_flush(b200_ctx * ctx);
+
+// row split, flagged-payload exchange: fills `g` with every rank's row bounds of the launch's matrices (full row count = dst_cs[i],
+// the column stride of the full dst) and returns true if the launch can use it (configured, not deferred, slices match the rule,
+// every dst inside the symmetric region)
+bool b200_split_ll_geom(const b200_ctx * ctx, int n_mats, const int64_t * Ms, float * const * dsts, const int64_t * dst_cs, int ncols, b200::SplitGeom * g);
 
 // grow-only device buffer owned by the context (fails instead of reallocating while the stream is being captured)
 b200_status b200_ensure(b200_ctx * ctx, void ** buf, size_t * cur, size_t need);

@@ -483,6 +483,7 @@ b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, cons
         p.U = U; p.ncols = ncols; p.n_cons = n_cons; p.n_stages = n_stages; p.pdl = ctx->pdl;
         p.act_main = act_main; p.act_aux = act_aux;
         p.split = ctx->split;
+        if (b200_split_ll_geom(ctx, p.n_mats, Ms + o0, dsts + o0, dst_cs + o0, ncols, &p.geom)) p.split.ll = 1;
         const int grid = tiles < ctx->sm_count ? tiles : ctx->sm_count;
         if (b200_status ast = mma_set_attr(ctx, type)) return ast;
         cudaLaunchConfig_t cfg = {};

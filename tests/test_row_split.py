@@ -175,3 +175,65 @@ def test_fused_exchange_writes_every_destination(pkg, oracle, t, N, deferred):
     finally:
         c.close()
     assert oracle.nmse(oracle.mul_mat(t, W, X), ref) <= (NMSE_TIGHT if N <= 8 else 1e-6)   # N > 8: fp16-operand prefill GEMM
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("t,N,graph", [(Q4_K, 1, False), (Q4_K, 1, True), (Q4_0, 2, False), (Q8_0, 1, False), (Q4_K, 5, True), (Q4_0, 8, False)])
+def test_flagged_payload_exchange_loopback(pkg, oracle, t, N, graph):
+    """rank 0 of a 2-rank split on ONE GPU with the flagged-payload exchange (b200_ctx_set_row_split_ll). The 'peer' staging area is
+    this rank's own, shifted by the byte distance between a row of rank 0 and the same row of rank 1 - so the {value, epoch} records
+    rank 0 sends land exactly where it polls for rank 1's rows: after every launch the lower half of the full dst must equal the
+    upper half, bit for bit, over several launches (both epoch parities) and through CUDA-graph replays (epochs live on the device)."""
+    import torch
+    from oracle.pyoracle import RefQuant, have_ref
+
+    def cu(a):
+        return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+    if not have_ref() and t == Q4_K:
+        pytest.skip("q4_K weights need oracle/_ref")
+    rng = np.random.default_rng(77 + t + N)
+    Ml, K = 384, 1024
+    Mf = 2 * Ml
+    w = rng.uniform(-1, 1, (Ml, K)).astype(np.float32)
+    W = RefQuant().quantize_weights(t, w) if have_ref() else oracle.quantize("q4_0" if t == Q4_0 else "q8_0", w)
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        c = pkg.Context(0)                      # bound to `stream` (graph capture needs a non-default stream)
+        try:
+            Wd = cu(W)
+            region = N * Mf                                                         # floats: the full dst [N][Mf]
+            pool = torch.zeros(region + 64, dtype=torch.float32, device="cuda")     # [full dst][sync words x2]
+            stage = torch.zeros(4 * region + 2 * Ml, dtype=torch.float32, device="cuda")
+            xs = [cu(rng.uniform(-1, 1, (N, K)).astype(np.float32)) for _ in range(5)]
+            refs = [c.mul_mat(t, Wd, xv).cpu().numpy() for xv in xs]                # the same kernel without the split
+            base = pool.data_ptr()
+            s0, s1 = base + 4 * region, base + 4 * region + 128
+            c.row_split(0, [base, base], [s0, s1])
+            c.row_split_ll([stage.data_ptr(), stage.data_ptr() + 8 * Ml], base, 4 * region, rounding=1)
+            out = pool[:region].view(N, Mf)[:, :Ml]
+            d = pkg.MulMatDesc.contiguous(t, Ml, K, N)
+            d.nb1, d.nb2, d.nb3 = 4 * Mf, 4 * Mf * N, 4 * Mf * N
+            x = torch.empty_like(xs[0])
+            run = lambda: c.mul_mat(t, Wd, x, out=out, desc=d)   # noqa: E731
+            if graph:
+                x.copy_(xs[0])
+                run()
+                stream.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=stream):
+                    run()
+                run = g.replay
+            for rep, xv in enumerate(xs):
+                x.copy_(xv)
+                pool[:region].zero_()
+                run()
+                stream.synchronize()
+                full = pool[:region].view(N, Mf).cpu().numpy()
+                assert np.array_equal(full[:, :Ml], refs[rep]), f"own rows differ at launch {rep}"
+                assert np.array_equal(full[:, Ml:], refs[rep]), f"received rows differ at launch {rep}"
+            words = pool[region:].view(torch.int32).cpu().numpy()
+            assert words[9] == 0 and words[8] >= len(xs)                            # CTA counter reset, epoch counted on the device
+            assert words[32] == 0                                                   # no flag was published: the data carried the epoch
+        finally:
+            c.close()
