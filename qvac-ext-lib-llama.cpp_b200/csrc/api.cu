@@ -489,7 +489,7 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
     const int U = (int) (K / 256);
     for (int c0 = 0; c0 < ncols;) {
         int     nc = ncols - c0 < MV_MAX_COLS ? ncols - c0 : MV_MAX_COLS;
-        if (!x && ctx->mma_min_cols > 0 && nc >= ctx->mma_min_cols && mv_mma_usable(type)) {  // 3..8 columns: tensor-core mat-vec (mvmma.cu)
+        if (!x && ctx->mma_min_cols > 0 && nc >= ctx->mma_min_cols && mv_mma_usable(type) && mv_mma_fits(type, K)) {  // 3..8 columns: tensor-core mat-vec (mvmma.cu)
             float * ds[MV_MAX_MATS * 8];
             for (int i = 0; i < n_ops; i++) ds[i] = dsts[i] + (int64_t) c0 * dst_cs[i];
             b200_status st = b200_mv_mma_run(ctx, type, K, n_ops, ws, nb01s, Ms, ds, dst_cs, nc, act_main + (size_t) c0 * U * ACT_MAIN,
@@ -593,6 +593,18 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
     for (int i = 0; i < n_ops && mmq; i++) mmq = b200_mmq_usable(type, K, src0s[i], descs[i].nb01);
     if (mmq) {
         if (b200_status fst = b200_split_flush(ctx)) return fst;
+        if (n_ops > 1 && d.ne12 == 1 && d.ne13 == 1) {  // q/k/v, gate/up: one launch for the whole group when every expansion is cached
+            const void * ws[MV_MAX_MATS]; size_t nb01s[MV_MAX_MATS]; int64_t Ms[MV_MAX_MATS], ldcs[MV_MAX_MATS];
+            bool plain = n_ops <= MV_MAX_MATS;
+            for (int i = 0; i < n_ops && plain; i++) {
+                plain = descs[i].ne12 == 1 && descs[i].ne13 == 1 && descs[i].ne02 == 1 && descs[i].ne03 == 1;
+                ws[i] = src0s[i]; nb01s[i] = descs[i].nb01; Ms[i] = descs[i].ne01; ldcs[i] = (int64_t) (descs[i].nb1 / 4);
+            }
+            if (plain) {
+                const b200_status gst = b200_mmq_run_group(ctx, type, n_ops, ws, nb01s, Ms, K, src1, d.nb11, N, dsts, ldcs);
+                if (gst != B200_ERR_UNSUPPORTED) return gst;
+            }
+        }
         for (int i = 0; i < n_ops; i++) {
             const b200_mul_mat_desc & di = descs[i];
             const int64_t r2 = di.ne12 / di.ne02, r3 = di.ne13 / di.ne03;

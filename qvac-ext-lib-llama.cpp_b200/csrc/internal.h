@@ -88,7 +88,7 @@ bool b200_split_ll_geom(const b200_ctx * ctx, int n_mats, const int64_t * Ms, fl
 b200_status b200_ensure(b200_ctx * ctx, void ** buf, size_t * cur, size_t need);
 
 // mvmma.cu: the IMMA mat-vec kernel for 3..8 columns (q4_0, q4_K)
-namespace b200 { bool mv_mma_usable(int type); }
+namespace b200 { bool mv_mma_usable(int type); bool mv_mma_fits(int type, int64_t K); }
 b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, const uint8_t * const * ws, const size_t * nb01s, const int64_t * Ms,
                             float * const * dsts, const int64_t * dst_cs, int ncols, const uint8_t * act_main, const uint8_t * act_aux);
 
@@ -98,6 +98,9 @@ b200_status b200_mv_mma_run_ids(b200_ctx * ctx, int type, int64_t K, const uint8
 
 // mmq.cu: the tcgen05 int8 tile kernel
 bool        b200_mmq_usable(int type, int64_t K, const void * w, size_t nb01);
+// several matrices sharing src1 in one launch (kind::f16 path, weight cache on, every expansion cached); B200_ERR_UNSUPPORTED = loop
+b200_status b200_mmq_run_group(b200_ctx * ctx, int type, int n_ops, const void * const * ws, const size_t * nb01s, const int64_t * Ms, int64_t K,
+                               const float * x, size_t x_rs, int64_t N, float * const * dsts, const int64_t * ldcs);
 // act_shared: this call belongs to a group of MUL_MATs that read the same src1 (b200_mul_mat_shared_src1) and is not the group's first:
 // the fp16 activation operand built by the previous call of the group is still in scratch and is used as it is
 b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, int64_t M, int64_t K, const float * x, size_t x_rs, int64_t N,

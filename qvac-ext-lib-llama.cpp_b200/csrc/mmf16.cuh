@@ -236,12 +236,19 @@ __global__ void __launch_bounds__(256) act_f16_kernel(const float * __restrict__
 
 // ------------------------------------------------------------------------------------------------ the GEMM (K5)
 
+constexpr int F_MAX_MATS = 4;  // weight matrices of one launch (MUL_MATs that read the same src1: q/k/v, gate/up)
+struct MmfMaps {
+    CUtensorMap a[F_MAX_MATS];
+};
 struct MmfParams {
     SplitParams   split;
-    float *       dst;
-    int64_t       ldc;  // floats between dst columns (tokens)
+    float *       dst[F_MAX_MATS];
+    int64_t       ldc[F_MAX_MATS];    // floats between dst columns (tokens)
+    int           Mi[F_MAX_MATS];     // rows of matrix i
+    int           tile0[F_MAX_MATS];  // first tile of matrix i in the launch's tile order (INT_MAX for unused slots)
+    int           n_mats;
     const float * rs;   // [N] 2^e[n]
-    int           M, N, K;
+    int           N, K;
     int           n_tiles, k_stages;
     long long     units;   // tiles x k_stages
     float *       ws;      // [gridDim.x][2][BN][128] partial accumulators of cut tiles (slot 1: the K-range that starts at 0)
@@ -256,7 +263,7 @@ struct MmfParams {
 
 template <int BN>
 __global__ void __launch_bounds__(F_THREADS, 1)
-mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const MmfParams p) {
+mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ MmfParams p) {
     constexpr int STAGES = f_stages(BN), SLOTS = 2;
     constexpr int B_BYTES = f_b_bytes(BN), STAGE_BYTES = F_A_BYTES + B_BYTES;
     extern __shared__ uint8_t smem_raw[];
@@ -285,7 +292,7 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
             mbar_init(smem_u32(tempty + i), F_EPI_WARPS);
         }
         fence_mbar_init();
-        tma_prefetch_desc(&map_a);
+        for (int i = 0; i < p.n_mats; i++) tma_prefetch_desc(&maps.a[i]);
         tma_prefetch_desc(&map_b);
     }
     if (warp == 1) tmem_alloc<SLOTS * BN>(smem_u32(tmem_slot));
@@ -299,14 +306,22 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
     // one (tile, K-stage) unit after the other of this CTA's span
     struct Cursor {
         long long u;
-        int       ks, k1, m0, n0;
+        int       ks, k1, m0, n0, mat;
+    };
+    auto mat_of = [&](int tile) {  // which matrix of the launch a tile belongs to
+        int i = 0;
+#pragma unroll
+        for (int j = 1; j < F_MAX_MATS; j++) if (tile >= p.tile0[j]) i = j;
+        return i;
     };
     auto open_item = [&](Cursor & c) {
         const int tile = (int) (c.u / KS);
         c.ks = (int) (c.u - (long long) tile * KS);
         c.k1 = (int) min((long long) KS, c.ks + (u_end - c.u));
-        c.m0 = (tile / p.n_tiles) * F_BM;
-        c.n0 = (tile % p.n_tiles) * BN;
+        c.mat = mat_of(tile);
+        const int lt = tile - p.tile0[c.mat];
+        c.m0 = (lt / p.n_tiles) * F_BM;
+        c.n0 = (lt % p.n_tiles) * BN;
     };
     auto step = [&](Cursor & c) {
         c.u++;
@@ -326,7 +341,7 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
             for (; npre < STAGES && ca.u < u_end; npre++, step(ca)) {
                 const uint32_t bar = smem_u32(full + npre);
                 mbar_expect_tx(bar, STAGE_BYTES);
-                tma_load_2d(smem_u32(smem + npre * STAGE_BYTES), &map_a, ca.ks * F_BK, ca.m0, bar);
+                tma_load_2d(smem_u32(smem + npre * STAGE_BYTES), &maps.a[ca.mat], ca.ks * F_BK, ca.m0, bar);
             }
             MMF_TRACE(2);
             if (p.early_a) asm volatile("griddepcontrol.wait;" ::: "memory");  // the activations are the previous kernel's output
@@ -335,12 +350,12 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
             }
             int stage = npre == STAGES ? 0 : npre; uint32_t phase = npre == STAGES ? 0 : 1;
             for (; c.u < u_end; step(c)) {
-                if (p.pf > 0 && c.ks + p.pf < c.k1) tma_prefetch_l2_2d(&map_a, (c.ks + p.pf) * F_BK, c.m0);
+                if (p.pf > 0 && c.ks + p.pf < c.k1) tma_prefetch_l2_2d(&maps.a[c.mat], (c.ks + p.pf) * F_BK, c.m0);
                 mbar_wait(smem_u32(empty + stage), phase);
                 const uint32_t bar = smem_u32(full + stage);
                 const uint32_t st  = smem_u32(smem + stage * STAGE_BYTES);
                 mbar_expect_tx(bar, STAGE_BYTES);
-                tma_load_2d(st, &map_a, c.ks * F_BK, c.m0, bar);
+                tma_load_2d(st, &maps.a[c.mat], c.ks * F_BK, c.m0, bar);
                 tma_load_2d(st + F_A_BYTES, &map_b, c.ks * F_BK, c.n0, bar);
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
@@ -388,7 +403,8 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
         for (long long u = u_begin; u < u_end;) {
             const int tile = (int) (u / KS), k0 = (int) (u - (long long) tile * KS);
             const int k1 = (int) min((long long) KS, k0 + (u_end - u));
-            const int m0 = (tile / p.n_tiles) * F_BM, n0 = (tile % p.n_tiles) * BN;
+            const int mi = mat_of(tile), lt = tile - p.tile0[mi];
+            const int m0 = (lt / p.n_tiles) * F_BM, n0 = (lt % p.n_tiles) * BN;
             const int m  = m0 + row;
             mbar_wait(smem_u32(tfull + slot), tphase);
             tc_fence_after();
@@ -427,7 +443,7 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; j++) v[j] = __uint_as_float(c[j]) * __shfl_sync(0xffffffffu, rsv, j);
-                    if (m < p.M) split_store_cols32(p.split, p.dst + (int64_t) nb * p.ldc + m, p.ldc, v, p.N - nb);
+                    if (m < p.Mi[mi]) split_store_cols32(p.split, p.dst[mi] + (int64_t) nb * p.ldc[mi] + m, p.ldc[mi], v, p.N - nb);
                 }
                 tc_fence_before();
                 __syncwarp();
@@ -441,7 +457,11 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
         // data) for its own share of the tile's columns and stores that share - the fix-up of a tile cut P ways runs on P SMs
         for (int r = 0; r < n_cut; r++) {
             const int tile = cut_tile[r];
-            const int m0 = (tile / p.n_tiles) * F_BM, n0 = (tile % p.n_tiles) * BN;
+            const int mi = mat_of(tile), lt = tile - p.tile0[mi];
+            const int m0 = (lt / p.n_tiles) * F_BM, n0 = (lt % p.n_tiles) * BN;
+            const int     M_ = p.Mi[mi];
+            const int64_t ldc_ = p.ldc[mi];
+            float * const dst_ = p.dst[mi];
             const int h  = (int) ((((long long) tile * KS + 1) * G + p.units - 1) / p.units) - 1;
             const int l  = (int) ((((long long) (tile + 1) * KS) * G + p.units - 1) / p.units) - 1;
             const int P  = l - h + 1, me = (int) blockIdx.x - h;
@@ -454,7 +474,7 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
             __syncwarp();
             const int c_lo = BN * me / P, c_hi = BN * (me + 1) / P;
             const int n_pos = (c_hi - c_lo) * 32;  // positions of 4 consecutive rows (16 bytes) of one column
-            const bool vec = p.split.n_ranks <= 1 && (p.ldc & 3) == 0 && ((uintptr_t) p.dst & 15) == 0;
+            const bool vec = p.split.n_ranks <= 1 && (ldc_ & 3) == 0 && ((uintptr_t) dst_ & 15) == 0;
             const size_t slot_floats = (size_t) BN * F_BM;
             // a thread keeps NP positions x JB parts in flight: the sums are L2-latency bound otherwise (2 loads per round trip
             // made this phase 20 us). Few parts: many positions at once; many parts: many parts at once.
@@ -490,18 +510,18 @@ mmf_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
                         const int pos = pos0 + i * 32 * F_EPI_WARPS;
                         if (pos >= n_pos) continue;
                         const int n = n0 + c_lo + (pos >> 5), m = m0 + 4 * (pos & 31);
-                        if (n >= p.N || m >= p.M) continue;
+                        if (n >= p.N || m >= M_) continue;
                         const float rsv = __ldg(p.rs + n);
                         float4 a = acc[i];
                         a.x *= rsv; a.y *= rsv; a.z *= rsv; a.w *= rsv;
-                        float * d = p.dst + (int64_t) n * p.ldc + m;
-                        if (vec && m + 3 < p.M) {
+                        float * d = dst_ + (int64_t) n * ldc_ + m;
+                        if (vec && m + 3 < M_) {
                             *(float4 *) d = a;
                         } else {
                             split_store(p.split, d, a.x);
-                            if (m + 1 < p.M) split_store(p.split, d + 1, a.y);
-                            if (m + 2 < p.M) split_store(p.split, d + 2, a.z);
-                            if (m + 3 < p.M) split_store(p.split, d + 3, a.w);
+                            if (m + 1 < M_) split_store(p.split, d + 1, a.y);
+                            if (m + 2 < M_) split_store(p.split, d + 2, a.z);
+                            if (m + 3 < M_) split_store(p.split, d + 3, a.w);
                         }
                     }
                 }
@@ -538,14 +558,13 @@ int mmf_env(const char * name, int dflt) {
 }
 
 template <int BN>
-b200_status mmf_launch(b200_ctx * ctx, const CUtensorMap & map_a, const CUtensorMap & map_b, MmfParams & p, int m_tiles) {
+b200_status mmf_launch(b200_ctx * ctx, const MmfMaps & maps, const CUtensorMap & map_b, MmfParams & p, int tiles) {
     static bool attr_done[64] = {};
     if (ctx->device < 64 && !attr_done[ctx->device]) {
         CU(cudaFuncSetAttribute(mmf_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, f_smem(BN)));
         attr_done[ctx->device] = true;
     }
     static const int env_sk = mmf_env("GGML_B200_MMF_STREAMK", 1), env_min = mmf_env("GGML_B200_MMF_MIN_SPAN", 8);
-    const int tiles = m_tiles * p.n_tiles;
     p.units = (long long) tiles * p.k_stages;
     int grid;
     if (env_sk) {  // equal spans of at least env_min stages
@@ -576,16 +595,17 @@ b200_status mmf_launch(b200_ctx * ctx, const CUtensorMap & map_a, const CUtensor
     cfg.stream           = ctx->stream;
     cfg.attrs            = attr;
     cfg.numAttrs         = ctx->pdl ? 1 : 0;
-    CU(cudaLaunchKernelEx(&cfg, mmf_kernel<BN>, map_a, map_b, p));
+    CU(cudaLaunchKernelEx(&cfg, mmf_kernel<BN>, maps, map_b, p));
     ctx->launches++;
     return B200_OK;
 }
 
-// dst[n*ldc + m] = sum_k W[m][k] * X[n][k]: e holds the fp16 weights, h / rs are scratch for the fp16 activations and 2^e[n]
+// dst_i[n*ldc_i + m] = sum_k W_i[m][k] * X[n][k] for the n_mats matrices es[i] (fp16 expansions, same type and K) in ONE launch:
+// h / rs are scratch for the fp16 activations and 2^e[n]
 // have_act: h / rs already hold this src1 (an earlier matrix of the same shared-src1 group built them): no quantizer launch
-b200_status mmf_run(b200_ctx * ctx, WEntry * e, bool settled, const float * x, size_t x_rs, int64_t N, __half * h, float * rs, float * dst, int64_t ldc,
-                    bool have_act) {
-    const int64_t M = e->M, K = e->K;
+b200_status mmf_run(b200_ctx * ctx, int n_mats, WEntry * const * es, bool settled, const float * x, size_t x_rs, int64_t N, __half * h, float * rs,
+                    float * const * dsts, const int64_t * ldcs, bool have_act) {
+    const int64_t K = es[0]->K;
     const int     vec_ok = ((uintptr_t) x % 16 == 0) && (x_rs % 16 == 0);
     for (int64_t r0 = 0; r0 < N && !have_act; r0 += 1 << 30) {
         const int64_t nr = N - r0 < (1 << 30) ? N - r0 : (1 << 30);
@@ -600,7 +620,7 @@ b200_status mmf_run(b200_ctx * ctx, WEntry * e, bool settled, const float * x, s
         cfg.attrs    = attr;
         cfg.numAttrs = ctx->pdl ? 1 : 0;
         const int64_t units = (K + 255) / 256;
-        const bool    k8    = e->type == B200_TYPE_Q4_K;
+        const bool    k8    = es[0]->type == B200_TYPE_Q4_K;
 #define ACT_LAUNCH(UPW) (k8 ? cudaLaunchKernelEx(&cfg, act_f16_kernel<ACT_KIND_Q8_K, UPW>, xs, K, x_rs, h + r0 * K, rs + r0, vec_ok) \
                             : cudaLaunchKernelEx(&cfg, act_f16_kernel<ACT_KIND_Q8_0, UPW>, xs, K, x_rs, h + r0 * K, rs + r0, vec_ok))
         if (units <= 16)      CU(ACT_LAUNCH(2));
@@ -612,18 +632,33 @@ b200_status mmf_run(b200_ctx * ctx, WEntry * e, bool settled, const float * x, s
     }
 
     static const int env_bn = mmf_env("GGML_B200_MMF_BN", 0), env_pf = mmf_env("GGML_B200_MMF_PF", 0);
-    const int m_tiles = (int) ((M + F_BM - 1) / F_BM);
     const int bn = env_bn ? env_bn : (N <= 128 ? 128 : 256);
     MmfParams p;
+    MmfMaps   maps;
+    memset(&maps, 0, sizeof(maps));
     p.split = ctx->split;
-    p.dst = dst; p.ldc = ldc; p.rs = rs; p.M = (int) M; p.N = (int) N; p.K = (int) K;
+    p.rs = rs; p.N = (int) N; p.K = (int) K;
     p.n_tiles  = (int) ((N + bn - 1) / bn);
     p.k_stages = (int) ((K + F_BK - 1) / F_BK);
     p.pf       = env_pf;
     p.early_a  = settled;
+    p.n_mats   = n_mats;
+    int tiles = 0;
+    for (int i = 0; i < F_MAX_MATS; i++) {
+        if (i < n_mats) {
+            maps.a[i]  = es[i]->map_q;
+            p.dst[i]   = dsts[i];
+            p.ldc[i]   = ldcs[i];
+            p.Mi[i]    = (int) es[i]->M;
+            p.tile0[i] = tiles;
+            tiles += (int) ((es[i]->M + F_BM - 1) / F_BM) * p.n_tiles;
+        } else {
+            p.dst[i] = nullptr; p.ldc[i] = 0; p.Mi[i] = 0; p.tile0[i] = INT32_MAX;
+        }
+    }
     CUtensorMap map_b;
     if (!make_map(&map_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, h, (uint64_t) K, (uint64_t) N, (uint64_t) K * 2, F_BK, (uint32_t) bn, true)) {
         return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the fp16 activations (N=%lld K=%lld)", (long long) N, (long long) K);
     }
-    return bn == 256 ? mmf_launch<256>(ctx, e->map_q, map_b, p, m_tiles) : mmf_launch<128>(ctx, e->map_q, map_b, p, m_tiles);
+    return bn == 256 ? mmf_launch<256>(ctx, maps, map_b, p, tiles) : mmf_launch<128>(ctx, maps, map_b, p, tiles);
 }

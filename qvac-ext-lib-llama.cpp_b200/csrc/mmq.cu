@@ -838,7 +838,9 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
         const bool have_act = act_shared && ctx->act_x == x && ctx->act_rs == x_rs && ctx->act_N == N && ctx->act_K == K && ctx->act_buf == s2 &&
                               ctx->act_kind == kind;
         ctx->act_x = x; ctx->act_rs = x_rs; ctx->act_N = N; ctx->act_K = K; ctx->act_buf = s2; ctx->act_kind = kind;
-        return mmf_run(ctx, e, cached && e->settled, x, x_rs, N, (__half *) s2, (float *) (s2 + hb), dst, ldc, have_act);
+        WEntry * es[1] = { e };
+        float *  ds[1] = { dst };
+        return mmf_run(ctx, 1, es, cached && e->settled, x, x_rs, N, (__half *) s2, (float *) (s2 + hb), ds, &ldc, have_act);
     }
     ctx->act_x = nullptr;
 
@@ -901,4 +903,35 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
     CU(cudaGetLastError());
     ctx->launches++;
     return B200_OK;
+}
+
+// Several weight matrices (same type and K) against the same N activation rows in ONE launch of the kind::f16 GEMM: one activation
+// conversion, one pipeline fill / drain and one stream-K fix-up for q/k/v or gate/up. Only with the weight cache on (every
+// matrix's fp16 expansion must be alive at the same time); returns B200_ERR_UNSUPPORTED when the caller should loop instead.
+b200_status b200_mmq_run_group(b200_ctx * ctx, int type, int n_ops, const void * const * ws, const size_t * nb01s, const int64_t * Ms, int64_t K,
+                               const float * x, size_t x_rs, int64_t N, float * const * dsts, const int64_t * ldcs) {
+    if (!ctx->mmq_f16 || !ctx->weight_cache || n_ops < 2 || n_ops > F_MAX_MATS || N <= 0) return B200_ERR_UNSUPPORTED;
+    for (int i = 0; i < n_ops; i++) if (Ms[i] <= 0 || Ms[i] > INT32_MAX - BM || N > INT32_MAX - BN || K > INT32_MAX - 128) return B200_ERR_UNSUPPORTED;
+    static const int env_group = mmf_env("GGML_B200_MMF_GROUP", 1);
+    if (!env_group) return B200_ERR_UNSUPPORTED;
+    WEntry * es[F_MAX_MATS];
+    bool     settled = true;
+    for (int i = 0; i < n_ops; i++) {
+        WEntry * e = nullptr;
+        {
+            std::lock_guard<std::mutex> lock(g_wmutex);
+            auto it = g_wcache.find(WKey{ ctx->device, ws[i] });
+            if (it != g_wcache.end() && it->second->type == type && it->second->M == Ms[i] && it->second->K == K && it->second->nb01 == nb01s[i] &&
+                it->second->f16)
+                e = it->second;
+        }
+        if (!e) return B200_ERR_UNSUPPORTED;  // not expanded yet: the per-matrix path fills the cache (first call of a tensor)
+        settled = settled && e->settled;
+        es[i] = e;
+    }
+    const size_t hb = ((size_t) N * K * 2 + 255) & ~(size_t) 255, rb = ((size_t) N * 4 + 255) & ~(size_t) 255;
+    if (b200_status st = b200_ensure(ctx, &ctx->scratch2, &ctx->scratch2_size, hb + rb)) return st;
+    uint8_t * s2 = (uint8_t *) ctx->scratch2;
+    ctx->act_x = nullptr;
+    return mmf_run(ctx, n_ops, es, settled, x, x_rs, N, (__half *) s2, (float *) (s2 + hb), dsts, ldcs, false);
 }

@@ -410,6 +410,9 @@ size_t mv_mma_smem(int type, int U, int n_cons, int n_stages) {
     return off + (size_t) n_stages * n_cons * MMA_ROWS * unit_bytes(type) + 1024;
 }
 
+// the 8 activation columns of a K-long row plus a minimal ring must fit in shared memory (K = 28672 does not: 258 KB of activations)
+bool mv_mma_fits(int type, int64_t K) { return mv_mma_smem(type, (int) (K / 256), 4, 2) <= 227 * 1024; }
+
 bool mv_mma_usable(int type) {
     return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0) && mma_get_encode() != nullptr;
 }

@@ -218,6 +218,34 @@ def test_shared_src1_fusion(ctx, oracle, t):
 
 
 @pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
+@pytest.mark.parametrize("N", [40, 300])
+def test_shared_src1_prefill_group(pkg, oracle, t, N):
+    """more than 8 columns and several matrices that read the same src1 (q/k/v, gate/up) with the weight cache on: the first call
+    expands every matrix (per-matrix launches, one shared activation operand), later calls run ONE grouped launch of the kind::f16
+    GEMM (tiles of all matrices in one stream-K schedule). Both must match the per-matrix results bit for bit and the oracle."""
+    rng = np.random.default_rng(90 + t + N)
+    K = 1024
+    Ws = [quantize_weights(oracle, t, rng.uniform(-1, 1, (M, K)).astype(np.float32)) for M in (640, 130, 128, 257)]
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    Wd, Xd = [cu(W) for W in Ws], cu(X)
+    c = pkg.Context(0)
+    try:
+        c.weight_cache(True)
+        single = [c.mul_mat(t, W, Xd).cpu().numpy() for W in Wd]
+        first = [o.cpu().numpy() for o in c.mul_mat_shared(t, Wd, Xd)]
+        grouped = [o.cpu().numpy() for o in c.mul_mat_shared(t, Wd, Xd)]
+        again = [o.cpu().numpy() for o in c.mul_mat_shared(t, Wd[:2], Xd)]
+        for i, W in enumerate(Ws):
+            assert oracle.nmse(oracle.mul_mat(t, W, X), grouped[i]) <= 1e-6
+            assert np.allclose(first[i], single[i], rtol=0, atol=0) or oracle.nmse(single[i], first[i]) <= 1e-12
+            assert oracle.nmse(single[i], grouped[i]) <= 1e-12   # the K split of a tile may differ between schedules: fp32 order only
+        assert oracle.nmse(single[1], again[1]) <= 1e-12
+    finally:
+        c.weight_cache_clear()
+        c.close()
+
+
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
 def test_decode_weight_prefetch_changes_nothing(pkg, oracle, t):
     """b200_ctx_set_prefetch: a repeating chain of mat-vecs (what a decode step is) with the next kernel's weights pulled into
     L2 by the current one. Same bits as without it; a chain that changes under the predictor (wrong predictions) too."""
