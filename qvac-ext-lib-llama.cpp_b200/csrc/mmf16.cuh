@@ -34,8 +34,8 @@ constexpr int F_EPI_WARPS = 8, F_FIRST_EPI = 4;
 constexpr int F_THREADS = 32 * (F_FIRST_EPI + F_EPI_WARPS);
 constexpr int F_A_BYTES = F_BM * 128;
 __host__ __device__ constexpr int f_b_bytes(int bn) { return bn * 128; }
-__host__ __device__ constexpr int f_stages(int bn) { return bn == 256 ? 4 : 6; }
-__host__ __device__ constexpr int f_smem(int bn) { return 1024 + f_stages(bn) * (F_A_BYTES + f_b_bytes(bn)) + 256; }
+__host__ __device__ constexpr int f_stages(int bn, int cl = 1) { return bn / cl == 256 ? 4 : 6; }
+__host__ __device__ constexpr int f_smem(int bn, int cl = 1) { return 1024 + f_stages(bn, cl) * (F_A_BYTES + f_b_bytes(bn / cl)) + 256; }
 
 // ---- instruction descriptor for kind::f16: D = f32 ([4,6) = 1), A and B fp16 ([7,10) = [10,13) = 0), both K-major
 __host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N) { return (1u << 4) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (M >> 4) << 24); }
@@ -48,6 +48,69 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint6
         "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// ---- CTA pair (cta_group::2): one tcgen05.mma spans two SMs - M = 256 (128 rows of A from each CTA), N = 256 with each CTA holding
+// half of the B rows - so an SM ingests 16 + 16 KB per K stage instead of 16 + 32 KB for the same 128 x 256 x 64 MACs
+template <int CL>
+__device__ __forceinline__ void umma_f16_cl(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    if (CL == 1) {
+        umma_f16(d_tmem, a_desc, b_desc, idesc, accumulate);
+    } else {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+            "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+            : "memory");
+    }
+}
+template <int CL>
+__device__ __forceinline__ void umma_commit_cl(uint32_t bar) {  // CL == 2: arrives on the barrier at this offset in BOTH CTAs of the pair
+    if (CL == 1) {
+        umma_commit(bar);
+    } else {
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"((uint16_t) 3)
+                     : "memory");
+    }
+}
+// TMA load whose completion bytes go to the barrier `bar` (a shared::cluster address: the LEADER CTA's barrier for a pair)
+template <int CL>
+__device__ __forceinline__ void tma_load_2d_cl(uint32_t dst, const void * tmap, int c0, int c1, uint32_t bar) {
+    if (CL == 1) {
+        tma_load_2d(dst, tmap, c0, c1, bar);
+    } else {
+        asm volatile(
+            "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+            "l"(tmap), "r"(c0), "r"(c1), "r"(bar)
+            : "memory");
+    }
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t mapa_cta(uint32_t addr, uint32_t cta) {  // the same shared-memory offset in CTA `cta` of the cluster
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+template <int NCOLS>
+__device__ __forceinline__ void tmem_alloc2(uint32_t smem_dst) {  // one full warp of each CTA of the pair
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "n"(NCOLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <int NCOLS>
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(NCOLS) : "memory");
+}
+
 __device__ __forceinline__ void tma_prefetch_l2_2d(const void * tmap, int c0, int c1) {
     asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(tmap), "r"(c0), "r"(c1) : "memory");
 }
@@ -261,11 +324,16 @@ struct MmfParams {
 
 #define MMF_TRACE(i) do { if (p.trace) p.trace[(size_t) blockIdx.x * 8 + (i)] = mmf_ns(); } while (0)
 
-template <int BN>
+template <int BN, int CL>
 __global__ void __launch_bounds__(F_THREADS, 1)
 mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ MmfParams p) {
-    constexpr int STAGES = f_stages(BN), SLOTS = 2;
-    constexpr int B_BYTES = f_b_bytes(BN), STAGE_BYTES = F_A_BYTES + B_BYTES;
+    constexpr int STAGES = f_stages(BN, CL), SLOTS = 2;
+    constexpr int B_ROWS = BN / CL;  // rows of the activation tile this CTA loads (a pair: half each)
+    constexpr int B_BYTES = f_b_bytes(B_ROWS), STAGE_BYTES = F_A_BYTES + B_BYTES;
+    constexpr int TILE_M = F_BM * CL;
+    const int       crank = CL == 2 ? (int) cluster_ctarank() : 0;                 // 0 = the CTA of a pair that issues the MMAs
+    const int       bid   = CL == 2 ? (int) (blockIdx.x >> 1) : (int) blockIdx.x;  // this CTA's (pair's) place in the schedule
+    const long long G     = CL == 2 ? (long long) (gridDim.x >> 1) : (long long) gridDim.x;
     extern __shared__ uint8_t smem_raw[];
     uint8_t * smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
     uint64_t * bars      = (uint64_t *) (smem + STAGES * STAGE_BYTES);
@@ -278,8 +346,8 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int KS = p.k_stages;
     // this CTA's span of the launch's tile-major (tile, K-stage) units
-    const long long u_begin = p.whole_tiles ? (p.units / KS * blockIdx.x / gridDim.x) * KS : p.units * blockIdx.x / gridDim.x;
-    const long long u_end   = p.whole_tiles ? (p.units / KS * (blockIdx.x + 1) / gridDim.x) * KS : p.units * (blockIdx.x + 1) / gridDim.x;
+    const long long u_begin = p.whole_tiles ? (p.units / KS * bid / G) * KS : p.units * bid / G;
+    const long long u_end   = p.whole_tiles ? (p.units / KS * (bid + 1) / G) * KS : p.units * (bid + 1) / G;
 
     if (threadIdx.x == 0) {
         MMF_TRACE(0);
@@ -289,15 +357,19 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
         }
         for (int i = 0; i < SLOTS; i++) {
             mbar_init(smem_u32(tfull + i), 1);
-            mbar_init(smem_u32(tempty + i), F_EPI_WARPS);
+            mbar_init(smem_u32(tempty + i), F_EPI_WARPS * CL);  // a pair: the leader's barrier counts the epilogue warps of both CTAs
         }
         fence_mbar_init();
         for (int i = 0; i < p.n_mats; i++) tma_prefetch_desc(&maps.a[i]);
         tma_prefetch_desc(&map_b);
     }
-    if (warp == 1) tmem_alloc<SLOTS * BN>(smem_u32(tmem_slot));
+    if (warp == 1) {
+        if (CL == 2) tmem_alloc2<SLOTS * BN>(smem_u32(tmem_slot));
+        else tmem_alloc<SLOTS * BN>(smem_u32(tmem_slot));
+    }
     tc_fence_before();
-    __syncthreads();
+    if (CL == 2) cluster_sync_all();  // the peer's barriers are initialised before anything arrives on them
+    else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -320,8 +392,8 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
         c.k1 = (int) min((long long) KS, c.ks + (u_end - c.u));
         c.mat = mat_of(tile);
         const int lt = tile - p.tile0[c.mat];
-        c.m0 = (lt / p.n_tiles) * F_BM;
-        c.n0 = (lt % p.n_tiles) * BN;
+        c.m0 = (lt / p.n_tiles) * TILE_M + crank * F_BM;  // this CTA's 128 weight rows of the tile
+        c.n0 = (lt % p.n_tiles) * BN + crank * B_ROWS;    // and the activation rows it loads
     };
     auto step = [&](Cursor & c) {
         c.u++;
@@ -338,32 +410,33 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
             if (!p.early_a) asm volatile("griddepcontrol.wait;" ::: "memory");  // the fp16 weights were written on this stream just now
             Cursor ca = c;
             int npre = 0;
+            // completion bytes of both CTAs of a pair go to the leader's barrier, which expects the bytes of both
+            auto full_bar = [&](int s_) { return CL == 2 ? mapa_cta(smem_u32(full + s_), 0) : smem_u32(full + s_); };
             for (; npre < STAGES && ca.u < u_end; npre++, step(ca)) {
-                const uint32_t bar = smem_u32(full + npre);
-                mbar_expect_tx(bar, STAGE_BYTES);
-                tma_load_2d(smem_u32(smem + npre * STAGE_BYTES), &maps.a[ca.mat], ca.ks * F_BK, ca.m0, bar);
+                if (crank == 0) mbar_expect_tx(smem_u32(full + npre), CL * STAGE_BYTES);
+                tma_load_2d_cl<CL>(smem_u32(smem + npre * STAGE_BYTES), &maps.a[ca.mat], ca.ks * F_BK, ca.m0, full_bar(npre));
             }
             MMF_TRACE(2);
             if (p.early_a) asm volatile("griddepcontrol.wait;" ::: "memory");  // the activations are the previous kernel's output
             for (int i = 0; i < npre; i++, step(c)) {
-                tma_load_2d(smem_u32(smem + i * STAGE_BYTES) + F_A_BYTES, &map_b, c.ks * F_BK, c.n0, smem_u32(full + i));
+                tma_load_2d_cl<CL>(smem_u32(smem + i * STAGE_BYTES) + F_A_BYTES, &map_b, c.ks * F_BK, c.n0, full_bar(i));
             }
             int stage = npre == STAGES ? 0 : npre; uint32_t phase = npre == STAGES ? 0 : 1;
             for (; c.u < u_end; step(c)) {
                 if (p.pf > 0 && c.ks + p.pf < c.k1) tma_prefetch_l2_2d(&maps.a[c.mat], (c.ks + p.pf) * F_BK, c.m0);
                 mbar_wait(smem_u32(empty + stage), phase);
-                const uint32_t bar = smem_u32(full + stage);
+                const uint32_t bar = full_bar(stage);
                 const uint32_t st  = smem_u32(smem + stage * STAGE_BYTES);
-                mbar_expect_tx(bar, STAGE_BYTES);
-                tma_load_2d(st, &maps.a[c.mat], c.ks * F_BK, c.m0, bar);
-                tma_load_2d(st + F_A_BYTES, &map_b, c.ks * F_BK, c.n0, bar);
+                if (crank == 0) mbar_expect_tx(smem_u32(full + stage), CL * STAGE_BYTES);
+                tma_load_2d_cl<CL>(st, &maps.a[c.mat], c.ks * F_BK, c.m0, bar);
+                tma_load_2d_cl<CL>(st + F_A_BYTES, &map_b, c.ks * F_BK, c.n0, bar);
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
         // ================================================================ MMA issuer: four UTCHMMA (128 x BN x 16) per stage
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_f16(F_BM, BN);
+        if (lane == 0 && crank == 0) {
+            constexpr uint32_t idesc = umma_idesc_f16(TILE_M, BN);
             int stage = 0, slot = 0; uint32_t phase = 0, tphase = 1;
             bool first = true;
             for (long long u = u_begin; u < u_end;) {
@@ -378,12 +451,12 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
                     const uint32_t a0 = smem_u32(smem + stage * STAGE_BYTES), b0 = a0 + F_A_BYTES;
 #pragma unroll
                     for (int k = 0; k < F_BK / 16; k++) {
-                        umma_f16(tmem_base + slot * BN, umma_desc_sw128(a0 + k * 32), umma_desc_sw128(b0 + k * 32), idesc, (uint32_t) ((ks - k0) | k));
+                        umma_f16_cl<CL>(tmem_base + slot * BN, umma_desc_sw128(a0 + k * 32), umma_desc_sw128(b0 + k * 32), idesc, (uint32_t) ((ks - k0) | k));
                     }
-                    umma_commit(smem_u32(empty + stage));
+                    umma_commit_cl<CL>(smem_u32(empty + stage));
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(smem_u32(tfull + slot));
+                umma_commit_cl<CL>(smem_u32(tfull + slot));
                 if (first) { MMF_TRACE(5); first = false; }
                 if (++slot == SLOTS) { slot = 0; tphase ^= 1; }
                 u += k1 - k0;
@@ -395,7 +468,11 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
         const int quad = warp & 3, half = (warp - F_FIRST_EPI) >> 2;
         const int row  = quad * 32 + lane;
         const int te   = (warp - F_FIRST_EPI) * 32 + lane;  // 0 .. 255
-        const long long G = gridDim.x;
+        // the accumulator is free again once the epilogue warps of both CTAs of a pair have drained their halves
+        auto release_slot = [&](int slot_) {
+            if (CL == 2) mbar_arrive_cluster(mapa_cta(smem_u32(tempty + slot_), 0));
+            else mbar_arrive(smem_u32(tempty + slot_));
+        };
         int slot = 0; uint32_t tphase = 0;
         bool first = true;
         int  cut_tile[2], n_cut = 0;  // the (at most two) tiles of this span that other CTAs share: finished in phase 2
@@ -404,7 +481,7 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
             const int tile = (int) (u / KS), k0 = (int) (u - (long long) tile * KS);
             const int k1 = (int) min((long long) KS, k0 + (u_end - u));
             const int mi = mat_of(tile), lt = tile - p.tile0[mi];
-            const int m0 = (lt / p.n_tiles) * F_BM, n0 = (lt % p.n_tiles) * BN;
+            const int m0 = (lt / p.n_tiles) * TILE_M + crank * F_BM, n0 = (lt % p.n_tiles) * BN;
             const int m  = m0 + row;
             mbar_wait(smem_u32(tfull + slot), tphase);
             tc_fence_after();
@@ -424,12 +501,12 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
                 }
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(tempty + slot));
+                if (lane == 0) release_slot(slot);
                 __threadfence();
                 asm volatile("bar.sync 1, %0;" ::"n"(32 * F_EPI_WARPS) : "memory");
                 if (warp == F_FIRST_EPI && lane == 0) {
-                    const int h = (int) ((((long long) tile * KS + 1) * G + p.units - 1) / p.units) - 1;  // the CTA whose span holds the tile's first stage
-                    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.flags + h) : "memory");
+                    const int h = (int) ((((long long) tile * KS + 1) * G + p.units - 1) / p.units) - 1;  // the CTA (pair) whose span holds the tile's first stage
+                    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.flags + (CL * h + crank)) : "memory");
                 }
                 cut_tile[n_cut++] = tile;
             } else {
@@ -447,7 +524,7 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
                 }
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(tempty + slot));
+                if (lane == 0) release_slot(slot);
             }
             if (first) first = false;
             if (++slot == SLOTS) { slot = 0; tphase ^= 1; }
@@ -458,16 +535,17 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
         for (int r = 0; r < n_cut; r++) {
             const int tile = cut_tile[r];
             const int mi = mat_of(tile), lt = tile - p.tile0[mi];
-            const int m0 = (lt / p.n_tiles) * F_BM, n0 = (lt % p.n_tiles) * BN;
+            const int m0 = (lt / p.n_tiles) * TILE_M + crank * F_BM, n0 = (lt % p.n_tiles) * BN;
             const int     M_ = p.Mi[mi];
             const int64_t ldc_ = p.ldc[mi];
             float * const dst_ = p.dst[mi];
             const int h  = (int) ((((long long) tile * KS + 1) * G + p.units - 1) / p.units) - 1;
             const int l  = (int) ((((long long) (tile + 1) * KS) * G + p.units - 1) / p.units) - 1;
-            const int P  = l - h + 1, me = (int) blockIdx.x - h;
+            const int P  = l - h + 1, me = bid - h;
+            const int hc = CL * h + crank;  // a pair: the two CTAs reduce their own 128 rows with the same-rank CTAs of the other pairs
             if (lane == 0) {
                 long long spins = 0;
-                while (ld_acquire_gpu(p.flags + h) < (unsigned) P) {
+                while (ld_acquire_gpu(p.flags + hc) < (unsigned) P) {
                     if (++spins > (1ll << 24)) { printf("mmf_kernel: CTA %d timed out waiting for the parts of tile %d\n", blockIdx.x, tile); __trap(); }
                 }
             }
@@ -487,7 +565,7 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
                     for (int i = 0; i < NP; i++) {
                         const int pos = min(pos0 + i * 32 * F_EPI_WARPS, n_pos - 1);  // out-of-range lanes repeat the last position (not stored)
                         src[i] = p.ws + ((size_t) (c_lo + (pos >> 5)) * F_BM + 4 * (pos & 31));
-                        acc[i] = __ldcg((const float4 *) (src[i] + (size_t) (2 * h + 1) * slot_floats));  // the range that starts at 0: the head's slot 1
+                        acc[i] = __ldcg((const float4 *) (src[i] + (size_t) (2 * hc + 1) * slot_floats));  // the range that starts at 0: the head's slot 1
                     }
                     for (int j0 = 1; j0 < P; j0 += JB) {  // ascending K
                         float4 v[JB][NP];
@@ -495,7 +573,7 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
                         for (int j = 0; j < JB; j++) {
                             const int jj = min(j0 + j, P - 1);
 #pragma unroll
-                            for (int i = 0; i < NP; i++) v[j][i] = __ldcg((const float4 *) (src[i] + (size_t) (2 * (h + jj)) * slot_floats));
+                            for (int i = 0; i < NP; i++) v[j][i] = __ldcg((const float4 *) (src[i] + (size_t) (2 * (hc + CL * jj)) * slot_floats));
                         }
 #pragma unroll
                         for (int j = 0; j < JB; j++) {
@@ -531,9 +609,9 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
             // the last of the P readers lowers the counters for the next launch
             asm volatile("bar.sync 1, %0;" ::"n"(32 * F_EPI_WARPS) : "memory");
             if (warp == F_FIRST_EPI && lane == 0) {
-                if (atomicAdd(p.flags + 512 + h, 1u) == (unsigned) (P - 1)) {
-                    p.flags[h]       = 0u;
-                    p.flags[512 + h] = 0u;
+                if (atomicAdd(p.flags + 512 + hc, 1u) == (unsigned) (P - 1)) {
+                    p.flags[hc]       = 0u;
+                    p.flags[512 + hc] = 0u;
                 }
             }
         }
@@ -541,12 +619,14 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
     }
 
     tc_fence_before();
-    __syncthreads();
+    if (CL == 2) cluster_sync_all();  // the leader's MMAs read the peer's shared memory and the peer arrives on the leader's barriers
+    else __syncthreads();
     if (threadIdx.x == 0) MMF_TRACE(4);  // every role of this CTA is through its span
     if (p.split.n_ranks > 1 && warp == 0) split_complete(p.split, gridDim.x);
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc<SLOTS * BN>(tmem_base);
+        if (CL == 2) tmem_dealloc2<SLOTS * BN>(tmem_base);
+        else tmem_dealloc<SLOTS * BN>(tmem_base);
     }
 }
 
@@ -557,23 +637,25 @@ int mmf_env(const char * name, int dflt) {
     return s && *s ? atoi(s) : dflt;
 }
 
-template <int BN>
+template <int BN, int CL>
 b200_status mmf_launch(b200_ctx * ctx, const MmfMaps & maps, const CUtensorMap & map_b, MmfParams & p, int tiles) {
     static bool attr_done[64] = {};
     if (ctx->device < 64 && !attr_done[ctx->device]) {
-        CU(cudaFuncSetAttribute(mmf_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, f_smem(BN)));
+        CU(cudaFuncSetAttribute(mmf_kernel<BN, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, f_smem(BN, CL)));
         attr_done[ctx->device] = true;
     }
     static const int env_sk = mmf_env("GGML_B200_MMF_STREAMK", 1), env_min = mmf_env("GGML_B200_MMF_MIN_SPAN", 8);
     p.units = (long long) tiles * p.k_stages;
+    const int slots = ctx->sm_count / CL;  // CTAs (CL == 2: CTA pairs) that run at once
     int grid;
     if (env_sk) {  // equal spans of at least env_min stages
         const long long g = p.units / (env_min > 0 ? env_min : 1);
-        grid = (int) (g < 1 ? 1 : g < ctx->sm_count ? g : ctx->sm_count);
-        if (grid > 512) grid = 512;  // the counters of the cut tiles are indexed by CTA
+        grid = (int) (g < 1 ? 1 : g < slots ? g : slots);
     } else {       // whole tiles only
-        grid = tiles < ctx->sm_count ? tiles : ctx->sm_count;
+        grid = tiles < slots ? tiles : slots;
     }
+    grid *= CL;
+    if (grid > 512) grid = 512;  // the counters of the cut tiles are indexed by CTA
     p.whole_tiles = !env_sk;
     // workspace: [counters: 4 KB (parts parked per head CTA, readers done per head CTA)][2 slots per CTA][BN][128] floats
     const size_t need = 4096 + (size_t) 2 * ctx->sm_count * 256 * F_BM * 4;
@@ -586,16 +668,27 @@ b200_status mmf_launch(b200_ctx * ctx, const MmfMaps & maps, const CUtensorMap &
     p.ws    = (float *) ((uint8_t *) ctx->scratch3 + 4096);
     p.trace = ctx->trace ? ctx->trace + (size_t) (ctx->launches % ctx->trace_slots) * ctx->sm_count * 8 : nullptr;
     cudaLaunchConfig_t  cfg = {};
-    cudaLaunchAttribute attr[1];
-    attr[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (CL == 2) {
+        attr[na].id               = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = 2;
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        na++;
+    }
+    if (ctx->pdl) {
+        attr[na].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
     cfg.gridDim          = dim3((unsigned) grid);
     cfg.blockDim         = dim3(F_THREADS);
-    cfg.dynamicSmemBytes = f_smem(BN);
+    cfg.dynamicSmemBytes = f_smem(BN, CL);
     cfg.stream           = ctx->stream;
     cfg.attrs            = attr;
-    cfg.numAttrs         = ctx->pdl ? 1 : 0;
-    CU(cudaLaunchKernelEx(&cfg, mmf_kernel<BN>, maps, map_b, p));
+    cfg.numAttrs         = na;
+    CU(cudaLaunchKernelEx(&cfg, mmf_kernel<BN, CL>, maps, map_b, p));
     ctx->launches++;
     return B200_OK;
 }
@@ -631,8 +724,9 @@ b200_status mmf_run(b200_ctx * ctx, int n_mats, WEntry * const * es, bool settle
         ctx->launches++;
     }
 
-    static const int env_bn = mmf_env("GGML_B200_MMF_BN", 0), env_pf = mmf_env("GGML_B200_MMF_PF", 0);
+    static const int env_bn = mmf_env("GGML_B200_MMF_BN", 0), env_pf = mmf_env("GGML_B200_MMF_PF", 0), env_cl = mmf_env("GGML_B200_MMF_CL", 2);
     const int bn = env_bn ? env_bn : (N <= 128 ? 128 : 256);
+    const int cl = bn == 256 && env_cl == 2 ? 2 : 1;  // CTA pairs (cta_group::2): 256 x 256 tiles over two SMs
     MmfParams p;
     MmfMaps   maps;
     memset(&maps, 0, sizeof(maps));
@@ -651,14 +745,15 @@ b200_status mmf_run(b200_ctx * ctx, int n_mats, WEntry * const * es, bool settle
             p.ldc[i]   = ldcs[i];
             p.Mi[i]    = (int) es[i]->M;
             p.tile0[i] = tiles;
-            tiles += (int) ((es[i]->M + F_BM - 1) / F_BM) * p.n_tiles;
+            tiles += (int) ((es[i]->M + F_BM * cl - 1) / (F_BM * cl)) * p.n_tiles;
         } else {
             p.dst[i] = nullptr; p.ldc[i] = 0; p.Mi[i] = 0; p.tile0[i] = INT32_MAX;
         }
     }
     CUtensorMap map_b;
-    if (!make_map(&map_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, h, (uint64_t) K, (uint64_t) N, (uint64_t) K * 2, F_BK, (uint32_t) bn, true)) {
+    if (!make_map(&map_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, h, (uint64_t) K, (uint64_t) N, (uint64_t) K * 2, F_BK, (uint32_t) (bn / cl), true)) {
         return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the fp16 activations (N=%lld K=%lld)", (long long) N, (long long) K);
     }
-    return bn == 256 ? mmf_launch<256>(ctx, maps, map_b, p, tiles) : mmf_launch<128>(ctx, maps, map_b, p, tiles);
+    if (cl == 2) return mmf_launch<256, 2>(ctx, maps, map_b, p, tiles);
+    return bn == 256 ? mmf_launch<256, 1>(ctx, maps, map_b, p, tiles) : mmf_launch<128, 1>(ctx, maps, map_b, p, tiles);
 }
