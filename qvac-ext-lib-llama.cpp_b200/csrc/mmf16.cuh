@@ -342,6 +342,7 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
     uint64_t * tfull     = bars + 2 * STAGES;  // [SLOTS]   MMA commit -> epilogue
     uint64_t * tempty    = tfull + SLOTS;      // [SLOTS]   epilogue warps -> MMA
     uint32_t * tmem_slot = (uint32_t *) (tempty + SLOTS);
+    uint64_t * fbar      = tempty + SLOTS + 1;  // parts of a cut tile -> shared memory (phase 2 of the fix-up)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int KS = p.k_stages;
@@ -359,6 +360,7 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
             mbar_init(smem_u32(tfull + i), 1);
             mbar_init(smem_u32(tempty + i), F_EPI_WARPS * CL);  // a pair: the leader's barrier counts the epilogue warps of both CTAs
         }
+        mbar_init(smem_u32(fbar), 1);
         fence_mbar_init();
         for (int i = 0; i < p.n_mats; i++) tma_prefetch_desc(&maps.a[i]);
         tma_prefetch_desc(&map_b);
@@ -416,7 +418,6 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
                 if (crank == 0) mbar_expect_tx(smem_u32(full + npre), CL * STAGE_BYTES);
                 tma_load_2d_cl<CL>(smem_u32(smem + npre * STAGE_BYTES), &maps.a[ca.mat], ca.ks * F_BK, ca.m0, full_bar(npre));
             }
-            MMF_TRACE(2);
             if (p.early_a) asm volatile("griddepcontrol.wait;" ::: "memory");  // the activations are the previous kernel's output
             for (int i = 0; i < npre; i++, step(c)) {
                 tma_load_2d_cl<CL>(smem_u32(smem + i * STAGE_BYTES) + F_A_BYTES, &map_b, c.ks * F_BK, c.n0, full_bar(i));
@@ -485,7 +486,6 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
             const int m  = m0 + row;
             mbar_wait(smem_u32(tfull + slot), tphase);
             tc_fence_after();
-            if (first && warp == F_FIRST_EPI && lane == 0) MMF_TRACE(6);
             const uint32_t t_lane = tmem_base + ((uint32_t) (quad * 32) << 16) + slot * BN + half * (BN / 2);
             if (k0 > 0 || k1 < KS) {
                 // part of a tile that is cut by span boundaries: park the accumulator (slot 1 of this CTA for the K-range that starts
@@ -502,6 +502,7 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) release_slot(slot);
+                asm volatile("fence.proxy.async;" ::: "memory");  // the parts are read back with bulk copies (async proxy)
                 __threadfence();
                 asm volatile("bar.sync 1, %0;" ::"n"(32 * F_EPI_WARPS) : "memory");
                 if (warp == F_FIRST_EPI && lane == 0) {
@@ -530,6 +531,7 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
             if (++slot == SLOTS) { slot = 0; tphase ^= 1; }
             u += k1 - k0;
         }
+        if (warp == F_FIRST_EPI && lane == 0) MMF_TRACE(6);  // every item of the span drained (stored or parked)
         // ---- phase 2: every CTA that holds a part of a cut tile sums ALL of the tile's parts (ascending K: fixed order, no atomics on
         // data) for its own share of the tile's columns and stores that share - the fix-up of a tile cut P ways runs on P SMs
         for (int r = 0; r < n_cut; r++) {
@@ -550,62 +552,50 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
                 }
             }
             __syncwarp();
+            if (r == 0 && warp == F_FIRST_EPI && lane == 0) MMF_TRACE(2);  // the parts of the first cut tile are all parked
             const int c_lo = BN * me / P, c_hi = BN * (me + 1) / P;
             const int n_pos = (c_hi - c_lo) * 32;  // positions of 4 consecutive rows (16 bytes) of one column
             const bool vec = p.split.n_ranks <= 1 && (ldc_ & 3) == 0 && ((uintptr_t) dst_ & 15) == 0;
-            const size_t slot_floats = (size_t) BN * F_BM;
-            // a thread keeps NP positions x JB parts in flight: the sums are L2-latency bound otherwise (2 loads per round trip
-            // made this phase 20 us). Few parts: many positions at once; many parts: many parts at once.
-            auto reduce = [&](auto np_c, auto jb_c) {
-                constexpr int NP = decltype(np_c)::value, JB = decltype(jb_c)::value;
-                for (int pos0 = te; pos0 < n_pos; pos0 += NP * 32 * F_EPI_WARPS) {
-                    float4        acc[NP];
-                    const float * src[NP];
-#pragma unroll
-                    for (int i = 0; i < NP; i++) {
-                        const int pos = min(pos0 + i * 32 * F_EPI_WARPS, n_pos - 1);  // out-of-range lanes repeat the last position (not stored)
-                        src[i] = p.ws + ((size_t) (c_lo + (pos >> 5)) * F_BM + 4 * (pos & 31));
-                        acc[i] = __ldcg((const float4 *) (src[i] + (size_t) (2 * hc + 1) * slot_floats));  // the range that starts at 0: the head's slot 1
-                    }
-                    for (int j0 = 1; j0 < P; j0 += JB) {  // ascending K
-                        float4 v[JB][NP];
-#pragma unroll
-                        for (int j = 0; j < JB; j++) {
-                            const int jj = min(j0 + j, P - 1);
-#pragma unroll
-                            for (int i = 0; i < NP; i++) v[j][i] = __ldcg((const float4 *) (src[i] + (size_t) (2 * (hc + CL * jj)) * slot_floats));
-                        }
-#pragma unroll
-                        for (int j = 0; j < JB; j++) {
-                            if (j0 + j < P) {
-#pragma unroll
-                                for (int i = 0; i < NP; i++) { acc[i].x += v[j][i].x; acc[i].y += v[j][i].y; acc[i].z += v[j][i].z; acc[i].w += v[j][i].w; }
-                            }
-                        }
-                    }
-#pragma unroll
-                    for (int i = 0; i < NP; i++) {
-                        const int pos = pos0 + i * 32 * F_EPI_WARPS;
-                        if (pos >= n_pos) continue;
-                        const int n = n0 + c_lo + (pos >> 5), m = m0 + 4 * (pos & 31);
-                        if (n >= p.N || m >= M_) continue;
-                        const float rsv = __ldg(p.rs + n);
-                        float4 a = acc[i];
-                        a.x *= rsv; a.y *= rsv; a.z *= rsv; a.w *= rsv;
-                        float * d = dst_ + (int64_t) n * ldc_ + m;
-                        if (vec && m + 3 < M_) {
-                            *(float4 *) d = a;
-                        } else {
-                            split_store(p.split, d, a.x);
-                            if (m + 1 < M_) split_store(p.split, d + 1, a.y);
-                            if (m + 2 < M_) split_store(p.split, d + 2, a.z);
-                            if (m + 3 < M_) split_store(p.split, d + 3, a.w);
-                        }
-                    }
+            const size_t   slot_floats = (size_t) BN * F_BM;
+            const uint32_t part_bytes  = (uint32_t) (c_hi - c_lo) * F_BM * 4;  // this CTA's columns of one part: contiguous in the workspace
+            // The ring is idle by now (every TMA load has landed and every MMA that read it has completed): the P x part_bytes
+            // (= one tile, 128 KB) are fetched into it with P bulk copies - the copy engine hides the L2 latency that bounded
+            // this phase when the threads loaded the parts themselves (4 us per tile with 24 x 16 B in flight per thread)
+            if (warp == F_FIRST_EPI && lane == 0) {
+                asm volatile("fence.proxy.async;" ::: "memory");
+                const uint64_t pol = l2_policy_evict_first();
+                mbar_expect_tx(smem_u32(fbar), (uint32_t) P * part_bytes);
+                for (int j = 0; j < P; j++) {
+                    const int sl = j == 0 ? 2 * hc + 1 : 2 * (hc + CL * j);  // ascending K: the head's slot 1, then slot 0 of the followers
+                    bulk_g2s(smem_u32(smem) + (uint32_t) j * part_bytes, p.ws + (size_t) sl * slot_floats + (size_t) c_lo * F_BM, part_bytes, smem_u32(fbar), pol);
                 }
-            };
-            if (P <= 3) reduce(std::integral_constant<int, 8>{}, std::integral_constant<int, 2>{});
-            else        reduce(std::integral_constant<int, 4>{}, std::integral_constant<int, 4>{});
+            }
+            mbar_wait(smem_u32(fbar), (uint32_t) (r & 1));
+            for (int pos = te; pos < n_pos; pos += 32 * F_EPI_WARPS) {
+                const uint32_t sp = smem_u32(smem) + (uint32_t) pos * 16;
+                float4 acc;
+                {
+                    const uint4 v = lds128(sp);
+                    acc = make_float4(__uint_as_float(v.x), __uint_as_float(v.y), __uint_as_float(v.z), __uint_as_float(v.w));
+                }
+                for (int j = 1; j < P; j++) {
+                    const uint4 v = lds128(sp + (uint32_t) j * part_bytes);
+                    acc.x += __uint_as_float(v.x); acc.y += __uint_as_float(v.y); acc.z += __uint_as_float(v.z); acc.w += __uint_as_float(v.w);
+                }
+                const int n = n0 + c_lo + (pos >> 5), m = m0 + 4 * (pos & 31);
+                if (n >= p.N || m >= M_) continue;
+                const float rsv = __ldg(p.rs + n);
+                acc.x *= rsv; acc.y *= rsv; acc.z *= rsv; acc.w *= rsv;
+                float * d = dst_ + (int64_t) n * ldc_ + m;
+                if (vec && m + 3 < M_) {
+                    *(float4 *) d = acc;
+                } else {
+                    split_store(p.split, d, acc.x);
+                    if (m + 1 < M_) split_store(p.split, d + 1, acc.y);
+                    if (m + 2 < M_) split_store(p.split, d + 2, acc.z);
+                    if (m + 3 < M_) split_store(p.split, d + 3, acc.w);
+                }
+            }
             // the last of the P readers lowers the counters for the next launch
             asm volatile("bar.sync 1, %0;" ::"n"(32 * F_EPI_WARPS) : "memory");
             if (warp == F_FIRST_EPI && lane == 0) {
@@ -716,10 +706,13 @@ b200_status mmf_run(b200_ctx * ctx, int n_mats, WEntry * const * es, bool settle
         const bool    k8    = es[0]->type == B200_TYPE_Q4_K;
 #define ACT_LAUNCH(UPW) (k8 ? cudaLaunchKernelEx(&cfg, act_f16_kernel<ACT_KIND_Q8_K, UPW>, xs, K, x_rs, h + r0 * K, rs + r0, vec_ok) \
                             : cudaLaunchKernelEx(&cfg, act_f16_kernel<ACT_KIND_Q8_0, UPW>, xs, K, x_rs, h + r0 * K, rs + r0, vec_ok))
-        if (units <= 16)      CU(ACT_LAUNCH(2));
-        else if (units <= 32) CU(ACT_LAUNCH(4));
-        else if (units <= 64) CU(ACT_LAUNCH(8));
-        else                  CU(ACT_LAUNCH(0));
+        // rows kept in registers between the two steps up to `env_reg` units; longer rows are read twice (the second read hits L2):
+        // 8 units per warp cost 117 registers - two CTAs per SM, two waves for 512 rows
+        static const int env_reg = mmf_env("GGML_B200_MMF_ACT_REG", 64);
+        if (units <= 16 && units <= env_reg)      CU(ACT_LAUNCH(2));
+        else if (units <= 32 && units <= env_reg) CU(ACT_LAUNCH(4));
+        else if (units <= 64 && units <= env_reg) CU(ACT_LAUNCH(8));
+        else                                      CU(ACT_LAUNCH(0));
 #undef ACT_LAUNCH
         ctx->launches++;
     }

@@ -33,9 +33,14 @@ def main():
         ctx.weight_cache(True)
         ops = bench.build_stack(torch, m, args.type, args.tokens, 1, 0, device)
 
-        def step():
-            for o in ops:
-                ctx.mul_mat(t, o["W"], o["x"], out=o["out"])
+        groups = bench.group_ops(ops)
+
+        def step():   # like bench.py: MUL_MATs that share src1 go through b200_mul_mat_shared_src1 (one grouped launch)
+            for grp in groups:
+                if len(grp) == 1:
+                    ctx.mul_mat(t, grp[0]["W"], grp[0]["x"], out=grp[0]["out"])
+                else:
+                    ctx.mul_mat_shared(t, [o["W"] for o in grp], grp[0]["x"], outs=[o["out"] for o in grp])
 
         step()
         l0 = ctx.launches
@@ -58,7 +63,7 @@ def main():
     starts = np.array([tr[s, :, 0][tr[s, :, 0] > 0].min() for s in used])
     order = [used[i] for i in np.argsort(starts)]
     t0 = starts.min()
-    lines = [f"{'launch':<10}{'ctas':>5} | {'start':>13} | {'dep ok':>13} | {'tma 0':>13} | {'stage 0':>13} | {'cta done':>13} | {'last mma':>13} | {'acc full':>13} | {'epi done':>13}"]
+    lines = [f"{'launch':<14}{'ctas':>5} | {'start':>13} | {'dep ok':>13} | {'parts 0 in':>13} | {'stage 0':>13} | {'cta done':>13} | {'last mma':>13} | {'drained':>13} | {'epi done':>13}"]
     for k, s in enumerate(order):
         live = tr[s, :, 0] > 0
         cols = []
@@ -66,7 +71,8 @@ def main():
             v = tr[s, live, i]
             v = v[v > 0]
             cols.append(f"{(v.min() - t0) / 1e3:6.2f}-{(v.max() - t0) / 1e3:6.2f}" if v.size else "      -      ")
-        lines.append(f"{ops[k % len(ops)]['name'][:9]:<10}{int(live.sum()):>5} | " + " | ".join(cols))
+        name = "+".join(o["name"] for o in groups[k % len(groups)])
+        lines.append(f"{name[:13]:<14}{int(live.sum()):>5} | " + " | ".join(cols))
     txt = "\n".join(lines)
     print(txt)
     if args.out:
