@@ -622,6 +622,43 @@ mmf_kernel(const __grid_constant__ MmfMaps maps, const __grid_constant__ CUtenso
 
 // ------------------------------------------------------------------------------------------------ host side
 
+// ------------------------------------------------------------------------------------------------ row split: slice -> peers
+
+// Row split with more than 8 columns: the GEMM stores this rank's row slice into the LOCAL dst only, and this kernel then copies
+// the slice into every peer's dst with 16-byte stores, coalesced along the rows, before the flag exchange (split_complete).
+// Peer stores issued from the GEMM epilogue itself (4-byte stores, 32 per thread and rank, from 8 of 12 warps) ran 8x below the
+// NVLink rate on 8 GPUs (profiles/README.md, pass 10).
+struct ScatterParams {
+    SplitParams split;
+    float *     dst[F_MAX_MATS];
+    int64_t     ldc[F_MAX_MATS];
+    int         M[F_MAX_MATS];
+    int         n_mats, N;
+};
+template <bool VEC>
+__global__ void __launch_bounds__(512) split_scatter_kernel(const ScatterParams p) {
+    const long long tid = (long long) blockIdx.x * blockDim.x + threadIdx.x, T = (long long) gridDim.x * blockDim.x;
+    for (int i = 0; i < p.n_mats; i++) {
+        const int       per_row = VEC ? p.M[i] / 4 : p.M[i];
+        const long long total   = (long long) per_row * p.N;
+        for (long long e = tid; e < total; e += T) {
+            const long long n = e / per_row;
+            const int       c = (int) (e - n * per_row);
+            if (VEC) {
+                float4 * a = (float4 *) (p.dst[i] + n * p.ldc[i]) + c;
+                const float4 v = *a;
+                for (int r = 0; r < p.split.n_ranks; r++) if (r != p.split.rank) *(float4 *) ((char *) a + p.split.dst_delta[r]) = v;
+            } else {
+                float * a = p.dst[i] + n * p.ldc[i] + c;
+                const float v = *a;
+                for (int r = 0; r < p.split.n_ranks; r++) if (r != p.split.rank) *(float *) ((char *) a + p.split.dst_delta[r]) = v;
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) split_complete(p.split, gridDim.x);
+}
+
 int mmf_env(const char * name, int dflt) {
     const char * s = getenv(name);
     return s && *s ? atoi(s) : dflt;
@@ -747,6 +784,27 @@ b200_status mmf_run(b200_ctx * ctx, int n_mats, WEntry * const * es, bool settle
     if (!make_map(&map_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, h, (uint64_t) K, (uint64_t) N, (uint64_t) K * 2, F_BK, (uint32_t) (bn / cl), true)) {
         return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the fp16 activations (N=%lld K=%lld)", (long long) N, (long long) K);
     }
-    if (cl == 2) return mmf_launch<256, 2>(ctx, maps, map_b, p, tiles);
-    return bn == 256 ? mmf_launch<256, 1>(ctx, maps, map_b, p, tiles) : mmf_launch<128, 1>(ctx, maps, map_b, p, tiles);
+    static const int env_scatter = mmf_env("GGML_B200_MMF_SCATTER", 1);
+    const bool scatter = ctx->split.n_ranks > 1 && env_scatter;
+    if (scatter) p.split = SplitParams{};  // the GEMM writes the local dst only
+    b200_status st = cl == 2     ? mmf_launch<256, 2>(ctx, maps, map_b, p, tiles)
+                     : bn == 256 ? mmf_launch<256, 1>(ctx, maps, map_b, p, tiles)
+                                 : mmf_launch<128, 1>(ctx, maps, map_b, p, tiles);
+    if (st != B200_OK || !scatter) return st;
+    ScatterParams sp;
+    sp.split = ctx->split;
+    sp.n_mats = n_mats; sp.N = (int) N;
+    bool vec = true;
+    for (int i = 0; i < F_MAX_MATS; i++) {
+        sp.dst[i] = i < n_mats ? dsts[i] : nullptr;
+        sp.ldc[i] = i < n_mats ? ldcs[i] : 0;
+        sp.M[i]   = i < n_mats ? (int) es[i]->M : 0;
+        if (i < n_mats) vec = vec && es[i]->M % 4 == 0 && ldcs[i] % 4 == 0 && (uintptr_t) dsts[i] % 16 == 0;
+    }
+    for (int r = 0; r < ctx->split.n_ranks; r++) vec = vec && ctx->split.dst_delta[r] % 16 == 0;
+    if (vec) split_scatter_kernel<true><<<ctx->sm_count, 512, 0, ctx->stream>>>(sp);
+    else     split_scatter_kernel<false><<<ctx->sm_count, 512, 0, ctx->stream>>>(sp);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    return B200_OK;
 }
