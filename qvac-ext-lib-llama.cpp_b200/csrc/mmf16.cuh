@@ -14,17 +14,21 @@
 // activation range, and a power of two commutes with the rounding. GGML_B200_MMQ_F16=0 (b200_ctx_set_mmq_f16) selects the
 // exact-block-sum kind::i8 kernels instead.
 //
-// Tiling: CTA tile 128 (M) x BN (N, 256 or 128), K in stages of 64 halfs (= one 128-byte swizzle row), four UTCHMMA
-// 128 x BN x 16 per stage, 2 TMEM accumulator slots of BN columns (the epilogue of one work item overlaps the main loop of the next).
-// Scheduling is stream-K: the launch's tiles x K-stages are cut into gridDim.x equal contiguous spans (one persistent CTA per SM),
-// so every SM is busy for the same time whatever the tile count (wk/wv of Llama-3-8B at n = 512 are 16 tiles). A tile cut by
+// Tiling: a CTA PAIR (tcgen05.mma cta_group::2, SASS UTCHMMA.2CTA) owns a 256 (M) x 256 (N) tile: each CTA loads its 128 weight rows
+// and HALF of the activation tile (16 + 16 KB per K stage of 64 halfs = one 128-byte swizzle row), the leader's elected thread issues
+// four 256 x 256 x 16 MMAs per stage, both CTAs keep 128 lanes x 256 columns of the fp32 accumulator in their TMEM (2 slots: the
+// epilogue of one work item overlaps the main loop of the next). Up to 128 columns (N <= 128) and with GGML_B200_MMF_CL=1 a single
+// CTA owns a 128 x BN tile. The SM's operand ingest (~50 B/clk), not the L2 read rate, is what a single-CTA 128 x 256 tile is short
+// of: a cluster that merely multicasts the activation tile is no faster, the pair that SPLITS it is (755 -> 805 TOPS).
+// Scheduling is stream-K: the launch's tiles x K-stages (tiles of up to four weight matrices that share src1: q/k/v, gate/up) are
+// cut into equal contiguous spans, one per CTA (pair),
+// so every SM is busy for the same time whatever the tile count (wk/wv of Llama-3-8B at n = 512 are 8 tiles). A tile cut by
 // span boundaries is finished deterministically in two phases: every CTA parks the partial accumulator of its part in a
 // workspace and bumps a counter; at the end of its span each of the P CTAs that share the tile waits for the P parts and sums
-// all of them in ascending K order for ITS 1/P of the tile's columns, scales and stores that share (no atomics on data: results
-// do not depend on timing; the fix-up of a tile cut P ways runs on P SMs - a single owner summing P x 128 KB took 28 us on wk).
-// Warp roles (384 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 4..11 epilogue.
-// Tried and dropped: clusters of two CTAs sharing the activation tile by TMA multicast (same speed: the SM's ingest, not the
-// L2 read rate, is what a 128 x 256 tile is short of - profiles/README.md).
+// all of them in ascending K order for ITS 1/P of the tile's columns (parts fetched into the idle operand ring by bulk copies),
+// scales and stores that share (no atomics on data: results do not depend on timing; the fix-up of a tile cut P ways runs on P SMs -
+// a single owner summing P x 128 KB took 28 us on wk).
+// Warp roles (384 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer (leader CTA of a pair), warps 4..11 epilogue.
 
 #include <cuda_fp16.h>
 #include <type_traits>
