@@ -118,6 +118,7 @@ b200_status b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     if (const char * s = getenv("GGML_B200_DBG")) c->dbg = atoi(s);
     if (const char * s = getenv("GGML_B200_MMA_MIN")) c->mma_min_cols = atoi(s);
     if (const char * s = getenv("GGML_B200_MMA_WARPS")) c->mma_warps = atoi(s);
+    if (const char * s = getenv("GGML_B200_MMA_FUSE_UNITS")) c->mma_fuse_units = atoi(s);
     if (const char * s = getenv("GGML_B200_MOE_GROUP_MIN")) c->moe_group_min = atoi(s);
     if (const char * s = getenv("GGML_B200_MMQ_F16")) c->mmq_f16 = atoi(s) != 0;
     *out = c;
@@ -489,11 +490,16 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
     const int U = (int) (K / 256);
     for (int c0 = 0; c0 < ncols;) {
         int     nc = ncols - c0 < MV_MAX_COLS ? ncols - c0 : MV_MAX_COLS;
-        if (!x && ctx->mma_min_cols > 0 && nc >= ctx->mma_min_cols && mv_mma_usable(type) && mv_mma_fits(type, K)) {  // 3..8 columns: tensor-core mat-vec (mvmma.cu)
+        if (ctx->mma_min_cols > 0 && nc >= ctx->mma_min_cols && mv_mma_usable(type) && mv_mma_fits(type, K)) {  // 3..8 columns: tensor-core mat-vec (mvmma.cu)
             float * ds[MV_MAX_MATS * 8];
             for (int i = 0; i < n_ops; i++) ds[i] = dsts[i] + (int64_t) c0 * dst_cs[i];
-            b200_status st = b200_mv_mma_run(ctx, type, K, n_ops, ws, nb01s, Ms, ds, dst_cs, nc, act_main + (size_t) c0 * U * ACT_MAIN,
-                                             act_aux + (size_t) c0 * U * ACT_AUX);
+            if (x && ctx->split.n_ranks > 1 && ctx->split_deferred) {
+                if (b200_status fst = b200_split_flush(ctx)) return fst;  // this kernel reads src1 without a split_wait prologue
+            }
+            b200_status st = x ? b200_mv_mma_run(ctx, type, K, n_ops, ws, nb01s, Ms, ds, dst_cs, nc, nullptr, nullptr,
+                                                 (const float *) ((const char *) x + (size_t) c0 * x_cs), x_cs)
+                               : b200_mv_mma_run(ctx, type, K, n_ops, ws, nb01s, Ms, ds, dst_cs, nc, act_main + (size_t) c0 * U * ACT_MAIN,
+                                                 act_aux + (size_t) c0 * U * ACT_AUX);
             if (st != B200_OK) return st;
             c0 += nc;
             continue;
@@ -629,7 +635,9 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
     if (fast) {
         const int  U    = (int) (K / 256);
         const bool mma  = ctx->mma_min_cols > 0 && N >= ctx->mma_min_cols && mv_mma_usable(type);  // the IMMA kernel reads pre-quantized columns
-        const bool fuse = !mma && mv_fuse_quant(ctx, U, N);
+        // src1 is quantized inside the mat-vec kernel while the per-CTA redundancy is small (no quantizer launch); the IMMA kernel
+        // has its own bound (it is used for more columns) and needs the row to fit its 8 columns in shared memory
+        const bool fuse = mma ? (ctx->fuse_quant && N <= MV_MAX_COLS && N * U <= ctx->mma_fuse_units && mv_mma_fits(type, K)) : mv_fuse_quant(ctx, U, N);
         uint8_t * am = nullptr, * ax = nullptr;
         if (!fuse) {
             if (b200_status fst = b200_split_flush(ctx)) return fst;  // the quantizer launch reads src1 without a split_wait prologue

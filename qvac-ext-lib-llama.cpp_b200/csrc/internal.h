@@ -63,6 +63,7 @@ struct b200_ctx {
     int          trace_slots = 0;
     int          dbg = 0;                      // GGML_B200_DBG: experiment switches handed to the kernels
     int          mma_min_cols = 3;             // columns from which the IMMA mat-vec kernel (mvmma.cu) replaces the dp4a one; GGML_B200_MMA_MIN
+    int          mma_fuse_units = 0;           // the IMMA kernel quantizes src1 itself up to this many (column, unit) pairs (0: never - measured no faster than the PDL-chained quantizer launch); GGML_B200_MMA_FUSE_UNITS
     int          mma_warps = 0;                // 0 = auto; GGML_B200_MMA_WARPS
     // the fp16 activation operand last built in scratch2 (kind::f16 prefill): valid for further matrices of the same shared-src1 group
     const void * act_x = nullptr; size_t act_rs = 0; int64_t act_N = 0, act_K = 0; const void * act_buf = nullptr; int act_kind = -1;
@@ -90,7 +91,8 @@ b200_status b200_ensure(b200_ctx * ctx, void ** buf, size_t * cur, size_t need);
 // mvmma.cu: the IMMA mat-vec kernel for 3..8 columns (q4_0, q4_K)
 namespace b200 { bool mv_mma_usable(int type); bool mv_mma_fits(int type, int64_t K); }
 b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, const uint8_t * const * ws, const size_t * nb01s, const int64_t * Ms,
-                            float * const * dsts, const int64_t * dst_cs, int ncols, const uint8_t * act_main, const uint8_t * act_aux);
+                            float * const * dsts, const int64_t * dst_cs, int ncols, const uint8_t * act_main, const uint8_t * act_aux,
+                            const float * x = nullptr, size_t x_cs = 0);  // x: F32 columns quantized inside the kernel (no quantizer launch)
 
 b200_status b200_mv_mma_run_ids(b200_ctx * ctx, int type, int64_t K, const uint8_t * as, size_t nb01, size_t nb02, int64_t M, int64_t n_as,
                                 float * dst, const b200::MvIds & ids, const int32_t * sp, const int32_t * eb, const uint8_t * act_main,

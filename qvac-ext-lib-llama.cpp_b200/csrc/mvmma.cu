@@ -17,6 +17,7 @@
 
 #include "internal.h"
 #include "tc.cuh"
+#include "quant_core.cuh"
 
 #include <cuda.h>
 
@@ -30,6 +31,9 @@ struct MmaMvParams {
     int             U, ncols, n_cons, n_stages, pdl;
     const uint8_t * act_main;           // [ncols][U][272]
     const uint8_t * act_aux;            // [ncols][U][16]
+    const float *   x;                  // fuse_quant: F32 activations, column c at (char*)x + c*x_cs - quantized by the kernel itself
+    int64_t         x_cs;
+    int             fuse_quant, x_vec;
     SplitParams     split;
     SplitGeom       geom;               // split.ll: who owns which rows of mat[i]
     // MUL_MAT_ID mode (sp != nullptr): blockIdx.y = expert e; its (slot, token) pairs sp[eb[e] .. eb[e+1]) are the columns, 8 at a
@@ -304,7 +308,39 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
         // zero (the MMA always multiplies 8). The previous pass's readers are behind its last reduction barrier.
         for (int i = threadIdx.x; i < (8 - nc) * (int) (cs_m / 16); i += NWC * 32) ((uint4 *) (act_m + (size_t) nc * cs_m))[i] = make_uint4(0, 0, 0, 0);
         for (int i = threadIdx.x; i < (8 - nc) * (int) (cs_x / 16); i += NWC * 32) ((uint4 *) (act_x + (size_t) nc * cs_x))[i] = make_uint4(0, 0, 0, 0);
-        if (w == 0 && lane == 0) {
+        if (p.fuse_quant) {
+            // fused K1 (as in mv_fast_kernel): unit (c, u) of the activations, F32 global -> unit record in shared memory; up to 4
+            // units per warp are loaded before the first is quantized, so the L2 round trips overlap. No quantizer launch.
+            constexpr int KIND = act_kind_for(TYPE);
+            const int n_tasks = nc * U;
+            for (int t0 = w; t0 < n_tasks; t0 += 4 * NWC) {
+                float v[4][8];
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    const int tk = t0 + b * NWC;
+                    if (tk < n_tasks) {
+                        const int c = tk / U, u = tk - c * U;
+                        const float * xr = (const float *) ((const char *) p.x + (int64_t) c * p.x_cs) + (int64_t) u * UNIT_ELEMS + lane * 8;
+                        if (p.x_vec) {
+                            const float4 a = __ldg((const float4 *) xr), bb = __ldg((const float4 *) xr + 1);
+                            v[b][0] = a.x; v[b][1] = a.y; v[b][2] = a.z; v[b][3] = a.w;
+                            v[b][4] = bb.x; v[b][5] = bb.y; v[b][6] = bb.z; v[b][7] = bb.w;
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 8; i++) v[b][i] = __ldg(xr + i);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    const int tk = t0 + b * NWC;
+                    if (tk < n_tasks) {
+                        const int c = tk / U, u = tk - c * U;
+                        quant_unit_store<KIND>(v[b], lane, act_m + (size_t) c * cs_m + (size_t) u * ACT_MAIN, act_x + (size_t) c * cs_x + (size_t) u * ACT_AUX);
+                    }
+                }
+            }
+        } else if (w == 0 && lane == 0) {
             const uint64_t pol_keep = l2_policy_evict_last();
             const uint32_t bytes_m = (uint32_t) U * ACT_MAIN, bytes_x = (uint32_t) U * ACT_AUX;
             mbar_expect_tx(smem_u32(act_bar), (uint32_t) nc * (bytes_m + bytes_x));
@@ -319,8 +355,8 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
                 bulk_g2s(smem_u32(act_x + (size_t) c * cs_x), p.act_aux + (size_t) arow * bytes_x, bytes_x, smem_u32(act_bar), pol_keep);
             }
         }
-        mbar_wait(smem_u32(act_bar), (uint32_t) (pass & 1));
-        bar_named(1, NWC * 32);  // the zero fill of the unused columns is visible
+        if (!p.fuse_quant) mbar_wait(smem_u32(act_bar), (uint32_t) (pass & 1));
+        bar_named(1, NWC * 32);  // the zero fill of the unused columns (and the fused quantization) is visible
 
         for (int tile0 = t_begin; tile0 < t_end; tile0 += MMA_RT) {
             const int nt = min(MMA_RT, t_end - tile0);
@@ -433,7 +469,8 @@ static b200_status mma_set_attr(b200_ctx * ctx, int type) {
 
 // host: n_ops matrices (same type, K) against `ncols` pre-quantized activation columns
 b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, const uint8_t * const * ws, const size_t * nb01s, const int64_t * Ms,
-                            float * const * dsts, const int64_t * dst_cs, int ncols, const uint8_t * act_main, const uint8_t * act_aux) {
+                            float * const * dsts, const int64_t * dst_cs, int ncols, const uint8_t * act_main, const uint8_t * act_aux,
+                            const float * x, size_t x_cs) {
     const int U  = (int) (K / 256);
     const int UB = unit_bytes(type);
     // consumer warps: as many as leave room for >= 3 ring stages next to the 8 activation columns (K = 14336: 129 KB of them)
@@ -485,6 +522,11 @@ b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, cons
         p.total_tiles = tiles;
         p.U = U; p.ncols = ncols; p.n_cons = n_cons; p.n_stages = n_stages; p.pdl = ctx->pdl;
         p.act_main = act_main; p.act_aux = act_aux;
+        if (x) {
+            p.fuse_quant = 1;
+            p.x = x; p.x_cs = (int64_t) x_cs;
+            p.x_vec = (uintptr_t) x % 16 == 0 && x_cs % 16 == 0;
+        }
         p.split = ctx->split;
         if (b200_split_ll_geom(ctx, p.n_mats, Ms + o0, dsts + o0, dst_cs + o0, ncols, &p.geom)) p.split.ll = 1;
         const int grid = tiles < ctx->sm_count ? tiles : ctx->sm_count;
