@@ -83,6 +83,12 @@ B200_API b200_status  b200_memset(int device, void * dst, int value, size_t size
 B200_API b200_status  b200_memcpy_h2d_async(b200_ctx * ctx, void * dst, const void * src, size_t size);
 B200_API b200_status  b200_memcpy_d2h_async(b200_ctx * ctx, void * dst, const void * src, size_t size);
 B200_API b200_status  b200_memcpy_d2d_async(b200_ctx * ctx, void * dst, const void * src, size_t size);
+/* split tensors (ggml_cuda_op_mul_mat, ggml-cuda.cu:1676-1734): src1 to the other devices and their dst slices back to the main
+ * device. `height` rows of `width` bytes between any two devices of the process, on the context's stream (the reference's
+ * cudaMemcpy2DPeerAsync / cudaMemcpyPeerAsync); b200_enable_peer_access lets the copies and kernels of `device` reach `peer`'s
+ * memory directly (best effort: without it the driver stages the copies) */
+B200_API b200_status  b200_memcpy2d_async(b200_ctx * ctx, void * dst, size_t dpitch, const void * src, size_t spitch, size_t width, size_t height);
+B200_API b200_status  b200_enable_peer_access(int device, int peer);
 
 /* events: device event_new/free/synchronize, backend event_record/event_wait (ggml-cuda.cu:2836-2862, 4649-4677) */
 B200_API b200_status  b200_event_create(int device, void ** event);

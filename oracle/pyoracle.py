@@ -205,6 +205,8 @@ class RefHarness:
         L.refh_dev_description.argtypes = [C.c_int, C.c_int]
         L.refh_mul_mat.restype = C.c_int
         L.refh_mul_mat.argtypes = [C.c_int] * 4 + [C.c_int64] * 7 + [C.c_void_p] * 3 + [C.c_double, C.POINTER(C.c_double)]
+        L.refh_mul_mat_split.restype = C.c_int
+        L.refh_mul_mat_split.argtypes = [C.c_int] * 3 + [C.c_int64] * 3 + [C.c_void_p] * 4 + [C.c_int, C.c_void_p, C.c_int]
         L.refh_mul_mat_id.restype = C.c_int
         L.refh_mul_mat_id.argtypes = [C.c_int] * 4 + [C.c_int64] * 6 + [C.c_void_p] * 4 + [C.c_double, C.POINTER(C.c_double)]
         L.refh_mul_mat_stack.restype = C.c_int
@@ -268,6 +270,22 @@ class RefHarness:
             raise RuntimeError(f"refh_mul_mat rc={rc} (2 = backend does not support the op)")
         out = out if X.ndim == 4 else out[0, 0]
         return out, (us.value if seconds > 0 else None)
+
+    def mul_mat_split(self, reg: int, t: int, W: np.ndarray, X: np.ndarray, tensor_split=None, dev=0, repeats=1):
+        """MUL_MAT with W in the backend's split buffer type (ggml_backend_split_buffer_type): W uint8 [M, row_bytes], X float32
+        [N, K]; tensor_split = proportions per device (None: the backend's default). returns (out [N, M], weight bytes read back)"""
+        X = np.ascontiguousarray(X, dtype=np.float32)
+        W = np.ascontiguousarray(W, dtype=np.uint8)
+        N, K = X.shape
+        M = W.size // row_size(t, K)
+        out = np.zeros((N, M), dtype=np.float32)
+        back = np.zeros_like(W)
+        ts = None if tensor_split is None else np.ascontiguousarray(tensor_split, dtype=np.float32)
+        rc = self.lib.refh_mul_mat_split(reg, dev, t, M, K, N, _ptr(W), _ptr(X), _ptr(out), None if ts is None else _ptr(ts),
+                                         0 if ts is None else len(ts), _ptr(back), repeats)
+        if rc:
+            raise RuntimeError(f"refh_mul_mat_split rc={rc} (2 = op not supported, 5 = no split buffer type)")
+        return out, back
 
     def mul_mat_id(self, reg: int, t: int, W: np.ndarray, B: np.ndarray, ids: np.ndarray, n_threads=0, dev=0,
                    seconds=0.0):

@@ -145,6 +145,52 @@ int refh_mul_mat(int reg, int dev, int n_threads, int type, int64_t M, int64_t K
     return 0;
 }
 
+// The same MUL_MAT with W in the backend's SPLIT buffer type (ggml_backend_split_buffer_type, ggml-backend.h:199-200: weight rows
+// spread over the devices of the registry; how llama places weights with --split-mode row, src/llama-model.cpp:385-403).
+// tensor_split: n_split proportions (nullptr / all zero = the backend's default). W_back (optional) receives the weight bytes read
+// back through the split buffer. returns 0 on success, 5 if the registry has no split buffer type.
+int refh_mul_mat_split(int reg, int dev, int type, int64_t M, int64_t K, int64_t N, const void * W, const float * X, float * dst,
+                       const float * tensor_split, int n_split, void * W_back, int repeats) {
+    if (reg < 0 || reg >= (int) g_regs.size()) return 1;
+    auto split_fn = (ggml_backend_split_buffer_type_t) ggml_backend_reg_get_proc_address(g_regs[reg], "ggml_backend_split_buffer_type");
+    if (!split_fn) return 5;
+    float ts[64] = {};
+    for (int i = 0; i < n_split && i < 64; i++) ts[i] = tensor_split ? tensor_split[i] : 0.0f;
+    ggml_backend_buffer_type_t sbuft = split_fn(dev, ts);
+    if (!sbuft) return 5;
+    graph_run g;
+    g.be = open_backend(reg, dev, 0);
+    if (!g.be) return 1;
+    // weights in their own context: allocated from the split buffer type; activations and result from the device's default one
+    ggml_init_params ipw = { ggml_tensor_overhead() * 4, nullptr, true };
+    ggml_context * wctx = ggml_init(ipw);
+    if (!wctx || !make_ctx(g)) return 1;
+    ggml_tensor * w = ggml_new_tensor_2d(wctx, (ggml_type) type, K, M);
+    ggml_backend_buffer_t wbuf = ggml_backend_alloc_ctx_tensors_from_buft(wctx, sbuft);
+    int rc = 0;
+    if (!wbuf) {
+        rc = 3;
+    } else {
+        ggml_tensor * x = ggml_new_tensor_2d(g.ctx, GGML_TYPE_F32, K, N);
+        ggml_tensor * o = ggml_mul_mat(g.ctx, w, x);
+        if (!ggml_backend_supports_op(g.be, o)) rc = 2;
+        else if (!finish(g, o)) rc = 3;
+        else {
+            ggml_backend_tensor_set(w, W, 0, ggml_nbytes(w));
+            if (W_back) ggml_backend_tensor_get(w, W_back, 0, ggml_nbytes(w));
+            ggml_backend_tensor_set(x, X, 0, ggml_nbytes(x));
+            for (int r = 0; r < (repeats > 0 ? repeats : 1) && rc == 0; r++) {
+                if (ggml_backend_graph_compute(g.be, g.graph) != GGML_STATUS_SUCCESS) rc = 4;
+            }
+            ggml_backend_synchronize(g.be);
+            if (rc == 0 && dst) ggml_backend_tensor_get(o, dst, 0, ggml_nbytes(o));
+        }
+    }
+    if (wbuf) ggml_backend_buffer_free(wbuf);
+    ggml_free(wctx);
+    return rc;
+}
+
 // dst[M, n_used, n_tok] = MUL_MAT_ID(as[K, M, n_as] (type), b[K, ne11, n_tok] f32, ids[n_used, n_tok] i32)
 int refh_mul_mat_id(int reg, int dev, int n_threads, int type, int64_t M, int64_t K, int64_t n_as,
                     int64_t n_used, int64_t ne11, int64_t n_tok,

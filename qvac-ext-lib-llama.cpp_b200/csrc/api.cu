@@ -352,6 +352,26 @@ b200_status b200_memcpy_d2d_async(b200_ctx * ctx, void * dst, const void * src, 
     return B200_OK;
 }
 
+b200_status b200_memcpy2d_async(b200_ctx * ctx, void * dst, size_t dpitch, const void * src, size_t spitch, size_t width, size_t height) {
+    if (!ctx) return fail(B200_ERR_ARG, "null context");
+    if (width == 0 || height == 0) return B200_OK;
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, height, cudaMemcpyDefault, ctx->stream));  // unified addressing names the devices
+    return B200_OK;
+}
+b200_status b200_enable_peer_access(int device, int peer) {
+    if (device == peer) return B200_OK;
+    int can = 0;
+    CU(cudaDeviceCanAccessPeer(&can, device, peer));
+    if (!can) return fail(B200_ERR_UNSUPPORTED, "device %d cannot access device %d directly", device, peer);
+    CU(cudaSetDevice(device));
+    const cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(B200_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d -> %d): %s", device, peer, cudaGetErrorString(e));
+    cudaGetLastError();
+    return B200_OK;
+}
+
 b200_status b200_event_create(int device, void ** event) {
     CU(cudaSetDevice(device));
     cudaEvent_t ev;

@@ -18,7 +18,10 @@
 
 #include <cstdint>
 #include <cstdio>
+#include <algorithm>
+#include <array>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -40,11 +43,23 @@ struct buf_ctx {
     void * base;
 };
 
+// a split MUL_MAT runs one slice on every device: the backend keeps a context (stream), an event and scratch for the replicated
+// src1 and the dst slice on each of the other devices (created on first use)
+struct split_peer {
+    b200_ctx * ctx     = nullptr;
+    void *     event   = nullptr;
+    void *     x       = nullptr;
+    size_t     x_size  = 0;
+    void *     d       = nullptr;
+    size_t     d_size  = 0;
+};
 struct be_ctx {
     int        device;
     b200_ctx * ctx;
     std::string name;
     bool       fuse;
+    void *     split_event = nullptr;              // "src1 is ready" on the main stream
+    split_peer peers[B200_MAX_DEVICES];
 };
 
 ggml_backend_reg_t b200_reg();
@@ -165,6 +180,141 @@ const ggml_backend_buffer_type_i host_buft_iface = {
     /* .is_host        = */ host_buft_is_host,
 };
 
+// ------------------------------------------------------------------------------------------------ split buffer type
+//
+// ggml_backend_split_buffer_type(main_device, tensor_split) (ggml-backend.h:199-200; the reference's version: ggml-cuda.cu:773-1102):
+// a 2-D weight tensor placed in such a buffer is stored as one row slice per device of the process - rows [low, high) by the
+// get_row_split rule (:786-799: cumulative fractions, boundaries rounded down, the last device takes the rest). There is no single
+// base address: tensor->extra carries the per-device pointers (the reference keeps them there too, common.cuh:943-946).
+
+const int64_t SPLIT_ROUNDING = 128;  // rows: the tile height of the tensor-core kernels (the reference rounds to its mmq_y, :773-784)
+
+struct split_buft_ctx {
+    int         main_device;
+    std::array<float, B200_MAX_DEVICES> tensor_split;  // cumulative start fraction of every device
+    std::string name;
+};
+struct split_extra {
+    void *  data[B200_MAX_DEVICES]     = {};
+    int64_t row_low[B200_MAX_DEVICES]  = {};
+    int64_t row_high[B200_MAX_DEVICES] = {};
+};
+struct split_buf_ctx {
+    std::vector<split_extra *> extras;
+};
+
+int split_dev_count() { return std::min(b200_device_count(), B200_MAX_DEVICES); }
+
+void split_rows(const split_buft_ctx * c, int64_t nrows, int id, int64_t * low, int64_t * high) {
+    const int n = split_dev_count();
+    *low = id == 0 ? 0 : (int64_t) (nrows * c->tensor_split[id]);
+    *low -= *low % SPLIT_ROUNDING;
+    if (id == n - 1) {
+        *high = nrows;
+    } else {
+        *high = (int64_t) (nrows * c->tensor_split[id + 1]);
+        *high -= *high % SPLIT_ROUNDING;
+    }
+}
+
+const char * split_buft_name(ggml_backend_buffer_type_t buft) { return ((split_buft_ctx *) buft->context)->name.c_str(); }
+bool buft_is_split(ggml_backend_buffer_type_t buft) { return buft->iface.get_name == split_buft_name; }
+
+void split_buf_free(ggml_backend_buffer_t buffer) {
+    split_buf_ctx * c = (split_buf_ctx *) buffer->context;
+    for (split_extra * e : c->extras) {
+        for (int id = 0; id < B200_MAX_DEVICES; id++) {
+            if (!e->data[id]) continue;
+            b200_weight_cache_invalidate(id, e->data[id], 1);
+            b200_free(id, e->data[id]);
+        }
+        delete e;
+    }
+    delete c;
+}
+void * split_buf_get_base(ggml_backend_buffer_t) { return (void *) 0x1000; }  // never dereferenced (the reference returns the same dummy, :833-837)
+ggml_status split_buf_init_tensor(ggml_backend_buffer_t buffer, ggml_tensor * t) {
+    GGML_ASSERT(t->view_src == nullptr);  // views of split tensors are not supported (:846-848)
+    GGML_ASSERT(ggml_is_contiguous(t) && "split buffers only support contiguous tensors");
+    split_buf_ctx *  c  = (split_buf_ctx *) buffer->context;
+    split_buft_ctx * bc = (split_buft_ctx *) buffer->buft->context;
+    split_extra * e = new split_extra();
+    c->extras.push_back(e);
+    const int64_t nrows = ggml_nrows(t);
+    const size_t  nb1   = t->nb[1];
+    for (int id = 0; id < split_dev_count(); id++) {
+        split_rows(bc, nrows, id, &e->row_low[id], &e->row_high[id]);
+        const int64_t n = e->row_high[id] - e->row_low[id];
+        if (n <= 0) continue;
+        if (b200_malloc(id, (size_t) n * nb1, &e->data[id]) != B200_OK) {
+            GGML_LOG_ERROR("ggml-b200: allocating a %.2f MiB slice of %s on device %d failed: %s\n", n * nb1 / 1048576.0, t->name, id, b200_last_error());
+            return GGML_STATUS_ALLOC_FAILED;
+        }
+    }
+    t->extra = e;
+    return GGML_STATUS_SUCCESS;
+}
+void split_buf_set_tensor(ggml_backend_buffer_t, ggml_tensor * t, const void * data, size_t offset, size_t size) {
+    GGML_ASSERT(offset == 0 && size == ggml_nbytes(t));  // split tensors are set in one piece (:908-909)
+    split_extra * e = (split_extra *) t->extra;
+    const size_t nb1 = t->nb[1];
+    for (int id = 0; id < split_dev_count(); id++) {
+        const int64_t n = e->row_high[id] - e->row_low[id];
+        if (n <= 0) continue;
+        b200_weight_cache_invalidate(id, e->data[id], (size_t) n * nb1);
+        CHECK(b200_memcpy_h2d(id, e->data[id], (const char *) data + e->row_low[id] * nb1, (size_t) n * nb1));
+    }
+}
+void split_buf_get_tensor(ggml_backend_buffer_t, const ggml_tensor * t, void * data, size_t offset, size_t size) {
+    GGML_ASSERT(offset == 0 && size == ggml_nbytes(t));
+    const split_extra * e = (const split_extra *) t->extra;
+    const size_t nb1 = t->nb[1];
+    for (int id = 0; id < split_dev_count(); id++) {
+        const int64_t n = e->row_high[id] - e->row_low[id];
+        if (n > 0) CHECK(b200_memcpy_d2h(id, (char *) data + e->row_low[id] * nb1, e->data[id], (size_t) n * nb1));
+    }
+}
+void split_buf_clear(ggml_backend_buffer_t, uint8_t) {}  // as the reference (:960-963)
+
+const ggml_backend_buffer_i split_buf_iface = {
+    /* .free_buffer   = */ split_buf_free,
+    /* .get_base      = */ split_buf_get_base,
+    /* .init_tensor   = */ split_buf_init_tensor,
+    /* .memset_tensor = */ nullptr,
+    /* .set_tensor    = */ split_buf_set_tensor,
+    /* .get_tensor    = */ split_buf_get_tensor,
+    /* .cpy_tensor    = */ nullptr,
+    /* .clear         = */ split_buf_clear,
+    /* .reset         = */ nullptr,
+};
+
+ggml_backend_buffer_t split_buft_alloc(ggml_backend_buffer_type_t buft, size_t size) {
+    // the slices are allocated tensor by tensor in init_tensor; `size` only has to be what get_alloc_size promised
+    return ggml_backend_buffer_init(buft, split_buf_iface, new split_buf_ctx(), size);
+}
+size_t split_buft_alignment(ggml_backend_buffer_type_t) { return 256; }
+size_t split_buft_alloc_size(ggml_backend_buffer_type_t buft, const ggml_tensor * t) {
+    const split_buft_ctx * c = (const split_buft_ctx *) buft->context;
+    GGML_ASSERT(ggml_is_contiguous(t) && "split buffers only support contiguous tensors");
+    size_t total = 0;
+    for (int id = 0; id < split_dev_count(); id++) {
+        int64_t lo, hi;
+        split_rows(c, ggml_nrows(t), id, &lo, &hi);
+        if (hi > lo) total += (size_t) (hi - lo) * t->nb[1];
+    }
+    return total;
+}
+bool split_buft_is_host(ggml_backend_buffer_type_t) { return false; }
+
+const ggml_backend_buffer_type_i split_buft_iface = {
+    /* .get_name       = */ split_buft_name,
+    /* .alloc_buffer   = */ split_buft_alloc,
+    /* .get_alignment  = */ split_buft_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ split_buft_alloc_size,
+    /* .is_host        = */ split_buft_is_host,
+};
+
 // ------------------------------------------------------------------------------------------------ op geometry
 
 bool is_noop(const ggml_tensor * t) {
@@ -209,6 +359,16 @@ bool fill_mul_mat_id(const ggml_tensor * op, b200_mul_mat_id_desc * d) {
 const char * be_name(ggml_backend_t backend) { return ((be_ctx *) backend->context)->name.c_str(); }
 void be_free(ggml_backend_t backend) {
     be_ctx * c = (be_ctx *) backend->context;
+    for (int id = 0; id < B200_MAX_DEVICES; id++) {
+        split_peer & sp = c->peers[id];
+        if (!sp.ctx) continue;
+        b200_ctx_synchronize(sp.ctx);
+        if (sp.x) b200_free(id, sp.x);
+        if (sp.d) b200_free(id, sp.d);
+        if (sp.event) b200_event_destroy(id, sp.event);
+        b200_ctx_destroy(sp.ctx);
+    }
+    if (c->split_event) b200_event_destroy(c->device, c->split_event);
     b200_ctx_destroy(c->ctx);
     delete c;
     delete backend;
@@ -228,6 +388,67 @@ bool ranges_overlap(const ggml_tensor * a, const ggml_tensor * b) {
     return a0 < b0 + ggml_nbytes(b) && b0 < a0 + ggml_nbytes(a);
 }
 
+bool grow(int device, void ** buf, size_t * cur, size_t need) {
+    if (*cur >= need) return true;
+    if (*buf) b200_free(device, *buf);
+    *buf = nullptr; *cur = 0;
+    if (b200_malloc(device, need, buf) != B200_OK) return false;
+    *cur = need;
+    return true;
+}
+
+// MUL_MAT whose src0 lives in a split buffer (ggml_cuda_op_mul_mat for split tensors, ggml-cuda.cu:1447-1765): every device
+// multiplies its row slice by the whole src1. The main device (this backend's) works in place: its slice of dst is written straight
+// into node->data with the full column stride. For every other device src1 is copied over once the main stream has produced it,
+// the slice is computed into scratch [N][rows] on that device's own stream, copied back into its rows of dst as a 2-D copy
+// (:1721-1734) and the main stream waits for that copy.
+ggml_status split_mul_mat(be_ctx * c, ggml_tensor * node, const b200_mul_mat_desc & full) {
+    const ggml_tensor * a = node->src[0], * b = node->src[1];
+    const split_extra * e = (const split_extra *) a->extra;
+    const split_buft_ctx * bc = (const split_buft_ctx *) a->buffer->buft->context;
+    GGML_ASSERT(e && bc->main_device == c->device && "a split tensor is computed by the backend of its main device");
+    const int64_t N = full.ne11, K = full.ne00;
+    const size_t x_bytes = (size_t) N * K * sizeof(float);
+    if (!c->split_event) CHECK(b200_event_create(c->device, &c->split_event));
+    CHECK(b200_event_record(c->ctx, c->split_event));
+    for (int id = 0; id < split_dev_count(); id++) {
+        const int64_t rows = e->row_high[id] - e->row_low[id];
+        if (rows <= 0) continue;
+        b200_mul_mat_desc d = full;
+        d.ne01 = rows;
+        if (id == c->device) {
+            CHECK(b200_mul_mat(c->ctx, &d, e->data[id], (const float *) b->data, (float *) node->data + e->row_low[id]));
+            continue;
+        }
+        split_peer & sp = c->peers[id];
+        if (!sp.ctx) {
+            if (b200_ctx_create(id, nullptr, &sp.ctx) != B200_OK) {
+                GGML_LOG_ERROR("ggml-b200: cannot create a context on device %d for a split tensor: %s\n", id, b200_last_error());
+                return GGML_STATUS_FAILED;
+            }
+            const char * wc = getenv("GGML_B200_WEIGHT_CACHE");
+            b200_ctx_set_weight_cache(sp.ctx, !(wc && !atoi(wc)));
+            CHECK(b200_event_create(id, &sp.event));
+            b200_enable_peer_access(id, c->device);  // best effort: the copies are staged by the driver otherwise
+            b200_enable_peer_access(c->device, id);
+        }
+        if (!grow(id, &sp.x, &sp.x_size, x_bytes) || !grow(id, &sp.d, &sp.d_size, (size_t) N * rows * sizeof(float))) return GGML_STATUS_ALLOC_FAILED;
+        CHECK(b200_event_wait(sp.ctx, c->split_event));
+        // src1 rows may be strided on the main device: pack them into [N][K] on the peer
+        CHECK(b200_memcpy2d_async(sp.ctx, sp.x, (size_t) K * sizeof(float), b->data, full.nb11, (size_t) K * sizeof(float), (size_t) N));
+        d.nb11 = (size_t) K * sizeof(float); d.nb12 = d.nb11 * N; d.nb13 = d.nb12;
+        d.nb1  = (size_t) rows * sizeof(float); d.nb2 = d.nb1 * N; d.nb3 = d.nb2;
+        CHECK(b200_mul_mat(sp.ctx, &d, e->data[id], (const float *) sp.x, (float *) sp.d));
+        CHECK(b200_memcpy2d_async(sp.ctx, (float *) node->data + e->row_low[id], full.nb1, sp.d, (size_t) rows * sizeof(float),
+                                  (size_t) rows * sizeof(float), (size_t) N));
+        CHECK(b200_event_record(sp.ctx, sp.event));
+    }
+    for (int id = 0; id < split_dev_count(); id++) {
+        if (id != c->device && e->row_high[id] > e->row_low[id]) CHECK(b200_event_wait(c->ctx, c->peers[id].event));
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
 ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     be_ctx * c = (be_ctx *) backend->context;
     for (int i = 0; i < cgraph->n_nodes; i++) {
@@ -241,6 +462,11 @@ ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
                 GGML_LOG_ERROR("ggml-b200: unsupported MUL_MAT reached graph_compute (%s)\n", node->name);
                 return GGML_STATUS_FAILED;
             }
+            if (node->src[0]->buffer && buft_is_split(node->src[0]->buffer->buft)) {
+                const ggml_status st = split_mul_mat(c, node, descs[0]);
+                if (st != GGML_STATUS_SUCCESS) return st;
+                continue;
+            }
             w[0] = node->src[0]->data;
             o[0] = (float *) node->data;
             int n = 1;
@@ -249,6 +475,7 @@ ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
             while (c->fuse && n < 4 && i + n < cgraph->n_nodes) {
                 ggml_tensor * nx = cgraph->nodes[i + n];
                 if (nx->op != GGML_OP_MUL_MAT || nx->src[1] != node->src[1] || !fill_mul_mat(nx, &descs[n])) break;
+                if (nx->src[0]->buffer && buft_is_split(nx->src[0]->buffer->buft)) break;
                 if (descs[n].type != descs[0].type || descs[n].ne00 != descs[0].ne00 || descs[0].ne12 != 1 || descs[0].ne13 != 1) break;
                 bool clash = ranges_overlap(nx, node->src[1]);
                 for (int j = 0; j < n; j++) clash = clash || ranges_overlap(nx, cgraph->nodes[i + j]) || nx->src[0] == cgraph->nodes[i + j];
@@ -339,7 +566,9 @@ ggml_backend_t dev_init_backend(ggml_backend_dev_t dev, const char *) {
 ggml_backend_buffer_type_t dev_buffer_type(ggml_backend_dev_t dev) { return &((dev_ctx *) dev->context)->buft; }
 ggml_backend_buffer_type_t dev_host_buffer_type(ggml_backend_dev_t dev) { return &((dev_ctx *) dev->context)->host_buft; }
 
-bool dev_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) { return buft_is_b200(buft) && buft->device == dev; }
+bool dev_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
+    return (buft_is_b200(buft) && buft->device == dev) || buft_is_split(buft);  // as ggml-cuda.cu:4587-4590
+}
 
 bool dev_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
     // tensors must live in our buffers when they are already allocated (llama probes with 0-byte buffers of the
@@ -359,10 +588,17 @@ bool dev_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
             return true;
         case GGML_OP_MUL_MAT: {
             b200_mul_mat_desc d;
-            return fill_mul_mat(op, &d);
+            if (!fill_mul_mat(op, &d)) return false;
+            const ggml_tensor * a = op->src[0];
+            if (a->buffer && buft_is_split(a->buffer->buft)) {  // row slices: plain 2-D matrices only, computed on the main device's backend
+                const split_buft_ctx * bc = (const split_buft_ctx *) a->buffer->buft->context;
+                return d.ne02 == 1 && d.ne03 == 1 && d.ne12 == 1 && d.ne13 == 1 && bc->main_device == ((dev_ctx *) dev->context)->device;
+            }
+            return true;
         }
         case GGML_OP_MUL_MAT_ID: {
             b200_mul_mat_id_desc d;
+            if (op->src[0] && op->src[0]->buffer && buft_is_split(op->src[0]->buffer->buft)) return false;  // as ggml-cuda.cu:4261-4268
             return fill_mul_mat_id(op, &d);
         }
         default:
@@ -426,9 +662,38 @@ ggml_backend_feature * reg_features(ggml_backend_reg_t) {
     return f;
 }
 
+// ggml_backend_split_buffer_type_t (ggml-backend.h:199-200): singletons per (main device, normalised split), mutex guarded
+// because llama calls it from loader threads (ggml-cuda.cu:1062-1099)
+ggml_backend_buffer_type_t split_buffer_type(int main_device, const float * tensor_split) {
+    static std::mutex mutex;
+    std::lock_guard<std::mutex> lock(mutex);
+    static std::map<std::pair<int, std::array<float, B200_MAX_DEVICES>>, ggml_backend_buffer_type> bufts;
+    const int n = split_dev_count();
+    if (main_device < 0 || main_device >= n) return nullptr;
+    std::array<float, B200_MAX_DEVICES> ts = {};
+    bool all_zero = tensor_split == nullptr;
+    if (!all_zero) {
+        all_zero = true;
+        for (int i = 0; i < n; i++) all_zero = all_zero && tensor_split[i] == 0.0f;
+    }
+    if (all_zero) {  // default: equal shares (the reference weighs by device memory, ggml-cuda.cu:277-285; these are identical parts)
+        for (int i = 0; i < n; i++) ts[i] = (float) i / (float) n;
+    } else {         // cumulative sum of the requested proportions, normalised (:1070-1080)
+        float sum = 0.0f;
+        for (int i = 0; i < n; i++) { ts[i] = sum; sum += tensor_split[i]; }
+        for (int i = 0; i < n; i++) ts[i] /= sum;
+    }
+    auto it = bufts.find({ main_device, ts });
+    if (it != bufts.end()) return &it->second;
+    split_buft_ctx * c = new split_buft_ctx{ main_device, ts, std::string(B200_NAME) + std::to_string(main_device) + "_Split" };
+    ggml_backend_buffer_type buft = { split_buft_iface, ggml_backend_reg_dev_get(b200_reg(), (size_t) main_device), c };
+    return &bufts.emplace(std::make_pair(main_device, ts), buft).first->second;
+}
+
 void * reg_proc_address(ggml_backend_reg_t, const char * name) {
     if (!strcmp(name, "ggml_backend_get_features")) return (void *) reg_features;
-    // "ggml_backend_split_buffer_type", "ggml_backend_set_n_threads", "ggml_backend_dev_get_extra_bufts": not provided
+    if (!strcmp(name, "ggml_backend_split_buffer_type")) return (void *) split_buffer_type;
+    // "ggml_backend_set_n_threads", "ggml_backend_dev_get_extra_bufts": not provided
     return nullptr;
 }
 

@@ -64,3 +64,28 @@ def test_reference_conformance_harness(pkg, op):
     assert m.group(1) == m.group(2), tail
     assert int(m.group(2)) > 50, tail   # it really ran our quantized cases
     assert rc == 0, tail
+
+
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
+@pytest.mark.parametrize("M,K,N,split", [(512, 1024, 1, None), (700, 512, 3, None), (1024, 2048, 40, None), (640, 1024, 2, [3.0, 1.0]),
+                                         (100, 256, 1, None)])
+def test_split_buffer_type_mul_mat(harness, refq, oracle, b200, t, M, K, N, split):
+    """ggml_backend_split_buffer_type through the registry's get_proc_address (ggml-backend.h:199-200), the way llama places weights
+    with --split-mode row (src/llama-model.cpp:385-403): the weight tensor's rows are spread over the devices of the process by the
+    get_row_split rule, a MUL_MAT on it must match ggml-cpu, repeated computes must agree, and reading the tensor back must return
+    the original bytes. On a one-GPU box the single device owns every row; with more devices the slices are real (M = 100 leaves
+    devices without rows: boundaries are rounded down to 128)."""
+    rng = np.random.default_rng(M + K + N + t)
+    W = refq.quantize_weights(t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    n_dev = harness.lib.refh_reg_dev_count(b200)
+    ts = None if split is None else (split + [0.0] * 16)[:max(n_dev, 1)]
+    if ts is not None and sum(ts) == 0:
+        ts = None
+    got, back = harness.mul_mat_split(b200, t, W, X, tensor_split=ts, repeats=3)
+    ref, _ = harness.mul_mat(harness.cpu("x64"), t, W, X, n_threads=4)
+    assert np.array_equal(back, W.reshape(back.shape))
+    assert oracle.nmse(ref, got) <= (1e-10 if N <= 8 else 1e-6)
+    plain, _ = harness.mul_mat(b200, t, W, X)
+    if n_dev == 1:
+        assert np.array_equal(plain, got)      # one device: the same kernels on the same rows
