@@ -7,7 +7,8 @@
 // the exported symbols are ggml_backend_init / ggml_backend_score (ggml-backend-impl.h:215-251).
 //
 // What it mirrors in ggml-cuda (paths relative to /root/reference/ggml/src/ggml-cuda/ggml-cuda.cu):
-//   buffer + buffer type :564-769, pinned host buffer type :1104-1168, backend (stream) iface :2748-2862, 3679-3754,
+//   buffer + buffer type :564-769, split buffer type :773-1102 + split MUL_MAT :1447-1765, pinned host buffer type :1104-1168,
+//   backend (stream) iface :2748-2862, 3679-3754,
 //   device iface :4160-4677, reg + get_proc_address :4683-4830.
 
 #include "ggml-backend-impl.h"
