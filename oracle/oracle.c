@@ -60,6 +60,7 @@ size_t orc_row_size(int type, int64_t k) {
         case ORC_Q4_0: return (size_t)(k / ORC_QK) * ORC_SZ_Q4_0;
         case ORC_Q8_0: return (size_t)(k / ORC_QK) * ORC_SZ_Q8_0;
         case ORC_Q4_K: return (size_t)(k / ORC_QK_K) * ORC_SZ_Q4_K;
+        case ORC_Q6_K: return (size_t)(k / ORC_QK_K) * ORC_SZ_Q6_K;
     }
     return 0;
 }
@@ -275,18 +276,66 @@ float orc_vec_dot_q4_K_q8_K(int64_t k, const void *vx, const void *vy) {
     return sumf;
 }
 
+/* block_q6_K = { uint8 ql[128]; uint8 qh[64]; int8 scales[16]; fp16 d } (ggml-common.h:335-343). Weight l of a 128-half:
+ * low nibble / high nibble of ql[l], ql[l+32] plus two bits of qh[l], minus 32; one int8 scale per 16 weights
+ * (ggml-quants.c:1762-1791) */
+static void q6k_unpack(const uint8_t *x, int8_t *a) {
+    const uint8_t *ql = x, *qh = x + 128;
+    for (int n = 0; n < ORC_QK_K; n += 128, a += 128, ql += 64, qh += 32) {
+        for (int l = 0; l < 32; l++) {
+            a[l +  0] = (int8_t)((ql[l +  0] & 0xF) | (((qh[l] >> 0) & 3) << 4)) - 32;
+            a[l + 32] = (int8_t)((ql[l + 32] & 0xF) | (((qh[l] >> 2) & 3) << 4)) - 32;
+            a[l + 64] = (int8_t)((ql[l +  0] >>  4) | (((qh[l] >> 4) & 3) << 4)) - 32;
+            a[l + 96] = (int8_t)((ql[l + 32] >>  4) | (((qh[l] >> 6) & 3) << 4)) - 32;
+        }
+    }
+}
+void orc_dequantize_row_q6_K(const void *vx, float *y, int64_t k) {
+    const uint8_t *x = (const uint8_t *)vx;
+    for (int64_t b = 0; b < k / ORC_QK_K; b++, x += ORC_SZ_Q6_K, y += ORC_QK_K) {
+        uint16_t hd; memcpy(&hd, x + 208, 2);
+        const float d = orc_fp16_to_fp32(hd);
+        const int8_t *sc = (const int8_t *)(x + 192);
+        int8_t a[ORC_QK_K];
+        q6k_unpack(x, a);
+        for (int i = 0; i < ORC_QK_K; i++) y[i] = d * sc[i / 16] * a[i];   /* (d * sc) * q, left to right as :1780-1783 */
+    }
+}
+/* ggml-cpu/quants.c:705-758: 8 interleaved int32 lanes, each 16-group scaled by its int8 scale, sums[l] += (d*y.d)*aux32[l],
+ * sumf = sum_l sums[l] at the very end. The lane structure is kept so that fp32 rounding matches the generic code. */
+float orc_vec_dot_q6_K_q8_K(int64_t k, const void *vx, const void *vy) {
+    const uint8_t *x = (const uint8_t *)vx, *y = (const uint8_t *)vy;
+    float sums[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int64_t b = 0; b < k / ORC_QK_K; b++, x += ORC_SZ_Q6_K, y += ORC_SZ_Q8_K) {
+        float yd; memcpy(&yd, y, 4);
+        const int8_t *q8 = (const int8_t *)(y + 4);
+        const int8_t *sc = (const int8_t *)(x + 192);
+        uint16_t hd; memcpy(&hd, x + 208, 2);
+        int8_t a[ORC_QK_K];
+        q6k_unpack(x, a);
+        int32_t lane[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int i = 0; i < ORC_QK_K; i++) lane[i & 7] += (int32_t)sc[i / 16] * (int16_t)(q8[i] * a[i]);
+        const float d = orc_fp16_to_fp32(hd) * yd;
+        for (int l = 0; l < 8; l++) sums[l] += d * lane[l];
+    }
+    float sumf = 0;
+    for (int l = 0; l < 8; l++) sumf += sums[l];
+    return sumf;
+}
+
 /* ---------- the ops ---------- */
 
 static size_t act_row_size(int type, int64_t k) {
-    return type == ORC_Q4_K ? (size_t)(k / ORC_QK_K) * ORC_SZ_Q8_K : (size_t)(k / ORC_QK) * ORC_SZ_Q8_0;
+    return (type == ORC_Q4_K || type == ORC_Q6_K) ? (size_t)(k / ORC_QK_K) * ORC_SZ_Q8_K : (size_t)(k / ORC_QK) * ORC_SZ_Q8_0;
 }
 static void act_quantize(int type, const float *x, void *y, int64_t k) {
-    if (type == ORC_Q4_K) orc_quantize_row_q8_K(x, y, k); else orc_quantize_row_q8_0(x, y, k);
+    if (type == ORC_Q4_K || type == ORC_Q6_K) orc_quantize_row_q8_K(x, y, k); else orc_quantize_row_q8_0(x, y, k);
 }
 static float dot(int type, int64_t k, const void *w, const void *a) {
     switch (type) {
         case ORC_Q4_0: return orc_vec_dot_q4_0_q8_0(k, w, a);
         case ORC_Q8_0: return orc_vec_dot_q8_0_q8_0(k, w, a);
+        case ORC_Q6_K: return orc_vec_dot_q6_K_q8_K(k, w, a);
         default:       return orc_vec_dot_q4_K_q8_K(k, w, a);
     }
 }
@@ -337,6 +386,7 @@ void orc_mul_mat_f64(int type, const void *W, int64_t M, int64_t K, size_t nb01,
         const void *row = (const char *)W + r * nb01;
         if (type == ORC_Q4_0) orc_dequantize_row_q4_0(row, wf, K);
         else if (type == ORC_Q8_0) orc_dequantize_row_q8_0(row, wf, K);
+        else if (type == ORC_Q6_K) orc_dequantize_row_q6_K(row, wf, K);
         else orc_dequantize_row_q4_K(row, wf, K);
         for (int64_t n = 0; n < N; n++) {
             const float *x = (const float *)((const char *)X + n * nb11);
