@@ -435,7 +435,7 @@ b200_status b200_quantize_units(b200_ctx * ctx, int kind, const float * x, int64
 
 // ------------------------------------------------------------------------------------------------ MUL_MAT
 
-static bool type_ok(int t) { return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K; }
+static bool type_ok(int t) { return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q6_K; }
 
 static size_t row_bytes(int type, int64_t k) { return (size_t) (k / type_block_elems(type)) * type_block_bytes(type); }
 
@@ -495,7 +495,7 @@ static void mv_geometry(int U, MvParams * p) {
 }
 
 static bool fast_layout_ok(int type, int64_t K, const void * w, size_t nb01, size_t nb02, size_t nb03) {
-    (void) type;
+    if (type == B200_TYPE_Q6_K && K % 2048 != 0) return false;  // 210-byte units: a row slice is a whole number of 16-byte words only 8 units at a time
     return K % 256 == 0 && (uintptr_t) w % 16 == 0 && nb01 % 16 == 0 && nb02 % 16 == 0 && nb03 % 16 == 0;
 }
 
@@ -704,8 +704,8 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
 
     if (b200_status fst = b200_split_flush(ctx)) return fst;
     // generic path: reference block layout for the activations, one warp per row
-    const int    val    = type == B200_TYPE_Q4_K ? 1 : 0;
-    const size_t act_rs = type == B200_TYPE_Q4_K ? (size_t) (K / QK_K) * SZ_Q8_K : (size_t) (K / QK) * SZ_Q8_0;
+    const int    val    = type_is_k(type) ? 1 : 0;
+    const size_t act_rs = type_is_k(type) ? (size_t) (K / QK_K) * SZ_Q8_K : (size_t) (K / QK) * SZ_Q8_0;
     b200_status  st     = ensure(ctx, &ctx->scratch, &ctx->scratch_size, (size_t) n_rows * act_rs + 16);
     if (st != B200_OK) return st;
     uint8_t * act = (uint8_t *) ctx->scratch;

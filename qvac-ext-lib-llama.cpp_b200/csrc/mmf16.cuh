@@ -167,6 +167,19 @@ __global__ void __launch_bounds__(256) expand_f16_kernel(const uint8_t * __restr
 #pragma unroll
             for (int j = 0; j < 4; j++) v[4 * i + j] = (float) (int) (int8_t) (x >> (8 * j)) * d;
         }
+    } else if (TYPE == B200_TYPE_Q6_K) {
+        // 32-element block kb of the row = quarter (j & 3) of half (j >> 2) of a 256-weight q6_K block (2-byte aligned: byte loads)
+        const uint8_t * b = wr + (kb >> 3) * SZ_Q6_K;
+        const int j = (int) (kb & 7), hf = j >> 2, qv = j & 3;
+        const uint8_t * ql = b + 64 * hf + 32 * (qv & 1), * qh = b + 128 + 32 * hf;
+        const int8_t *  sc = (const int8_t *) (b + 192) + 8 * hf + 2 * qv;
+        const float d = half_bits_to_float(*(const uint16_t *) (b + 208));
+#pragma unroll
+        for (int l = 0; l < 32; l++) {
+            const int lo = (qv & 2) ? (ql[l] >> 4) : (ql[l] & 0xF);
+            const int q  = (lo | (((qh[l] >> (2 * qv)) & 3) << 4)) - 32;
+            v[l] = __fmul_rn(__fmul_rn(d, (float) (int) sc[l >> 4]), (float) q);  // d * sc * q, left to right (ggml-quants.c:1780-1783)
+        }
     } else {
         const uint8_t * b = wr + (kb >> 3) * SZ_Q4_K;
         const int j = (int) (kb & 7);
@@ -744,7 +757,7 @@ b200_status mmf_run(b200_ctx * ctx, int n_mats, WEntry * const * es, bool settle
         cfg.attrs    = attr;
         cfg.numAttrs = ctx->pdl ? 1 : 0;
         const int64_t units = (K + 255) / 256;
-        const bool    k8    = es[0]->type == B200_TYPE_Q4_K;
+        const bool    k8    = type_is_k(es[0]->type);
 #define ACT_LAUNCH(UPW) (k8 ? cudaLaunchKernelEx(&cfg, act_f16_kernel<ACT_KIND_Q8_K, UPW>, xs, K, x_rs, h + r0 * K, rs + r0, vec_ok) \
                             : cudaLaunchKernelEx(&cfg, act_f16_kernel<ACT_KIND_Q8_0, UPW>, xs, K, x_rs, h + r0 * K, rs + r0, vec_ok))
         // rows kept in registers between the two steps up to `env_reg` units; longer rows are read twice (the second read hits L2):

@@ -85,7 +85,7 @@ b200_status b200_mm_ids_sort(b200_ctx * ctx, const int32_t * ids, int64_t n_used
 
 int b200_mul_mat_id_supported(const b200_mul_mat_id_desc * d) {
     if (!d) return 0;
-    if (d->type != B200_TYPE_Q4_0 && d->type != B200_TYPE_Q8_0 && d->type != B200_TYPE_Q4_K) return 0;
+    if (d->type != B200_TYPE_Q4_0 && d->type != B200_TYPE_Q8_0 && d->type != B200_TYPE_Q4_K && d->type != B200_TYPE_Q6_K) return 0;
     if (d->ne00 <= 0 || d->ne00 % type_block_elems(d->type) != 0) return 0;
     if (d->ne01 < 0 || d->n_as <= 0 || d->ne11 <= 0 || d->n_tok < 0 || d->n_used <= 0) return 0;
     if (d->nb01 < (size_t) (d->ne00 / type_block_elems(d->type)) * type_block_bytes(d->type)) return 0;
@@ -113,7 +113,8 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
     mi.ne11   = (int) d->ne11;
     mi.n_as   = (int) d->n_as;
 
-    const bool fast = ctx->force_path != B200_PATH_SIMPLE && K % 256 == 0 && (uintptr_t) as % 16 == 0 && d->nb01 % 16 == 0 && d->nb02 % 16 == 0;
+    const bool fast = ctx->force_path != B200_PATH_SIMPLE && K % 256 == 0 && (uintptr_t) as % 16 == 0 && d->nb01 % 16 == 0 && d->nb02 % 16 == 0 &&
+                      (d->type != B200_TYPE_Q6_K || K % 2048 == 0);  // 210-byte units: bulk-copyable 8 at a time
     const int64_t n_rows = d->ne11 * d->n_tok;
 
     if (fast) {
@@ -208,8 +209,8 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
     }
 
     // generic path
-    const int    val    = d->type == B200_TYPE_Q4_K ? 1 : 0;
-    const size_t act_rs = d->type == B200_TYPE_Q4_K ? (size_t) (K / QK_K) * SZ_Q8_K : (size_t) (K / QK) * SZ_Q8_0;
+    const int    val    = type_is_k(d->type) ? 1 : 0;
+    const size_t act_rs = type_is_k(d->type) ? (size_t) (K / QK_K) * SZ_Q8_K : (size_t) (K / QK) * SZ_Q8_0;
     b200_status  st     = b200_ensure(ctx, &ctx->scratch, &ctx->scratch_size, (size_t) n_rows * act_rs + 16);
     if (st != B200_OK) return st;
     uint8_t * act = (uint8_t *) ctx->scratch;

@@ -187,9 +187,75 @@ __device__ __forceinline__ void unit_dot_q8_0(uint32_t w, uint32_t am, uint32_t 
     });
 }
 
+// q6_K: { uint8 ql[128]; uint8 qh[64]; int8 scales[16]; half d } = 210 bytes, so a lane's unit is only 2-byte aligned in shared
+// memory: every run of words is read as aligned 32-bit words and realigned with a funnel shift by 0 or 16 bits (lane dependent).
+// Weight l of a 128-half: nibbles of ql[l] / ql[l + 32] plus two bits of qh[l], minus 32 (ggml-quants.c:1762-1791). The two
+// fields occupy disjoint bits, so  signed byte = ((low + high + 0x60) ^ 0x80)  per byte (v in 0..63: v + 0x60 never carries and the
+// flipped top bit is v - 32 as int8): one 3-input add and one xor per four weights, shared by all columns; dp4a.s32.s32 against
+// the q8_K activations, one int8 scale per 16 weights applied in int32 exactly like vec_dot_q6_K_q8_K (ggml-cpu/quants.c:743-754).
+template <int NC>
+__device__ __forceinline__ void unit_dot_q6_K(uint32_t w, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc)[NC]) {
+    const uint32_t base = w & ~3u, sh = (w & 2u) * 8u;
+    auto run4 = [&](int word0, uint32_t (&o)[4]) {  // words word0 .. word0 + 3 of the unit
+        uint32_t r[5];
+#pragma unroll
+        for (int i = 0; i < 5; i++) r[i] = lds32(base + 4 * (word0 + i));
+#pragma unroll
+        for (int i = 0; i < 4; i++) o[i] = __funnelshift_r(r[i], r[i + 1], sh);
+    };
+    uint32_t scw[4];
+    run4(48, scw);  // 16 int8 scales
+    const float d = half_bits_to_float((uint16_t) (__funnelshift_r(lds32(base + 208), lds32(base + 212), sh) & 0xffff));
+    int      isum[NC];
+    uint32_t ac[NC];
+#pragma unroll
+    for (int c = 0; c < NC; c++) {
+        isum[c] = 0;
+        ac[c]   = am + c * cs_m;
+    }
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+#pragma unroll
+        for (int gq = 0; gq < 2; gq++) {  // 16 values of l: one scale group in each of the four 32-weight quarters
+            uint32_t A[4], B[4], H[4], s1[4], s2[4], s3[4], s4[4];
+            run4(16 * h + 4 * gq, A);
+            run4(16 * h + 8 + 4 * gq, B);
+            run4(32 + 8 * h + 4 * gq, H);
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                s1[i] = ((A[i] & 0x0F0F0F0Fu) + ((H[i] << 4) & 0x30303030u) + 0x60606060u) ^ 0x80808080u;
+                s2[i] = ((B[i] & 0x0F0F0F0Fu) + ((H[i] << 2) & 0x30303030u) + 0x60606060u) ^ 0x80808080u;
+                s3[i] = (((A[i] >> 4) & 0x0F0F0F0Fu) + (H[i] & 0x30303030u) + 0x60606060u) ^ 0x80808080u;
+                s4[i] = (((B[i] >> 4) & 0x0F0F0F0Fu) + ((H[i] >> 2) & 0x30303030u) + 0x60606060u) ^ 0x80808080u;
+            }
+            const int g1 = 8 * h + gq;  // scale groups g1, g1 + 2, g1 + 4, g1 + 6
+            auto scale = [&](int g) { return (int) (int8_t) (scw[g >> 2] >> (8 * (g & 3))); };
+            const int c1 = scale(g1), c2 = scale(g1 + 2), c3 = scale(g1 + 4), c4 = scale(g1 + 6);
+#pragma unroll
+            for (int c = 0; c < NC; c++) {
+                const uint32_t yb = ac[c] + 128 * h + 16 * gq;
+                const uint4 y1 = lds128(yb), y2 = lds128(yb + 32), y3 = lds128(yb + 64), y4 = lds128(yb + 96);
+                auto dot4 = [](const uint32_t (&q)[4], const uint4 & y) {
+                    int t = dp4a_ss((int) q[0], (int) y.x, 0);
+                    t     = dp4a_ss((int) q[1], (int) y.y, t);
+                    t     = dp4a_ss((int) q[2], (int) y.z, t);
+                    return dp4a_ss((int) q[3], (int) y.w, t);
+                };
+                isum[c] += c1 * dot4(s1, y1) + c2 * dot4(s2, y2) + c3 * dot4(s3, y3) + c4 * dot4(s4, y4);
+            }
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NC; c++) {
+        const float dy = __uint_as_float(lds32(ax + c * cs_x));
+        acc[c] = fmaf(d * dy, (float) isum[c], acc[c]);
+    }
+}
+
 template <int TYPE, int NC>
 __device__ __forceinline__ void unit_dot(uint32_t w, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc)[NC]) {
-    if (TYPE == B200_TYPE_Q4_K) unit_dot_q4_K<NC>(w, am, ax, cs_m, cs_x, acc);
+    if (TYPE == B200_TYPE_Q6_K) unit_dot_q6_K<NC>(w, am, ax, cs_m, cs_x, acc);
+    else if (TYPE == B200_TYPE_Q4_K) unit_dot_q4_K<NC>(w, am, ax, cs_m, cs_x, acc);
     else if (TYPE == B200_TYPE_Q4_0) unit_dot_q4_0<NC>(w, am, ax, cs_m, cs_x, acc);
     else unit_dot_q8_0<NC>(w, am, ax, cs_m, cs_x, acc);
 }
@@ -231,6 +297,7 @@ size_t mv_fast_smem(int type, int U, int ncols, int n_cons, int n_stages) {
     s += (size_t) ncols * U * (ACT_MAIN + ACT_AUX);
     s = mv_align(s, 128);
     s += (size_t) n_cons * n_stages * stage;
+    if (type == B200_TYPE_Q6_K) s += 16;  // the realigning loads of the last unit read up to 6 bytes past it
     return s;
 }
 
@@ -579,6 +646,7 @@ cudaError_t mv_fast_launch(int type, int ncols, const MvParams & p, int n_ctas, 
         case B200_TYPE_Q4_0: return mv_fast_launch_n<B200_TYPE_Q4_0>(ncols, p, n_ctas, n_pairs, smem, st);
         case B200_TYPE_Q8_0: return mv_fast_launch_n<B200_TYPE_Q8_0>(ncols, p, n_ctas, n_pairs, smem, st);
         case B200_TYPE_Q4_K: return mv_fast_launch_n<B200_TYPE_Q4_K>(ncols, p, n_ctas, n_pairs, smem, st);
+        case B200_TYPE_Q6_K: return mv_fast_launch_n<B200_TYPE_Q6_K>(ncols, p, n_ctas, n_pairs, smem, st);
     }
     return cudaErrorInvalidValue;
 }
@@ -613,7 +681,30 @@ __global__ void __launch_bounds__(128) mv_simple_kernel(const MvSimpleParams p) 
     const uint8_t * wr = p.w + w_off + (int64_t) row * p.nb01;
     const uint8_t * ar = p.act + (int64_t) act_row * p.act_rs;
     float acc = 0.0f;
-    if (TYPE == B200_TYPE_Q4_K) {
+    if (TYPE == B200_TYPE_Q6_K) {
+        for (int b = lane; b < p.K / QK_K; b += 32) {
+            const uint8_t * wb = wr + (int64_t) b * SZ_Q6_K;   // 2-byte aligned: byte and 16-bit loads only
+            const uint8_t * ab = ar + (int64_t) b * SZ_Q8_K;
+            const float     dy = *(const float *) ab;
+            const int8_t *  q8 = (const int8_t *) (ab + 4);
+            const int8_t *  sc = (const int8_t *) (wb + 192);
+            const float     d  = half_bits_to_float(*(const uint16_t *) (wb + 208));
+            int isum = 0;
+            for (int h = 0; h < 2; h++) {
+                const uint8_t * ql = wb + 64 * h, * qh = wb + 128 + 32 * h;
+                for (int l = 0; l < 32; l++) {
+                    const int is = 8 * h + l / 16;
+                    const int q1 = (int) ((ql[l] & 0xF) | (((qh[l] >> 0) & 3) << 4)) - 32;
+                    const int q2 = (int) ((ql[l + 32] & 0xF) | (((qh[l] >> 2) & 3) << 4)) - 32;
+                    const int q3 = (int) ((ql[l] >> 4) | (((qh[l] >> 4) & 3) << 4)) - 32;
+                    const int q4 = (int) ((ql[l + 32] >> 4) | (((qh[l] >> 6) & 3) << 4)) - 32;
+                    isum += sc[is] * q1 * q8[128 * h + l] + sc[is + 2] * q2 * q8[128 * h + 32 + l] + sc[is + 4] * q3 * q8[128 * h + 64 + l] +
+                            sc[is + 6] * q4 * q8[128 * h + 96 + l];
+                }
+            }
+            acc = fmaf(d * dy, (float) isum, acc);
+        }
+    } else if (TYPE == B200_TYPE_Q4_K) {
         for (int b = lane; b < p.K / QK_K; b += 32) {
             const uint8_t * wb = wr + (int64_t) b * SZ_Q4_K;
             const uint8_t * ab = ar + (int64_t) b * SZ_Q8_K;
@@ -678,6 +769,7 @@ cudaError_t mv_simple_launch(int type, const MvSimpleParams & p, cudaStream_t st
         case B200_TYPE_Q4_0: mv_simple_kernel<B200_TYPE_Q4_0><<<grid, 128, 0, st>>>(p); break;
         case B200_TYPE_Q8_0: mv_simple_kernel<B200_TYPE_Q8_0><<<grid, 128, 0, st>>>(p); break;
         case B200_TYPE_Q4_K: mv_simple_kernel<B200_TYPE_Q4_K><<<grid, 128, 0, st>>>(p); break;
+        case B200_TYPE_Q6_K: mv_simple_kernel<B200_TYPE_Q6_K><<<grid, 128, 0, st>>>(p); break;
         default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

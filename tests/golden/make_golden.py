@@ -1,6 +1,6 @@
 """Generates tests/golden/*.npz from the REFERENCE's own compiled code (oracle/_ref, built from /root/reference by
 oracle/Makefile): the reference quantizers (ggml-quants.c) and the ggml-cpu x64 (generic scalar) backend running
-one-op graphs. Run in the build container:  python tests/golden/make_golden.py
+one-op graphs. Run in the build container:  python tests/golden/make_golden.py  (first set)  and  ... --q6k  (the q6_K files)
 The fixtures are small on purpose; they pin oracle/oracle.c and, on the GPU box, the CUDA path."""
 import sys
 from pathlib import Path
@@ -9,7 +9,7 @@ import numpy as np
 
 ROOT = Path(__file__).resolve().parents[2]
 sys.path.insert(0, str(ROOT))
-from oracle.pyoracle import Q4_0, Q4_K, Q8_0, TYPE_NAMES, RefHarness, RefQuant  # noqa: E402
+from oracle.pyoracle import Q4_0, Q4_K, Q6_K, Q8_0, TYPE_NAMES, RefHarness, RefQuant  # noqa: E402
 
 OUT = Path(__file__).resolve().parent
 
@@ -68,5 +68,26 @@ def main():
     print("golden fixtures written to", OUT)
 
 
+def main_q6k():
+    """the q6_K fixtures (added after the first set; own seed so that the earlier files stay byte-identical)"""
+    rq, h = RefQuant(), RefHarness.get()
+    cpu = h.cpu("x64")
+    rng = np.random.default_rng(20261105)
+    t = Q6_K
+    for (M, K, N) in ((48, 1024, 5), (19, 256, 2)):
+        W = rq.quantize_weights(t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+        X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+        out, _ = h.mul_mat(cpu, t, W, X, n_threads=1)
+        np.savez_compressed(OUT / f"mul_mat_{TYPE_NAMES[t]}_{M}x{K}x{N}.npz", type=t, W=W, X=X, out=out, w_f32=np.zeros(0))
+    n_as, M, K, n_used, n_tok = 4, 32, 512, 2, 5
+    W = rq.quantize_weights(t, rng.uniform(-1, 1, (n_as * M, K)).astype(np.float32)).reshape(n_as, M, -1)
+    B = rng.uniform(-1, 1, (n_tok, 1, K)).astype(np.float32)
+    ids = np.stack([rng.permutation(n_as)[:n_used] for _ in range(n_tok)]).astype(np.int32)
+    out, _ = h.mul_mat_id(cpu, t, W, B, ids, n_threads=1)
+    np.savez_compressed(OUT / f"mul_mat_id_{TYPE_NAMES[t]}_b1.npz", type=t, W=W, B=B, ids=ids, out=out)
+    np.savez(OUT / "weight_slabs_q6_K.npz", q6_K=rq.quantize_weights(t, rng.uniform(-1, 1, (2048, 256)).astype(np.float32)))
+    print("q6_K golden fixtures written to", OUT)
+
+
 if __name__ == "__main__":
-    main()
+    main_q6k() if "--q6k" in sys.argv else main()
