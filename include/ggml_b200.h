@@ -175,6 +175,54 @@ B200_API b200_status  b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc
 B200_API b200_status  b200_mm_ids_sort(b200_ctx * ctx, const int32_t * ids, int64_t n_used, int64_t n_tok, size_t ids_nb1,
                                        int64_t n_as, int32_t * sorted_pairs, int32_t * expert_bounds);
 
+/* ---------------------------------------------------------------- K7: fused epilogues of the one-column mat-vec ---- */
+
+/* SURVEY 8(f) rank 1. The reference fuses, for one dst column only, {MUL_MAT(up), MUL_MAT(gate), GLU}, the same with an ADD
+ * (ADD_ID for MUL_MAT_ID) of a bias row behind each MUL_MAT, and {MUL_MAT, ADD} (ggml_cuda_should_fuse_mul_mat + the
+ * graph loop, ggml-cuda.cu:2020-2176, 3404-3600; epilogue of mul_mat_vec_q, mmvq.cu:181-328; test_mul_mat_vec_fusion,
+ * tests/test-backend-ops.cpp:5120-5249). Here it is an epilogue of the TMA-staged mat-vec kernel: a warp runs the gate rows
+ * of a row group, keeps the sums in registers, runs the same rows of the up matrix and stores glu(gate, up) - one launch,
+ * one quantization of src1, no intermediate tensors. glu_op values are enum ggml_glu_op (ggml.h:596-605). */
+#define B200_GLU_NONE        (-1)  /* dst = up . x + up_bias   ({MUL_MAT, ADD}) */
+#define B200_GLU_REGLU       0
+#define B200_GLU_GEGLU       1
+#define B200_GLU_SWIGLU      2
+#define B200_GLU_SWIGLU_OAI  3
+#define B200_GLU_GEGLU_ERF   4
+#define B200_GLU_GEGLU_QUICK 5
+
+typedef struct {
+    int32_t       glu_op;             /* B200_GLU_* */
+    float         alpha, limit;       /* SWIGLU_OAI (op_params 2, 3 of the GLU node; ggml-cpu/ops.cpp:3236-3237) */
+    const float * up_bias;            /* nullable. MUL_MAT: F32 of dst's shape [M, 1, ne12, ne13]; MUL_MAT_ID: [M, n_as] */
+    const float * gate_bias;          /* nullable; only with a GLU */
+    size_t        bias_nb1;           /* MUL_MAT_ID: bytes between the bias rows of two experts */
+    size_t        bias_nb2, bias_nb3; /* MUL_MAT: batch strides of the bias tensors */
+} b200_fusion;
+
+/* 1 if b200_mul_mat_fused would run this geometry as ONE fused launch; 0: run the nodes one by one (b200_mul_mat, b200_add,
+ * b200_glu). d describes the up MUL_MAT (ne11 must be 1); the gate matrix has the same type, shape and strides. */
+B200_API int          b200_mul_mat_fused_supported(const b200_ctx * ctx, const b200_mul_mat_desc * d);
+/* d->nb1..nb3 are the strides of `dst`, the output of the LAST fused node. gate == NULL iff f->glu_op == B200_GLU_NONE. */
+B200_API b200_status  b200_mul_mat_fused(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * up, const void * gate, const float * src1,
+                                         const b200_fusion * f, float * dst);
+/* same for MUL_MAT_ID with one token (d->n_tok == 1): dst[:, i] = glu(gate_as[ids[i]] . b + gate_bias[:, ids[i]], up_as[ids[i]] . b + ...) */
+B200_API int          b200_mul_mat_id_fused_supported(const b200_ctx * ctx, const b200_mul_mat_id_desc * d);
+B200_API b200_status  b200_mul_mat_id_fused(b200_ctx * ctx, const b200_mul_mat_id_desc * d, const void * up_as, const void * gate_as,
+                                            const float * b, const int32_t * ids, const b200_fusion * f, float * dst);
+
+/* The same nodes stand-alone (F32, dimension 0 contiguous), for when the pattern above does not apply.
+ * GGML_OP_GLU (ggml-cpu/ops.cpp:2934-3290; ggml-cuda/unary.cu ggml_cuda_op_unary_gated): dst[r][c] = glu(gate[r][c], up[r][c]) over
+ * nrows rows of nc values; the single-tensor and swapped forms are the caller's pointer arithmetic. */
+B200_API b200_status  b200_glu(b200_ctx * ctx, int glu_op, float alpha, float limit, const float * gate, size_t gate_nb1, const float * up,
+                               size_t up_nb1, float * dst, size_t dst_nb1, int64_t nc, int64_t nrows);
+/* GGML_OP_ADD with ggml broadcasting (ggml-cpu/binary-ops.cpp; ggml-cuda/binbcast.cu): ne/nb_* as struct ggml_tensor carries them */
+B200_API b200_status  b200_add(b200_ctx * ctx, const int64_t * ne, const float * a, const size_t * nb_a, const float * b, const int64_t * ne_b,
+                               const size_t * nb_b, float * dst, const size_t * nb_d);
+/* GGML_OP_ADD_ID (ggml-cpu/ops.cpp:701-750; ggml-cuda/add-id.cu): dst[:, i, t] = a[:, i, t] + bias[:, ids[i, t]] */
+B200_API b200_status  b200_add_id(b200_ctx * ctx, const float * a, size_t a_nb1, size_t a_nb2, const float * bias, size_t bias_nb1, int64_t n_as,
+                                  const int32_t * ids, size_t ids_nb1, float * dst, size_t nb1, size_t nb2, int64_t M, int64_t n_used, int64_t n_tok);
+
 /* ---------------------------------------------------------------- row-split tensor parallelism ---- */
 
 /* Weight rows split over n_ranks GPUs of one box (ggml_backend_split_buffer_type + ggml_cuda_op_mul_mat,

@@ -379,6 +379,41 @@ void orc_mul_mat_id(int type, const void *W, int64_t M, int64_t K, int64_t n_as,
     free(act);
 }
 
+/* ---------------------------------------------------------------- K7: GLU / ADD / ADD_ID ---- */
+
+float orc_glu_single(int op, float x, float g, float alpha, float limit) {
+    switch (op) {
+        case 0: return x > 0.0f ? x * g : 0.0f;                                       /* ggml_vec_reglu_f32 */
+        case 1: return 0.5f * x * (1.0f + tanhf(0.79788456080286535587989211986876f * x * (1.0f + 0.044715f * x * x))) * g; /* vec.h:873-875 */
+        case 2: return x / (1.0f + expf(-x)) * g;                                       /* vec.h:958-960 */
+        case 3: {                                                                       /* ops.cpp:3254-3259 */
+            const float xc = x < limit ? x : limit;
+            const float gc = g < -limit ? -limit : (g > limit ? limit : g);
+            return xc / (1.0f + expf(alpha * (-xc))) * (gc + 1.0f);
+        }
+        case 4: return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440084436210484f)) * g;
+        default: return x * (1.0f / (1.0f + expf(-1.702f * x))) * g;
+    }
+}
+
+void orc_glu(int op, float alpha, float limit, const float *gate, const float *up, float *dst, int64_t n) {
+    for (int64_t i = 0; i < n; i++) dst[i] = orc_glu_single(op, gate[i], up[i], alpha, limit);
+}
+
+void orc_add_row(const float *a, const float *bias, float *dst, int64_t M, int64_t nrows) {
+    for (int64_t r = 0; r < nrows; r++)
+        for (int64_t c = 0; c < M; c++) dst[r * M + c] = a[r * M + c] + bias[c];
+}
+
+void orc_add_id(const float *a, const float *bias, const int32_t *ids, float *dst, int64_t M, int64_t n_used, int64_t n_tok, int64_t n_as) {
+    for (int64_t t = 0; t < n_tok; t++)
+        for (int64_t i = 0; i < n_used; i++) {
+            const int32_t e = ids[t * n_used + i];
+            if (e < 0 || e >= n_as) abort();                                            /* ops.cpp:743 asserts */
+            for (int64_t c = 0; c < M; c++) dst[(t * n_used + i) * M + c] = a[(t * n_used + i) * M + c] + bias[(int64_t)e * M + c];
+        }
+}
+
 void orc_mul_mat_f64(int type, const void *W, int64_t M, int64_t K, size_t nb01,
                      const float *X, int64_t N, size_t nb11, double *dst) {
     float *wf = (float *)malloc(sizeof(float) * (size_t)K);

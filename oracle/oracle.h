@@ -76,6 +76,19 @@ void orc_mul_mat_id(int type, const void *W, int64_t M, int64_t K, int64_t n_as,
                     const int32_t *ids, int64_t n_used, size_t ids_nb1,
                     float *dst);
 
+/* K7 element-wise nodes around the MUL_MATs. glu_op = enum ggml_glu_op (ggml.h:596-605):
+ * 0 REGLU, 1 GEGLU, 2 SWIGLU, 3 SWIGLU_OAI, 4 GEGLU_ERF, 5 GEGLU_QUICK. x = gate branch (src0), g = linear branch (src1).
+ * Scalar float forms: ggml-cpu/vec.h:873-875 (gelu), 958-960 (silu), ops.cpp:3254-3259 (swiglu_oai), vec.h reglu /
+ * geglu_erf / geglu_quick. REGLU, SWIGLU_OAI and GEGLU_ERF are bit-identical to the compiled reference; ggml-cpu's vector paths use
+ * a polynomial expf for SWIGLU (ggml_v_silu, vec.cpp:376-410) and fp16 lookup tables for GEGLU / GEGLU_QUICK (vec.h:1326-1340), which
+ * these float formulas are the definition of: tests/test_fusion_k7.py pins those three at NMSE <= 1e-6 (measured <= 7e-8). */
+float orc_glu_single(int glu_op, float x, float g, float alpha, float limit);
+void  orc_glu(int glu_op, float alpha, float limit, const float *gate, const float *up, float *dst, int64_t n);
+/* dst[r][c] = a[r][c] + bias[c]  (GGML_OP_ADD of a [M] bias row onto [M, nrows]; ggml-cpu/binary-ops.cpp) */
+void  orc_add_row(const float *a, const float *bias, float *dst, int64_t M, int64_t nrows);
+/* GGML_OP_ADD_ID (ggml-cpu/ops.cpp:701-750): dst[:, i, t] = a[:, i, t] + bias[:, ids[i, t]]; all contiguous */
+void  orc_add_id(const float *a, const float *bias, const int32_t *ids, float *dst, int64_t M, int64_t n_used, int64_t n_tok, int64_t n_as);
+
 /* float64 reference of the same op on dequantized weights and UNquantized activations
  * (for NMSE context only; not the parity target) */
 void orc_mul_mat_f64(int type, const void *W, int64_t M, int64_t K, size_t nb01,

@@ -70,6 +70,12 @@ class Oracle:
                                      C.c_void_p, C.c_int64, C.c_size_t, C.c_void_p]
         L.orc_nmse.restype = C.c_double
         L.orc_nmse.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        L.orc_glu.restype = None
+        L.orc_glu.argtypes = [C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+        L.orc_add_row.restype = None
+        L.orc_add_row.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]
+        L.orc_add_id.restype = None
+        L.orc_add_id.argtypes = [C.c_void_p] * 4 + [C.c_int64] * 4
 
     # -- quantizers: x float32 [rows, k] -> uint8 [rows, row_bytes]
     def quantize(self, name: str, x: np.ndarray) -> np.ndarray:
@@ -127,6 +133,55 @@ class Oracle:
         self.lib.orc_mul_mat_id(t, _ptr(W), M, K, n_as, rb, rb * M, _ptr(B), ne11, n_tok, 4 * K, 4 * K * ne11,
                                 _ptr(ids), n_used, 4 * n_used, _ptr(out))
         return out
+
+    # -- K7: the element-wise nodes around the MUL_MATs
+    def glu(self, op: int, gate: np.ndarray, up: np.ndarray, alpha: float = 1.702, limit: float = 7.0) -> np.ndarray:
+        gate = np.ascontiguousarray(gate, dtype=np.float32)
+        up = np.ascontiguousarray(up, dtype=np.float32)
+        assert gate.shape == up.shape
+        out = np.zeros_like(gate)
+        self.lib.orc_glu(op, alpha, limit, _ptr(gate), _ptr(up), _ptr(out), gate.size)
+        return out
+
+    def add_row(self, a: np.ndarray, bias: np.ndarray) -> np.ndarray:
+        """a float32 [..., M] + bias [M]"""
+        a = np.ascontiguousarray(a, dtype=np.float32)
+        bias = np.ascontiguousarray(bias, dtype=np.float32)
+        out = np.zeros_like(a)
+        self.lib.orc_add_row(_ptr(a), _ptr(bias), _ptr(out), a.shape[-1], a.size // a.shape[-1])
+        return out
+
+    def add_id(self, a: np.ndarray, bias: np.ndarray, ids: np.ndarray) -> np.ndarray:
+        """a float32 [n_tok, n_used, M]; bias [n_as, M]; ids int32 [n_tok, n_used]"""
+        a = np.ascontiguousarray(a, dtype=np.float32)
+        bias = np.ascontiguousarray(bias, dtype=np.float32)
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        out = np.zeros_like(a)
+        self.lib.orc_add_id(_ptr(a), _ptr(bias), _ptr(ids), _ptr(out), a.shape[2], a.shape[1], a.shape[0], bias.shape[0])
+        return out
+
+    def mul_mat_glu(self, t: int, W_up, W_gate, X, up_bias=None, gate_bias=None, glu_op: int = -1, alpha=1.702, limit=7.0) -> np.ndarray:
+        """the fused patterns of test_mul_mat_vec_fusion as a composition of the node oracles: X [N, K] -> [N, M]"""
+        up = self.mul_mat(t, W_up, X)
+        if up_bias is not None:
+            up = self.add_row(up, up_bias)
+        if glu_op < 0:
+            return up
+        gate = self.mul_mat(t, W_gate, X)
+        if gate_bias is not None:
+            gate = self.add_row(gate, gate_bias)
+        return self.glu(glu_op, gate, up, alpha, limit)
+
+    def mul_mat_id_glu(self, t: int, W_up, W_gate, B, ids, up_bias=None, gate_bias=None, glu_op: int = -1, alpha=1.702, limit=7.0) -> np.ndarray:
+        up = self.mul_mat_id(t, W_up, B, ids)
+        if up_bias is not None:
+            up = self.add_id(up, up_bias, ids)
+        if glu_op < 0:
+            return up
+        gate = self.mul_mat_id(t, W_gate, B, ids)
+        if gate_bias is not None:
+            gate = self.add_id(gate, gate_bias, ids)
+        return self.glu(glu_op, gate, up, alpha, limit)
 
     def nmse(self, ref: np.ndarray, got: np.ndarray) -> float:
         a = np.ascontiguousarray(ref, dtype=np.float32).ravel()
@@ -210,6 +265,12 @@ class RefHarness:
         L.refh_mul_mat_id.restype = C.c_int
         L.refh_mul_mat_id.argtypes = [C.c_int] * 4 + [C.c_int64] * 6 + [C.c_void_p] * 4 + [C.c_double, C.POINTER(C.c_double)]
         L.refh_mul_mat_stack.restype = C.c_int
+        L.refh_proc_u64.restype = C.c_uint64
+        L.refh_proc_u64.argtypes = [C.c_int, C.c_char_p]
+        L.refh_mul_mat_glu.restype = C.c_int
+        L.refh_mul_mat_glu.argtypes = [C.c_int] * 4 + [C.c_int64] * 3 + [C.c_void_p] * 5 + [C.c_int, C.c_float, C.c_float, C.c_void_p]
+        L.refh_mul_mat_id_glu.restype = C.c_int
+        L.refh_mul_mat_id_glu.argtypes = [C.c_int] * 4 + [C.c_int64] * 6 + [C.c_void_p] * 6 + [C.c_int, C.c_float, C.c_float, C.c_void_p]
         L.refh_mul_mat_stack.argtypes = [C.c_int] * 5 + [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                                         C.c_double, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         self._loaded = {}
@@ -303,6 +364,47 @@ class RefHarness:
         if rc:
             raise RuntimeError(f"refh_mul_mat_id rc={rc}")
         return out, (us.value if seconds > 0 else None)
+
+    def proc_u64(self, reg: int, name: str):
+        """value of a `uint64_t (*)(void)` the registry exposes via get_proc_address; None if it has no such entry"""
+        v = int(self.lib.refh_proc_u64(reg, name.encode()))
+        return None if v == 2 ** 64 - 1 else v
+
+    def mul_mat_glu(self, reg: int, t: int, W_up, W_gate, X, up_bias=None, gate_bias=None, glu_op: int = -1, alpha=1.702, limit=7.0,
+                    n_threads=0, dev=0) -> np.ndarray:
+        """{MUL_MAT [, ADD], MUL_MAT [, ADD], GLU} (glu_op >= 0) or {MUL_MAT, ADD} as one graph on backend `reg`: X [N, K] -> [N, M]"""
+        X = np.ascontiguousarray(X, dtype=np.float32)
+        N, K = X.shape
+        W_up = np.ascontiguousarray(W_up, dtype=np.uint8)
+        M = W_up.size // row_size(t, K)
+        opt = lambda a, dt: None if a is None else np.ascontiguousarray(a, dtype=dt)
+        W_gate, up_bias, gate_bias = opt(W_gate, np.uint8), opt(up_bias, np.float32), opt(gate_bias, np.float32)
+        p = lambda a: None if a is None else _ptr(a)
+        out = np.zeros((N, M), dtype=np.float32)
+        rc = self.lib.refh_mul_mat_glu(reg, dev, n_threads, t, M, K, N, _ptr(W_up), p(W_gate), _ptr(X), p(up_bias), p(gate_bias), glu_op,
+                                       alpha, limit, _ptr(out))
+        if rc:
+            raise RuntimeError(f"refh_mul_mat_glu rc={rc} (2 = backend does not support a node)")
+        return out
+
+    def mul_mat_id_glu(self, reg: int, t: int, W_up, W_gate, B, ids, up_bias=None, gate_bias=None, glu_op: int = -1, alpha=1.702, limit=7.0,
+                       n_threads=0, dev=0) -> np.ndarray:
+        """the MUL_MAT_ID / ADD_ID forms: W uint8 [n_as, M, row_bytes]; B [n_tok, ne11, K]; ids [n_tok, n_used]; biases [n_as, M]"""
+        B = np.ascontiguousarray(B, dtype=np.float32)
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        W_up = np.ascontiguousarray(W_up, dtype=np.uint8)
+        n_tok, ne11, K = B.shape
+        n_as, M, _ = W_up.shape
+        n_used = ids.shape[1]
+        opt = lambda a, dt: None if a is None else np.ascontiguousarray(a, dtype=dt)
+        W_gate, up_bias, gate_bias = opt(W_gate, np.uint8), opt(up_bias, np.float32), opt(gate_bias, np.float32)
+        p = lambda a: None if a is None else _ptr(a)
+        out = np.zeros((n_tok, n_used, M), dtype=np.float32)
+        rc = self.lib.refh_mul_mat_id_glu(reg, dev, n_threads, t, M, K, n_as, n_used, ne11, n_tok, _ptr(W_up), p(W_gate), _ptr(B), _ptr(ids),
+                                          p(up_bias), p(gate_bias), glu_op, alpha, limit, _ptr(out))
+        if rc:
+            raise RuntimeError(f"refh_mul_mat_id_glu rc={rc} (2 = backend does not support a node)")
+        return out
 
     def mul_mat_stack(self, reg: int, t: int, shapes, N: int, W_all: np.ndarray, X_all: np.ndarray, n_threads=0,
                       dev=0, seconds=1.0, reps=1):

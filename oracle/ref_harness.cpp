@@ -259,4 +259,84 @@ int refh_mul_mat_stack(int reg, int dev, int n_threads, int type, int n_mats, co
     return 0;
 }
 
+// calls a `uint64_t (*)(void)` the registry exposes through get_proc_address (e.g. a backend's own counters); ~0 if absent
+uint64_t refh_proc_u64(int reg, const char * name) {
+    if (reg < 0 || reg >= (int) g_regs.size()) return ~(uint64_t) 0;
+    auto fn = (uint64_t (*)(void)) ggml_backend_reg_get_proc_address(g_regs[reg], name);
+    return fn ? fn() : ~(uint64_t) 0;
+}
+
+// K7 patterns (test_mul_mat_vec_fusion, tests/test-backend-ops.cpp:5120-5249) as ONE graph on any registered backend:
+//   glu_op >= 0: out = GLU(W_gate . X [+ gate_bias], W_up . X [+ up_bias])   (ggml_glu_split / ggml_swiglu_oai)
+//   glu_op <  0: out = W_up . X + up_bias
+// W_*: [K, M] of `type`; X: F32 [K, N]; biases: F32 [M] (added to every column; nullptr = none).
+// returns 0 on success, 2 if the backend does not support one of the nodes.
+int refh_mul_mat_glu(int reg, int dev, int n_threads, int type, int64_t M, int64_t K, int64_t N, const void * W_up, const void * W_gate,
+                     const float * X, const float * up_bias, const float * gate_bias, int glu_op, float alpha, float limit, float * dst) {
+    graph_run g;
+    g.be = open_backend(reg, dev, n_threads);
+    if (!g.be || !make_ctx(g)) return 1;
+    ggml_tensor * x  = ggml_new_tensor_2d(g.ctx, GGML_TYPE_F32, K, N);
+    ggml_tensor * wu = ggml_new_tensor_2d(g.ctx, (ggml_type) type, K, M);
+    ggml_tensor * wg = glu_op >= 0 ? ggml_new_tensor_2d(g.ctx, (ggml_type) type, K, M) : nullptr;
+    ggml_tensor * bu = up_bias ? ggml_new_tensor_2d(g.ctx, GGML_TYPE_F32, M, 1) : nullptr;
+    ggml_tensor * bg = gate_bias && wg ? ggml_new_tensor_2d(g.ctx, GGML_TYPE_F32, M, 1) : nullptr;
+    ggml_tensor * up = ggml_mul_mat(g.ctx, wu, x);
+    if (bu) up = ggml_add(g.ctx, up, bu);
+    ggml_tensor * out = up;
+    if (wg) {
+        ggml_tensor * gate = ggml_mul_mat(g.ctx, wg, x);
+        if (bg) gate = ggml_add(g.ctx, gate, bg);
+        out = glu_op == GGML_GLU_OP_SWIGLU_OAI ? ggml_swiglu_oai(g.ctx, gate, up, alpha, limit) : ggml_glu_split(g.ctx, gate, up, (ggml_glu_op) glu_op);
+    }
+    if (!finish(g, out)) return 3;
+    for (int i = 0; i < ggml_graph_n_nodes(g.graph); i++)
+        if (!ggml_backend_supports_op(g.be, ggml_graph_node(g.graph, i))) return 2;
+    ggml_backend_tensor_set(x, X, 0, ggml_nbytes(x));
+    ggml_backend_tensor_set(wu, W_up, 0, ggml_nbytes(wu));
+    if (wg) ggml_backend_tensor_set(wg, W_gate, 0, ggml_nbytes(wg));
+    if (bu) ggml_backend_tensor_set(bu, up_bias, 0, ggml_nbytes(bu));
+    if (bg) ggml_backend_tensor_set(bg, gate_bias, 0, ggml_nbytes(bg));
+    if (ggml_backend_graph_compute(g.be, g.graph) != GGML_STATUS_SUCCESS) return 4;
+    ggml_backend_synchronize(g.be);
+    ggml_backend_tensor_get(out, dst, 0, ggml_nbytes(out));
+    return 0;
+}
+
+// the MUL_MAT_ID form: experts W_*: [K, M, n_as]; B: F32 [K, ne11, n_tok]; ids: I32 [n_used, n_tok]; biases: F32 [M, n_as] (ADD_ID)
+int refh_mul_mat_id_glu(int reg, int dev, int n_threads, int type, int64_t M, int64_t K, int64_t n_as, int64_t n_used, int64_t ne11, int64_t n_tok,
+                        const void * W_up, const void * W_gate, const float * B, const int32_t * ids, const float * up_bias, const float * gate_bias,
+                        int glu_op, float alpha, float limit, float * dst) {
+    graph_run g;
+    g.be = open_backend(reg, dev, n_threads);
+    if (!g.be || !make_ctx(g)) return 1;
+    ggml_tensor * b  = ggml_new_tensor_3d(g.ctx, GGML_TYPE_F32, K, ne11, n_tok);
+    ggml_tensor * id = ggml_new_tensor_2d(g.ctx, GGML_TYPE_I32, n_used, n_tok);
+    ggml_tensor * wu = ggml_new_tensor_3d(g.ctx, (ggml_type) type, K, M, n_as);
+    ggml_tensor * wg = glu_op >= 0 ? ggml_new_tensor_3d(g.ctx, (ggml_type) type, K, M, n_as) : nullptr;
+    ggml_tensor * bu = up_bias ? ggml_new_tensor_2d(g.ctx, GGML_TYPE_F32, M, n_as) : nullptr;
+    ggml_tensor * bg = gate_bias && wg ? ggml_new_tensor_2d(g.ctx, GGML_TYPE_F32, M, n_as) : nullptr;
+    ggml_tensor * up = ggml_mul_mat_id(g.ctx, wu, b, id);
+    if (bu) up = ggml_add_id(g.ctx, up, bu, id);
+    ggml_tensor * out = up;
+    if (wg) {
+        ggml_tensor * gate = ggml_mul_mat_id(g.ctx, wg, b, id);
+        if (bg) gate = ggml_add_id(g.ctx, gate, bg, id);
+        out = glu_op == GGML_GLU_OP_SWIGLU_OAI ? ggml_swiglu_oai(g.ctx, gate, up, alpha, limit) : ggml_glu_split(g.ctx, gate, up, (ggml_glu_op) glu_op);
+    }
+    if (!finish(g, out)) return 3;
+    for (int i = 0; i < ggml_graph_n_nodes(g.graph); i++)
+        if (!ggml_backend_supports_op(g.be, ggml_graph_node(g.graph, i))) return 2;
+    ggml_backend_tensor_set(b, B, 0, ggml_nbytes(b));
+    ggml_backend_tensor_set(id, ids, 0, ggml_nbytes(id));
+    ggml_backend_tensor_set(wu, W_up, 0, ggml_nbytes(wu));
+    if (wg) ggml_backend_tensor_set(wg, W_gate, 0, ggml_nbytes(wg));
+    if (bu) ggml_backend_tensor_set(bu, up_bias, 0, ggml_nbytes(bu));
+    if (bg) ggml_backend_tensor_set(bg, gate_bias, 0, ggml_nbytes(bg));
+    if (ggml_backend_graph_compute(g.be, g.graph) != GGML_STATUS_SUCCESS) return 4;
+    ggml_backend_synchronize(g.be);
+    ggml_backend_tensor_get(out, dst, 0, ggml_nbytes(out));
+    return 0;
+}
+
 } // extern "C"

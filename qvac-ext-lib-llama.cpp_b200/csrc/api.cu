@@ -504,13 +504,16 @@ static bool mv_fuse_quant(const b200_ctx * ctx, int U, int64_t ncols) { return c
 
 // run `n_ops` matrices (same type, K) against `ncols` activation columns: either F32 columns x (+ c*x_cs bytes), quantized
 // inside the kernel, or already-quantized unit-record columns (act_main / act_aux)
+// K7 epilogue of a one-column launch: bias rows per matrix; glu >= 0: ws[0] = gate, ws[1] = up, dsts[0] = the GLU's output
+struct mv_epilogue { int glu; float alpha, limit; const float * bias[MV_MAX_MATS]; };
+
 static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, const uint8_t * const * ws, const size_t * nb01s,
                                const int64_t * Ms, float * const * dsts, const int64_t * dst_cs, int ncols,
-                               const float * x, size_t x_cs, const uint8_t * act_main, const uint8_t * act_aux) {
+                               const float * x, size_t x_cs, const uint8_t * act_main, const uint8_t * act_aux, const mv_epilogue * ep = nullptr) {
     const int U = (int) (K / 256);
     for (int c0 = 0; c0 < ncols;) {
         int     nc = ncols - c0 < MV_MAX_COLS ? ncols - c0 : MV_MAX_COLS;
-        if (ctx->mma_min_cols > 0 && nc >= ctx->mma_min_cols && mv_mma_usable(type) && mv_mma_fits(type, K)) {  // 3..8 columns: tensor-core mat-vec (mvmma.cu)
+        if (!ep && ctx->mma_min_cols > 0 && nc >= ctx->mma_min_cols && mv_mma_usable(type) && mv_mma_fits(type, K)) {  // 3..8 columns: tensor-core mat-vec (mvmma.cu)
             float * ds[MV_MAX_MATS * 8];
             for (int i = 0; i < n_ops; i++) ds[i] = dsts[i] + (int64_t) c0 * dst_cs[i];
             if (x && ctx->split.n_ranks > 1 && ctx->split_deferred) {
@@ -543,6 +546,16 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
                 g += (int) ((Ms[o0 + i] + p.rpg - 1) / p.rpg);
             }
             for (int i = p.n_mats; i < MV_MAX_MATS; i++) p.mat[i].group0 = INT32_MAX;
+            if (ep) {
+                for (int i = 0; i < p.n_mats; i++) p.mat[i].bias = ep->bias[o0 + i];
+                if (ep->glu >= 0) {  // gate rows and up rows of a group run back to back on one warp (kernels.h MvEpi)
+                    p.mat[1].group0 = 0;
+                    g               = (int) ((Ms[0] + p.rpg - 1) / p.rpg);
+                    p.epi.glu       = ep->glu + 1;
+                    p.epi.alpha     = ep->alpha;
+                    p.epi.limit     = ep->limit;
+                }
+            }
             p.total_groups = g;
             if (g == 0) continue;
             p.n_cons   = cfg.nw;
@@ -761,6 +774,66 @@ b200_status b200_mul_mat_shared_src1(b200_ctx * ctx, int n_ops, const b200_mul_m
         }
     }
     return mul_mat_impl(ctx, n_ops, descs, src0s, src1, dsts);
+}
+
+// ------------------------------------------------------------------------------------------------ K7: fused epilogues
+
+int b200_mul_mat_fused_supported(const b200_ctx * ctx, const b200_mul_mat_desc * d) {
+    if (!ctx || !d || !b200_mul_mat_supported(d) || d->ne11 != 1) return 0;
+    if (ctx->split.n_ranks > 1 || ctx->force_path == B200_PATH_SIMPLE || ctx->force_path == B200_PATH_MMQ) return 0;
+    if (d->ne00 % 256 != 0 || d->nb01 % 16 || d->nb02 % 16 || d->nb03 % 16 || (d->type == B200_TYPE_Q6_K && d->ne00 % 2048 != 0)) return 0;
+    mv_cfg cfg;
+    return pick_mv_cfg(ctx, d->type, (int) (d->ne00 / 256), 1, &cfg) ? 1 : 0;
+}
+
+b200_status b200_mul_mat_fused(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * up, const void * gate, const float * src1,
+                               const b200_fusion * f, float * dst) {
+    if (!ctx || !d || !f) return fail(B200_ERR_ARG, "null argument");
+    const bool glu = f->glu_op != B200_GLU_NONE;
+    if (glu ? (f->glu_op < 0 || f->glu_op > B200_GLU_GEGLU_QUICK || !gate) : (gate != nullptr || f->gate_bias != nullptr))
+        return fail(B200_ERR_ARG, "fused MUL_MAT: glu_op / gate / bias arguments do not agree");
+    if (f->bias_nb2 % 4 || f->bias_nb3 % 4) return fail(B200_ERR_ARG, "fused MUL_MAT: bias strides");
+    if (!b200_mul_mat_fused_supported(ctx, d) || !fast_layout_ok(d->type, d->ne00, up, d->nb01, d->nb02, d->nb03) ||
+        (gate && (uintptr_t) gate % 16 != 0))
+        return fail(B200_ERR_UNSUPPORTED, "fused MUL_MAT: one column on the TMA-staged kernel only (run the nodes one by one)");
+    if (d->ne01 == 0) return B200_OK;
+    if (!up || !src1 || !dst) return fail(B200_ERR_ARG, "null argument");
+    CU(cudaSetDevice(ctx->device));
+    const int64_t K = d->ne00, r2 = d->ne12 / d->ne02, r3 = d->ne13 / d->ne03;
+    const int     U = (int) (K / 256);
+    const bool    fuse = mv_fuse_quant(ctx, U, 1);
+    for (int64_t i13 = 0; i13 < d->ne13; i13++)
+        for (int64_t i12 = 0; i12 < d->ne12; i12++) {
+            const float * x = (const float *) ((const char *) src1 + i12 * d->nb12 + i13 * d->nb13);
+            uint8_t * am = nullptr, * ax = nullptr;
+            if (!fuse) {  // long rows: one quantizer launch in front (as in mul_mat_impl)
+                const size_t aux_o = ((size_t) U * ACT_MAIN + 255) & ~(size_t) 255;
+                if (b200_status st = ensure(ctx, &ctx->scratch, &ctx->scratch_size, aux_o + (size_t) U * ACT_AUX)) return st;
+                am = (uint8_t *) ctx->scratch;
+                ax = am + aux_o;
+                int l = 0;
+                CU(quantize_units(act_kind_for(d->type), x, K, 1, d->nb11, am, ax, ctx->stream, &l, ctx->pdl));
+                ctx->launches += l;
+            }
+            const size_t    w_off = (size_t) (i12 / r2) * d->nb02 + (size_t) (i13 / r3) * d->nb03;
+            const size_t    b_off = (size_t) i12 * f->bias_nb2 + (size_t) i13 * f->bias_nb3;
+            const uint8_t * ws[2]; size_t nb01s[2] = { d->nb01, d->nb01 }; int64_t Ms[2] = { d->ne01, d->ne01 }, dcs[2] = { 0, 0 };
+            float *         ds[2];
+            mv_epilogue     ep = {};
+            ep.glu = glu ? f->glu_op : -1; ep.alpha = f->alpha; ep.limit = f->limit;
+            const float * ub = f->up_bias ? (const float *) ((const char *) f->up_bias + b_off) : nullptr;
+            const float * gb = f->gate_bias ? (const float *) ((const char *) f->gate_bias + b_off) : nullptr;
+            ds[0] = ds[1] = (float *) ((char *) dst + i12 * d->nb2 + i13 * d->nb3);
+            if (glu) {
+                ws[0] = (const uint8_t *) gate + w_off; ws[1] = (const uint8_t *) up + w_off;
+                ep.bias[0] = gb; ep.bias[1] = ub;
+            } else {
+                ws[0] = (const uint8_t *) up + w_off;
+                ep.bias[0] = ub;
+            }
+            if (b200_status st = mv_fast_run(ctx, d->type, K, glu ? 2 : 1, ws, nb01s, Ms, ds, dcs, 1, fuse ? x : nullptr, d->nb11, am, ax, &ep)) return st;
+        }
+    return B200_OK;
 }
 
 b200_status b200_mul_mat_host(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * src0, int w_on_device, const float * src1_host,

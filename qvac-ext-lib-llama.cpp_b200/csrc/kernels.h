@@ -209,6 +209,16 @@ struct MvMat {
     int64_t         dst_cs;   // floats between dst columns
     int             M;        // rows
     int             group0;   // first global row-group id of this matrix
+    const float *   bias;     // K7: added to the row's dot product before the GLU / store (one column only); nullptr = none
+    int64_t         bias_es;  // MUL_MAT_ID (ADD_ID): floats between the bias rows of two experts
+};
+
+// K7 epilogue of the one-column mat-vec (ggml_cuda_mm_fusion_args, ggml-cuda/common.cuh; mmvq.cu:181-328 in the reference):
+// glu != 0: mat[0] = gate and mat[1] = up matrix of the same shape, both with group0 = 0; a warp runs the gate rows of a group,
+// keeps the result in registers, runs the up rows and stores glu(gate + gate_bias, up + up_bias) to mat[0].dst.
+struct MvEpi {
+    int   glu;            // 0 = none, else 1 + enum ggml_glu_op (ggml.h:596-605)
+    float alpha, limit;   // SWIGLU_OAI
 };
 
 // Cross-kernel weight prefetch. A decode step is a dependent chain of small mat-vec kernels: every kernel boundary costs
@@ -251,6 +261,7 @@ struct MvParams {
     SplitParams     split;
     SplitGeom       geom;     // split.ll: who owns which rows of mat[i]
     MvNext          next;
+    MvEpi           epi;
     // debug timeline (b200_ctx_trace): 8 x u64 per CTA at trace + blockIdx.x*8: globaltimer ns of [0] CTA start, [1] first and
     // [2] last weight copy issued, [3] consumer warp 0 past griddepcontrol.wait, [4] activations quantized, [5] first stage
     // landed, [6] consumer warp 0 done, [7] SM id. nullptr = off.

@@ -94,7 +94,15 @@ int b200_mul_mat_id_supported(const b200_mul_mat_id_desc * d) {
     return 1;
 }
 
-b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, const void * as, const float * b, const int32_t * ids, float * dst) {
+static bool mmid_fast_layout(const b200_ctx * ctx, const b200_mul_mat_id_desc * d, const void * as) {
+    const int64_t K = d->ne00;
+    return ctx->force_path != B200_PATH_SIMPLE && K % 256 == 0 && (uintptr_t) as % 16 == 0 && d->nb01 % 16 == 0 && d->nb02 % 16 == 0 &&
+           (d->type != B200_TYPE_Q6_K || K % 2048 == 0);  // 210-byte units: bulk-copyable 8 at a time
+}
+
+// fz != nullptr: K7 - one token, the epilogue of b200_fusion on the TMA-staged kernel (gate_as != nullptr iff a GLU is fused)
+static b200_status mul_mat_id_impl(b200_ctx * ctx, const b200_mul_mat_id_desc * d, const void * as, const void * gate_as, const float * b,
+                                   const int32_t * ids, float * dst, const b200_fusion * fz) {
     if (!ctx || !d || !as || !b || !ids || !dst) return fail(B200_ERR_ARG, "null argument");
     if (!b200_mul_mat_id_supported(d)) return fail(B200_ERR_UNSUPPORTED, "MUL_MAT_ID geometry/type not supported");
     const int64_t K = d->ne00, M = d->ne01;
@@ -113,15 +121,15 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
     mi.ne11   = (int) d->ne11;
     mi.n_as   = (int) d->n_as;
 
-    const bool fast = ctx->force_path != B200_PATH_SIMPLE && K % 256 == 0 && (uintptr_t) as % 16 == 0 && d->nb01 % 16 == 0 && d->nb02 % 16 == 0 &&
-                      (d->type != B200_TYPE_Q6_K || K % 2048 == 0);  // 210-byte units: bulk-copyable 8 at a time
+    const bool fast = mmid_fast_layout(ctx, d, as) && (!gate_as || mmid_fast_layout(ctx, d, gate_as));
     const int64_t n_rows = d->ne11 * d->n_tok;
+    if (fz && (!fast || d->n_tok != 1 || ctx->split.n_ranks > 1)) return fail(B200_ERR_UNSUPPORTED, "fused MUL_MAT_ID: one token on the TMA-staged kernel only");
 
     if (fast) {
         const int  U    = (int) (K / 256);
         // enough pairs per expert: sort the pairs by expert and let every expert multiply its tokens 8 columns at a time on the
         // tensor-core mat-vec kernel (mvmma.cu) - an expert's weights are then read once per 8 tokens instead of once per token
-        const bool grouped = ctx->moe_group_min > 0 && n_pairs >= (int64_t) ctx->moe_group_min * d->n_as && n_pairs >= 8 && mv_mma_usable(d->type) &&
+        const bool grouped = !fz && ctx->moe_group_min > 0 && n_pairs >= (int64_t) ctx->moe_group_min * d->n_as && n_pairs >= 8 && mv_mma_usable(d->type) &&
                              d->nb12 == d->nb11 * (size_t) d->ne11;
         const bool fuse = !grouped && ctx->fuse_quant && U <= 64;  // every pair's CTAs quantize that pair's activation row themselves
         uint8_t * am = nullptr, * ax = nullptr;
@@ -169,6 +177,19 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
         p.mat[0].M      = (int) M;
         p.mat[0].group0 = 0;
         for (int i = 1; i < MV_MAX_MATS; i++) p.mat[i].group0 = INT32_MAX;
+        if (fz) {
+            p.mat[0].bias    = fz->up_bias;
+            p.mat[0].bias_es = (int64_t) (fz->bias_nb1 / 4);
+            if (gate_as) {  // mat[0] = gate, mat[1] = up: same rows, one after the other (kernels.h MvEpi)
+                p.mat[1]      = p.mat[0];
+                p.mat[0].w    = (const uint8_t *) gate_as;
+                p.mat[0].bias = fz->gate_bias;
+                p.n_mats      = 2;
+                p.epi.glu     = fz->glu_op + 1;
+                p.epi.alpha   = fz->alpha;
+                p.epi.limit   = fz->limit;
+            }
+        }
         p.total_groups = (int) ((M + p.rpg - 1) / p.rpg);
         p.pdl          = ctx->pdl;
         p.split        = ctx->split;
@@ -196,6 +217,7 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
             MvParams q = p;
             q.ids.ids    = ids + t0 * mi.ids_rs;
             q.mat[0].dst = dst + t0 * mi.dst_ts;
+            q.mat[1].dst = q.mat[0].dst;
             if (fuse) {
                 q.x = (const float *) ((const char *) b + t0 * d->nb12);
             } else {
@@ -236,4 +258,27 @@ b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, cons
     CU(mv_simple_launch(d->type, sp, ctx->stream));
     ctx->launches++;
     return B200_OK;
+}
+
+b200_status b200_mul_mat_id(b200_ctx * ctx, const b200_mul_mat_id_desc * d, const void * as, const float * b, const int32_t * ids, float * dst) {
+    return mul_mat_id_impl(ctx, d, as, nullptr, b, ids, dst, nullptr);
+}
+
+// ------------------------------------------------------------------------------------------------ K7: one token, fused epilogue
+
+int b200_mul_mat_id_fused_supported(const b200_ctx * ctx, const b200_mul_mat_id_desc * d) {
+    if (!ctx || !d || !b200_mul_mat_id_supported(d)) return 0;
+    if (d->n_tok != 1 || ctx->split.n_ranks > 1 || ctx->force_path == B200_PATH_SIMPLE) return 0;
+    if (d->ne00 % 256 != 0 || d->nb01 % 16 != 0 || d->nb02 % 16 != 0 || (d->type == B200_TYPE_Q6_K && d->ne00 % 2048 != 0)) return 0;
+    return mv_fast_smem(d->type, (int) (d->ne00 / 256), 1, 1, 2) <= 227 * 1024;
+}
+
+b200_status b200_mul_mat_id_fused(b200_ctx * ctx, const b200_mul_mat_id_desc * d, const void * up_as, const void * gate_as, const float * b,
+                                  const int32_t * ids, const b200_fusion * f, float * dst) {
+    if (!f) return fail(B200_ERR_ARG, "null argument");
+    const bool glu = f->glu_op != B200_GLU_NONE;
+    if (glu ? (f->glu_op < 0 || f->glu_op > B200_GLU_GEGLU_QUICK || !gate_as) : (gate_as != nullptr || f->gate_bias != nullptr))
+        return fail(B200_ERR_ARG, "fused MUL_MAT_ID: glu_op / gate / bias arguments do not agree");
+    if (f->bias_nb1 % 4) return fail(B200_ERR_ARG, "fused MUL_MAT_ID: bias stride");
+    return mul_mat_id_impl(ctx, d, up_as, gate_as, b, ids, dst, f);
 }

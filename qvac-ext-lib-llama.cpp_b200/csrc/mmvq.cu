@@ -20,6 +20,7 @@
 
 #include "quant_core.cuh"
 #include "kernels.h"
+#include "epilogue.cuh"
 
 #include <type_traits>
 
@@ -335,7 +336,9 @@ __device__ __forceinline__ int mv_find_mat(const MvParams & p, int group) {
 // WCLASS (CTA shapes): 0 = up to 8 consumer warps, two CTAs per SM for <= 4 columns; 1 = up to 16 consumer warps, the SM to
 // itself; 2 = up to 11 consumer warps and two CTAs per SM (<= 80 registers): consecutive kernels of a stream co-reside
 constexpr int mv_class_warps(int c) { return c == 1 ? MV_MAX_CONS + 1 : c == 2 ? 12 : 9; }
-template <int TYPE, int NC, int WCLASS>
+// EPI: the K7 epilogues (bias rows, GLU of a gate / up matrix pair; kernels.h MvEpi) - one column only, own instantiation so that
+// the plain mat-vec keeps its code
+template <int TYPE, int NC, int WCLASS, bool EPI = false>
 __global__ void __launch_bounds__(32 * mv_class_warps(WCLASS), (WCLASS == 2 || (WCLASS == 0 && NC <= 4)) ? 2 : 1)
 mv_fast_kernel(const __grid_constant__ MvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -358,7 +361,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
 
     // MUL_MAT_ID: this CTA row (blockIdx.y) is one (slot, token) pair with its own expert, activation row and dst column
     int64_t w_off = 0, dst_off = 0, x_off = 0;
-    int     act_col = 0;
+    int     act_col = 0, expert = 0;  // expert: row of the ADD_ID bias
     if (p.ids.ids) {
         const int pair = blockIdx.y;
         const int t = pair / p.ids.n_used, i = pair - t * p.ids.n_used;
@@ -368,6 +371,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
             return;
         }
         w_off   = (int64_t) e * p.ids.nb02;
+        expert  = e;
         dst_off = (int64_t) t * p.ids.dst_ts + (int64_t) i * p.ids.dst_is;
         act_col = t * p.ids.ne11 + i % p.ids.ne11;
         x_off   = (int64_t) t * p.ids.x_ts + (int64_t) (i % p.ids.ne11) * p.ids.x_is;
@@ -403,9 +407,14 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
 
     const uint64_t pol_stream = l2_policy_evict_first();
     // one stage of consumer warp w_: row group j_ of the warp's list, 32-unit slice slice_ -> ring stage stage_
+    // K7 GLU: a group is the gate rows followed by the same rows of the up matrix: SPG = 2 * slices stages per group
+    const bool GLU = EPI && p.epi.glu != 0;
+    const int  SPG = GLU ? 2 * p.slices : p.slices;
     auto issue = [&](int w_, int stage_, int j_, int slice_) {
         const int     group = g_begin + w_ + j_ * NWC;
-        const MvMat & mat   = p.mat[mv_find_mat(p, group)];
+        const int     half_ = GLU && slice_ >= p.slices ? 1 : 0;
+        if (half_) slice_ -= p.slices;
+        const MvMat & mat   = p.mat[GLU ? half_ : mv_find_mat(p, group)];
         const int     row0  = (group - mat.group0) * p.rpg;
         const int     nrow  = min(p.rpg, mat.M - row0);
         const int     u0    = slice_ * 32;
@@ -425,7 +434,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
         // ================================================================ producer warp: lane w feeds consumer warp w
         const int w = lane;
         int my_total = 0;
-        if (w < NWC && g_end - g_begin > w) my_total = ((g_end - g_begin - w + NWC - 1) / NWC) * p.slices;
+        if (w < NWC && g_end - g_begin > w) my_total = ((g_end - g_begin - w + NWC - 1) / NWC) * SPG;
         int issued = 0, stage = 0, j = 0, slice = 0;
         uint32_t phase = 1;  // parity of the "previous" phase of a fresh barrier: the first NS waits fall through
         while (__any_sync(0xffffffffu, issued < my_total)) {
@@ -437,7 +446,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
                 if (p.trace && w == 0 && issued == 0) p.trace[(size_t) blockIdx.x * 8 + 2] = global_ns();
                 issued++;
                 if (++stage == NS) { stage = 0; phase ^= 1; }
-                if (++slice == p.slices) { slice = 0; j++; }
+                if (++slice == SPG) { slice = 0; j++; }
             }
         }
         // every copy of this kernel is in flight: keep HBM busy across the kernel boundary with the head of the predicted
@@ -469,7 +478,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
     // ==================================================================== consumer warps
     const int w = warp;
     int my_total = 0;
-    if (g_end - g_begin > w) my_total = ((g_end - g_begin - w + NWC - 1) / NWC) * p.slices;
+    if (g_end - g_begin > w) my_total = ((g_end - g_begin - w + NWC - 1) / NWC) * SPG;
 
     griddep_wait();  // everything below reads src1 / writes dst, which earlier kernels of the stream may produce / still read
 
@@ -534,6 +543,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
     float acc[NC];
 #pragma unroll
     for (int c = 0; c < NC; c++) acc[c] = 0.0f;
+    float gate_v = 0.0f;  // K7: the finished gate row while the up row is being summed
 
     int stage = 0, j = 0, slice = 0;
     uint32_t phase = 0;
@@ -541,10 +551,12 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
         mbar_wait(smem_u32(full + w * NS + stage), phase);
         if (w == 0 && q == 0) MV_TRACE(5);
         const int group = g_begin + w + j * NWC;
-        const int m     = mv_find_mat(p, group);
+        const int half  = GLU && slice >= p.slices ? 1 : 0;
+        const int sl    = slice - half * p.slices;
+        const int m     = GLU ? half : mv_find_mat(p, group);
         const int row0  = (group - p.mat[m].group0) * p.rpg;
         const int M     = p.mat[m].M;
-        const int u0    = slice * 32;
+        const int u0    = sl * 32;
         const int nu    = min(32, U - u0);
         const int row   = row0 + rr;
         const int u     = u0 + sub;
@@ -557,7 +569,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(empty + w * NS + stage));  // the stage's bytes are in registers: hand it back
 
-        if (slice == p.slices - 1) {  // row finished: reduce the L lanes of each row and store
+        if (sl == p.slices - 1) {  // row finished: reduce the L lanes of each row and store
 #pragma unroll
             for (int c = 0; c < NC; c++) {
                 float v = acc[c];
@@ -567,15 +579,21 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
                     if (o < L) v += t;
                 }
                 if (sub == 0 && row < M && rr < p.rpg) {
-                    float * a = p.mat[m].dst + dst_off + (int64_t) c * p.mat[m].dst_cs + row;
-                    if (ll) ll_store(p.split, ep, a, v);
-                    else split_store(p.split, a, v);
+                    if (EPI && p.mat[m].bias) v += p.mat[m].bias[(int64_t) expert * p.mat[m].bias_es + row];  // ADD / ADD_ID of the bias row
+                    if (GLU) {
+                        if (half == 0) gate_v = v;
+                        else p.mat[0].dst[dst_off + row] = glu_apply(p.epi.glu - 1, gate_v, v, p.epi.alpha, p.epi.limit);
+                    } else {
+                        float * a = p.mat[m].dst + dst_off + (int64_t) c * p.mat[m].dst_cs + row;
+                        if (ll) ll_store(p.split, ep, a, v);
+                        else split_store(p.split, a, v);
+                    }
                 }
                 acc[c] = 0.0f;
             }
         }
         if (++stage == NS) { stage = 0; phase ^= 1; }
-        if (++slice == p.slices) { slice = 0; j++; }
+        if (++slice == SPG) { slice = 0; j++; }
     }
     if (w == 0) MV_TRACE(6);
     if (ll) {  // flagged-payload exchange: this CTA's rows are on their way to every rank; collect this CTA's share of the peers' rows
@@ -588,17 +606,17 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
     }
 }
 
-template <int TYPE, int NC, int WIDE>
+template <int TYPE, int NC, int WIDE, bool EPI = false>
 static cudaError_t mv_fast_launch_w(const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
     static bool attr_done[64] = {};  // one attribute call per instantiation and device
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(mv_fast_kernel<TYPE, NC, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(mv_fast_kernel<TYPE, NC, WIDE, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
         // always the largest shared-memory carve-out: a CTA of the NEXT kernel can only become co-resident if the SM does not
         // have to be reconfigured between the two launches
-        e = cudaFuncSetAttribute(mv_fast_kernel<TYPE, NC, WIDE>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        e = cudaFuncSetAttribute(mv_fast_kernel<TYPE, NC, WIDE, EPI>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
@@ -612,11 +630,20 @@ static cudaError_t mv_fast_launch_w(const MvParams & p, int n_ctas, int n_pairs,
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs    = attr;
     cfg.numAttrs = p.pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, mv_fast_kernel<TYPE, NC, WIDE>, p);
+    return cudaLaunchKernelEx(&cfg, mv_fast_kernel<TYPE, NC, WIDE, EPI>, p);
 }
 
 template <int TYPE, int NC>
 static cudaError_t mv_fast_launch_t(const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
+    bool epi = p.epi.glu != 0;
+    for (int i = 0; i < p.n_mats; i++) epi = epi || p.mat[i].bias != nullptr;
+    if (epi) {  // K7: one column; the wide CTA shape (or the 8-warp one for rows that leave less shared memory)
+        if constexpr (NC == 1) {
+            if (p.n_cons > 8) return mv_fast_launch_w<TYPE, 1, 1, true>(p, n_ctas, n_pairs, smem, st);
+            return mv_fast_launch_w<TYPE, 1, 0, true>(p, n_ctas, n_pairs, smem, st);
+        }
+        return cudaErrorInvalidValue;
+    }
     if (p.n_cons > 8) {
         if constexpr (NC <= MV_WIDE_MAX_COLS) {
             if (p.n_cons <= 11) return mv_fast_launch_w<TYPE, NC, 2>(p, n_ctas, n_pairs, smem, st);

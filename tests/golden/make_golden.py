@@ -89,5 +89,42 @@ def main_q6k():
     print("q6_K golden fixtures written to", OUT)
 
 
+def main_fusion():
+    """K7 fixtures: the fused patterns of test_mul_mat_vec_fusion (tests/test-backend-ops.cpp:5120-5249) run as whole graphs on the
+    reference's ggml-cpu (x64 generic build). Own seed: the earlier files stay byte-identical."""
+    rq, h = RefQuant(), RefHarness.get()
+    cpu = h.cpu("x64")
+    rng = np.random.default_rng(20261106)
+    cases = {}
+    M, K = 96, 512
+    for t in (Q4_0, Q8_0, Q4_K, Q6_K):
+        Wu = rq.quantize_weights(t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+        Wg = rq.quantize_weights(t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+        X = rng.uniform(-1, 1, (1, K)).astype(np.float32)
+        bu = rng.uniform(-1, 1, M).astype(np.float32)
+        bg = rng.uniform(-1, 1, M).astype(np.float32)
+        tn = TYPE_NAMES[t]
+        cases[f"{tn}_Wu"], cases[f"{tn}_Wg"], cases[f"{tn}_X"], cases[f"{tn}_bu"], cases[f"{tn}_bg"] = Wu, Wg, X, bu, bg
+        for op in range(6):
+            cases[f"{tn}_glu{op}"] = h.mul_mat_glu(cpu, t, Wu, Wg, X, glu_op=op, n_threads=1)
+            cases[f"{tn}_glu{op}_bias"] = h.mul_mat_glu(cpu, t, Wu, Wg, X, bu, bg, glu_op=op, n_threads=1)
+        cases[f"{tn}_bias_only"] = h.mul_mat_glu(cpu, t, Wu, None, X, bu, None, glu_op=-1, n_threads=1)
+    # MUL_MAT_ID / ADD_ID: one token, 4 of 6 experts
+    t, n_as, n_used = Q4_K, 6, 4
+    Wu = rq.quantize_weights(t, rng.uniform(-1, 1, (n_as * M, K)).astype(np.float32)).reshape(n_as, M, -1)
+    Wg = rq.quantize_weights(t, rng.uniform(-1, 1, (n_as * M, K)).astype(np.float32)).reshape(n_as, M, -1)
+    B = rng.uniform(-1, 1, (1, 1, K)).astype(np.float32)
+    ids = rng.permutation(n_as)[:n_used].astype(np.int32).reshape(1, n_used)
+    bu = rng.uniform(-1, 1, (n_as, M)).astype(np.float32)
+    bg = rng.uniform(-1, 1, (n_as, M)).astype(np.float32)
+    cases.update(id_Wu=Wu, id_Wg=Wg, id_B=B, id_ids=ids, id_bu=bu, id_bg=bg)
+    for op in (1, 2, 3):
+        cases[f"id_glu{op}"] = h.mul_mat_id_glu(cpu, t, Wu, Wg, B, ids, glu_op=op, n_threads=1)
+        cases[f"id_glu{op}_bias"] = h.mul_mat_id_glu(cpu, t, Wu, Wg, B, ids, bu, bg, glu_op=op, n_threads=1)
+    cases["id_bias_only"] = h.mul_mat_id_glu(cpu, t, Wu, None, B, ids, bu, None, glu_op=-1, n_threads=1)
+    np.savez_compressed(OUT / "fusion_k7.npz", **cases)
+    print("K7 golden fixture written to", OUT)
+
+
 if __name__ == "__main__":
-    main_q6k() if "--q6k" in sys.argv else main()
+    main_fusion() if "--fusion" in sys.argv else main_q6k() if "--q6k" in sys.argv else main()
