@@ -33,6 +33,8 @@ EXPORTS = [
     "b200_event_elapsed_ms", "b200_quantize_q8_0", "b200_quantize_q8_1", "b200_quantize_q8_K", "b200_quantize_units",
     "b200_mul_mat_supported", "b200_mul_mat", "b200_mul_mat_shared_src1", "b200_mul_mat_host", "b200_mul_mat_id_supported",
     "b200_mul_mat_id", "b200_mm_ids_sort", "b200_ctx_set_row_split", "b200_ctx_set_row_split_ll", "b200_ctx_set_row_split_deferred", "b200_ctx_row_split_wait", "b200_ctx_set_weight_cache", "b200_ctx_set_mmq_f16", "b200_ctx_set_prefetch", "b200_ctx_trace", "b200_ctx_trace_read", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
+    "b200_mul_mat_fused_supported", "b200_mul_mat_fused", "b200_mul_mat_id_fused_supported", "b200_mul_mat_id_fused",
+    "b200_glu", "b200_add", "b200_add_id",
 ]
 
 
@@ -73,6 +75,16 @@ class MulMatIdDesc(C.Structure):
     def contiguous(cls, t, M, K, n_as, n_used, ne11, n_tok):
         rb = row_size(t, K)
         return cls(t, K, M, n_as, rb, rb * M, ne11, n_tok, 4 * K, 4 * K * ne11, n_used, 4 * n_used, 4 * M, 4 * M * n_used)
+
+
+GLU_NONE, GLU_REGLU, GLU_GEGLU, GLU_SWIGLU, GLU_SWIGLU_OAI, GLU_GEGLU_ERF, GLU_GEGLU_QUICK = -1, 0, 1, 2, 3, 4, 5
+
+
+class Fusion(C.Structure):
+    """b200_fusion (include/ggml_b200.h): the K7 epilogue of a one-column MUL_MAT / one-token MUL_MAT_ID"""
+    _fields_ = [("glu_op", C.c_int32), ("alpha", C.c_float), ("limit", C.c_float),
+                ("up_bias", C.c_void_p), ("gate_bias", C.c_void_p),
+                ("bias_nb1", C.c_size_t), ("bias_nb2", C.c_size_t), ("bias_nb3", C.c_size_t)]
 
 
 class RowSplit(C.Structure):
@@ -146,6 +158,13 @@ def lib() -> C.CDLL:
         L.b200_mul_mat_id_supported.argtypes = [C.POINTER(MulMatIdDesc)]
         L.b200_mul_mat_id.argtypes = [vp, C.POINTER(MulMatIdDesc), vp, vp, vp, vp]
         L.b200_mm_ids_sort.argtypes = [vp, vp, i64, i64, sz, i64, vp, vp]
+        L.b200_mul_mat_fused_supported.argtypes = [vp, C.POINTER(MulMatDesc)]
+        L.b200_mul_mat_fused.argtypes = [vp, C.POINTER(MulMatDesc), vp, vp, vp, C.POINTER(Fusion), vp]
+        L.b200_mul_mat_id_fused_supported.argtypes = [vp, C.POINTER(MulMatIdDesc)]
+        L.b200_mul_mat_id_fused.argtypes = [vp, C.POINTER(MulMatIdDesc), vp, vp, vp, vp, C.POINTER(Fusion), vp]
+        L.b200_glu.argtypes = [vp, ci, C.c_float, C.c_float, vp, sz, vp, sz, vp, sz, i64, i64]
+        L.b200_add.argtypes = [vp, C.POINTER(i64), vp, C.POINTER(sz), vp, C.POINTER(i64), C.POINTER(sz), vp, C.POINTER(sz)]
+        L.b200_add_id.argtypes = [vp, vp, sz, sz, vp, sz, i64, vp, sz, vp, sz, sz, i64, i64, i64]
         for n in ("b200_memcpy_h2d_async", "b200_memcpy_d2h_async", "b200_memcpy_d2d_async"):
             getattr(L, n).argtypes = [vp, vp, vp, sz]
         L.b200_ctx_set_row_split.argtypes = [vp, C.POINTER(RowSplit)]
@@ -362,6 +381,62 @@ class Context:
         if out is None:
             out = torch.empty((n_tok, n_used, M), dtype=torch.float32, device=B.device)
         check(lib().b200_mul_mat_id(self.h, C.byref(desc), W.data_ptr(), B.data_ptr(), ids.data_ptr(), out.data_ptr()), "b200_mul_mat_id")
+        return out
+
+    # ---- K7: fused epilogues and the stand-alone element-wise nodes
+    def mul_mat_fused(self, t: int, W_up, W_gate, X, up_bias=None, gate_bias=None, glu_op: int = GLU_NONE, alpha=1.702, limit=7.0, out=None):
+        """one column: X float32 [1, K]; W_* uint8 [M, row_bytes]; biases float32 [M] -> float32 [1, M] in ONE launch"""
+        torch = self.torch
+        K = X.shape[-1]
+        M = W_up.numel() // row_size(t, K)
+        desc = MulMatDesc.contiguous(t, M, K, 1)
+        f = Fusion(glu_op, alpha, limit, None if up_bias is None else up_bias.data_ptr(), None if gate_bias is None else gate_bias.data_ptr(),
+                   0, 4 * M, 4 * M)
+        if out is None:
+            out = torch.empty((1, M), dtype=torch.float32, device=X.device)
+        check(lib().b200_mul_mat_fused(self.h, C.byref(desc), W_up.data_ptr(), None if W_gate is None else W_gate.data_ptr(), X.data_ptr(),
+                                       C.byref(f), out.data_ptr()), "b200_mul_mat_fused")
+        return out
+
+    def mul_mat_id_fused(self, t: int, W_up, W_gate, B, ids, up_bias=None, gate_bias=None, glu_op: int = GLU_NONE, alpha=1.702, limit=7.0, out=None):
+        """one token: W_* uint8 [n_as, M, row_bytes]; B float32 [1, ne11, K]; ids int32 [1, n_used]; biases float32 [n_as, M]"""
+        torch = self.torch
+        n_tok, ne11, K = B.shape
+        n_as, M = W_up.shape[0], W_up.shape[1]
+        n_used = ids.shape[1]
+        desc = MulMatIdDesc.contiguous(t, M, K, n_as, n_used, ne11, n_tok)
+        f = Fusion(glu_op, alpha, limit, None if up_bias is None else up_bias.data_ptr(), None if gate_bias is None else gate_bias.data_ptr(),
+                   4 * M, 0, 0)
+        if out is None:
+            out = torch.empty((n_tok, n_used, M), dtype=torch.float32, device=B.device)
+        check(lib().b200_mul_mat_id_fused(self.h, C.byref(desc), W_up.data_ptr(), None if W_gate is None else W_gate.data_ptr(), B.data_ptr(),
+                                          ids.data_ptr(), C.byref(f), out.data_ptr()), "b200_mul_mat_id_fused")
+        return out
+
+    def glu(self, op: int, gate, up, alpha=1.702, limit=7.0):
+        """GGML_OP_GLU, split form: gate / up float32 [rows, nc] (row strides honoured) -> [rows, nc]"""
+        out = self.torch.empty((gate.shape[0], gate.shape[1]), dtype=self.torch.float32, device=gate.device)
+        check(lib().b200_glu(self.h, op, alpha, limit, gate.data_ptr(), gate.stride(0) * 4, up.data_ptr(), up.stride(0) * 4, out.data_ptr(),
+                             out.stride(0) * 4, gate.shape[1], gate.shape[0]), "b200_glu")
+        return out
+
+    def add(self, a, b):
+        """GGML_OP_ADD with ggml broadcasting: a, b float32 tensors of up to 4 dims in torch order [ne3, ne2, ne1, ne0]"""
+        a4 = a.reshape((1,) * (4 - a.dim()) + tuple(a.shape))
+        b4 = b.reshape((1,) * (4 - b.dim()) + tuple(b.shape))
+        out = self.torch.empty_like(a4)
+        i64x4, szx4 = C.c_int64 * 4, C.c_size_t * 4
+        ne = lambda x: i64x4(*reversed(x.shape))
+        nb = lambda x: szx4(*[s * 4 for s in reversed(x.stride())])
+        check(lib().b200_add(self.h, ne(a4), a4.data_ptr(), nb(a4), b4.data_ptr(), ne(b4), nb(b4), out.data_ptr(), nb(out)), "b200_add")
+        return out.reshape(a.shape)
+
+    def add_id(self, a, bias, ids):
+        """GGML_OP_ADD_ID: a float32 [n_tok, n_used, M]; bias [n_as, M]; ids int32 [n_tok, n_used]"""
+        out = self.torch.empty_like(a)
+        n_tok, n_used, M = a.shape
+        check(lib().b200_add_id(self.h, a.data_ptr(), a.stride(1) * 4, a.stride(0) * 4, bias.data_ptr(), bias.stride(0) * 4, bias.shape[0],
+                                ids.data_ptr(), ids.stride(0) * 4, out.data_ptr(), out.stride(1) * 4, out.stride(0) * 4, M, n_used, n_tok), "b200_add_id")
         return out
 
     def mm_ids_sort(self, ids, n_as: int):
