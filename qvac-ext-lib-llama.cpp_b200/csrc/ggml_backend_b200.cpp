@@ -21,6 +21,7 @@
 #include <cstdio>
 #include <algorithm>
 #include <array>
+#include <atomic>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -58,7 +59,8 @@ struct be_ctx {
     int        device;
     b200_ctx * ctx;
     std::string name;
-    bool       fuse;
+    bool       fuse;                                // shared-src1 peephole (q/k/v, gate/up in one launch)
+    bool       fuse_epilogue = true;               // K7 peephole: GLU / bias epilogues of the one-column mat-vec
     void *     split_event = nullptr;              // "src1 is ready" on the main stream
     split_peer peers[B200_MAX_DEVICES];
 };
@@ -450,11 +452,152 @@ ggml_status split_mul_mat(be_ctx * c, ggml_tensor * node, const b200_mul_mat_des
     return GGML_STATUS_SUCCESS;
 }
 
+// ------------------------------------------------------------------------------------------------ K7: GLU / ADD / ADD_ID nodes
+
+std::atomic<uint64_t> g_fused_epilogues{ 0 };  // fused K7 launches of this process (proc address "ggml_backend_b200_fused_epilogues": tests)
+uint64_t fused_epilogues() { return g_fused_epilogues.load(std::memory_order_relaxed); }
+
+bool f32_rows(const ggml_tensor * t) { return t && t->type == GGML_TYPE_F32 && t->nb[0] == sizeof(float); }
+
+// GGML_OP_GLU as ggml-cpu takes it (ops.cpp:2934-3290): F32, rows contiguous_1, split (src1) or single-tensor halves
+bool glu_ok(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0], * b = op->src[1];
+    const int g = ggml_get_op_params_i32(op, 0);
+    if (g < 0 || g > B200_GLU_GEGLU_QUICK) return false;
+    if (!f32_rows(a) || !f32_rows(op) || !ggml_is_contiguous_1(a) || !ggml_is_contiguous_1(op)) return false;
+    if (b && (!f32_rows(b) || !ggml_is_contiguous_1(b) || !ggml_are_same_shape(a, b))) return false;
+    return op->ne[0] == (b ? a->ne[0] : a->ne[0] / 2) && ggml_nrows(op) == ggml_nrows(a);
+}
+bool add_ok(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0], * b = op->src[1];
+    return f32_rows(a) && f32_rows(b) && f32_rows(op) && ggml_are_same_shape(a, op) && ggml_can_repeat(b, a);
+}
+bool add_id_ok(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0], * b = op->src[1], * ids = op->src[2];
+    if (!f32_rows(a) || !f32_rows(b) || !f32_rows(op) || !ids || ids->type != GGML_TYPE_I32 || ids->nb[0] != sizeof(int32_t)) return false;
+    if (!ggml_are_same_shape(a, op) || a->ne[3] != 1 || b->ne[0] != a->ne[0] || b->ne[2] != 1 || b->ne[3] != 1) return false;
+    return ids->ne[0] == a->ne[1] && ids->ne[1] == a->ne[2] && ids->ne[2] == 1 && ids->ne[3] == 1;
+}
+bool add_like_ok(const ggml_tensor * t) { return t->op == GGML_OP_ADD ? add_ok(t) : add_id_ok(t); }
+
+void run_glu(be_ctx * c, ggml_tensor * node) {
+    const ggml_tensor * a = node->src[0], * b = node->src[1];
+    const int64_t nc      = node->ne[0];
+    const bool    swapped = ggml_get_op_params_i32(node, 1) != 0;
+    const float * gate = (const float *) a->data, * up = b ? (const float *) b->data : (const float *) a->data;
+    if (!b) (swapped ? gate : up) += nc;  // single tensor: [gate | up] halves of every row, or [up | gate] when swapped
+    CHECK(b200_glu(c->ctx, ggml_get_op_params_i32(node, 0), ggml_get_op_params_f32(node, 2), ggml_get_op_params_f32(node, 3), gate, a->nb[1], up,
+                   b ? b->nb[1] : a->nb[1], (float *) node->data, node->nb[1], nc, ggml_nrows(node)));
+}
+void run_add(be_ctx * c, ggml_tensor * node) {
+    const ggml_tensor * a = node->src[0], * b = node->src[1];
+    CHECK(b200_add(c->ctx, node->ne, (const float *) a->data, a->nb, (const float *) b->data, b->ne, b->nb, (float *) node->data, node->nb));
+}
+void run_add_id(be_ctx * c, ggml_tensor * node) {
+    const ggml_tensor * a = node->src[0], * b = node->src[1], * ids = node->src[2];
+    CHECK(b200_add_id(c->ctx, (const float *) a->data, a->nb[1], a->nb[2], (const float *) b->data, b->nb[1], b->ne[1], (const int32_t *) ids->data,
+                      ids->nb[1], (float *) node->data, node->nb[1], node->nb[2], a->ne[0], a->ne[1], a->ne[2]));
+}
+
+// the bias operand of the ADD / ADD_ID that follows MUL_MAT(_ID) `mm` (either operand of an ADD; src1 of an ADD_ID), else nullptr
+const ggml_tensor * bias_of(const ggml_tensor * add, const ggml_tensor * mm) {
+    if (add->op == GGML_OP_ADD) return add->src[0] == mm ? add->src[1] : (add->src[1] == mm ? add->src[0] : nullptr);
+    return add->src[0] == mm && add->src[2] == mm->src[2] ? add->src[1] : nullptr;
+}
+
+// K7 peephole (the reference's: ggml_cuda_can_fuse + ggml_cuda_should_fuse_mul_mat, ggml-cuda.cu:2020-2104, 3087-3115, 3404-3600):
+// node i is a one-column MUL_MAT / one-token MUL_MAT_ID. Recognises {mm, add, mm, add, GLU}, {mm, mm, GLU} and {mm, add} whose
+// intermediate results have no other consumer and runs them as ONE launch. Returns the number of nodes consumed (0: no fusion).
+int try_fuse_epilogue(be_ctx * c, ggml_cgraph * cgraph, int i) {
+    ggml_tensor * n0 = cgraph->nodes[i];
+    const ggml_op mm = n0->op, bias_op = mm == GGML_OP_MUL_MAT ? GGML_OP_ADD : GGML_OP_ADD_ID;
+    if (mm == GGML_OP_MUL_MAT ? n0->ne[1] != 1 : n0->ne[2] != 1) return 0;
+    ggml_tensor * gate = nullptr, * up = nullptr, * glu = nullptr, * last = nullptr;
+    const ggml_tensor * gate_add = nullptr, * up_add = nullptr;
+    int count = 0;
+    if (ggml_can_fuse_subgraph(cgraph, i, { mm, bias_op, mm, bias_op, GGML_OP_GLU }, { i + 4 })) {
+        glu = cgraph->nodes[i + 4];
+        ggml_tensor * a = cgraph->nodes[i], * b = cgraph->nodes[i + 2];
+        if (!glu->src[0] || !glu->src[1]) return 0;
+        if (bias_of(glu->src[0], a) && bias_of(glu->src[1], b)) { gate = a; up = b; }
+        else if (bias_of(glu->src[0], b) && bias_of(glu->src[1], a)) { gate = b; up = a; }
+        else return 0;
+        gate_add = glu->src[0]; up_add = glu->src[1]; last = glu; count = 5;
+    } else if (ggml_can_fuse_subgraph(cgraph, i, { mm, mm, GGML_OP_GLU }, { i + 2 })) {
+        glu = cgraph->nodes[i + 2];
+        ggml_tensor * a = cgraph->nodes[i], * b = cgraph->nodes[i + 1];
+        if (glu->src[0] == a && glu->src[1] == b) { gate = a; up = b; }
+        else if (glu->src[0] == b && glu->src[1] == a) { gate = b; up = a; }
+        else return 0;
+        last = glu; count = 3;
+    } else if (ggml_can_fuse(cgraph, i, { mm, bias_op })) {
+        up = n0; up_add = cgraph->nodes[i + 1];
+        if (!bias_of(up_add, up)) return 0;
+        last = cgraph->nodes[i + 1]; count = 2;
+    } else {
+        return 0;
+    }
+    const ggml_tensor * w = up->src[0], * x = up->src[1];
+    if (w->buffer && buft_is_split(w->buffer->buft)) return 0;
+    b200_fusion f = {};
+    f.glu_op = B200_GLU_NONE;
+    if (glu) {
+        const ggml_tensor * wg = gate->src[0];
+        if (!glu_ok(glu) || ggml_get_op_params_i32(glu, 1) != 0) return 0;  // swapped operands: not fused (as ggml-cuda.cu:2090-2092)
+        if (wg->type != w->type || !ggml_are_same_shape(wg, w) || !ggml_are_same_stride(wg, w) || gate->src[1] != x || gate->src[2] != up->src[2]) return 0;
+        if (wg->buffer && buft_is_split(wg->buffer->buft)) return 0;
+        f.glu_op = ggml_get_op_params_i32(glu, 0);
+        f.alpha  = ggml_get_op_params_f32(glu, 2);
+        f.limit  = ggml_get_op_params_f32(glu, 3);
+    }
+    const ggml_tensor * biases[2] = { up_add ? bias_of(up_add, up) : nullptr, gate_add ? bias_of(gate_add, gate) : nullptr };
+    for (const ggml_tensor * b : biases) {
+        if (!b) continue;
+        if (!f32_rows(b) || ranges_overlap(last, b)) return 0;
+        if (mm == GGML_OP_MUL_MAT ? !ggml_are_same_shape(b, up) : (b->ne[0] != up->ne[0] || b->ne[1] != w->ne[2] || b->ne[2] != 1 || b->ne[3] != 1)) return 0;  // no repeating adds
+    }
+    if ((up_add && !add_like_ok(up_add)) || (gate_add && !add_like_ok(gate_add))) return 0;
+    if (biases[0] && biases[1] && (biases[0]->nb[1] != biases[1]->nb[1] || biases[0]->nb[2] != biases[1]->nb[2] || biases[0]->nb[3] != biases[1]->nb[3])) return 0;
+    // the fused launch writes `last` while other CTAs still read src1 / ids: the allocator may have given it their memory
+    if (ranges_overlap(last, x) || (up->src[2] && ranges_overlap(last, up->src[2])) || !f32_rows(last)) return 0;
+    const ggml_tensor * bn = biases[0] ? biases[0] : biases[1];
+    f.up_bias   = biases[0] ? (const float *) biases[0]->data : nullptr;
+    f.gate_bias = biases[1] ? (const float *) biases[1]->data : nullptr;
+    b200_status st;
+    if (mm == GGML_OP_MUL_MAT) {
+        b200_mul_mat_desc d;
+        if (!fill_mul_mat(up, &d)) return 0;
+        d.nb1 = last->nb[1]; d.nb2 = last->nb[2]; d.nb3 = last->nb[3];
+        if (bn) { f.bias_nb2 = bn->nb[2]; f.bias_nb3 = bn->nb[3]; }
+        if (!b200_mul_mat_fused_supported(c->ctx, &d)) return 0;
+        st = b200_mul_mat_fused(c->ctx, &d, w->data, gate ? gate->src[0]->data : nullptr, (const float *) x->data, &f, (float *) last->data);
+    } else {
+        b200_mul_mat_id_desc d;
+        if (!fill_mul_mat_id(up, &d)) return 0;
+        d.nb1 = last->nb[1]; d.nb2 = last->nb[2];
+        if (bn) f.bias_nb1 = bn->nb[1];
+        if (!b200_mul_mat_id_fused_supported(c->ctx, &d)) return 0;
+        st = b200_mul_mat_id_fused(c->ctx, &d, w->data, gate ? gate->src[0]->data : nullptr, (const float *) x->data, (const int32_t *) up->src[2]->data, &f,
+                                   (float *) last->data);
+    }
+    if (st == B200_ERR_UNSUPPORTED) return 0;  // e.g. a weight pointer the TMA-staged kernel cannot take: run the nodes one by one
+    CHECK(st);
+    return count;
+}
+
 ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     be_ctx * c = (be_ctx *) backend->context;
     for (int i = 0; i < cgraph->n_nodes; i++) {
         ggml_tensor * node = cgraph->nodes[i];
         if (is_noop(node)) continue;  // as ggml-cuda.cu:3333-3335
+        if (c->fuse_epilogue && (node->op == GGML_OP_MUL_MAT || node->op == GGML_OP_MUL_MAT_ID)) {
+            const int fused = try_fuse_epilogue(c, cgraph, i);
+            if (fused > 0) {
+                g_fused_epilogues.fetch_add(1, std::memory_order_relaxed);
+                i += fused - 1;
+                continue;
+            }
+        }
         if (node->op == GGML_OP_MUL_MAT) {
             b200_mul_mat_desc descs[4];
             const void *      w[4];
@@ -496,6 +639,12 @@ ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
             }
             CHECK(b200_mul_mat_id(c->ctx, &d, node->src[0]->data, (const float *) node->src[1]->data, (const int32_t *) node->src[2]->data,
                                   (float *) node->data));
+        } else if (node->op == GGML_OP_GLU && glu_ok(node)) {
+            run_glu(c, node);
+        } else if (node->op == GGML_OP_ADD && add_ok(node)) {
+            run_add(c, node);
+        } else if (node->op == GGML_OP_ADD_ID && add_id_ok(node)) {
+            run_add_id(c, node);
         } else {
             GGML_LOG_ERROR("ggml-b200: op %s is not implemented by this backend (%s)\n", ggml_op_name(node->op), node->name);
             return GGML_STATUS_FAILED;
@@ -562,6 +711,8 @@ ggml_backend_t dev_init_backend(ggml_backend_dev_t dev, const char *) {
     b200_ctx_set_prefetch(ctx, 32);
     const char * nf = getenv("GGML_B200_DISABLE_FUSION");
     be_ctx * c = new be_ctx{ d->device, ctx, d->name, !(nf && atoi(nf)) };
+    const char * ne = getenv("GGML_B200_DISABLE_EPILOGUE_FUSION");
+    c->fuse_epilogue = c->fuse && !(ne && atoi(ne));
     return new ggml_backend{ be_guid(), be_iface, dev, c };
 }
 ggml_backend_buffer_type_t dev_buffer_type(ggml_backend_dev_t dev) { return &((dev_ctx *) dev->context)->buft; }
@@ -602,6 +753,14 @@ bool dev_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
             if (op->src[0] && op->src[0]->buffer && buft_is_split(op->src[0]->buffer->buft)) return false;  // as ggml-cuda.cu:4261-4268
             return fill_mul_mat_id(op, &d);
         }
+        // K7: the nodes the fused mat-vec epilogue absorbs; owned stand-alone as well so that the scheduler keeps
+        // {MUL_MAT, ADD, GLU} chains on this backend (the reference: ggml-cuda.cu:4331-4345 GLU, :4509-4516 ADD / ADD_ID)
+        case GGML_OP_GLU:
+            return glu_ok(op);
+        case GGML_OP_ADD:
+            return add_ok(op);
+        case GGML_OP_ADD_ID:
+            return add_id_ok(op);
         default:
             return false;
     }
@@ -694,6 +853,7 @@ ggml_backend_buffer_type_t split_buffer_type(int main_device, const float * tens
 void * reg_proc_address(ggml_backend_reg_t, const char * name) {
     if (!strcmp(name, "ggml_backend_get_features")) return (void *) reg_features;
     if (!strcmp(name, "ggml_backend_split_buffer_type")) return (void *) split_buffer_type;
+    if (!strcmp(name, "ggml_backend_b200_fused_epilogues")) return (void *) fused_epilogues;  // uint64_t (*)(void): K7 launches so far
     // "ggml_backend_set_n_threads", "ggml_backend_dev_get_extra_bufts": not provided
     return nullptr;
 }

@@ -44,6 +44,67 @@ def test_backend_mul_mat_id_matches_ggml_cpu(harness, refq, oracle, b200, t):
     assert oracle.nmse(ref, got) <= 1e-10
 
 
+FUSED = "ggml_backend_b200_fused_epilogues"
+
+
+@pytest.mark.parametrize("t,K", [(Q4_0, 512), (Q8_0, 1024), (Q4_K, 4096), (Q6_K, 2048)])
+def test_backend_fused_ffn_graph(harness, refq, oracle, b200, t, K):
+    """K7 through the reference's public API: {MUL_MAT [, ADD], MUL_MAT [, ADD], GLU} and {MUL_MAT, ADD} graphs. One column: the
+    backend's peephole runs the whole pattern as one launch (its counter moves); three columns: the nodes run one by one."""
+    rng = np.random.default_rng(K + t)
+    M = 200
+    Wu = refq.quantize_weights(t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    Wg = refq.quantize_weights(t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    bu, bg = rng.uniform(-1, 1, M).astype(np.float32), rng.uniform(-1, 1, M).astype(np.float32)
+    cpu = harness.cpu("x64")
+    for N in (1, 3):
+        X = (rng.uniform(-1, 1, (N, K)) * 0.2).astype(np.float32)
+        for op, bias in ((2, False), (2, True), (1, True), (3, False), (0, False), (4, True), (5, False), (-1, True)):
+            args = (t, Wu, Wg if op >= 0 else None, X, bu if bias else None, bg if bias and op >= 0 else None)
+            n0 = harness.proc_u64(b200, FUSED)
+            got = harness.mul_mat_glu(b200, *args, glu_op=op, alpha=1.5, limit=4.0)
+            n1 = harness.proc_u64(b200, FUSED)
+            ref = harness.mul_mat_glu(cpu, *args, glu_op=op, alpha=1.5, limit=4.0, n_threads=4)
+            assert oracle.nmse(ref, got) <= 1e-6, (op, bias, N)
+            assert n1 - n0 == (1 if N == 1 else 0), (op, bias, N)
+
+
+def test_backend_fused_moe_ffn_graph(harness, refq, oracle, b200):
+    """the MUL_MAT_ID / ADD_ID forms (gpt-oss style experts with biases and SWIGLU_OAI): one token fused, several tokens node by node"""
+    rng = np.random.default_rng(123)
+    t, n_as, M, K, n_used = Q4_K, 8, 96, 1024, 4
+    Wu = refq.quantize_weights(t, rng.uniform(-1, 1, (n_as * M, K)).astype(np.float32)).reshape(n_as, M, -1)
+    Wg = refq.quantize_weights(t, rng.uniform(-1, 1, (n_as * M, K)).astype(np.float32)).reshape(n_as, M, -1)
+    bu, bg = rng.uniform(-1, 1, (n_as, M)).astype(np.float32), rng.uniform(-1, 1, (n_as, M)).astype(np.float32)
+    cpu = harness.cpu("x64")
+    for n_tok in (1, 5):
+        B = (rng.uniform(-1, 1, (n_tok, 1, K)) * 0.2).astype(np.float32)
+        ids = np.stack([rng.permutation(n_as)[:n_used] for _ in range(n_tok)]).astype(np.int32)
+        for op, bias in ((3, True), (2, False), (-1, True)):
+            args = (t, Wu, Wg if op >= 0 else None, B, ids, bu if bias else None, bg if bias and op >= 0 else None)
+            n0 = harness.proc_u64(b200, FUSED)
+            got = harness.mul_mat_id_glu(b200, *args, glu_op=op)
+            n1 = harness.proc_u64(b200, FUSED)
+            ref = harness.mul_mat_id_glu(cpu, *args, glu_op=op, n_threads=4)
+            assert oracle.nmse(ref, got) <= 1e-6, (op, bias, n_tok)
+            assert n1 - n0 == (1 if n_tok == 1 else 0), (op, bias, n_tok)
+
+
+@pytest.mark.parametrize("op,min_tests", [("MUL_MAT_VEC_FUSION", 20), ("REGLU,GEGLU,SWIGLU,GEGLU_ERF,GEGLU_QUICK", 20), ("SWIGLU_OAI", 4), ("ADD", 20),
+                                          ("ADD_ID", 4)])
+def test_reference_conformance_harness_k7(pkg, op, min_tests):
+    """the reference's own cases for the K7 nodes (test_mul_mat_vec_fusion runs whole graphs: tests/test-backend-ops.cpp:5120-5249)"""
+    if not have_ref() or not (REF_DIR / "test-backend-ops").exists():
+        pytest.skip("oracle/_ref/test-backend-ops not built")
+    rc, out = run_tbo(pkg, "test", "-b", "B2000", "-o", op)
+    tail = "\n".join(out.splitlines()[-25:])
+    m = re.search(r"(\d+)/(\d+) tests passed", out)
+    assert m, tail
+    assert m.group(1) == m.group(2), tail
+    assert int(m.group(2)) >= min_tests, tail
+    assert rc == 0, tail
+
+
 def run_tbo(pkg, *args, timeout=900):
     env = dict(os.environ, GGML_BACKEND_PATH=str(pkg.BACKEND_PATH))
     p = subprocess.run([str(REF_DIR / "test-backend-ops"), *args], env=env, capture_output=True, text=True, timeout=timeout)
