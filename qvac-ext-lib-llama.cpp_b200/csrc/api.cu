@@ -605,6 +605,10 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
                     nx.row_bytes      = U * unit_bytes(type);
                     const int64_t gb  = (int64_t) p.rpg * nx.row_bytes;
                     nx.groups_per_cta = (int) (((int64_t) ctx->prefetch_kb * 1024 + gb - 1) / gb);
+                    if (p.epi.glu) {  // a group streams rows of both matrices: half as many groups for the same bytes
+                        nx.glu            = 1;
+                        nx.groups_per_cta = (nx.groups_per_cta + 1) / 2;
+                    }
                 }
                 ctx->last_key = key;
             }

@@ -238,6 +238,7 @@ struct MvNext {
     int             rpg;
     int             row_bytes;        // U * unit_bytes
     int             groups_per_cta;   // prefetch depth
+    int             glu;              // the predicted launch is a K7 gate / up pair: a group is rows of w[0] AND the same rows of w[1]
 };
 
 struct MvParams {

@@ -456,10 +456,12 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
             for (int b = blockIdx.x; b < nx.n_ctas; b += gridDim.x) {
                 const int nb = (int) ((int64_t) nx.total_groups * b / nx.n_ctas);
                 const int ne = min((int) ((int64_t) nx.total_groups * (b + 1) / nx.n_ctas), nb + nx.groups_per_cta);
-                for (int g = nb + lane; g < ne; g += 32) {
-                    int m = 0;
+                const int gs = nx.glu ? 2 : 1;  // a gate / up pair: lanes 2k and 2k + 1 take the two matrices of group k
+                for (int gl = gs * nb + lane; gl < gs * ne; gl += 32) {
+                    const int g = gl / gs;
+                    int m = nx.glu ? gl - 2 * g : 0;
 #pragma unroll
-                    for (int i = 1; i < MV_MAX_MATS; i++) if (i < nx.n_mats && g >= nx.group0[i]) m = i;
+                    for (int i = 1; i < MV_MAX_MATS; i++) if (!nx.glu && i < nx.n_mats && g >= nx.group0[i]) m = i;
                     const int row0 = (g - nx.group0[m]) * nx.rpg;
                     const int nrow = min(nx.rpg, nx.M[m] - row0);
                     const uint8_t * src = nx.w[m] + (int64_t) row0 * nx.nb01[m];

@@ -182,7 +182,8 @@ def test_standalone_glu_add_add_id(ctx, oracle):
     for op in range(6):
         got = ctx.glu(op, cu(gate), cu(up), alpha=1.702, limit=7.0).cpu().numpy()
         ref = oracle.glu(op, gate, up)
-        assert np.allclose(got, ref, rtol=2e-6, atol=1e-7), GLU_NAMES[op]
+        # device tanhf / erff / expf are within a few ulp of glibc's; 1 + tanh(..) cancels for large negative gates
+        assert oracle.nmse(ref, got) <= 1e-12 and np.allclose(got, ref, rtol=1e-4, atol=1e-6), GLU_NAMES[op]
     # the single-tensor form (halves of one row) is the caller's pointer arithmetic: row stride 2 * nc
     both = cu(np.concatenate([gate, up], axis=1))
     got = ctx.glu(2, both[:, :333], both[:, 333:]).cpu().numpy()
