@@ -200,9 +200,65 @@ __device__ __forceinline__ void unit_mma_q8_0(uint32_t wt, uint32_t am, uint32_t
     }
 }
 
+__device__ __forceinline__ void mma_s8s8_k16(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%7,%8,%9,%10};"
+                 : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
+                 : "r"(a0), "r"(a1), "r"(b0), "r"(0), "r"(0), "r"(0), "r"(0));
+}
+
+// q6_K: one block_q6_K = 210 B per unit (ql[128] | qh[64] | int8 scales[16] | half d, ggml-common.h:330-336). The stage holds
+// [16 rows][8 units x 210 B] (row pitch Q6_ROW = 1680 B = 420 words: the 8 rows x 4 words of a fragment load fall into 32 different
+// banks); warp w owns unit w of every row, which starts on a 2-byte phase for odd w: aligned 32-bit loads, realigned by a funnel shift
+// (the phase is warp-uniform). The scales apply per 16 weights, so a 16-group is one m16n8k16 MMA (SASS IMMA.16816) on signed
+// operands: ((lo + hi + 0x60606060) ^ 0x80808080) turns four 6-bit codes into int8 q - 32. isum += sc * c in int32, one fp32 FMA per
+// 256 weights with d * d_y: the arithmetic of ggml_vec_dot_q6_K_q8_K_generic (ggml-cpu/quants.c:705-758).
+constexpr int Q6_ROW = 8 * SZ_Q6_K;
+__device__ __forceinline__ void unit_mma_q6_K(uint32_t wt, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, int g, int t, float (&acc)[4]) {
+    const bool     odd = (wt & 2u) != 0;
+    const uint32_t r0 = (wt & ~3u) + g * Q6_ROW, r1 = r0 + 8 * Q6_ROW;
+    auto ldw = [&](uint32_t row, int word) {  // 32-bit word `word` of the unit
+        const uint32_t a = row + 4 * word;
+        return odd ? __funnelshift_r(lds32(a), lds32(a + 4), 16) : lds32(a);
+    };
+    uint32_t sc0[4], sc1[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) { sc0[i] = ldw(r0, 48 + i); sc1[i] = ldw(r1, 48 + i); }
+    const float d0 = half_bits_to_float((uint16_t) (ldw(r0, 52) & 0xffff)), d1 = half_bits_to_float((uint16_t) (ldw(r1, 52) & 0xffff));
+    const uint32_t bcol = am + g * cs_m + 4 * t;  // B fragment: column g, k bytes 4t .. 4t + 3 of a 16-group
+    int isum[4] = { 0, 0, 0, 0 };
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+#pragma unroll
+        for (int s = 0; s < 2; s++) {  // l = 16 s + 4 t .. + 3 of the 32 l values of a half
+            const uint32_t A0 = ldw(r0, 16 * h + 4 * s + t), B0 = ldw(r0, 16 * h + 8 + 4 * s + t), H0 = ldw(r0, 32 + 8 * h + 4 * s + t);
+            const uint32_t A1 = ldw(r1, 16 * h + 4 * s + t), B1 = ldw(r1, 16 * h + 8 + 4 * s + t), H1 = ldw(r1, 32 + 8 * h + 4 * s + t);
+#pragma unroll
+            for (int qv = 0; qv < 4; qv++) {  // elements 128 h + 32 qv + l
+                const uint32_t l0 = ((qv & 1) ? B0 : A0) >> ((qv & 2) ? 4 : 0), l1 = ((qv & 1) ? B1 : A1) >> ((qv & 2) ? 4 : 0);
+                const uint32_t h0 = qv == 0 ? H0 << 4 : qv == 1 ? H0 << 2 : qv == 2 ? H0 : H0 >> 2;
+                const uint32_t h1 = qv == 0 ? H1 << 4 : qv == 1 ? H1 << 2 : qv == 2 ? H1 : H1 >> 2;
+                const uint32_t a0 = ((l0 & 0x0F0F0F0Fu) + (h0 & 0x30303030u) + 0x60606060u) ^ 0x80808080u;
+                const uint32_t a1 = ((l1 & 0x0F0F0F0Fu) + (h1 & 0x30303030u) + 0x60606060u) ^ 0x80808080u;
+                int c[4];
+                mma_s8s8_k16(c, a0, a1, lds32(bcol + 128 * h + 32 * qv + 16 * s));
+                const int gi = 8 * h + 2 * qv + s;  // scale group (16 weights)
+                const int s0 = (int) (int8_t) (sc0[gi >> 2] >> (8 * (gi & 3))), s1 = (int) (int8_t) (sc1[gi >> 2] >> (8 * (gi & 3)));
+                isum[0] += s0 * c[0]; isum[1] += s0 * c[1];
+                isum[2] += s1 * c[2]; isum[3] += s1 * c[3];
+            }
+        }
+    }
+    const float dy0 = __uint_as_float(lds32(ax + (2 * t) * cs_x)), dy1 = __uint_as_float(lds32(ax + (2 * t + 1) * cs_x));
+    acc[0] = fmaf(d0 * dy0, (float) isum[0], acc[0]);
+    acc[1] = fmaf(d0 * dy1, (float) isum[1], acc[1]);
+    acc[2] = fmaf(d1 * dy0, (float) isum[2], acc[2]);
+    acc[3] = fmaf(d1 * dy1, (float) isum[3], acc[3]);
+}
+
 template <int TYPE>
 __device__ __forceinline__ void unit_mma(uint32_t wt, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, int g, int t, float (&acc)[4]) {
-    if (TYPE == B200_TYPE_Q4_K) unit_mma_q4_K(wt, am, ax, cs_m, cs_x, g, t, acc);
+    if (TYPE == B200_TYPE_Q6_K) unit_mma_q6_K(wt, am, ax, cs_m, cs_x, g, t, acc);
+    else if (TYPE == B200_TYPE_Q4_K) unit_mma_q4_K(wt, am, ax, cs_m, cs_x, g, t, acc);
     else if (TYPE == B200_TYPE_Q8_0) unit_mma_q8_0(wt, am, ax, cs_m, cs_x, g, t, acc);
     else unit_mma_q4_0(wt, am, ax, cs_m, cs_x, g, t, acc);
 }
@@ -223,7 +279,9 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
     constexpr int UB = unit_bytes(TYPE);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int NWC = p.n_cons, NS = p.n_stages, U = p.U;
-    const int stage_bytes = NWC * MMA_ROWS * UB;
+    // q6_K: a chunk is 8 units of a row as one 1680-byte line (the 210-byte units are not 16-byte multiples): NWC == 8, U % 8 == 0
+    constexpr bool LINE = TYPE == B200_TYPE_Q6_K;
+    const int stage_bytes = LINE ? MMA_ROWS * Q6_ROW : NWC * MMA_ROWS * UB;
     const int n_chunks = (U + NWC - 1) / NWC;
 
     uint64_t * act_bar = (uint64_t *) smem;
@@ -283,8 +341,9 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
                         const uint32_t bar = smem_u32(full + stage);
                         mbar_expect_tx(bar, (uint32_t) stage_bytes);  // out-of-range rows / units are zero filled and still counted
                         const uint32_t dst = smem_u32(ring + (size_t) stage * stage_bytes);
-                        if (by_expert) tma_load_4d(dst, &maps.m[0], 0, row0, ch * NWC, e, bar);
-                        else tma_load_3d(dst, &maps.m[m], 0, row0, ch * NWC, bar);
+                        const int c2 = LINE ? ch : ch * NWC;  // q6_K maps count dimension 2 in 8-unit lines
+                        if (by_expert) tma_load_4d(dst, &maps.m[0], 0, row0, c2, e, bar);
+                        else tma_load_3d(dst, &maps.m[m], 0, row0, c2, bar);
                         if (++stage == NS) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -370,7 +429,7 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
                         mbar_wait(smem_u32(full + stage), phase);
                         const int u = ch * NWC + w;
                         if (u < U) {
-                            const uint32_t wt = smem_u32(ring + (size_t) stage * stage_bytes) + (uint32_t) w * MMA_ROWS * UB;
+                            const uint32_t wt = smem_u32(ring + (size_t) stage * stage_bytes) + (uint32_t) w * (LINE ? UB : MMA_ROWS * UB);
                             unit_mma<TYPE>(wt, am0 + (uint32_t) u * ACT_MAIN, ax0 + (uint32_t) u * ACT_AUX, cs_m, cs_x, g, t, acc[r]);
                         }
                         __syncwarp();
@@ -443,28 +502,80 @@ size_t mv_mma_smem(int type, int U, int n_cons, int n_stages) {
     size_t off = (64 + 16 * (size_t) n_stages + 127) / 128 * 128;
     off = (off + (size_t) 8 * ((size_t) U * (ACT_MAIN + ACT_AUX) + 16) + 127) / 128 * 128;
     off = (off + (size_t) 2 * n_cons * MMA_RT * 128 * 4 + 1023) / 1024 * 1024;
-    return off + (size_t) n_stages * n_cons * MMA_ROWS * unit_bytes(type) + 1024;
+    return off + (size_t) n_stages * (type == B200_TYPE_Q6_K ? 8 : n_cons) * MMA_ROWS * unit_bytes(type) + 1024;
 }
 
 // the 8 activation columns of a K-long row plus a minimal ring must fit in shared memory (K = 28672 does not: 258 KB of activations)
-bool mv_mma_fits(int type, int64_t K) { return mv_mma_smem(type, (int) (K / 256), 4, 2) <= 227 * 1024; }
+bool mv_mma_fits(int type, int64_t K) {
+    if (type == B200_TYPE_Q6_K) return K % 2048 == 0 && mv_mma_smem(type, (int) (K / 256), 8, 2) <= 227 * 1024;
+    return mv_mma_smem(type, (int) (K / 256), 4, 2) <= 227 * 1024;
+}
 
 bool mv_mma_usable(int type) {
-    return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0) && mma_get_encode() != nullptr;
+    return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q6_K) && mma_get_encode() != nullptr;
+}
+
+// consumer warps / ring stages: as many warps as leave room for >= 3 stages next to the 8 activation columns (K = 14336: 129 KB of
+// them); q6_K is tied to 8 warps (one per unit of a 1680-byte line)
+static bool mma_pick_cfg(const b200_ctx * ctx, int type, int U, int * n_cons, int * n_stages) {
+    static const int cand[] = { 16, 12, 8, 6, 4 };
+    const int forced = type == B200_TYPE_Q6_K ? 8 : ctx->mma_warps;
+    for (int nc : cand) {
+        if (forced > 0 && nc != forced) continue;
+        for (int ns = 6; ns >= 2; ns--) {
+            if (ns < 3 && nc > 4 && type != B200_TYPE_Q6_K) continue;
+            if (mv_mma_smem(type, U, nc, ns) <= 227 * 1024) { *n_cons = nc; *n_stages = ns; return true; }
+        }
+    }
+    if (forced > 0 && mv_mma_smem(type, U, forced, 2) <= 227 * 1024) { *n_cons = forced; *n_stages = 2; return true; }
+    return false;
+}
+
+// the weight stream as a tensor map: [unit][row][unit bytes] (a box lands as NWC dense [16][unit bytes] sub-tiles) or, for q6_K,
+// [8-unit line][row][1680 B] as 210 uint64 per line (inner box dimensions are limited to 256 elements); dimension 3 = experts
+static CUresult mma_encode_map(CUtensorMap * map, int type, const void * w, int64_t M, int U, size_t nb01, int n_cons, int64_t n_as, size_t nb02) {
+    const int  UB   = unit_bytes(type);
+    const bool line = type == B200_TYPE_Q6_K;
+    cuuint64_t dims[4]    = { (cuuint64_t) (line ? Q6_ROW / 8 : UB / 4), (cuuint64_t) M, (cuuint64_t) (line ? U / 8 : U), (cuuint64_t) (n_as > 0 ? n_as : 1) };
+    cuuint64_t strides[3] = { (cuuint64_t) nb01, (cuuint64_t) (line ? Q6_ROW : UB), (cuuint64_t) nb02 };
+    cuuint32_t box[4]     = { (cuuint32_t) dims[0], MMA_ROWS, (cuuint32_t) (line ? 1 : n_cons), 1 };
+    cuuint32_t estr[4]    = { 1, 1, 1, 1 };
+    return mma_get_encode()(map, line ? CU_TENSOR_MAP_DATA_TYPE_UINT64 : CU_TENSOR_MAP_DATA_TYPE_UINT32, n_as > 0 ? 4 : 3, (void *) w, dims, strides, box,
+                            estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 }
 
 } // namespace b200
 
-static b200_status mma_set_attr(b200_ctx * ctx, int type) {
-    static bool done[3][64] = {};
-    const int ti = type == B200_TYPE_Q4_K ? 0 : type == B200_TYPE_Q4_0 ? 1 : 2;
-    if (ctx->device < 64 && !done[ti][ctx->device]) {
-        if (ti == 0)      CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        else if (ti == 1) CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q4_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        else              CU(cudaFuncSetAttribute(mv_mma_kernel<B200_TYPE_Q8_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        done[ti][ctx->device] = true;
+template <int TYPE>
+static b200_status mma_launch_t(b200_ctx * ctx, const cudaLaunchConfig_t & cfg, const MmaMaps & maps, const MmaMvParams & p) {
+    static bool done[64] = {};
+    if (ctx->device < 64 && !done[ctx->device]) {
+        CU(cudaFuncSetAttribute(mv_mma_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        done[ctx->device] = true;
     }
+    CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<TYPE>, maps, p));
+    ctx->launches++;
     return B200_OK;
+}
+
+static b200_status mma_launch(b200_ctx * ctx, int type, dim3 grid, size_t smem, const MmaMaps & maps, const MmaMvParams & p) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim          = grid;
+    cfg.blockDim         = dim3(32 * (p.n_cons + 1));
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream           = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs    = attr;
+    cfg.numAttrs = p.pdl ? 1 : 0;
+    switch (type) {
+        case B200_TYPE_Q4_K: return mma_launch_t<B200_TYPE_Q4_K>(ctx, cfg, maps, p);
+        case B200_TYPE_Q8_0: return mma_launch_t<B200_TYPE_Q8_0>(ctx, cfg, maps, p);
+        case B200_TYPE_Q6_K: return mma_launch_t<B200_TYPE_Q6_K>(ctx, cfg, maps, p);
+        default:             return mma_launch_t<B200_TYPE_Q4_0>(ctx, cfg, maps, p);
+    }
 }
 
 // host: n_ops matrices (same type, K) against `ncols` pre-quantized activation columns
@@ -472,22 +583,9 @@ b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, cons
                             float * const * dsts, const int64_t * dst_cs, int ncols, const uint8_t * act_main, const uint8_t * act_aux,
                             const float * x, size_t x_cs) {
     const int U  = (int) (K / 256);
-    const int UB = unit_bytes(type);
-    // consumer warps: as many as leave room for >= 3 ring stages next to the 8 activation columns (K = 14336: 129 KB of them)
     int n_cons = 0, n_stages = 0;
-    static const int cand[] = { 16, 12, 8, 6, 4 };
-    for (int nc : cand) {
-        if (ctx->mma_warps > 0 && nc != ctx->mma_warps) continue;
-        for (int ns = 6; ns >= 2 && !n_cons; ns--) {
-            if (ns < 3 && nc > 4) continue;
-            if (mv_mma_smem(type, U, nc, ns) <= 227 * 1024) { n_cons = nc; n_stages = ns; }
-        }
-        if (n_cons) break;
-    }
-    if (!n_cons && ctx->mma_warps > 0 && mv_mma_smem(type, U, ctx->mma_warps, 2) <= 227 * 1024) { n_cons = ctx->mma_warps; n_stages = 2; }
-    if (n_cons == 0) return b200_fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
+    if (!mma_pick_cfg(ctx, type, U, &n_cons, &n_stages)) return b200_fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
     const size_t smem = mv_mma_smem(type, U, n_cons, n_stages);
-    encode_tiled_fn enc = mma_get_encode();
     for (int o0 = 0; o0 < n_ops; o0 += MV_MAX_MATS) {
         MmaMvParams p;
         MmaMaps     maps;
@@ -503,15 +601,9 @@ b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, cons
             p.mat[i].M      = (int) Ms[o0 + i];
             p.mat[i].group0 = tiles;
             tiles += (int) ((Ms[o0 + i] + MMA_ROWS - 1) / MMA_ROWS);
-            // 3-D view of the row-major block stream: [unit][row][unit bytes] - a box lands as NWC dense [16][144 B] sub-tiles. (A 2-D
-            // box with long rows is no faster and needs an odd unit count to stay bank-conflict free: measured 2441 vs 2612 GB/s.)
-            cuuint64_t dims[3]    = { (cuuint64_t) (UB / 4), (cuuint64_t) Ms[o0 + i], (cuuint64_t) U };
-            cuuint64_t strides[2] = { (cuuint64_t) nb01s[o0 + i], (cuuint64_t) UB };
-            cuuint32_t box[3]     = { (cuuint32_t) (UB / 4), MMA_ROWS, (cuuint32_t) n_cons };
-            cuuint32_t estr[3]    = { 1, 1, 1 };
-            const CUresult cr = enc(&maps.m[i], CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, (void *) ws[o0 + i], dims, strides, box, estr,
-                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            // (a 2-D box with long rows is no faster for the 144 / 272-byte units and needs an odd unit count to stay bank-conflict free:
+            // measured 2441 vs 2612 GB/s)
+            const CUresult cr = mma_encode_map(&maps.m[i], type, ws[o0 + i], Ms[o0 + i], U, nb01s[o0 + i], n_cons, 0, 0);
             if (cr != CUDA_SUCCESS) {
                 return b200_fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the weight stream (M=%lld K=%lld nb01=%zu)", (long long) Ms[o0 + i],
                                  (long long) K, nb01s[o0 + i]);
@@ -530,21 +622,7 @@ b200_status b200_mv_mma_run(b200_ctx * ctx, int type, int64_t K, int n_ops, cons
         p.split = ctx->split;
         if (b200_split_ll_geom(ctx, p.n_mats, Ms + o0, dsts + o0, dst_cs + o0, ncols, &p.geom)) p.split.ll = 1;
         const int grid = tiles < ctx->sm_count ? tiles : ctx->sm_count;
-        if (b200_status ast = mma_set_attr(ctx, type)) return ast;
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim          = dim3(grid);
-        cfg.blockDim         = dim3(32 * (n_cons + 1));
-        cfg.dynamicSmemBytes = smem;
-        cfg.stream           = ctx->stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs    = attr;
-        cfg.numAttrs = p.pdl ? 1 : 0;
-        if (type == B200_TYPE_Q4_K)      CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_K>, maps, p));
-        else if (type == B200_TYPE_Q8_0) CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q8_0>, maps, p));
-        else                             CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_0>, maps, p));
-        ctx->launches++;
+        if (b200_status lst = mma_launch(ctx, type, dim3(grid), smem, maps, p)) return lst;
     }
     return B200_OK;
 }
@@ -555,28 +633,14 @@ b200_status b200_mv_mma_run_ids(b200_ctx * ctx, int type, int64_t K, const uint8
                                 float * dst, const MvIds & ids, const int32_t * sp, const int32_t * eb, const uint8_t * act_main,
                                 const uint8_t * act_aux) {
     const int U  = (int) (K / 256);
-    const int UB = unit_bytes(type);
     int n_cons = 0, n_stages = 0;
-    static const int cand[] = { 16, 12, 8, 6, 4 };
-    for (int nc : cand) {
-        for (int ns = 6; ns >= 2 && !n_cons; ns--) {
-            if (ns < 3 && nc > 4) continue;
-            if (mv_mma_smem(type, U, nc, ns) <= 227 * 1024) { n_cons = nc; n_stages = ns; }
-        }
-        if (n_cons) break;
-    }
-    if (n_cons == 0) return b200_fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
+    if (!mma_pick_cfg(ctx, type, U, &n_cons, &n_stages)) return b200_fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
     const size_t smem = mv_mma_smem(type, U, n_cons, n_stages);
     MmaMvParams p;
     MmaMaps     maps;
     memset(&p, 0, sizeof(p));
     memset(&maps, 0, sizeof(maps));
-    cuuint64_t dims[4]    = { (cuuint64_t) (UB / 4), (cuuint64_t) M, (cuuint64_t) U, (cuuint64_t) n_as };
-    cuuint64_t strides[3] = { (cuuint64_t) nb01, (cuuint64_t) UB, (cuuint64_t) nb02 };
-    cuuint32_t box[4]     = { (cuuint32_t) (UB / 4), MMA_ROWS, (cuuint32_t) n_cons, 1 };
-    cuuint32_t estr[4]    = { 1, 1, 1, 1 };
-    if (mma_get_encode()(&maps.m[0], CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, (void *) as, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                         CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+    if (mma_encode_map(&maps.m[0], type, as, M, U, nb01, n_cons, n_as, nb02) != CUDA_SUCCESS) {
         return b200_fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the expert weight stream (M=%lld K=%lld n_as=%lld)", (long long) M,
                          (long long) K, (long long) n_as);
     }
@@ -596,20 +660,5 @@ b200_status b200_mv_mma_run_ids(b200_ctx * ctx, int type, int64_t K, const uint8
     int per_expert = (int) (ctx->sm_count / n_as);
     if (per_expert < 1) per_expert = 1;
     if (per_expert > p.total_tiles) per_expert = p.total_tiles;
-    if (b200_status ast = mma_set_attr(ctx, type)) return ast;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim          = dim3(per_expert, (unsigned) n_as);
-    cfg.blockDim         = dim3(32 * (n_cons + 1));
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream           = ctx->stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs    = attr;
-    cfg.numAttrs = p.pdl ? 1 : 0;
-    if (type == B200_TYPE_Q4_K)      CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_K>, maps, p));
-    else if (type == B200_TYPE_Q8_0) CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q8_0>, maps, p));
-    else                             CU(cudaLaunchKernelEx(&cfg, mv_mma_kernel<B200_TYPE_Q4_0>, maps, p));
-    ctx->launches++;
-    return B200_OK;
+    return mma_launch(ctx, type, dim3(per_expert, (unsigned) n_as), smem, maps, p);
 }

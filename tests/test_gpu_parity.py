@@ -297,9 +297,43 @@ def test_q6_K_decode(ctx, pkg, oracle, M, K, N):
     X = (rng.standard_normal((N, K)) * rng.choice([0.05, 1.0, 20.0], (N, 1))).astype(np.float32)
     got = ctx.mul_mat(Q6_K, cu(W), cu(X)).cpu().numpy()
     assert oracle.nmse(oracle.mul_mat(Q6_K, W, X), got) <= NMSE_TIGHT
-    if N > 1:   # column c of an N-column call equals the 1-column call
-        one = ctx.mul_mat(Q6_K, cu(W), cu(X[1:2])).cpu().numpy()
-        assert np.array_equal(one[0], got[1])
+    if N > 1:   # column c of an N-column call equals the 1-column call (from 3 columns on the tensor-core kernel sums a row's
+        one = ctx.mul_mat(Q6_K, cu(W), cu(X[1:2])).cpu().numpy()   # units in another fp32 order: same integer sums, NMSE at the fp32 floor)
+        if N <= 2 or K % 2048:
+            assert np.array_equal(one[0], got[1])
+        else:
+            assert oracle.nmse(one[0], got[1]) <= 1e-12
+
+
+@pytest.mark.parametrize("M,K,N", [(16, 2048, 3), (100, 2048, 5), (333, 4096, 8), (48, 14336, 4), (1000, 6144, 7)])
+def test_q6_K_tensor_core_matvec(ctx, pkg, oracle, M, K, N):
+    """3..8 columns: mma.sync m16n8k16 on signed 6-bit operands, one MMA per 16-weight scale group, units read from 1680-byte lines
+    of 8 (2-byte unit phases realigned by funnel shifts); against the oracle, the dp4a kernel and the generic kernel"""
+    rng = np.random.default_rng(M * 3 + K + N)
+    W = quantize_weights(oracle, Q6_K, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = (rng.standard_normal((N, K)) * rng.choice([0.05, 1.0, 20.0], (N, 1))).astype(np.float32)
+    ref = oracle.mul_mat(Q6_K, W, X)
+    l0 = ctx.launches
+    got = ctx.mul_mat(Q6_K, cu(W), cu(X)).cpu().numpy()
+    assert ctx.launches - l0 == 2, "quantizer + one tensor-core mat-vec launch"
+    assert oracle.nmse(ref, got) <= NMSE_TIGHT
+    ctx.force_path(pkg.PATH_SIMPLE)
+    gen = ctx.mul_mat(Q6_K, cu(W), cu(X)).cpu().numpy()
+    ctx.force_path(pkg.PATH_AUTO)
+    assert oracle.nmse(gen, got) <= 1e-12
+    two = ctx.mul_mat(Q6_K, cu(W), cu(X[:2])).cpu().numpy()   # dp4a kernel
+    assert oracle.nmse(two, got[:2]) <= 1e-12
+
+
+def test_q6_K_grouped_mul_mat_id(ctx, oracle):
+    """enough pairs per expert: pairs sorted by expert, every expert multiplies its tokens 8 at a time on the tensor-core kernel (4-D map)"""
+    rng = np.random.default_rng(67)
+    n_as, M, K, n_used, n_tok = 4, 80, 2048, 2, 37
+    W = quantize_weights(oracle, Q6_K, rng.uniform(-1, 1, (n_as * M, K)).astype(np.float32)).reshape(n_as, M, -1)
+    B = rng.uniform(-1, 1, (n_tok, 1, K)).astype(np.float32)
+    ids = np.stack([rng.permutation(n_as)[:n_used] for _ in range(n_tok)]).astype(np.int32)
+    got = ctx.mul_mat_id(Q6_K, cu(W), cu(B), cu(ids)).cpu().numpy()
+    assert oracle.nmse(oracle.mul_mat_id(Q6_K, W, B, ids), got) <= NMSE_TIGHT
 
 
 @pytest.mark.parametrize("N", [9, 40, 300])
