@@ -280,9 +280,11 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int NWC = p.n_cons, NS = p.n_stages, U = p.U;
     // q6_K: a chunk is 8 units of a row as one 1680-byte line (the 210-byte units are not 16-byte multiples): NWC == 8, U % 8 == 0
+    // With 16 consumer warps the two groups of 8 take the chunks alternately (twice the warps in flight: the unpack chain of a unit is
+    // long), and all 16 partial tiles meet in the reduction.
     constexpr bool LINE = TYPE == B200_TYPE_Q6_K;
     const int stage_bytes = LINE ? MMA_ROWS * Q6_ROW : NWC * MMA_ROWS * UB;
-    const int n_chunks = (U + NWC - 1) / NWC;
+    const int n_chunks = LINE ? U / 8 : (U + NWC - 1) / NWC;
 
     uint64_t * act_bar = (uint64_t *) smem;
     uint64_t * full    = (uint64_t *) (smem + 64);
@@ -319,7 +321,7 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
         mbar_init(smem_u32(act_bar), 1);
         for (int i = 0; i < NS; i++) {
             mbar_init(smem_u32(full + i), 1);
-            mbar_init(smem_u32(empty + i), NWC);
+            mbar_init(smem_u32(empty + i), TYPE == B200_TYPE_Q6_K ? 8 : NWC);  // q6_K: a stage (8 units) belongs to one group of 8 warps
         }
         fence_mbar_init();
     }
@@ -361,6 +363,8 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
     const uint32_t am0 = smem_u32(act_m), ax0 = smem_u32(act_x);
     int stage = 0; uint32_t phase = 0;
     int parity = 0;
+    const int n_groups = LINE ? NWC / 8 : 1, my_group = LINE ? w >> 3 : 0, wu = LINE ? (w & 7) : w;
+    int seq = 0;  // q6_K: running chunk number, chunk seq belongs to group seq % n_groups
     for (int pass = 0; pass < n_passes; pass++) {
         const int nc = min(8, n_pairs - 8 * pass);
         // activations: nc columns of U records (one bulk copy per column: the shared column stride is padded); columns nc..7 are
@@ -426,14 +430,17 @@ mv_mma_kernel(const __grid_constant__ MmaMaps maps, const __grid_constant__ MmaM
             for (int r = 0; r < MMA_RT; r++) {
                 if (r < nt) {
                     for (int ch = 0; ch < n_chunks; ch++) {
-                        mbar_wait(smem_u32(full + stage), phase);
-                        const int u = ch * NWC + w;
-                        if (u < U) {
-                            const uint32_t wt = smem_u32(ring + (size_t) stage * stage_bytes) + (uint32_t) w * (LINE ? UB : MMA_ROWS * UB);
-                            unit_mma<TYPE>(wt, am0 + (uint32_t) u * ACT_MAIN, ax0 + (uint32_t) u * ACT_AUX, cs_m, cs_x, g, t, acc[r]);
+                        const bool mine = !LINE || (seq++ % n_groups) == my_group;
+                        if (mine) {
+                            mbar_wait(smem_u32(full + stage), phase);
+                            const int u = LINE ? ch * 8 + wu : ch * NWC + w;
+                            if (u < U) {
+                                const uint32_t wt = smem_u32(ring + (size_t) stage * stage_bytes) + (uint32_t) wu * (LINE ? UB : MMA_ROWS * UB);
+                                unit_mma<TYPE>(wt, am0 + (uint32_t) u * ACT_MAIN, ax0 + (uint32_t) u * ACT_AUX, cs_m, cs_x, g, t, acc[r]);
+                            }
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(smem_u32(empty + stage));
                         }
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(smem_u32(empty + stage));
                         if (++stage == NS) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -516,12 +523,13 @@ bool mv_mma_usable(int type) {
 }
 
 // consumer warps / ring stages: as many warps as leave room for >= 3 stages next to the 8 activation columns (K = 14336: 129 KB of
-// them); q6_K is tied to 8 warps (one per unit of a 1680-byte line)
+// them); q6_K takes 16 or 8 warps (groups of 8: one warp per unit of a 1680-byte line)
 static bool mma_pick_cfg(const b200_ctx * ctx, int type, int U, int * n_cons, int * n_stages) {
     static const int cand[] = { 16, 12, 8, 6, 4 };
-    const int forced = type == B200_TYPE_Q6_K ? 8 : ctx->mma_warps;
+    const int forced = type == B200_TYPE_Q6_K ? (ctx->mma_warps == 8 ? 8 : 0) : ctx->mma_warps;
     for (int nc : cand) {
         if (forced > 0 && nc != forced) continue;
+        if (type == B200_TYPE_Q6_K && nc != 16 && nc != 8) continue;  // groups of 8 warps: one per unit of a 1680-byte line
         for (int ns = 6; ns >= 2; ns--) {
             if (ns < 3 && nc > 4 && type != B200_TYPE_Q6_K) continue;
             if (mv_mma_smem(type, U, nc, ns) <= 227 * 1024) { *n_cons = nc; *n_stages = ns; return true; }
