@@ -213,12 +213,12 @@ __device__ __forceinline__ void mma_s8s8_k16(int (&c)[4], uint32_t a0, uint32_t 
 // operands: ((lo + hi + 0x60606060) ^ 0x80808080) turns four 6-bit codes into int8 q - 32. isum += sc * c in int32, one fp32 FMA per
 // 256 weights with d * d_y: the arithmetic of ggml_vec_dot_q6_K_q8_K_generic (ggml-cpu/quants.c:705-758).
 constexpr int Q6_ROW = 8 * SZ_Q6_K;
-__device__ __forceinline__ void unit_mma_q6_K(uint32_t wt, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, int g, int t, float (&acc)[4]) {
-    const bool     odd = (wt & 2u) != 0;
+template <bool ODD>  // ODD: the unit starts 2 bytes behind a word boundary (warp-uniform: own code path, no predicated second loads)
+__device__ __forceinline__ void unit_mma_q6_K_t(uint32_t wt, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, int g, int t, float (&acc)[4]) {
     const uint32_t r0 = (wt & ~3u) + g * Q6_ROW, r1 = r0 + 8 * Q6_ROW;
     auto ldw = [&](uint32_t row, int word) {  // 32-bit word `word` of the unit
         const uint32_t a = row + 4 * word;
-        return odd ? __funnelshift_r(lds32(a), lds32(a + 4), 16) : lds32(a);
+        return ODD ? __funnelshift_r(lds32(a), lds32(a + 4), 16) : lds32(a);
     };
     uint32_t sc0[4], sc1[4];
 #pragma unroll
@@ -237,8 +237,9 @@ __device__ __forceinline__ void unit_mma_q6_K(uint32_t wt, uint32_t am, uint32_t
                 const uint32_t l0 = ((qv & 1) ? B0 : A0) >> ((qv & 2) ? 4 : 0), l1 = ((qv & 1) ? B1 : A1) >> ((qv & 2) ? 4 : 0);
                 const uint32_t h0 = qv == 0 ? H0 << 4 : qv == 1 ? H0 << 2 : qv == 2 ? H0 : H0 >> 2;
                 const uint32_t h1 = qv == 0 ? H1 << 4 : qv == 1 ? H1 << 2 : qv == 2 ? H1 : H1 >> 2;
-                const uint32_t a0 = ((l0 & 0x0F0F0F0Fu) + (h0 & 0x30303030u) + 0x60606060u) ^ 0x80808080u;
-                const uint32_t a1 = ((l1 & 0x0F0F0F0Fu) + (h1 & 0x30303030u) + 0x60606060u) ^ 0x80808080u;
+                // (lo | hi) + 0x60 never carries out of a byte; ^ 0x80 then gives q - 32 as int8. The two ANDs and the OR are one LOP3 pair
+                const uint32_t a0 = (((l0 & 0x0F0F0F0Fu) | (h0 & 0x30303030u)) + 0x60606060u) ^ 0x80808080u;
+                const uint32_t a1 = (((l1 & 0x0F0F0F0Fu) | (h1 & 0x30303030u)) + 0x60606060u) ^ 0x80808080u;
                 int c[4];
                 mma_s8s8_k16(c, a0, a1, lds32(bcol + 128 * h + 32 * qv + 16 * s));
                 const int gi = 8 * h + 2 * qv + s;  // scale group (16 weights)
@@ -253,6 +254,11 @@ __device__ __forceinline__ void unit_mma_q6_K(uint32_t wt, uint32_t am, uint32_t
     acc[1] = fmaf(d0 * dy1, (float) isum[1], acc[1]);
     acc[2] = fmaf(d1 * dy0, (float) isum[2], acc[2]);
     acc[3] = fmaf(d1 * dy1, (float) isum[3], acc[3]);
+}
+
+__device__ __forceinline__ void unit_mma_q6_K(uint32_t wt, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, int g, int t, float (&acc)[4]) {
+    if (wt & 2u) unit_mma_q6_K_t<true>(wt, am, ax, cs_m, cs_x, g, t, acc);
+    else unit_mma_q6_K_t<false>(wt, am, ax, cs_m, cs_x, g, t, acc);
 }
 
 template <int TYPE>
