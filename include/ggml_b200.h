@@ -219,6 +219,9 @@ B200_API b200_status  b200_glu(b200_ctx * ctx, int glu_op, float alpha, float li
 /* GGML_OP_ADD with ggml broadcasting (ggml-cpu/binary-ops.cpp; ggml-cuda/binbcast.cu): ne/nb_* as struct ggml_tensor carries them */
 B200_API b200_status  b200_add(b200_ctx * ctx, const int64_t * ne, const float * a, const size_t * nb_a, const float * b, const int64_t * ne_b,
                                const size_t * nb_b, float * dst, const size_t * nb_d);
+/* GGML_OP_MUL, same geometry rules (the expert-weight scaling behind a fused MoE FFN: test_mul_mat_vec_fusion, test-backend-ops.cpp:5227-5229) */
+B200_API b200_status  b200_mul(b200_ctx * ctx, const int64_t * ne, const float * a, const size_t * nb_a, const float * b, const int64_t * ne_b,
+                               const size_t * nb_b, float * dst, const size_t * nb_d);
 /* GGML_OP_ADD_ID (ggml-cpu/ops.cpp:701-750; ggml-cuda/add-id.cu): dst[:, i, t] = a[:, i, t] + bias[:, ids[i, t]] */
 B200_API b200_status  b200_add_id(b200_ctx * ctx, const float * a, size_t a_nb1, size_t a_nb2, const float * bias, size_t bias_nb1, int64_t n_as,
                                   const int32_t * ids, size_t ids_nb1, float * dst, size_t nb1, size_t nb2, int64_t M, int64_t n_used, int64_t n_tok);

@@ -34,7 +34,7 @@ EXPORTS = [
     "b200_mul_mat_supported", "b200_mul_mat", "b200_mul_mat_shared_src1", "b200_mul_mat_host", "b200_mul_mat_id_supported",
     "b200_mul_mat_id", "b200_mm_ids_sort", "b200_ctx_set_row_split", "b200_ctx_set_row_split_ll", "b200_ctx_set_row_split_deferred", "b200_ctx_row_split_wait", "b200_ctx_set_weight_cache", "b200_ctx_set_mmq_f16", "b200_ctx_set_prefetch", "b200_ctx_trace", "b200_ctx_trace_read", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
     "b200_mul_mat_fused_supported", "b200_mul_mat_fused", "b200_mul_mat_id_fused_supported", "b200_mul_mat_id_fused",
-    "b200_glu", "b200_add", "b200_add_id",
+    "b200_glu", "b200_add", "b200_mul", "b200_add_id",
 ]
 
 
@@ -164,6 +164,7 @@ def lib() -> C.CDLL:
         L.b200_mul_mat_id_fused.argtypes = [vp, C.POINTER(MulMatIdDesc), vp, vp, vp, vp, C.POINTER(Fusion), vp]
         L.b200_glu.argtypes = [vp, ci, C.c_float, C.c_float, vp, sz, vp, sz, vp, sz, i64, i64]
         L.b200_add.argtypes = [vp, C.POINTER(i64), vp, C.POINTER(sz), vp, C.POINTER(i64), C.POINTER(sz), vp, C.POINTER(sz)]
+        L.b200_mul.argtypes = L.b200_add.argtypes
         L.b200_add_id.argtypes = [vp, vp, sz, sz, vp, sz, i64, vp, sz, vp, sz, sz, i64, i64, i64]
         for n in ("b200_memcpy_h2d_async", "b200_memcpy_d2h_async", "b200_memcpy_d2d_async"):
             getattr(L, n).argtypes = [vp, vp, vp, sz]
@@ -420,7 +421,11 @@ class Context:
                              out.stride(0) * 4, gate.shape[1], gate.shape[0]), "b200_glu")
         return out
 
-    def add(self, a, b):
+    def mul(self, a, b):
+        """GGML_OP_MUL, same broadcasting as add"""
+        return self.add(a, b, fn="b200_mul")
+
+    def add(self, a, b, fn="b200_add"):
         """GGML_OP_ADD with ggml broadcasting: a, b float32 tensors of up to 4 dims in torch order [ne3, ne2, ne1, ne0]"""
         a4 = a.reshape((1,) * (4 - a.dim()) + tuple(a.shape))
         b4 = b.reshape((1,) * (4 - b.dim()) + tuple(b.shape))
@@ -428,7 +433,7 @@ class Context:
         i64x4, szx4 = C.c_int64 * 4, C.c_size_t * 4
         ne = lambda x: i64x4(*reversed(x.shape))
         nb = lambda x: szx4(*[s * 4 for s in reversed(x.stride())])
-        check(lib().b200_add(self.h, ne(a4), a4.data_ptr(), nb(a4), b4.data_ptr(), ne(b4), nb(b4), out.data_ptr(), nb(out)), "b200_add")
+        check(getattr(lib(), fn)(self.h, ne(a4), a4.data_ptr(), nb(a4), b4.data_ptr(), ne(b4), nb(b4), out.data_ptr(), nb(out)), fn)
         return out.reshape(a.shape)
 
     def add_id(self, a, bias, ids):

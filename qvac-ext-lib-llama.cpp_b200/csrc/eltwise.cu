@@ -25,6 +25,7 @@ struct AddParams {
 };
 
 // no __restrict__: ggml_add_inplace makes dst alias src0 (element for element, which this kernel tolerates)
+template <bool MUL>
 __global__ void __launch_bounds__(256) add_kernel(const AddParams p, const float * a, const float * b, float * dst, int64_t total) {
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t r = i;
@@ -34,7 +35,7 @@ __global__ void __launch_bounds__(256) add_kernel(const AddParams p, const float
         const int64_t i3 = r / p.ne[2];
         const float va = a[i0 + i1 * p.s0[1] + i2 * p.s0[2] + i3 * p.s0[3]];
         const float vb = b[i0 % p.ne1[0] + (i1 % p.ne1[1]) * p.s1[1] + (i2 % p.ne1[2]) * p.s1[2] + (i3 % p.ne1[3]) * p.s1[3]];
-        dst[i0 + i1 * p.sd[1] + i2 * p.sd[2] + i3 * p.sd[3]] = va + vb;
+        dst[i0 + i1 * p.sd[1] + i2 * p.sd[2] + i3 * p.sd[3]] = MUL ? va * vb : va + vb;
     }
 }
 
@@ -84,29 +85,40 @@ b200_status b200_glu(b200_ctx * ctx, int glu_op, float alpha, float limit, const
     return B200_OK;
 }
 
-b200_status b200_add(b200_ctx * ctx, const int64_t * ne, const float * a, const size_t * nb_a, const float * b, const int64_t * ne_b,
-                     const size_t * nb_b, float * dst, const size_t * nb_d) {
+static b200_status binary_bcast(b200_ctx * ctx, bool mul, const int64_t * ne, const float * a, const size_t * nb_a, const float * b, const int64_t * ne_b,
+                                const size_t * nb_b, float * dst, const size_t * nb_d) {
     if (!ctx || !ne || !nb_a || !ne_b || !nb_b || !nb_d) return b200_fail(B200_ERR_ARG, "null argument");
     AddParams p;
     int64_t total = 1;
     for (int i = 0; i < 4; i++) {
-        if (ne[i] < 0 || ne_b[i] <= 0 || ne[i] % ne_b[i] != 0) return b200_fail(B200_ERR_UNSUPPORTED, "ADD: src1 does not broadcast onto src0");
-        if (nb_a[i] % 4 || nb_b[i] % 4 || nb_d[i] % 4) return b200_fail(B200_ERR_ARG, "ADD strides");
+        if (ne[i] < 0 || ne_b[i] <= 0 || ne[i] % ne_b[i] != 0) return b200_fail(B200_ERR_UNSUPPORTED, "ADD / MUL: src1 does not broadcast onto src0");
+        if (nb_a[i] % 4 || nb_b[i] % 4 || nb_d[i] % 4) return b200_fail(B200_ERR_ARG, "ADD / MUL strides");
         p.ne[i] = ne[i]; p.ne1[i] = ne_b[i];
         p.s0[i] = (int64_t) (nb_a[i] / 4); p.s1[i] = (int64_t) (nb_b[i] / 4); p.sd[i] = (int64_t) (nb_d[i] / 4);
         total *= ne[i];
     }
-    if (nb_a[0] != 4 || nb_b[0] != 4 || nb_d[0] != 4) return b200_fail(B200_ERR_UNSUPPORTED, "ADD: dimension 0 must be contiguous F32");
+    if (nb_a[0] != 4 || nb_b[0] != 4 || nb_d[0] != 4) return b200_fail(B200_ERR_UNSUPPORTED, "ADD / MUL: dimension 0 must be contiguous F32");
     if (total == 0) return B200_OK;
     if (!a || !b || !dst) return b200_fail(B200_ERR_ARG, "null argument");
     cudaError_t e = cudaSetDevice(ctx->device);
     if (e != cudaSuccess) return FAIL_CUDA(e);
     if (b200_status fst = b200_split_flush(ctx)) return fst;
-    add_kernel<<<grid_for(ctx, total), 256, 0, ctx->stream>>>(p, a, b, dst, total);
+    if (mul) add_kernel<true><<<grid_for(ctx, total), 256, 0, ctx->stream>>>(p, a, b, dst, total);
+    else add_kernel<false><<<grid_for(ctx, total), 256, 0, ctx->stream>>>(p, a, b, dst, total);
     e = cudaGetLastError();
     if (e != cudaSuccess) return FAIL_CUDA(e);
     ctx->launches++;
     return B200_OK;
+}
+
+b200_status b200_add(b200_ctx * ctx, const int64_t * ne, const float * a, const size_t * nb_a, const float * b, const int64_t * ne_b,
+                     const size_t * nb_b, float * dst, const size_t * nb_d) {
+    return binary_bcast(ctx, false, ne, a, nb_a, b, ne_b, nb_b, dst, nb_d);
+}
+
+b200_status b200_mul(b200_ctx * ctx, const int64_t * ne, const float * a, const size_t * nb_a, const float * b, const int64_t * ne_b,
+                     const size_t * nb_b, float * dst, const size_t * nb_d) {
+    return binary_bcast(ctx, true, ne, a, nb_a, b, ne_b, nb_b, dst, nb_d);
 }
 
 b200_status b200_add_id(b200_ctx * ctx, const float * a, size_t a_nb1, size_t a_nb2, const float * bias, size_t bias_nb1, int64_t n_as,

@@ -491,7 +491,7 @@ void run_glu(be_ctx * c, ggml_tensor * node) {
 }
 void run_add(be_ctx * c, ggml_tensor * node) {
     const ggml_tensor * a = node->src[0], * b = node->src[1];
-    CHECK(b200_add(c->ctx, node->ne, (const float *) a->data, a->nb, (const float *) b->data, b->ne, b->nb, (float *) node->data, node->nb));
+    CHECK((node->op == GGML_OP_MUL ? b200_mul : b200_add)(c->ctx, node->ne, (const float *) a->data, a->nb, (const float *) b->data, b->ne, b->nb, (float *) node->data, node->nb));
 }
 void run_add_id(be_ctx * c, ggml_tensor * node) {
     const ggml_tensor * a = node->src[0], * b = node->src[1], * ids = node->src[2];
@@ -641,7 +641,7 @@ ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
                                   (float *) node->data));
         } else if (node->op == GGML_OP_GLU && glu_ok(node)) {
             run_glu(c, node);
-        } else if (node->op == GGML_OP_ADD && add_ok(node)) {
+        } else if ((node->op == GGML_OP_ADD || node->op == GGML_OP_MUL) && add_ok(node)) {
             run_add(c, node);
         } else if (node->op == GGML_OP_ADD_ID && add_id_ok(node)) {
             run_add_id(c, node);
@@ -758,6 +758,7 @@ bool dev_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
         case GGML_OP_GLU:
             return glu_ok(op);
         case GGML_OP_ADD:
+        case GGML_OP_MUL:  // same broadcasting kernel; the expert-weight scaling behind a fused MoE FFN
             return add_ok(op);
         case GGML_OP_ADD_ID:
             return add_id_ok(op);

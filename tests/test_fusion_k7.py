@@ -194,6 +194,7 @@ def test_standalone_glu_add_add_id(ctx, oracle):
         b = rng.standard_normal(bshape).astype(np.float32)
         ref = a + np.tile(b, [a.shape[i] // b.shape[i] for i in range(4)])
         assert np.array_equal(ctx.add(cu(a), cu(b)).cpu().numpy(), ref), bshape
+        assert np.array_equal(ctx.mul(cu(a), cu(b)).cpu().numpy(), a * np.tile(b, [a.shape[i] // b.shape[i] for i in range(4)])), bshape
     # ADD_ID
     n_tok, n_used, M, n_as = 6, 3, 50, 5
     x = rng.standard_normal((n_tok, n_used, M)).astype(np.float32)
