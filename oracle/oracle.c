@@ -60,6 +60,7 @@ size_t orc_row_size(int type, int64_t k) {
         case ORC_Q4_0: return (size_t)(k / ORC_QK) * ORC_SZ_Q4_0;
         case ORC_Q8_0: return (size_t)(k / ORC_QK) * ORC_SZ_Q8_0;
         case ORC_Q4_K: return (size_t)(k / ORC_QK_K) * ORC_SZ_Q4_K;
+        case ORC_Q5_K: return (size_t)(k / ORC_QK_K) * ORC_SZ_Q5_K;
         case ORC_Q6_K: return (size_t)(k / ORC_QK_K) * ORC_SZ_Q6_K;
     }
     return 0;
@@ -276,6 +277,58 @@ float orc_vec_dot_q4_K_q8_K(int64_t k, const void *vx, const void *vy) {
     return sumf;
 }
 
+/* block_q5_K = { fp16 d, dmin; uint8 scales[12]; uint8 qh[32]; uint8 qs[128] } (ggml-common.h:310-325): q4_K's layout plus a fifth
+ * bit: sub-block s (32 weights) takes the low (s even) / high (s odd) nibbles of qs[32*(s/2) + l] and bit s of qh[l]
+ * (dequantize_row_q5_K, ggml-quants.c; vec_dot: ggml-cpu/quants.c:625-703, same lane structure as q4_K) */
+void orc_dequantize_row_q5_K(const void *vx, float *y, int64_t k) {
+    const uint8_t *x = (const uint8_t *)vx;
+    for (int64_t b = 0; b < k / ORC_QK_K; b++, x += ORC_SZ_Q5_K) {
+        uint16_t hd, hm; memcpy(&hd, x, 2); memcpy(&hm, x + 2, 2);
+        const float d = orc_fp16_to_fp32(hd), dmin = orc_fp16_to_fp32(hm);
+        const uint8_t *sc12 = x + 4, *qh = x + 16, *q = x + 48;
+        for (int g = 0; g < 4; g++, q += 32) {
+            uint8_t s, m;
+            q4k_scale_min(2 * g, sc12, &s, &m);
+            const float d1 = d * s, m1 = dmin * m;
+            q4k_scale_min(2 * g + 1, sc12, &s, &m);
+            const float d2 = d * s, m2 = dmin * m;
+            for (int l = 0; l < 32; l++) *y++ = d1 * ((q[l] & 0x0f) + ((qh[l] >> (2 * g)) & 1 ? 16 : 0)) - m1;
+            for (int l = 0; l < 32; l++) *y++ = d2 * ((q[l] >> 4) + ((qh[l] >> (2 * g + 1)) & 1 ? 16 : 0)) - m2;
+        }
+    }
+}
+
+float orc_vec_dot_q5_K_q8_K(int64_t k, const void *vx, const void *vy) {
+    const uint8_t *x = (const uint8_t *)vx, *y = (const uint8_t *)vy;
+    float sums[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    float sumf = 0;
+    for (int64_t b = 0; b < k / ORC_QK_K; b++, x += ORC_SZ_Q5_K, y += ORC_SZ_Q8_K) {
+        float yd; memcpy(&yd, y, 4);
+        const int8_t *q8 = (const int8_t *)(y + 4);
+        int16_t bsums[16]; memcpy(bsums, y + 4 + ORC_QK_K, 32);
+        uint16_t hd, hm; memcpy(&hd, x, 2); memcpy(&hm, x + 2, 2);
+        const uint8_t *sc12 = x + 4, *qh = x + 16, *q4 = x + 48;
+        int32_t lane[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        int summin = 0;
+        for (int s = 0; s < 8; s++) {                 /* sub-block s: 32 weights */
+            uint8_t sc, mn;
+            q4k_scale_min(s, sc12, &sc, &mn);
+            summin += (bsums[2 * s] + bsums[2 * s + 1]) * mn;
+            const uint8_t *qq = q4 + 32 * (s / 2);
+            for (int l = 0; l < 32; l++) {
+                int w = ((s & 1) ? (qq[l] >> 4) : (qq[l] & 0x0f)) + (((qh[l] >> s) & 1) ? 16 : 0);
+                lane[l & 7] += (int32_t)sc * (int16_t)(q8[32 * s + l] * w);
+            }
+        }
+        const float d = orc_fp16_to_fp32(hd) * yd;
+        for (int l = 0; l < 8; l++) sums[l] += d * lane[l];
+        const float dmin = orc_fp16_to_fp32(hm) * yd;
+        sumf -= dmin * summin;
+    }
+    for (int l = 0; l < 8; l++) sumf += sums[l];
+    return sumf;
+}
+
 /* block_q6_K = { uint8 ql[128]; uint8 qh[64]; int8 scales[16]; fp16 d } (ggml-common.h:335-343). Weight l of a 128-half:
  * low nibble / high nibble of ql[l], ql[l+32] plus two bits of qh[l], minus 32; one int8 scale per 16 weights
  * (ggml-quants.c:1762-1791) */
@@ -326,15 +379,16 @@ float orc_vec_dot_q6_K_q8_K(int64_t k, const void *vx, const void *vy) {
 /* ---------- the ops ---------- */
 
 static size_t act_row_size(int type, int64_t k) {
-    return (type == ORC_Q4_K || type == ORC_Q6_K) ? (size_t)(k / ORC_QK_K) * ORC_SZ_Q8_K : (size_t)(k / ORC_QK) * ORC_SZ_Q8_0;
+    return (type == ORC_Q4_K || type == ORC_Q5_K || type == ORC_Q6_K) ? (size_t)(k / ORC_QK_K) * ORC_SZ_Q8_K : (size_t)(k / ORC_QK) * ORC_SZ_Q8_0;
 }
 static void act_quantize(int type, const float *x, void *y, int64_t k) {
-    if (type == ORC_Q4_K || type == ORC_Q6_K) orc_quantize_row_q8_K(x, y, k); else orc_quantize_row_q8_0(x, y, k);
+    if (type == ORC_Q4_K || type == ORC_Q5_K || type == ORC_Q6_K) orc_quantize_row_q8_K(x, y, k); else orc_quantize_row_q8_0(x, y, k);
 }
 static float dot(int type, int64_t k, const void *w, const void *a) {
     switch (type) {
         case ORC_Q4_0: return orc_vec_dot_q4_0_q8_0(k, w, a);
         case ORC_Q8_0: return orc_vec_dot_q8_0_q8_0(k, w, a);
+        case ORC_Q5_K: return orc_vec_dot_q5_K_q8_K(k, w, a);
         case ORC_Q6_K: return orc_vec_dot_q6_K_q8_K(k, w, a);
         default:       return orc_vec_dot_q4_K_q8_K(k, w, a);
     }
@@ -421,6 +475,7 @@ void orc_mul_mat_f64(int type, const void *W, int64_t M, int64_t K, size_t nb01,
         const void *row = (const char *)W + r * nb01;
         if (type == ORC_Q4_0) orc_dequantize_row_q4_0(row, wf, K);
         else if (type == ORC_Q8_0) orc_dequantize_row_q8_0(row, wf, K);
+        else if (type == ORC_Q5_K) orc_dequantize_row_q5_K(row, wf, K);
         else if (type == ORC_Q6_K) orc_dequantize_row_q6_K(row, wf, K);
         else orc_dequantize_row_q4_K(row, wf, K);
         for (int64_t n = 0; n < N; n++) {

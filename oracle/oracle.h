@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-enum orc_type { ORC_Q4_0 = 2, ORC_Q8_0 = 8, ORC_Q4_K = 12, ORC_Q6_K = 14 }; /* == enum ggml_type values, ggml/include/ggml.h:378-395 */
+enum orc_type { ORC_Q4_0 = 2, ORC_Q8_0 = 8, ORC_Q4_K = 12, ORC_Q5_K = 13, ORC_Q6_K = 14 }; /* == enum ggml_type values, ggml/include/ggml.h:378-395 */
 
 /* block sizes in bytes / elements (ggml/src/ggml-common.h:170-175, 218-238, 291-305, 322-328) */
 #define ORC_QK      32
@@ -30,6 +30,7 @@ enum orc_type { ORC_Q4_0 = 2, ORC_Q8_0 = 8, ORC_Q4_K = 12, ORC_Q6_K = 14 }; /* =
 #define ORC_SZ_Q8_1 36
 #define ORC_SZ_Q4_K 144
 #define ORC_SZ_Q8_K 292
+#define ORC_SZ_Q5_K 176   /* fp16 d, dmin; uint8 scales[12]; uint8 qh[32]; uint8 qs[128] (ggml-common.h:310-325) */
 #define ORC_SZ_Q6_K 210   /* uint8 ql[128]; uint8 qh[64]; int8 scales[16]; fp16 d (ggml-common.h:335-343) */
 
 uint16_t orc_fp32_to_fp16(float f);   /* ggml/src/ggml-impl.h ggml_compute_fp32_to_fp16 (IEEE RNE) */
@@ -49,12 +50,14 @@ void orc_quantize_row_q4_0(const float *x, void *y, int64_t k);  /* ggml-quants.
 void orc_dequantize_row_q4_0(const void *x, float *y, int64_t k); /* ggml-quants.c:307-325 */
 void orc_dequantize_row_q8_0(const void *x, float *y, int64_t k); /* ggml-quants.c:370-384 */
 void orc_dequantize_row_q4_K(const void *x, float *y, int64_t k); /* ggml-quants.c:1352-1373 */
+void orc_dequantize_row_q5_K(const void *x, float *y, int64_t k); /* ggml-quants.c dequantize_row_q5_K */
 void orc_dequantize_row_q6_K(const void *x, float *y, int64_t k); /* ggml-quants.c:1762-1791 */
 
 /* dot products, generic (scalar) versions */
 float orc_vec_dot_q4_0_q8_0(int64_t k, const void *vx, const void *vy); /* ggml-cpu/quants.c:115-150 */
 float orc_vec_dot_q8_0_q8_0(int64_t k, const void *vx, const void *vy); /* ggml-cpu/quants.c:305-333 */
 float orc_vec_dot_q4_K_q8_K(int64_t k, const void *vx, const void *vy); /* ggml-cpu/quants.c:550-623 */
+float orc_vec_dot_q5_K_q8_K(int64_t k, const void *vx, const void *vy); /* ggml-cpu/quants.c:625-703 */
 float orc_vec_dot_q6_K_q8_K(int64_t k, const void *vx, const void *vy); /* ggml-cpu/quants.c:705-758 */
 
 /* GGML_OP_MUL_MAT as ggml-cpu computes it (ggml-cpu.c:1202-1394, 1112-1200):

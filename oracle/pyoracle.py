@@ -21,10 +21,11 @@ import numpy as np
 HERE = Path(__file__).resolve().parent
 REF_DIR = HERE / "_ref"
 
-Q4_0, Q8_0, Q4_K, Q6_K = 2, 8, 12, 14   # enum ggml_type values (ggml/include/ggml.h:378-395)
+Q4_0, Q8_0, Q4_K, Q6_K = 2, 8, 12, 14
+Q5_K = 13   # enum ggml_type values (ggml/include/ggml.h:378-395)
 GGML_TYPE_Q8_1, GGML_TYPE_Q8_K = 9, 15
-TYPE_NAMES = {Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q6_K: "q6_K"}
-BLOCK = {Q4_0: (32, 18), Q8_0: (32, 34), Q4_K: (256, 144), Q6_K: (256, 210)}   # (elements, bytes)
+TYPE_NAMES = {Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q5_K: "q5_K", Q6_K: "q6_K"}
+BLOCK = {Q4_0: (32, 18), Q8_0: (32, 34), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210)}   # (elements, bytes)
 
 
 def row_size(t: int, k: int) -> int:
@@ -53,11 +54,11 @@ class Oracle:
             f = getattr(L, f"orc_quantize_row_{n}")
             f.restype = None
             f.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
-        for n in ("q4_0", "q8_0", "q4_K", "q6_K"):
+        for n in ("q4_0", "q8_0", "q4_K", "q5_K", "q6_K"):
             f = getattr(L, f"orc_dequantize_row_{n}")
             f.restype = None
             f.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
-        for n in ("q4_0_q8_0", "q8_0_q8_0", "q4_K_q8_K", "q6_K_q8_K"):
+        for n in ("q4_0_q8_0", "q8_0_q8_0", "q4_K_q8_K", "q5_K_q8_K", "q6_K_q8_K"):
             f = getattr(L, f"orc_vec_dot_{n}")
             f.restype = C.c_float
             f.argtypes = [C.c_int64, C.c_void_p, C.c_void_p]
@@ -98,7 +99,7 @@ class Oracle:
         return out
 
     def vec_dot(self, t: int, k: int, w_row: np.ndarray, a_row: np.ndarray) -> float:
-        n = {Q4_0: "q4_0_q8_0", Q8_0: "q8_0_q8_0", Q4_K: "q4_K_q8_K", Q6_K: "q6_K_q8_K"}[t]
+        n = {Q4_0: "q4_0_q8_0", Q8_0: "q8_0_q8_0", Q4_K: "q4_K_q8_K", Q5_K: "q5_K_q8_K", Q6_K: "q6_K_q8_K"}[t]
         return float(getattr(self.lib, f"orc_vec_dot_{n}")(k, _ptr(np.ascontiguousarray(w_row)), _ptr(np.ascontiguousarray(a_row))))
 
     def mul_mat(self, t: int, W: np.ndarray, X: np.ndarray, ne02: int = 1, ne03: int = 1) -> np.ndarray:
@@ -204,7 +205,7 @@ class RefQuant:
             f.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.ggml_quantize_chunk.restype = C.c_size_t
         L.ggml_quantize_chunk.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]
-        for n in ("q4_0", "q8_0", "q4_K", "q6_K"):
+        for n in ("q4_0", "q8_0", "q4_K", "q5_K", "q6_K"):
             f = getattr(L, f"dequantize_row_{n}")
             f.restype = None
             f.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
