@@ -35,6 +35,7 @@ typedef enum {
 #define B200_TYPE_Q4_0 2
 #define B200_TYPE_Q8_0 8
 #define B200_TYPE_Q4_K 12
+#define B200_TYPE_Q5_K 13   /* the Q5_K tensors of Q5_K_M / Q5_K_S files (src/llama-quant.cpp); 176-byte blocks: q4_K plus a fifth bit */
 #define B200_TYPE_Q6_K 14   /* the attn_v / ffn_down / output tensors of a Q4_K_M file (src/llama-quant.cpp:226,303,360-363) */
 
 /* which kernel family a MUL_MAT is routed to (b200_set_force_path / B200 env GGML_B200_FORCE) */

@@ -19,8 +19,9 @@ LIB_PATH = HERE / "libb200mm.so"
 BACKEND_PATH = HERE / "libggml-b200.so"
 
 Q4_0, Q8_0, Q4_K, Q6_K = 2, 8, 12, 14
-TYPE_NAMES = {Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q6_K: "q6_K"}
-BLOCK = {Q4_0: (32, 18), Q8_0: (32, 34), Q4_K: (256, 144), Q6_K: (256, 210)}
+Q5_K = 13
+TYPE_NAMES = {Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q5_K: "q5_K", Q6_K: "q6_K"}
+BLOCK = {Q4_0: (32, 18), Q8_0: (32, 34), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210)}
 PATH_AUTO, PATH_MMVQ, PATH_MMQ, PATH_SIMPLE = 0, 1, 2, 3
 
 EXPORTS = [

@@ -435,7 +435,7 @@ b200_status b200_quantize_units(b200_ctx * ctx, int kind, const float * x, int64
 
 // ------------------------------------------------------------------------------------------------ MUL_MAT
 
-static bool type_ok(int t) { return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q6_K; }
+static bool type_ok(int t) { return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K; }
 
 static size_t row_bytes(int type, int64_t k) { return (size_t) (k / type_block_elems(type)) * type_block_bytes(type); }
 

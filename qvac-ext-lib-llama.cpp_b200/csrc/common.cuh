@@ -17,6 +17,7 @@ constexpr int SZ_Q8_0 = 34;
 constexpr int SZ_Q8_1 = 36;
 constexpr int SZ_Q4_K = 144;
 constexpr int SZ_Q8_K = 292;
+constexpr int SZ_Q5_K = 176;  // half d, dmin; uint8 scales[12]; uint8 qh[32]; uint8 qs[128] (ggml-common.h:310-325): 11 x 16 B
 constexpr int SZ_Q6_K = 210;  // uint8 ql[128]; uint8 qh[64]; int8 scales[16]; half d (ggml-common.h:335-343): only 2-byte aligned
 
 // ---- "unit": 256 consecutive weights of one row. 8 q4_0 blocks and one q4_K block are both 144 bytes = 9 x 16 B,
@@ -25,11 +26,11 @@ constexpr int SZ_Q6_K = 210;  // uint8 ql[128]; uint8 qh[64]; int8 scales[16]; h
 constexpr int UNIT_ELEMS = 256;
 // A q6_K unit is its 210-byte block: NOT a multiple of 16 - units of a row are only 2-byte aligned in shared memory (the dot product
 // realigns them with funnel shifts), and a row slice is bulk-copyable only when it holds a multiple of 8 units (K % 2048 == 0).
-__host__ __device__ constexpr int unit_bytes(int type) { return type == B200_TYPE_Q8_0 ? 272 : type == B200_TYPE_Q6_K ? 210 : 144; }
-__host__ __device__ constexpr bool type_is_k(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q6_K; }
+__host__ __device__ constexpr int unit_bytes(int type) { return type == B200_TYPE_Q8_0 ? 272 : type == B200_TYPE_Q6_K ? 210 : type == B200_TYPE_Q5_K ? 176 : 144; }
+__host__ __device__ constexpr bool type_is_k(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K; }
 __host__ __device__ constexpr int type_block_elems(int type) { return type_is_k(type) ? 256 : 32; }
 __host__ __device__ constexpr int type_block_bytes(int type) {
-    return type == B200_TYPE_Q4_0 ? SZ_Q4_0 : type == B200_TYPE_Q8_0 ? SZ_Q8_0 : type == B200_TYPE_Q6_K ? SZ_Q6_K : SZ_Q4_K;
+    return type == B200_TYPE_Q4_0 ? SZ_Q4_0 : type == B200_TYPE_Q8_0 ? SZ_Q8_0 : type == B200_TYPE_Q6_K ? SZ_Q6_K : type == B200_TYPE_Q5_K ? SZ_Q5_K : SZ_Q4_K;
 }
 
 // ---- activation unit record (kernel-internal layout, written by quantize.cu, read by mmvq.cu / mmq)

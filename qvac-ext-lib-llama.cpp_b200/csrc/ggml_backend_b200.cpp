@@ -324,7 +324,7 @@ bool is_noop(const ggml_tensor * t) {
     return ggml_is_empty(t) || t->op == GGML_OP_NONE || t->op == GGML_OP_RESHAPE || t->op == GGML_OP_VIEW || t->op == GGML_OP_PERMUTE ||
            t->op == GGML_OP_TRANSPOSE;
 }
-bool weight_type_ok(ggml_type t) { return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q6_K; }
+bool weight_type_ok(ggml_type t) { return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q5_K || t == GGML_TYPE_Q6_K; }
 
 bool fill_mul_mat(const ggml_tensor * op, b200_mul_mat_desc * d) {
     const ggml_tensor * a = op->src[0], * b = op->src[1];

@@ -181,7 +181,8 @@ __global__ void __launch_bounds__(256) expand_f16_kernel(const uint8_t * __restr
             v[l] = __fmul_rn(__fmul_rn(d, (float) (int) sc[l >> 4]), (float) q);  // d * sc * q, left to right (ggml-quants.c:1780-1783)
         }
     } else {
-        const uint8_t * b = wr + (kb >> 3) * SZ_Q4_K;
+        constexpr bool Q5 = TYPE == B200_TYPE_Q5_K;  // q4_K's layout with 32 bytes of fifth bits behind the header (dequantize_row_q5_K)
+        const uint8_t * b = wr + (kb >> 3) * (Q5 ? SZ_Q5_K : SZ_Q4_K);
         const int j = (int) (kb & 7);
         const uint32_t hdr = *(const uint32_t *) b;
         const float d = half_bits_to_float((uint16_t) (hdr & 0xffff)), dmin = half_bits_to_float((uint16_t) (hdr >> 16));
@@ -195,14 +196,24 @@ __global__ void __launch_bounds__(256) expand_f16_kernel(const uint8_t * __restr
             mv  = (s[j + 4] >> 4) | ((s[j] >> 6) << 4);
         }
         const float d1 = __fmul_rn(d, (float) scv), m1 = __fmul_rn(dmin, (float) mv);  // dequantize_row_q4_K: y = d1 * q - m1
-        const uint4 * qs = (const uint4 *) (b + 16 + 32 * (j >> 1));
+        const uint4 * qs = (const uint4 *) (b + (Q5 ? 48 : 16) + 32 * (j >> 1));
         const uint4 a = qs[0], c = qs[1];
         const uint32_t x[8] = { a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w };
+        uint32_t hb[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+        if (Q5) {
+            const uint4 ha = ((const uint4 *) (b + 16))[0], hc = ((const uint4 *) (b + 16))[1];
+            const uint32_t hw[8] = { ha.x, ha.y, ha.z, ha.w, hc.x, hc.y, hc.z, hc.w };
+#pragma unroll
+            for (int i = 0; i < 8; i++) hb[i] = hw[i] >> j;  // bit j of qh[l] -> bit 0 of byte l
+        }
         const int sh = (j & 1) ? 4 : 0;
 #pragma unroll
         for (int i = 0; i < 8; i++) {
 #pragma unroll
-            for (int l = 0; l < 4; l++) v[4 * i + l] = __fsub_rn(__fmul_rn(d1, (float) ((x[i] >> (8 * l + sh)) & 0xf)), m1);
+            for (int l = 0; l < 4; l++) {
+                const int q = (int) ((x[i] >> (8 * l + sh)) & 0xf) + (int) (((hb[i] >> (8 * l)) & 1) << 4);
+                v[4 * i + l] = __fsub_rn(__fmul_rn(d1, (float) q), m1);
+            }
         }
     }
     uint4 * dst = (uint4 *) (h + row * K + kb * 32);

@@ -85,7 +85,7 @@ b200_status b200_mm_ids_sort(b200_ctx * ctx, const int32_t * ids, int64_t n_used
 
 int b200_mul_mat_id_supported(const b200_mul_mat_id_desc * d) {
     if (!d) return 0;
-    if (d->type != B200_TYPE_Q4_0 && d->type != B200_TYPE_Q8_0 && d->type != B200_TYPE_Q4_K && d->type != B200_TYPE_Q6_K) return 0;
+    if (d->type != B200_TYPE_Q4_0 && d->type != B200_TYPE_Q8_0 && d->type != B200_TYPE_Q4_K && d->type != B200_TYPE_Q5_K && d->type != B200_TYPE_Q6_K) return 0;
     if (d->ne00 <= 0 || d->ne00 % type_block_elems(d->type) != 0) return 0;
     if (d->ne01 < 0 || d->n_as <= 0 || d->ne11 <= 0 || d->n_tok < 0 || d->n_used <= 0) return 0;
     if (d->nb01 < (size_t) (d->ne00 / type_block_elems(d->type)) * type_block_bytes(d->type)) return 0;

@@ -676,6 +676,7 @@ b200_status wentry_fill(b200_ctx * ctx, WEntry * e, const void * src, uint8_t * 
         switch (e->type) {
             case B200_TYPE_Q4_0: expand_f16_kernel<B200_TYPE_Q4_0><<<grid, 256, 0, ctx->stream>>>((const uint8_t *) src, (int64_t) e->nb01, M, K, h); break;
             case B200_TYPE_Q8_0: expand_f16_kernel<B200_TYPE_Q8_0><<<grid, 256, 0, ctx->stream>>>((const uint8_t *) src, (int64_t) e->nb01, M, K, h); break;
+            case B200_TYPE_Q5_K: expand_f16_kernel<B200_TYPE_Q5_K><<<grid, 256, 0, ctx->stream>>>((const uint8_t *) src, (int64_t) e->nb01, M, K, h); break;
             case B200_TYPE_Q6_K: expand_f16_kernel<B200_TYPE_Q6_K><<<grid, 256, 0, ctx->stream>>>((const uint8_t *) src, (int64_t) e->nb01, M, K, h); break;
             default:             expand_f16_kernel<B200_TYPE_Q4_K><<<grid, 256, 0, ctx->stream>>>((const uint8_t *) src, (int64_t) e->nb01, M, K, h); break;
         }
@@ -751,7 +752,7 @@ size_t b200_weight_cache_bytes(void) {
 bool b200_mmq_usable(int type, int64_t K, const void * w, size_t nb01) {
     (void) type;
     if (K % 32 != 0 || K < 32) return false;
-    if (type == B200_TYPE_Q4_K && ((uintptr_t) w % 16 != 0 || nb01 % 16 != 0)) return false;
+    if ((type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K) && ((uintptr_t) w % 16 != 0 || nb01 % 16 != 0)) return false;
     if (type_is_k(type) && K % 256 != 0) return false;
     if ((uintptr_t) w % 2 != 0 || nb01 % 2 != 0) return false;
     return get_encode() != nullptr;
@@ -769,7 +770,7 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
     // ---- activations: int8 [N][K] + scales [KB][Np] (+ sums) in scratch2
     const size_t aq = ((size_t) N * K + 255) & ~(size_t) 255;
     const size_t as = (((size_t) KB * Np * 4) + 255) & ~(size_t) 255;
-    const bool   f16 = ctx->mmq_f16 != 0 || type == B200_TYPE_Q6_K;  // q6_K has no exact kind::i8 kernel: always the kind::f16 GEMM
+    const bool   f16 = ctx->mmq_f16 != 0 || type == B200_TYPE_Q6_K || type == B200_TYPE_Q5_K;  // q5_K / q6_K have no exact kind::i8 kernel: always the kind::f16 GEMM
     const size_t hb  = ((size_t) N * K * 2 + 255) & ~(size_t) 255;   // fp16 activations [N][K] + 2^e[n]
     const size_t rb  = ((size_t) N * 4 + 255) & ~(size_t) 255;
     const size_t act_bytes = f16 ? hb + rb : aq + as * (has_min ? 2 : 1);
@@ -912,7 +913,7 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
 // matrix's fp16 expansion must be alive at the same time); returns B200_ERR_UNSUPPORTED when the caller should loop instead.
 b200_status b200_mmq_run_group(b200_ctx * ctx, int type, int n_ops, const void * const * ws, const size_t * nb01s, const int64_t * Ms, int64_t K,
                                const float * x, size_t x_rs, int64_t N, float * const * dsts, const int64_t * ldcs) {
-    if ((!ctx->mmq_f16 && type != B200_TYPE_Q6_K) || !ctx->weight_cache || n_ops < 2 || n_ops > F_MAX_MATS || N <= 0) return B200_ERR_UNSUPPORTED;
+    if ((!ctx->mmq_f16 && type != B200_TYPE_Q6_K && type != B200_TYPE_Q5_K) || !ctx->weight_cache || n_ops < 2 || n_ops > F_MAX_MATS || N <= 0) return B200_ERR_UNSUPPORTED;
     for (int i = 0; i < n_ops; i++) if (Ms[i] <= 0 || Ms[i] > INT32_MAX - BM || N > INT32_MAX - BN || K > INT32_MAX - 128) return B200_ERR_UNSUPPORTED;
     static const int env_group = mmf_env("GGML_B200_MMF_GROUP", 1);
     if (!env_group) return B200_ERR_UNSUPPORTED;

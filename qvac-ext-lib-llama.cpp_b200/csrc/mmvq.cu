@@ -188,6 +188,73 @@ __device__ __forceinline__ void unit_dot_q8_0(uint32_t w, uint32_t am, uint32_t 
     });
 }
 
+// q5_K: q4_K's unit with 32 bytes of fifth bits between the header and the nibbles (176 B = 11 x 16 B, lane stride 44 words == 12 mod
+// 32: conflict free for 128-bit loads). Sub-block 2g takes the low nibbles of qs[32 g + l] and bit 2g of qh[l], sub-block 2g + 1 the
+// high nibbles and bit 2g + 1 (ggml-cpu/quants.c:655-669): the bit is moved to bit 4 of the byte and OR-ed in, u8 x s8 dp4a as for q4_K.
+template <int NC>
+__device__ __forceinline__ void unit_dot_q5_K(uint32_t w, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc)[NC]) {
+    const uint4 hdr = lds128o<0>(w);
+    const float d    = half_bits_to_float((uint16_t) (hdr.x & 0xffff));
+    const float dmin = half_bits_to_float((uint16_t) (hdr.x >> 16));
+    const uint32_t sc_lo = hdr.y & 0x3f3f3f3fu;
+    const uint32_t mn_lo = hdr.z & 0x3f3f3f3fu;
+    const uint32_t sc_hi = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
+    const uint32_t mn_hi = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
+    const uint4 ha = lds128o<16>(w), hb = lds128o<32>(w);
+    const uint32_t H[8] = { ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w };
+
+    int      isum[NC];
+    uint32_t ac[NC];
+#pragma unroll
+    for (int c = 0; c < NC; c++) {
+        isum[c] = 0;
+        ac[c]   = am + c * cs_m;
+    }
+
+    static_for<0, 4>([&](auto gi) {
+        constexpr int g = decltype(gi)::value;
+        const uint4 qa = lds128o<48 + 32 * g>(w);
+        const uint4 qb = lds128o<64 + 32 * g>(w);
+        const uint32_t q[8] = { qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w };
+        uint32_t vl[8], vh[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {  // bit 2g -> bit 4 of the low value, bit 2g + 1 -> bit 4 of the high value
+            const uint32_t bl = g == 0 ? H[k] << 4 : g == 1 ? H[k] << 2 : g == 2 ? H[k] : H[k] >> 2;
+            const uint32_t bh = g == 0 ? H[k] << 3 : g == 1 ? H[k] << 1 : g == 2 ? H[k] >> 1 : H[k] >> 3;
+            vl[k] = (q[k] & 0x0f0f0f0fu) | (bl & 0x10101010u);
+            vh[k] = ((q[k] >> 4) & 0x0f0f0f0fu) | (bh & 0x10101010u);
+        }
+        const uint32_t scw  = g < 2 ? sc_lo : sc_hi;
+        const int      s0   = (scw >> (16 * (g & 1))) & 0xff;
+        const int      s1   = (scw >> (16 * (g & 1) + 8)) & 0xff;
+#pragma unroll
+        for (int c = 0; c < NC; c++) {
+            const uint4 l0 = lds128o<64 * g>(ac[c]), l1 = lds128o<64 * g + 16>(ac[c]), h0 = lds128o<64 * g + 32>(ac[c]),
+                        h1 = lds128o<64 * g + 48>(ac[c]);
+            const int lo[8] = { (int) l0.x, (int) l0.y, (int) l0.z, (int) l0.w, (int) l1.x, (int) l1.y, (int) l1.z, (int) l1.w };
+            const int hi[8] = { (int) h0.x, (int) h0.y, (int) h0.z, (int) h0.w, (int) h1.x, (int) h1.y, (int) h1.z, (int) h1.w };
+            int sl = 0, sh = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                sl = dp4a_us(vl[k], lo[k], sl);
+                sh = dp4a_us(vh[k], hi[k], sh);
+            }
+            isum[c] += s0 * sl + s1 * sh;
+        }
+    });
+#pragma unroll
+    for (int c = 0; c < NC; c++) {
+        const uint4 bs = lds128o<256>(ac[c]);  // int16 sum of q per 32-block (x8)
+        int imin = dp2a_lo_su((int) bs.x, mn_lo, 0);
+        imin     = dp2a_hi_su((int) bs.y, mn_lo, imin);
+        imin     = dp2a_lo_su((int) bs.z, mn_hi, imin);
+        imin     = dp2a_hi_su((int) bs.w, mn_hi, imin);
+        const float dy = __uint_as_float(lds32(ax + c * cs_x));
+        acc[c] = fmaf(d * dy, (float) isum[c], acc[c]);
+        acc[c] = fmaf(-(dmin * dy), (float) imin, acc[c]);
+    }
+}
+
 // q6_K: { uint8 ql[128]; uint8 qh[64]; int8 scales[16]; half d } = 210 bytes, so a lane's unit is only 2-byte aligned in shared
 // memory: every run of words is read as aligned 32-bit words and realigned with a funnel shift by 0 or 16 bits (lane dependent).
 // Weight l of a 128-half: nibbles of ql[l] / ql[l + 32] plus two bits of qh[l], minus 32 (ggml-quants.c:1762-1791). The two
@@ -256,6 +323,7 @@ __device__ __forceinline__ void unit_dot_q6_K(uint32_t w, uint32_t am, uint32_t 
 template <int TYPE, int NC>
 __device__ __forceinline__ void unit_dot(uint32_t w, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc)[NC]) {
     if (TYPE == B200_TYPE_Q6_K) unit_dot_q6_K<NC>(w, am, ax, cs_m, cs_x, acc);
+    else if (TYPE == B200_TYPE_Q5_K) unit_dot_q5_K<NC>(w, am, ax, cs_m, cs_x, acc);
     else if (TYPE == B200_TYPE_Q4_K) unit_dot_q4_K<NC>(w, am, ax, cs_m, cs_x, acc);
     else if (TYPE == B200_TYPE_Q4_0) unit_dot_q4_0<NC>(w, am, ax, cs_m, cs_x, acc);
     else unit_dot_q8_0<NC>(w, am, ax, cs_m, cs_x, acc);
@@ -675,6 +743,7 @@ cudaError_t mv_fast_launch(int type, int ncols, const MvParams & p, int n_ctas, 
         case B200_TYPE_Q4_0: return mv_fast_launch_n<B200_TYPE_Q4_0>(ncols, p, n_ctas, n_pairs, smem, st);
         case B200_TYPE_Q8_0: return mv_fast_launch_n<B200_TYPE_Q8_0>(ncols, p, n_ctas, n_pairs, smem, st);
         case B200_TYPE_Q4_K: return mv_fast_launch_n<B200_TYPE_Q4_K>(ncols, p, n_ctas, n_pairs, smem, st);
+        case B200_TYPE_Q5_K: return mv_fast_launch_n<B200_TYPE_Q5_K>(ncols, p, n_ctas, n_pairs, smem, st);
         case B200_TYPE_Q6_K: return mv_fast_launch_n<B200_TYPE_Q6_K>(ncols, p, n_ctas, n_pairs, smem, st);
     }
     return cudaErrorInvalidValue;
@@ -733,9 +802,10 @@ __global__ void __launch_bounds__(128) mv_simple_kernel(const MvSimpleParams p) 
             }
             acc = fmaf(d * dy, (float) isum, acc);
         }
-    } else if (TYPE == B200_TYPE_Q4_K) {
+    } else if (TYPE == B200_TYPE_Q4_K || TYPE == B200_TYPE_Q5_K) {
+        constexpr bool Q5 = TYPE == B200_TYPE_Q5_K;  // 32 bytes of fifth bits between the header and the nibbles
         for (int b = lane; b < p.K / QK_K; b += 32) {
-            const uint8_t * wb = wr + (int64_t) b * SZ_Q4_K;
+            const uint8_t * wb = wr + (int64_t) b * (Q5 ? SZ_Q5_K : SZ_Q4_K);
             const uint8_t * ab = ar + (int64_t) b * SZ_Q8_K;
             const uint32_t  h0 = ld16x2(wb), u0 = ld16x2(wb + 4), u1 = ld16x2(wb + 8), u2 = ld16x2(wb + 12);
             const float d = half_bits_to_float((uint16_t) (h0 & 0xffff)), dmin = half_bits_to_float((uint16_t) (h0 >> 16));
@@ -748,12 +818,17 @@ __global__ void __launch_bounds__(128) mv_simple_kernel(const MvSimpleParams p) 
             for (int s = 0; s < 8; s++) {
                 const int sc = (sc4[s >> 2] >> (8 * (s & 3))) & 0xff, mn = (mn4[s >> 2] >> (8 * (s & 3))) & 0xff;
                 imin += mn * (bs[2 * s] + bs[2 * s + 1]);
-                const uint8_t * qq = wb + 16 + 32 * (s >> 1);
+                const uint8_t * qq = wb + (Q5 ? 48 : 16) + 32 * (s >> 1);
                 int dot = 0;
                 for (int l = 0; l < 32; l += 2) {
                     const uint16_t two = *(const uint16_t *) (qq + l);
-                    const int w0 = (s & 1) ? (two >> 4) & 0xf : two & 0xf;
-                    const int w1 = (s & 1) ? (two >> 12) & 0xf : (two >> 8) & 0xf;
+                    int w0 = (s & 1) ? (two >> 4) & 0xf : two & 0xf;
+                    int w1 = (s & 1) ? (two >> 12) & 0xf : (two >> 8) & 0xf;
+                    if (Q5) {
+                        const uint16_t hb = *(const uint16_t *) (wb + 16 + l);
+                        w0 += ((hb >> s) & 1) << 4;
+                        w1 += ((hb >> (8 + s)) & 1) << 4;
+                    }
                     dot += w0 * q8[32 * s + l] + w1 * q8[32 * s + l + 1];
                 }
                 isum += sc * dot;
@@ -798,6 +873,7 @@ cudaError_t mv_simple_launch(int type, const MvSimpleParams & p, cudaStream_t st
         case B200_TYPE_Q4_0: mv_simple_kernel<B200_TYPE_Q4_0><<<grid, 128, 0, st>>>(p); break;
         case B200_TYPE_Q8_0: mv_simple_kernel<B200_TYPE_Q8_0><<<grid, 128, 0, st>>>(p); break;
         case B200_TYPE_Q4_K: mv_simple_kernel<B200_TYPE_Q4_K><<<grid, 128, 0, st>>>(p); break;
+        case B200_TYPE_Q5_K: mv_simple_kernel<B200_TYPE_Q5_K><<<grid, 128, 0, st>>>(p); break;
         case B200_TYPE_Q6_K: mv_simple_kernel<B200_TYPE_Q6_K><<<grid, 128, 0, st>>>(p); break;
         default: return cudaErrorInvalidValue;
     }

@@ -89,6 +89,28 @@ def main_q6k():
     print("q6_K golden fixtures written to", OUT)
 
 
+def main_q5k():
+    """the q5_K fixtures (own seed: the earlier files stay byte-identical)"""
+    from oracle.pyoracle import Q5_K
+    rq, h = RefQuant(), RefHarness.get()
+    cpu = h.cpu("x64")
+    rng = np.random.default_rng(20261107)
+    t = Q5_K
+    for (M, K, N) in ((48, 1024, 5), (19, 256, 2)):
+        W = rq.quantize_weights(t, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+        X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+        out, _ = h.mul_mat(cpu, t, W, X, n_threads=1)
+        np.savez_compressed(OUT / f"mul_mat_{TYPE_NAMES[t]}_{M}x{K}x{N}.npz", type=t, W=W, X=X, out=out, w_f32=np.zeros(0))
+    n_as, M, K, n_used, n_tok = 4, 32, 512, 2, 5
+    W = rq.quantize_weights(t, rng.uniform(-1, 1, (n_as * M, K)).astype(np.float32)).reshape(n_as, M, -1)
+    B = rng.uniform(-1, 1, (n_tok, 1, K)).astype(np.float32)
+    ids = np.stack([rng.permutation(n_as)[:n_used] for _ in range(n_tok)]).astype(np.int32)
+    out, _ = h.mul_mat_id(cpu, t, W, B, ids, n_threads=1)
+    np.savez_compressed(OUT / f"mul_mat_id_{TYPE_NAMES[t]}_b1.npz", type=t, W=W, B=B, ids=ids, out=out)
+    np.savez(OUT / "weight_slabs_q5_K.npz", q5_K=rq.quantize_weights(t, rng.uniform(-1, 1, (2048, 256)).astype(np.float32)))
+    print("q5_K golden fixtures written to", OUT)
+
+
 def main_fusion():
     """K7 fixtures: the fused patterns of test_mul_mat_vec_fusion (tests/test-backend-ops.cpp:5120-5249) run as whole graphs on the
     reference's ggml-cpu (x64 generic build). Own seed: the earlier files stay byte-identical."""
@@ -127,4 +149,4 @@ def main_fusion():
 
 
 if __name__ == "__main__":
-    main_fusion() if "--fusion" in sys.argv else main_q6k() if "--q6k" in sys.argv else main()
+    main_q5k() if "--q5k" in sys.argv else main_fusion() if "--fusion" in sys.argv else main_q6k() if "--q6k" in sys.argv else main()

@@ -8,7 +8,7 @@ import subprocess
 import numpy as np
 import pytest
 
-from oracle.pyoracle import Q4_0, Q4_K, Q6_K, Q8_0, REF_DIR, have_ref
+from oracle.pyoracle import Q4_0, Q4_K, Q5_K, Q6_K, Q8_0, REF_DIR, have_ref
 
 pytestmark = pytest.mark.gpu
 
@@ -20,7 +20,7 @@ def b200(pkg, harness):
     return harness.load(pkg.BACKEND_PATH)
 
 
-@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q6_K])
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q5_K, Q6_K])
 @pytest.mark.parametrize("M,K,N", [(64, 256, 1), (128, 1024, 4), (96, 4096, 1), (50, 512, 33)])
 def test_backend_mul_mat_matches_ggml_cpu(harness, refq, oracle, b200, t, M, K, N):
     rng = np.random.default_rng(M + K + N + t)

@@ -7,7 +7,7 @@ from pathlib import Path
 import numpy as np
 import pytest
 
-from oracle.pyoracle import Q4_0, Q4_K, Q6_K, Q8_0, TYPE_NAMES, have_ref
+from oracle.pyoracle import Q4_0, Q4_K, Q5_K, Q6_K, Q8_0, TYPE_NAMES, have_ref
 
 pytestmark = pytest.mark.gpu
 GOLD = Path(__file__).resolve().parent / "golden"
@@ -25,7 +25,7 @@ def quantize_weights(oracle, t, w):
     if have_ref():
         from oracle.pyoracle import RefQuant
         return RefQuant().quantize_weights(t, w)
-    if t in (Q4_K, Q6_K):
+    if t in (Q4_K, Q5_K, Q6_K):
         pytest.skip("K-quant weights need oracle/_ref")
     return oracle.quantize("q4_0" if t == Q4_0 else "q8_0", w)
 
@@ -129,7 +129,7 @@ SHAPES = [  # (M, K): K/256 = 1, 2, 3 (L=4, one idle lane group), 16 (two rows p
 ]
 
 
-@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q6_K])
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q5_K, Q6_K])
 @pytest.mark.parametrize("M,K", SHAPES)
 @pytest.mark.parametrize("N", [1, 2, 5, 8])
 def test_mul_mat_vs_oracle(ctx, oracle, t, M, K, N):
@@ -163,7 +163,7 @@ def test_generic_kernel_for_k_not_multiple_of_256(ctx, oracle, t, K):
     assert oracle.nmse(oracle.mul_mat(t, W, X), got) <= NMSE_TIGHT
 
 
-@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q6_K])
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q5_K, Q6_K])
 def test_fast_and_generic_kernels_agree(ctx, pkg, oracle, t):
     """two independent CUDA implementations of the same integer arithmetic"""
     rng = np.random.default_rng(3 + t)
@@ -273,7 +273,7 @@ def test_decode_weight_prefetch_changes_nothing(pkg, oracle, t):
 
 # ---------------------------------------------------------------- K5/K6
 
-@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q6_K])
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q5_K, Q6_K])
 @pytest.mark.parametrize("n_as,n_used,bcast,n_tok", [(4, 1, 1, 1), (8, 2, 1, 1), (8, 4, 0, 5), (4, 2, 1, 17), (8, 2, 0, 32)])
 def test_mul_mat_id_vs_oracle(ctx, oracle, t, n_as, n_used, bcast, n_tok):
     """the shapes of the reference's own cases (tests/test-backend-ops.cpp:7394-7407: m=512, k=256), scaled down in m"""
@@ -284,6 +284,53 @@ def test_mul_mat_id_vs_oracle(ctx, oracle, t, n_as, n_used, bcast, n_tok):
     ids = np.stack([rng.permutation(n_as)[:n_used] for _ in range(n_tok)]).astype(np.int32)
     got = ctx.mul_mat_id(t, cu(W), cu(B), cu(ids)).cpu().numpy()
     assert oracle.nmse(oracle.mul_mat_id(t, W, B, ids), got) <= NMSE_TIGHT
+
+
+# ---------------------------------------------------------------- q5_K (second half: Q5_K_M / Q5_K_S files)
+
+@pytest.mark.parametrize("M,K,N", [(96, 256, 1), (200, 1024, 3), (130, 4096, 1), (64, 4096, 2), (40, 4096, 8), (33, 14336, 1), (257, 1280, 5)])
+def test_q5_K_decode(ctx, pkg, oracle, M, K, N):
+    """176-byte blocks (q4_K + 32 bytes of fifth bits) are 16-byte multiples: the TMA-staged kernel takes any K % 256 == 0; all column
+    counts up to 8 run the dp4a kernel (no tensor-core mat-vec for q5_K), so column c of an N-column call is bit-identical to the 1-column call"""
+    rng = np.random.default_rng(M + K + N + 5)
+    W = quantize_weights(oracle, Q5_K, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = (rng.standard_normal((N, K)) * rng.choice([0.05, 1.0, 20.0], (N, 1))).astype(np.float32)
+    got = ctx.mul_mat(Q5_K, cu(W), cu(X)).cpu().numpy()
+    assert oracle.nmse(oracle.mul_mat(Q5_K, W, X), got) <= NMSE_TIGHT
+    if N > 1:
+        one = ctx.mul_mat(Q5_K, cu(W), cu(X[1:2])).cpu().numpy()
+        assert np.array_equal(one[0], got[1])
+    ctx.force_path(pkg.PATH_SIMPLE)
+    gen = ctx.mul_mat(Q5_K, cu(W), cu(X)).cpu().numpy()
+    ctx.force_path(pkg.PATH_AUTO)
+    assert oracle.nmse(gen, got) <= 1e-12
+
+
+@pytest.mark.parametrize("N", [9, 40, 300])
+def test_q5_K_prefill(ctx, oracle, N):
+    """more than 8 columns: weights expanded to fp16 (dequantize_row_q5_K values), the kind::f16 GEMM - q5_K has no kind::i8 kernel"""
+    rng = np.random.default_rng(N + 5)
+    M, K = 300, 1024
+    W = quantize_weights(oracle, Q5_K, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+    X = (rng.standard_normal((N, K)) * rng.choice([0.01, 1.0, 30.0], (N, 1))).astype(np.float32)
+    for f16 in (True, False):   # the switch does not apply to q5_K
+        ctx.mmq_f16(f16)
+        got = ctx.mul_mat(Q5_K, cu(W), cu(X)).cpu().numpy()
+        assert oracle.nmse(oracle.mul_mat(Q5_K, W, X), got) <= NMSE_F16
+    ctx.mmq_f16(True)
+
+
+def test_q5_K_shared_src1_and_fused_glu(ctx, oracle):
+    rng = np.random.default_rng(55)
+    K = 2048
+    Ws = [quantize_weights(oracle, Q5_K, rng.uniform(-1, 1, (m, K)).astype(np.float32)) for m in (64, 17, 130)]
+    X = rng.uniform(-1, 1, (2, K)).astype(np.float32)
+    outs = ctx.mul_mat_shared(Q5_K, [cu(w) for w in Ws], cu(X))
+    for w, o in zip(Ws, outs):
+        assert oracle.nmse(oracle.mul_mat(Q5_K, w, X), o.cpu().numpy()) <= NMSE_TIGHT
+    Wg = quantize_weights(oracle, Q5_K, rng.uniform(-1, 1, (130, K)).astype(np.float32))
+    got = ctx.mul_mat_fused(Q5_K, cu(Ws[2]), cu(Wg), cu(X[:1]), glu_op=2).cpu().numpy()
+    assert oracle.nmse(oracle.mul_mat_glu(Q5_K, Ws[2], Wg, X[:1], glu_op=2), got) <= NMSE_TIGHT
 
 
 # ---------------------------------------------------------------- q6_K (SURVEY 8f rank 2: the Q6_K tensors of a Q4_K_M file)

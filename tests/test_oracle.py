@@ -6,7 +6,7 @@ from pathlib import Path
 import numpy as np
 import pytest
 
-from oracle.pyoracle import Q4_0, Q4_K, Q6_K, Q8_0, TYPE_NAMES, row_size
+from oracle.pyoracle import Q4_0, Q4_K, Q5_K, Q6_K, Q8_0, TYPE_NAMES, row_size
 
 GOLD = Path(__file__).resolve().parent / "golden"
 
@@ -81,7 +81,7 @@ def test_quantizers_vs_ref(oracle, refq, seed):
         assert np.array_equal(a, b), name
 
 
-@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q6_K])
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q5_K, Q6_K])
 def test_dequant_and_mul_mat_vs_ref(oracle, refq, harness, t):
     rng = np.random.default_rng(100 + t)
     M, K, N = 40, 768, 7
@@ -96,7 +96,7 @@ def test_dequant_and_mul_mat_vs_ref(oracle, refq, harness, t):
     assert oracle.nmse(fast, mine) < 1e-9
 
 
-@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q6_K])
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q5_K, Q6_K])
 def test_mul_mat_id_vs_ref(oracle, refq, harness, t):
     rng = np.random.default_rng(200 + t)
     n_as, M, K, n_used, n_tok = 8, 24, 512, 4, 9
