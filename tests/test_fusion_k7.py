@@ -11,7 +11,7 @@ from pathlib import Path
 import numpy as np
 import pytest
 
-from oracle.pyoracle import Q4_0, Q4_K, Q5_K, Q6_K, Q8_0, TYPE_NAMES, have_ref
+from oracle.pyoracle import Q4_0, Q4_K, Q6_K, Q8_0, TYPE_NAMES, have_ref
 
 GOLD = Path(__file__).resolve().parent / "golden"
 # ggml-cpu evaluates GEGLU / GEGLU_QUICK through fp16 tables and SWIGLU through a polynomial expf (vec.h:1326-1340, vec.cpp:376-410);
@@ -24,7 +24,7 @@ GLU_NAMES = {0: "reglu", 1: "geglu", 2: "swiglu", 3: "swiglu_oai", 4: "geglu_erf
 
 # ---------------------------------------------------------------- oracle vs the reference (CPU)
 
-@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q5_K, Q6_K])
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q6_K])
 def test_oracle_fused_patterns_vs_golden(oracle, t):
     g = np.load(GOLD / "fusion_k7.npz")
     tn = TYPE_NAMES[t]
@@ -76,7 +76,7 @@ def cu(a):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q5_K, Q6_K])
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q6_K])
 def test_fused_mul_mat_golden(ctx, oracle, pkg, t):
     g = np.load(GOLD / "fusion_k7.npz")
     tn = TYPE_NAMES[t]
