@@ -277,7 +277,7 @@ float orc_vec_dot_q4_K_q8_K(int64_t k, const void *vx, const void *vy) {
     return sumf;
 }
 
-/* block_q5_K = { fp16 d, dmin; uint8 scales[12]; uint8 qh[32]; uint8 qs[128] } (ggml-common.h:310-325): q4_K's layout plus a fifth
+/* block_q5_K = { fp16 d, dmin; uint8 scales[12]; uint8 qh[32]; uint8 qs[128] } (ggml-common.h:312-323): q4_K's layout plus a fifth
  * bit: sub-block s (32 weights) takes the low (s even) / high (s odd) nibbles of qs[32*(s/2) + l] and bit s of qh[l]
  * (dequantize_row_q5_K, ggml-quants.c; vec_dot: ggml-cpu/quants.c:625-703, same lane structure as q4_K) */
 void orc_dequantize_row_q5_K(const void *vx, float *y, int64_t k) {

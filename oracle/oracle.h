@@ -30,7 +30,7 @@ enum orc_type { ORC_Q4_0 = 2, ORC_Q8_0 = 8, ORC_Q4_K = 12, ORC_Q5_K = 13, ORC_Q6
 #define ORC_SZ_Q8_1 36
 #define ORC_SZ_Q4_K 144
 #define ORC_SZ_Q8_K 292
-#define ORC_SZ_Q5_K 176   /* fp16 d, dmin; uint8 scales[12]; uint8 qh[32]; uint8 qs[128] (ggml-common.h:310-325) */
+#define ORC_SZ_Q5_K 176   /* fp16 d, dmin; uint8 scales[12]; uint8 qh[32]; uint8 qs[128] (ggml-common.h:312-323) */
 #define ORC_SZ_Q6_K 210   /* uint8 ql[128]; uint8 qh[64]; int8 scales[16]; fp16 d (ggml-common.h:335-343) */
 
 uint16_t orc_fp32_to_fp16(float f);   /* ggml/src/ggml-impl.h ggml_compute_fp32_to_fp16 (IEEE RNE) */

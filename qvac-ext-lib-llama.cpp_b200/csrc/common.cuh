@@ -17,7 +17,7 @@ constexpr int SZ_Q8_0 = 34;
 constexpr int SZ_Q8_1 = 36;
 constexpr int SZ_Q4_K = 144;
 constexpr int SZ_Q8_K = 292;
-constexpr int SZ_Q5_K = 176;  // half d, dmin; uint8 scales[12]; uint8 qh[32]; uint8 qs[128] (ggml-common.h:310-325): 11 x 16 B
+constexpr int SZ_Q5_K = 176;  // half d, dmin; uint8 scales[12]; uint8 qh[32]; uint8 qs[128] (ggml-common.h:312-323): 11 x 16 B
 constexpr int SZ_Q6_K = 210;  // uint8 ql[128]; uint8 qh[64]; int8 scales[16]; half d (ggml-common.h:335-343): only 2-byte aligned
 
 // ---- "unit": 256 consecutive weights of one row. 8 q4_0 blocks and one q4_K block are both 144 bytes = 9 x 16 B,
