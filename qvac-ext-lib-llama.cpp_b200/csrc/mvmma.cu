@@ -120,6 +120,52 @@ __device__ __forceinline__ void unit_mma_q4_K(uint32_t wt, uint32_t am, uint32_t
     acc[3] = fmaf(d1 * dy1, (float) isum[3], acc[3]); acc[3] = fmaf(-(m1 * dy1), (float) mdot(bs1, mn1), acc[3]);
 }
 
+// q5_K: q4_K's unit with the fifth bits at +16 and the nibbles at +48 (176 B, row pitch 44 words == 12 mod 32: the 8 rows x 4 words of a
+// fragment load still fall into 32 different banks). Sub-block j takes bit j of qh[l]: moved to bit 4 and OR-ed onto the nibble.
+__device__ __forceinline__ void unit_mma_q5_K(uint32_t wt, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, int g, int t, float (&acc)[4]) {
+    const uint32_t r0 = wt + g * 176, r1 = r0 + 8 * 176;
+    const uint4 h0 = lds128(r0), h1 = lds128(r1);
+    const uint32_t sc0[2] = { h0.y & 0x3f3f3f3fu, (h0.w & 0x0f0f0f0fu) | ((h0.y >> 2) & 0x30303030u) };
+    const uint32_t mn0[2] = { h0.z & 0x3f3f3f3fu, ((h0.w >> 4) & 0x0f0f0f0fu) | ((h0.z >> 2) & 0x30303030u) };
+    const uint32_t sc1[2] = { h1.y & 0x3f3f3f3fu, (h1.w & 0x0f0f0f0fu) | ((h1.y >> 2) & 0x30303030u) };
+    const uint32_t mn1[2] = { h1.z & 0x3f3f3f3fu, ((h1.w >> 4) & 0x0f0f0f0fu) | ((h1.z >> 2) & 0x30303030u) };
+    // fifth bits of l = 4t .. 4t + 3 (k-half 0) and l = 16 + 4t .. (k-half 1), rows g and g + 8
+    const uint32_t qa0 = lds32(r0 + 16 + 4 * t), qb0 = lds32(r0 + 32 + 4 * t), qa1 = lds32(r1 + 16 + 4 * t), qb1 = lds32(r1 + 32 + 4 * t);
+    const uint32_t bcol = am + g * cs_m + 4 * t;
+    int isum[4] = { 0, 0, 0, 0 };
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const uint32_t wa = lds32(r0 + 48 + 32 * i + 4 * t), wb = lds32(r0 + 64 + 32 * i + 4 * t);
+        const uint32_t wc = lds32(r1 + 48 + 32 * i + 4 * t), wd = lds32(r1 + 64 + 32 * i + 4 * t);
+#pragma unroll
+        for (int hn = 0; hn < 2; hn++) {
+            const int j = 2 * i + hn;
+            auto bit = [&](uint32_t q) { return (j < 4 ? q << (4 - j) : q >> (j - 4)) & 0x10101010u; };
+            const uint32_t b0 = lds32(bcol + 32 * j), b1 = lds32(bcol + 32 * j + 16);
+            int c[4];
+            mma_u8s8(c, ((wa >> (4 * hn)) & 0x0f0f0f0fu) | bit(qa0), ((wc >> (4 * hn)) & 0x0f0f0f0fu) | bit(qa1),
+                     ((wb >> (4 * hn)) & 0x0f0f0f0fu) | bit(qb0), ((wd >> (4 * hn)) & 0x0f0f0f0fu) | bit(qb1), b0, b1);
+            const int s0 = (int) ((sc0[j >> 2] >> (8 * (j & 3))) & 0xff), s1 = (int) ((sc1[j >> 2] >> (8 * (j & 3))) & 0xff);
+            isum[0] += s0 * c[0]; isum[1] += s0 * c[1];
+            isum[2] += s1 * c[2]; isum[3] += s1 * c[3];
+        }
+    }
+    const uint4 bs0 = lds128(am + (2 * t) * cs_m + 256), bs1 = lds128(am + (2 * t + 1) * cs_m + 256);
+    auto mdot = [](const uint4 & bs, const uint32_t (&mn)[2]) {
+        int v = dp2a_lo_su((int) bs.x, mn[0], 0);
+        v     = dp2a_hi_su((int) bs.y, mn[0], v);
+        v     = dp2a_lo_su((int) bs.z, mn[1], v);
+        return dp2a_hi_su((int) bs.w, mn[1], v);
+    };
+    const float dy0 = __uint_as_float(lds32(ax + (2 * t) * cs_x)), dy1 = __uint_as_float(lds32(ax + (2 * t + 1) * cs_x));
+    const float d0 = half_bits_to_float((uint16_t) (h0.x & 0xffff)), m0 = half_bits_to_float((uint16_t) (h0.x >> 16));
+    const float d1 = half_bits_to_float((uint16_t) (h1.x & 0xffff)), m1 = half_bits_to_float((uint16_t) (h1.x >> 16));
+    acc[0] = fmaf(d0 * dy0, (float) isum[0], acc[0]); acc[0] = fmaf(-(m0 * dy0), (float) mdot(bs0, mn0), acc[0]);
+    acc[1] = fmaf(d0 * dy1, (float) isum[1], acc[1]); acc[1] = fmaf(-(m0 * dy1), (float) mdot(bs1, mn0), acc[1]);
+    acc[2] = fmaf(d1 * dy0, (float) isum[2], acc[2]); acc[2] = fmaf(-(m1 * dy0), (float) mdot(bs0, mn1), acc[2]);
+    acc[3] = fmaf(d1 * dy1, (float) isum[3], acc[3]); acc[3] = fmaf(-(m1 * dy1), (float) mdot(bs1, mn1), acc[3]);
+}
+
 // q4_0: 8 blocks of { half d; uint8 qs[16] } = 144 B per unit; element k = low nibble of qs[k], k + 16 = high nibble (one word
 // holds both k-halves of a fragment). Blocks are 18 bytes: even blocks start on a word boundary (qs is shifted by 16 bits), odd
 // blocks have qs word aligned. sum((q - 8) * y) = sum(q * y) - 8 * sum(y)  (ggml-cpu/quants.c:135-146)
@@ -264,6 +310,7 @@ __device__ __forceinline__ void unit_mma_q6_K(uint32_t wt, uint32_t am, uint32_t
 template <int TYPE>
 __device__ __forceinline__ void unit_mma(uint32_t wt, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, int g, int t, float (&acc)[4]) {
     if (TYPE == B200_TYPE_Q6_K) unit_mma_q6_K(wt, am, ax, cs_m, cs_x, g, t, acc);
+    else if (TYPE == B200_TYPE_Q5_K) unit_mma_q5_K(wt, am, ax, cs_m, cs_x, g, t, acc);
     else if (TYPE == B200_TYPE_Q4_K) unit_mma_q4_K(wt, am, ax, cs_m, cs_x, g, t, acc);
     else if (TYPE == B200_TYPE_Q8_0) unit_mma_q8_0(wt, am, ax, cs_m, cs_x, g, t, acc);
     else unit_mma_q4_0(wt, am, ax, cs_m, cs_x, g, t, acc);
@@ -525,7 +572,7 @@ bool mv_mma_fits(int type, int64_t K) {
 }
 
 bool mv_mma_usable(int type) {
-    return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q6_K) && mma_get_encode() != nullptr;
+    return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K) && mma_get_encode() != nullptr;
 }
 
 // consumer warps / ring stages: as many warps as leave room for >= 3 stages next to the 8 activation columns (K = 14336: 129 KB of
@@ -587,6 +634,7 @@ static b200_status mma_launch(b200_ctx * ctx, int type, dim3 grid, size_t smem, 
     switch (type) {
         case B200_TYPE_Q4_K: return mma_launch_t<B200_TYPE_Q4_K>(ctx, cfg, maps, p);
         case B200_TYPE_Q8_0: return mma_launch_t<B200_TYPE_Q8_0>(ctx, cfg, maps, p);
+        case B200_TYPE_Q5_K: return mma_launch_t<B200_TYPE_Q5_K>(ctx, cfg, maps, p);
         case B200_TYPE_Q6_K: return mma_launch_t<B200_TYPE_Q6_K>(ctx, cfg, maps, p);
         default:             return mma_launch_t<B200_TYPE_Q4_0>(ctx, cfg, maps, p);
     }

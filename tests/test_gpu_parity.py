@@ -290,8 +290,9 @@ def test_mul_mat_id_vs_oracle(ctx, oracle, t, n_as, n_used, bcast, n_tok):
 
 @pytest.mark.parametrize("M,K,N", [(96, 256, 1), (200, 1024, 3), (130, 4096, 1), (64, 4096, 2), (40, 4096, 8), (33, 14336, 1), (257, 1280, 5)])
 def test_q5_K_decode(ctx, pkg, oracle, M, K, N):
-    """176-byte blocks (q4_K + 32 bytes of fifth bits) are 16-byte multiples: the TMA-staged kernel takes any K % 256 == 0; all column
-    counts up to 8 run the dp4a kernel (no tensor-core mat-vec for q5_K), so column c of an N-column call is bit-identical to the 1-column call"""
+    """176-byte blocks (q4_K + 32 bytes of fifth bits) are 16-byte multiples: the TMA-staged kernels take any K % 256 == 0; 1-2 columns run
+    the dp4a kernel (column c of a 2-column call is bit-identical to the 1-column call), 3-8 the tensor-core mat-vec (same integer sums,
+    another fp32 order)"""
     rng = np.random.default_rng(M + K + N + 5)
     W = quantize_weights(oracle, Q5_K, rng.uniform(-1, 1, (M, K)).astype(np.float32))
     X = (rng.standard_normal((N, K)) * rng.choice([0.05, 1.0, 20.0], (N, 1))).astype(np.float32)
@@ -299,7 +300,7 @@ def test_q5_K_decode(ctx, pkg, oracle, M, K, N):
     assert oracle.nmse(oracle.mul_mat(Q5_K, W, X), got) <= NMSE_TIGHT
     if N > 1:
         one = ctx.mul_mat(Q5_K, cu(W), cu(X[1:2])).cpu().numpy()
-        assert np.array_equal(one[0], got[1])
+        assert np.array_equal(one[0], got[1]) if N <= 2 else oracle.nmse(one[0], got[1]) <= 1e-12
     ctx.force_path(pkg.PATH_SIMPLE)
     gen = ctx.mul_mat(Q5_K, cu(W), cu(X)).cpu().numpy()
     ctx.force_path(pkg.PATH_AUTO)
