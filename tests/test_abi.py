@@ -39,7 +39,7 @@ def test_supported_geometry_queries(pkg):
     d = pkg.MulMatDesc.contiguous(pkg.Q4_K, 128, 512, 3, 2, 1, 4, 2)
     assert L.b200_mul_mat_supported(C.byref(d)) == 1
     d = pkg.MulMatDesc.contiguous(pkg.Q4_0, 64, 64, 1)
-    d.type = 14  # q6_K is outside the hot path
+    d.type = 10  # q2_K is outside the hot path
     assert L.b200_mul_mat_supported(C.byref(d)) == 0
     d = pkg.MulMatDesc.contiguous(pkg.Q4_K, 64, 256, 1)
     d.ne00 = 128  # not a multiple of the 256 super-block
@@ -48,6 +48,29 @@ def test_supported_geometry_queries(pkg):
     assert L.b200_mul_mat_supported(C.byref(d)) == 0
     e = pkg.MulMatIdDesc.contiguous(pkg.Q4_0, 512, 256, 8, 2, 1, 17)
     assert L.b200_mul_mat_id_supported(C.byref(e)) == 1
+
+
+def test_python_structs_match_the_header(pkg, tmp_path):
+    """the ctypes mirrors of the C-ABI structs have the size and field offsets the C compiler gives include/ggml_b200.h"""
+    structs = {"b200_mul_mat_desc": pkg.MulMatDesc, "b200_mul_mat_id_desc": pkg.MulMatIdDesc, "b200_row_split": pkg.RowSplit,
+               "b200_row_split_ll": pkg.RowSplitLL, "b200_fusion": pkg.Fusion}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "ggml_b200.h"', 'int main(void) {']
+    for cname, cls in structs.items():
+        lines.append(f'  printf("{cname} %zu", sizeof({cname}));')
+        for fname, *_ in cls._fields_:
+            lines.append(f'  printf(" %zu", offsetof({cname}, {fname}));')
+        lines.append('  printf("\\n");')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-std=c11", "-I", str(ROOT / "include"), str(src), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines()
+    for line, (cname, cls) in zip(out, structs.items()):
+        parts = line.split()
+        assert parts[0] == cname
+        assert int(parts[1]) == C.sizeof(cls), cname
+        assert [int(x) for x in parts[2:]] == [getattr(cls, f[0]).offset for f in cls._fields_], cname
 
 
 def test_no_cpu_fallback(pkg):
