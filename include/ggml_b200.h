@@ -91,6 +91,9 @@ B200_API b200_status  b200_memcpy_d2d_async(b200_ctx * ctx, void * dst, const vo
  * memory directly (best effort: without it the driver stages the copies) */
 B200_API b200_status  b200_memcpy2d_async(b200_ctx * ctx, void * dst, size_t dpitch, const void * src, size_t spitch, size_t width, size_t height);
 B200_API b200_status  b200_enable_peer_access(int device, int peer);
+/* iface.cpy_tensor_async between two backends of this library (ggml_backend_cuda_cpy_tensor_async, ggml-cuda.cu:2773-2826): a copy
+ * between (or within) devices on ctx's stream; the caller orders the destination backend's stream behind it with an event */
+B200_API b200_status  b200_memcpy_peer_async(b200_ctx * ctx, void * dst, int dst_device, const void * src, int src_device, size_t size);
 
 /* events: device event_new/free/synchronize, backend event_record/event_wait (ggml-cuda.cu:2836-2862, 4649-4677) */
 B200_API b200_status  b200_event_create(int device, void ** event);
@@ -99,6 +102,20 @@ B200_API b200_status  b200_event_record(b200_ctx * ctx, void * event);
 B200_API b200_status  b200_event_wait(b200_ctx * ctx, void * event);
 B200_API b200_status  b200_event_synchronize(void * event);
 B200_API b200_status  b200_event_elapsed_ms(void * start, void * stop, float * ms);
+
+/* ---------------------------------------------------------------- CUDA graphs ---- */
+
+/* graph_compute with CUDA-graph replay (ggml_backend_cuda_graph_compute, ggml-cuda.cu:3679-3754): everything the context launches
+ * between capture_begin and capture_end is recorded instead of run; capture_end instantiates it. A call that would have to grow
+ * a scratch buffer or build a weight expansion fails during capture (run the same sequence once uncaptured first); after a failed
+ * call the caller must still call capture_end (which then fails too) and fall back to plain launches. b200_graph_launch replays
+ * the recorded launches on the context's stream and adds their number to b200_ctx_launch_count. */
+typedef struct b200_graph b200_graph;
+B200_API b200_status  b200_graph_capture_begin(b200_ctx * ctx);
+B200_API b200_status  b200_graph_capture_end(b200_ctx * ctx, b200_graph ** out);
+B200_API b200_status  b200_graph_launch(b200_ctx * ctx, b200_graph * g);
+B200_API void         b200_graph_destroy(b200_graph * g);
+B200_API uint64_t     b200_graph_kernel_count(const b200_graph * g);
 
 /* ---------------------------------------------------------------- K1: activation quantizer ---- */
 

@@ -274,6 +274,9 @@ class RefHarness:
         L.refh_mul_mat_id_glu.argtypes = [C.c_int] * 4 + [C.c_int64] * 6 + [C.c_void_p] * 6 + [C.c_int, C.c_float, C.c_float, C.c_void_p]
         L.refh_mul_mat_stack.argtypes = [C.c_int] * 5 + [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                                         C.c_double, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
+        L.refh_stack_e2e.restype = C.c_int
+        L.refh_stack_e2e.argtypes = [C.c_int] * 5 + [C.c_void_p] * 3 + [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                                     C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         self._loaded = {}
 
     @classmethod
@@ -332,6 +335,25 @@ class RefHarness:
             raise RuntimeError(f"refh_mul_mat rc={rc} (2 = backend does not support the op)")
         out = out if X.ndim == 4 else out[0, 0]
         return out, (us.value if seconds > 0 else None)
+
+    def stack_e2e(self, reg: int, t: int, shapes, x_of, x_K, N, W_all, X_all, warmup=3, steps=10, n_threads=0, dev=0, want_out=True):
+        """the MUL_MAT stack of one step as ONE cgraph through ggml_backend_tensor_set_async / graph_compute_async / tensor_get_async /
+        synchronize (refh_stack_e2e). shapes: [(M, K)]; x_of[i]: which activation tensor matrix i reads; x_K: K of every activation
+        tensor. returns (us_compute, us_e2e, out float32 [sum(M) * N] | None)"""
+        Ms = np.ascontiguousarray([m for m, _ in shapes], dtype=np.int64)
+        Ks = np.ascontiguousarray([k for _, k in shapes], dtype=np.int64)
+        xo = np.ascontiguousarray(x_of, dtype=np.int32)
+        xk = np.ascontiguousarray(x_K, dtype=np.int64)
+        W_all = np.ascontiguousarray(W_all, dtype=np.uint8)
+        X_all = np.ascontiguousarray(X_all, dtype=np.float32)
+        assert X_all.size == int(xk.sum()) * N and len(xo) == len(Ms)
+        out = np.zeros(int(Ms.sum()) * N, dtype=np.float32) if want_out else None
+        uc, ue = C.c_double(0), C.c_double(0)
+        rc = self.lib.refh_stack_e2e(reg, dev, n_threads, t, len(Ms), _ptr(Ms), _ptr(Ks), _ptr(xo), len(xk), _ptr(xk), N, _ptr(W_all), _ptr(X_all),
+                                     warmup, steps, None if out is None else _ptr(out), C.byref(uc), C.byref(ue))
+        if rc:
+            raise RuntimeError(f"refh_stack_e2e rc={rc} (2 = op not supported, 3 = allocation failed, 4 = graph_compute failed)")
+        return uc.value, ue.value, out
 
     def mul_mat_split(self, reg: int, t: int, W: np.ndarray, X: np.ndarray, tensor_split=None, dev=0, repeats=1):
         """MUL_MAT with W in the backend's split buffer type (ggml_backend_split_buffer_type): W uint8 [M, row_bytes], X float32

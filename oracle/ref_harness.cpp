@@ -259,6 +259,96 @@ int refh_mul_mat_stack(int reg, int dev, int n_threads, int type, int n_mats, co
     return 0;
 }
 
+// The MUL_MAT stack of one decode / prefill step as ONE ggml_cgraph on any registered backend, driven the way a host drives a
+// backend: activations from (pinned) host memory with ggml_backend_tensor_set_async, ggml_backend_graph_compute_async, the step's
+// results back with ggml_backend_tensor_get_async, ggml_backend_synchronize. Matrix i multiplies activation tensor x_of[i]
+// (q/k/v and gate/up share theirs, as in the llama graph, src/llama-graph.cpp:612-660). The dst tensors are placed back to back
+// in one buffer (ggml_backend_tensor_alloc), so the results of a step are one copy. Wall clock:
+//   *us_compute  graph_compute + synchronize only
+//   *us_e2e      set_async of every activation + graph_compute + get_async of the results + synchronize
+// out_all (optional): the concatenated results of the last step. returns 0 on success.
+int refh_stack_e2e(int reg, int dev, int n_threads, int type, int n_mats, const int64_t * Ms, const int64_t * Ks, const int32_t * x_of,
+                   int n_x, const int64_t * x_K, int64_t N, const void * W_all, const float * X_all, int warmup, int steps,
+                   float * out_all, double * us_compute, double * us_e2e) {
+    graph_run g;
+    g.be = open_backend(reg, dev, n_threads);
+    if (!g.be) return 1;
+    attach_threadpool(g, reg, n_threads);
+    ggml_backend_dev_t device = ggml_backend_get_device(g.be);
+    const size_t n_nodes = (size_t) 3 * n_mats + n_x + 16;
+    ggml_init_params ip  = { ggml_tensor_overhead() * n_nodes + ggml_graph_overhead_custom(n_nodes, false), nullptr, true };
+    ggml_init_params ipo = { ggml_tensor_overhead() * ((size_t) n_mats + 8), nullptr, true };
+    g.ctx = ggml_init(ip);
+    ggml_context * octx = ggml_init(ipo);
+    if (!g.ctx || !octx) return 1;
+    std::vector<ggml_tensor *> ws(n_mats), xs(n_x), os(n_mats);
+    for (int i = 0; i < n_mats; i++) ws[i] = ggml_new_tensor_2d(g.ctx, (ggml_type) type, Ks[i], Ms[i]);
+    for (int j = 0; j < n_x; j++) xs[j] = ggml_new_tensor_2d(g.ctx, GGML_TYPE_F32, x_K[j], N);
+    g.buf = ggml_backend_alloc_ctx_tensors(g.ctx, g.be);
+    if (!g.buf) { ggml_free(octx); return 3; }
+    g.graph = ggml_new_graph_custom(octx, n_nodes, false);
+    size_t out_floats = 0;
+    for (int i = 0; i < n_mats; i++) {
+        os[i] = ggml_mul_mat(octx, ws[i], xs[x_of[i]]);
+        if (!ggml_backend_supports_op(g.be, os[i])) { ggml_free(octx); return 2; }
+        ggml_build_forward_expand(g.graph, os[i]);
+        out_floats += (size_t) Ms[i] * N;
+    }
+    ggml_tensor * pool = ggml_new_tensor_1d(octx, GGML_TYPE_F32, (int64_t) out_floats);
+    ggml_backend_buffer_t obuf = ggml_backend_alloc_buffer(g.be, out_floats * sizeof(float) + 256);
+    if (!obuf) { ggml_free(octx); return 3; }
+    char * base = (char *) ggml_backend_buffer_get_base(obuf);
+    size_t off = 0;
+    for (int i = 0; i < n_mats; i++) {
+        ggml_backend_tensor_alloc(obuf, os[i], base + off);
+        off += ggml_nbytes(os[i]);
+    }
+    ggml_backend_tensor_alloc(obuf, pool, base);
+    const char * wp = (const char *) W_all;
+    for (int i = 0; i < n_mats; i++) {
+        ggml_backend_tensor_set(ws[i], wp, 0, ggml_nbytes(ws[i]));
+        wp += ggml_nbytes(ws[i]);
+    }
+    // host side of the copies: the device's pinned host buffer type where it has one (llama's input / output buffers)
+    size_t x_bytes = 0;
+    for (int j = 0; j < n_x; j++) x_bytes += ggml_nbytes(xs[j]);
+    ggml_backend_buffer_type_t hbuft = ggml_backend_dev_host_buffer_type(device);
+    ggml_backend_buffer_t hbuf = hbuft ? ggml_backend_buft_alloc_buffer(hbuft, x_bytes + out_floats * sizeof(float) + 512) : nullptr;
+    std::vector<char> pageable;
+    char * hx = nullptr;
+    if (hbuf) hx = (char *) ggml_backend_buffer_get_base(hbuf);
+    else { pageable.resize(x_bytes + out_floats * sizeof(float) + 512); hx = pageable.data(); }
+    char * hy = hx + ((x_bytes + 255) & ~(size_t) 255);
+    memcpy(hx, X_all, x_bytes);
+
+    auto step_e2e = [&]() {
+        size_t o = 0;
+        for (int j = 0; j < n_x; j++) {
+            ggml_backend_tensor_set_async(g.be, xs[j], hx + o, 0, ggml_nbytes(xs[j]));
+            o += ggml_nbytes(xs[j]);
+        }
+        ggml_backend_graph_compute_async(g.be, g.graph);
+        ggml_backend_tensor_get_async(g.be, pool, hy, 0, out_floats * sizeof(float));
+        ggml_backend_synchronize(g.be);
+    };
+    int rc = 0;
+    for (int i = 0; i < warmup + 2; i++) step_e2e();
+    auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < steps; i++) {
+        if (ggml_backend_graph_compute_async(g.be, g.graph) != GGML_STATUS_SUCCESS) rc = 4;
+        ggml_backend_synchronize(g.be);
+    }
+    if (us_compute) *us_compute = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() / steps * 1e6;
+    t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < steps; i++) step_e2e();
+    if (us_e2e) *us_e2e = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() / steps * 1e6;
+    if (out_all) memcpy(out_all, hy, out_floats * sizeof(float));
+    if (hbuf) ggml_backend_buffer_free(hbuf);
+    ggml_backend_buffer_free(obuf);
+    ggml_free(octx);
+    return rc;
+}
+
 // calls a `uint64_t (*)(void)` the registry exposes through get_proc_address (e.g. a backend's own counters); ~0 if absent
 uint64_t refh_proc_u64(int reg, const char * name) {
     if (reg < 0 || reg >= (int) g_regs.size()) return ~(uint64_t) 0;

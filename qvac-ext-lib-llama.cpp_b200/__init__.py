@@ -29,7 +29,8 @@ EXPORTS = [
     "b200_ctx_stream", "b200_ctx_synchronize", "b200_last_error", "b200_ctx_launch_count", "b200_ctx_set_force_path",
     "b200_malloc", "b200_free", "b200_host_malloc", "b200_host_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_memcpy_d2d",
     "b200_memcpy_peer", "b200_memset", "b200_memcpy_h2d_async", "b200_memcpy_d2h_async", "b200_memcpy_d2d_async",
-    "b200_memcpy2d_async", "b200_enable_peer_access",
+    "b200_memcpy2d_async", "b200_enable_peer_access", "b200_memcpy_peer_async",
+    "b200_graph_capture_begin", "b200_graph_capture_end", "b200_graph_launch", "b200_graph_destroy", "b200_graph_kernel_count",
     "b200_event_create", "b200_event_destroy", "b200_event_record", "b200_event_wait", "b200_event_synchronize",
     "b200_event_elapsed_ms", "b200_quantize_q8_0", "b200_quantize_q8_1", "b200_quantize_q8_K", "b200_quantize_units",
     "b200_mul_mat_supported", "b200_mul_mat", "b200_mul_mat_shared_src1", "b200_mul_mat_host", "b200_mul_mat_id_supported",

@@ -360,6 +360,15 @@ b200_status b200_memcpy2d_async(b200_ctx * ctx, void * dst, size_t dpitch, const
     CU(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, height, cudaMemcpyDefault, ctx->stream));  // unified addressing names the devices
     return B200_OK;
 }
+b200_status b200_memcpy_peer_async(b200_ctx * ctx, void * dst, int dst_device, const void * src, int src_device, size_t size) {
+    if (!ctx) return fail(B200_ERR_ARG, "null context");
+    if (size == 0) return B200_OK;
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
+    CU(cudaSetDevice(ctx->device));
+    if (dst_device == src_device) CU(cudaMemcpyAsync(dst, src, size, cudaMemcpyDeviceToDevice, ctx->stream));
+    else CU(cudaMemcpyPeerAsync(dst, dst_device, src, src_device, size, ctx->stream));
+    return B200_OK;
+}
 b200_status b200_enable_peer_access(int device, int peer) {
     if (device == peer) return B200_OK;
     int can = 0;
@@ -403,6 +412,68 @@ b200_status b200_event_elapsed_ms(void * start, void * stop, float * ms) {
     CU(cudaEventElapsedTime(ms, (cudaEvent_t) start, (cudaEvent_t) stop));
     return B200_OK;
 }
+
+// ------------------------------------------------------------------------------------------------ CUDA graphs
+//
+// graph_compute of a decode step is a chain of short launches: ~2.5 us of host time each when launched one by one. The ggml
+// backend captures the launches of a cgraph it has seen before into a CUDA graph and replays it (the reference does the same,
+// ggml-cuda.cu:3679-3754); programmatic-dependent-launch edges between the mat-vec kernels survive the capture.
+
+struct b200_graph {
+    cudaGraphExec_t exec;
+    uint64_t        launches;  // kernels inside
+    int             device;
+};
+
+b200_status b200_graph_capture_begin(b200_ctx * ctx) {
+    if (!ctx) return fail(B200_ERR_ARG, "null context");
+    if (b200_status fst = b200_split_flush(ctx)) return fst;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
+    ctx->capture_launches0 = ctx->launches;
+    return B200_OK;
+}
+
+b200_status b200_graph_capture_end(b200_ctx * ctx, b200_graph ** out) {
+    if (!ctx || !out) return fail(B200_ERR_ARG, "null argument");
+    *out = nullptr;
+    CU(cudaSetDevice(ctx->device));
+    cudaGraph_t g = nullptr;
+    cudaError_t e = cudaStreamEndCapture(ctx->stream, &g);
+    const uint64_t n = ctx->launches - ctx->capture_launches0;
+    ctx->launches = ctx->capture_launches0;  // nothing has run yet: b200_graph_launch counts the kernels when they do
+    if (e != cudaSuccess || !g) {
+        cudaGetLastError();
+        if (g) cudaGraphDestroy(g);
+        return fail(B200_ERR_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
+    }
+    cudaGraphExec_t x = nullptr;
+    e = cudaGraphInstantiate(&x, g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(B200_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));
+    }
+    *out = new b200_graph{ x, n, ctx->device };
+    return B200_OK;
+}
+
+b200_status b200_graph_launch(b200_ctx * ctx, b200_graph * g) {
+    if (!ctx || !g) return fail(B200_ERR_ARG, "null argument");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaGraphLaunch(g->exec, ctx->stream));
+    ctx->launches += g->launches;
+    return B200_OK;
+}
+
+void b200_graph_destroy(b200_graph * g) {
+    if (!g) return;
+    cudaSetDevice(g->device);
+    cudaGraphExecDestroy(g->exec);
+    delete g;
+}
+
+uint64_t b200_graph_kernel_count(const b200_graph * g) { return g ? g->launches : 0; }
 
 // ------------------------------------------------------------------------------------------------ K1
 

@@ -1,6 +1,7 @@
 // ggml_backend_b200.cpp — the drop-in: a ggml backend ("B200") that implements the reference's five backend vtables
-// (/root/reference/ggml/src/ggml-backend-impl.h:16-204, API version 2) for exactly GGML_OP_MUL_MAT and
-// GGML_OP_MUL_MAT_ID on q4_0 / q8_0 / q4_K weights x F32 activations. All device work goes through the C-ABI of
+// (/root/reference/ggml/src/ggml-backend-impl.h:16-204, API version 2) for GGML_OP_MUL_MAT and GGML_OP_MUL_MAT_ID on
+// q4_0 / q8_0 / q4_K / q5_K / q6_K weights x F32 activations, plus the element-wise nodes the fused mat-vec epilogue
+// absorbs (GLU, ADD, MUL, ADD_ID). All device work goes through the C-ABI of
 // include/ggml_b200.h (libb200mm.so); this file contains no CUDA and no CPU compute.
 //
 // Loaded out of tree: GGML_BACKEND_PATH=/path/libggml-b200.so (ggml-backend-reg.cpp:711-715) or ggml_backend_load();
@@ -61,8 +62,26 @@ struct be_ctx {
     std::string name;
     bool       fuse;                                // shared-src1 peephole (q/k/v, gate/up in one launch)
     bool       fuse_epilogue = true;               // K7 peephole: GLU / bias epilogues of the one-column mat-vec
+    bool       weight_cache  = true;               // prefill operand expansions are kept per weight tensor (GGML_B200_WEIGHT_CACHE=0: rebuilt per call)
     void *     split_event = nullptr;              // "src1 is ready" on the main stream
+    void *     copy_event  = nullptr;              // cpy_tensor_async: "the copy issued on this backend's stream is done"
     split_peer peers[B200_MAX_DEVICES];
+    // CUDA-graph replay of graph_compute (ggml-cuda.cu:3679-3754): a cgraph whose node properties match one seen before is
+    // captured on its second appearance and replayed from then on
+    bool       use_graphs      = true;             // GGML_B200_DISABLE_GRAPHS=1 switches it off
+    int        graph_min_nodes = 4;                // GGML_B200_GRAPH_MIN_NODES: shorter cgraphs are launched directly
+    bool       capturing       = false;
+    struct cached_graph {
+        std::vector<uint64_t> key;                 // the properties of every node, flattened
+        b200_graph *          exec  = nullptr;
+        int                   seen  = 0;
+        bool                  bad   = false;       // capture failed once: never again for this key
+        uint64_t              stamp = 0;           // last use (LRU)
+    };
+    std::map<uint64_t, std::vector<cached_graph>> graphs;  // hash -> entries
+    size_t     n_graphs    = 0;
+    uint64_t   graph_clock = 0;
+    uint64_t   graph_replays = 0, graph_captures = 0;
 };
 
 ggml_backend_reg_t b200_reg();
@@ -72,6 +91,10 @@ ggml_backend_reg_t b200_reg();
     GGML_ABORT("ggml-b200 fatal error");  // same convention as CUDA_CHECK -> ggml_cuda_error (ggml-cuda.cu:82-93)
 }
 #define CHECK(call) do { if ((call) != B200_OK) die(#call); } while (0)
+// inside graph_compute: a failure while the stream is being captured (a scratch buffer that would have to grow, a weight
+// expansion that is not cached yet) is not fatal - the capture is abandoned and the nodes are launched directly
+struct capture_failed {};
+#define CHECK_RUN(c, call) do { if ((call) != B200_OK) { if ((c)->capturing) throw capture_failed{}; die(#call); } } while (0)
 
 // ------------------------------------------------------------------------------------------------ device buffer
 
@@ -111,7 +134,7 @@ bool buf_cpy_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * src, ggml_
     buf_ctx * s = (buf_ctx *) sb->context, * d = (buf_ctx *) buffer->context;
     drop_cached(buffer, dst);
     if (s->device == d->device) CHECK(b200_memcpy_d2d(d->device, dst->data, src->data, ggml_nbytes(src)));
-    else CHECK(b200_memcpy_peer(d->device, dst->data, s->device, src->data, ggml_nbytes(src)));
+    else CHECK(b200_memcpy_peer(d->device, dst->data, s->device, src->data, ggml_nbytes(src)));  // synchronous on return (ggml-cuda.cu:648-651)
     return true;
 }
 void buf_clear(ggml_backend_buffer_t buffer, uint8_t value) {
@@ -201,6 +224,7 @@ struct split_extra {
     void *  data[B200_MAX_DEVICES]     = {};
     int64_t row_low[B200_MAX_DEVICES]  = {};
     int64_t row_high[B200_MAX_DEVICES] = {};
+    size_t  bytes[B200_MAX_DEVICES]    = {};
 };
 struct split_buf_ctx {
     std::vector<split_extra *> extras;
@@ -228,7 +252,7 @@ void split_buf_free(ggml_backend_buffer_t buffer) {
     for (split_extra * e : c->extras) {
         for (int id = 0; id < B200_MAX_DEVICES; id++) {
             if (!e->data[id]) continue;
-            b200_weight_cache_invalidate(id, e->data[id], 1);
+            b200_weight_cache_invalidate(id, e->data[id], e->bytes[id]);
             b200_free(id, e->data[id]);
         }
         delete e;
@@ -253,6 +277,7 @@ ggml_status split_buf_init_tensor(ggml_backend_buffer_t buffer, ggml_tensor * t)
             GGML_LOG_ERROR("ggml-b200: allocating a %.2f MiB slice of %s on device %d failed: %s\n", n * nb1 / 1048576.0, t->name, id, b200_last_error());
             return GGML_STATUS_ALLOC_FAILED;
         }
+        e->bytes[id] = (size_t) n * nb1;
     }
     t->extra = e;
     return GGML_STATUS_SUCCESS;
@@ -372,6 +397,9 @@ void be_free(ggml_backend_t backend) {
         b200_ctx_destroy(sp.ctx);
     }
     if (c->split_event) b200_event_destroy(c->device, c->split_event);
+    if (c->copy_event) b200_event_destroy(c->device, c->copy_event);
+    b200_ctx_synchronize(c->ctx);
+    for (auto & kv : c->graphs) for (auto & g : kv.second) b200_graph_destroy(g.exec);
     b200_ctx_destroy(c->ctx);
     delete c;
     delete backend;
@@ -383,7 +411,34 @@ void be_set_tensor_async(ggml_backend_t backend, ggml_tensor * t, const void * d
 void be_get_tensor_async(ggml_backend_t backend, const ggml_tensor * t, void * data, size_t offset, size_t size) {
     CHECK(b200_memcpy_d2h_async(((be_ctx *) backend->context)->ctx, data, (const char *) t->data + offset, size));
 }
-bool be_cpy_tensor_async(ggml_backend_t, ggml_backend_t, const ggml_tensor *, ggml_tensor *) { return false; }  // caller falls back (ggml-backend.cpp:408-429)
+const char * be_name(ggml_backend_t backend);
+// copy between two B200 backends (streams), possibly on different devices, without a host bounce
+// (ggml_backend_cuda_cpy_tensor_async, ggml-cuda.cu:2773-2826): issued on the SOURCE backend's stream, which has produced src; the
+// destination stream then waits for an event. Anything else returns false and the caller falls back to a synchronous copy
+// (ggml-backend.cpp:408-429).
+bool be_cpy_tensor_async(ggml_backend_t backend_src, ggml_backend_t backend_dst, const ggml_tensor * src, ggml_tensor * dst) {
+    if (backend_src->iface.get_name != be_name || backend_dst->iface.get_name != be_name) return false;
+    ggml_backend_buffer_t sb = src->view_src ? src->view_src->buffer : src->buffer;
+    ggml_backend_buffer_t db = dst->view_src ? dst->view_src->buffer : dst->buffer;
+    if (!sb || !db || !buft_is_b200(sb->buft) || !buft_is_b200(db->buft)) return false;
+    be_ctx * cs = (be_ctx *) backend_src->context, * cd = (be_ctx *) backend_dst->context;
+    buf_ctx * bs = (buf_ctx *) sb->context, * bd = (buf_ctx *) db->context;
+    if (bs->device != cs->device || bd->device != cd->device) return false;  // a backend only touches buffers of its own device (:2797-2803)
+    if (ggml_is_quantized(dst->type)) b200_weight_cache_invalidate(bd->device, dst->data, ggml_nbytes(dst));
+    if (backend_src == backend_dst) {
+        CHECK(b200_memcpy_d2d_async(cs->ctx, dst->data, src->data, ggml_nbytes(dst)));
+        return true;
+    }
+    if (cs->device != cd->device) {
+        b200_enable_peer_access(cs->device, cd->device);  // best effort: the driver stages the copy otherwise
+        b200_enable_peer_access(cd->device, cs->device);
+    }
+    CHECK(b200_memcpy_peer_async(cs->ctx, dst->data, cd->device, src->data, cs->device, ggml_nbytes(dst)));
+    if (!cs->copy_event) CHECK(b200_event_create(cs->device, &cs->copy_event));
+    CHECK(b200_event_record(cs->ctx, cs->copy_event));
+    CHECK(b200_event_wait(cd->ctx, cs->copy_event));
+    return true;
+}
 void be_synchronize(ggml_backend_t backend) { CHECK(b200_ctx_synchronize(((be_ctx *) backend->context)->ctx)); }
 
 bool ranges_overlap(const ggml_tensor * a, const ggml_tensor * b) {
@@ -429,8 +484,7 @@ ggml_status split_mul_mat(be_ctx * c, ggml_tensor * node, const b200_mul_mat_des
                 GGML_LOG_ERROR("ggml-b200: cannot create a context on device %d for a split tensor: %s\n", id, b200_last_error());
                 return GGML_STATUS_FAILED;
             }
-            const char * wc = getenv("GGML_B200_WEIGHT_CACHE");
-            b200_ctx_set_weight_cache(sp.ctx, !(wc && !atoi(wc)));
+            b200_ctx_set_weight_cache(sp.ctx, c->weight_cache);
             CHECK(b200_event_create(id, &sp.event));
             b200_enable_peer_access(id, c->device);  // best effort: the copies are staged by the driver otherwise
             b200_enable_peer_access(c->device, id);
@@ -486,16 +540,16 @@ void run_glu(be_ctx * c, ggml_tensor * node) {
     const bool    swapped = ggml_get_op_params_i32(node, 1) != 0;
     const float * gate = (const float *) a->data, * up = b ? (const float *) b->data : (const float *) a->data;
     if (!b) (swapped ? gate : up) += nc;  // single tensor: [gate | up] halves of every row, or [up | gate] when swapped
-    CHECK(b200_glu(c->ctx, ggml_get_op_params_i32(node, 0), ggml_get_op_params_f32(node, 2), ggml_get_op_params_f32(node, 3), gate, a->nb[1], up,
-                   b ? b->nb[1] : a->nb[1], (float *) node->data, node->nb[1], nc, ggml_nrows(node)));
+    CHECK_RUN(c, b200_glu(c->ctx, ggml_get_op_params_i32(node, 0), ggml_get_op_params_f32(node, 2), ggml_get_op_params_f32(node, 3), gate, a->nb[1], up,
+                       b ? b->nb[1] : a->nb[1], (float *) node->data, node->nb[1], nc, ggml_nrows(node)));
 }
 void run_add(be_ctx * c, ggml_tensor * node) {
     const ggml_tensor * a = node->src[0], * b = node->src[1];
-    CHECK((node->op == GGML_OP_MUL ? b200_mul : b200_add)(c->ctx, node->ne, (const float *) a->data, a->nb, (const float *) b->data, b->ne, b->nb, (float *) node->data, node->nb));
+    CHECK_RUN(c, (node->op == GGML_OP_MUL ? b200_mul : b200_add)(c->ctx, node->ne, (const float *) a->data, a->nb, (const float *) b->data, b->ne, b->nb, (float *) node->data, node->nb));
 }
 void run_add_id(be_ctx * c, ggml_tensor * node) {
     const ggml_tensor * a = node->src[0], * b = node->src[1], * ids = node->src[2];
-    CHECK(b200_add_id(c->ctx, (const float *) a->data, a->nb[1], a->nb[2], (const float *) b->data, b->nb[1], b->ne[1], (const int32_t *) ids->data,
+    CHECK_RUN(c, b200_add_id(c->ctx, (const float *) a->data, a->nb[1], a->nb[2], (const float *) b->data, b->nb[1], b->ne[1], (const int32_t *) ids->data,
                       ids->nb[1], (float *) node->data, node->nb[1], node->nb[2], a->ne[0], a->ne[1], a->ne[2]));
 }
 
@@ -581,12 +635,11 @@ int try_fuse_epilogue(be_ctx * c, ggml_cgraph * cgraph, int i) {
                                    (float *) last->data);
     }
     if (st == B200_ERR_UNSUPPORTED) return 0;  // e.g. a weight pointer the TMA-staged kernel cannot take: run the nodes one by one
-    CHECK(st);
+    CHECK_RUN(c, st);
     return count;
 }
 
-ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
-    be_ctx * c = (be_ctx *) backend->context;
+ggml_status run_nodes(be_ctx * c, ggml_cgraph * cgraph) {
     for (int i = 0; i < cgraph->n_nodes; i++) {
         ggml_tensor * node = cgraph->nodes[i];
         if (is_noop(node)) continue;  // as ggml-cuda.cu:3333-3335
@@ -628,8 +681,8 @@ ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
                 o[n] = (float *) nx->data;
                 n++;
             }
-            if (n == 1) CHECK(b200_mul_mat(c->ctx, &descs[0], w[0], (const float *) node->src[1]->data, o[0]));
-            else CHECK(b200_mul_mat_shared_src1(c->ctx, n, descs, w, (const float *) node->src[1]->data, o));
+            if (n == 1) CHECK_RUN(c, b200_mul_mat(c->ctx, &descs[0], w[0], (const float *) node->src[1]->data, o[0]));
+            else CHECK_RUN(c, b200_mul_mat_shared_src1(c->ctx, n, descs, w, (const float *) node->src[1]->data, o));
             i += n - 1;
         } else if (node->op == GGML_OP_MUL_MAT_ID) {
             b200_mul_mat_id_desc d;
@@ -637,7 +690,7 @@ ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
                 GGML_LOG_ERROR("ggml-b200: unsupported MUL_MAT_ID reached graph_compute (%s)\n", node->name);
                 return GGML_STATUS_FAILED;
             }
-            CHECK(b200_mul_mat_id(c->ctx, &d, node->src[0]->data, (const float *) node->src[1]->data, (const int32_t *) node->src[2]->data,
+            CHECK_RUN(c, b200_mul_mat_id(c->ctx, &d, node->src[0]->data, (const float *) node->src[1]->data, (const int32_t *) node->src[2]->data,
                                   (float *) node->data));
         } else if (node->op == GGML_OP_GLU && glu_ok(node)) {
             run_glu(c, node);
@@ -650,6 +703,115 @@ ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
             return GGML_STATUS_FAILED;
         }
     }
+    return GGML_STATUS_SUCCESS;
+}
+
+// ---- CUDA-graph replay. The key of a cgraph is everything a launch depends on: per node the op, its parameters, shape, strides
+// and address, and shape, strides and address of every source (ggml_graph_node_properties, ggml-cuda.cu:2870-2935 does the same).
+// Weight CONTENTS are not part of it: kernels read them through the same pointers on every replay.
+void graph_key(const ggml_cgraph * cgraph, std::vector<uint64_t> & key, int * n_run, bool * capturable) {
+    *n_run = 0;
+    *capturable = true;
+    key.clear();
+    auto put_tensor = [&](const ggml_tensor * t) {
+        key.push_back((uint64_t) (uintptr_t) t->data);
+        key.push_back((uint64_t) t->type);
+        for (int d = 0; d < GGML_MAX_DIMS; d++) { key.push_back((uint64_t) t->ne[d]); key.push_back((uint64_t) t->nb[d]); }
+    };
+    for (int i = 0; i < cgraph->n_nodes; i++) {
+        const ggml_tensor * n = cgraph->nodes[i];
+        if (is_noop(n)) continue;
+        (*n_run)++;
+        key.push_back((uint64_t) n->op | ((uint64_t) n->flags << 32));
+        put_tensor(n);
+        uint64_t w[GGML_MAX_OP_PARAMS / sizeof(uint64_t)];
+        memcpy(w, n->op_params, sizeof(w));
+        for (uint64_t v : w) key.push_back(v);
+        for (int k = 0; k < GGML_MAX_SRC; k++) {
+            const ggml_tensor * s = n->src[k];
+            if (!s) { key.push_back(~(uint64_t) 0); continue; }
+            put_tensor(s);
+            if (s->buffer && buft_is_split(s->buffer->buft)) *capturable = false;  // several streams and devices: launched directly
+        }
+    }
+}
+
+uint64_t hash_key(const std::vector<uint64_t> & key) {
+    uint64_t h = 0xcbf29ce484222325ull;
+    for (uint64_t v : key) { h ^= v; h *= 0x100000001b3ull; h ^= h >> 29; }
+    return h;
+}
+
+void evict_graphs(be_ctx * c) {  // bounded cache: drop the least recently used half
+    std::vector<uint64_t> stamps;
+    for (auto & kv : c->graphs) for (auto & g : kv.second) stamps.push_back(g.stamp);
+    std::sort(stamps.begin(), stamps.end());
+    const uint64_t cut = stamps[stamps.size() / 2];
+    b200_ctx_synchronize(c->ctx);
+    for (auto it = c->graphs.begin(); it != c->graphs.end();) {
+        auto & v = it->second;
+        for (size_t i = 0; i < v.size();) {
+            if (v[i].stamp < cut) { b200_graph_destroy(v[i].exec); v.erase(v.begin() + (long) i); c->n_graphs--; }
+            else i++;
+        }
+        it = v.empty() ? c->graphs.erase(it) : std::next(it);
+    }
+}
+
+std::atomic<uint64_t> g_graph_replays{ 0 };  // proc address "ggml_backend_b200_graph_replays" (tests, bench.py)
+uint64_t graph_replays() { return g_graph_replays.load(std::memory_order_relaxed); }
+
+ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
+    be_ctx * c = (be_ctx *) backend->context;
+    if (!c->use_graphs) return run_nodes(c, cgraph);
+    static thread_local std::vector<uint64_t> key;
+    int  n_run = 0;
+    bool capturable = true;
+    graph_key(cgraph, key, &n_run, &capturable);
+    if (!capturable || n_run < c->graph_min_nodes) return run_nodes(c, cgraph);
+    auto & bucket = c->graphs[hash_key(key)];
+    be_ctx::cached_graph * g = nullptr;
+    for (auto & e : bucket) if (e.key == key) { g = &e; break; }
+    if (!g) {
+        if (c->n_graphs >= 1024) {
+            evict_graphs(c);
+            return be_graph_compute(backend, cgraph);  // `bucket` may be gone
+        }
+        bucket.emplace_back();
+        g = &bucket.back();
+        g->key = key;
+        c->n_graphs++;
+    }
+    g->stamp = ++c->graph_clock;
+    g->seen++;
+    if (g->exec) {
+        CHECK(b200_graph_launch(c->ctx, g->exec));
+        g_graph_replays.fetch_add(1, std::memory_order_relaxed);
+        return GGML_STATUS_SUCCESS;
+    }
+    // first appearance: launched directly (this also sizes the scratch buffers and fills the weight-expansion cache, neither of
+    // which can happen inside a capture); second appearance: captured, then launched
+    if (g->seen < 2 || g->bad) return run_nodes(c, cgraph);
+    if (b200_graph_capture_begin(c->ctx) != B200_OK) { g->bad = true; return run_nodes(c, cgraph); }
+    c->capturing = true;
+    ggml_status st = GGML_STATUS_SUCCESS;
+    bool ok = true;
+    try {
+        st = run_nodes(c, cgraph);
+    } catch (const capture_failed &) {
+        ok = false;
+    }
+    c->capturing = false;
+    b200_graph * exec = nullptr;
+    if (b200_graph_capture_end(c->ctx, &exec) != B200_OK || !ok || st != GGML_STATUS_SUCCESS) {
+        if (exec) b200_graph_destroy(exec);
+        g->bad = true;
+        GGML_LOG_DEBUG("ggml-b200: CUDA graph capture of a %d-node cgraph failed (%s); launching directly\n", n_run, b200_last_error());
+        return run_nodes(c, cgraph);
+    }
+    g->exec = exec;
+    CHECK(b200_graph_launch(c->ctx, g->exec));
+    g_graph_replays.fetch_add(1, std::memory_order_relaxed);
     return GGML_STATUS_SUCCESS;
 }
 
@@ -705,7 +867,8 @@ ggml_backend_t dev_init_backend(ggml_backend_dev_t dev, const char *) {
     // this backend owns its buffers and reports every write to them (drop_cached), so the int8 expansion of a weight
     // matrix used by the tcgen05 prefill kernel is built once and kept (GGML_B200_WEIGHT_CACHE=0 rebuilds it per call)
     const char * wc = getenv("GGML_B200_WEIGHT_CACHE");
-    b200_ctx_set_weight_cache(ctx, !(wc && !atoi(wc)));
+    const bool weight_cache = !(wc && !atoi(wc));
+    b200_ctx_set_weight_cache(ctx, weight_cache);
     // every src0 this backend sees lives in a buffer it allocated with b200_malloc and frees with b200_free (which drops the
     // learned next-kernel predictions), so the decode weight prefetch is safe to leave on
     b200_ctx_set_prefetch(ctx, 32);
@@ -713,6 +876,10 @@ ggml_backend_t dev_init_backend(ggml_backend_dev_t dev, const char *) {
     be_ctx * c = new be_ctx{ d->device, ctx, d->name, !(nf && atoi(nf)) };
     const char * ne = getenv("GGML_B200_DISABLE_EPILOGUE_FUSION");
     c->fuse_epilogue = c->fuse && !(ne && atoi(ne));
+    c->weight_cache  = weight_cache;
+    const char * ng = getenv("GGML_B200_DISABLE_GRAPHS");
+    c->use_graphs = !(ng && atoi(ng));
+    if (const char * mn = getenv("GGML_B200_GRAPH_MIN_NODES")) c->graph_min_nodes = std::max(1, atoi(mn));
     return new ggml_backend{ be_guid(), be_iface, dev, c };
 }
 ggml_backend_buffer_type_t dev_buffer_type(ggml_backend_dev_t dev) { return &((dev_ctx *) dev->context)->buft; }
@@ -723,14 +890,9 @@ bool dev_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) 
 }
 
 bool dev_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
-    // tensors must live in our buffers when they are already allocated (llama probes with 0-byte buffers of the
-    // candidate buft, src/llama-model.cpp:165-305, and test-backend-ops asks for leaves and views too, :1265-1272)
-    for (int i = 0; i < GGML_MAX_SRC; i++) {
-        const ggml_tensor * s = op->src[i];
-        if (s && s->buffer && !dev_supports_buft(dev, s->buffer->buft) && op->op != GGML_OP_NONE) {
-            // weights in a foreign buffer are handled by the scheduler through offload_op copies; activations likewise
-        }
-    }
+    // answered for hypothetical tensors too: llama probes with 0-byte buffers of the candidate buft (src/llama-model.cpp:165-305)
+    // and test-backend-ops asks for leaves and views (:1265-1272). Sources in foreign buffers are the scheduler's business
+    // (it copies them in: offload_op, ggml-backend.cpp:750-772).
     switch (op->op) {
         case GGML_OP_NONE:
         case GGML_OP_RESHAPE:
@@ -855,6 +1017,7 @@ void * reg_proc_address(ggml_backend_reg_t, const char * name) {
     if (!strcmp(name, "ggml_backend_get_features")) return (void *) reg_features;
     if (!strcmp(name, "ggml_backend_split_buffer_type")) return (void *) split_buffer_type;
     if (!strcmp(name, "ggml_backend_b200_fused_epilogues")) return (void *) fused_epilogues;  // uint64_t (*)(void): K7 launches so far
+    if (!strcmp(name, "ggml_backend_b200_graph_replays")) return (void *) graph_replays;      // uint64_t (*)(void): CUDA-graph launches so far
     // "ggml_backend_set_n_threads", "ggml_backend_dev_get_extra_bufts": not provided
     return nullptr;
 }

@@ -28,6 +28,7 @@ struct b200_ctx {
     bool         own_stream = false;
     int          sm_count   = 148;
     uint64_t     launches   = 0;
+    uint64_t     capture_launches0 = 0;         // launch counter when b200_graph_capture_begin was called
     int          force_path = B200_PATH_AUTO;
     // scratch: quantized activations (grow-only; stream ordered because one stream per context)
     void *       scratch      = nullptr;
