@@ -71,6 +71,8 @@ def test_greedy_stream_matches_ggml_cpu(pkg, tmp_path, tname):
     """4 layers of Llama-3-8B geometry (n_embd 4096, n_ff 14336, GQA 32/8): 64-token prompt + 256 generated tokens, B200 backend
     against ggml-cpu, for the file / memory-buffer / split-future loaders"""
     _need_harness()
+    if os.environ.get("B200_GREEDY_TYPES") and tname not in os.environ["B200_GREEDY_TYPES"].split(","):
+        pytest.skip("not in B200_GREEDY_TYPES")
     if not pkg.BACKEND_PATH.exists():
         pytest.fail("libggml-b200.so missing: build it with __graft_entry__.build()")
     prefix = tmp_path / f"parity_{tname}"
@@ -91,5 +93,5 @@ def test_greedy_stream_matches_ggml_cpu(pkg, tmp_path, tname):
                             f"top-2 logit margin there: cpu {cpu['margins'][d]:.3g}, b200 {got['margins'][d]:.3g}")
     out = ROOT / "gpurun_out"
     if out.exists():
-        (out / f"greedy_{tname}.json").write_text(json.dumps(report, indent=1))
+        (out / f"greedy_{os.environ.get('B200_GREEDY_TAG', 'default')}_{tname}.json").write_text(json.dumps(report, indent=1))
     assert not failures, "\n".join(failures)
