@@ -277,7 +277,7 @@ int refh_stack_e2e(int reg, int dev, int n_threads, int type, int n_mats, const 
     ggml_backend_dev_t device = ggml_backend_get_device(g.be);
     const size_t n_nodes = (size_t) 3 * n_mats + n_x + 16;
     ggml_init_params ip  = { ggml_tensor_overhead() * n_nodes + ggml_graph_overhead_custom(n_nodes, false), nullptr, true };
-    ggml_init_params ipo = { ggml_tensor_overhead() * ((size_t) n_mats + 8), nullptr, true };
+    ggml_init_params ipo = { ggml_tensor_overhead() * ((size_t) n_mats + 8) + ggml_graph_overhead_custom(n_nodes, false), nullptr, true };  // results + pool + the cgraph
     g.ctx = ggml_init(ip);
     ggml_context * octx = ggml_init(ipo);
     if (!g.ctx || !octx) return 1;
