@@ -167,6 +167,20 @@ B200_API b200_status  b200_mul_mat_shared_src1(b200_ctx * ctx, int n_ops, const 
 B200_API b200_status  b200_mul_mat_host(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * src0, int w_on_device,
                                         const float * src1_host, float * dst_host);
 
+/* GGML_OP_MUL_MAT for callers that may not allocate device memory (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE. Same arithmetic and
+ * kernels as b200_mul_mat's decode path (K1 quantizes src1 into unit records, the TMA-staged mat-vec kernels read them), but the
+ * records live in a file-scope `static __device__` array of B200_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds
+ * until exit; the call performs no cudaMalloc / cudaFree and calls no allocating library routine. Limits (B200_ERR_UNSUPPORTED
+ * with a message otherwise): plain 2-D MUL_MAT (ne02 = ne03 = ne12 = ne13 = 1), 1..8 activation columns, K % 256 == 0,
+ * columns x K/256 <= B200_NOALLOC_MAX_UNITS (e.g. 8 columns of K = 32768), 16-byte aligned weight rows, not in row-split mode.
+ * All calls on a device share the array, which keeps the last call's records (every byte that is read is rewritten by the call
+ * itself, nothing needs to start at zero): calls that overlap on the GPU - two streams or contexts of one device - race. */
+#define B200_NOALLOC_MAX_UNITS     1024
+#define B200_NOALLOC_SCRATCH_BYTES (B200_NOALLOC_MAX_UNITS * (272 + 16))
+B200_API b200_status  b200_mul_mat_noalloc(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * src0, const float * src1, float * dst);
+B200_API size_t       b200_mul_mat_noalloc_max_units(void);
+
 /* ---------------------------------------------------------------- K5/K6: MUL_MAT_ID ---- */
 
 /* as = experts [K, M, n_as] of `type` (expert e at as + e*nb02); b F32 [K, ne11, n_tok] (nb11, nb12);

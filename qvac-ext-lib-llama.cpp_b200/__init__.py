@@ -37,6 +37,7 @@ EXPORTS = [
     "b200_mul_mat_id", "b200_mm_ids_sort", "b200_ctx_set_row_split", "b200_ctx_set_row_split_ll", "b200_ctx_set_row_split_deferred", "b200_ctx_row_split_wait", "b200_ctx_set_weight_cache", "b200_ctx_set_mmq_f16", "b200_ctx_set_prefetch", "b200_ctx_trace", "b200_ctx_trace_read", "b200_weight_cache_invalidate", "b200_weight_cache_clear", "b200_weight_cache_bytes",
     "b200_mul_mat_fused_supported", "b200_mul_mat_fused", "b200_mul_mat_id_fused_supported", "b200_mul_mat_id_fused",
     "b200_glu", "b200_add", "b200_mul", "b200_add_id",
+    "b200_mul_mat_noalloc", "b200_mul_mat_noalloc_max_units",
 ]
 
 
@@ -155,6 +156,8 @@ def lib() -> C.CDLL:
         L.b200_quantize_units.argtypes = [vp, ci, vp, i64, i64, sz, vp, vp]
         L.b200_mul_mat_supported.argtypes = [C.POINTER(MulMatDesc)]
         L.b200_mul_mat.argtypes = [vp, C.POINTER(MulMatDesc), vp, vp, vp]
+        L.b200_mul_mat_noalloc.argtypes = [vp, C.POINTER(MulMatDesc), vp, vp, vp]
+        L.b200_mul_mat_noalloc_max_units.restype = sz
         L.b200_mul_mat_shared_src1.argtypes = [vp, ci, C.POINTER(MulMatDesc), C.POINTER(vp), vp, C.POINTER(vp)]
         L.b200_mul_mat_host.argtypes = [vp, C.POINTER(MulMatDesc), vp, ci, vp, vp]
         L.b200_mul_mat_id_supported.argtypes = [C.POINTER(MulMatIdDesc)]

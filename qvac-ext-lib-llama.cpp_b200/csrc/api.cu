@@ -937,3 +937,68 @@ b200_status b200_mul_mat_host(b200_ctx * ctx, const b200_mul_mat_desc * d, const
     return B200_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------ MUL_MAT without allocations
+//
+// b200_mul_mat_noalloc: the decode mat-vec for callers that may not allocate device memory (code under CUDA-graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc). No counterpart in the reference.
+// It is the "pre-quantized activations" path of b200_mul_mat - K1 writes src1's unit records to scratch, the
+// TMA-staged mat-vec kernels read them - with the scratch in a file-scope __device__ array instead of the context's grow-on-demand
+// cudaMalloc buffer. Every GPU that loads the library holds the array (B200_NOALLOC_SCRATCH_BYTES) until exit.
+// The array is shared by every call on a device and keeps the last call's records: K1 rewrites every byte the mat-vec kernels
+// read (256 int8 + 16 bytes of scales / block sums + the 16-byte aux record per unit), so nothing has to start at zero, but two
+// calls that overlap on the GPU (different streams or contexts of one device) race on it.
+
+static __device__ __align__(256) uint8_t g_noalloc_scratch[B200_NOALLOC_MAX_UNITS * (ACT_MAIN + ACT_AUX)];
+
+// host code: the symbol's name is a host-side stand-in, not a device address - ask the runtime, once per device, with it current
+static b200_status noalloc_scratch_ptr(int device, uint8_t ** out) {
+    static std::mutex mutex;
+    static uint8_t *  ptrs[64] = {};
+    if (device < 0 || device >= 64) return fail(B200_ERR_ARG, "device %d out of range", device);
+    std::lock_guard<std::mutex> lock(mutex);
+    if (!ptrs[device]) {
+        CU(cudaSetDevice(device));
+        void * p = nullptr;
+        CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p || (uintptr_t) p % 256 != 0) return fail(B200_ERR_CUDA, "cudaGetSymbolAddress returned an unusable address %p", p);
+        ptrs[device] = (uint8_t *) p;
+    }
+    *out = ptrs[device];
+    return B200_OK;
+}
+
+size_t b200_mul_mat_noalloc_max_units(void) { return B200_NOALLOC_MAX_UNITS; }
+
+b200_status b200_mul_mat_noalloc(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * src0, const float * src1, float * dst) {
+    if (!ctx || !d) return fail(B200_ERR_ARG, "null argument");
+    if (!b200_mul_mat_supported(d)) return fail(B200_ERR_UNSUPPORTED, "MUL_MAT geometry/type not supported");
+    if (d->ne02 != 1 || d->ne03 != 1 || d->ne12 != 1 || d->ne13 != 1) return fail(B200_ERR_UNSUPPORTED, "b200_mul_mat_noalloc: plain 2-D MUL_MAT only");
+    if (d->ne11 < 1 || d->ne11 > MV_MAX_COLS) return fail(B200_ERR_UNSUPPORTED, "b200_mul_mat_noalloc: 1..%d activation columns (got %lld)", MV_MAX_COLS, (long long) d->ne11);
+    if (d->ne00 % 256 != 0) return fail(B200_ERR_UNSUPPORTED, "b200_mul_mat_noalloc: K=%lld is not a multiple of 256", (long long) d->ne00);
+    const int64_t U = d->ne00 / 256, N = d->ne11;
+    if (N * U > (int64_t) B200_NOALLOC_MAX_UNITS)
+        return fail(B200_ERR_UNSUPPORTED, "b200_mul_mat_noalloc: %lld columns x K=%lld need %lld activation units; the static scratch holds %d (columns x K <= %lld)",
+                    (long long) N, (long long) d->ne00, (long long) (N * U), B200_NOALLOC_MAX_UNITS, (long long) B200_NOALLOC_MAX_UNITS * 256);
+    if (ctx->split.n_ranks > 1) return fail(B200_ERR_UNSUPPORTED, "b200_mul_mat_noalloc: not in row-split mode");
+    if (d->ne01 == 0) return B200_OK;
+    if (!src0 || !src1 || !dst) return fail(B200_ERR_ARG, "null argument");
+    if (!fast_layout_ok(d->type, d->ne00, src0, d->nb01, d->nb02, d->nb03))
+        return fail(B200_ERR_UNSUPPORTED, "b200_mul_mat_noalloc: weights must be 16-byte aligned rows of whole 256-weight units (q6_K: K %% 2048 == 0)");
+    if (N >= 3 && mv_mma_usable(d->type) && !mv_mma_fits(d->type, d->ne00)) {
+        mv_cfg cfg;
+        if (!pick_mv_cfg(ctx, d->type, (int) U, 1, &cfg)) return fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) d->ne00);
+    }
+    uint8_t * scratch = nullptr;
+    if (b200_status st = noalloc_scratch_ptr(ctx->device, &scratch)) return st;
+    CU(cudaSetDevice(ctx->device));
+    uint8_t * am = scratch, * ax = scratch + (size_t) B200_NOALLOC_MAX_UNITS * ACT_MAIN;
+    int l = 0;
+    CU(quantize_units(act_kind_for(d->type), src1, d->ne00, N, d->nb11, am, ax, ctx->stream, &l, ctx->pdl));
+    ctx->launches += l;
+    const uint8_t * ws[1] = { (const uint8_t *) src0 };
+    size_t          nb01s[1] = { d->nb01 };
+    int64_t         Ms[1] = { d->ne01 }, dcs[1] = { (int64_t) (d->nb1 / 4) };
+    float *         ds[1] = { dst };
+    return mv_fast_run(ctx, d->type, d->ne00, 1, ws, nb01s, Ms, ds, dcs, (int) N, nullptr, d->nb11, am, ax);
+}
