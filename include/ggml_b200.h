@@ -66,6 +66,12 @@ B200_API b200_status  b200_ctx_synchronize(b200_ctx * ctx);                  /* 
 B200_API const char * b200_last_error(void);                                 /* thread-local message of the last failure */
 B200_API uint64_t     b200_ctx_launch_count(const b200_ctx * ctx);           /* kernels launched so far (bench.py gpu_launches) */
 B200_API void         b200_ctx_set_force_path(b200_ctx * ctx, int path);     /* B200_PATH_* */
+/* Exact mode (env GGML_B200_EXACT=1): every MUL_MAT / MUL_MAT_ID of the context runs on a one-thread-per-element kernel that
+ * performs the fp32 operations of ggml-cpu's generic ggml_vec_dot_<type>_q8_* (ggml-cpu/quants.c:115-150, 305-333, 550-623,
+ * 625-703, 705-758) in the same order with the same roundings: results are bit-identical to the reference's x86-64 baseline
+ * build of ggml-cpu. For validation (free-running greedy token streams against ggml-cpu); one to two orders of magnitude
+ * slower than the default kernels, whose integer block sums are the same but whose fp32 summation order is not. */
+B200_API void         b200_ctx_set_exact(b200_ctx * ctx, int enable);
 
 /* ---------------------------------------------------------------- memory ---- */
 

@@ -216,6 +216,7 @@ int cmd_run(int argc, char ** argv) {
     int ngl = 0, n_prompt = 64, n_gen = 256, n_threads = 0, n_split = 3, n_batch = 512, n_ubatch = 512;
     uint64_t seed = 5;
     bool quiet = true, mmap = true;
+    std::string force_path;   // teacher forcing: a file of token ids; token i of it is fed after step i instead of this run's own argmax
     for (int i = 0; i < argc; i++) {
         const std::string a = argv[i];
         auto val = [&]() { return i + 1 < argc ? argv[++i] : ""; };
@@ -232,6 +233,7 @@ int cmd_run(int argc, char ** argv) {
         else if (a == "--seed") seed = strtoull(val(), nullptr, 10);
         else if (a == "--verbose") quiet = false;
         else if (a == "--no-mmap") mmap = false;
+        else if (a == "--force") force_path = val();
     }
     if (quiet) llama_log_set([](ggml_log_level level, const char * text, void *) { if (level >= GGML_LOG_LEVEL_ERROR) fputs(text, stderr); }, nullptr);
     for (const std::string & b : backends) {
@@ -283,6 +285,7 @@ int cmd_run(int argc, char ** argv) {
     cp.n_threads_batch = n_threads;
     cp.offload_kqv     = false;  // the KV cache and the attention ops stay on the CPU backend: the backend under test owns MUL_MAT(_ID) only
     cp.no_perf         = true;
+    cp.flash_attn_type = LLAMA_FLASH_ATTN_TYPE_DISABLED;  // one attention arithmetic whatever the devices
     llama_context * ctx = llama_init_from_model(model, cp);
     if (!ctx) { fprintf(stderr, "llama_harness: context creation failed\n"); return 1; }
     const int n_vocab = llama_vocab_n_tokens(llama_model_get_vocab(model));
@@ -290,8 +293,15 @@ int cmd_run(int argc, char ** argv) {
     std::vector<llama_token> toks;
     uint64_t s = seed;
     for (int i = 0; i < n_prompt; i++) toks.push_back((llama_token) (splitmix(s) % (uint64_t) n_vocab));
+    std::vector<llama_token> forced;
+    if (!force_path.empty()) {
+        std::ifstream f(force_path);
+        long v;
+        while (f >> v) forced.push_back((llama_token) v);
+        if ((int) forced.size() < n_gen) { fprintf(stderr, "llama_harness: %s holds %zu tokens, need %d\n", force_path.c_str(), forced.size(), n_gen); return 2; }
+    }
     std::vector<llama_token> out;
-    std::vector<float> margins;
+    std::vector<float> margins, deficits;   // deficit: this run's top logit minus its logit of the forced token (0 where they agree)
     auto pick = [&]() {
         const float * lg = llama_get_logits_ith(ctx, -1);
         int best = 0;
@@ -301,6 +311,7 @@ int cmd_run(int argc, char ** argv) {
             else if (lg[v] > b2) b2 = lg[v];
         }
         margins.push_back(b1 - b2);
+        if (!forced.empty()) deficits.push_back(b1 - lg[forced[margins.size() - 1]]);
         return (llama_token) best;
     };
     const auto t0 = std::chrono::steady_clock::now();
@@ -308,11 +319,13 @@ int cmd_run(int argc, char ** argv) {
     const double prompt_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     llama_token cur = pick();
     out.push_back(cur);
+    if (!forced.empty()) cur = forced[0];
     const auto t1 = std::chrono::steady_clock::now();
     for (int i = 1; i < n_gen; i++) {
         if (llama_decode(ctx, llama_batch_get_one(&cur, 1)) != 0) { fprintf(stderr, "llama_decode(token %d) failed\n", i); return 1; }
         cur = pick();
         out.push_back(cur);
+        if (!forced.empty()) cur = forced[i];
     }
     const double gen_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
 
@@ -321,6 +334,8 @@ int cmd_run(int argc, char ** argv) {
     for (size_t i = 0; i < out.size(); i++) printf("%s%d", i ? ", " : "", out[i]);
     printf("], \"margins\": [");
     for (size_t i = 0; i < margins.size(); i++) printf("%s%.6g", i ? ", " : "", margins[i]);
+    printf("], \"deficits\": [");
+    for (size_t i = 0; i < deficits.size(); i++) printf("%s%.6g", i ? ", " : "", deficits[i]);
     printf("]}\n");
     fflush(stdout);
     llama_free(ctx);

@@ -26,7 +26,7 @@ PATH_AUTO, PATH_MMVQ, PATH_MMQ, PATH_SIMPLE = 0, 1, 2, 3
 
 EXPORTS = [
     "b200_device_count", "b200_device_info", "b200_device_memory", "b200_ctx_create", "b200_ctx_destroy", "b200_ctx_device",
-    "b200_ctx_stream", "b200_ctx_synchronize", "b200_last_error", "b200_ctx_launch_count", "b200_ctx_set_force_path",
+    "b200_ctx_stream", "b200_ctx_synchronize", "b200_last_error", "b200_ctx_launch_count", "b200_ctx_set_force_path", "b200_ctx_set_exact",
     "b200_malloc", "b200_free", "b200_host_malloc", "b200_host_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_memcpy_d2d",
     "b200_memcpy_peer", "b200_memset", "b200_memcpy_h2d_async", "b200_memcpy_d2h_async", "b200_memcpy_d2d_async",
     "b200_memcpy2d_async", "b200_enable_peer_access", "b200_memcpy_peer_async",
@@ -148,6 +148,8 @@ def lib() -> C.CDLL:
         L.b200_ctx_launch_count.restype = C.c_uint64
         L.b200_ctx_set_force_path.argtypes = [vp, ci]
         L.b200_ctx_set_force_path.restype = None
+        L.b200_ctx_set_exact.argtypes = [vp, ci]
+        L.b200_ctx_set_exact.restype = None
         L.b200_device_info.argtypes = [ci, C.c_char_p, sz, C.c_char_p, sz, C.POINTER(ci), C.POINTER(ci), C.POINTER(ci)]
         L.b200_host_malloc.argtypes = [sz, C.POINTER(vp)]
         L.b200_host_free.argtypes = [vp]
@@ -238,6 +240,10 @@ class Context:
 
     def force_path(self, p: int):
         lib().b200_ctx_set_force_path(self.h, p)
+
+    def exact(self, enable: bool):
+        """every MUL_MAT(_ID) on the exact-order kernel: bit-identical to ggml-cpu's generic build (validation only)"""
+        lib().b200_ctx_set_exact(self.h, 1 if enable else 0)
 
     def row_split(self, rank: int, dst_ptrs, sync_ptrs):
         """fused all-gather mode: dst_ptrs[r] / sync_ptrs[r] = base address of the symmetric dst region / sync words on rank r"""

@@ -108,6 +108,9 @@ b200_status b200_ctx_create(int device, void * stream, b200_ctx ** out) {
         else if (!strcmp(s, "mmq")) c->force_path = B200_PATH_MMQ;
         else if (!strcmp(s, "simple")) c->force_path = B200_PATH_SIMPLE;
     }
+    if (const char * s = getenv("GGML_B200_EXACT")) {
+        if (atoi(s)) { c->exact = 1; c->force_path = B200_PATH_SIMPLE; }
+    }
     if (const char * s = getenv("GGML_B200_MV_WARPS")) c->mv_warps = atoi(s);
     if (const char * s = getenv("GGML_B200_MV_STAGES")) c->mv_stages = atoi(s);
     if (const char * s = getenv("GGML_B200_PDL")) c->pdl = atoi(s) != 0;
@@ -141,7 +144,11 @@ void b200_ctx_destroy(b200_ctx * ctx) {
 int          b200_ctx_device(const b200_ctx * ctx) { return ctx->device; }
 void *       b200_ctx_stream(const b200_ctx * ctx) { return (void *) ctx->stream; }
 uint64_t     b200_ctx_launch_count(const b200_ctx * ctx) { return ctx->launches; }
-void         b200_ctx_set_force_path(b200_ctx * ctx, int path) { ctx->force_path = path; }
+void         b200_ctx_set_force_path(b200_ctx * ctx, int path) { ctx->force_path = ctx->exact ? B200_PATH_SIMPLE : path; }
+void         b200_ctx_set_exact(b200_ctx * ctx, int enable) {
+    ctx->exact      = enable != 0;
+    ctx->force_path = enable ? B200_PATH_SIMPLE : B200_PATH_AUTO;
+}
 void         b200_ctx_set_weight_cache(b200_ctx * ctx, int enable) { ctx->weight_cache = enable != 0; }
 void         b200_ctx_set_mmq_f16(b200_ctx * ctx, int enable) { ctx->mmq_f16 = enable != 0; }
 b200_status  b200_ctx_trace(b200_ctx * ctx, int n_slots) {
@@ -819,6 +826,7 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
                     sp.M      = (int) di.ne01;
                     sp.K      = (int) K;
                     sp.ncols  = (int) (N - c0 < 65535 ? N - c0 : 65535);
+                    sp.exact  = ctx->exact;
                     CU(mv_simple_launch(type, sp, ctx->stream));
                     ctx->launches++;
                 }

@@ -889,6 +889,14 @@ bool dev_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) 
     return (buft_is_b200(buft) && buft->device == dev) || buft_is_split(buft);  // as ggml-cuda.cu:4587-4590
 }
 
+// GGML_B200_EXACT=1: validation mode - the MUL_MAT(_ID) kernels reproduce ggml-cpu's generic fp32 operation order bit for bit
+// (b200_ctx_set_exact), and the backend declines GLU (its libm-accurate expf is not ggml-cpu's) so that everything around the
+// matmuls is computed by the same ggml-cpu code as in a CPU-only run
+bool exact_mode() {
+    static const bool on = [] { const char * s = getenv("GGML_B200_EXACT"); return s && atoi(s) != 0; }();
+    return on;
+}
+
 bool dev_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
     // answered for hypothetical tensors too: llama probes with 0-byte buffers of the candidate buft (src/llama-model.cpp:165-305)
     // and test-backend-ops asks for leaves and views (:1265-1272). Sources in foreign buffers are the scheduler's business
@@ -918,7 +926,7 @@ bool dev_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
         // K7: the nodes the fused mat-vec epilogue absorbs; owned stand-alone as well so that the scheduler keeps
         // {MUL_MAT, ADD, GLU} chains on this backend (the reference: ggml-cuda.cu:4331-4345 GLU, :4509-4516 ADD / ADD_ID)
         case GGML_OP_GLU:
-            return glu_ok(op);
+            return !exact_mode() && glu_ok(op);
         case GGML_OP_ADD:
         case GGML_OP_MUL:  // same broadcasting kernel; the expert-weight scaling behind a fused MoE FFN
             return add_ok(op);

@@ -30,6 +30,7 @@ struct b200_ctx {
     uint64_t     launches   = 0;
     uint64_t     capture_launches0 = 0;         // launch counter when b200_graph_capture_begin was called
     int          force_path = B200_PATH_AUTO;
+    int          exact      = 0;                // b200_ctx_set_exact: every MUL_MAT(_ID) on mv_exact_kernel (bit-identical to ggml-cpu's generic build)
     // scratch: quantized activations (grow-only; stream ordered because one stream per context)
     void *       scratch      = nullptr;
     size_t       scratch_size = 0;

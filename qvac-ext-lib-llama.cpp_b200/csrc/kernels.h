@@ -285,6 +285,7 @@ struct MvSimpleParams {
     int64_t         dst_cs;
     int             M, K, ncols;
     MvIds           ids;      // ids.ids != nullptr: blockIdx.y = pair, act row = t*ne11 + i % ne11
+    int             exact;    // 1: mv_exact_kernel - fp32 operation order of ggml-cpu's generic vec_dots, bit-identical results
 };
 cudaError_t mv_simple_launch(int type, const MvSimpleParams & p, cudaStream_t st);
 

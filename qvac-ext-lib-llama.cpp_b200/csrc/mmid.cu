@@ -255,6 +255,7 @@ static b200_status mul_mat_id_impl(b200_ctx * ctx, const b200_mul_mat_id_desc * 
     sp.K      = (int) K;
     sp.ncols  = (int) n_pairs;
     sp.ids    = mi;
+    sp.exact  = ctx->exact;
     CU(mv_simple_launch(d->type, sp, ctx->stream));
     ctx->launches++;
     return B200_OK;

@@ -866,8 +866,133 @@ __global__ void __launch_bounds__(128) mv_simple_kernel(const MvSimpleParams p) 
     if (lane == 0) p.dst[dst_off + (int64_t) col * p.dst_cs + row] = acc;
 }
 
+// ------------------------------------------------------------------------------------------------
+// exact kernel (b200_ctx_set_exact / GGML_B200_EXACT=1): one thread per dst element, walking the row the way the generic scalar
+// ggml_vec_dot_q4_0_q8_0 / q8_0_q8_0 / q4_K_q8_K / q5_K_q8_K / q6_K_q8_K do (ggml-cpu/quants.c:115-150, 305-333, 550-623, 625-703,
+// 705-758): the same integer sums AND the same order and rounding of every fp32 operation (one accumulator walked block by block
+// for q4_0 / q8_0; eight interleaved lane accumulators plus the min accumulator for the K-quants; __fmul_rn / __fadd_rn so that
+// nothing is contracted into an FMA - the x86-64 baseline build of ggml-cpu has none). Results are BIT-IDENTICAL to ggml-cpu's
+// generic build, which is what makes a free-running greedy token stream comparable at all: activation quantization turns any
+// fp32 difference of an earlier layer into rounding flips, so two correct implementations with different summation orders
+// (the reference's own x64 and AVX2 builds included) drift apart within a few dozen tokens. Slow by design; never the default.
+// ------------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ float ld_f32_unaligned2(const uint8_t * p) { return __uint_as_float(ld16x2(p)); }
+
+template <int TYPE>
+__global__ void __launch_bounds__(128) mv_exact_kernel(const MvSimpleParams p) {
+    const int row = blockIdx.x * 128 + threadIdx.x;
+    int     col = blockIdx.y, act_row = blockIdx.y;
+    int64_t w_off = 0, dst_off = 0;
+    if (row >= p.M) return;
+    if (p.ids.ids) {
+        const int t = col / p.ids.n_used, i = col - t * p.ids.n_used;
+        const int e = p.ids.ids[(int64_t) t * p.ids.ids_rs + i];
+        if (e < 0 || e >= p.ids.n_as) return;
+        w_off   = (int64_t) e * p.ids.nb02;
+        dst_off = (int64_t) t * p.ids.dst_ts + (int64_t) i * p.ids.dst_is;
+        act_row = t * p.ids.ne11 + i % p.ids.ne11;
+        col     = 0;
+    }
+    const uint8_t * wr = p.w + w_off + (int64_t) row * p.nb01;
+    const uint8_t * ar = p.act + (int64_t) act_row * p.act_rs;
+    float sumf = 0.0f;
+    if (TYPE == B200_TYPE_Q4_0 || TYPE == B200_TYPE_Q8_0) {
+        constexpr int WB = TYPE == B200_TYPE_Q4_0 ? SZ_Q4_0 : SZ_Q8_0;
+        for (int b = 0; b < p.K / QK; b++) {
+            const uint8_t * wb = wr + (int64_t) b * WB;
+            const uint8_t * ab = ar + (int64_t) b * SZ_Q8_0;
+            const float     dx = half_bits_to_float(*(const uint16_t *) wb);
+            const float     dy = half_bits_to_float(*(const uint16_t *) ab);
+            const int8_t *  q8 = (const int8_t *) (ab + 2);
+            int sumi = 0;
+            if (TYPE == B200_TYPE_Q4_0) {
+                for (int j = 0; j < 16; j++) {
+                    const int v = wb[2 + j];
+                    sumi += ((v & 0xf) - 8) * q8[j] + ((v >> 4) - 8) * q8[j + 16];
+                }
+                sumf = __fadd_rn(sumf, __fmul_rn(__fmul_rn((float) sumi, dx), dy));  // sumf += sumi*dx*dy, left to right (quants.c:146)
+            } else {
+                const int8_t * qw = (const int8_t *) (wb + 2);
+                for (int j = 0; j < 32; j++) sumi += qw[j] * q8[j];
+                sumf = __fadd_rn(sumf, __fmul_rn((float) sumi, __fmul_rn(dx, dy)));  // sumf += sumi*(dx*dy) (quants.c:329)
+            }
+        }
+    } else {
+        float sums[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+        for (int b = 0; b < p.K / QK_K; b++) {
+            const uint8_t * ab = ar + (int64_t) b * SZ_Q8_K;
+            const float     yd = *(const float *) ab;
+            const int8_t *  q8 = (const int8_t *) (ab + 4);
+            const int16_t * bs = (const int16_t *) (ab + 4 + QK_K);
+            int lane[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+            if (TYPE == B200_TYPE_Q6_K) {
+                const uint8_t * wb = wr + (int64_t) b * SZ_Q6_K;
+                const int8_t *  sc = (const int8_t *) (wb + 192);
+                const float     d  = __fmul_rn(half_bits_to_float(*(const uint16_t *) (wb + 208)), yd);
+                for (int h = 0; h < 2; h++) {
+                    const uint8_t * ql = wb + 64 * h, * qh = wb + 128 + 32 * h;
+                    for (int l = 0; l < 32; l++) {
+                        const int q1 = (int) ((ql[l] & 0xF) | (((qh[l] >> 0) & 3) << 4)) - 32;
+                        const int q2 = (int) ((ql[l + 32] & 0xF) | (((qh[l] >> 2) & 3) << 4)) - 32;
+                        const int q3 = (int) ((ql[l] >> 4) | (((qh[l] >> 4) & 3) << 4)) - 32;
+                        const int q4 = (int) ((ql[l + 32] >> 4) | (((qh[l] >> 6) & 3) << 4)) - 32;
+                        const int i0 = 128 * h + l;
+                        lane[l & 7] += sc[(i0) / 16] * (q8[i0] * q1) + sc[(i0 + 32) / 16] * (q8[i0 + 32] * q2) +
+                                       sc[(i0 + 64) / 16] * (q8[i0 + 64] * q3) + sc[(i0 + 96) / 16] * (q8[i0 + 96] * q4);
+                    }
+                }
+#pragma unroll
+                for (int l = 0; l < 8; l++) sums[l] = __fadd_rn(sums[l], __fmul_rn(d, (float) lane[l]));
+            } else {
+                constexpr bool Q5 = TYPE == B200_TYPE_Q5_K;
+                const uint8_t * wb = wr + (int64_t) b * (Q5 ? SZ_Q5_K : SZ_Q4_K);
+                const uint32_t  h0 = ld16x2(wb), u0 = ld16x2(wb + 4), u1 = ld16x2(wb + 8), u2 = ld16x2(wb + 12);
+                const uint32_t sc4[2] = { u0 & 0x3f3f3f3fu, (u2 & 0x0f0f0f0fu) | ((u0 >> 2) & 0x30303030u) };
+                const uint32_t mn4[2] = { u1 & 0x3f3f3f3fu, ((u2 >> 4) & 0x0f0f0f0fu) | ((u1 >> 2) & 0x30303030u) };
+                int summin = 0;
+                for (int s = 0; s < 8; s++) {
+                    const int sc = (sc4[s >> 2] >> (8 * (s & 3))) & 0xff, mn = (mn4[s >> 2] >> (8 * (s & 3))) & 0xff;
+                    summin += (bs[2 * s] + bs[2 * s + 1]) * mn;
+                    const uint8_t * qq = wb + (Q5 ? 48 : 16) + 32 * (s >> 1);
+                    for (int l = 0; l < 32; l++) {
+                        int w = (s & 1) ? (qq[l] >> 4) : (qq[l] & 0xf);
+                        if (Q5) w += ((wb[16 + l] >> s) & 1) << 4;
+                        lane[l & 7] += sc * (q8[32 * s + l] * w);
+                    }
+                }
+                const float d    = __fmul_rn(half_bits_to_float((uint16_t) (h0 & 0xffff)), yd);
+                const float dmin = __fmul_rn(half_bits_to_float((uint16_t) (h0 >> 16)), yd);
+#pragma unroll
+                for (int l = 0; l < 8; l++) sums[l] = __fadd_rn(sums[l], __fmul_rn(d, (float) lane[l]));
+                sumf = __fsub_rn(sumf, __fmul_rn(dmin, (float) summin));
+            }
+        }
+#pragma unroll
+        for (int l = 0; l < 8; l++) sumf = __fadd_rn(sumf, sums[l]);
+    }
+    p.dst[dst_off + (int64_t) col * p.dst_cs + row] = sumf;
+}
+
+template <int TYPE>
+static void mv_exact_launch_t(const MvSimpleParams & p, cudaStream_t st) {
+    dim3 grid((unsigned) ((p.M + 127) / 128), (unsigned) p.ncols);
+    mv_exact_kernel<TYPE><<<grid, 128, 0, st>>>(p);
+}
+
 cudaError_t mv_simple_launch(int type, const MvSimpleParams & p, cudaStream_t st) {
     if (p.M == 0 || p.ncols == 0) return cudaSuccess;
+    if (p.exact) {
+        switch (type) {
+            case B200_TYPE_Q4_0: mv_exact_launch_t<B200_TYPE_Q4_0>(p, st); break;
+            case B200_TYPE_Q8_0: mv_exact_launch_t<B200_TYPE_Q8_0>(p, st); break;
+            case B200_TYPE_Q4_K: mv_exact_launch_t<B200_TYPE_Q4_K>(p, st); break;
+            case B200_TYPE_Q5_K: mv_exact_launch_t<B200_TYPE_Q5_K>(p, st); break;
+            case B200_TYPE_Q6_K: mv_exact_launch_t<B200_TYPE_Q6_K>(p, st); break;
+            default: return cudaErrorInvalidValue;
+        }
+        return cudaGetLastError();
+    }
     dim3 grid((unsigned) ((p.M + 3) / 4), (unsigned) p.ncols);
     switch (type) {
         case B200_TYPE_Q4_0: mv_simple_kernel<B200_TYPE_Q4_0><<<grid, 128, 0, st>>>(p); break;

@@ -24,12 +24,6 @@ for recipe in "$@"; do
     greedy)
       timeout 1500 python -m pytest tests/test_llama_greedy.py -m gpu -q > $O/${TAG}_greedy.log 2>&1
       echo "greedy rc=$? $(tail -1 $O/${TAG}_greedy.log)"; tail -30 $O/${TAG}_greedy.log | cut -c1-400;;
-    greedy-f16)   # the same streams with the fp16-operand prefill GEMM (GGML_B200_MMQ_F16=1)
-      GGML_B200_MMQ_F16=1 B200_GREEDY_TAG=f16 timeout 1500 python -m pytest tests/test_llama_greedy.py -m gpu -q > $O/${TAG}_greedy_f16.log 2>&1
-      echo "greedy-f16 rc=$? $(tail -1 $O/${TAG}_greedy_f16.log)"; tail -30 $O/${TAG}_greedy_f16.log | cut -c1-400;;
-    greedy-i8)    # ... and with the exact kind::i8 prefill kernels (GGML_B200_MMQ_F16=0)
-      GGML_B200_MMQ_F16=0 B200_GREEDY_TAG=i8 timeout 1500 python -m pytest tests/test_llama_greedy.py -m gpu -q > $O/${TAG}_greedy_i8.log 2>&1
-      echo "greedy-i8 rc=$? $(tail -1 $O/${TAG}_greedy_i8.log)"; tail -30 $O/${TAG}_greedy_i8.log | cut -c1-400;;
     bench)
       if [ -z "$rest" ]; then
         timeout 900 python bench.py --impl reference --steps 3 --warmup 1 > $O/${TAG}_bench_reference.json 2> $O/${TAG}_bench_reference.err
