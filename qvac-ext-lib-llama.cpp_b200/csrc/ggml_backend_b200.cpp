@@ -871,7 +871,7 @@ ggml_backend_t dev_init_backend(ggml_backend_dev_t dev, const char *) {
     b200_ctx_set_weight_cache(ctx, weight_cache);
     // every src0 this backend sees lives in a buffer it allocated with b200_malloc and frees with b200_free (which drops the
     // learned next-kernel predictions), so the decode weight prefetch is safe to leave on
-    b200_ctx_set_prefetch(ctx, 32);
+    b200_ctx_set_prefetch(ctx, 64);
     const char * nf = getenv("GGML_B200_DISABLE_FUSION");
     be_ctx * c = new be_ctx{ d->device, ctx, d->name, !(nf && atoi(nf)) };
     const char * ne = getenv("GGML_B200_DISABLE_EPILOGUE_FUSION");

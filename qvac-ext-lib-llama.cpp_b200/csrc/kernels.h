@@ -250,6 +250,7 @@ struct MvParams {
     int             rpg;      // rows per group: 32 / L when U <= 32, else 1
     int             slices;   // ceil(U / 32)
     int             n_cons, n_stages; // consumer warps (<= MV_MAX_CONS), ring stages per consumer warp
+    int             n_helpers;        // mv_lean_kernel: extra warps that only share the K1 prologue (set by the launcher)
     int             fuse_quant;       // 1: quantize src1 inside the kernel (x, x_cs); 0: load act_main / act_aux
     int             x_vec;            // x rows are 16-byte aligned
     int             pdl;              // launch with programmatic stream serialization
@@ -270,6 +271,8 @@ struct MvParams {
     int             dbg;      // experiment switches (GGML_B200_DBG)
 };
 
+// one-column plain launches of these formats run on mv_lean_kernel, which consumes ring stages in pairs (wants 4 stages)
+bool mv_lean_type(int type);
 // smem bytes needed by the fast kernel for a configuration
 size_t mv_fast_smem(int type, int U, int ncols, int n_cons, int n_stages);
 // launches the persistent TMA-staged mat-vec kernel (type, ncols 1..8); grid = n_ctas

@@ -676,6 +676,430 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// the lean one-column kernel (round 2): the same ring / producer / fused-K1 structure as mv_fast_kernel for the case a decode
+// token is made of - one activation column, plain MUL_MAT (no expert routing, no row-split exchange, no K7 epilogue) - with
+// the consumer loop rebuilt around what the round-1 profile showed: the kernel was ISSUE-bound at ~370 instructions per
+// 256 weights (ncu: issue active 47 %, 23.6 M warp instructions for lm_head), half of them bookkeeping. Here
+//   * a warp consumes its row groups in PAIRS: the two stages of a pair hold the same unit indices of different rows, so a lane
+//     loads its activation unit from shared memory once for two weight units (27 -> 18 ld.shared.v4 per unit) and the two
+//     independent dot-product chains give the scheduler twice the instruction-level parallelism;
+//   * everything that does not change per stage (matrix lookup, row numbers, unit addresses) is computed once per pair,
+//     and the store is a plain st.global.
+// The ring order follows the pairs: (group A slice 0, group B slice 0, A slice 1, B slice 1, ...), an even number of stages.
+// ------------------------------------------------------------------------------------------------
+
+// two weight units (w0, w1: same unit index, different rows) against one activation unit
+__device__ __forceinline__ void unit_dot2_q4_K(uint32_t w0, uint32_t w1, uint32_t am, uint32_t ax, float & acc0, float & acc1) {
+    const uint4 hA = lds128o<0>(w0), hB = lds128o<0>(w1);
+    const uint32_t scA_lo = hA.y & 0x3f3f3f3fu, scA_hi = (hA.w & 0x0f0f0f0fu) | ((hA.y >> 2) & 0x30303030u);
+    const uint32_t scB_lo = hB.y & 0x3f3f3f3fu, scB_hi = (hB.w & 0x0f0f0f0fu) | ((hB.y >> 2) & 0x30303030u);
+    int isA = 0, isB = 0;
+    static_for<0, 4>([&](auto gi) {
+        constexpr int g = decltype(gi)::value;
+        const uint4 l0 = lds128o<64 * g>(am), l1 = lds128o<64 * g + 16>(am), h0 = lds128o<64 * g + 32>(am), h1 = lds128o<64 * g + 48>(am);
+        const int lo[8] = { (int) l0.x, (int) l0.y, (int) l0.z, (int) l0.w, (int) l1.x, (int) l1.y, (int) l1.z, (int) l1.w };
+        const int hi[8] = { (int) h0.x, (int) h0.y, (int) h0.z, (int) h0.w, (int) h1.x, (int) h1.y, (int) h1.z, (int) h1.w };
+        const uint4 a0 = lds128o<16 + 32 * g>(w0), a1 = lds128o<32 + 32 * g>(w0);
+        const uint4 b0 = lds128o<16 + 32 * g>(w1), b1 = lds128o<32 + 32 * g>(w1);
+        const uint32_t qa[8] = { a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w };
+        const uint32_t qb[8] = { b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w };
+        int sAl = 0, sAh = 0, sBl = 0, sBh = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            sAl = dp4a_us(qa[k] & 0x0f0f0f0fu, lo[k], sAl);
+            sBl = dp4a_us(qb[k] & 0x0f0f0f0fu, lo[k], sBl);
+            sAh = dp4a_us(qa[k] & 0xf0f0f0f0u, hi[k], sAh);  // 16 x the high-nibble dot product
+            sBh = dp4a_us(qb[k] & 0xf0f0f0f0u, hi[k], sBh);
+        }
+        const uint32_t wA = g < 2 ? scA_lo : scA_hi, wB = g < 2 ? scB_lo : scB_hi;
+        isA += (int) ((wA >> (16 * (g & 1))) & 0xff) * sAl + (int) ((wA >> (16 * (g & 1) + 8)) & 0xff) * (sAh >> 4);
+        isB += (int) ((wB >> (16 * (g & 1))) & 0xff) * sBl + (int) ((wB >> (16 * (g & 1) + 8)) & 0xff) * (sBh >> 4);
+    });
+    const uint4 bs = lds128o<256>(am);  // int16 sum of q per 32-block (x8)
+    const float dy = __uint_as_float(lds32(ax));
+    const uint32_t mnA_lo = hA.z & 0x3f3f3f3fu, mnA_hi = ((hA.w >> 4) & 0x0f0f0f0fu) | ((hA.z >> 2) & 0x30303030u);
+    const uint32_t mnB_lo = hB.z & 0x3f3f3f3fu, mnB_hi = ((hB.w >> 4) & 0x0f0f0f0fu) | ((hB.z >> 2) & 0x30303030u);
+    int mA = dp2a_lo_su((int) bs.x, mnA_lo, 0), mB = dp2a_lo_su((int) bs.x, mnB_lo, 0);
+    mA = dp2a_hi_su((int) bs.y, mnA_lo, mA); mB = dp2a_hi_su((int) bs.y, mnB_lo, mB);
+    mA = dp2a_lo_su((int) bs.z, mnA_hi, mA); mB = dp2a_lo_su((int) bs.z, mnB_hi, mB);
+    mA = dp2a_hi_su((int) bs.w, mnA_hi, mA); mB = dp2a_hi_su((int) bs.w, mnB_hi, mB);
+    // the same two fused multiply-adds per unit as unit_dot_q4_K: results are bit-identical to the one-unit path
+    acc0 = fmaf(half_bits_to_float((uint16_t) (hA.x & 0xffff)) * dy, (float) isA, acc0);
+    acc0 = fmaf(-(half_bits_to_float((uint16_t) (hA.x >> 16)) * dy), (float) mA, acc0);
+    acc1 = fmaf(half_bits_to_float((uint16_t) (hB.x & 0xffff)) * dy, (float) isB, acc1);
+    acc1 = fmaf(-(half_bits_to_float((uint16_t) (hB.x >> 16)) * dy), (float) mB, acc1);
+}
+
+// q4_0 / q8_0 pairs: the unit is walked in two halves of four blocks, so that two rows' weights fit in registers next to the
+// activation words they share. Same operations per block and row as unit_dot_q4_0 / unit_dot_q8_0 (bit-identical results).
+__device__ __forceinline__ void unit_dot2_q4_0(uint32_t w0, uint32_t w1, uint32_t am, uint32_t ax, float & acc0, float & acc1) {
+    const uint4 dyh = lds128o<256>(am);   // half d[8]
+    const uint4 ys  = lds128(ax);         // int16 sum[8]
+    static_for<0, 2>([&](auto hi_) {
+        constexpr int H  = decltype(hi_)::value;
+        constexpr int W0 = 16 * H;        // first word held: words W0 .. W0 + 19 cover block pairs 2H and 2H + 1 (words 18H .. 18H + 17)
+        uint32_t a[20], b[20];
+        static_for<0, 5>([&](auto ii) {
+            constexpr int i = decltype(ii)::value;
+            const uint4 v = lds128o<4 * W0 + 16 * i>(w0), u = lds128o<4 * W0 + 16 * i>(w1);
+            a[4 * i] = v.x; a[4 * i + 1] = v.y; a[4 * i + 2] = v.z; a[4 * i + 3] = v.w;
+            b[4 * i] = u.x; b[4 * i + 1] = u.y; b[4 * i + 2] = u.z; b[4 * i + 3] = u.w;
+        });
+        static_for<0, 4>([&](auto bi) {
+            constexpr int blk = 4 * H + decltype(bi)::value;
+            constexpr int p   = 9 * (blk >> 1) - W0;  // index of the block pair's first word in a[] / b[]
+            const uint4 l = lds128o<32 * blk>(am), h = lds128o<32 * blk + 16>(am);
+            const int lo[4] = { (int) l.x, (int) l.y, (int) l.z, (int) l.w }, hi[4] = { (int) h.x, (int) h.y, (int) h.z, (int) h.w };
+            const uint32_t dword = blk < 2 ? dyh.x : blk < 4 ? dyh.y : blk < 6 ? dyh.z : dyh.w;
+            const uint32_t sword = blk < 2 ? ys.x : blk < 4 ? ys.y : blk < 6 ? ys.z : ys.w;
+            const float    dy    = half_bits_to_float((uint16_t) ((blk & 1) ? dword >> 16 : dword & 0xffff));
+            const int      ysum  = (int) (int16_t) ((blk & 1) ? sword >> 16 : sword & 0xffff);
+            float dA, dB;
+            uint32_t qa[4], qb[4];
+            if ((blk & 1) == 0) {
+                dA = half_bits_to_float((uint16_t) (a[p] & 0xffff)); dB = half_bits_to_float((uint16_t) (b[p] & 0xffff));
+#pragma unroll
+                for (int k = 0; k < 4; k++) { qa[k] = __funnelshift_r(a[p + k], a[p + k + 1], 16); qb[k] = __funnelshift_r(b[p + k], b[p + k + 1], 16); }
+            } else {
+                dA = half_bits_to_float((uint16_t) (a[p + 4] >> 16)); dB = half_bits_to_float((uint16_t) (b[p + 4] >> 16));
+#pragma unroll
+                for (int k = 0; k < 4; k++) { qa[k] = a[p + 5 + k]; qb[k] = b[p + 5 + k]; }
+            }
+            int sAl = 0, sAh = 0, sBl = 0, sBh = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                sAl = dp4a_us(qa[k] & 0x0f0f0f0fu, lo[k], sAl); sAh = dp4a_us(qa[k] & 0xf0f0f0f0u, hi[k], sAh);
+                sBl = dp4a_us(qb[k] & 0x0f0f0f0fu, lo[k], sBl); sBh = dp4a_us(qb[k] & 0xf0f0f0f0u, hi[k], sBh);
+            }
+            acc0 = fmaf((float) (sAl + (sAh >> 4) - 8 * ysum) * dA, dy, acc0);
+            acc1 = fmaf((float) (sBl + (sBh >> 4) - 8 * ysum) * dB, dy, acc1);
+        });
+    });
+}
+
+__device__ __forceinline__ void unit_dot2_q8_0(uint32_t w0, uint32_t w1, uint32_t am, float & acc0, float & acc1) {
+    const uint4 dyh = lds128o<256>(am);
+    static_for<0, 4>([&](auto pi) {
+        constexpr int P = decltype(pi)::value;           // block pair: 68 bytes = words 17P .. 17P + 16
+        constexpr int W0 = (17 * P) & ~3;                 // 16-byte aligned start; up to 3 words of slack in front
+        constexpr int NW = ((17 * P + 17 - W0) + 3) / 4;  // 128-bit loads needed (5 or 6)
+        uint32_t a[4 * NW], b[4 * NW];
+        static_for<0, NW>([&](auto ii) {
+            constexpr int i = decltype(ii)::value;
+            if constexpr (4 * W0 + 16 * i < 272) {
+                const uint4 v = lds128o<4 * W0 + 16 * i>(w0), u = lds128o<4 * W0 + 16 * i>(w1);
+                a[4 * i] = v.x; a[4 * i + 1] = v.y; a[4 * i + 2] = v.z; a[4 * i + 3] = v.w;
+                b[4 * i] = u.x; b[4 * i + 1] = u.y; b[4 * i + 2] = u.z; b[4 * i + 3] = u.w;
+            }
+        });
+        constexpr int p = 17 * P - W0;
+        static_for<0, 2>([&](auto ei) {
+            constexpr int e = decltype(ei)::value, blk = 2 * P + e;
+            const uint4 y0 = lds128o<32 * blk>(am), y1 = lds128o<32 * blk + 16>(am);
+            const int y[8] = { (int) y0.x, (int) y0.y, (int) y0.z, (int) y0.w, (int) y1.x, (int) y1.y, (int) y1.z, (int) y1.w };
+            const uint32_t dword = blk < 2 ? dyh.x : blk < 4 ? dyh.y : blk < 6 ? dyh.z : dyh.w;
+            const float    dy    = half_bits_to_float((uint16_t) ((blk & 1) ? dword >> 16 : dword & 0xffff));
+            float dA, dB;
+            int sA = 0, sB = 0;
+            if (e == 0) {
+                dA = half_bits_to_float((uint16_t) (a[p] & 0xffff)); dB = half_bits_to_float((uint16_t) (b[p] & 0xffff));
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    sA = dp4a_ss((int) __funnelshift_r(a[p + k], a[p + k + 1], 16), y[k], sA);
+                    sB = dp4a_ss((int) __funnelshift_r(b[p + k], b[p + k + 1], 16), y[k], sB);
+                }
+            } else {
+                dA = half_bits_to_float((uint16_t) (a[p + 8] >> 16)); dB = half_bits_to_float((uint16_t) (b[p + 8] >> 16));
+#pragma unroll
+                for (int k = 0; k < 8; k++) { sA = dp4a_ss((int) a[p + 9 + k], y[k], sA); sB = dp4a_ss((int) b[p + 9 + k], y[k], sB); }
+            }
+            acc0 = fmaf((float) sA, dA * dy, acc0);
+            acc1 = fmaf((float) sB, dB * dy, acc1);
+        });
+    });
+}
+
+template <int TYPE>
+__device__ __forceinline__ void unit_dot2(uint32_t w0, uint32_t w1, uint32_t am, uint32_t ax, float & acc0, float & acc1) {
+    if (TYPE == B200_TYPE_Q4_K) {
+        unit_dot2_q4_K(w0, w1, am, ax, acc0, acc1);
+    } else if (TYPE == B200_TYPE_Q4_0) {
+        unit_dot2_q4_0(w0, w1, am, ax, acc0, acc1);
+    } else if (TYPE == B200_TYPE_Q8_0) {
+        unit_dot2_q8_0(w0, w1, am, acc0, acc1);
+    } else {  // the other formats keep their one-unit dot products (their register footprint does not allow two at once)
+        float a[1] = { acc0 }, b[1] = { acc1 };
+        unit_dot<TYPE, 1>(w0, am, ax, 0, 0, a);
+        unit_dot<TYPE, 1>(w1, am, ax, 0, 0, b);
+        acc0 = a[0]; acc1 = b[0];
+    }
+}
+
+template <int TYPE>
+__global__ void __launch_bounds__(32 * (MV_MAX_CONS + 1), 1)
+mv_lean_kernel(const __grid_constant__ MvParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    constexpr int UB    = unit_bytes(TYPE);
+    constexpr int STAGE = 32 * UB;
+    constexpr int KIND  = act_kind_for(TYPE);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int NWC = p.n_cons, NS = p.n_stages;  // NS is even
+    const int U = p.U, SL = p.slices;
+
+    uint64_t * act_bar = (uint64_t *) smem;
+    uint64_t * full    = (uint64_t *) (smem + MV_HDR_BYTES);
+    uint64_t * empty   = full + NWC * NS;
+    size_t     off     = mv_align(MV_HDR_BYTES + (size_t) 16 * NWC * NS, 128);
+    uint8_t *  act_m   = smem + off;
+    uint8_t *  act_x   = act_m + (size_t) U * ACT_MAIN;
+    off                = mv_align(off + (size_t) U * (ACT_MAIN + ACT_AUX), 128);
+    uint8_t *  ring0   = smem + off;
+
+    const int g_begin = (int) ((int64_t) p.total_groups * blockIdx.x / gridDim.x);
+    const int g_end   = (int) ((int64_t) p.total_groups * (blockIdx.x + 1) / gridDim.x);
+
+    if (warp == NWC) {
+        if (lane == 0) mbar_init(smem_u32(act_bar), 1);
+        if (lane < NWC) {
+            for (int i = 0; i < NS; i++) {
+                mbar_init(smem_u32(full + lane * NS + i), 1);
+                mbar_init(smem_u32(empty + lane * NS + i), 1);
+            }
+        }
+        fence_mbar_init();
+        __syncwarp();
+        asm volatile("bar.arrive 0, %0;" ::"r"(blockDim.x) : "memory");
+    } else {
+        asm volatile("bar.sync 0, %0;" ::"r"(blockDim.x) : "memory");
+    }
+    griddep_launch_dependents();
+    if (p.trace && threadIdx.x == 0) p.trace[(size_t) blockIdx.x * 8 + 0] = global_ns();
+
+    if (warp == NWC) {
+        // ================================================================ producer warp: lane w feeds consumer warp w
+        const uint64_t pol_stream = l2_policy_evict_first();
+        const int w = lane;
+        int cnt = 0;
+        if (w < NWC && g_end - g_begin > w) cnt = (g_end - g_begin - w + NWC - 1) / NWC;
+        const int n_pair_stages = (cnt >> 1) * 2 * SL, my_total = cnt * SL;
+        int issued = 0, stage = 0, pg = 0, r = 0;  // r: position inside the pair (slice = r >> 1, which = r & 1)
+        uint32_t phase = 1;
+        while (__any_sync(0xffffffffu, issued < my_total)) {
+            bool can = issued < my_total;
+            if (can) can = mbar_test_wait(smem_u32(empty + w * NS + stage), phase);
+            if (can) {
+                int j, slice;
+                if (issued < n_pair_stages) { j = 2 * pg + (r & 1); slice = r >> 1; }
+                else                        { j = cnt - 1; slice = issued - n_pair_stages; }
+                const int     group = g_begin + w + j * NWC;
+                const MvMat & mat   = p.mat[mv_find_mat(p, group)];
+                const int     row0  = (group - mat.group0) * p.rpg;
+                const int     nrow  = min(p.rpg, mat.M - row0);
+                const int     u0    = slice * 32;
+                const int     nu    = min(32, U - u0);
+                const uint32_t bar  = smem_u32(full + w * NS + stage);
+                const uint32_t dst  = smem_u32(ring0 + ((size_t) w * NS + stage) * STAGE);
+                const uint32_t row_bytes = (uint32_t) nu * UB;
+                if (p.trace && w == 0 && issued == 0) p.trace[(size_t) blockIdx.x * 8 + 1] = global_ns();
+                mbar_expect_tx(bar, row_bytes * nrow);
+                const uint8_t * src = mat.w + (int64_t) row0 * mat.nb01 + (int64_t) u0 * UB;
+                if (nrow > 1 && mat.nb01 == (int64_t) U * UB) {
+                    bulk_g2s(dst, src, row_bytes * nrow, bar, pol_stream);
+                } else {
+                    for (int i = 0; i < nrow; i++) bulk_g2s(dst + i * row_bytes, src + (int64_t) i * mat.nb01, row_bytes, bar, pol_stream);
+                }
+                if (p.trace && w == 0 && issued == 0) p.trace[(size_t) blockIdx.x * 8 + 2] = global_ns();
+                issued++;
+                if (++stage == NS) { stage = 0; phase ^= 1; }
+                if (++r == 2 * SL) { r = 0; pg++; }
+            }
+        }
+        if (p.next.n_mats > 0) {  // head of the predicted next kernel's weight stream -> L2 (see MvNext)
+            const MvNext & nx = p.next;
+            for (int b = blockIdx.x; b < nx.n_ctas; b += gridDim.x) {
+                const int nb = (int) ((int64_t) nx.total_groups * b / nx.n_ctas);
+                const int ne = min((int) ((int64_t) nx.total_groups * (b + 1) / nx.n_ctas), nb + nx.groups_per_cta);
+                const int gs = nx.glu ? 2 : 1;
+                for (int gl = gs * nb + lane; gl < gs * ne; gl += 32) {
+                    const int g = gl / gs;
+                    int m = nx.glu ? gl - 2 * g : 0;
+#pragma unroll
+                    for (int i = 1; i < MV_MAX_MATS; i++) if (!nx.glu && i < nx.n_mats && g >= nx.group0[i]) m = i;
+                    const int row0 = (g - nx.group0[m]) * nx.rpg;
+                    const int nrow = min(nx.rpg, nx.M[m] - row0);
+                    const uint8_t * src = nx.w[m] + (int64_t) row0 * nx.nb01[m];
+                    if (nx.nb01[m] == (int64_t) nx.row_bytes) {
+                        bulk_prefetch_l2(src, (uint32_t) (nrow * nx.row_bytes));
+                    } else {
+                        for (int i = 0; i < nrow; i++) bulk_prefetch_l2(src + (int64_t) i * nx.nb01[m], (uint32_t) nx.row_bytes);
+                    }
+                }
+            }
+        }
+        return;
+    }
+    // ==================================================================== consumer warps (+ helper warps behind the producer warp:
+    // they only take a share of the K1 prologue, which is issue-bound - 16 units over 11 warps are two rounds, over 16 warps one)
+    const int w  = warp;
+    const int NQ = NWC + p.n_helpers;            // warps that quantize
+    const int qw = warp < NWC ? warp : warp - 1; // this warp's index among them
+    int cnt = 0;
+    if (w < NWC && g_end - g_begin > w) cnt = (g_end - g_begin - w + NWC - 1) / NWC;
+
+    griddep_wait();
+    if (w == 0) MV_TRACE(3);
+    if (warp > NWC && !p.fuse_quant) return;
+    if (p.fuse_quant) {
+        for (int t0 = qw; t0 < U; t0 += 4 * NQ) {
+            float v[4][8];
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                const int t = t0 + b * NQ;
+                if (t < U) {
+                    const float * xr = p.x + (int64_t) t * UNIT_ELEMS + lane * 8;
+                    if (p.x_vec) {
+                        const float4 a = __ldg((const float4 *) xr);
+                        const float4 bb = __ldg((const float4 *) xr + 1);
+                        v[b][0] = a.x; v[b][1] = a.y; v[b][2] = a.z; v[b][3] = a.w;
+                        v[b][4] = bb.x; v[b][5] = bb.y; v[b][6] = bb.z; v[b][7] = bb.w;
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 8; i++) v[b][i] = __ldg(xr + i);
+                    }
+                }
+            }
+            if (p.trace && w == 0 && t0 == qw) {
+                asm volatile("" : "+f"(v[0][0]), "+f"(v[0][7]));
+                MV_TRACE(7);
+            }
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                const int t = t0 + b * NQ;
+                if (t < U) quant_unit_store<KIND>(v[b], lane, act_m + (size_t) t * ACT_MAIN, act_x + (size_t) t * ACT_AUX);
+            }
+        }
+        bar_sync_named(1, NQ * 32);
+        if (warp > NWC) return;   // helper warps are done
+    } else {
+        if (w == 0 && lane == 0) {
+            const uint64_t pol_keep = l2_policy_evict_last();
+            const uint32_t bytes_m = (uint32_t) U * ACT_MAIN, bytes_x = (uint32_t) U * ACT_AUX;
+            mbar_expect_tx(smem_u32(act_bar), bytes_m + bytes_x);
+            bulk_g2s(smem_u32(act_m), p.act_main, bytes_m, smem_u32(act_bar), pol_keep);
+            bulk_g2s(smem_u32(act_x), p.act_aux, bytes_x, smem_u32(act_bar), pol_keep);
+        }
+        mbar_wait(smem_u32(act_bar), 0);
+    }
+    if (w == 0) MV_TRACE(4);
+
+    const int L   = p.L;
+    const int sub = lane & (L - 1);
+    const int rr  = lane / L;
+    const uint32_t ring  = smem_u32(ring0 + (size_t) w * NS * STAGE);
+    const uint32_t fullw = smem_u32(full + w * NS), emptyw = smem_u32(empty + w * NS);
+    const uint32_t am0 = smem_u32(act_m) + (uint32_t) sub * ACT_MAIN, ax0 = smem_u32(act_x) + (uint32_t) sub * ACT_AUX;
+    const bool     lane_on = rr < p.rpg;
+
+    auto reduce_store = [&](float v, int group) {  // sum over the L lanes of a row, one store per row
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float t = __shfl_xor_sync(0xffffffffu, v, o);
+            if (o < L) v += t;
+        }
+        const MvMat & mat = p.mat[mv_find_mat(p, group)];
+        const int     row = (group - mat.group0) * p.rpg + rr;
+        if (sub == 0 && lane_on && row < mat.M) mat.dst[row] = v;
+    };
+
+    int stage = 0;
+    uint32_t phase = 0;
+    const int n_pairs = cnt >> 1;
+    for (int pg = 0; pg < n_pairs; pg++) {
+        float accA = 0.0f, accB = 0.0f;
+        for (int s = 0; s < SL; s++) {
+            mbar_wait(fullw + 8 * stage, phase);
+            mbar_wait(fullw + 8 * stage + 8, phase);
+            if (w == 0 && pg == 0 && s == 0) MV_TRACE(5);
+            const int nu = min(32, U - s * 32);
+            if (lane_on && sub < nu) {
+                const uint32_t wp = ring + (uint32_t) stage * STAGE + (uint32_t) (rr * nu + sub) * UB;
+                unit_dot2<TYPE>(wp, wp + STAGE, am0 + (uint32_t) s * 32 * ACT_MAIN, ax0 + (uint32_t) s * 32 * ACT_AUX, accA, accB);
+            }
+            __syncwarp();
+            if (lane == 0) { mbar_arrive(emptyw + 8 * stage); mbar_arrive(emptyw + 8 * stage + 8); }
+            stage += 2;
+            if (stage == NS) { stage = 0; phase ^= 1; }
+        }
+        const int groupA = g_begin + w + 2 * pg * NWC;
+        reduce_store(accA, groupA);
+        reduce_store(accB, groupA + NWC);
+    }
+    if (cnt & 1) {  // the odd group at the end of the warp's list: one stage per slice
+        float acc[1] = { 0.0f };
+        for (int s = 0; s < SL; s++) {
+            mbar_wait(fullw + 8 * stage, phase);
+            if (w == 0 && n_pairs == 0 && s == 0) MV_TRACE(5);
+            const int nu = min(32, U - s * 32);
+            if (lane_on && sub < nu) {
+                const uint32_t wp = ring + (uint32_t) stage * STAGE + (uint32_t) (rr * nu + sub) * UB;
+                unit_dot<TYPE, 1>(wp, am0 + (uint32_t) s * 32 * ACT_MAIN, ax0 + (uint32_t) s * 32 * ACT_AUX, 0, 0, acc);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(emptyw + 8 * stage);
+            if (++stage == NS) { stage = 0; phase ^= 1; }
+        }
+        reduce_store(acc[0], g_begin + w + (cnt - 1) * NWC);
+    }
+    if (w == 0) MV_TRACE(6);
+}
+
+template <int TYPE>
+static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t smem, cudaStream_t st) {
+    MvParams p = p_in;
+    p.n_helpers = 0;
+    if (p.fuse_quant && !(p.dbg & 4)) {   // as many quantizing warps as src1 has units, up to the 16 + 1 warps the kernel is compiled for
+        const int room = MV_MAX_CONS - p.n_cons, want = p.U - p.n_cons;
+        p.n_helpers = want < 0 ? 0 : (want < room ? want : room);
+    }
+    static bool attr_done[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        if (e != cudaSuccess) return e;
+        attr_done[dev] = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim          = dim3(n_ctas);
+    cfg.blockDim         = dim3(32 * (p.n_cons + 1 + p.n_helpers));
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream           = st;
+    cudaLaunchAttribute attr[1];
+    int na = 0;
+    if (p.pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
+    cfg.attrs    = attr;
+    cfg.numAttrs = na;
+    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE>, p);
+}
+
+// the launch can take the lean kernel: one column, plain MUL_MAT, no exchange, no epilogue, an even ring
+bool mv_lean_type(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0; }  // formats with a two-unit dot product
+
+static bool mv_lean_ok(int type, int ncols, const MvParams & p, int n_pairs) {
+    if (!mv_lean_type(type) || ncols != 1 || n_pairs != 1 || p.ids.ids || p.split.n_ranks > 1 || p.epi.glu || (p.n_stages & 1) || (p.dbg & 1)) return false;
+    for (int i = 0; i < p.n_mats; i++) if (p.mat[i].bias) return false;
+    return true;
+}
+
 template <int TYPE, int NC, int WIDE, bool EPI = false>
 static cudaError_t mv_fast_launch_w(const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
     static bool attr_done[64] = {};  // one attribute call per instantiation and device
@@ -739,6 +1163,15 @@ static cudaError_t mv_fast_launch_n(int nc, const MvParams & p, int n_ctas, int 
 }
 
 cudaError_t mv_fast_launch(int type, int ncols, const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
+    if (mv_lean_ok(type, ncols, p, n_pairs)) {
+        switch (type) {
+            case B200_TYPE_Q4_0: return mv_lean_launch_t<B200_TYPE_Q4_0>(p, n_ctas, smem, st);
+            case B200_TYPE_Q8_0: return mv_lean_launch_t<B200_TYPE_Q8_0>(p, n_ctas, smem, st);
+            case B200_TYPE_Q4_K: return mv_lean_launch_t<B200_TYPE_Q4_K>(p, n_ctas, smem, st);
+            case B200_TYPE_Q5_K: return mv_lean_launch_t<B200_TYPE_Q5_K>(p, n_ctas, smem, st);
+            case B200_TYPE_Q6_K: return mv_lean_launch_t<B200_TYPE_Q6_K>(p, n_ctas, smem, st);
+        }
+    }
     switch (type) {
         case B200_TYPE_Q4_0: return mv_fast_launch_n<B200_TYPE_Q4_0>(ncols, p, n_ctas, n_pairs, smem, st);
         case B200_TYPE_Q8_0: return mv_fast_launch_n<B200_TYPE_Q8_0>(ncols, p, n_ctas, n_pairs, smem, st);
