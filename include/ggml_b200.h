@@ -319,6 +319,10 @@ B200_API void         b200_ctx_set_weight_cache(b200_ctx * ctx, int enable);
 B200_API void         b200_weight_cache_invalidate(int device, const void * base, size_t size);
 B200_API void         b200_weight_cache_clear(int device);
 B200_API size_t       b200_weight_cache_bytes(void);
+/* Upper bound for the cached expansions, all devices together (default: 40 % of the first device's memory; env
+ * GGML_B200_WEIGHT_CACHE_MB). Beyond it the least recently used expansions nobody is using are dropped; a matrix that still does not
+ * fit - or whose allocation fails, or whose source keeps being rewritten - is expanded into scratch memory for the one call. */
+B200_API void         b200_weight_cache_set_budget(size_t bytes);
 
 /* Prefill arithmetic (more than 8 activation columns). enable = 1 (default; env GGML_B200_MMQ_F16): tcgen05 kind::f16 GEMM on
  * fp16 operands that carry the block scales (weights: dequantize_row_<type> rounded to fp16; activations: the bit-exact

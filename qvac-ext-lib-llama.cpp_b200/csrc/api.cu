@@ -846,9 +846,54 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
     return B200_OK;
 }
 
+// Row split: a rank whose slice of a MUL_MAT is EMPTY (get_row_split rounds boundaries down: M = 512 over 8 ranks with rounding 128
+// leaves four ranks without rows) still takes part in the exchange - both protocols count launches in the sync words, and in the
+// flagged-payload protocol the rank must collect the peers' rows. One small launch: no weights, no dot products.
+__global__ void __launch_bounds__(256) split_empty_kernel(const __grid_constant__ MvParams p, int ncols) {
+    if (p.split.ll) {
+        const uint32_t ep = ll_epoch(p.split);
+        ll_receive(p.split, ep, p.geom, p.mat, p.n_mats, ncols, (int) (blockIdx.x * blockDim.x + threadIdx.x), (int) (gridDim.x * blockDim.x));
+        __syncthreads();
+        if (threadIdx.x == 0) ll_finish(p.split, ep, gridDim.x);
+    } else if (threadIdx.x < 32) {
+        split_complete(p.split, gridDim.x);
+    }
+}
+
+static b200_status split_empty_participant(b200_ctx * ctx, int n_ops, const b200_mul_mat_desc * descs, float * const * dsts) {
+    CU(cudaSetDevice(ctx->device));
+    for (int o0 = 0; o0 < n_ops; o0 += MV_MAX_MATS) {
+        MvParams p;
+        memset(&p, 0, sizeof(p));
+        p.n_mats = n_ops - o0 < MV_MAX_MATS ? n_ops - o0 : MV_MAX_MATS;
+        int64_t Ms[MV_MAX_MATS], dcs[MV_MAX_MATS];
+        const int ncols = (int) descs[0].ne11;
+        for (int i = 0; i < p.n_mats; i++) {
+            p.mat[i].dst    = dsts[o0 + i];
+            p.mat[i].dst_cs = (int64_t) (descs[o0 + i].nb1 / 4);
+            Ms[i] = 0; dcs[i] = p.mat[i].dst_cs;
+        }
+        p.split = ctx->split;
+        // the decode kernels (at most 8 columns, plain 2-D MUL_MAT) use the flagged-payload exchange when it is configured: the
+        // peers will send records, so this rank has to receive them; everything else runs the flag protocol
+        const bool ll = ncols <= MV_MAX_COLS && descs[0].ne12 == 1 && descs[0].ne13 == 1 &&
+                        b200_split_ll_geom(ctx, p.n_mats, Ms, dsts + o0, dcs, ncols, &p.geom);
+        if (ll) p.split.ll = 1;
+        else if (b200_status st = b200_split_flush(ctx)) return st;
+        split_empty_kernel<<<ll ? 8 : 1, 256, 0, ctx->stream>>>(p, ncols);
+        CU(cudaGetLastError());
+        ctx->launches++;
+    }
+    return B200_OK;
+}
+
 b200_status b200_mul_mat(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * src0, const float * src1, float * dst) {
     if (!ctx || !d) return fail(B200_ERR_ARG, "null argument");
     if (!b200_mul_mat_supported(d)) return fail(B200_ERR_UNSUPPORTED, "MUL_MAT geometry/type not supported");
+    if (d->ne11 > 0 && d->ne01 == 0 && ctx->split.n_ranks > 1 && dst) {  // an empty row slice still takes part in the exchange
+        float * ds0[1] = { dst };
+        return split_empty_participant(ctx, 1, d, ds0);
+    }
     if (d->ne11 == 0 || d->ne01 == 0) return B200_OK;  // empty tensors carry no storage (ggml_is_empty nodes are skipped upstream too)
     if (!src0 || !src1 || !dst) return fail(B200_ERR_ARG, "null argument");
     const void * s0[1] = { src0 };
@@ -866,6 +911,11 @@ b200_status b200_mul_mat_shared_src1(b200_ctx * ctx, int n_ops, const b200_mul_m
             a.nb12 != b.nb12 || a.nb13 != b.nb13) {
             return fail(B200_ERR_ARG, "fused MUL_MATs must share type, K and the src1 geometry");
         }
+    }
+    if (ctx->split.n_ranks > 1 && descs[0].ne11 > 0) {
+        bool all_empty = true;
+        for (int i = 0; i < n_ops; i++) all_empty = all_empty && descs[i].ne01 == 0;
+        if (all_empty) return split_empty_participant(ctx, n_ops, descs, dsts);
     }
     return mul_mat_impl(ctx, n_ops, descs, src0s, src1, dsts);
 }

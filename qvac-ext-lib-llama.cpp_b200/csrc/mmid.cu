@@ -129,7 +129,7 @@ static b200_status mul_mat_id_impl(b200_ctx * ctx, const b200_mul_mat_id_desc * 
         const int  U    = (int) (K / 256);
         // enough pairs per expert: sort the pairs by expert and let every expert multiply its tokens 8 columns at a time on the
         // tensor-core mat-vec kernel (mvmma.cu) - an expert's weights are then read once per 8 tokens instead of once per token
-        const bool grouped = !fz && ctx->moe_group_min > 0 && n_pairs >= (int64_t) ctx->moe_group_min * d->n_as && n_pairs >= 8 && mv_mma_usable(d->type) &&
+        const bool grouped = !fz && ctx->moe_group_min > 0 && n_pairs >= (int64_t) ctx->moe_group_min * d->n_as && n_pairs >= 8 && mv_mma_usable(d->type) && mv_mma_fits(d->type, K) &&
                              d->nb12 == d->nb11 * (size_t) d->ne11;
         const bool fuse = !grouped && ctx->fuse_quant && U <= 64;  // every pair's CTAs quantize that pair's activation row themselves
         uint8_t * am = nullptr, * ax = nullptr;

@@ -630,6 +630,11 @@ struct WEntry {  // expanded form of one weight matrix
     CUtensorMap map_qb, map_dw;
     bool        f16 = false;      // fp16 [M][K] for the kind::f16 kernel (mmf16.cuh): map_q only
     bool        settled = false;  // the expansion kernel is known to have finished (set after a stream synchronize)
+    // cache bookkeeping (under g_wmutex)
+    size_t      extent = 0;       // bytes of the SOURCE tensor the expansion was made from: (M - 1) * nb01 + one row
+    uint64_t    stamp  = 0;       // last use (LRU)
+    int         refs   = 0;       // calls that are using the entry right now: never freed under them
+    bool        dead   = false;   // invalidated while in use: the last user frees it
 };
 
 #include "mmf16.cuh"
@@ -643,6 +648,51 @@ struct WKey {
 std::mutex                 g_wmutex;
 std::map<WKey, WEntry *>   g_wcache;
 size_t                     g_wbytes = 0;
+uint64_t                   g_wclock = 0;
+std::map<WKey, int>        g_wrewrites;   // how often a cached source was overwritten: tensors rewritten every graph are not cached
+size_t                     g_wbudget = 0; // 0 = not set yet: 40 % of the device's memory (GGML_B200_WEIGHT_CACHE_MB overrides)
+
+size_t wcache_budget(int device) {
+    if (g_wbudget == 0) {
+        if (const char * s = getenv("GGML_B200_WEIGHT_CACHE_MB")) g_wbudget = (size_t) atoll(s) << 20;
+        if (g_wbudget == 0) {
+            size_t fr = 0, tot = 0;
+            cudaSetDevice(device);
+            if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) { cudaGetLastError(); tot = (size_t) 64 << 30; }
+            g_wbudget = tot / 5 * 2;
+        }
+    }
+    return g_wbudget;
+}
+
+void wentry_free(WEntry * e, int device) {  // g_wmutex held; cudaFree synchronizes with the device: no kernel still reads the buffer
+    cudaSetDevice(device);
+    cudaFree(e->buf);
+    delete e;
+}
+
+// makes room for `need` more bytes on `device` by dropping least recently used entries nobody is using; g_wmutex held
+bool wcache_make_room(int device, size_t need) {
+    const size_t budget = wcache_budget(device);
+    if (need > budget) return false;
+    while (g_wbytes + need > budget) {
+        auto victim = g_wcache.end();
+        for (auto it = g_wcache.begin(); it != g_wcache.end(); ++it) {
+            if (it->second->refs > 0) continue;
+            if (victim == g_wcache.end() || it->second->stamp < victim->second->stamp) victim = it;
+        }
+        if (victim == g_wcache.end()) return false;
+        g_wbytes -= victim->second->bytes;
+        wentry_free(victim->second, victim->first.device);
+        g_wcache.erase(victim);
+    }
+    return true;
+}
+
+void wcache_release(WEntry * e, int device) {
+    std::lock_guard<std::mutex> lock(g_wmutex);
+    if (--e->refs == 0 && e->dead) wentry_free(e, device);
+}
 
 bool q4k_planes_enabled() {
     static const bool on = [] { const char * s = getenv("GGML_B200_MMQ_Q4K_PLANES"); return !(s && atoi(s) == 0); }();
@@ -727,19 +777,27 @@ b200_status wentry_fill(b200_ctx * ctx, WEntry * e, const void * src, uint8_t * 
 
 void b200_weight_cache_invalidate(int device, const void * base, size_t size) {
     std::lock_guard<std::mutex> lock(g_wmutex);
-    const char * lo = (const char *) base, * hi = lo + size;
+    const char * lo = (const char *) base, * hi = size > (size_t) (UINTPTR_MAX - (uintptr_t) lo) ? (const char *) UINTPTR_MAX : lo + size;
     for (auto it = g_wcache.begin(); it != g_wcache.end();) {
         const char * s = (const char *) it->first.src;
-        if (it->first.device == device && s >= lo && s < hi) {
-            cudaSetDevice(device);
-            cudaFree(it->second->buf);  // synchronizes with the device: no kernel is still reading it
+        // any overlap of the written range with the bytes the expansion was made from (a write through a view that starts behind
+        // row 0 must drop the entry too)
+        if (it->first.device == device && s < hi && s + it->second->extent > lo) {
+            if (g_wrewrites.size() > 65536) g_wrewrites.clear();
+            g_wrewrites[it->first]++;
             g_wbytes -= it->second->bytes;
-            delete it->second;
+            if (it->second->refs > 0) it->second->dead = true;  // a call on another thread is using it: that call frees it
+            else wentry_free(it->second, device);
             it = g_wcache.erase(it);
         } else {
             ++it;
         }
     }
+    if (size == SIZE_MAX) g_wrewrites.clear();
+}
+void b200_weight_cache_set_budget(size_t bytes) {
+    std::lock_guard<std::mutex> lock(g_wmutex);
+    g_wbudget = bytes;   // 0: back to the default (recomputed on next use)
 }
 void b200_weight_cache_clear(int device) { b200_weight_cache_invalidate(device, nullptr, SIZE_MAX); }
 size_t b200_weight_cache_bytes(void) {
@@ -778,42 +836,62 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
     // ---- weights: cached or transient (transient copies live behind the activations in scratch2)
     WEntry * e = nullptr;
     WEntry   tmp;
-    bool     cached = false;
+    bool     cached = false, held = false;
+    const size_t wb = wentry_bytes(type, M, K, Mp, f16);
+    const size_t src_extent = (size_t) (M - 1) * nb01 + (size_t) (K / type_block_elems(type)) * type_block_bytes(type);
+    bool cacheable = ctx->weight_cache != 0;
+    uint8_t * cbuf = nullptr;
     if (ctx->weight_cache) {
         std::lock_guard<std::mutex> lock(g_wmutex);
-        auto it = g_wcache.find(WKey{ ctx->device, w });
+        const WKey key{ ctx->device, w };
+        auto it = g_wcache.find(key);
         if (it != g_wcache.end() && it->second->type == type && it->second->M == M && it->second->K == K && it->second->nb01 == nb01 &&
             it->second->f16 == f16) {
             e = it->second;
-            cached = true;
+            e->refs++;
+            e->stamp = ++g_wclock;
+            cached = held = true;
+        } else {
+            if (it != g_wcache.end()) {  // geometry changed under the same address: drop the old expansion
+                g_wbytes -= it->second->bytes;
+                if (it->second->refs > 0) it->second->dead = true; else wentry_free(it->second, ctx->device);
+                g_wcache.erase(it);
+            }
+            // a tensor that keeps being rewritten (the scheduler copies weights of CPU buffers in for every graph) is expanded per
+            // call; so is one that does not fit the budget even after evicting everything idle, or when the allocation fails
+            auto rw = g_wrewrites.find(key);
+            cacheable = !(rw != g_wrewrites.end() && rw->second >= 2) && wcache_make_room(ctx->device, wb);
+            if (cacheable) {
+                cudaSetDevice(ctx->device);
+                if (cudaMalloc((void **) &cbuf, wb) != cudaSuccess) {
+                    cudaGetLastError();
+                    cbuf = nullptr;
+                    cacheable = false;
+                } else {
+                    g_wbytes += wb;   // reserved now, so that concurrent calls see the budget
+                }
+            }
         }
     }
-    const size_t wb = wentry_bytes(type, M, K, Mp, f16);
-    if (!e && !ctx->weight_cache) need += wb;
+    if (!e && !cacheable) need += wb;
     b200_status st = b200_ensure(ctx, &ctx->scratch2, &ctx->scratch2_size, need);
-    if (st != B200_OK) return st;
+    if (st != B200_OK) {
+        if (cbuf) { std::lock_guard<std::mutex> lock(g_wmutex); g_wbytes -= wb; cudaFree(cbuf); }
+        if (held) wcache_release(e, ctx->device);
+        return st;
+    }
     uint8_t * s2 = (uint8_t *) ctx->scratch2;
 
     if (!e) {
-        WEntry * ne = ctx->weight_cache ? new WEntry() : &tmp;
-        ne->type = type; ne->M = M; ne->K = K; ne->Mp = Mp; ne->nb01 = nb01; ne->bytes = wb; ne->f16 = f16;
-        uint8_t * buf = nullptr;
-        if (ctx->weight_cache) {
-            cudaError_t ce = cudaMalloc((void **) &buf, wb);
-            if (ce != cudaSuccess) {
-                cudaGetLastError();
-                delete ne;
-                return fail(B200_ERR_ALLOC, "weight cache: cudaMalloc(%zu): %s", wb, cudaGetErrorString(ce));
-            }
-        } else {
-            buf = s2 + act_bytes;
-        }
+        WEntry * ne = cacheable ? new WEntry() : &tmp;
+        ne->type = type; ne->M = M; ne->K = K; ne->Mp = Mp; ne->nb01 = nb01; ne->bytes = wb; ne->f16 = f16; ne->extent = src_extent;
+        uint8_t * buf = cacheable ? cbuf : s2 + act_bytes;
         st = wentry_fill(ctx, ne, w, buf);
         if (st != B200_OK) {
-            if (ctx->weight_cache) { cudaFree(buf); delete ne; }
+            if (cacheable) { std::lock_guard<std::mutex> lock(g_wmutex); g_wbytes -= wb; cudaFree(buf); delete ne; }
             return st;
         }
-        if (ctx->weight_cache) {
+        if (cacheable) {
             // filling the cache is a load-time step: wait for it once, so that later launches may read the expansion ahead of
             // their stream dependency (not possible while the stream is being captured: such an entry stays unsettled)
             cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
@@ -823,18 +901,21 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
                 ne->settled = true;
             }
             std::lock_guard<std::mutex> lock(g_wmutex);
-            auto it = g_wcache.find(WKey{ ctx->device, w });
-            if (it != g_wcache.end()) {  // geometry changed under the same address: replace
-                cudaFree(it->second->buf);
+            const WKey key{ ctx->device, w };
+            auto it = g_wcache.find(key);
+            if (it != g_wcache.end()) {  // another thread expanded the same tensor meanwhile: keep ours, retire theirs
                 g_wbytes -= it->second->bytes;
-                delete it->second;
+                if (it->second->refs > 0) it->second->dead = true; else wentry_free(it->second, ctx->device);
                 g_wcache.erase(it);
             }
-            g_wcache[WKey{ ctx->device, w }] = ne;
-            g_wbytes += wb;
+            ne->refs  = 1;
+            ne->stamp = ++g_wclock;
+            g_wcache[key] = ne;
+            held = true;
         }
         e = ne;
     }
+    struct Release { WEntry * e; int dev; bool on; ~Release() { if (on) wcache_release(e, dev); } } release{ e, ctx->device, held };
     (void) cached;
     if (f16) {
         const int kind = act_kind_for(type);
@@ -925,13 +1006,20 @@ b200_status b200_mmq_run_group(b200_ctx * ctx, int type, int n_ops, const void *
             std::lock_guard<std::mutex> lock(g_wmutex);
             auto it = g_wcache.find(WKey{ ctx->device, ws[i] });
             if (it != g_wcache.end() && it->second->type == type && it->second->M == Ms[i] && it->second->K == K && it->second->nb01 == nb01s[i] &&
-                it->second->f16)
+                it->second->f16) {
                 e = it->second;
+                e->refs++;
+                e->stamp = ++g_wclock;
+            }
         }
-        if (!e) return B200_ERR_UNSUPPORTED;  // not expanded yet: the per-matrix path fills the cache (first call of a tensor)
+        if (!e) {  // not expanded yet (or evicted): the per-matrix path fills the cache
+            for (int j = 0; j < i; j++) wcache_release(es[j], ctx->device);
+            return B200_ERR_UNSUPPORTED;
+        }
         settled = settled && e->settled;
         es[i] = e;
     }
+    struct ReleaseAll { WEntry ** es; int n, dev; ~ReleaseAll() { for (int j = 0; j < n; j++) wcache_release(es[j], dev); } } release_all{ es, n_ops, ctx->device };
     const size_t hb = ((size_t) N * K * 2 + 255) & ~(size_t) 255, rb = ((size_t) N * 4 + 255) & ~(size_t) 255;
     if (b200_status st = b200_ensure(ctx, &ctx->scratch2, &ctx->scratch2_size, hb + rb)) return st;
     uint8_t * s2 = (uint8_t *) ctx->scratch2;

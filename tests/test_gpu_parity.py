@@ -570,6 +570,47 @@ def test_mmq_weight_cache(ctx, pkg, oracle, mmq_bound):
     assert oracle.nmse(oracle.mul_mat(Q4_0, W2, X), b) <= mmq_bound
 
 
+def test_mmq_weight_cache_budget_lru_and_view_invalidation(ctx, pkg, oracle):
+    """the cache is bounded (least recently used expansions go first, a matrix that cannot be cached is expanded for the
+    one call instead of failing), and a write through a view that starts behind row 0 drops the expansion too"""
+    import torch
+    L = pkg.lib()
+    L.b200_weight_cache_set_budget.argtypes = [__import__("ctypes").c_size_t]
+    rng = np.random.default_rng(31)
+    M, K, N = 256, 1024, 40
+    Ws = [quantize_weights(oracle, Q4_K, rng.uniform(-1, 1, (M, K)).astype(np.float32)) for _ in range(4)]
+    X = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    Wd, Xd = [cu(w) for w in Ws], cu(X)
+    refs = [oracle.mul_mat(Q4_K, w, X) for w in Ws]
+    one = M * K * 2                                   # fp16 expansion of one matrix
+    ctx.weight_cache(True)
+    try:
+        L.b200_weight_cache_set_budget(2 * one + 4096)                      # room for two of the four
+        for rnd in range(2):
+            for i in range(4):
+                assert oracle.nmse(refs[i], ctx.mul_mat(Q4_K, Wd[i], Xd).cpu().numpy()) <= NMSE_F16
+                assert 0 < L.b200_weight_cache_bytes() <= 2 * one + 4096
+        L.b200_weight_cache_set_budget(one // 2)                            # nothing fits: expanded per call, nothing cached, no error
+        ctx.weight_cache_clear()
+        assert oracle.nmse(refs[0], ctx.mul_mat(Q4_K, Wd[0], Xd).cpu().numpy()) <= NMSE_F16
+        assert L.b200_weight_cache_bytes() == 0
+        L.b200_weight_cache_set_budget(64 * one)
+        a = ctx.mul_mat(Q4_K, Wd[0], Xd).cpu().numpy()
+        assert L.b200_weight_cache_bytes() == one
+        # overwrite the LAST rows only and report exactly that byte range (a view of the tensor)
+        rb = Ws[1].shape[1]
+        Wd[0][M - 8:].copy_(torch.from_numpy(Ws[1][M - 8:]))
+        L.b200_weight_cache_invalidate(0, Wd[0].data_ptr() + (M - 8) * rb, 8 * rb)
+        assert L.b200_weight_cache_bytes() == 0
+        b = ctx.mul_mat(Q4_K, Wd[0], Xd).cpu().numpy()
+        mixed = np.concatenate([Ws[0][:M - 8], Ws[1][M - 8:]])
+        assert oracle.nmse(oracle.mul_mat(Q4_K, mixed, X), b) <= NMSE_F16 and not np.array_equal(a, b)
+    finally:
+        L.b200_weight_cache_set_budget(0)
+        ctx.weight_cache(False)
+        ctx.weight_cache_clear()
+
+
 @pytest.fixture(params=["f16", "i8"])
 def mmq_bound(request, ctx):
     """both prefill arithmetics (b200_ctx_set_mmq_f16): scale-carrying fp16 operands (default) and exact per-block int8"""

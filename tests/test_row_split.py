@@ -178,6 +178,36 @@ def test_fused_exchange_writes_every_destination(pkg, oracle, t, N, deferred):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("N", [1, 40])
+def test_empty_row_slice_still_takes_part_in_the_exchange(pkg, N):
+    """get_row_split can leave a rank without rows (M = 512 over 8 ranks, rounding 128). Such a rank must still count the launch:
+    flag protocol - epoch bumped, CTA counter reset, flag published to the peers (the peers would spin and trap)."""
+    import torch
+    c = pkg.Context(0)
+    try:
+        pool = torch.zeros(2 * N * 64 + 64, dtype=torch.float32, device="cuda")
+        sync = pool[2 * N * 64:].view(torch.int32)
+        sync[1] = 0x7FFFFFF0
+        torch.cuda.synchronize()
+        base = pool.data_ptr()
+        s0, s1 = base + 8 * N * 64, base + 8 * N * 64 + 128
+        c.row_split(0, [base, base + 4 * N * 64], [s0, s1])
+        d = pkg.MulMatDesc.contiguous(Q4_K, 0, 1024, N)          # this rank's slice: zero rows of a 64-row matrix
+        d.nb1, d.nb2, d.nb3 = 4 * 64, 4 * 64 * N, 4 * 64 * N
+        x = torch.zeros((N, 1024), dtype=torch.float32, device="cuda")
+        for rep in range(3):
+            l0 = c.launches
+            pkg.check(pkg.lib().b200_mul_mat(c.h, __import__("ctypes").byref(d), 256, x.data_ptr(), base), "b200_mul_mat")
+            c.sync()
+            words = pool[2 * N * 64:].view(torch.int32).cpu().numpy()
+            assert c.launches == l0 + 1
+            assert words[8] == rep + 1 and words[9] == 0 and words[32] == rep + 1
+        assert not pool[:2 * N * 64].any()
+    finally:
+        c.close()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("t,N,graph", [(Q4_K, 1, False), (Q4_K, 1, True), (Q4_0, 2, False), (Q8_0, 1, False), (Q4_K, 5, True), (Q4_0, 8, False)])
 def test_flagged_payload_exchange_loopback(pkg, oracle, t, N, graph):
     """rank 0 of a 2-rank split on ONE GPU with the flagged-payload exchange (b200_ctx_set_row_split_ll). The 'peer' staging area is
