@@ -542,7 +542,7 @@ static bool pick_mv_cfg(const b200_ctx * ctx, int type, int U, int nc, mv_cfg * 
         // measured on the Llama-3-8B stack (profiles/r02): 11 x 4 beats 12 x 4, 10 x 4, 8 x 4, 8 x 6 and every 2-deep ring
         static const int lean_cfg[][2] = { { 11, 4 }, { 10, 4 }, { 8, 4 }, { 6, 4 }, { 4, 4 }, { 2, 4 }, { 1, 2 } };
         for (auto & c : lean_cfg) {
-            const size_t s = mv_fast_smem(type, U, 1, c[0], c[1]);
+            const size_t s = mv_fast_smem(type, U, nc, c[0], c[1]);
             if (s <= MV_SMEM_MAX) { *out = { c[0], c[1], s }; return true; }
         }
         return false;
@@ -616,8 +616,8 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
             continue;
         }
         mv_cfg  cfg;
-        const bool lean = !ep && nc == 1 && ctx->split.n_ranks <= 1 && !(ctx->dbg & 1) && mv_lean_type(type);
-        while (nc >= 1 && !pick_mv_cfg(ctx, type, U, nc, &cfg, lean && nc == 1)) nc--;
+        const bool lean = !ep && ctx->split.n_ranks <= 1 && !(ctx->dbg & 1) && mv_lean_type(type);
+        while (nc >= 1 && !pick_mv_cfg(ctx, type, U, nc, &cfg, lean && nc <= MV_LEAN_MAX_COLS)) nc--;
         if (nc < 1) return fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
         for (int o0 = 0; o0 < n_ops; o0 += MV_MAX_MATS) {
             MvParams p;

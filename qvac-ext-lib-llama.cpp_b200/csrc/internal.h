@@ -64,7 +64,7 @@ struct b200_ctx {
     unsigned long long * trace = nullptr;
     int          trace_slots = 0;
     int          dbg = 0;                      // GGML_B200_DBG: experiment switches handed to the kernels
-    int          mma_min_cols = 3;             // columns from which the IMMA mat-vec kernel (mvmma.cu) replaces the dp4a one; GGML_B200_MMA_MIN
+    int          mma_min_cols = 4;             // columns from which the IMMA mat-vec kernel (mvmma.cu) replaces the dp4a one; GGML_B200_MMA_MIN
     int          mma_fuse_units = 0;           // the IMMA kernel quantizes src1 itself up to this many (column, unit) pairs (0: never - measured no faster than the PDL-chained quantizer launch); GGML_B200_MMA_FUSE_UNITS
     int          mma_warps = 0;                // 0 = auto; GGML_B200_MMA_WARPS
     // the fp16 activation operand last built in scratch2 (kind::f16 prefill): valid for further matrices of the same shared-src1 group

@@ -273,6 +273,7 @@ struct MvParams {
 
 // one-column plain launches of these formats run on mv_lean_kernel, which consumes ring stages in pairs (wants 4 stages)
 bool mv_lean_type(int type);
+constexpr int MV_LEAN_MAX_COLS = 4;
 // smem bytes needed by the fast kernel for a configuration
 size_t mv_fast_smem(int type, int U, int ncols, int n_cons, int n_stages);
 // launches the persistent TMA-staged mat-vec kernel (type, ncols 1..8); grid = n_ctas

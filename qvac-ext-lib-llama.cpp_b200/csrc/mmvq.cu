@@ -691,52 +691,75 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
 // ------------------------------------------------------------------------------------------------
 
 // two weight units (w0, w1: same unit index, different rows) against one activation unit
-__device__ __forceinline__ void unit_dot2_q4_K(uint32_t w0, uint32_t w1, uint32_t am, uint32_t ax, float & acc0, float & acc1) {
+template <int NC>
+__device__ __forceinline__ void unit_dot2_q4_K(uint32_t w0, uint32_t w1, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc0)[NC],
+                                               float (&acc1)[NC]) {
     const uint4 hA = lds128o<0>(w0), hB = lds128o<0>(w1);
     const uint32_t scA_lo = hA.y & 0x3f3f3f3fu, scA_hi = (hA.w & 0x0f0f0f0fu) | ((hA.y >> 2) & 0x30303030u);
     const uint32_t scB_lo = hB.y & 0x3f3f3f3fu, scB_hi = (hB.w & 0x0f0f0f0fu) | ((hB.y >> 2) & 0x30303030u);
-    int isA = 0, isB = 0;
+    int isA[NC], isB[NC];
+    uint32_t ac[NC];
+#pragma unroll
+    for (int c = 0; c < NC; c++) { isA[c] = 0; isB[c] = 0; ac[c] = am + c * cs_m; }
     static_for<0, 4>([&](auto gi) {
         constexpr int g = decltype(gi)::value;
-        const uint4 l0 = lds128o<64 * g>(am), l1 = lds128o<64 * g + 16>(am), h0 = lds128o<64 * g + 32>(am), h1 = lds128o<64 * g + 48>(am);
-        const int lo[8] = { (int) l0.x, (int) l0.y, (int) l0.z, (int) l0.w, (int) l1.x, (int) l1.y, (int) l1.z, (int) l1.w };
-        const int hi[8] = { (int) h0.x, (int) h0.y, (int) h0.z, (int) h0.w, (int) h1.x, (int) h1.y, (int) h1.z, (int) h1.w };
         const uint4 a0 = lds128o<16 + 32 * g>(w0), a1 = lds128o<32 + 32 * g>(w0);
         const uint4 b0 = lds128o<16 + 32 * g>(w1), b1 = lds128o<32 + 32 * g>(w1);
         const uint32_t qa[8] = { a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w };
         const uint32_t qb[8] = { b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w };
-        int sAl = 0, sAh = 0, sBl = 0, sBh = 0;
-#pragma unroll
-        for (int k = 0; k < 8; k++) {
-            sAl = dp4a_us(qa[k] & 0x0f0f0f0fu, lo[k], sAl);
-            sBl = dp4a_us(qb[k] & 0x0f0f0f0fu, lo[k], sBl);
-            sAh = dp4a_us(qa[k] & 0xf0f0f0f0u, hi[k], sAh);  // 16 x the high-nibble dot product
-            sBh = dp4a_us(qb[k] & 0xf0f0f0f0u, hi[k], sBh);
-        }
         const uint32_t wA = g < 2 ? scA_lo : scA_hi, wB = g < 2 ? scB_lo : scB_hi;
-        isA += (int) ((wA >> (16 * (g & 1))) & 0xff) * sAl + (int) ((wA >> (16 * (g & 1) + 8)) & 0xff) * (sAh >> 4);
-        isB += (int) ((wB >> (16 * (g & 1))) & 0xff) * sBl + (int) ((wB >> (16 * (g & 1) + 8)) & 0xff) * (sBh >> 4);
+        const int sA0 = (int) ((wA >> (16 * (g & 1))) & 0xff), sA1 = (int) ((wA >> (16 * (g & 1) + 8)) & 0xff);
+        const int sB0 = (int) ((wB >> (16 * (g & 1))) & 0xff), sB1 = (int) ((wB >> (16 * (g & 1) + 8)) & 0xff);
+#pragma unroll
+        for (int c = 0; c < NC; c++) {
+            const uint4 l0 = lds128o<64 * g>(ac[c]), l1 = lds128o<64 * g + 16>(ac[c]), h0 = lds128o<64 * g + 32>(ac[c]), h1 = lds128o<64 * g + 48>(ac[c]);
+            const int lo[8] = { (int) l0.x, (int) l0.y, (int) l0.z, (int) l0.w, (int) l1.x, (int) l1.y, (int) l1.z, (int) l1.w };
+            const int hi[8] = { (int) h0.x, (int) h0.y, (int) h0.z, (int) h0.w, (int) h1.x, (int) h1.y, (int) h1.z, (int) h1.w };
+            int sAl = 0, sAh = 0, sBl = 0, sBh = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                sAl = dp4a_us(qa[k] & 0x0f0f0f0fu, lo[k], sAl);
+                sBl = dp4a_us(qb[k] & 0x0f0f0f0fu, lo[k], sBl);
+                sAh = dp4a_us(qa[k] & 0xf0f0f0f0u, hi[k], sAh);  // 16 x the high-nibble dot product
+                sBh = dp4a_us(qb[k] & 0xf0f0f0f0u, hi[k], sBh);
+            }
+            isA[c] += sA0 * sAl + sA1 * (sAh >> 4);
+            isB[c] += sB0 * sBl + sB1 * (sBh >> 4);
+        }
     });
-    const uint4 bs = lds128o<256>(am);  // int16 sum of q per 32-block (x8)
-    const float dy = __uint_as_float(lds32(ax));
     const uint32_t mnA_lo = hA.z & 0x3f3f3f3fu, mnA_hi = ((hA.w >> 4) & 0x0f0f0f0fu) | ((hA.z >> 2) & 0x30303030u);
     const uint32_t mnB_lo = hB.z & 0x3f3f3f3fu, mnB_hi = ((hB.w >> 4) & 0x0f0f0f0fu) | ((hB.z >> 2) & 0x30303030u);
-    int mA = dp2a_lo_su((int) bs.x, mnA_lo, 0), mB = dp2a_lo_su((int) bs.x, mnB_lo, 0);
-    mA = dp2a_hi_su((int) bs.y, mnA_lo, mA); mB = dp2a_hi_su((int) bs.y, mnB_lo, mB);
-    mA = dp2a_lo_su((int) bs.z, mnA_hi, mA); mB = dp2a_lo_su((int) bs.z, mnB_hi, mB);
-    mA = dp2a_hi_su((int) bs.w, mnA_hi, mA); mB = dp2a_hi_su((int) bs.w, mnB_hi, mB);
-    // the same two fused multiply-adds per unit as unit_dot_q4_K: results are bit-identical to the one-unit path
-    acc0 = fmaf(half_bits_to_float((uint16_t) (hA.x & 0xffff)) * dy, (float) isA, acc0);
-    acc0 = fmaf(-(half_bits_to_float((uint16_t) (hA.x >> 16)) * dy), (float) mA, acc0);
-    acc1 = fmaf(half_bits_to_float((uint16_t) (hB.x & 0xffff)) * dy, (float) isB, acc1);
-    acc1 = fmaf(-(half_bits_to_float((uint16_t) (hB.x >> 16)) * dy), (float) mB, acc1);
+    const float dA = half_bits_to_float((uint16_t) (hA.x & 0xffff)), mA_ = half_bits_to_float((uint16_t) (hA.x >> 16));
+    const float dB = half_bits_to_float((uint16_t) (hB.x & 0xffff)), mB_ = half_bits_to_float((uint16_t) (hB.x >> 16));
+#pragma unroll
+    for (int c = 0; c < NC; c++) {
+        const uint4 bs = lds128o<256>(ac[c]);  // int16 sum of q per 32-block (x8)
+        const float dy = __uint_as_float(lds32(ax + c * cs_x));
+        int mA = dp2a_lo_su((int) bs.x, mnA_lo, 0), mB = dp2a_lo_su((int) bs.x, mnB_lo, 0);
+        mA = dp2a_hi_su((int) bs.y, mnA_lo, mA); mB = dp2a_hi_su((int) bs.y, mnB_lo, mB);
+        mA = dp2a_lo_su((int) bs.z, mnA_hi, mA); mB = dp2a_lo_su((int) bs.z, mnB_hi, mB);
+        mA = dp2a_hi_su((int) bs.w, mnA_hi, mA); mB = dp2a_hi_su((int) bs.w, mnB_hi, mB);
+        // the same two fused multiply-adds per unit and column as unit_dot_q4_K: results are bit-identical to the one-unit path
+        acc0[c] = fmaf(dA * dy, (float) isA[c], acc0[c]);
+        acc0[c] = fmaf(-(mA_ * dy), (float) mA, acc0[c]);
+        acc1[c] = fmaf(dB * dy, (float) isB[c], acc1[c]);
+        acc1[c] = fmaf(-(mB_ * dy), (float) mB, acc1[c]);
+    }
 }
 
 // q4_0 / q8_0 pairs: the unit is walked in two halves of four blocks, so that two rows' weights fit in registers next to the
 // activation words they share. Same operations per block and row as unit_dot_q4_0 / unit_dot_q8_0 (bit-identical results).
-__device__ __forceinline__ void unit_dot2_q4_0(uint32_t w0, uint32_t w1, uint32_t am, uint32_t ax, float & acc0, float & acc1) {
-    const uint4 dyh = lds128o<256>(am);   // half d[8]
-    const uint4 ys  = lds128(ax);         // int16 sum[8]
+template <int NC>
+__device__ __forceinline__ void unit_dot2_q4_0(uint32_t w0, uint32_t w1, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc0)[NC],
+                                               float (&acc1)[NC]) {
+    uint4    dyh[NC], ys[NC];
+    uint32_t ac[NC];
+#pragma unroll
+    for (int c = 0; c < NC; c++) {
+        ac[c]  = am + c * cs_m;
+        dyh[c] = lds128o<256>(ac[c]);      // half d[8]
+        ys[c]  = lds128(ax + c * cs_x);    // int16 sum[8]
+    }
     static_for<0, 2>([&](auto hi_) {
         constexpr int H  = decltype(hi_)::value;
         constexpr int W0 = 16 * H;        // first word held: words W0 .. W0 + 19 cover block pairs 2H and 2H + 1 (words 18H .. 18H + 17)
@@ -750,12 +773,6 @@ __device__ __forceinline__ void unit_dot2_q4_0(uint32_t w0, uint32_t w1, uint32_
         static_for<0, 4>([&](auto bi) {
             constexpr int blk = 4 * H + decltype(bi)::value;
             constexpr int p   = 9 * (blk >> 1) - W0;  // index of the block pair's first word in a[] / b[]
-            const uint4 l = lds128o<32 * blk>(am), h = lds128o<32 * blk + 16>(am);
-            const int lo[4] = { (int) l.x, (int) l.y, (int) l.z, (int) l.w }, hi[4] = { (int) h.x, (int) h.y, (int) h.z, (int) h.w };
-            const uint32_t dword = blk < 2 ? dyh.x : blk < 4 ? dyh.y : blk < 6 ? dyh.z : dyh.w;
-            const uint32_t sword = blk < 2 ? ys.x : blk < 4 ? ys.y : blk < 6 ? ys.z : ys.w;
-            const float    dy    = half_bits_to_float((uint16_t) ((blk & 1) ? dword >> 16 : dword & 0xffff));
-            const int      ysum  = (int) (int16_t) ((blk & 1) ? sword >> 16 : sword & 0xffff);
             float dA, dB;
             uint32_t qa[4], qb[4];
             if ((blk & 1) == 0) {
@@ -767,20 +784,33 @@ __device__ __forceinline__ void unit_dot2_q4_0(uint32_t w0, uint32_t w1, uint32_
 #pragma unroll
                 for (int k = 0; k < 4; k++) { qa[k] = a[p + 5 + k]; qb[k] = b[p + 5 + k]; }
             }
-            int sAl = 0, sAh = 0, sBl = 0, sBh = 0;
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-                sAl = dp4a_us(qa[k] & 0x0f0f0f0fu, lo[k], sAl); sAh = dp4a_us(qa[k] & 0xf0f0f0f0u, hi[k], sAh);
-                sBl = dp4a_us(qb[k] & 0x0f0f0f0fu, lo[k], sBl); sBh = dp4a_us(qb[k] & 0xf0f0f0f0u, hi[k], sBh);
+            for (int c = 0; c < NC; c++) {
+                const uint4 l = lds128o<32 * blk>(ac[c]), h = lds128o<32 * blk + 16>(ac[c]);
+                const int lo[4] = { (int) l.x, (int) l.y, (int) l.z, (int) l.w }, hi[4] = { (int) h.x, (int) h.y, (int) h.z, (int) h.w };
+                const uint32_t dword = blk < 2 ? dyh[c].x : blk < 4 ? dyh[c].y : blk < 6 ? dyh[c].z : dyh[c].w;
+                const uint32_t sword = blk < 2 ? ys[c].x : blk < 4 ? ys[c].y : blk < 6 ? ys[c].z : ys[c].w;
+                const float    dy    = half_bits_to_float((uint16_t) ((blk & 1) ? dword >> 16 : dword & 0xffff));
+                const int      ysum  = (int) (int16_t) ((blk & 1) ? sword >> 16 : sword & 0xffff);
+                int sAl = 0, sAh = 0, sBl = 0, sBh = 0;
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    sAl = dp4a_us(qa[k] & 0x0f0f0f0fu, lo[k], sAl); sAh = dp4a_us(qa[k] & 0xf0f0f0f0u, hi[k], sAh);
+                    sBl = dp4a_us(qb[k] & 0x0f0f0f0fu, lo[k], sBl); sBh = dp4a_us(qb[k] & 0xf0f0f0f0u, hi[k], sBh);
+                }
+                acc0[c] = fmaf((float) (sAl + (sAh >> 4) - 8 * ysum) * dA, dy, acc0[c]);
+                acc1[c] = fmaf((float) (sBl + (sBh >> 4) - 8 * ysum) * dB, dy, acc1[c]);
             }
-            acc0 = fmaf((float) (sAl + (sAh >> 4) - 8 * ysum) * dA, dy, acc0);
-            acc1 = fmaf((float) (sBl + (sBh >> 4) - 8 * ysum) * dB, dy, acc1);
         });
     });
 }
 
-__device__ __forceinline__ void unit_dot2_q8_0(uint32_t w0, uint32_t w1, uint32_t am, float & acc0, float & acc1) {
-    const uint4 dyh = lds128o<256>(am);
+template <int NC>
+__device__ __forceinline__ void unit_dot2_q8_0(uint32_t w0, uint32_t w1, uint32_t am, uint32_t cs_m, float (&acc0)[NC], float (&acc1)[NC]) {
+    uint4    dyh[NC];
+    uint32_t ac[NC];
+#pragma unroll
+    for (int c = 0; c < NC; c++) { ac[c] = am + c * cs_m; dyh[c] = lds128o<256>(ac[c]); }
     static_for<0, 4>([&](auto pi) {
         constexpr int P = decltype(pi)::value;           // block pair: 68 bytes = words 17P .. 17P + 16
         constexpr int W0 = (17 * P) & ~3;                 // 16-byte aligned start; up to 3 words of slack in front
@@ -797,47 +827,49 @@ __device__ __forceinline__ void unit_dot2_q8_0(uint32_t w0, uint32_t w1, uint32_
         constexpr int p = 17 * P - W0;
         static_for<0, 2>([&](auto ei) {
             constexpr int e = decltype(ei)::value, blk = 2 * P + e;
-            const uint4 y0 = lds128o<32 * blk>(am), y1 = lds128o<32 * blk + 16>(am);
-            const int y[8] = { (int) y0.x, (int) y0.y, (int) y0.z, (int) y0.w, (int) y1.x, (int) y1.y, (int) y1.z, (int) y1.w };
-            const uint32_t dword = blk < 2 ? dyh.x : blk < 4 ? dyh.y : blk < 6 ? dyh.z : dyh.w;
-            const float    dy    = half_bits_to_float((uint16_t) ((blk & 1) ? dword >> 16 : dword & 0xffff));
             float dA, dB;
-            int sA = 0, sB = 0;
+            uint32_t qa[8], qb[8];
             if (e == 0) {
                 dA = half_bits_to_float((uint16_t) (a[p] & 0xffff)); dB = half_bits_to_float((uint16_t) (b[p] & 0xffff));
 #pragma unroll
-                for (int k = 0; k < 8; k++) {
-                    sA = dp4a_ss((int) __funnelshift_r(a[p + k], a[p + k + 1], 16), y[k], sA);
-                    sB = dp4a_ss((int) __funnelshift_r(b[p + k], b[p + k + 1], 16), y[k], sB);
-                }
+                for (int k = 0; k < 8; k++) { qa[k] = __funnelshift_r(a[p + k], a[p + k + 1], 16); qb[k] = __funnelshift_r(b[p + k], b[p + k + 1], 16); }
             } else {
                 dA = half_bits_to_float((uint16_t) (a[p + 8] >> 16)); dB = half_bits_to_float((uint16_t) (b[p + 8] >> 16));
 #pragma unroll
-                for (int k = 0; k < 8; k++) { sA = dp4a_ss((int) a[p + 9 + k], y[k], sA); sB = dp4a_ss((int) b[p + 9 + k], y[k], sB); }
+                for (int k = 0; k < 8; k++) { qa[k] = a[p + 9 + k]; qb[k] = b[p + 9 + k]; }
             }
-            acc0 = fmaf((float) sA, dA * dy, acc0);
-            acc1 = fmaf((float) sB, dB * dy, acc1);
+#pragma unroll
+            for (int c = 0; c < NC; c++) {
+                const uint4 y0 = lds128o<32 * blk>(ac[c]), y1 = lds128o<32 * blk + 16>(ac[c]);
+                const int y[8] = { (int) y0.x, (int) y0.y, (int) y0.z, (int) y0.w, (int) y1.x, (int) y1.y, (int) y1.z, (int) y1.w };
+                const uint32_t dword = blk < 2 ? dyh[c].x : blk < 4 ? dyh[c].y : blk < 6 ? dyh[c].z : dyh[c].w;
+                const float    dy    = half_bits_to_float((uint16_t) ((blk & 1) ? dword >> 16 : dword & 0xffff));
+                int sA = 0, sB = 0;
+#pragma unroll
+                for (int k = 0; k < 8; k++) { sA = dp4a_ss((int) qa[k], y[k], sA); sB = dp4a_ss((int) qb[k], y[k], sB); }
+                acc0[c] = fmaf((float) sA, dA * dy, acc0[c]);
+                acc1[c] = fmaf((float) sB, dB * dy, acc1[c]);
+            }
         });
     });
 }
 
-template <int TYPE>
-__device__ __forceinline__ void unit_dot2(uint32_t w0, uint32_t w1, uint32_t am, uint32_t ax, float & acc0, float & acc1) {
+template <int TYPE, int NC>
+__device__ __forceinline__ void unit_dot2(uint32_t w0, uint32_t w1, uint32_t am, uint32_t ax, uint32_t cs_m, uint32_t cs_x, float (&acc0)[NC],
+                                          float (&acc1)[NC]) {
     if (TYPE == B200_TYPE_Q4_K) {
-        unit_dot2_q4_K(w0, w1, am, ax, acc0, acc1);
+        unit_dot2_q4_K<NC>(w0, w1, am, ax, cs_m, cs_x, acc0, acc1);
     } else if (TYPE == B200_TYPE_Q4_0) {
-        unit_dot2_q4_0(w0, w1, am, ax, acc0, acc1);
+        unit_dot2_q4_0<NC>(w0, w1, am, ax, cs_m, cs_x, acc0, acc1);
     } else if (TYPE == B200_TYPE_Q8_0) {
-        unit_dot2_q8_0(w0, w1, am, acc0, acc1);
-    } else {  // the other formats keep their one-unit dot products (their register footprint does not allow two at once)
-        float a[1] = { acc0 }, b[1] = { acc1 };
-        unit_dot<TYPE, 1>(w0, am, ax, 0, 0, a);
-        unit_dot<TYPE, 1>(w1, am, ax, 0, 0, b);
-        acc0 = a[0]; acc1 = b[0];
+        unit_dot2_q8_0<NC>(w0, w1, am, cs_m, acc0, acc1);
+    } else {  // the other formats keep their one-unit dot products
+        unit_dot<TYPE, NC>(w0, am, ax, cs_m, cs_x, acc0);
+        unit_dot<TYPE, NC>(w1, am, ax, cs_m, cs_x, acc1);
     }
 }
 
-template <int TYPE>
+template <int TYPE, int NC>
 __global__ void __launch_bounds__(32 * (MV_MAX_CONS + 1), 1)
 mv_lean_kernel(const __grid_constant__ MvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -854,8 +886,8 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     uint64_t * empty   = full + NWC * NS;
     size_t     off     = mv_align(MV_HDR_BYTES + (size_t) 16 * NWC * NS, 128);
     uint8_t *  act_m   = smem + off;
-    uint8_t *  act_x   = act_m + (size_t) U * ACT_MAIN;
-    off                = mv_align(off + (size_t) U * (ACT_MAIN + ACT_AUX), 128);
+    uint8_t *  act_x   = act_m + (size_t) NC * U * ACT_MAIN;
+    off                = mv_align(off + (size_t) NC * U * (ACT_MAIN + ACT_AUX), 128);
     uint8_t *  ring0   = smem + off;
 
     const int g_begin = (int) ((int64_t) p.total_groups * blockIdx.x / gridDim.x);
@@ -953,13 +985,16 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     if (w == 0) MV_TRACE(3);
     if (warp > NWC && !p.fuse_quant) return;
     if (p.fuse_quant) {
-        for (int t0 = qw; t0 < U; t0 += 4 * NQ) {
+        constexpr int n_tasks_per_col = 0; (void) n_tasks_per_col;
+        const int n_tasks = NC * U;   // task t = (column t / U, unit t % U); the records of column c start at c * U
+        for (int t0 = qw; t0 < n_tasks; t0 += 4 * NQ) {
             float v[4][8];
 #pragma unroll
             for (int b = 0; b < 4; b++) {
                 const int t = t0 + b * NQ;
-                if (t < U) {
-                    const float * xr = p.x + (int64_t) t * UNIT_ELEMS + lane * 8;
+                if (t < n_tasks) {
+                    const int c = NC == 1 ? 0 : t / U, u = t - c * U;
+                    const float * xr = (const float *) ((const char *) p.x + (int64_t) c * p.x_cs) + (int64_t) u * UNIT_ELEMS + lane * 8;
                     if (p.x_vec) {
                         const float4 a = __ldg((const float4 *) xr);
                         const float4 bb = __ldg((const float4 *) xr + 1);
@@ -978,7 +1013,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
 #pragma unroll
             for (int b = 0; b < 4; b++) {
                 const int t = t0 + b * NQ;
-                if (t < U) quant_unit_store<KIND>(v[b], lane, act_m + (size_t) t * ACT_MAIN, act_x + (size_t) t * ACT_AUX);
+                if (t < n_tasks) quant_unit_store<KIND>(v[b], lane, act_m + (size_t) t * ACT_MAIN, act_x + (size_t) t * ACT_AUX);
             }
         }
         bar_sync_named(1, NQ * 32);
@@ -986,7 +1021,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     } else {
         if (w == 0 && lane == 0) {
             const uint64_t pol_keep = l2_policy_evict_last();
-            const uint32_t bytes_m = (uint32_t) U * ACT_MAIN, bytes_x = (uint32_t) U * ACT_AUX;
+            const uint32_t bytes_m = (uint32_t) NC * U * ACT_MAIN, bytes_x = (uint32_t) NC * U * ACT_AUX;
             mbar_expect_tx(smem_u32(act_bar), bytes_m + bytes_x);
             bulk_g2s(smem_u32(act_m), p.act_main, bytes_m, smem_u32(act_bar), pol_keep);
             bulk_g2s(smem_u32(act_x), p.act_aux, bytes_x, smem_u32(act_bar), pol_keep);
@@ -1002,23 +1037,30 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     const uint32_t fullw = smem_u32(full + w * NS), emptyw = smem_u32(empty + w * NS);
     const uint32_t am0 = smem_u32(act_m) + (uint32_t) sub * ACT_MAIN, ax0 = smem_u32(act_x) + (uint32_t) sub * ACT_AUX;
     const bool     lane_on = rr < p.rpg;
+    const uint32_t cs_m = (uint32_t) U * ACT_MAIN, cs_x = (uint32_t) U * ACT_AUX;
 
-    auto reduce_store = [&](float v, int group) {  // sum over the L lanes of a row, one store per row
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const float t = __shfl_xor_sync(0xffffffffu, v, o);
-            if (o < L) v += t;
-        }
+    auto reduce_store = [&](float (&a)[NC], int group) {  // sum over the L lanes of a row, one store per row and column
         const MvMat & mat = p.mat[mv_find_mat(p, group)];
         const int     row = (group - mat.group0) * p.rpg + rr;
-        if (sub == 0 && lane_on && row < mat.M) mat.dst[row] = v;
+#pragma unroll
+        for (int c = 0; c < NC; c++) {
+            float v = a[c];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float t = __shfl_xor_sync(0xffffffffu, v, o);
+                if (o < L) v += t;
+            }
+            if (sub == 0 && lane_on && row < mat.M) mat.dst[(int64_t) c * mat.dst_cs + row] = v;
+        }
     };
 
     int stage = 0;
     uint32_t phase = 0;
     const int n_pairs = cnt >> 1;
     for (int pg = 0; pg < n_pairs; pg++) {
-        float accA = 0.0f, accB = 0.0f;
+        float accA[NC], accB[NC];
+#pragma unroll
+        for (int c = 0; c < NC; c++) { accA[c] = 0.0f; accB[c] = 0.0f; }
         for (int s = 0; s < SL; s++) {
             mbar_wait(fullw + 8 * stage, phase);
             mbar_wait(fullw + 8 * stage + 8, phase);
@@ -1026,7 +1068,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
             const int nu = min(32, U - s * 32);
             if (lane_on && sub < nu) {
                 const uint32_t wp = ring + (uint32_t) stage * STAGE + (uint32_t) (rr * nu + sub) * UB;
-                unit_dot2<TYPE>(wp, wp + STAGE, am0 + (uint32_t) s * 32 * ACT_MAIN, ax0 + (uint32_t) s * 32 * ACT_AUX, accA, accB);
+                unit_dot2<TYPE, NC>(wp, wp + STAGE, am0 + (uint32_t) s * 32 * ACT_MAIN, ax0 + (uint32_t) s * 32 * ACT_AUX, cs_m, cs_x, accA, accB);
             }
             __syncwarp();
             if (lane == 0) { mbar_arrive(emptyw + 8 * stage); mbar_arrive(emptyw + 8 * stage + 8); }
@@ -1038,39 +1080,41 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
         reduce_store(accB, groupA + NWC);
     }
     if (cnt & 1) {  // the odd group at the end of the warp's list: one stage per slice
-        float acc[1] = { 0.0f };
+        float acc[NC];
+#pragma unroll
+        for (int c = 0; c < NC; c++) acc[c] = 0.0f;
         for (int s = 0; s < SL; s++) {
             mbar_wait(fullw + 8 * stage, phase);
             if (w == 0 && n_pairs == 0 && s == 0) MV_TRACE(5);
             const int nu = min(32, U - s * 32);
             if (lane_on && sub < nu) {
                 const uint32_t wp = ring + (uint32_t) stage * STAGE + (uint32_t) (rr * nu + sub) * UB;
-                unit_dot<TYPE, 1>(wp, am0 + (uint32_t) s * 32 * ACT_MAIN, ax0 + (uint32_t) s * 32 * ACT_AUX, 0, 0, acc);
+                unit_dot<TYPE, NC>(wp, am0 + (uint32_t) s * 32 * ACT_MAIN, ax0 + (uint32_t) s * 32 * ACT_AUX, cs_m, cs_x, acc);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(emptyw + 8 * stage);
             if (++stage == NS) { stage = 0; phase ^= 1; }
         }
-        reduce_store(acc[0], g_begin + w + (cnt - 1) * NWC);
+        reduce_store(acc, g_begin + w + (cnt - 1) * NWC);
     }
     if (w == 0) MV_TRACE(6);
 }
 
-template <int TYPE>
+template <int TYPE, int NC>
 static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t smem, cudaStream_t st) {
     MvParams p = p_in;
     p.n_helpers = 0;
     if (p.fuse_quant && !(p.dbg & 4)) {   // as many quantizing warps as src1 has units, up to the 16 + 1 warps the kernel is compiled for
-        const int room = MV_MAX_CONS - p.n_cons, want = p.U - p.n_cons;
+        const int room = MV_MAX_CONS - p.n_cons, want = NC * p.U - p.n_cons;
         p.n_helpers = want < 0 ? 0 : (want < room ? want : room);
     }
     static bool attr_done[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
@@ -1088,14 +1132,25 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
     }
     cfg.attrs    = attr;
     cfg.numAttrs = na;
-    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE>, p);
+    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE, NC>, p);
 }
 
 // the launch can take the lean kernel: one column, plain MUL_MAT, no exchange, no epilogue, an even ring
+template <int TYPE>
+static cudaError_t mv_lean_launch_n(int nc, const MvParams & p, int n_ctas, size_t smem, cudaStream_t st) {
+    switch (nc) {
+        case 1: return mv_lean_launch_t<TYPE, 1>(p, n_ctas, smem, st);
+        case 2: return mv_lean_launch_t<TYPE, 2>(p, n_ctas, smem, st);
+        case 3: return mv_lean_launch_t<TYPE, 3>(p, n_ctas, smem, st);
+        case 4: return mv_lean_launch_t<TYPE, 4>(p, n_ctas, smem, st);
+    }
+    return cudaErrorInvalidValue;
+}
+
 bool mv_lean_type(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0; }  // formats with a two-unit dot product
 
 static bool mv_lean_ok(int type, int ncols, const MvParams & p, int n_pairs) {
-    if (!mv_lean_type(type) || ncols != 1 || n_pairs != 1 || p.ids.ids || p.split.n_ranks > 1 || p.epi.glu || (p.n_stages & 1) || (p.dbg & 1)) return false;
+    if (!mv_lean_type(type) || ncols < 1 || ncols > MV_LEAN_MAX_COLS || n_pairs != 1 || p.ids.ids || p.split.n_ranks > 1 || p.epi.glu || (p.n_stages & 1) || (p.dbg & 1)) return false;
     for (int i = 0; i < p.n_mats; i++) if (p.mat[i].bias) return false;
     return true;
 }
@@ -1165,11 +1220,11 @@ static cudaError_t mv_fast_launch_n(int nc, const MvParams & p, int n_ctas, int 
 cudaError_t mv_fast_launch(int type, int ncols, const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
     if (mv_lean_ok(type, ncols, p, n_pairs)) {
         switch (type) {
-            case B200_TYPE_Q4_0: return mv_lean_launch_t<B200_TYPE_Q4_0>(p, n_ctas, smem, st);
-            case B200_TYPE_Q8_0: return mv_lean_launch_t<B200_TYPE_Q8_0>(p, n_ctas, smem, st);
-            case B200_TYPE_Q4_K: return mv_lean_launch_t<B200_TYPE_Q4_K>(p, n_ctas, smem, st);
-            case B200_TYPE_Q5_K: return mv_lean_launch_t<B200_TYPE_Q5_K>(p, n_ctas, smem, st);
-            case B200_TYPE_Q6_K: return mv_lean_launch_t<B200_TYPE_Q6_K>(p, n_ctas, smem, st);
+            case B200_TYPE_Q4_0: return mv_lean_launch_n<B200_TYPE_Q4_0>(ncols, p, n_ctas, smem, st);
+            case B200_TYPE_Q8_0: return mv_lean_launch_n<B200_TYPE_Q8_0>(ncols, p, n_ctas, smem, st);
+            case B200_TYPE_Q4_K: return mv_lean_launch_n<B200_TYPE_Q4_K>(ncols, p, n_ctas, smem, st);
+            case B200_TYPE_Q5_K: return mv_lean_launch_n<B200_TYPE_Q5_K>(ncols, p, n_ctas, smem, st);
+            case B200_TYPE_Q6_K: return mv_lean_launch_n<B200_TYPE_Q6_K>(ncols, p, n_ctas, smem, st);
         }
     }
     switch (type) {
