@@ -55,6 +55,7 @@ struct split_peer {
     size_t     x_size  = 0;
     void *     d       = nullptr;
     size_t     d_size  = 0;
+    bool       direct  = false;   // peer access works both ways: the slice is stored straight into the main device's dst
 };
 struct be_ctx {
     int        device;
@@ -486,18 +487,30 @@ ggml_status split_mul_mat(be_ctx * c, ggml_tensor * node, const b200_mul_mat_des
             }
             b200_ctx_set_weight_cache(sp.ctx, c->weight_cache);
             CHECK(b200_event_create(id, &sp.event));
-            b200_enable_peer_access(id, c->device);  // best effort: the copies are staged by the driver otherwise
-            b200_enable_peer_access(c->device, id);
+            // with peer access the other device's kernels write their rows of dst where they belong - in the main device's memory,
+            // through NVLink - instead of into scratch that is then copied over (the reference's cudaMemcpy2DPeerAsync per device,
+            // ggml-cuda.cu:1721-1734); without it the copies are staged by the driver
+            const bool to_main = b200_enable_peer_access(id, c->device) == B200_OK;
+            const bool from_main = b200_enable_peer_access(c->device, id) == B200_OK;
+            const char * nd = getenv("GGML_B200_SPLIT_NO_DIRECT");
+            sp.direct = to_main && from_main && !(nd && atoi(nd));
         }
-        if (!grow(id, &sp.x, &sp.x_size, x_bytes) || !grow(id, &sp.d, &sp.d_size, (size_t) N * rows * sizeof(float))) return GGML_STATUS_ALLOC_FAILED;
+        if (!grow(id, &sp.x, &sp.x_size, x_bytes)) return GGML_STATUS_ALLOC_FAILED;
+        // (prefill-sized results go through scratch + one coalesced 2-D copy: 4-byte epilogue stores over NVLink ran 2-3x slower)
+        const bool direct = sp.direct && N <= 8;
+        if (!direct && !grow(id, &sp.d, &sp.d_size, (size_t) N * rows * sizeof(float))) return GGML_STATUS_ALLOC_FAILED;
         CHECK(b200_event_wait(sp.ctx, c->split_event));
         // src1 rows may be strided on the main device: pack them into [N][K] on the peer
         CHECK(b200_memcpy2d_async(sp.ctx, sp.x, (size_t) K * sizeof(float), b->data, full.nb11, (size_t) K * sizeof(float), (size_t) N));
         d.nb11 = (size_t) K * sizeof(float); d.nb12 = d.nb11 * N; d.nb13 = d.nb12;
-        d.nb1  = (size_t) rows * sizeof(float); d.nb2 = d.nb1 * N; d.nb3 = d.nb2;
-        CHECK(b200_mul_mat(sp.ctx, &d, e->data[id], (const float *) sp.x, (float *) sp.d));
-        CHECK(b200_memcpy2d_async(sp.ctx, (float *) node->data + e->row_low[id], full.nb1, sp.d, (size_t) rows * sizeof(float),
-                                  (size_t) rows * sizeof(float), (size_t) N));
+        if (direct) {   // dst keeps the full tensor's strides: row slice [row_low, row_high) of every column, on the main device
+            CHECK(b200_mul_mat(sp.ctx, &d, e->data[id], (const float *) sp.x, (float *) node->data + e->row_low[id]));
+        } else {
+            d.nb1 = (size_t) rows * sizeof(float); d.nb2 = d.nb1 * N; d.nb3 = d.nb2;
+            CHECK(b200_mul_mat(sp.ctx, &d, e->data[id], (const float *) sp.x, (float *) sp.d));
+            CHECK(b200_memcpy2d_async(sp.ctx, (float *) node->data + e->row_low[id], full.nb1, sp.d, (size_t) rows * sizeof(float),
+                                      (size_t) rows * sizeof(float), (size_t) N));
+        }
         CHECK(b200_event_record(sp.ctx, sp.event));
     }
     for (int id = 0; id < split_dev_count(); id++) {

@@ -983,6 +983,9 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
 
     griddep_wait();
     if (w == 0) MV_TRACE(3);
+    // row split, flagged-payload exchange (kernels.h ll_store / ll_receive): this launch's epoch is final once the stream dependency is
+    const bool     ll = p.split.n_ranks > 1;   // the launcher only sends split launches here when they use the flagged payload
+    const uint32_t ep = ll ? ll_epoch(p.split) : 0u;
     if (warp > NWC && !p.fuse_quant) return;
     if (p.fuse_quant) {
         constexpr int n_tasks_per_col = 0; (void) n_tasks_per_col;
@@ -1050,7 +1053,11 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
                 const float t = __shfl_xor_sync(0xffffffffu, v, o);
                 if (o < L) v += t;
             }
-            if (sub == 0 && lane_on && row < mat.M) mat.dst[(int64_t) c * mat.dst_cs + row] = v;
+            if (sub == 0 && lane_on && row < mat.M) {
+                float * a = mat.dst + (int64_t) c * mat.dst_cs + row;
+                if (ll) ll_store(p.split, ep, a, v);
+                else *a = v;
+            }
         }
     };
 
@@ -1098,6 +1105,11 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
         reduce_store(acc, g_begin + w + (cnt - 1) * NWC);
     }
     if (w == 0) MV_TRACE(6);
+    if (ll) {  // this CTA's rows are on their way to every rank; collect this CTA's share of the peers' rows
+        ll_receive(p.split, ep, p.geom, p.mat, p.n_mats, NC, (int) blockIdx.x * NWC * 32 + w * 32 + lane, (int) gridDim.x * NWC * 32);
+        bar_sync_named(2, NWC * 32);
+        if (w == 0 && lane == 0) ll_finish(p.split, ep, gridDim.x);
+    }
 }
 
 template <int TYPE, int NC>
@@ -1150,7 +1162,7 @@ static cudaError_t mv_lean_launch_n(int nc, const MvParams & p, int n_ctas, size
 bool mv_lean_type(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0; }  // formats with a two-unit dot product
 
 static bool mv_lean_ok(int type, int ncols, const MvParams & p, int n_pairs) {
-    if (!mv_lean_type(type) || ncols < 1 || ncols > MV_LEAN_MAX_COLS || n_pairs != 1 || p.ids.ids || p.split.n_ranks > 1 || p.epi.glu || (p.n_stages & 1) || (p.dbg & 1)) return false;
+    if (!mv_lean_type(type) || ncols < 1 || ncols > MV_LEAN_MAX_COLS || n_pairs != 1 || p.ids.ids || (p.split.n_ranks > 1 && !p.split.ll) || p.epi.glu || (p.n_stages & 1) || (p.dbg & 1)) return false;
     for (int i = 0; i < p.n_mats; i++) if (p.mat[i].bias) return false;
     return true;
 }

@@ -267,3 +267,105 @@ def test_flagged_payload_exchange_loopback(pkg, oracle, t, N, graph):
             assert words[32] == 0                                                   # no flag was published: the data carried the epoch
         finally:
             c.close()
+
+
+# ---------------------------------------------------------------- two real devices (skipped on a one-GPU box)
+
+@pytest.mark.gpu
+def test_flagged_payload_exchange_on_two_devices_full_70b_step(pkg, oracle):
+    """Both ranks of a 2-way row split in ONE process on two real GPUs (peer access over NVLink): every MUL_MAT of a Llama-3-70B decode
+    step (80 layers x 7 + lm_head = 561 ops, 401 launches per rank after the shared-src1 fusion) through the flagged-payload exchange.
+    After each op BOTH ranks must hold the full dst, bit-identical to the same MUL_MAT computed unsplit on one GPU: exercises the epoch
+    counting, both staging halves and who-owns-which-rows over several hundred dependent launches. Weights: one matrix per shape
+    (shared by the layers), activations differ per op."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import bench
+    L = pkg.lib()
+    pkg.check(L.b200_enable_peer_access(0, 1), "peer 0->1")
+    pkg.check(L.b200_enable_peer_access(1, 0), "peer 1->0")
+    t, tname = Q4_K, "q4_K"
+    m = bench.MODELS["70b"]
+    shapes = dict((name, (M, K, grp)) for (name, M, K, grp) in bench.layer_ops(m))
+    shapes["lm_head"] = (m["n_vocab"], m["n_embd"], "head_in")
+    slab = bench.load_slab(tname)
+    rng = np.random.default_rng(70)
+    dev = [torch.device("cuda", 0), torch.device("cuda", 1)]
+    Wfull, Wpart, bounds = {}, [{}, {}], {}
+    for name, (M, K, _) in shapes.items():
+        w = torch.from_numpy(slab[rng.integers(0, slab.shape[0], (M, K // 256))].reshape(M, -1))
+        Wfull[name] = w.to(dev[0])
+        bounds[name] = [pkg.row_split_bounds(M, 2, r, rounding=1) for r in range(2)]
+        for r in range(2):
+            lo, hi = bounds[name][r]
+            Wpart[r][name] = w[lo:hi].contiguous().to(dev[r])
+    order = []
+    for _ in range(m["n_layer"]):
+        order += [["wq", "wk", "wv"], ["wo"], ["gate", "up"], ["down"]]
+    order.append(["lm_head"])
+    n_out = sum(shapes[n][0] for grp in order for n in grp)
+    pools, stages, ctxs, streams = [], [], [], []
+    for r in range(2):
+        with torch.cuda.device(r):
+            pools.append(torch.zeros(n_out + 64, dtype=torch.float32, device=dev[r]))
+            stages.append(torch.zeros(4 * n_out, dtype=torch.float32, device=dev[r]))
+            streams.append(torch.cuda.Stream(device=dev[r]))
+    torch.cuda.synchronize(0); torch.cuda.synchronize(1)
+    for r in range(2):
+        with torch.cuda.device(r), torch.cuda.stream(streams[r]):
+            c = pkg.Context(r)
+            c.row_split(r, [pools[0].data_ptr(), pools[1].data_ptr()], [pools[0].data_ptr() + 4 * n_out, pools[1].data_ptr() + 4 * n_out])
+            c.row_split_ll([stages[0].data_ptr(), stages[1].data_ptr()], pools[r].data_ptr(), 4 * n_out, rounding=1)
+            ctxs.append(c)
+    ref_ctx = None
+    try:
+        gx = torch.Generator(device=dev[0]); gx.manual_seed(5)
+        xs = []
+        for grp in order:   # all activations up front, on both devices (nothing but launches inside the exchange loop)
+            x0 = (torch.rand((1, shapes[grp[0]][1]), generator=gx, device=dev[0]) * 2 - 1).contiguous()
+            xs.append([x0, x0.to(dev[1])])
+        torch.cuda.synchronize(0); torch.cuda.synchronize(1)
+        off, placed = 0, []
+        for gi, grp in enumerate(order):
+            K = shapes[grp[0]][1]
+            offs = []
+            for n in grp:
+                offs.append(off)
+                off += shapes[n][0]
+            placed.append(offs)
+            for r in range(2):
+                with torch.cuda.device(r), torch.cuda.stream(streams[r]):
+                    outs = [pools[r][o + bounds[n][r][0]:o + bounds[n][r][1]].view(1, -1) for n, o in zip(grp, offs)]
+                    if len(grp) == 1:
+                        n = grp[0]
+                        d = pkg.MulMatDesc.contiguous(t, bounds[n][r][1] - bounds[n][r][0], K, 1)
+                        d.nb1 = d.nb2 = d.nb3 = 4 * shapes[n][0]
+                        ctxs[r].mul_mat(t, Wpart[r][n], xs[gi][r], out=outs[0], desc=d)
+                    else:
+                        ctxs[r].mul_mat_shared(t, [Wpart[r][n] for n in grp], xs[gi][r], outs=outs, dst_strides=[4 * shapes[n][0] for n in grp])
+        for r in range(2):
+            with torch.cuda.device(r):
+                streams[r].synchronize()
+        # the unsplit reference for a sample of the ops (every shape; first, middle and last layers), computed afterwards on one GPU
+        n_checked = 0
+        with torch.cuda.device(0):
+            ref_ctx = pkg.Context(0)
+            for gi, grp in enumerate(order):
+                if not (gi % 40 == 0 or gi % 40 == 1 or gi % 40 == 2 or gi % 40 == 3 or gi >= len(order) - 2):
+                    continue
+                for n, o in zip(grp, placed[gi]):
+                    ref = ref_ctx.mul_mat(t, Wfull[n], xs[gi][0]).view(-1).cpu()
+                    for r in range(2):
+                        got = pools[r][o:o + shapes[n][0]].cpu()
+                        assert torch.equal(got, ref), f"op {gi} ({n}) on rank {r} differs from the unsplit result"
+                    n_checked += 1
+        assert n_checked >= 50
+        for r in range(2):
+            words = pools[r][n_out:].view(torch.int32).cpu().numpy()
+            assert words[8] == len(order) and words[9] == 0     # one epoch per launch, CTA counter back at zero
+    finally:
+        if ref_ctx is not None:
+            ref_ctx.close()
+        for c in ctxs:
+            c.close()
