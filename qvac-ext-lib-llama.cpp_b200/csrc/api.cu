@@ -121,6 +121,8 @@ b200_status b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     if (const char * s = getenv("GGML_B200_DBG")) c->dbg = atoi(s);
     if (const char * s = getenv("GGML_B200_MMA_MIN")) c->mma_min_cols = atoi(s);
     if (const char * s = getenv("GGML_B200_MMA_WARPS")) c->mma_warps = atoi(s);
+    if (const char * s = getenv("GGML_B200_TC_MIN")) c->tc_min_cols = atoi(s);
+    if (const char * s = getenv("GGML_B200_TC_MAX")) c->tc_max_cols = atoi(s);
     if (const char * s = getenv("GGML_B200_MMA_FUSE_UNITS")) c->mma_fuse_units = atoi(s);
     if (const char * s = getenv("GGML_B200_MOE_GROUP_MIN")) c->moe_group_min = atoi(s);
     if (const char * s = getenv("GGML_B200_MMQ_F16")) c->mmq_f16 = atoi(s) != 0;
@@ -137,6 +139,7 @@ void b200_ctx_destroy(b200_ctx * ctx) {
     if (ctx->scratch2) cudaFree(ctx->scratch2);
     if (ctx->scratch3) cudaFree(ctx->scratch3);
     if (ctx->trace) cudaFree(ctx->trace);
+    if (ctx->tc_turn) cudaFree(ctx->tc_turn);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -719,6 +722,29 @@ static b200_status mul_mat_impl(b200_ctx * ctx, int n_ops, const b200_mul_mat_de
     if (N == 0 || d.ne01 == 0) return B200_OK;
     CU(cudaSetDevice(ctx->device));
 
+    // 4..32 columns of q4_K: the tcgen05 mat-vec that expands the raw blocks in shared memory (mvtc.cuh)
+    if (ctx->force_path == B200_PATH_AUTO && ctx->split.n_ranks <= 1) {
+        bool tc = true;
+        for (int i = 0; i < n_ops && tc; i++) tc = b200_mvtc_usable(ctx, type, K, N, src0s[i], descs[i].nb01);
+        if (tc) {
+            bool first = true;
+            for (int64_t i13 = 0; i13 < d.ne13; i13++)
+                for (int64_t i12 = 0; i12 < d.ne12; i12++) {
+                    for (int i = 0; i < n_ops; i++) {
+                        const b200_mul_mat_desc & di = descs[i];
+                        const int64_t r2 = di.ne12 / di.ne02, r3 = di.ne13 / di.ne03;
+                        b200_status st = b200_mvtc_run(ctx, (const uint8_t *) src0s[i] + (i12 / r2) * di.nb02 + (i13 / r3) * di.nb03, di.nb01, di.ne01, K,
+                                                       (const float *) ((const char *) src1 + i12 * di.nb12 + i13 * di.nb13), di.nb11, N,
+                                                       (float *) ((char *) dsts[i] + i12 * di.nb2 + i13 * di.nb3), (int64_t) (di.nb1 / 4),
+                                                       /* act_shared = */ !first && i > 0);
+                        if (st != B200_OK) return st;
+                        first = false;
+                    }
+                    first = true;
+                }
+            return B200_OK;
+        }
+    }
     // more columns than the mat-vec kernels hold in registers: the tcgen05 int8 tile kernel (K4)
     const int64_t mmq_min = ctx->mmq_min_cols > 0 ? ctx->mmq_min_cols : (ctx->weight_cache ? 9 : 33);
     bool mmq = ctx->force_path == B200_PATH_MMQ || (ctx->force_path == B200_PATH_AUTO && N >= mmq_min);

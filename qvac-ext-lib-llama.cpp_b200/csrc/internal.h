@@ -70,6 +70,11 @@ struct b200_ctx {
     // the fp16 activation operand last built in scratch2 (kind::f16 prefill): valid for further matrices of the same shared-src1 group
     const void * act_x = nullptr; size_t act_rs = 0; int64_t act_N = 0, act_K = 0; const void * act_buf = nullptr; int act_kind = -1;
     int          mmq_f16 = 1;                  // prefill GEMM on kind::f16 with the block scales folded into fp16 operands (mmf16.cuh); 0: kind::i8
+    // tcgen05 mat-vec from raw blocks (mvtc.cuh): q4_K, tc_min_cols..tc_max_cols columns (GGML_B200_TC_MIN / _MAX; min 0 = off). Measured on
+    // the 8B stack: wins at 9..16 columns (62 vs 51 TOPS at 16), loses to the IMMA mat-vec below 9 and to the kind::f16 GEMM from 32
+    int          tc_min_cols = 9, tc_max_cols = 16;
+    uint32_t *   tc_turn = nullptr;            // per-tile turn counters of its split-K accumulation
+    const void * tc_act_x = nullptr; size_t tc_act_rs = 0; int64_t tc_act_N = 0, tc_act_K = 0; const void * tc_act_buf = nullptr;
     int          moe_group_min = 2;            // MUL_MAT_ID: group by expert (tensor-core mat-vec) from this many pairs per expert on
                                                // average; 0 = never; GGML_B200_MOE_GROUP_MIN
 };
@@ -100,6 +105,10 @@ b200_status b200_mv_mma_run_ids(b200_ctx * ctx, int type, int64_t K, const uint8
                                 float * dst, const b200::MvIds & ids, const int32_t * sp, const int32_t * eb, const uint8_t * act_main,
                                 const uint8_t * act_aux);
 
+// mvtc.cuh (in mmq.cu): tcgen05 mat-vec for 4..32 columns from raw q4_K blocks
+bool        b200_mvtc_usable(const b200_ctx * ctx, int type, int64_t K, int64_t N, const void * w, size_t nb01);
+b200_status b200_mvtc_run(b200_ctx * ctx, const void * w, size_t nb01, int64_t M, int64_t K, const float * x, size_t x_rs, int64_t N, float * dst,
+                          int64_t ldc, bool act_shared);
 // mmq.cu: the tcgen05 int8 tile kernel
 bool        b200_mmq_usable(int type, int64_t K, const void * w, size_t nb01);
 // several matrices sharing src1 in one launch (kind::f16 path, weight cache on, every expansion cached); B200_ERR_UNSUPPORTED = loop

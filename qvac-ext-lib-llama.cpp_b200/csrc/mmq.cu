@@ -638,6 +638,7 @@ struct WEntry {  // expanded form of one weight matrix
 };
 
 #include "mmf16.cuh"
+#include "mvtc.cuh"
 
 struct WKey {
     int          device;
@@ -1026,3 +1027,93 @@ b200_status b200_mmq_run_group(b200_ctx * ctx, int type, int n_ops, const void *
     ctx->act_x = nullptr;
     return mmf_run(ctx, n_ops, es, settled, x, x_rs, N, (__half *) s2, (float *) (s2 + hb), dsts, ldcs, false);
 }
+
+// ------------------------------------------------------------------------------------------------ mvtc.cuh: host side
+
+bool b200_mvtc_usable(const b200_ctx * ctx, int type, int64_t K, int64_t N, const void * w, size_t nb01) {
+    if (ctx->tc_min_cols <= 0 || N < ctx->tc_min_cols || N > ctx->tc_max_cols || N > 32 || type != B200_TYPE_Q4_K) return false;
+    if (K % 256 != 0 || (uintptr_t) w % 16 != 0 || nb01 % 16 != 0 || K > INT32_MAX - 256) return false;
+    return get_encode() != nullptr;
+}
+
+// dst[n * ldc + m] = sum_k W[m][k] * X[n][k], N <= 32 activation rows, weights read as raw q4_K blocks.
+// act_shared: the q8_K activation tiles of the previous call (same x, N, K: a shared-src1 group) are still in scratch2
+b200_status b200_mvtc_run(b200_ctx * ctx, const void * w, size_t nb01, int64_t M, int64_t K, const float * x, size_t x_rs, int64_t N, float * dst,
+                          int64_t ldc, bool act_shared) {
+    if (M <= 0 || N <= 0) return B200_OK;
+    const int64_t KB = K / 32, n_sb = K / 256, Np = (N + 3) & ~(int64_t) 3;
+    const size_t aq = ((size_t) N * K + 255) & ~(size_t) 255;
+    const size_t as = (((size_t) KB * Np * 4) + 255) & ~(size_t) 255;
+    const size_t ab = (((size_t) N * n_sb * 16) + 255) & ~(size_t) 255;
+    if (b200_status st = b200_ensure(ctx, &ctx->scratch2, &ctx->scratch2_size, aq + as + ab)) return st;
+    uint8_t * s2 = (uint8_t *) ctx->scratch2;
+    int8_t *  xq = (int8_t *) s2;
+    float *   sA = (float *) (s2 + aq);
+    int16_t * bsums = (int16_t *) (s2 + aq + as);
+    if (!ctx->tc_turn) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        cudaStreamIsCapturing(ctx->stream, &cs);
+        if (cs != cudaStreamCaptureStatusNone) return fail(B200_ERR_ARG, "first use of the tcgen05 mat-vec kernel during stream capture; run once uncaptured first");
+        CU(cudaMalloc((void **) &ctx->tc_turn, 16384 * sizeof(uint32_t)));
+        CU(cudaMemsetAsync(ctx->tc_turn, 0, 16384 * sizeof(uint32_t), ctx->stream));
+    }
+    ctx->act_x = nullptr;   // scratch2 no longer holds the fp16 operand of the kind::f16 path
+    if (!(act_shared && ctx->tc_act_x == x && ctx->tc_act_rs == x_rs && ctx->tc_act_N == N && ctx->tc_act_K == K && ctx->tc_act_buf == s2)) {
+        const int64_t units  = K / 256;
+        const int     vec_ok = ((uintptr_t) x % 16 == 0) && (x_rs % 16 == 0);
+        dim3 grid((unsigned) ((units + 3) / 4), (unsigned) N);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = grid; cfg.blockDim = dim3(128); cfg.stream = ctx->stream;
+        CU(cudaLaunchKernelEx(&cfg, quantize_tiles_kernel<ACT_KIND_Q8_K>, x, K, N, x_rs, xq, sA, sA, Np, vec_ok, bsums));
+        ctx->launches++;
+        ctx->tc_act_x = x; ctx->tc_act_rs = x_rs; ctx->tc_act_N = N; ctx->tc_act_K = K; ctx->tc_act_buf = s2;
+    }
+    const int BN = N <= 16 ? 16 : 32;
+    CUtensorMap map_w, map_b, map_bs, map_da;
+    if (!make_map(&map_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (void *) w, (uint64_t) n_sb * SZ_Q4_K, (uint64_t) M, (uint64_t) nb01, SZ_Q4_K, TC_BM, false) ||
+        !make_map(&map_b, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, xq, (uint64_t) K, (uint64_t) N, (uint64_t) K, 128, BN, true) ||
+        !make_map(&map_bs, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, bsums, (uint64_t) n_sb * 8, (uint64_t) N, (uint64_t) n_sb * 16, 8, BN, false) ||
+        !make_map(&map_da, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, sA, (uint64_t) N, (uint64_t) n_sb, (uint64_t) Np * 4 * 8, BN, 1, false)) {
+        return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the tcgen05 mat-vec operands (M=%lld K=%lld N=%lld nb01=%zu)", (long long) M,
+                    (long long) K, (long long) N, nb01);
+    }
+    TcParams p;
+    p.dst = dst; p.ldc = ldc; p.M = (int) M; p.N = (int) N; p.K = (int) K;
+    p.m_tiles = (int) ((M + TC_BM - 1) / TC_BM);
+    // cut K so that every SM has work: waves x (super-blocks per part + ~3 of pipeline fill) is what a launch costs
+    int best = 1;
+    if (p.m_tiles <= 16384) {
+        double best_cost = 1e30;
+        for (int s = 1; s <= 8 && s <= n_sb; s++) {
+            const int per = (int) ((n_sb + s - 1) / s);
+            const int parts = (int) ((n_sb + per - 1) / per);
+            if (parts != s) continue;
+            const int waves = (p.m_tiles * s + ctx->sm_count - 1) / ctx->sm_count;
+            const double cost = (double) waves * (per + 3);
+            if (cost < best_cost - 1e-9) { best_cost = cost; best = s; }
+        }
+    }
+    p.splits = best;
+    p.sb_per_split = (int) ((n_sb + best - 1) / best);
+    p.count = ctx->tc_turn;
+    p.dbg   = ctx->dbg;
+    p.ws    = nullptr;
+    if (p.splits > 1) {
+        const int NRc = N <= 8 ? 8 : (N <= 16 ? 16 : 32);
+        // scratch3 is shared with the kind::f16 GEMM's stream-K workspace: its first 4 KB are flags that stay zero between launches
+        const size_t need3 = 4096 + (size_t) p.m_tiles * p.splits * NRc * TC_BM * sizeof(float);
+        if (ctx->scratch3_size < need3) {
+            if (b200_status st = b200_ensure(ctx, &ctx->scratch3, &ctx->scratch3_size, need3)) return st;
+            CU(cudaMemsetAsync(ctx->scratch3, 0, 4096, ctx->stream));
+        }
+        p.ws = (float *) ((uint8_t *) ctx->scratch3 + 4096);
+    }
+    const int items = p.m_tiles * p.splits;
+    const int grid  = items < ctx->sm_count ? items : ctx->sm_count;
+    if (BN == 16) {
+        if (N <= 8) return mvtc_launch<16, 8>(ctx, map_w, map_b, map_bs, map_da, p, grid);
+        return mvtc_launch<16, 16>(ctx, map_w, map_b, map_bs, map_da, p, grid);
+    }
+    return mvtc_launch<32, 32>(ctx, map_w, map_b, map_bs, map_da, p, grid);
+}
+

@@ -353,9 +353,9 @@ def test_q6_K_decode(ctx, pkg, oracle, M, K, N):
             assert oracle.nmse(one[0], got[1]) <= 1e-12
 
 
-@pytest.mark.parametrize("M,K,N", [(16, 2048, 3), (100, 2048, 5), (333, 4096, 8), (48, 14336, 4), (1000, 6144, 7)])
+@pytest.mark.parametrize("M,K,N", [(16, 2048, 4), (100, 2048, 5), (333, 4096, 8), (48, 14336, 4), (1000, 6144, 7)])
 def test_q6_K_tensor_core_matvec(ctx, pkg, oracle, M, K, N):
-    """3..8 columns: mma.sync m16n8k16 on signed 6-bit operands, one MMA per 16-weight scale group, units read from 1680-byte lines
+    """4..8 columns: mma.sync m16n8k16 on signed 6-bit operands, one MMA per 16-weight scale group, units read from 1680-byte lines
     of 8 (2-byte unit phases realigned by funnel shifts); against the oracle, the dp4a kernel and the generic kernel"""
     rng = np.random.default_rng(M * 3 + K + N)
     W = quantize_weights(oracle, Q6_K, rng.uniform(-1, 1, (M, K)).astype(np.float32))
@@ -423,6 +423,30 @@ def test_mm_ids_sort(ctx):
         order = np.argsort(flat, kind="stable")
         assert np.array_equal(sp, order.astype(np.int32))
         assert np.array_equal(eb, np.concatenate([[0], np.cumsum(np.bincount(flat, minlength=n_as))]).astype(np.int32))
+
+
+# ---------------------------------------------------------------- tcgen05 mat-vec from raw q4_K blocks (mvtc.cuh)
+
+@pytest.mark.parametrize("M,K,N", [(300, 1024, 4), (128, 4096, 8), (1000, 2048, 9), (129, 14336, 16), (4096, 4096, 13), (77, 512, 17), (640, 8192, 32)])
+def test_tcgen05_matvec_from_raw_blocks(pkg, oracle, monkeypatch, M, K, N):
+    """mvtc_q4k_kernel over its whole column range (the default only uses it for 9..16 columns): tail tiles (M % 128 != 0), K cut into
+    parts whose partial sums meet in the workspace (small M, long K), 8 / 16 / 32-column instantiations. Same integers as ggml-cpu:
+    the bound is the decode kernels' 1e-10. Also twice in a row: the part counters must be back at zero."""
+    monkeypatch.setenv("GGML_B200_TC_MIN", "4")
+    monkeypatch.setenv("GGML_B200_TC_MAX", "32")
+    c = pkg.Context(0)
+    try:
+        rng = np.random.default_rng(M + K + N)
+        W = quantize_weights(oracle, Q4_K, rng.uniform(-1, 1, (M, K)).astype(np.float32))
+        X = (rng.standard_normal((N, K)) * rng.choice([0.05, 1.0, 20.0], (N, 1))).astype(np.float32)
+        ref = oracle.mul_mat(Q4_K, W, X)
+        l0 = c.launches
+        a = c.mul_mat(Q4_K, cu(W), cu(X)).cpu().numpy()
+        assert c.launches - l0 == 2          # the q8_K tile quantizer + the tcgen05 kernel
+        b = c.mul_mat(Q4_K, cu(W), cu(X)).cpu().numpy()
+        assert oracle.nmse(ref, a) <= NMSE_TIGHT and np.array_equal(a, b)
+    finally:
+        c.close()
 
 
 # ---------------------------------------------------------------- exact mode (the arithmetic behind the free-running greedy streams)
