@@ -869,7 +869,7 @@ __device__ __forceinline__ void unit_dot2(uint32_t w0, uint32_t w1, uint32_t am,
     }
 }
 
-template <int TYPE, int NC>
+template <int TYPE, int NC, bool LL>   // LL: row split with the flagged-payload exchange (its own instantiation: the plain kernel keeps its registers)
 __global__ void __launch_bounds__(32 * (MV_MAX_CONS + 1), 1)
 mv_lean_kernel(const __grid_constant__ MvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -984,7 +984,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     griddep_wait();
     if (w == 0) MV_TRACE(3);
     // row split, flagged-payload exchange (kernels.h ll_store / ll_receive): this launch's epoch is final once the stream dependency is
-    const bool     ll = p.split.n_ranks > 1;   // the launcher only sends split launches here when they use the flagged payload
+    constexpr bool ll = LL;                    // the launcher only sends split launches here when they use the flagged payload
     const uint32_t ep = ll ? ll_epoch(p.split) : 0u;
     if (warp > NWC && !p.fuse_quant) return;
     if (p.fuse_quant) {
@@ -1112,7 +1112,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     }
 }
 
-template <int TYPE, int NC>
+template <int TYPE, int NC, bool LL>
 static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t smem, cudaStream_t st) {
     MvParams p = p_in;
     p.n_helpers = 0;
@@ -1124,9 +1124,9 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
@@ -1144,17 +1144,26 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
     }
     cfg.attrs    = attr;
     cfg.numAttrs = na;
-    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE, NC>, p);
+    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE, NC, LL>, p);
 }
 
 // the launch can take the lean kernel: one column, plain MUL_MAT, no exchange, no epilogue, an even ring
 template <int TYPE>
 static cudaError_t mv_lean_launch_n(int nc, const MvParams & p, int n_ctas, size_t smem, cudaStream_t st) {
+    if (p.split.n_ranks > 1) {
+        switch (nc) {
+            case 1: return mv_lean_launch_t<TYPE, 1, true>(p, n_ctas, smem, st);
+            case 2: return mv_lean_launch_t<TYPE, 2, true>(p, n_ctas, smem, st);
+            case 3: return mv_lean_launch_t<TYPE, 3, true>(p, n_ctas, smem, st);
+            case 4: return mv_lean_launch_t<TYPE, 4, true>(p, n_ctas, smem, st);
+        }
+        return cudaErrorInvalidValue;
+    }
     switch (nc) {
-        case 1: return mv_lean_launch_t<TYPE, 1>(p, n_ctas, smem, st);
-        case 2: return mv_lean_launch_t<TYPE, 2>(p, n_ctas, smem, st);
-        case 3: return mv_lean_launch_t<TYPE, 3>(p, n_ctas, smem, st);
-        case 4: return mv_lean_launch_t<TYPE, 4>(p, n_ctas, smem, st);
+        case 1: return mv_lean_launch_t<TYPE, 1, false>(p, n_ctas, smem, st);
+        case 2: return mv_lean_launch_t<TYPE, 2, false>(p, n_ctas, smem, st);
+        case 3: return mv_lean_launch_t<TYPE, 3, false>(p, n_ctas, smem, st);
+        case 4: return mv_lean_launch_t<TYPE, 4, false>(p, n_ctas, smem, st);
     }
     return cudaErrorInvalidValue;
 }
@@ -1235,8 +1244,6 @@ cudaError_t mv_fast_launch(int type, int ncols, const MvParams & p, int n_ctas, 
             case B200_TYPE_Q4_0: return mv_lean_launch_n<B200_TYPE_Q4_0>(ncols, p, n_ctas, smem, st);
             case B200_TYPE_Q8_0: return mv_lean_launch_n<B200_TYPE_Q8_0>(ncols, p, n_ctas, smem, st);
             case B200_TYPE_Q4_K: return mv_lean_launch_n<B200_TYPE_Q4_K>(ncols, p, n_ctas, smem, st);
-            case B200_TYPE_Q5_K: return mv_lean_launch_n<B200_TYPE_Q5_K>(ncols, p, n_ctas, smem, st);
-            case B200_TYPE_Q6_K: return mv_lean_launch_n<B200_TYPE_Q6_K>(ncols, p, n_ctas, smem, st);
         }
     }
     switch (type) {
