@@ -125,6 +125,7 @@ b200_status b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     if (const char * s = getenv("GGML_B200_TC_MAX")) c->tc_max_cols = atoi(s);
     if (const char * s = getenv("GGML_B200_MMA_FUSE_UNITS")) c->mma_fuse_units = atoi(s);
     if (const char * s = getenv("GGML_B200_MOE_GROUP_MIN")) c->moe_group_min = atoi(s);
+    if (const char * s = getenv("GGML_B200_MOE_TILE_MIN")) c->moe_tile_min = atoi(s);
     if (const char * s = getenv("GGML_B200_MMQ_F16")) c->mmq_f16 = atoi(s) != 0;
     *out = c;
     return B200_OK;

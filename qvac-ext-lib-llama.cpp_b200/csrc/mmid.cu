@@ -14,6 +14,8 @@
 
 #include "internal.h"
 
+#include <vector>
+
 using namespace b200;
 
 #define fail b200_fail
@@ -81,6 +83,74 @@ b200_status b200_mm_ids_sort(b200_ctx * ctx, const int32_t * ids, int64_t n_used
     return B200_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ K6: per-expert tile GEMMs
+//
+// Enough pairs per expert (prefill): what the reference does with ids helper -> gathered quantize -> mul_mat_q per expert window ->
+// un-permuting store (ggml-cuda/mmq.cu:148-206, mmq.cuh:3425-3455, 3006-3053). Here: device-side sort, ONE small read-back of the
+// expert bounds (the launches are sized on the host), the pairs' activation rows gathered expert by expert into a contiguous
+// buffer, one MUL_MAT per expert that has pairs - through the ordinary dispatcher, so every expert gets the kernel its column count
+// calls for (tcgen05 GEMM, tcgen05 mat-vec, mat-vec) and its weights are read ONCE - and a scatter of the result rows to their
+// (slot, token) places in dst.
+
+__global__ void __launch_bounds__(256) moe_gather_rows_kernel(const float * __restrict__ b, int64_t x_is, int64_t x_ts, int n_used, int ne11,
+                                                              const int32_t * __restrict__ sp, float * __restrict__ xg, int64_t K) {
+    const int pr = sp[blockIdx.x];
+    const int t = pr / n_used, i = pr - t * n_used;
+    const float * src = (const float *) ((const char *) b + (int64_t) t * x_ts + (int64_t) (i % ne11) * x_is);
+    float * dst = xg + (int64_t) blockIdx.x * K;
+    if (((uintptr_t) src % 16) == 0 && K % 4 == 0) {
+        for (int64_t k = threadIdx.x; k < K / 4; k += blockDim.x) ((float4 *) dst)[k] = __ldg((const float4 *) src + k);
+    } else {
+        for (int64_t k = threadIdx.x; k < K; k += blockDim.x) dst[k] = __ldg(src + k);
+    }
+}
+
+__global__ void __launch_bounds__(256) moe_scatter_rows_kernel(const float * __restrict__ yg, const int32_t * __restrict__ sp, int n_used,
+                                                               int64_t dst_is, int64_t dst_ts, float * __restrict__ dst, int64_t M) {
+    const int pr = sp[blockIdx.x];
+    const int t = pr / n_used, i = pr - t * n_used;
+    const float * src = yg + (int64_t) blockIdx.x * M;
+    float * out = dst + (int64_t) t * dst_ts + (int64_t) i * dst_is;
+    for (int64_t m = threadIdx.x; m < M; m += blockDim.x) out[m] = src[m];
+}
+
+static b200_status mul_mat_id_tiled(b200_ctx * ctx, const b200_mul_mat_id_desc * d, const void * as, const float * b, const int32_t * ids, float * dst,
+                                    const MvIds & mi) {
+    const int64_t K = d->ne00, M = d->ne01, n_pairs = d->n_used * d->n_tok;
+    const size_t sp_b = (size_t) ((n_pairs + 63) & ~(int64_t) 63) * 4, eb_b = (size_t) ((d->n_as + 1 + 63) & ~(int64_t) 63) * 4;
+    const size_t xg_b = (size_t) n_pairs * K * 4, yg_b = (size_t) n_pairs * M * 4;
+    if (b200_status st = b200_ensure(ctx, &ctx->io, &ctx->io_size, sp_b + eb_b + xg_b + yg_b + 256)) return st;
+    int32_t * sp = (int32_t *) ctx->io;
+    int32_t * eb = (int32_t *) ((uint8_t *) ctx->io + sp_b);
+    float *   xg = (float *) ((uint8_t *) ctx->io + sp_b + eb_b);
+    float *   yg = (float *) ((uint8_t *) xg + xg_b);
+    if (b200_status st = b200_mm_ids_sort(ctx, ids, d->n_used, d->n_tok, d->ids_nb1, d->n_as, sp, eb)) return st;
+    std::vector<int32_t> bounds((size_t) d->n_as + 1);
+    CU(cudaMemcpyAsync(bounds.data(), eb, bounds.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    moe_gather_rows_kernel<<<(unsigned) n_pairs, 256, 0, ctx->stream>>>(b, mi.x_is, mi.x_ts, mi.n_used, mi.ne11, sp, xg, K);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    CU(cudaStreamSynchronize(ctx->stream));   // the expert bounds size the launches
+    if (bounds[(size_t) d->n_as] != (int32_t) n_pairs) return fail(B200_ERR_ARG, "MUL_MAT_ID: expert ids out of range");  // ggml-cpu asserts (ggml-cpu.c:1574)
+    for (int64_t e = 0; e < d->n_as; e++) {
+        const int64_t n0 = bounds[(size_t) e], cnt = bounds[(size_t) e + 1] - n0;
+        if (cnt <= 0) continue;
+        b200_mul_mat_desc md;
+        memset(&md, 0, sizeof(md));
+        md.type = d->type;
+        md.ne00 = K; md.ne01 = M; md.ne02 = 1; md.ne03 = 1;
+        md.nb01 = d->nb01; md.nb02 = d->nb02; md.nb03 = d->nb02;
+        md.ne11 = cnt; md.ne12 = 1; md.ne13 = 1;
+        md.nb11 = (size_t) K * 4; md.nb12 = md.nb11 * (size_t) cnt; md.nb13 = md.nb12;
+        md.nb1 = (size_t) M * 4; md.nb2 = md.nb1 * (size_t) cnt; md.nb3 = md.nb2;
+        if (b200_status st = b200_mul_mat(ctx, &md, (const uint8_t *) as + e * d->nb02, xg + n0 * K, yg + n0 * M)) return st;
+    }
+    moe_scatter_rows_kernel<<<(unsigned) n_pairs, 256, 0, ctx->stream>>>(yg, sp, mi.n_used, mi.dst_is, mi.dst_ts, dst, M);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    return B200_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ K6: dispatch
 
 int b200_mul_mat_id_supported(const b200_mul_mat_id_desc * d) {
@@ -125,6 +195,15 @@ static b200_status mul_mat_id_impl(b200_ctx * ctx, const b200_mul_mat_id_desc * 
     const int64_t n_rows = d->ne11 * d->n_tok;
     if (fz && (!fast || d->n_tok != 1 || ctx->split.n_ranks > 1)) return fail(B200_ERR_UNSUPPORTED, "fused MUL_MAT_ID: one token on the TMA-staged kernel only");
 
+    mi.x_is = (int64_t) d->nb11;
+    mi.x_ts = (int64_t) d->nb12;
+    // prefill-sized batches: one tile GEMM per expert (no host sync is possible while the stream is being captured: then the paths below)
+    if (!fz && ctx->moe_tile_min > 0 && n_pairs >= (int64_t) ctx->moe_tile_min * d->n_as && n_pairs <= 65535 && ctx->force_path == B200_PATH_AUTO &&
+        ctx->split.n_ranks <= 1 && !ctx->exact) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        cudaStreamIsCapturing(ctx->stream, &cs);
+        if (cs == cudaStreamCaptureStatusNone) return mul_mat_id_tiled(ctx, d, as, b, ids, dst, mi);
+    }
     if (fast) {
         const int  U    = (int) (K / 256);
         // enough pairs per expert: sort the pairs by expert and let every expert multiply its tokens 8 columns at a time on the

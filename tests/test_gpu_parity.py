@@ -286,6 +286,28 @@ def test_mul_mat_id_vs_oracle(ctx, oracle, t, n_as, n_used, bcast, n_tok):
     assert oracle.nmse(oracle.mul_mat_id(t, W, B, ids), got) <= NMSE_TIGHT
 
 
+@pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K])
+@pytest.mark.parametrize("n_as,n_used,bcast,n_tok", [(4, 2, 1, 129), (8, 4, 0, 129), (4, 4, 1, 64), (8, 2, 1, 512), (8, 3, 0, 200)])
+def test_mul_mat_id_prefill_batches_per_expert_gemm(ctx, oracle, t, n_as, n_used, bcast, n_tok):
+    """from 48 pairs per expert on average: sort, gather, one tile GEMM per expert, un-permuting scatter (the reference's ids helper ->
+    mul_mat_q windows -> write-back, ggml-cuda/mmq.cu:148-206). The reference's largest case (n = 129, tests/test-backend-ops.cpp:
+    7394-7407) and a 512-token one; skewed routing (one hot expert, one unused); bound = the prefill GEMM's (fp16 operands)."""
+    rng = np.random.default_rng(n_as * 11 + n_used + n_tok + t)
+    M, K = 160, 512
+    W = quantize_weights(oracle, t, rng.uniform(-1, 1, (n_as * M, K)).astype(np.float32)).reshape(n_as, M, -1)
+    B = rng.uniform(-1, 1, (n_tok, 1 if bcast else n_used, K)).astype(np.float32)
+    n_pool = n_as - 1 if n_used < n_as else n_as                 # the last expert is never chosen (when the routing leaves a choice)
+    pool = np.arange(n_pool)
+    wts = np.ones(n_pool); wts[0] = 6.0; wts /= wts.sum()        # expert 0 is hot
+    ids = np.stack([rng.choice(pool, size=n_used, replace=False, p=wts) for _ in range(n_tok)]).astype(np.int32)
+    l0 = ctx.launches
+    got = ctx.mul_mat_id(t, cu(W), cu(B), cu(ids)).cpu().numpy()
+    assert ctx.launches - l0 >= 4                                # sort, gather, >= 1 GEMM (+ its operand conversion), scatter
+    assert oracle.nmse(oracle.mul_mat_id(t, W, B, ids), got) <= NMSE_F16
+    again = ctx.mul_mat_id(t, cu(W), cu(B), cu(ids)).cpu().numpy()
+    assert np.array_equal(got, again)
+
+
 # ---------------------------------------------------------------- q5_K (SURVEY 8f rank 2, second half: Q5_K_M / Q5_K_S files)
 
 @pytest.mark.parametrize("M,K,N", [(96, 256, 1), (200, 1024, 3), (130, 4096, 1), (64, 4096, 2), (40, 4096, 8), (33, 14336, 1), (257, 1280, 5)])
