@@ -32,6 +32,10 @@ typedef enum {
 } b200_status;
 
 /* enum ggml_type values of the three weight formats (ggml/include/ggml.h:378-395) */
+#define B200_TYPE_F32  0    /* activations; with F16 / I32 / I64 only as operands of the f3 ops at the end of this header */
+#define B200_TYPE_F16  1
+#define B200_TYPE_I32  26
+#define B200_TYPE_I64  27
 #define B200_TYPE_Q4_0 2
 #define B200_TYPE_Q8_0 8
 #define B200_TYPE_Q4_K 12
@@ -347,6 +351,64 @@ B200_API void         b200_ctx_set_prefetch(b200_ctx * ctx, int kb_per_cta);
  * consumer warp 0 done; [7] = SM id. n_slots = 0 frees it. b200_ctx_trace_read synchronizes the stream and copies it out. */
 B200_API b200_status  b200_ctx_trace(b200_ctx * ctx, int n_slots);
 B200_API b200_status  b200_ctx_trace_read(b200_ctx * ctx, void * host, size_t bytes);
+
+/* ---------------------------------------------------------------- f3: the ops between the matmuls of a decode graph ---- */
+
+/* SURVEY 8(f) rank 3, first slice: with these a Llama token step (src/llama-graph.cpp build_attn_mha :1335-1398, src/models/llama.cpp)
+ * runs on the device from the embedding lookup to the logits, instead of one scheduler split per MUL_MAT. Each replaces the
+ * ggml-cuda op named beside it and follows ggml-cpu's semantics (ggml/src/ggml-cpu/ops.cpp). A tensor is passed as struct
+ * ggml_tensor carries it (ggml/include/ggml.h:645-676): data pointer (device), ggml type, ne in elements, nb in bytes. Every
+ * op has a *_supported predicate (what dev_supports_op answers, ggml-cuda.cu:4258-4618); the op itself returns
+ * B200_ERR_UNSUPPORTED for anything else. All run on the context's stream; none allocates except FLASH_ATTN_EXT's split
+ * workspace (grow-only, fails instead of growing during a graph capture). */
+typedef struct {
+    void *  data;
+    int32_t type;     /* B200_TYPE_* (= enum ggml_type) */
+    int64_t ne[4];
+    size_t  nb[4];
+} b200_tensor;
+
+/* GGML_OP_RMS_NORM (ggml-cpu/ops.cpp:3646-3695; ggml-cuda/norm.cu rms_norm_f32): y = x / sqrt(mean(x^2) + eps) per F32 row */
+B200_API int          b200_rms_norm_supported(const b200_tensor * x, const b200_tensor * dst);
+B200_API b200_status  b200_rms_norm(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * dst, float eps);
+
+/* GGML_OP_GET_ROWS (ggml-cpu/ops.cpp ggml_compute_forward_get_rows; ggml-cuda/getrows.cu): dst[:, i, j, k] = row ids[i, j, k] of
+ * src0[:, :, j, k] as F32; src0 F32, F16 or one of the five quantized formats (dequantize_row_<type>, ggml-quants.c); ids I32 */
+B200_API int          b200_get_rows_supported(const b200_tensor * src0, const b200_tensor * ids, const b200_tensor * dst);
+B200_API b200_status  b200_get_rows(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * ids, const b200_tensor * dst);
+
+/* GGML_OP_ROPE (ggml-cpu/ops.cpp:5525-5780; ggml-cuda/rope.cu): rotary embedding of F32 [n_embd_head, n_head, n_tokens, n_batch]
+ * by I32 positions [n_tokens]; mode 0 rotates adjacent pairs, GGML_ROPE_TYPE_NEOX pairs (i, i + n_dims/2); optional per-channel
+ * frequency factors (src[2]); YaRN through ext_factor / attn_factor / beta_*; the fields are op_params[1,2,4..10] of the node */
+#define B200_ROPE_NORMAL 0
+#define B200_ROPE_NEOX   2
+typedef struct {
+    int32_t n_dims, mode, n_ctx_orig;
+    float   freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow;
+} b200_rope_params;
+B200_API int          b200_rope_supported(const b200_tensor * x, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst,
+                                          const b200_rope_params * rp);
+B200_API b200_status  b200_rope(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst,
+                                const b200_rope_params * rp);
+
+/* GGML_OP_SET_ROWS (ggml-cpu/ops.cpp:4828-4876; ggml-cuda/set-rows.cu): dst[:, idx[i, j % ne11, k % ne12], j, k] = src[:, i, j, k];
+ * src F32, dst F32 or F16 (the KV cache write of llama_kv_cache::cpy_k / cpy_v), idx I64 or I32 */
+B200_API int          b200_set_rows_supported(const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst);
+B200_API b200_status  b200_set_rows(b200_ctx * ctx, const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst);
+
+/* GGML_OP_CPY / CONT / DUP (ggml-cpu/ops.cpp ggml_compute_forward_dup; ggml-cuda/cpy.cu): element e of src (any strides) to
+ * element e of dst (any strides, same number of elements), F32 / F16 in any combination (F32 -> F16 rounds to nearest even) */
+B200_API int          b200_cpy_supported(const b200_tensor * src, const b200_tensor * dst);
+B200_API b200_status  b200_cpy(b200_ctx * ctx, const b200_tensor * src, const b200_tensor * dst);
+
+/* GGML_OP_FLASH_ATTN_EXT (ggml-cpu/ops.cpp:7994-8218; ggml-cuda/fattn*.cu): q F32 [D, n_q, n_head, n_batch], k / v F16
+ * [D, n_kv, n_head_kv, n_batch] (D = 64, 128 or 256; rows may be strided views of the KV cache), optional F16 mask
+ * [n_kv, >= n_q, 1 | n_head, 1 | n_batch] (-inf = masked, times the ALiBi slope when max_bias > 0), optional F32 sinks
+ * [n_head]; dst F32 [D, n_head, n_q, n_batch] = softmax(scale * q k^T (+ softcap) + mask) v. fp32 online softmax. */
+B200_API int          b200_flash_attn_ext_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
+                                                    const b200_tensor * sinks, const b200_tensor * dst);
+B200_API b200_status  b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
+                                          const b200_tensor * sinks, const b200_tensor * dst, float scale, float max_bias, float logit_softcap);
 
 #ifdef __cplusplus
 }

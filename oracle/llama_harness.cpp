@@ -210,12 +210,14 @@ std::vector<uint8_t> slurp(const std::string & path) {
     return b;
 }
 
+int g_graph_splits = -1;   // "graph splits = N" of llama_context's reserve pass
+
 int cmd_run(int argc, char ** argv) {
     std::string prefix = "/tmp/b200_parity", loader = "file";
     std::vector<std::string> backends;
     int ngl = 0, n_prompt = 64, n_gen = 256, n_threads = 0, n_split = 3, n_batch = 512, n_ubatch = 512;
     uint64_t seed = 5;
-    bool quiet = true, mmap = true;
+    bool quiet = true, mmap = true, offload_kqv = false, flash_attn = false;
     std::string force_path;   // teacher forcing: a file of token ids; token i of it is fed after step i instead of this run's own argmax
     for (int i = 0; i < argc; i++) {
         const std::string a = argv[i];
@@ -234,8 +236,14 @@ int cmd_run(int argc, char ** argv) {
         else if (a == "--verbose") quiet = false;
         else if (a == "--no-mmap") mmap = false;
         else if (a == "--force") force_path = val();
+        else if (a == "--kqv") offload_kqv = true;     // KV cache and attention on the device of the layer
+        else if (a == "--fa") flash_attn = true;       // GGML_OP_FLASH_ATTN_EXT instead of MUL_MAT / SOFT_MAX / MUL_MAT
     }
-    if (quiet) llama_log_set([](ggml_log_level level, const char * text, void *) { if (level >= GGML_LOG_LEVEL_ERROR) fputs(text, stderr); }, nullptr);
+    llama_log_set([](ggml_log_level level, const char * text, void * ud) {
+        const char * gs = strstr(text, "graph splits = ");   // llama_context reports the scheduler's split count of its reserve graphs
+        if (gs) g_graph_splits = atoi(gs + 15);
+        if (level >= GGML_LOG_LEVEL_ERROR || !*(bool *) ud) fputs(text, stderr);
+    }, &quiet);
     for (const std::string & b : backends) {
         if (!ggml_backend_load(b.c_str())) { fprintf(stderr, "llama_harness: cannot load backend %s\n", b.c_str()); return 1; }
     }
@@ -283,9 +291,9 @@ int cmd_run(int argc, char ** argv) {
     cp.n_ubatch        = (uint32_t) n_ubatch;
     cp.n_threads       = n_threads;
     cp.n_threads_batch = n_threads;
-    cp.offload_kqv     = false;  // the KV cache and the attention ops stay on the CPU backend: the backend under test owns MUL_MAT(_ID) only
+    cp.offload_kqv     = offload_kqv;  // default false: the KV cache and the attention ops stay on the CPU backend (the backend under test owns the matmuls only)
     cp.no_perf         = true;
-    cp.flash_attn_type = LLAMA_FLASH_ATTN_TYPE_DISABLED;  // one attention arithmetic whatever the devices
+    cp.flash_attn_type = flash_attn ? LLAMA_FLASH_ATTN_TYPE_ENABLED : LLAMA_FLASH_ATTN_TYPE_DISABLED;  // never AUTO: one attention arithmetic whatever the devices
     llama_context * ctx = llama_init_from_model(model, cp);
     if (!ctx) { fprintf(stderr, "llama_harness: context creation failed\n"); return 1; }
     const int n_vocab = llama_vocab_n_tokens(llama_model_get_vocab(model));
@@ -329,8 +337,8 @@ int cmd_run(int argc, char ** argv) {
     }
     const double gen_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
 
-    printf("{\"loader\": \"%s\", \"ngl\": %d, \"n_prompt\": %d, \"load_s\": %.3f, \"prompt_s\": %.3f, \"gen_s\": %.3f, \"tokens\": [", loader.c_str(), ngl,
-           n_prompt, load_s, prompt_s, gen_s);
+    printf("{\"loader\": \"%s\", \"ngl\": %d, \"n_prompt\": %d, \"load_s\": %.3f, \"prompt_s\": %.3f, \"gen_s\": %.3f, \"graph_splits\": %d, \"tokens\": [", loader.c_str(), ngl,
+           n_prompt, load_s, prompt_s, gen_s, g_graph_splits);
     for (size_t i = 0; i < out.size(); i++) printf("%s%d", i ? ", " : "", out[i]);
     printf("], \"margins\": [");
     for (size_t i = 0; i < margins.size(); i++) printf("%s%.6g", i ? ", " : "", margins[i]);

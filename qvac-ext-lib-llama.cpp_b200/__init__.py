@@ -38,6 +38,8 @@ EXPORTS = [
     "b200_mul_mat_fused_supported", "b200_mul_mat_fused", "b200_mul_mat_id_fused_supported", "b200_mul_mat_id_fused",
     "b200_glu", "b200_add", "b200_mul", "b200_add_id",
     "b200_mul_mat_noalloc", "b200_mul_mat_noalloc_max_units",
+    "b200_rms_norm_supported", "b200_rms_norm", "b200_get_rows_supported", "b200_get_rows", "b200_rope_supported", "b200_rope",
+    "b200_set_rows_supported", "b200_set_rows", "b200_cpy_supported", "b200_cpy", "b200_flash_attn_ext_supported", "b200_flash_attn_ext",
 ]
 
 
@@ -88,6 +90,35 @@ class Fusion(C.Structure):
     _fields_ = [("glu_op", C.c_int32), ("alpha", C.c_float), ("limit", C.c_float),
                 ("up_bias", C.c_void_p), ("gate_bias", C.c_void_p),
                 ("bias_nb1", C.c_size_t), ("bias_nb2", C.c_size_t), ("bias_nb3", C.c_size_t)]
+
+
+class Tensor(C.Structure):
+    """b200_tensor (include/ggml_b200.h): a ggml tensor's data pointer, type, ne (elements) and nb (bytes)"""
+    _fields_ = [("data", C.c_void_p), ("type", C.c_int32), ("ne", C.c_int64 * 4), ("nb", C.c_size_t * 4)]
+
+    @classmethod
+    def of(cls, t, gtype=None):
+        """a torch tensor of up to 4 dims in torch order [ne3, ne2, ne1, ne0] (any strides) as a ggml tensor"""
+        import torch
+        types = {torch.float32: 0, torch.float16: 1, torch.int32: 26, torch.int64: 27}
+        gt = types[t.dtype] if gtype is None else gtype
+        t4 = t
+        while t4.dim() < 4:
+            t4 = t4.unsqueeze(0)
+        es = t.element_size()
+        return cls(t.data_ptr(), gt, (C.c_int64 * 4)(*reversed(t4.shape)), (C.c_size_t * 4)(*[st * es for st in reversed(t4.stride())]))
+
+    @classmethod
+    def quantized(cls, data, gtype, K, M):
+        """a [K, M] weight matrix of ggml type `gtype` stored as bytes in `data` (torch uint8), rows contiguous"""
+        rb = row_size(gtype, K)
+        return cls(data.data_ptr(), gtype, (C.c_int64 * 4)(K, M, 1, 1), (C.c_size_t * 4)(BLOCK[gtype][1], rb, rb * M, rb * M))
+
+
+class RopeParams(C.Structure):
+    """b200_rope_params: op_params[1, 2, 4..10] of a GGML_OP_ROPE node"""
+    _fields_ = [("n_dims", C.c_int32), ("mode", C.c_int32), ("n_ctx_orig", C.c_int32), ("freq_base", C.c_float), ("freq_scale", C.c_float),
+                ("ext_factor", C.c_float), ("attn_factor", C.c_float), ("beta_fast", C.c_float), ("beta_slow", C.c_float)]
 
 
 class RowSplit(C.Structure):
@@ -156,6 +187,19 @@ def lib() -> C.CDLL:
         for n in ("b200_quantize_q8_0", "b200_quantize_q8_1", "b200_quantize_q8_K"):
             getattr(L, n).argtypes = [vp, vp, i64, i64, sz, vp]
         L.b200_quantize_units.argtypes = [vp, ci, vp, i64, i64, sz, vp, vp]
+        tp = C.POINTER(Tensor)
+        L.b200_rms_norm_supported.argtypes = [tp, tp]
+        L.b200_rms_norm.argtypes = [vp, tp, tp, C.c_float]
+        L.b200_get_rows_supported.argtypes = [tp, tp, tp]
+        L.b200_get_rows.argtypes = [vp, tp, tp, tp]
+        L.b200_rope_supported.argtypes = [tp, tp, tp, tp, C.POINTER(RopeParams)]
+        L.b200_rope.argtypes = [vp, tp, tp, tp, tp, C.POINTER(RopeParams)]
+        L.b200_set_rows_supported.argtypes = [tp, tp, tp]
+        L.b200_set_rows.argtypes = [vp, tp, tp, tp]
+        L.b200_cpy_supported.argtypes = [tp, tp]
+        L.b200_cpy.argtypes = [vp, tp, tp]
+        L.b200_flash_attn_ext_supported.argtypes = [tp, tp, tp, tp, tp, tp]
+        L.b200_flash_attn_ext.argtypes = [vp, tp, tp, tp, tp, tp, tp, C.c_float, C.c_float, C.c_float]
         L.b200_mul_mat_supported.argtypes = [C.POINTER(MulMatDesc)]
         L.b200_mul_mat.argtypes = [vp, C.POINTER(MulMatDesc), vp, vp, vp]
         L.b200_mul_mat_noalloc.argtypes = [vp, C.POINTER(MulMatDesc), vp, vp, vp]
@@ -446,6 +490,49 @@ class Context:
         nb = lambda x: szx4(*[s * 4 for s in reversed(x.stride())])
         check(getattr(lib(), fn)(self.h, ne(a4), a4.data_ptr(), nb(a4), b4.data_ptr(), ne(b4), nb(b4), out.data_ptr(), nb(out)), fn)
         return out.reshape(a.shape)
+
+    # ---- f3: the ops between the matmuls (ops.cu). Tensors are torch tensors in torch order [ne3, ne2, ne1, ne0], any strides.
+    def rms_norm(self, x, eps=1e-6, out=None):
+        """GGML_OP_RMS_NORM over the last torch dim"""
+        out = self.torch.empty(x.shape, dtype=self.torch.float32, device=x.device) if out is None else out
+        check(lib().b200_rms_norm(self.h, Tensor.of(x), Tensor.of(out), eps), "b200_rms_norm")
+        return out
+
+    def get_rows(self, src0, ids, out=None):
+        """GGML_OP_GET_ROWS: src0 a torch tensor [.., n_rows, K] (float32 / float16) or a Tensor (quantized); ids int32 [.., n_ids]"""
+        t0 = src0 if isinstance(src0, Tensor) else Tensor.of(src0)
+        ti = Tensor.of(ids)
+        if out is None:
+            out = self.torch.empty((ti.ne[2], ti.ne[1], ti.ne[0], t0.ne[0]), dtype=self.torch.float32, device=ids.device)
+        check(lib().b200_get_rows(self.h, t0, ti, Tensor.of(out)), "b200_get_rows")
+        return out
+
+    def rope(self, x, pos, n_dims, mode=0, freq_factors=None, n_ctx_orig=0, freq_base=10000.0, freq_scale=1.0, ext_factor=0.0, attn_factor=1.0,
+             beta_fast=32.0, beta_slow=1.0, out=None):
+        """GGML_OP_ROPE: x float32 [n_batch, n_tokens, n_head, n_embd_head]; pos int32 [n_tokens]"""
+        out = self.torch.empty(x.shape, dtype=self.torch.float32, device=x.device) if out is None else out
+        rp = RopeParams(n_dims, mode, n_ctx_orig, freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow)
+        check(lib().b200_rope(self.h, Tensor.of(x), Tensor.of(pos), None if freq_factors is None else Tensor.of(freq_factors), Tensor.of(out), rp), "b200_rope")
+        return out
+
+    def set_rows(self, dst, src, idx):
+        """GGML_OP_SET_ROWS: dst[.., idx[i], :] = src[.., i, :]; src float32, dst float32 / float16, idx int64 / int32"""
+        check(lib().b200_set_rows(self.h, Tensor.of(src), Tensor.of(idx), Tensor.of(dst)), "b200_set_rows")
+        return dst
+
+    def cpy(self, src, dst):
+        """GGML_OP_CPY / CONT / DUP between float32 / float16 tensors of equal element count, any strides"""
+        check(lib().b200_cpy(self.h, Tensor.of(src), Tensor.of(dst)), "b200_cpy")
+        return dst
+
+    def flash_attn_ext(self, q, k, v, mask=None, sinks=None, scale=1.0, max_bias=0.0, logit_softcap=0.0):
+        """GGML_OP_FLASH_ATTN_EXT: q float32 [n_batch, n_head, n_q, D]; k, v float16 [n_batch, n_head_kv, n_kv, D]; mask float16
+        [1 | n_batch, 1 | n_head, >= n_q, n_kv]; returns float32 [n_batch, n_q, n_head, D]"""
+        nb_, nh, nq, D = q.shape
+        out = self.torch.empty((nb_, nq, nh, D), dtype=self.torch.float32, device=q.device)
+        check(lib().b200_flash_attn_ext(self.h, Tensor.of(q), Tensor.of(k), Tensor.of(v), None if mask is None else Tensor.of(mask),
+                                        None if sinks is None else Tensor.of(sinks), Tensor.of(out), scale, max_bias, logit_softcap), "b200_flash_attn_ext")
+        return out
 
     def add_id(self, a, bias, ids):
         """GGML_OP_ADD_ID: a float32 [n_tok, n_used, M]; bias [n_as, M]; ids int32 [n_tok, n_used]"""

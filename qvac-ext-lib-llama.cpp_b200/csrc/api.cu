@@ -139,6 +139,7 @@ void b200_ctx_destroy(b200_ctx * ctx) {
     if (ctx->io) cudaFree(ctx->io);
     if (ctx->scratch2) cudaFree(ctx->scratch2);
     if (ctx->scratch3) cudaFree(ctx->scratch3);
+    if (ctx->fa_ws) cudaFree(ctx->fa_ws);
     if (ctx->trace) cudaFree(ctx->trace);
     if (ctx->tc_turn) cudaFree(ctx->tc_turn);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);

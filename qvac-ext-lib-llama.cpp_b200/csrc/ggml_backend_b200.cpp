@@ -652,6 +652,100 @@ int try_fuse_epilogue(be_ctx * c, ggml_cgraph * cgraph, int i) {
     return count;
 }
 
+// ------------------------------------------------------------------------------------------------ f3: the ops between the matmuls
+// SURVEY 8(f) rank 3, first slice (ops.cu): GET_ROWS, RMS_NORM, ROPE, SET_ROWS, CPY / CONT / DUP, FLASH_ATTN_EXT. With them a Llama
+// decode graph is ONE split on this backend. GGML_B200_F3=0 declines them all (the scheduler then leaves them to ggml-cpu as before).
+bool exact_mode();
+bool f3_on() {
+    static const bool on = [] { const char * s = getenv("GGML_B200_F3"); return !(s && atoi(s) == 0); }();
+    return on;
+}
+b200_tensor as_b200(const ggml_tensor * t) {
+    b200_tensor r;
+    r.data = t->data;
+    r.type = (int32_t) t->type;
+    for (int i = 0; i < 4; i++) { r.ne[i] = t->ne[i]; r.nb[i] = t->nb[i]; }
+    return r;
+}
+b200_rope_params rope_params_of(const ggml_tensor * op) {
+    b200_rope_params rp;
+    rp.n_dims      = ggml_get_op_params_i32(op, 1);
+    rp.mode        = ggml_get_op_params_i32(op, 2);
+    rp.n_ctx_orig  = ggml_get_op_params_i32(op, 4);
+    rp.freq_base   = ggml_get_op_params_f32(op, 5);
+    rp.freq_scale  = ggml_get_op_params_f32(op, 6);
+    rp.ext_factor  = ggml_get_op_params_f32(op, 7);
+    rp.attn_factor = ggml_get_op_params_f32(op, 8);
+    rp.beta_fast   = ggml_get_op_params_f32(op, 9);
+    rp.beta_slow   = ggml_get_op_params_f32(op, 10);
+    return rp;
+}
+// what dev_supports_op answers for the f3 ops; graph_compute runs exactly what this accepts
+bool f3_ok(const ggml_tensor * op) {
+    if (!f3_on() || exact_mode()) return false;
+    const b200_tensor d = as_b200(op);
+    b200_tensor s[5];
+    for (int i = 0; i < 5; i++) if (op->src[i]) s[i] = as_b200(op->src[i]);
+    switch (op->op) {
+        case GGML_OP_RMS_NORM:
+            return op->src[0] && b200_rms_norm_supported(&s[0], &d);
+        case GGML_OP_GET_ROWS:
+            return op->src[0] && op->src[1] && b200_get_rows_supported(&s[0], &s[1], &d);
+        case GGML_OP_ROPE: {
+            if (!op->src[0] || !op->src[1]) return false;
+            const b200_rope_params rp = rope_params_of(op);
+            return b200_rope_supported(&s[0], &s[1], op->src[2] ? &s[2] : nullptr, &d, &rp);
+        }
+        case GGML_OP_SET_ROWS:
+            return op->src[0] && op->src[1] && b200_set_rows_supported(&s[0], &s[1], &d);
+        case GGML_OP_CPY:   // dst = src[1]'s layout (the node is a view of it); CONT / DUP: the node's own
+        case GGML_OP_CONT:
+        case GGML_OP_DUP:
+            return op->src[0] && b200_cpy_supported(&s[0], &d);
+        case GGML_OP_FLASH_ATTN_EXT:
+            return op->src[0] && op->src[1] && op->src[2] &&
+                   b200_flash_attn_ext_supported(&s[0], &s[1], &s[2], op->src[3] ? &s[3] : nullptr, op->src[4] ? &s[4] : nullptr, &d);
+        default:
+            return false;
+    }
+}
+bool is_f3_op(ggml_op op) {
+    return op == GGML_OP_RMS_NORM || op == GGML_OP_GET_ROWS || op == GGML_OP_ROPE || op == GGML_OP_SET_ROWS || op == GGML_OP_CPY || op == GGML_OP_CONT ||
+           op == GGML_OP_DUP || op == GGML_OP_FLASH_ATTN_EXT;
+}
+void run_f3(be_ctx * c, ggml_tensor * op) {
+    const b200_tensor d = as_b200(op);
+    b200_tensor s[5];
+    for (int i = 0; i < 5; i++) if (op->src[i]) s[i] = as_b200(op->src[i]);
+    switch (op->op) {
+        case GGML_OP_RMS_NORM:
+            CHECK_RUN(c, b200_rms_norm(c->ctx, &s[0], &d, ggml_get_op_params_f32(op, 0)));
+            break;
+        case GGML_OP_GET_ROWS:
+            CHECK_RUN(c, b200_get_rows(c->ctx, &s[0], &s[1], &d));
+            break;
+        case GGML_OP_ROPE: {
+            const b200_rope_params rp = rope_params_of(op);
+            CHECK_RUN(c, b200_rope(c->ctx, &s[0], &s[1], op->src[2] ? &s[2] : nullptr, &d, &rp));
+            break;
+        }
+        case GGML_OP_SET_ROWS:
+            CHECK_RUN(c, b200_set_rows(c->ctx, &s[0], &s[1], &d));
+            break;
+        case GGML_OP_CPY:
+        case GGML_OP_CONT:
+        case GGML_OP_DUP:
+            CHECK_RUN(c, b200_cpy(c->ctx, &s[0], &d));
+            break;
+        case GGML_OP_FLASH_ATTN_EXT:
+            CHECK_RUN(c, b200_flash_attn_ext(c->ctx, &s[0], &s[1], &s[2], op->src[3] ? &s[3] : nullptr, op->src[4] ? &s[4] : nullptr, &d,
+                                             ggml_get_op_params_f32(op, 0), ggml_get_op_params_f32(op, 1), ggml_get_op_params_f32(op, 2)));
+            break;
+        default:
+            break;
+    }
+}
+
 ggml_status run_nodes(be_ctx * c, ggml_cgraph * cgraph) {
     for (int i = 0; i < cgraph->n_nodes; i++) {
         ggml_tensor * node = cgraph->nodes[i];
@@ -711,6 +805,8 @@ ggml_status run_nodes(be_ctx * c, ggml_cgraph * cgraph) {
             run_add(c, node);
         } else if (node->op == GGML_OP_ADD_ID && add_id_ok(node)) {
             run_add_id(c, node);
+        } else if (is_f3_op(node->op) && f3_ok(node)) {
+            run_f3(c, node);
         } else {
             GGML_LOG_ERROR("ggml-b200: op %s is not implemented by this backend (%s)\n", ggml_op_name(node->op), node->name);
             return GGML_STATUS_FAILED;
@@ -945,6 +1041,16 @@ bool dev_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
             return add_ok(op);
         case GGML_OP_ADD_ID:
             return add_id_ok(op);
+        // f3: ggml-cuda.cu:4346-4618 answers for the same ops
+        case GGML_OP_RMS_NORM:
+        case GGML_OP_GET_ROWS:
+        case GGML_OP_ROPE:
+        case GGML_OP_SET_ROWS:
+        case GGML_OP_CPY:
+        case GGML_OP_CONT:
+        case GGML_OP_DUP:
+        case GGML_OP_FLASH_ATTN_EXT:
+            return f3_ok(op);
         default:
             return false;
     }

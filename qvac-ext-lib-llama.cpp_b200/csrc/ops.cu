@@ -1,0 +1,583 @@
+// ops.cu — SURVEY 8(f) rank 3, first slice: the ops BETWEEN the matmuls of a Llama decode graph, so that the graph stays on the
+// device (no scheduler split per layer): GET_ROWS, RMS_NORM, ROPE, SET_ROWS, CPY / CONT / DUP and a FLASH_ATTN_EXT for F16 K/V.
+// Semantics are ggml-cpu's (/root/reference/ggml/src/ggml-cpu/ops.cpp: rms_norm :3646-3695, rope :5525-5780, set_rows :4828-4876,
+// get_rows :4540-4780, flash_attn_ext :7860-8140, dup/cpy :20-700); what the reference's CUDA backend does in norm.cu, rope.cu,
+// set-rows.cu, getrows.cu, cpy.cu, fattn*.cu. These are the small ops of a decode step (a few KB each): plain, coalesced,
+// one-pass kernels - the bytes of a token live in the weight matrices, which is where the tuned kernels are.
+
+#include "internal.h"
+
+#include <algorithm>
+
+using namespace b200;
+#define fail b200_fail
+
+namespace {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+struct T4 {   // a ggml tensor's geometry: elements and byte strides
+    int64_t ne[4];
+    int64_t nb[4];
+};
+T4 t4(const b200_tensor * t) {
+    T4 r;
+    for (int i = 0; i < 4; i++) { r.ne[i] = t->ne[i]; r.nb[i] = (int64_t) t->nb[i]; }
+    return r;
+}
+
+// ------------------------------------------------------------------------------------------------ RMS_NORM
+// y = x / sqrt(mean(x^2) + eps), one CTA per row (ggml-cpu sums in double; fp32 tree sums here: NMSE ~1e-13 apart)
+__global__ void __launch_bounds__(256) rms_norm_kernel(const char * x, T4 s, char * y, T4 d, float eps) {
+    const int64_t row = blockIdx.x;
+    const int64_t i1 = row % s.ne[1], i2 = (row / s.ne[1]) % s.ne[2], i3 = row / (s.ne[1] * s.ne[2]);
+    const float * xr = (const float *) (x + i1 * s.nb[1] + i2 * s.nb[2] + i3 * s.nb[3]);
+    float *       yr = (float *) (y + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    float sum = 0.0f;
+    for (int64_t i = threadIdx.x; i < s.ne[0]; i += blockDim.x) { const float v = xr[i]; sum += v * v; }
+    __shared__ float part[8];
+    sum = warp_sum(sum);
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    float tot = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) tot += part[i];
+    const float scale = 1.0f / sqrtf(tot / (float) s.ne[0] + eps);
+    for (int64_t i = threadIdx.x; i < s.ne[0]; i += blockDim.x) yr[i] = xr[i] * scale;
+}
+
+// ------------------------------------------------------------------------------------------------ dequantization of one element
+// the arithmetic of dequantize_row_<type> (ggml-quants.c:307-325, 400-420, 1352-1373, 1536-1560, 1762-1791), element by element
+__device__ __forceinline__ void k4_scale_min(int j, const uint8_t * q, int & sc, int & m) {
+    if (j < 4) { sc = q[j] & 63; m = q[j + 4] & 63; }
+    else { sc = (q[j + 4] & 0xF) | ((q[j - 4] >> 6) << 4); m = (q[j + 4] >> 4) | ((q[j] >> 6) << 4); }
+}
+__device__ __forceinline__ float dequant_at(int type, const uint8_t * row, int64_t k) {
+    switch (type) {
+        case B200_TYPE_Q4_0: {
+            const uint8_t * b = row + (k >> 5) * SZ_Q4_0;
+            const int j = (int) (k & 31);
+            const int q = j < 16 ? (b[2 + j] & 0xF) : (b[2 + j - 16] >> 4);
+            return (float) (q - 8) * half_bits_to_float(*(const uint16_t *) b);
+        }
+        case B200_TYPE_Q8_0: {
+            const uint8_t * b = row + (k >> 5) * SZ_Q8_0;
+            return (float) ((const int8_t *) (b + 2))[k & 31] * half_bits_to_float(*(const uint16_t *) b);
+        }
+        case B200_TYPE_Q4_K:
+        case B200_TYPE_Q5_K: {
+            const bool q5 = type == B200_TYPE_Q5_K;
+            const uint8_t * b = row + (k >> 8) * (q5 ? SZ_Q5_K : SZ_Q4_K);
+            const int e = (int) (k & 255), j = e >> 5, l = e & 31;
+            int sc, m;
+            k4_scale_min(j, b + 4, sc, m);
+            const float d = half_bits_to_float(*(const uint16_t *) b), dmin = half_bits_to_float(*(const uint16_t *) (b + 2));
+            const uint8_t qb = b[(q5 ? 48 : 16) + 32 * (j >> 1) + l];
+            int q = (j & 1) ? (qb >> 4) : (qb & 0xF);
+            if (q5) q += ((b[16 + l] >> j) & 1) ? 16 : 0;
+            // d1 = d * sc; m1 = dmin * m; y = d1 * q - m1, each rounded (no contraction: ggml-cpu's x86-64 baseline build has no FMA)
+            return __fsub_rn(__fmul_rn(__fmul_rn(d, (float) sc), (float) q), __fmul_rn(dmin, (float) m));
+        }
+        case B200_TYPE_Q6_K: {
+            const uint8_t * b = row + (k >> 8) * SZ_Q6_K;
+            const int e = (int) (k & 255), h = e >> 7, r = e & 127, quarter = r >> 5, l = r & 31;
+            const uint8_t * ql = b + 64 * h, * qh = b + 128 + 32 * h;
+            const int8_t *  sc = (const int8_t *) (b + 192);
+            const int lo = quarter == 0 ? (ql[l] & 0xF) : quarter == 1 ? (ql[l + 32] & 0xF) : quarter == 2 ? (ql[l] >> 4) : (ql[l + 32] >> 4);
+            const int q  = (lo | (((qh[l] >> (2 * quarter)) & 3) << 4)) - 32;
+            return __fmul_rn(__fmul_rn(half_bits_to_float(*(const uint16_t *) (b + 208)), (float) sc[e >> 4]), (float) q);
+        }
+    }
+    return 0.0f;
+}
+
+// ------------------------------------------------------------------------------------------------ GET_ROWS
+// dst[:, i10, i11, i12] = row ids[i10, i11, i12] of src0[:, :, i11, i12], as F32
+__global__ void __launch_bounds__(256) get_rows_kernel(int type, const char * src0, int64_t ne00, int64_t ne01, int64_t nb01, int64_t nb02, int64_t nb03,
+                                                       const char * ids, T4 is, char * dst, int64_t nb1, int64_t nb2, int64_t nb3) {
+    const int64_t r = blockIdx.x;
+    const int64_t i10 = r % is.ne[0], i11 = (r / is.ne[0]) % is.ne[1], i12 = r / (is.ne[0] * is.ne[1]);
+    const int32_t row = *(const int32_t *) (ids + i10 * is.nb[0] + i11 * is.nb[1] + i12 * is.nb[2]);
+    float * out = (float *) (dst + i10 * nb1 + i11 * nb2 + i12 * nb3);
+    if (row < 0 || row >= ne01) {   // ggml-cpu asserts; never read out of bounds
+        for (int64_t k = threadIdx.x; k < ne00; k += blockDim.x) out[k] = 0.0f;
+        return;
+    }
+    const char * in = src0 + row * nb01 + i11 * nb02 + i12 * nb03;
+    if (type == B200_TYPE_F32) {
+        for (int64_t k = threadIdx.x; k < ne00; k += blockDim.x) out[k] = ((const float *) in)[k];
+    } else if (type == B200_TYPE_F16) {
+        for (int64_t k = threadIdx.x; k < ne00; k += blockDim.x) out[k] = __half2float(((const __half *) in)[k]);
+    } else {
+        for (int64_t k = threadIdx.x; k < ne00; k += blockDim.x) out[k] = dequant_at(type, (const uint8_t *) in, k);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ ROPE (normal and neox pairs)
+struct RopeP {
+    int   n_dims, neox;
+    float theta_scale, freq_scale, ext_factor, attn_factor, corr0, corr1;
+};
+// one thread per rotated pair (or per pair of pass-through elements beyond n_dims) of one row (i1 = head, i2 = position, i3 = batch)
+__global__ void __launch_bounds__(256) rope_kernel(const char * x, T4 s, const int32_t * pos, const float * ff, char * y, T4 d, RopeP p) {
+    const int64_t row = blockIdx.x;
+    const int64_t i1 = row % s.ne[1], i2 = (row / s.ne[1]) % s.ne[2], i3 = row / (s.ne[1] * s.ne[2]);
+    const float * xr = (const float *) (x + i1 * s.nb[1] + i2 * s.nb[2] + i3 * s.nb[3]);
+    float *       yr = (float *) (y + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    const float   base = (float) pos[i2];
+    for (int64_t i0 = 2 * threadIdx.x; i0 < s.ne[0]; i0 += 2 * blockDim.x) {
+        if (i0 >= p.n_dims) {   // channels beyond n_dims are copied
+            yr[i0] = xr[i0]; yr[i0 + 1] = xr[i0 + 1];
+            continue;
+        }
+        // theta_base of pair i0/2 as ggml_rope_cache_init forms it (ops.cpp:5549-5563): pos times theta_scale, i0/2 times over, each
+        // product rounded - not powf, so that the angle is the reference's to the bit; then rope_yarn (ops.cpp:5532-5547)
+        float tb = base;
+        for (int64_t j = 0; j < i0 / 2; j++) tb = __fmul_rn(tb, p.theta_scale);
+        const float theta_extrap = tb / (ff ? ff[i0 / 2] : 1.0f);
+        const float theta_interp = p.freq_scale * theta_extrap;
+        float theta = theta_interp, mscale = p.attn_factor;
+        if (p.ext_factor != 0.0f) {
+            const float yv = ((float) (i0 / 2) - p.corr0) / fmaxf(0.001f, p.corr1 - p.corr0);
+            const float ramp_mix = (1.0f - fminf(1.0f, fmaxf(0.0f, yv))) * p.ext_factor;
+            theta = theta_interp * (1.0f - ramp_mix) + theta_extrap * ramp_mix;
+            mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
+        }
+        const float c = cosf(theta) * mscale, sn = sinf(theta) * mscale;
+        const int64_t ia = p.neox ? i0 / 2 : i0, ib = p.neox ? i0 / 2 + p.n_dims / 2 : i0 + 1;
+        const float x0 = xr[ia], x1 = xr[ib];
+        yr[ia] = x0 * c - x1 * sn;
+        yr[ib] = x0 * sn + x1 * c;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ SET_ROWS (F32 -> F32 / F16 rows by index)
+template <typename OUT>
+__device__ __forceinline__ OUT cvt_out(float v);
+template <> __device__ __forceinline__ float cvt_out<float>(float v) { return v; }
+template <> __device__ __forceinline__ __half cvt_out<__half>(float v) { return __float2half_rn(v); }
+
+template <typename OUT, typename IDX>
+__global__ void __launch_bounds__(256) set_rows_kernel(const char * src, T4 s, const char * idx, T4 is, char * dst, T4 d) {
+    const int64_t r = blockIdx.x;
+    const int64_t i = r % s.ne[1], i02 = (r / s.ne[1]) % s.ne[2], i03 = r / (s.ne[1] * s.ne[2]);
+    const int64_t i1 = (int64_t) *(const IDX *) (idx + i * is.nb[0] + (i02 % is.ne[1]) * is.nb[1] + (i03 % is.ne[2]) * is.nb[2]);
+    if (i1 < 0 || i1 >= d.ne[1]) return;   // ggml-cpu asserts
+    const float * in = (const float *) (src + i * s.nb[1] + i02 * s.nb[2] + i03 * s.nb[3]);
+    OUT * out = (OUT *) (dst + i1 * d.nb[1] + i02 * d.nb[2] + i03 * d.nb[3]);
+    for (int64_t k = threadIdx.x; k < s.ne[0]; k += blockDim.x) out[k] = cvt_out<OUT>(in[k]);
+}
+
+// ------------------------------------------------------------------------------------------------ CPY / CONT / DUP
+// element e (in the order of the SOURCE's logical index) goes to the same linear index of the destination's shape
+template <typename IN> __device__ __forceinline__ float cvt_in(IN v);
+template <> __device__ __forceinline__ float cvt_in<float>(float v) { return v; }
+template <> __device__ __forceinline__ float cvt_in<__half>(__half v) { return __half2float(v); }
+
+template <typename IN, typename OUT>
+__global__ void __launch_bounds__(256) cpy_kernel(const char * src, T4 s, char * dst, T4 d, int64_t n) {
+    const int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    int64_t r = e;
+    const int64_t s0 = r % s.ne[0]; r /= s.ne[0];
+    const int64_t s1 = r % s.ne[1]; r /= s.ne[1];
+    const int64_t s2 = r % s.ne[2]; const int64_t s3 = r / s.ne[2];
+    r = e;
+    const int64_t d0 = r % d.ne[0]; r /= d.ne[0];
+    const int64_t d1 = r % d.ne[1]; r /= d.ne[1];
+    const int64_t d2 = r % d.ne[2]; const int64_t d3 = r / d.ne[2];
+    const IN v = *(const IN *) (src + s0 * s.nb[0] + s1 * s.nb[1] + s2 * s.nb[2] + s3 * s.nb[3]);
+    *(OUT *) (dst + d0 * d.nb[0] + d1 * d.nb[1] + d2 * d.nb[2] + d3 * d.nb[3]) = cvt_out<OUT>(cvt_in<IN>(v));
+}
+
+// ------------------------------------------------------------------------------------------------ FLASH_ATTN_EXT (F16 K / V)
+// One CTA per (query row, head, batch) x KV split; 8 warps stride over the KV positions of the split, four at a time (their K and V
+// rows are in flight together); a lane owns E consecutive channels of the head (DK = DV = 32 E), so a K or V row is one coalesced
+// 64 E-byte read per warp. Online softmax per warp in fp32 (ggml-cpu keeps the F16-V accumulator in fp16: ops.cpp:8102-8123; this
+// one is the more accurate side), warps merged through shared memory, KV splits merged by fa_combine_kernel. The heads of one GQA
+// group read the same K/V rows out of L2. Decode-shaped: a wide prefill batch re-reads K/V per query row.
+struct FaP {
+    T4 q, k, v, m, d;
+    const char * qd, * kd, * vd, * md;
+    const float * sinks;
+    char * dd;
+    float  scale, softcap, max_bias, m0, m1;
+    uint32_t n_head_log2;
+    int      nsplit;
+    int64_t  chunk;
+    float *  ws;
+};
+constexpr int FA_WARPS = 8, FA_U = 4;
+
+template <int E>
+__device__ __forceinline__ void load_halfs(const char * p, float * out) {
+    if constexpr (E == 2) {
+        const __half2 h = *(const __half2 *) p;
+        out[0] = __low2float(h); out[1] = __high2float(h);
+    } else if constexpr (E == 4) {
+        const uint2 u = *(const uint2 *) p;
+        const __half2 a = *(const __half2 *) &u.x, b = *(const __half2 *) &u.y;
+        out[0] = __low2float(a); out[1] = __high2float(a); out[2] = __low2float(b); out[3] = __high2float(b);
+    } else {
+        const uint4 u = *(const uint4 *) p;
+        const __half2 a = *(const __half2 *) &u.x, b = *(const __half2 *) &u.y, c = *(const __half2 *) &u.z, d = *(const __half2 *) &u.w;
+        out[0] = __low2float(a); out[1] = __high2float(a); out[2] = __low2float(b); out[3] = __high2float(b);
+        out[4] = __low2float(c); out[5] = __high2float(c); out[6] = __low2float(d); out[7] = __high2float(d);
+    }
+}
+
+__device__ __forceinline__ float fa_slope(const FaP & p, uint32_t h) {
+    if (!(p.max_bias > 0.0f)) return 1.0f;
+    return h < p.n_head_log2 ? powf(p.m0, (float) (h + 1)) : powf(p.m1, (float) (2 * (h - p.n_head_log2) + 1));
+}
+
+// dst row of (query iq1, head iq2, batch iq3): dst is [DV, n_head, n_q, n_batch] (ops.cpp:8217)
+__device__ __forceinline__ float * fa_dst_row(const FaP & p, int64_t iq1, int64_t iq2, int64_t iq3) {
+    return (float *) (p.dd + (iq3 * p.d.ne[2] * p.d.ne[1] + iq2 + iq1 * p.d.ne[1]) * p.d.nb[1]);
+}
+
+template <int E>
+__global__ void __launch_bounds__(FA_WARPS * 32) fa_kernel(const FaP p) {
+    constexpr int D = 32 * E;
+    const int64_t row = blockIdx.x;
+    const int64_t iq1 = row % p.q.ne[1], iq2 = (row / p.q.ne[1]) % p.q.ne[2], iq3 = row / (p.q.ne[1] * p.q.ne[2]);
+    const int64_t ik2 = iq2 / (p.q.ne[2] / p.k.ne[2]), ik3 = iq3 / (p.q.ne[3] / p.k.ne[3]);
+    const int64_t iv2 = iq2 / (p.q.ne[2] / p.v.ne[2]), iv3 = iq3 / (p.q.ne[3] / p.v.ne[3]);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    float qf[E];
+    {
+        const float * pq = (const float *) (p.qd + iq1 * p.q.nb[1] + iq2 * p.q.nb[2] + iq3 * p.q.nb[3]) + lane * E;
+#pragma unroll
+        for (int e = 0; e < E; e++) qf[e] = __half2float(__float2half_rn(pq[e])) * p.scale;   // ggml-cpu converts q to the K type's vec_dot type: fp16
+    }
+    const __half * mp = p.md ? (const __half *) (p.md + iq1 * p.m.nb[1] + (iq2 % p.m.ne[2]) * p.m.nb[2] + (iq3 % p.m.ne[3]) * p.m.nb[3]) : nullptr;
+    const float slope = fa_slope(p, (uint32_t) iq2);
+    const char * kb = p.kd + ik2 * p.k.nb[2] + ik3 * p.k.nb[3] + lane * E * 2;
+    const char * vb = p.vd + iv2 * p.v.nb[2] + iv3 * p.v.nb[3] + lane * E * 2;
+
+    float M = -INFINITY, S = 0.0f, acc[E];
+#pragma unroll
+    for (int e = 0; e < E; e++) acc[e] = 0.0f;
+
+    const int64_t c0 = (int64_t) blockIdx.y * p.chunk, c1 = min(c0 + p.chunk, p.k.ne[1]);
+    for (int64_t base = c0 + warp * FA_U; base < c1; base += FA_WARPS * FA_U) {
+        float s[FA_U], mv[FA_U], kf[FA_U][E], vf[FA_U][E];
+#pragma unroll
+        for (int u = 0; u < FA_U; u++) {
+            const int64_t ic = base + u;
+            mv[u] = ic < c1 ? (mp ? slope * __half2float(mp[ic]) : 0.0f) : -INFINITY;
+        }
+#pragma unroll
+        for (int u = 0; u < FA_U; u++) {
+            if (mv[u] != -INFINITY) {   // warp-uniform
+                load_halfs<E>(kb + (base + u) * p.k.nb[1], kf[u]);
+                load_halfs<E>(vb + (base + u) * p.v.nb[1], vf[u]);
+            }
+        }
+        float mx = -INFINITY;
+#pragma unroll
+        for (int u = 0; u < FA_U; u++) {
+            s[u] = -INFINITY;
+            if (mv[u] != -INFINITY) {
+                float t = 0.0f;
+#pragma unroll
+                for (int e = 0; e < E; e++) t += qf[e] * kf[u][e];
+                t = warp_sum(t);
+                if (p.softcap != 0.0f) t = p.softcap * tanhf(t);
+                s[u] = t + mv[u];
+            }
+            mx = fmaxf(mx, s[u]);
+        }
+        if (mx == -INFINITY) continue;
+        const float Mn = fmaxf(M, mx), ms = expf(M - Mn);   // M = -inf: expf(-inf) = 0
+        M = Mn;
+        S *= ms;
+#pragma unroll
+        for (int e = 0; e < E; e++) acc[e] *= ms;
+#pragma unroll
+        for (int u = 0; u < FA_U; u++) {
+            if (s[u] != -INFINITY) {
+                const float pr = expf(s[u] - Mn);
+                S += pr;
+#pragma unroll
+                for (int e = 0; e < E; e++) acc[e] += pr * vf[u][e];
+            }
+        }
+    }
+
+    __shared__ float sh_acc[FA_WARPS][D];
+    __shared__ float sh_m[FA_WARPS], sh_s[FA_WARPS];
+#pragma unroll
+    for (int e = 0; e < E; e++) sh_acc[warp][lane * E + e] = acc[e];
+    if (lane == 0) { sh_m[warp] = M; sh_s[warp] = S; }
+    __syncthreads();
+    float Mx = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < FA_WARPS; w++) Mx = fmaxf(Mx, sh_m[w]);
+    float St = 0.0f;
+    float f[FA_WARPS];
+#pragma unroll
+    for (int w = 0; w < FA_WARPS; w++) { f[w] = sh_m[w] == -INFINITY ? 0.0f : expf(sh_m[w] - Mx); St += sh_s[w] * f[w]; }
+    for (int t = threadIdx.x; t < D; t += blockDim.x) {
+        float a = 0.0f;
+#pragma unroll
+        for (int w = 0; w < FA_WARPS; w++) a += sh_acc[w][t] * f[w];
+        if (p.nsplit > 1) {
+            p.ws[(row * p.nsplit + blockIdx.y) * (D + 2) + 2 + t] = a;
+        } else {
+            float Sf = St, af = a;
+            if (p.sinks) {   // ops.cpp:8190-8204
+                const float sk = p.sinks[iq2];
+                if (sk > Mx) { const float r = expf(Mx - sk); af *= r; Sf = Sf * r + 1.0f; } else { Sf += expf(sk - Mx); }
+            }
+            fa_dst_row(p, iq1, iq2, iq3)[t] = Sf == 0.0f ? 0.0f : af / Sf;
+        }
+    }
+    if (p.nsplit > 1 && threadIdx.x == 0) {
+        float * w = p.ws + (row * p.nsplit + blockIdx.y) * (D + 2);
+        w[0] = Mx; w[1] = St;
+    }
+}
+
+// merges the KV splits of one row: one CTA per row, one thread per channel
+__global__ void __launch_bounds__(256) fa_combine_kernel(const FaP p, int D) {
+    const int64_t row = blockIdx.x;
+    const int64_t iq1 = row % p.q.ne[1], iq2 = (row / p.q.ne[1]) % p.q.ne[2], iq3 = row / (p.q.ne[1] * p.q.ne[2]);
+    const float * w = p.ws + row * p.nsplit * (D + 2);
+    float Mx = -INFINITY;
+    for (int s = 0; s < p.nsplit; s++) Mx = fmaxf(Mx, w[s * (D + 2)]);
+    float St = 0.0f;
+    for (int s = 0; s < p.nsplit; s++) { const float m = w[s * (D + 2)]; St += m == -INFINITY ? 0.0f : w[s * (D + 2) + 1] * expf(m - Mx); }
+    float r = 1.0f;
+    if (p.sinks) {
+        const float sk = p.sinks[iq2];
+        if (sk > Mx) { r = expf(Mx - sk); St = St * r + 1.0f; } else { St += expf(sk - Mx); }
+    }
+    for (int t = threadIdx.x; t < D; t += blockDim.x) {
+        float a = 0.0f;
+        for (int s = 0; s < p.nsplit; s++) { const float m = w[s * (D + 2)]; if (m != -INFINITY) a += w[s * (D + 2) + 2 + t] * expf(m - Mx); }
+        fa_dst_row(p, iq1, iq2, iq3)[t] = St == 0.0f ? 0.0f : a * r / St;
+    }
+}
+
+bool rows_ok(const b200_tensor * t, size_t elem) { return t && t->nb[0] == elem; }
+int64_t nelem(const b200_tensor * t) { return t->ne[0] * t->ne[1] * t->ne[2] * t->ne[3]; }
+bool nonneg(const b200_tensor * t) { return t->ne[0] >= 0 && t->ne[1] >= 0 && t->ne[2] >= 0 && t->ne[3] >= 0; }
+
+#define OPS_PROLOGUE(ctx)                                                                      \
+    if (!(ctx)) return fail(B200_ERR_ARG, "null context");                                     \
+    CU(cudaSetDevice((ctx)->device));                                                          \
+    if (b200_status fst_ = b200_split_flush(ctx)) return fst_
+#define OPS_EPILOGUE(ctx)                                                                      \
+    CU(cudaGetLastError());                                                                    \
+    (ctx)->launches++;                                                                         \
+    return B200_OK
+
+} // namespace
+
+extern "C" {
+
+int b200_rms_norm_supported(const b200_tensor * x, const b200_tensor * dst) {
+    return x && dst && x->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && rows_ok(x, 4) && rows_ok(dst, 4) && nonneg(x) &&
+           x->ne[0] == dst->ne[0] && x->ne[1] == dst->ne[1] && x->ne[2] == dst->ne[2] && x->ne[3] == dst->ne[3] &&
+           x->ne[1] * x->ne[2] * x->ne[3] < (1ll << 31);
+}
+
+b200_status b200_rms_norm(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * dst, float eps) {
+    if (!b200_rms_norm_supported(x, dst)) return fail(B200_ERR_UNSUPPORTED, "RMS_NORM: F32 rows, same shapes");
+    const int64_t rows = x->ne[1] * x->ne[2] * x->ne[3];
+    if (rows == 0 || x->ne[0] == 0) return B200_OK;
+    if (!x->data || !dst->data) return fail(B200_ERR_ARG, "null argument");
+    OPS_PROLOGUE(ctx);
+    rms_norm_kernel<<<(unsigned) rows, 256, 0, ctx->stream>>>((const char *) x->data, t4(x), (char *) dst->data, t4(dst), eps);
+    OPS_EPILOGUE(ctx);
+}
+
+int b200_get_rows_supported(const b200_tensor * src0, const b200_tensor * ids, const b200_tensor * dst) {
+    if (!src0 || !ids || !dst || dst->type != B200_TYPE_F32 || ids->type != B200_TYPE_I32 || !rows_ok(dst, 4)) return 0;
+    if (!nonneg(src0) || !nonneg(ids) || ids->ne[3] != 1) return 0;
+    switch (src0->type) {
+        case B200_TYPE_F32: if (src0->nb[0] != 4) return 0; break;
+        case B200_TYPE_F16: if (src0->nb[0] != 2) return 0; break;
+        case B200_TYPE_Q4_0: case B200_TYPE_Q8_0: if (src0->ne[0] % 32) return 0; break;
+        case B200_TYPE_Q4_K: case B200_TYPE_Q5_K: case B200_TYPE_Q6_K: if (src0->ne[0] % 256) return 0; break;
+        default: return 0;
+    }
+    if (ids->ne[1] != src0->ne[2] || ids->ne[2] != src0->ne[3]) return 0;
+    return dst->ne[0] == src0->ne[0] && dst->ne[1] == ids->ne[0] && dst->ne[2] == ids->ne[1] && dst->ne[3] == ids->ne[2] &&
+           ids->ne[0] * ids->ne[1] * ids->ne[2] < (1ll << 31);
+}
+
+b200_status b200_get_rows(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * ids, const b200_tensor * dst) {
+    if (!b200_get_rows_supported(src0, ids, dst)) return fail(B200_ERR_UNSUPPORTED, "GET_ROWS: F32/F16/q4_0/q8_0/q4_K/q5_K/q6_K rows by I32 index into F32");
+    const int64_t rows = ids->ne[0] * ids->ne[1] * ids->ne[2];
+    if (rows == 0 || src0->ne[0] == 0) return B200_OK;
+    if (!src0->data || !ids->data || !dst->data) return fail(B200_ERR_ARG, "null argument");
+    OPS_PROLOGUE(ctx);
+    get_rows_kernel<<<(unsigned) rows, 256, 0, ctx->stream>>>(src0->type, (const char *) src0->data, src0->ne[0], src0->ne[1], (int64_t) src0->nb[1],
+                                                              (int64_t) src0->nb[2], (int64_t) src0->nb[3], (const char *) ids->data, t4(ids),
+                                                              (char *) dst->data, (int64_t) dst->nb[1], (int64_t) dst->nb[2], (int64_t) dst->nb[3]);
+    OPS_EPILOGUE(ctx);
+}
+
+int b200_rope_supported(const b200_tensor * x, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst, const b200_rope_params * rp) {
+    if (!x || !pos || !dst || !rp || x->type != B200_TYPE_F32 || dst->type != B200_TYPE_F32 || pos->type != B200_TYPE_I32) return 0;
+    if (!rows_ok(x, 4) || !rows_ok(dst, 4) || !nonneg(x) || pos->nb[0] != 4 || pos->ne[0] < x->ne[2]) return 0;
+    for (int i = 0; i < 4; i++) if (x->ne[i] != dst->ne[i]) return 0;
+    if (rp->mode != B200_ROPE_NORMAL && rp->mode != B200_ROPE_NEOX) return 0;   // mrope / vision: not on the Llama decode path
+    if (rp->n_dims <= 0 || rp->n_dims % 2 || rp->n_dims > x->ne[0] || x->ne[0] % 2) return 0;
+    if (freq_factors && (freq_factors->type != B200_TYPE_F32 || freq_factors->nb[0] != 4 || freq_factors->ne[0] < rp->n_dims / 2)) return 0;
+    return x->ne[1] * x->ne[2] * x->ne[3] < (1ll << 31);
+}
+
+b200_status b200_rope(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst,
+                      const b200_rope_params * rp) {
+    if (!b200_rope_supported(x, pos, freq_factors, dst, rp)) return fail(B200_ERR_UNSUPPORTED, "ROPE: F32, normal or neox mode");
+    const int64_t rows = x->ne[1] * x->ne[2] * x->ne[3];
+    if (rows == 0 || x->ne[0] == 0) return B200_OK;
+    if (!x->data || !pos->data || !dst->data) return fail(B200_ERR_ARG, "null argument");
+    // ggml_rope_yarn_corr_dims (ggml.c: ggml_rope_yarn_corr_dim): the channel range the YaRN ramp covers
+    RopeP p;
+    p.n_dims = rp->n_dims; p.neox = rp->mode == B200_ROPE_NEOX;
+    p.theta_scale = powf(rp->freq_base, -2.0f / (float) rp->n_dims);
+    p.freq_scale = rp->freq_scale; p.ext_factor = rp->ext_factor; p.attn_factor = rp->attn_factor;
+    auto corr_dim = [&](float n_rot) { return (float) rp->n_dims * logf((float) rp->n_ctx_orig / (n_rot * 2.0f * 3.14159265358979323846f)) / (2.0f * logf(rp->freq_base)); };
+    p.corr0 = fmaxf(0.0f, floorf(corr_dim(rp->beta_fast)));
+    p.corr1 = fminf((float) rp->n_dims - 1.0f, ceilf(corr_dim(rp->beta_slow)));
+    OPS_PROLOGUE(ctx);
+    const int threads = (int) std::min<int64_t>(256, std::max<int64_t>(32, (x->ne[0] / 2 + 31) / 32 * 32));
+    rope_kernel<<<(unsigned) rows, threads, 0, ctx->stream>>>((const char *) x->data, t4(x), (const int32_t *) pos->data,
+                                                              freq_factors ? (const float *) freq_factors->data : nullptr, (char *) dst->data, t4(dst), p);
+    OPS_EPILOGUE(ctx);
+}
+
+int b200_set_rows_supported(const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst) {
+    if (!src || !idx || !dst || src->type != B200_TYPE_F32 || !rows_ok(src, 4) || !nonneg(src) || !nonneg(idx)) return 0;
+    if (idx->type != B200_TYPE_I64 && idx->type != B200_TYPE_I32) return 0;
+    if (!((dst->type == B200_TYPE_F32 && dst->nb[0] == 4) || (dst->type == B200_TYPE_F16 && dst->nb[0] == 2))) return 0;
+    if (dst->ne[0] != src->ne[0] || dst->ne[2] != src->ne[2] || dst->ne[3] != src->ne[3] || idx->ne[0] != src->ne[1] || idx->ne[3] != 1) return 0;
+    if (idx->ne[1] <= 0 || idx->ne[2] <= 0 || src->ne[2] % idx->ne[1] || src->ne[3] % idx->ne[2]) return 0;
+    return src->ne[1] * src->ne[2] * src->ne[3] < (1ll << 31);
+}
+
+b200_status b200_set_rows(b200_ctx * ctx, const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst) {
+    if (!b200_set_rows_supported(src, idx, dst)) return fail(B200_ERR_UNSUPPORTED, "SET_ROWS: F32 rows into F32 / F16 by I64 / I32 index");
+    const int64_t rows = src->ne[1] * src->ne[2] * src->ne[3];
+    if (rows == 0 || src->ne[0] == 0) return B200_OK;
+    if (!src->data || !idx->data || !dst->data) return fail(B200_ERR_ARG, "null argument");
+    OPS_PROLOGUE(ctx);
+    const bool f16 = dst->type == B200_TYPE_F16, i64 = idx->type == B200_TYPE_I64;
+    const char * s = (const char *) src->data, * ix = (const char *) idx->data;
+    char * d = (char *) dst->data;
+    const unsigned g = (unsigned) rows;
+    if (f16 && i64)       set_rows_kernel<__half, int64_t><<<g, 256, 0, ctx->stream>>>(s, t4(src), ix, t4(idx), d, t4(dst));
+    else if (f16)         set_rows_kernel<__half, int32_t><<<g, 256, 0, ctx->stream>>>(s, t4(src), ix, t4(idx), d, t4(dst));
+    else if (i64)         set_rows_kernel<float, int64_t><<<g, 256, 0, ctx->stream>>>(s, t4(src), ix, t4(idx), d, t4(dst));
+    else                  set_rows_kernel<float, int32_t><<<g, 256, 0, ctx->stream>>>(s, t4(src), ix, t4(idx), d, t4(dst));
+    OPS_EPILOGUE(ctx);
+}
+
+int b200_cpy_supported(const b200_tensor * src, const b200_tensor * dst) {
+    if (!src || !dst || !nonneg(src) || !nonneg(dst) || nelem(src) != nelem(dst)) return 0;
+    const bool s_ok = src->type == B200_TYPE_F32 || src->type == B200_TYPE_F16, d_ok = dst->type == B200_TYPE_F32 || dst->type == B200_TYPE_F16;
+    return s_ok && d_ok;
+}
+
+b200_status b200_cpy(b200_ctx * ctx, const b200_tensor * src, const b200_tensor * dst) {
+    if (!b200_cpy_supported(src, dst)) return fail(B200_ERR_UNSUPPORTED, "CPY: F32 / F16 to F32 / F16 with the same number of elements");
+    const int64_t n = nelem(src);
+    if (n == 0) return B200_OK;
+    if (!src->data || !dst->data) return fail(B200_ERR_ARG, "null argument");
+    OPS_PROLOGUE(ctx);
+    const bool sf = src->type == B200_TYPE_F32, df = dst->type == B200_TYPE_F32;
+    const unsigned g = (unsigned) ((n + 255) / 256);
+    const char * s = (const char *) src->data;
+    char * d = (char *) dst->data;
+    if (sf && df)       cpy_kernel<float, float><<<g, 256, 0, ctx->stream>>>(s, t4(src), d, t4(dst), n);
+    else if (sf)        cpy_kernel<float, __half><<<g, 256, 0, ctx->stream>>>(s, t4(src), d, t4(dst), n);
+    else if (df)        cpy_kernel<__half, float><<<g, 256, 0, ctx->stream>>>(s, t4(src), d, t4(dst), n);
+    else                cpy_kernel<__half, __half><<<g, 256, 0, ctx->stream>>>(s, t4(src), d, t4(dst), n);
+    OPS_EPILOGUE(ctx);
+}
+
+int b200_flash_attn_ext_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * sinks,
+                                  const b200_tensor * dst) {
+    if (!q || !k || !v || !dst) return 0;
+    if (q->type != B200_TYPE_F32 || k->type != B200_TYPE_F16 || v->type != B200_TYPE_F16 || dst->type != B200_TYPE_F32) return 0;
+    if (!rows_ok(q, 4) || !rows_ok(k, 2) || !rows_ok(v, 2) || !rows_ok(dst, 4) || !nonneg(q) || !nonneg(k)) return 0;
+    const int64_t D = q->ne[0];
+    if (!(D == 64 || D == 128 || D == 256) || k->ne[0] != D || v->ne[0] != D || dst->ne[0] != D) return 0;
+    if (k->ne[1] != v->ne[1] || k->ne[2] <= 0 || k->ne[3] <= 0 || v->ne[2] <= 0 || v->ne[3] <= 0) return 0;
+    if (q->ne[2] % k->ne[2] || q->ne[3] % k->ne[3] || q->ne[2] % v->ne[2] || q->ne[3] % v->ne[3]) return 0;
+    if (dst->ne[1] != q->ne[2] || dst->ne[2] != q->ne[1] || dst->ne[3] != q->ne[3]) return 0;
+    const size_t al = (size_t) D / 16;   // bytes one lane reads of a K / V row
+    for (int i = 1; i < 4; i++) if (k->nb[i] % al || v->nb[i] % al || q->nb[i] % 4) return 0;
+    if (dst->nb[1] != (size_t) D * 4 || dst->nb[2] != dst->nb[1] * dst->ne[1] || dst->nb[3] != dst->nb[2] * dst->ne[2]) return 0;
+    if (mask) {
+        if (mask->type != B200_TYPE_F16 || mask->nb[0] != 2 || mask->ne[0] < k->ne[1] || mask->ne[1] < q->ne[1] || mask->ne[2] <= 0 || mask->ne[3] <= 0) return 0;
+    }
+    if (sinks && (sinks->type != B200_TYPE_F32 || sinks->nb[0] != 4 || sinks->ne[0] < q->ne[2])) return 0;
+    return q->ne[1] * q->ne[2] * q->ne[3] < (1ll << 31);
+}
+
+b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
+                                const b200_tensor * sinks, const b200_tensor * dst, float scale, float max_bias, float logit_softcap) {
+    if (!b200_flash_attn_ext_supported(q, k, v, mask, sinks, dst))
+        return fail(B200_ERR_UNSUPPORTED, "FLASH_ATTN_EXT: F32 q, F16 k / v of head size 64 / 128 / 256, F16 mask");
+    const int64_t rows = q->ne[1] * q->ne[2] * q->ne[3];
+    if (rows == 0) return B200_OK;
+    if (!q->data || !dst->data || (k->ne[1] > 0 && (!k->data || !v->data)) || (mask && !mask->data) || (sinks && !sinks->data)) return fail(B200_ERR_ARG, "null argument");
+    const int D = (int) q->ne[0];
+    if ((uintptr_t) k->data % (D / 16) || (uintptr_t) v->data % (D / 16)) return fail(B200_ERR_UNSUPPORTED, "FLASH_ATTN_EXT: K / V rows must be %d-byte aligned", D / 16);
+    FaP p;
+    p.q = t4(q); p.k = t4(k); p.v = t4(v); p.d = t4(dst);
+    p.m = mask ? t4(mask) : T4{};
+    p.qd = (const char *) q->data; p.kd = (const char *) k->data; p.vd = (const char *) v->data; p.md = mask ? (const char *) mask->data : nullptr;
+    p.sinks = sinks ? (const float *) sinks->data : nullptr;
+    p.dd = (char *) dst->data;
+    p.scale = logit_softcap != 0.0f ? scale / logit_softcap : scale;
+    p.softcap = logit_softcap; p.max_bias = max_bias;
+    const uint32_t n_head = (uint32_t) q->ne[2];
+    p.n_head_log2 = 1u << (uint32_t) floorf(log2f((float) n_head));
+    p.m0 = powf(2.0f, -max_bias / (float) p.n_head_log2);
+    p.m1 = powf(2.0f, -(max_bias / 2.0f) / (float) p.n_head_log2);
+    // KV splits: fill the SMs twice over, at least 256 positions per split
+    int nsplit = 1;
+    const int64_t n_kv = k->ne[1];
+    if (rows < 2 * ctx->sm_count && n_kv >= 512) {
+        nsplit = (int) std::min<int64_t>(std::min<int64_t>((2 * (int64_t) ctx->sm_count + rows - 1) / rows, n_kv / 256), 32);
+        if (nsplit < 1) nsplit = 1;
+    }
+    p.nsplit = nsplit;
+    p.chunk  = nsplit == 1 ? std::max<int64_t>(n_kv, 1) : ((n_kv + nsplit - 1) / nsplit + 31) / 32 * 32;
+    p.ws     = nullptr;
+    OPS_PROLOGUE(ctx);
+    if (nsplit > 1) {
+        if (b200_status st = b200_ensure(ctx, &ctx->fa_ws, &ctx->fa_ws_size, (size_t) rows * nsplit * (D + 2) * sizeof(float))) return st;
+        p.ws = (float *) ctx->fa_ws;
+    }
+    const dim3 grid((unsigned) rows, (unsigned) nsplit);
+    if (D == 64)       fa_kernel<2><<<grid, FA_WARPS * 32, 0, ctx->stream>>>(p);
+    else if (D == 128) fa_kernel<4><<<grid, FA_WARPS * 32, 0, ctx->stream>>>(p);
+    else               fa_kernel<8><<<grid, FA_WARPS * 32, 0, ctx->stream>>>(p);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    if (nsplit > 1) {
+        fa_combine_kernel<<<(unsigned) rows, std::min(D, 256), 0, ctx->stream>>>(p, D);
+        CU(cudaGetLastError());
+        ctx->launches++;
+    }
+    return B200_OK;
+}
+
+} // extern "C"

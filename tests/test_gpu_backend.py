@@ -105,6 +105,24 @@ def test_reference_conformance_harness_k7(pkg, op, min_tests):
     assert rc == 0, tail
 
 
+@pytest.mark.parametrize("op,min_tests", [("RMS_NORM", 4), ("GET_ROWS", 20), ("ROPE", 40), ("SET_ROWS", 8), ("CPY", 20), ("CONT", 8), ("DUP", 4),
+                                          ("FLASH_ATTN_EXT", 100)])
+def test_reference_conformance_harness_f3(pkg, op, min_tests):
+    """SURVEY 8(f) rank 3, first slice: the reference's own cases (tests/test-backend-ops.cpp) for the ops between the matmuls of a
+    decode graph, each compared with ggml-cpu by the harness's own NMSE bar; what supports_op declines (other types, mrope,
+    head sizes outside 64 / 128 / 256) is reported 'not supported' and does not count"""
+    if not have_ref() or not (REF_DIR / "test-backend-ops").exists():
+        pytest.skip("oracle/_ref/test-backend-ops not built")
+    rc, out = run_tbo(pkg, "test", "-b", "B2000", "-o", op, timeout=1500)
+    tail = "\n".join(out.splitlines()[-25:])
+    m = re.search(r"(\d+)/(\d+) tests passed", out)
+    assert m, tail
+    failed = [ln for ln in out.splitlines() if "FAIL" in ln][:10]
+    assert m.group(1) == m.group(2), "\n".join(failed) + "\n" + tail
+    assert int(m.group(2)) >= min_tests, tail
+    assert rc == 0, tail
+
+
 def run_tbo(pkg, *args, timeout=900):
     env = dict(os.environ, GGML_BACKEND_PATH=str(pkg.BACKEND_PATH))
     p = subprocess.run([str(REF_DIR / "test-backend-ops"), *args], env=env, capture_output=True, text=True, timeout=timeout)

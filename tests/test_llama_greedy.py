@@ -168,3 +168,49 @@ def test_greedy_default_kernels_teacher_forced(pkg, tmp_path, tname, arith):
     for i in flips(got):   # a different argmax is only acceptable as a near-tie: both candidates within the noise of each other
         assert cpu["margins"][i] <= 2.0 * n_ref and got["deficits"][i] <= 2.0 * n_ref, (i, cpu["margins"][i], got["deficits"][i], report)
     assert len(flips(got)) <= max(2, 2 * len(flips(alt))), report
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tname", TYPES)
+def test_greedy_whole_graph_on_device(pkg, tmp_path, tname):
+    """with GET_ROWS / RMS_NORM / ROPE / SET_ROWS / CPY / FLASH_ATTN_EXT on the device (csrc/ops.cu) the KV cache
+    is offloaded (offload_kqv) and the whole token step is one scheduler split on this backend instead of one per MUL_MAT. The
+    attention arithmetic now differs from ggml-cpu's by design (ggml-cpu accumulates V in fp16, ops.cpp:8102-8123; the device kernel
+    in fp32), so the comparison is teacher-forced against ggml-cpu x64 running the same flash-attention graph, and the yardstick is
+    again the reference's own spread: its AVX2 build on the same graph, and its x64 build with the non-flash attention graph."""
+    _need_harness()
+    _skip_type(tname)
+    prefix = tmp_path / f"parity_{tname}"
+    _gen(prefix, tname)
+    n_gen = int(os.environ.get("B200_GREEDY_TOKENS", "256"))
+    cpu = _decode(prefix, "file", [CPU_LIB], gen=n_gen, extra=["--fa"])
+    forced = _force_file(tmp_path, cpu["tokens"])
+    alt = _decode(prefix, "file", [REF_DIR / "libggml-cpu-haswell.so"], gen=n_gen, extra=["--fa", "--force", forced])
+    nofa = _decode(prefix, "file", [CPU_LIB], gen=n_gen, extra=["--force", forced])
+    got = _decode(prefix, "file", [CPU_LIB, pkg.BACKEND_PATH], ngl=99, gen=n_gen, extra=["--fa", "--kqv", "--force", forced])
+    off = _decode(prefix, "file", [CPU_LIB, pkg.BACKEND_PATH], ngl=99, gen=n_gen, extra=["--fa", "--kqv", "--force", forced], env=_env(GGML_B200_F3=0))
+
+    def noise(r):
+        return max(abs(a - b) for a, b in zip(cpu["margins"], r["margins"]))
+
+    def flips(r):
+        return [i for i, (a, b) in enumerate(zip(cpu["tokens"], r["tokens"])) if a != b]
+    n_ref = max(noise(alt), noise(nofa))
+    report = {"type": tname, "mode": "whole graph on the device (f3 ops, offload_kqv, flash attention), teacher-forced by ggml-cpu x64 + flash attention",
+              "n_gen": n_gen, "noise_ref_avx2_vs_x64": noise(alt), "noise_ref_nonflash_vs_flash": noise(nofa), "noise_b200_vs_x64": noise(got),
+              "argmax_flips_ref_avx2": len(flips(alt)), "argmax_flips_ref_nonflash": len(flips(nofa)), "argmax_flips_b200": len(flips(got)),
+              "graph_splits_b200": got["graph_splits"], "graph_splits_b200_matmuls_only": off["graph_splits"],
+              "gen_s_cpu": cpu["gen_s"], "gen_s_b200": got["gen_s"], "gen_s_b200_matmuls_only": off["gen_s"],
+              "prompt_s_cpu": cpu["prompt_s"], "prompt_s_b200": got["prompt_s"], "prompt_s_b200_matmuls_only": off["prompt_s"]}
+    ref_cuda = REF_DIR / "libggml-cuda.so"
+    if ref_cuda.exists():   # the reference's CUDA backend (built for sm_100 by oracle/Makefile `cuda`) on the same model and flags
+        rc = _decode(prefix, "file", [CPU_LIB, ref_cuda], ngl=99, gen=n_gen, extra=["--fa", "--kqv", "--force", forced])
+        report.update({"gen_s_ref_cuda": rc["gen_s"], "prompt_s_ref_cuda": rc["prompt_s"], "graph_splits_ref_cuda": rc["graph_splits"],
+                       "noise_ref_cuda_vs_x64": noise(rc), "argmax_flips_ref_cuda": len(flips(rc))})
+        n_ref = max(n_ref, noise(rc))
+    _report(f"greedy_device_{tname}.json", report)
+    assert got["graph_splits"] < off["graph_splits"], report
+    assert got["graph_splits"] <= 2, report
+    assert noise(got) <= 2.0 * n_ref, report
+    for i in flips(got):
+        assert cpu["margins"][i] <= 2.0 * n_ref and got["deficits"][i] <= 2.0 * n_ref, (i, cpu["margins"][i], got["deficits"][i], report)
