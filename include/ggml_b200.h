@@ -372,6 +372,12 @@ typedef struct {
 B200_API int          b200_rms_norm_supported(const b200_tensor * x, const b200_tensor * dst);
 B200_API b200_status  b200_rms_norm(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * dst, float eps);
 
+/* RMS_NORM followed by the MUL with the norm weight (build_norm, src/llama-graph.cpp; ggml-cuda fuses the same pair:
+ * ggml_cuda_op_rms_norm_fused, ggml-cuda.cu:3360-3380): dst = (x * scale) * w, both products rounded as the two nodes would;
+ * w F32 with w->ne[0] == x->ne[0], its other dimensions broadcast */
+B200_API int          b200_rms_norm_mul_supported(const b200_tensor * x, const b200_tensor * w, const b200_tensor * dst);
+B200_API b200_status  b200_rms_norm_mul(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * w, const b200_tensor * dst, float eps);
+
 /* GGML_OP_GET_ROWS (ggml-cpu/ops.cpp ggml_compute_forward_get_rows; ggml-cuda/getrows.cu): dst[:, i, j, k] = row ids[i, j, k] of
  * src0[:, :, j, k] as F32; src0 F32, F16 or one of the five quantized formats (dequantize_row_<type>, ggml-quants.c); ids I32 */
 B200_API int          b200_get_rows_supported(const b200_tensor * src0, const b200_tensor * ids, const b200_tensor * dst);
@@ -395,6 +401,17 @@ B200_API b200_status  b200_rope(b200_ctx * ctx, const b200_tensor * x, const b20
  * src F32, dst F32 or F16 (the KV cache write of llama_kv_cache::cpy_k / cpy_v), idx I64 or I32 */
 B200_API int          b200_set_rows_supported(const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst);
 B200_API b200_status  b200_set_rows(b200_ctx * ctx, const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst);
+
+/* The attention inputs of one layer in one launch (the reference fuses ROPE + VIEW + SET_ROWS: ggml-cuda.cu:3300-3330): ROPE(q) into
+ * q_dst, ROPE(k) into k_dst AND - as SET_ROWS(k_cache, k_dst seen as [n_embd_k_gqa, n_tokens], k_idx) would - into the cache rows, and
+ * SET_ROWS(v_cache, v, v_idx). Same results as the four nodes one after the other (build_attn, src/llama-graph.cpp:1593-1606). */
+B200_API int          b200_attn_prep_supported(const b200_tensor * q, const b200_tensor * q_dst, const b200_tensor * k, const b200_tensor * k_dst,
+                                               const b200_tensor * pos, const b200_tensor * freq_factors, const b200_rope_params * rp,
+                                               const b200_tensor * k_idx, const b200_tensor * k_cache, const b200_tensor * v, const b200_tensor * v_idx,
+                                               const b200_tensor * v_cache);
+B200_API b200_status  b200_attn_prep(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * q_dst, const b200_tensor * k, const b200_tensor * k_dst,
+                                     const b200_tensor * pos, const b200_tensor * freq_factors, const b200_rope_params * rp, const b200_tensor * k_idx,
+                                     const b200_tensor * k_cache, const b200_tensor * v, const b200_tensor * v_idx, const b200_tensor * v_cache);
 
 /* GGML_OP_CPY / CONT / DUP (ggml-cpu/ops.cpp ggml_compute_forward_dup; ggml-cuda/cpy.cu): element e of src (any strides) to
  * element e of dst (any strides, same number of elements), F32 / F16 in any combination (F32 -> F16 rounds to nearest even) */

@@ -218,6 +218,7 @@ int cmd_run(int argc, char ** argv) {
     int ngl = 0, n_prompt = 64, n_gen = 256, n_threads = 0, n_split = 3, n_batch = 512, n_ubatch = 512;
     uint64_t seed = 5;
     bool quiet = true, mmap = true, offload_kqv = false, flash_attn = false;
+    int n_warm = 0;
     std::string force_path;   // teacher forcing: a file of token ids; token i of it is fed after step i instead of this run's own argmax
     for (int i = 0; i < argc; i++) {
         const std::string a = argv[i];
@@ -236,6 +237,7 @@ int cmd_run(int argc, char ** argv) {
         else if (a == "--verbose") quiet = false;
         else if (a == "--no-mmap") mmap = false;
         else if (a == "--force") force_path = val();
+        else if (a == "--warmup") n_warm = atoi(val());   // untimed: the prompt + this many tokens first, then the cache is cleared (llama-bench's warmup run)
         else if (a == "--kqv") offload_kqv = true;     // KV cache and attention on the device of the layer
         else if (a == "--fa") flash_attn = true;       // GGML_OP_FLASH_ATTN_EXT instead of MUL_MAT / SOFT_MAX / MUL_MAT
     }
@@ -322,8 +324,18 @@ int cmd_run(int argc, char ** argv) {
         if (!forced.empty()) deficits.push_back(b1 - lg[forced[margins.size() - 1]]);
         return (llama_token) best;
     };
+    if (n_warm > 0) {
+        if (llama_decode(ctx, llama_batch_get_one(toks.data(), (int32_t) toks.size())) != 0) { fprintf(stderr, "llama_decode(warmup prompt) failed\n"); return 1; }
+        llama_token w = toks[0];
+        for (int i = 0; i < n_warm; i++) {
+            if (llama_decode(ctx, llama_batch_get_one(&w, 1)) != 0) { fprintf(stderr, "llama_decode(warmup token) failed\n"); return 1; }
+        }
+        llama_synchronize(ctx);
+        llama_memory_clear(llama_get_memory(ctx), true);
+    }
     const auto t0 = std::chrono::steady_clock::now();
     if (llama_decode(ctx, llama_batch_get_one(toks.data(), (int32_t) toks.size())) != 0) { fprintf(stderr, "llama_decode(prompt) failed\n"); return 1; }
+    llama_synchronize(ctx);   // device backends return from llama_decode before the work is done
     const double prompt_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     llama_token cur = pick();
     out.push_back(cur);

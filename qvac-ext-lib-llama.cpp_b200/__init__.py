@@ -38,7 +38,7 @@ EXPORTS = [
     "b200_mul_mat_fused_supported", "b200_mul_mat_fused", "b200_mul_mat_id_fused_supported", "b200_mul_mat_id_fused",
     "b200_glu", "b200_add", "b200_mul", "b200_add_id",
     "b200_mul_mat_noalloc", "b200_mul_mat_noalloc_max_units",
-    "b200_rms_norm_supported", "b200_rms_norm", "b200_get_rows_supported", "b200_get_rows", "b200_rope_supported", "b200_rope",
+    "b200_rms_norm_supported", "b200_rms_norm", "b200_rms_norm_mul_supported", "b200_rms_norm_mul", "b200_attn_prep_supported", "b200_attn_prep", "b200_get_rows_supported", "b200_get_rows", "b200_rope_supported", "b200_rope",
     "b200_set_rows_supported", "b200_set_rows", "b200_cpy_supported", "b200_cpy", "b200_flash_attn_ext_supported", "b200_flash_attn_ext",
 ]
 
@@ -190,6 +190,11 @@ def lib() -> C.CDLL:
         tp = C.POINTER(Tensor)
         L.b200_rms_norm_supported.argtypes = [tp, tp]
         L.b200_rms_norm.argtypes = [vp, tp, tp, C.c_float]
+        L.b200_rms_norm_mul_supported.argtypes = [tp, tp, tp]
+        L.b200_rms_norm_mul.argtypes = [vp, tp, tp, tp, C.c_float]
+        rpp = C.POINTER(RopeParams)
+        L.b200_attn_prep_supported.argtypes = [tp, tp, tp, tp, tp, tp, rpp, tp, tp, tp, tp, tp]
+        L.b200_attn_prep.argtypes = [vp, tp, tp, tp, tp, tp, tp, rpp, tp, tp, tp, tp, tp]
         L.b200_get_rows_supported.argtypes = [tp, tp, tp]
         L.b200_get_rows.argtypes = [vp, tp, tp, tp]
         L.b200_rope_supported.argtypes = [tp, tp, tp, tp, C.POINTER(RopeParams)]
@@ -497,6 +502,24 @@ class Context:
         out = self.torch.empty(x.shape, dtype=self.torch.float32, device=x.device) if out is None else out
         check(lib().b200_rms_norm(self.h, Tensor.of(x), Tensor.of(out), eps), "b200_rms_norm")
         return out
+
+    def rms_norm_mul(self, x, w, eps=1e-6):
+        """RMS_NORM followed by MUL with the per-channel weight w (broadcast over rows), one launch"""
+        out = self.torch.empty(x.shape, dtype=self.torch.float32, device=x.device)
+        check(lib().b200_rms_norm_mul(self.h, Tensor.of(x), Tensor.of(w), Tensor.of(out), eps), "b200_rms_norm_mul")
+        return out
+
+    def attn_prep(self, q, k, pos, k_cache, k_idx, v, v_cache, v_idx, n_dims, mode=0, freq_factors=None, **kw):
+        """ROPE(q), ROPE(k) + SET_ROWS(k_cache), SET_ROWS(v_cache) in one launch; returns (rope(q), rope(k)). q [1, n_tok, n_head, D],
+        k [1, n_tok, n_head_kv, D], v [n_tok, n_head_kv * D], caches [n_ctx, n_head_kv * D] float16 / float32"""
+        qo = self.torch.empty(q.shape, dtype=self.torch.float32, device=q.device)
+        ko = self.torch.empty(k.shape, dtype=self.torch.float32, device=k.device)
+        rp = RopeParams(n_dims, mode, kw.get("n_ctx_orig", 0), kw.get("freq_base", 10000.0), kw.get("freq_scale", 1.0), kw.get("ext_factor", 0.0),
+                        kw.get("attn_factor", 1.0), kw.get("beta_fast", 32.0), kw.get("beta_slow", 1.0))
+        check(lib().b200_attn_prep(self.h, Tensor.of(q), Tensor.of(qo), Tensor.of(k), Tensor.of(ko), Tensor.of(pos),
+                                   None if freq_factors is None else Tensor.of(freq_factors), rp, Tensor.of(k_idx), Tensor.of(k_cache), Tensor.of(v),
+                                   Tensor.of(v_idx), Tensor.of(v_cache)), "b200_attn_prep")
+        return qo, ko
 
     def get_rows(self, src0, ids, out=None):
         """GGML_OP_GET_ROWS: src0 a torch tensor [.., n_rows, K] (float32 / float16) or a Tensor (quantized); ids int32 [.., n_ids]"""

@@ -621,7 +621,8 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
             continue;
         }
         mv_cfg  cfg;
-        const bool lean = !ep && (ctx->split.n_ranks <= 1 || (ctx->ll_on && !ctx->split_deferred)) && !(ctx->dbg & 1) && mv_lean_type(type);
+        // the lean kernel takes a bias-only epilogue (MUL_MAT + ADD) on one device; GLU pairs stay on mv_fast_kernel's EPI instantiation
+        const bool lean = (!ep || (ep->glu < 0 && ctx->split.n_ranks <= 1 && nc == 1)) && (ctx->split.n_ranks <= 1 || (ctx->ll_on && !ctx->split_deferred)) && !(ctx->dbg & 1) && mv_lean_type(type);
         while (nc >= 1 && !pick_mv_cfg(ctx, type, U, nc, &cfg, lean && nc <= MV_LEAN_MAX_COLS)) nc--;
         if (nc < 1) return fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
         for (int o0 = 0; o0 < n_ops; o0 += MV_MAX_MATS) {

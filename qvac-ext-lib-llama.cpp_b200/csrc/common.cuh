@@ -43,6 +43,12 @@ constexpr int ACT_KIND_Q8_0 = 0;
 constexpr int ACT_KIND_Q8_K = 1;
 __host__ __device__ constexpr int act_kind_for(int type) { return type_is_k(type) ? ACT_KIND_Q8_K : ACT_KIND_Q8_0; }
 
+// programmatic dependent launch: the next kernel of the stream may be scheduled now (it parks in its own griddepcontrol.wait), and
+// this one must not touch memory before the previous kernel has completed. No-ops when the launch did not carry the attribute.
+__device__ __forceinline__ void pdl_prologue() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
 __device__ __forceinline__ float half_bits_to_float(uint16_t h) { return __half2float(__ushort_as_half(h)); }
 
 __device__ __forceinline__ int dp4a_ss(int a, int b, int c) { return __dp4a(a, b, c); }

@@ -12,6 +12,7 @@ namespace b200 {
 __global__ void __launch_bounds__(256) glu_kernel(int op, float alpha, float limit, const float * __restrict__ x, int64_t x_rs,
                                                   const float * __restrict__ g, int64_t g_rs, float * __restrict__ dst, int64_t d_rs, int64_t nc,
                                                   int64_t total) {
+    pdl_prologue();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
         const int64_t r = i / nc, c = i - r * nc;
         dst[r * d_rs + c] = glu_apply(op, x[r * x_rs + c], g[r * g_rs + c], alpha, limit);
@@ -27,6 +28,7 @@ struct AddParams {
 // no __restrict__: ggml_add_inplace makes dst alias src0 (element for element, which this kernel tolerates)
 template <bool MUL>
 __global__ void __launch_bounds__(256) add_kernel(const AddParams p, const float * a, const float * b, float * dst, int64_t total) {
+    pdl_prologue();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t r = i;
         const int64_t i0 = r % p.ne[0]; r /= p.ne[0];
@@ -43,6 +45,7 @@ __global__ void __launch_bounds__(256) add_kernel(const AddParams p, const float
 __global__ void __launch_bounds__(256) add_id_kernel(const float * a, int64_t a_s1, int64_t a_s2, const float * __restrict__ bias, int64_t b_s1,
                                                      int64_t n_as, const int32_t * __restrict__ ids, int64_t ids_s1, float * dst, int64_t d_s1,
                                                      int64_t d_s2, int64_t M, int64_t n_used, int64_t total) {
+    pdl_prologue();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t r = i;
         const int64_t m = r % M; r /= M;
@@ -77,9 +80,8 @@ b200_status b200_glu(b200_ctx * ctx, int glu_op, float alpha, float limit, const
     if (e != cudaSuccess) return FAIL_CUDA(e);
     const int64_t total = nc * nrows;
     if (b200_status fst = b200_split_flush(ctx)) return fst;  // the inputs may be a dst whose remote slices are still in flight
-    glu_kernel<<<grid_for(ctx, total), 256, 0, ctx->stream>>>(glu_op, alpha, limit, gate, (int64_t) (gate_nb1 / 4), up, (int64_t) (up_nb1 / 4), dst,
-                                                              (int64_t) (dst_nb1 / 4), nc, total);
-    e = cudaGetLastError();
+    e = b200_launch(ctx, glu_kernel, dim3(grid_for(ctx, total)), dim3(256), 0, glu_op, alpha, limit, gate, (int64_t) (gate_nb1 / 4), up, (int64_t) (up_nb1 / 4), dst,
+                    (int64_t) (dst_nb1 / 4), nc, total);
     if (e != cudaSuccess) return FAIL_CUDA(e);
     ctx->launches++;
     return B200_OK;
@@ -103,9 +105,8 @@ static b200_status binary_bcast(b200_ctx * ctx, bool mul, const int64_t * ne, co
     cudaError_t e = cudaSetDevice(ctx->device);
     if (e != cudaSuccess) return FAIL_CUDA(e);
     if (b200_status fst = b200_split_flush(ctx)) return fst;
-    if (mul) add_kernel<true><<<grid_for(ctx, total), 256, 0, ctx->stream>>>(p, a, b, dst, total);
-    else add_kernel<false><<<grid_for(ctx, total), 256, 0, ctx->stream>>>(p, a, b, dst, total);
-    e = cudaGetLastError();
+    e = mul ? b200_launch(ctx, add_kernel<true>, dim3(grid_for(ctx, total)), dim3(256), 0, p, a, b, dst, total)
+            : b200_launch(ctx, add_kernel<false>, dim3(grid_for(ctx, total)), dim3(256), 0, p, a, b, dst, total);
     if (e != cudaSuccess) return FAIL_CUDA(e);
     ctx->launches++;
     return B200_OK;
@@ -132,9 +133,8 @@ b200_status b200_add_id(b200_ctx * ctx, const float * a, size_t a_nb1, size_t a_
     cudaError_t e = cudaSetDevice(ctx->device);
     if (e != cudaSuccess) return FAIL_CUDA(e);
     if (b200_status fst = b200_split_flush(ctx)) return fst;
-    add_id_kernel<<<grid_for(ctx, total), 256, 0, ctx->stream>>>(a, (int64_t) (a_nb1 / 4), (int64_t) (a_nb2 / 4), bias, (int64_t) (bias_nb1 / 4), n_as, ids,
-                                                                 (int64_t) (ids_nb1 / 4), dst, (int64_t) (nb1 / 4), (int64_t) (nb2 / 4), M, n_used, total);
-    e = cudaGetLastError();
+    e = b200_launch(ctx, add_id_kernel, dim3(grid_for(ctx, total)), dim3(256), 0, a, (int64_t) (a_nb1 / 4), (int64_t) (a_nb2 / 4), bias, (int64_t) (bias_nb1 / 4), n_as,
+                    ids, (int64_t) (ids_nb1 / 4), dst, (int64_t) (nb1 / 4), (int64_t) (nb2 / 4), M, n_used, total);
     if (e != cudaSuccess) return FAIL_CUDA(e);
     ctx->launches++;
     return B200_OK;

@@ -24,6 +24,7 @@
 #include <array>
 #include <atomic>
 #include <cstring>
+#include <chrono>
 #include <map>
 #include <mutex>
 #include <string>
@@ -83,6 +84,14 @@ struct be_ctx {
     size_t     n_graphs    = 0;
     uint64_t   graph_clock = 0;
     uint64_t   graph_replays = 0, graph_captures = 0;
+    std::vector<char> done;                        // run_nodes: nodes already executed ahead of their position (hoisted into a fused launch)
+    bool       fuse_f3 = true;                     // GGML_B200_DISABLE_F3_FUSION=1: RMS_NORM+MUL, ROPE/SET_ROWS and the q/k/v hoist run node by node
+    // GGML_B200_TIMING=1: where a graph_compute goes (printed when the backend is freed)
+    bool       timing = false;
+    uint64_t   t_calls = 0, t_key_ns = 0, t_run_ns = 0, t_gpu_n = 0;
+    double     t_gpu_ms = 0;
+    void *     t_ev0 = nullptr, * t_ev1 = nullptr;
+    bool       t_pending = false;
 };
 
 ggml_backend_reg_t b200_reg();
@@ -386,6 +395,7 @@ bool fill_mul_mat_id(const ggml_tensor * op, b200_mul_mat_id_desc * d) {
 // ------------------------------------------------------------------------------------------------ backend (stream)
 
 const char * be_name(ggml_backend_t backend) { return ((be_ctx *) backend->context)->name.c_str(); }
+void timing_collect(be_ctx * c);
 void be_free(ggml_backend_t backend) {
     be_ctx * c = (be_ctx *) backend->context;
     for (int id = 0; id < B200_MAX_DEVICES; id++) {
@@ -400,6 +410,14 @@ void be_free(ggml_backend_t backend) {
     if (c->split_event) b200_event_destroy(c->device, c->split_event);
     if (c->copy_event) b200_event_destroy(c->device, c->copy_event);
     b200_ctx_synchronize(c->ctx);
+    if (c->timing) {
+        timing_collect(c);
+        fprintf(stderr, "ggml-b200 timing: %llu graph_compute calls; host per call: key %.1f us, launch %.1f us; device per call: %.1f us (%llu measured); "
+                "graph replays %llu, captures %llu\n", (unsigned long long) c->t_calls, c->t_calls ? c->t_key_ns / 1e3 / c->t_calls : 0.0,
+                c->t_calls ? c->t_run_ns / 1e3 / c->t_calls : 0.0, c->t_gpu_n ? c->t_gpu_ms * 1e3 / c->t_gpu_n : 0.0, (unsigned long long) c->t_gpu_n,
+                (unsigned long long) c->graph_replays, (unsigned long long) c->graph_captures);
+        if (c->t_ev0) { b200_event_destroy(c->device, c->t_ev0); b200_event_destroy(c->device, c->t_ev1); }
+    }
     for (auto & kv : c->graphs) for (auto & g : kv.second) b200_graph_destroy(g.exec);
     b200_ctx_destroy(c->ctx);
     delete c;
@@ -746,10 +764,60 @@ void run_f3(be_ctx * c, ggml_tensor * op) {
     }
 }
 
+// next node from `from` on that still has work to do (-1: none)
+int next_live(const be_ctx * c, const ggml_cgraph * cgraph, int from) {
+    for (int j = from; j < cgraph->n_nodes; j++) if (!c->done[j] && !is_noop(cgraph->nodes[j])) return j;
+    return -1;
+}
+
+// RMS_NORM at node i followed by MUL with a per-channel weight: one launch (build_norm's pair). Returns the number of nodes consumed.
+int try_fuse_norm_mul(be_ctx * c, ggml_cgraph * cgraph, int i) {
+    if (!c->fuse_f3 || i + 1 >= cgraph->n_nodes) return 0;
+    ggml_tensor * norm = cgraph->nodes[i], * mul = cgraph->nodes[i + 1];
+    if (mul->op != GGML_OP_MUL || c->done[i + 1] || !ggml_can_fuse(cgraph, i, { GGML_OP_RMS_NORM, GGML_OP_MUL })) return 0;
+    const ggml_tensor * w = mul->src[0] == norm ? mul->src[1] : (mul->src[1] == norm ? mul->src[0] : nullptr);
+    if (!w || w == norm || !ggml_are_same_shape(mul, norm)) return 0;
+    const ggml_tensor * x = norm->src[0];
+    if (ranges_overlap(mul, w) || (ranges_overlap(mul, x) && mul->data != x->data)) return 0;
+    const b200_tensor bx = as_b200(x), bw = as_b200(w), bd = as_b200(mul);
+    if (!b200_rms_norm_mul_supported(&bx, &bw, &bd)) return 0;
+    CHECK_RUN(c, b200_rms_norm_mul(c->ctx, &bx, &bw, &bd, ggml_get_op_params_f32(norm, 0)));
+    return 2;
+}
+
+// ROPE(q) at node i, then - as the next nodes with work - ROPE(k), SET_ROWS(k cache <- rope(k)), SET_ROWS(v cache <- v): the attention
+// inputs of a layer as build_attn lays them out (src/llama-graph.cpp:1593-1606) in one launch. Marks the three followers done.
+bool try_fuse_attn_prep(be_ctx * c, ggml_cgraph * cgraph, int i) {
+    if (!c->fuse_f3) return false;
+    ggml_tensor * rq = cgraph->nodes[i];
+    const int j1 = next_live(c, cgraph, i + 1), j2 = j1 < 0 ? -1 : next_live(c, cgraph, j1 + 1), j3 = j2 < 0 ? -1 : next_live(c, cgraph, j2 + 1);
+    if (j3 < 0) return false;
+    ggml_tensor * rk = cgraph->nodes[j1], * sk = cgraph->nodes[j2], * sv = cgraph->nodes[j3];
+    if (rk->op != GGML_OP_ROPE || sk->op != GGML_OP_SET_ROWS || sv->op != GGML_OP_SET_ROWS) return false;
+    if (memcmp(rq->op_params, rk->op_params, sizeof(rq->op_params)) != 0 || rq->src[1] != rk->src[1] || rq->src[2] != rk->src[2]) return false;
+    const ggml_tensor * ks = sk->src[0];   // must be rope(k)'s output seen as [n_embd_k_gqa, n_tokens]
+    if (!ks || ks->data != rk->data || ks->type != GGML_TYPE_F32 || ks->ne[0] != rk->ne[0] * rk->ne[1] || ks->ne[1] != rk->ne[2] || ks->ne[2] != 1 ||
+        ks->ne[3] != 1 || ks->nb[1] != rk->nb[2] || rk->ne[3] != 1) return false;
+    const ggml_tensor * vs = sv->src[0];
+    if (!vs || ranges_overlap(vs, rq) || ranges_overlap(vs, rk) || ranges_overlap(rk->src[0], rq) || ranges_overlap(rq, rk)) return false;
+    if (ranges_overlap(sk, sv) || ranges_overlap(sk, rq) || ranges_overlap(sk, rk) || ranges_overlap(sv, rq) || ranges_overlap(sv, rk)) return false;
+    if (ranges_overlap(sk, rq->src[0]) || ranges_overlap(sk, rk->src[0]) || ranges_overlap(sv, rq->src[0]) || ranges_overlap(sv, rk->src[0]) || ranges_overlap(sk, vs)) return false;
+    const b200_tensor q = as_b200(rq->src[0]), qd = as_b200(rq), k = as_b200(rk->src[0]), kd = as_b200(rk), pos = as_b200(rq->src[1]);
+    b200_tensor ff;
+    if (rq->src[2]) ff = as_b200(rq->src[2]);
+    const b200_tensor ki = as_b200(sk->src[1]), kc = as_b200(sk), v = as_b200(vs), vi = as_b200(sv->src[1]), vc = as_b200(sv);
+    const b200_rope_params rp = rope_params_of(rq);
+    if (!b200_attn_prep_supported(&q, &qd, &k, &kd, &pos, rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc)) return false;
+    CHECK_RUN(c, b200_attn_prep(c->ctx, &q, &qd, &k, &kd, &pos, rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc));
+    c->done[j1] = c->done[j2] = c->done[j3] = 1;
+    return true;
+}
+
 ggml_status run_nodes(be_ctx * c, ggml_cgraph * cgraph) {
+    c->done.assign((size_t) cgraph->n_nodes, 0);
     for (int i = 0; i < cgraph->n_nodes; i++) {
         ggml_tensor * node = cgraph->nodes[i];
-        if (is_noop(node)) continue;  // as ggml-cuda.cu:3333-3335
+        if (is_noop(node) || c->done[i]) continue;  // as ggml-cuda.cu:3333-3335; done: ran ahead of its position in a fused launch
         if (c->fuse_epilogue && (node->op == GGML_OP_MUL_MAT || node->op == GGML_OP_MUL_MAT_ID)) {
             const int fused = try_fuse_epilogue(c, cgraph, i);
             if (fused > 0) {
@@ -774,23 +842,41 @@ ggml_status run_nodes(be_ctx * c, ggml_cgraph * cgraph) {
             w[0] = node->src[0]->data;
             o[0] = (float *) node->data;
             int n = 1;
-            // peephole: consecutive MUL_MATs reading the same src1 (q/k/v, gate/up) share one activation quantization
-            // and one launch; the reference re-quantizes per op (mmvq.cu:667-674)
-            while (c->fuse && n < 4 && i + n < cgraph->n_nodes) {
-                ggml_tensor * nx = cgraph->nodes[i + n];
-                if (nx->op != GGML_OP_MUL_MAT || nx->src[1] != node->src[1] || !fill_mul_mat(nx, &descs[n])) break;
-                if (nx->src[0]->buffer && buft_is_split(nx->src[0]->buffer->buft)) break;
-                if (descs[n].type != descs[0].type || descs[n].ne00 != descs[0].ne00 || descs[0].ne12 != 1 || descs[0].ne13 != 1) break;
-                bool clash = ranges_overlap(nx, node->src[1]);
-                for (int j = 0; j < n; j++) clash = clash || ranges_overlap(nx, cgraph->nodes[i + j]) || nx->src[0] == cgraph->nodes[i + j];
-                if (clash) break;
-                w[n] = nx->src[0]->data;
-                o[n] = (float *) nx->data;
-                n++;
+            // peephole: MUL_MATs reading the same src1 (q/k/v, gate/up) share one activation quantization and one launch; the
+            // reference re-quantizes per op (mmvq.cu:667-674). llama's graphs put ROPE(q) and reshapes between the three attention
+            // projections (src/llama-graph.cpp:1593-1595), so the followers are looked for in a window and run AHEAD of their position
+            // - allowed when nothing that stays in between reads or writes what a hoisted MUL_MAT writes, or writes src1
+            int idx[4] = { i, -1, -1, -1 };
+            const ggml_tensor * between[16];
+            int n_between = 0;
+            const int window = c->fuse_f3 ? 12 : 1;
+            for (int j = i + 1; c->fuse && n < 4 && j < cgraph->n_nodes && j <= i + window && n_between < 16; j++) {
+                ggml_tensor * nx = cgraph->nodes[j];
+                if (c->done[j] || is_noop(nx)) continue;
+                bool take = nx->op == GGML_OP_MUL_MAT && nx->src[1] == node->src[1] && nx->src[0]->op == GGML_OP_NONE && fill_mul_mat(nx, &descs[n]) &&
+                            !(nx->src[0]->buffer && buft_is_split(nx->src[0]->buffer->buft)) && descs[n].type == descs[0].type &&
+                            descs[n].ne00 == descs[0].ne00 && descs[0].ne12 == 1 && descs[0].ne13 == 1;
+                if (take) {
+                    bool clash = ranges_overlap(nx, node->src[1]);
+                    for (int k = 0; k < n; k++) clash = clash || ranges_overlap(nx, cgraph->nodes[idx[k]]) || nx->src[0] == cgraph->nodes[idx[k]];
+                    for (int b = 0; b < n_between && !clash; b++) {
+                        clash = ranges_overlap(nx, between[b]);
+                        for (int k = 0; k < GGML_MAX_SRC && !clash; k++) clash = between[b]->src[k] && ranges_overlap(nx, between[b]->src[k]);
+                    }
+                    take = !clash;
+                }
+                if (take) {
+                    w[n] = nx->src[0]->data;
+                    o[n] = (float *) nx->data;
+                    idx[n++] = j;
+                    continue;
+                }
+                if (ranges_overlap(nx, node->src[1])) break;   // src1 changes here: nothing behind it may be hoisted
+                between[n_between++] = nx;
             }
             if (n == 1) CHECK_RUN(c, b200_mul_mat(c->ctx, &descs[0], w[0], (const float *) node->src[1]->data, o[0]));
             else CHECK_RUN(c, b200_mul_mat_shared_src1(c->ctx, n, descs, w, (const float *) node->src[1]->data, o));
-            i += n - 1;
+            for (int k = 1; k < n; k++) c->done[idx[k]] = 1;
         } else if (node->op == GGML_OP_MUL_MAT_ID) {
             b200_mul_mat_id_desc d;
             if (!fill_mul_mat_id(node, &d)) {
@@ -806,6 +892,12 @@ ggml_status run_nodes(be_ctx * c, ggml_cgraph * cgraph) {
         } else if (node->op == GGML_OP_ADD_ID && add_id_ok(node)) {
             run_add_id(c, node);
         } else if (is_f3_op(node->op) && f3_ok(node)) {
+            if (node->op == GGML_OP_RMS_NORM) {
+                const int fused = try_fuse_norm_mul(c, cgraph, i);
+                if (fused > 0) { i += fused - 1; continue; }
+            } else if (node->op == GGML_OP_ROPE && try_fuse_attn_prep(c, cgraph, i)) {
+                continue;
+            }
             run_f3(c, node);
         } else {
             GGML_LOG_ERROR("ggml-b200: op %s is not implemented by this backend (%s)\n", ggml_op_name(node->op), node->name);
@@ -870,21 +962,53 @@ void evict_graphs(be_ctx * c) {  // bounded cache: drop the least recently used 
 std::atomic<uint64_t> g_graph_replays{ 0 };  // proc address "ggml_backend_b200_graph_replays" (tests, bench.py)
 uint64_t graph_replays() { return g_graph_replays.load(std::memory_order_relaxed); }
 
+ggml_status be_graph_compute_impl(ggml_backend_t backend, ggml_cgraph * cgraph, uint64_t * key_ns);
+
+uint64_t now_ns() { return (uint64_t) std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+// GGML_B200_TIMING=1: host time spent keying / launching and device time between two events around the launches of every
+// graph_compute (read back at the next call, when the caller has long synchronized)
+void timing_collect(be_ctx * c) {
+    if (!c->t_pending) return;
+    float ms = 0;
+    if (b200_event_synchronize(c->t_ev1) == B200_OK && b200_event_elapsed_ms(c->t_ev0, c->t_ev1, &ms) == B200_OK) { c->t_gpu_ms += ms; c->t_gpu_n++; }
+    c->t_pending = false;
+}
+
 ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
+    be_ctx * c = (be_ctx *) backend->context;
+    if (!c->timing) return be_graph_compute_impl(backend, cgraph, nullptr);
+    timing_collect(c);
+    if (!c->t_ev0) { CHECK(b200_event_create(c->device, &c->t_ev0)); CHECK(b200_event_create(c->device, &c->t_ev1)); }
+    const uint64_t t0 = now_ns();
+    uint64_t key_ns = 0;
+    CHECK(b200_event_record(c->ctx, c->t_ev0));
+    const ggml_status st = be_graph_compute_impl(backend, cgraph, &key_ns);
+    CHECK(b200_event_record(c->ctx, c->t_ev1));
+    c->t_pending = true;
+    c->t_calls++;
+    c->t_key_ns += key_ns;
+    c->t_run_ns += now_ns() - t0 - key_ns;
+    return st;
+}
+
+ggml_status be_graph_compute_impl(ggml_backend_t backend, ggml_cgraph * cgraph, uint64_t * key_ns) {
     be_ctx * c = (be_ctx *) backend->context;
     if (!c->use_graphs) return run_nodes(c, cgraph);
     static thread_local std::vector<uint64_t> key;
     int  n_run = 0;
     bool capturable = true;
+    const uint64_t tk0 = key_ns ? now_ns() : 0;
     graph_key(cgraph, key, &n_run, &capturable);
     if (!capturable || n_run < c->graph_min_nodes) return run_nodes(c, cgraph);
     auto & bucket = c->graphs[hash_key(key)];
+    if (key_ns) *key_ns = now_ns() - tk0;
     be_ctx::cached_graph * g = nullptr;
     for (auto & e : bucket) if (e.key == key) { g = &e; break; }
     if (!g) {
         if (c->n_graphs >= 1024) {
             evict_graphs(c);
-            return be_graph_compute(backend, cgraph);  // `bucket` may be gone
+            return be_graph_compute_impl(backend, cgraph, key_ns);  // `bucket` may be gone
         }
         bucket.emplace_back();
         g = &bucket.back();
@@ -896,6 +1020,7 @@ ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     if (g->exec) {
         CHECK(b200_graph_launch(c->ctx, g->exec));
         g_graph_replays.fetch_add(1, std::memory_order_relaxed);
+        c->graph_replays++;
         return GGML_STATUS_SUCCESS;
     }
     // first appearance: launched directly (this also sizes the scratch buffers and fills the weight-expansion cache, neither of
@@ -986,6 +1111,8 @@ ggml_backend_t dev_init_backend(ggml_backend_dev_t dev, const char *) {
     const char * ne = getenv("GGML_B200_DISABLE_EPILOGUE_FUSION");
     c->fuse_epilogue = c->fuse && !(ne && atoi(ne));
     c->weight_cache  = weight_cache;
+    if (const char * tm = getenv("GGML_B200_TIMING")) c->timing = atoi(tm) != 0;
+    if (const char * nf3 = getenv("GGML_B200_DISABLE_F3_FUSION")) c->fuse_f3 = atoi(nf3) == 0;
     const char * ng = getenv("GGML_B200_DISABLE_GRAPHS");
     c->use_graphs = !(ng && atoi(ng));
     if (const char * mn = getenv("GGML_B200_GRAPH_MIN_NODES")) c->graph_min_nodes = std::max(1, atoi(mn));

@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <unordered_map>
+#include <utility>
 
 b200_status b200_fail(b200_status st, const char * fmt, ...);
 
@@ -80,6 +81,23 @@ struct b200_ctx {
     int          moe_group_min = 2;            // MUL_MAT_ID: group by expert (tensor-core mat-vec) from this many pairs per expert on
                                                // average; 0 = never; GGML_B200_MOE_GROUP_MIN
 };
+
+// launch on the context's stream with programmatic stream serialization (ctx->pdl): kernels launched this way start with
+// pdl_prologue(), so that launch latency overlaps the previous kernel instead of adding to the dependent chain of a token step
+template <typename... KArgs, typename... Args>
+inline cudaError_t b200_launch(const b200_ctx * ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, Args &&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim          = grid;
+    cfg.blockDim         = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream           = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs    = attr;
+    cfg.numAttrs = ctx->pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
 
 // bumped whenever device memory the library may hold predictions / caches for is freed or rewritten
 uint64_t b200_mem_generation();

@@ -869,7 +869,9 @@ __device__ __forceinline__ void unit_dot2(uint32_t w0, uint32_t w1, uint32_t am,
     }
 }
 
-template <int TYPE, int NC, bool LL>   // LL: row split with the flagged-payload exchange (its own instantiation: the plain kernel keeps its registers)
+// LL: row split with the flagged-payload exchange (its own instantiation: the plain kernel keeps its registers). BIAS: the ADD of a
+// K7 epilogue without GLU (attn_output / ffn_down + residual in a decode graph): mat.bias[row] is added before the store
+template <int TYPE, int NC, bool LL, bool BIAS = false>
 __global__ void __launch_bounds__(32 * (MV_MAX_CONS + 1), 1)
 mv_lean_kernel(const __grid_constant__ MvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -1055,6 +1057,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
             }
             if (sub == 0 && lane_on && row < mat.M) {
                 float * a = mat.dst + (int64_t) c * mat.dst_cs + row;
+                if constexpr (BIAS) { if (mat.bias) v += mat.bias[row]; }
                 if (ll) ll_store(p.split, ep, a, v);
                 else *a = v;
             }
@@ -1112,7 +1115,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     }
 }
 
-template <int TYPE, int NC, bool LL>
+template <int TYPE, int NC, bool LL, bool BIAS = false>
 static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t smem, cudaStream_t st) {
     MvParams p = p_in;
     p.n_helpers = 0;
@@ -1124,9 +1127,9 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
@@ -1144,12 +1147,15 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
     }
     cfg.attrs    = attr;
     cfg.numAttrs = na;
-    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE, NC, LL>, p);
+    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE, NC, LL, BIAS>, p);
 }
 
 // the launch can take the lean kernel: one column, plain MUL_MAT, no exchange, no epilogue, an even ring
 template <int TYPE>
 static cudaError_t mv_lean_launch_n(int nc, const MvParams & p, int n_ctas, size_t smem, cudaStream_t st) {
+    for (int i = 0; i < p.n_mats; i++) {
+        if (p.mat[i].bias) return nc == 1 && p.split.n_ranks <= 1 ? mv_lean_launch_t<TYPE, 1, false, true>(p, n_ctas, smem, st) : cudaErrorInvalidValue;
+    }
     if (p.split.n_ranks > 1) {
         switch (nc) {
             case 1: return mv_lean_launch_t<TYPE, 1, true>(p, n_ctas, smem, st);
@@ -1172,7 +1178,7 @@ bool mv_lean_type(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE
 
 static bool mv_lean_ok(int type, int ncols, const MvParams & p, int n_pairs) {
     if (!mv_lean_type(type) || ncols < 1 || ncols > MV_LEAN_MAX_COLS || n_pairs != 1 || p.ids.ids || (p.split.n_ranks > 1 && !p.split.ll) || p.epi.glu || (p.n_stages & 1) || (p.dbg & 1)) return false;
-    for (int i = 0; i < p.n_mats; i++) if (p.mat[i].bias) return false;
+    for (int i = 0; i < p.n_mats; i++) if (p.mat[i].bias && (ncols != 1 || p.split.n_ranks > 1)) return false;
     return true;
 }
 

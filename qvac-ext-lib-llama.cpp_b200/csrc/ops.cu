@@ -35,24 +35,63 @@ T4 t4(const b200_tensor * t) {
     return r;
 }
 
-// ------------------------------------------------------------------------------------------------ RMS_NORM
-// y = x / sqrt(mean(x^2) + eps), one CTA per row (ggml-cpu sums in double; fp32 tree sums here: NMSE ~1e-13 apart)
-__global__ void __launch_bounds__(256) rms_norm_kernel(const char * x, T4 s, char * y, T4 d, float eps) {
-    const int64_t row = blockIdx.x;
-    const int64_t i1 = row % s.ne[1], i2 = (row / s.ne[1]) % s.ne[2], i3 = row / (s.ne[1] * s.ne[2]);
-    const float * xr = (const float *) (x + i1 * s.nb[1] + i2 * s.nb[2] + i3 * s.nb[3]);
-    float *       yr = (float *) (y + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
-    float sum = 0.0f;
-    for (int64_t i = threadIdx.x; i < s.ne[0]; i += blockDim.x) { const float v = xr[i]; sum += v * v; }
-    __shared__ float part[8];
-    sum = warp_sum(sum);
-    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = sum;
+// ------------------------------------------------------------------------------------------------ RMS_NORM (+ MUL)
+// y = x / sqrt(mean(x^2) + eps) [* w], one CTA per row (ggml-cpu sums in double; fp32 tree sums here: NMSE ~1e-13 apart). The MUL that
+// follows every norm of a transformer graph (the norm weight, broadcast over the rows: build_norm, src/llama-graph.cpp) rides along:
+// (x * scale) * w with both products rounded, bit for bit what the two nodes give one after the other.
+struct NormP {
+    T4 s, d, w;
+    const char * x, * wd;   // wd == nullptr: no MUL
+    char * y;
+    float eps;
+};
+__device__ __forceinline__ float block_sum(float v, float * part) {   // all threads get the sum; blockDim a multiple of 32, <= 1024
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = v;
     __syncthreads();
-    float tot = 0.0f;
+    const int nw = blockDim.x >> 5;
+    float t = (int) (threadIdx.x & 31) < nw ? part[threadIdx.x & 31] : 0.0f;
+    return warp_sum(t);
+}
+template <bool VEC>   // VEC: rows are 16-byte aligned, ne0 % 4 == 0 and a row fits the CTA's registers (4 float4 per thread)
+__global__ void __launch_bounds__(1024) rms_norm_kernel(const NormP p) {
+    __shared__ float part[32];
+    pdl_prologue();
+    const int64_t row = blockIdx.x;
+    const int64_t i1 = row % p.s.ne[1], i2 = (row / p.s.ne[1]) % p.s.ne[2], i3 = row / (p.s.ne[1] * p.s.ne[2]);
+    const char * xr = p.x + i1 * p.s.nb[1] + i2 * p.s.nb[2] + i3 * p.s.nb[3];
+    char *       yr = p.y + i1 * p.d.nb[1] + i2 * p.d.nb[2] + i3 * p.d.nb[3];
+    const char * wr = p.wd ? p.wd + (i1 % p.w.ne[1]) * p.w.nb[1] + (i2 % p.w.ne[2]) * p.w.nb[2] + (i3 % p.w.ne[3]) * p.w.nb[3] : nullptr;
+    const int64_t n = p.s.ne[0];
+    if constexpr (VEC) {
+        const int64_t n4 = n >> 2;
+        float4 v[4];
+        float sum = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 8; i++) tot += part[i];
-    const float scale = 1.0f / sqrtf(tot / (float) s.ne[0] + eps);
-    for (int64_t i = threadIdx.x; i < s.ne[0]; i += blockDim.x) yr[i] = xr[i] * scale;
+        for (int j = 0; j < 4; j++) {
+            const int64_t i = threadIdx.x + (int64_t) j * blockDim.x;
+            if (i < n4) { v[j] = ((const float4 *) xr)[i]; sum += v[j].x * v[j].x + v[j].y * v[j].y + v[j].z * v[j].z + v[j].w * v[j].w; }
+        }
+        const float scale = 1.0f / sqrtf(block_sum(sum, part) / (float) n + p.eps);
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int64_t i = threadIdx.x + (int64_t) j * blockDim.x;
+            if (i < n4) {
+                float4 o = make_float4(v[j].x * scale, v[j].y * scale, v[j].z * scale, v[j].w * scale);
+                if (wr) { const float4 w = ((const float4 *) wr)[i]; o.x *= w.x; o.y *= w.y; o.z *= w.z; o.w *= w.w; }
+                ((float4 *) yr)[i] = o;
+            }
+        }
+    } else {
+        float sum = 0.0f;
+        for (int64_t i = threadIdx.x; i < n; i += blockDim.x) { const float v = ((const float *) xr)[i]; sum += v * v; }
+        const float scale = 1.0f / sqrtf(block_sum(sum, part) / (float) n + p.eps);
+        for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
+            float o = ((const float *) xr)[i] * scale;
+            if (wr) o *= ((const float *) wr)[i % p.w.ne[0]];
+            ((float *) yr)[i] = o;
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ dequantization of one element
@@ -104,6 +143,7 @@ __device__ __forceinline__ float dequant_at(int type, const uint8_t * row, int64
 // dst[:, i10, i11, i12] = row ids[i10, i11, i12] of src0[:, :, i11, i12], as F32
 __global__ void __launch_bounds__(256) get_rows_kernel(int type, const char * src0, int64_t ne00, int64_t ne01, int64_t nb01, int64_t nb02, int64_t nb03,
                                                        const char * ids, T4 is, char * dst, int64_t nb1, int64_t nb2, int64_t nb3) {
+    pdl_prologue();
     const int64_t r = blockIdx.x;
     const int64_t i10 = r % is.ne[0], i11 = (r / is.ne[0]) % is.ne[1], i12 = r / (is.ne[0] * is.ne[1]);
     const int32_t row = *(const int32_t *) (ids + i10 * is.nb[0] + i11 * is.nb[1] + i12 * is.nb[2]);
@@ -127,23 +167,54 @@ struct RopeP {
     int   n_dims, neox;
     float theta_scale, freq_scale, ext_factor, attn_factor, corr0, corr1;
 };
-// one thread per rotated pair (or per pair of pass-through elements beyond n_dims) of one row (i1 = head, i2 = position, i3 = batch)
-__global__ void __launch_bounds__(256) rope_kernel(const char * x, T4 s, const int32_t * pos, const float * ff, char * y, T4 d, RopeP p) {
-    const int64_t row = blockIdx.x;
-    const int64_t i1 = row % s.ne[1], i2 = (row / s.ne[1]) % s.ne[2], i3 = row / (s.ne[1] * s.ne[2]);
-    const float * xr = (const float *) (x + i1 * s.nb[1] + i2 * s.nb[2] + i3 * s.nb[3]);
-    float *       yr = (float *) (y + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
-    const float   base = (float) pos[i2];
-    for (int64_t i0 = 2 * threadIdx.x; i0 < s.ne[0]; i0 += 2 * blockDim.x) {
+// where a rotated K row also goes (attn_prep_kernel): row idx[token] of the KV cache, at this head's channels, as F16 or F32 -
+// the SET_ROWS that follows ROPE(k) in build_attn (src/llama-graph.cpp:1604, llama_kv_cache::cpy_k)
+struct RowStore {
+    char *       base;      // nullptr: none
+    const char * idx;
+    int64_t      idx_nb0, row_nb, n_rows;
+    int          f16, i64;
+};
+struct RopeJob {
+    T4 s, d;
+    const char * x;
+    char * y;
+    const int32_t * pos;
+    const float * ff;
+    RowStore st;
+};
+template <typename OUT>
+__device__ __forceinline__ OUT cvt_out(float v);
+template <> __device__ __forceinline__ float cvt_out<float>(float v) { return v; }
+template <> __device__ __forceinline__ __half cvt_out<__half>(float v) { return __float2half_rn(v); }
+
+__device__ __forceinline__ int64_t load_idx(const char * p, int i64) { return i64 ? *(const int64_t *) p : (int64_t) *(const int32_t *) p; }
+
+// one CTA rotates row `row` (i1 = head, i2 = position, i3 = batch): one thread per pair, or per two pass-through channels beyond n_dims
+__device__ __forceinline__ void rope_row(const RopeJob & j, const RopeP & p, int64_t row) {
+    const int64_t i1 = row % j.s.ne[1], i2 = (row / j.s.ne[1]) % j.s.ne[2], i3 = row / (j.s.ne[1] * j.s.ne[2]);
+    const float * xr = (const float *) (j.x + i1 * j.s.nb[1] + i2 * j.s.nb[2] + i3 * j.s.nb[3]);
+    float *       yr = (float *) (j.y + i1 * j.d.nb[1] + i2 * j.d.nb[2] + i3 * j.d.nb[3]);
+    const float   base = (float) j.pos[i2];
+    char * sr = nullptr;   // the cache row of this token, this head's first channel
+    if (j.st.base) {
+        const int64_t r = load_idx(j.st.idx + i2 * j.st.idx_nb0, j.st.i64);
+        if (r >= 0 && r < j.st.n_rows) sr = j.st.base + r * j.st.row_nb + i1 * j.s.ne[0] * (j.st.f16 ? 2 : 4);
+    }
+    auto put = [&](int64_t i, float v) {
+        yr[i] = v;
+        if (sr) { if (j.st.f16) ((__half *) sr)[i] = __float2half_rn(v); else ((float *) sr)[i] = v; }
+    };
+    for (int64_t i0 = 2 * threadIdx.x; i0 < j.s.ne[0]; i0 += 2 * blockDim.x) {
         if (i0 >= p.n_dims) {   // channels beyond n_dims are copied
-            yr[i0] = xr[i0]; yr[i0 + 1] = xr[i0 + 1];
+            put(i0, xr[i0]); put(i0 + 1, xr[i0 + 1]);
             continue;
         }
         // theta_base of pair i0/2 as ggml_rope_cache_init forms it (ops.cpp:5549-5563): pos times theta_scale, i0/2 times over, each
         // product rounded - not powf, so that the angle is the reference's to the bit; then rope_yarn (ops.cpp:5532-5547)
         float tb = base;
-        for (int64_t j = 0; j < i0 / 2; j++) tb = __fmul_rn(tb, p.theta_scale);
-        const float theta_extrap = tb / (ff ? ff[i0 / 2] : 1.0f);
+        for (int64_t k = 0; k < i0 / 2; k++) tb = __fmul_rn(tb, p.theta_scale);
+        const float theta_extrap = tb / (j.ff ? j.ff[i0 / 2] : 1.0f);
         const float theta_interp = p.freq_scale * theta_extrap;
         float theta = theta_interp, mscale = p.attn_factor;
         if (p.ext_factor != 0.0f) {
@@ -155,26 +226,45 @@ __global__ void __launch_bounds__(256) rope_kernel(const char * x, T4 s, const i
         const float c = cosf(theta) * mscale, sn = sinf(theta) * mscale;
         const int64_t ia = p.neox ? i0 / 2 : i0, ib = p.neox ? i0 / 2 + p.n_dims / 2 : i0 + 1;
         const float x0 = xr[ia], x1 = xr[ib];
-        yr[ia] = x0 * c - x1 * sn;
-        yr[ib] = x0 * sn + x1 * c;
+        put(ia, x0 * c - x1 * sn);
+        put(ib, x0 * sn + x1 * c);
     }
+}
+__global__ void __launch_bounds__(256) rope_kernel(const RopeJob j, const RopeP p) {
+    pdl_prologue();
+    rope_row(j, p, blockIdx.x);
 }
 
 // ------------------------------------------------------------------------------------------------ SET_ROWS (F32 -> F32 / F16 rows by index)
-template <typename OUT>
-__device__ __forceinline__ OUT cvt_out(float v);
-template <> __device__ __forceinline__ float cvt_out<float>(float v) { return v; }
-template <> __device__ __forceinline__ __half cvt_out<__half>(float v) { return __float2half_rn(v); }
+struct SetRowsJob {
+    T4 s, is, d;
+    const char * src, * idx;
+    char * dst;
+    int f16, i64;
+};
+__device__ __forceinline__ void set_rows_row(const SetRowsJob & j, int64_t r) {
+    const int64_t i = r % j.s.ne[1], i02 = (r / j.s.ne[1]) % j.s.ne[2], i03 = r / (j.s.ne[1] * j.s.ne[2]);
+    const int64_t i1 = load_idx(j.idx + i * j.is.nb[0] + (i02 % j.is.ne[1]) * j.is.nb[1] + (i03 % j.is.ne[2]) * j.is.nb[2], j.i64);
+    if (i1 < 0 || i1 >= j.d.ne[1]) return;   // ggml-cpu asserts
+    const float * in = (const float *) (j.src + i * j.s.nb[1] + i02 * j.s.nb[2] + i03 * j.s.nb[3]);
+    char * out = j.dst + i1 * j.d.nb[1] + i02 * j.d.nb[2] + i03 * j.d.nb[3];
+    if (j.f16) { for (int64_t k = threadIdx.x; k < j.s.ne[0]; k += blockDim.x) ((__half *) out)[k] = __float2half_rn(in[k]); }
+    else       { for (int64_t k = threadIdx.x; k < j.s.ne[0]; k += blockDim.x) ((float *) out)[k] = in[k]; }
+}
+__global__ void __launch_bounds__(256) set_rows_kernel(const SetRowsJob j) {
+    pdl_prologue();
+    set_rows_row(j, blockIdx.x);
+}
 
-template <typename OUT, typename IDX>
-__global__ void __launch_bounds__(256) set_rows_kernel(const char * src, T4 s, const char * idx, T4 is, char * dst, T4 d) {
-    const int64_t r = blockIdx.x;
-    const int64_t i = r % s.ne[1], i02 = (r / s.ne[1]) % s.ne[2], i03 = r / (s.ne[1] * s.ne[2]);
-    const int64_t i1 = (int64_t) *(const IDX *) (idx + i * is.nb[0] + (i02 % is.ne[1]) * is.nb[1] + (i03 % is.ne[2]) * is.nb[2]);
-    if (i1 < 0 || i1 >= d.ne[1]) return;   // ggml-cpu asserts
-    const float * in = (const float *) (src + i * s.nb[1] + i02 * s.nb[2] + i03 * s.nb[3]);
-    OUT * out = (OUT *) (dst + i1 * d.nb[1] + i02 * d.nb[2] + i03 * d.nb[3]);
-    for (int64_t k = threadIdx.x; k < s.ne[0]; k += blockDim.x) out[k] = cvt_out<OUT>(in[k]);
+// ------------------------------------------------------------------------------------------------ attention inputs in one launch
+// ROPE(q), ROPE(k) + SET_ROWS(k cache), SET_ROWS(v cache): four nodes of every layer of a decode graph, independent of each other
+// once ROPE(k) stores its rows into the cache itself. CTAs [0, nq) rotate q rows, [nq, nq + nk) k rows, the rest copy v rows.
+__global__ void __launch_bounds__(256) attn_prep_kernel(const RopeJob q, const RopeJob k, const SetRowsJob v, const RopeP p, int nq, int nk) {
+    pdl_prologue();
+    const int b = blockIdx.x;
+    if (b < nq) rope_row(q, p, b);
+    else if (b < nq + nk) rope_row(k, p, b - nq);
+    else set_rows_row(v, b - nq - nk);
 }
 
 // ------------------------------------------------------------------------------------------------ CPY / CONT / DUP
@@ -185,6 +275,7 @@ template <> __device__ __forceinline__ float cvt_in<__half>(__half v) { return _
 
 template <typename IN, typename OUT>
 __global__ void __launch_bounds__(256) cpy_kernel(const char * src, T4 s, char * dst, T4 d, int64_t n) {
+    pdl_prologue();
     const int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
     int64_t r = e;
@@ -203,7 +294,7 @@ __global__ void __launch_bounds__(256) cpy_kernel(const char * src, T4 s, char *
 // One CTA per (query row, head, batch) x KV split; 8 warps stride over the KV positions of the split, four at a time (their K and V
 // rows are in flight together); a lane owns E consecutive channels of the head (DK = DV = 32 E), so a K or V row is one coalesced
 // 64 E-byte read per warp. Online softmax per warp in fp32 (ggml-cpu keeps the F16-V accumulator in fp16: ops.cpp:8102-8123; this
-// one is the more accurate side), warps merged through shared memory, KV splits merged by fa_combine_kernel. The heads of one GQA
+// one is the more accurate side), warps merged through shared memory, KV splits merged by whichever CTA of a row finishes last. The heads of one GQA
 // group read the same K/V rows out of L2. Decode-shaped: a wide prefill batch re-reads K/V per query row.
 struct FaP {
     T4 q, k, v, m, d;
@@ -214,7 +305,8 @@ struct FaP {
     uint32_t n_head_log2;
     int      nsplit;
     int64_t  chunk;
-    float *  ws;
+    float *  ws;       // partials of the KV splits: [row][split][2 + D] = running maximum, sum, accumulator
+    unsigned * cnt;    // arrivals per row; the CTA that completes a row merges its splits and puts the counter back to 0
 };
 constexpr int FA_WARPS = 8, FA_U = 4;
 
@@ -248,6 +340,7 @@ __device__ __forceinline__ float * fa_dst_row(const FaP & p, int64_t iq1, int64_
 template <int E>
 __global__ void __launch_bounds__(FA_WARPS * 32) fa_kernel(const FaP p) {
     constexpr int D = 32 * E;
+    pdl_prologue();
     const int64_t row = blockIdx.x;
     const int64_t iq1 = row % p.q.ne[1], iq2 = (row / p.q.ne[1]) % p.q.ne[2], iq3 = row / (p.q.ne[1] * p.q.ne[2]);
     const int64_t ik2 = iq2 / (p.q.ne[2] / p.k.ne[2]), ik3 = iq3 / (p.q.ne[3] / p.k.ne[3]);
@@ -343,30 +436,37 @@ __global__ void __launch_bounds__(FA_WARPS * 32) fa_kernel(const FaP p) {
             fa_dst_row(p, iq1, iq2, iq3)[t] = Sf == 0.0f ? 0.0f : af / Sf;
         }
     }
-    if (p.nsplit > 1 && threadIdx.x == 0) {
+    if (p.nsplit == 1) return;
+    if (threadIdx.x == 0) {
         float * w = p.ws + (row * p.nsplit + blockIdx.y) * (D + 2);
         w[0] = Mx; w[1] = St;
     }
-}
-
-// merges the KV splits of one row: one CTA per row, one thread per channel
-__global__ void __launch_bounds__(256) fa_combine_kernel(const FaP p, int D) {
-    const int64_t row = blockIdx.x;
-    const int64_t iq1 = row % p.q.ne[1], iq2 = (row / p.q.ne[1]) % p.q.ne[2], iq3 = row / (p.q.ne[1] * p.q.ne[2]);
+    // the last CTA of this row to get here merges the splits (threadfence reduction: partials are published before the arrival)
+    __shared__ unsigned last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned n = atomicAdd(p.cnt + row, 1u);
+        last = n == (unsigned) p.nsplit - 1;
+        if (last) p.cnt[row] = 0;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
     const float * w = p.ws + row * p.nsplit * (D + 2);
-    float Mx = -INFINITY;
-    for (int s = 0; s < p.nsplit; s++) Mx = fmaxf(Mx, w[s * (D + 2)]);
-    float St = 0.0f;
-    for (int s = 0; s < p.nsplit; s++) { const float m = w[s * (D + 2)]; St += m == -INFINITY ? 0.0f : w[s * (D + 2) + 1] * expf(m - Mx); }
+    float Mg = -INFINITY;
+    for (int s = 0; s < p.nsplit; s++) Mg = fmaxf(Mg, __ldcg(w + s * (D + 2)));
+    float Sg = 0.0f;
+    for (int s = 0; s < p.nsplit; s++) { const float m = __ldcg(w + s * (D + 2)); Sg += m == -INFINITY ? 0.0f : __ldcg(w + s * (D + 2) + 1) * expf(m - Mg); }
     float r = 1.0f;
     if (p.sinks) {
         const float sk = p.sinks[iq2];
-        if (sk > Mx) { r = expf(Mx - sk); St = St * r + 1.0f; } else { St += expf(sk - Mx); }
+        if (sk > Mg) { r = expf(Mg - sk); Sg = Sg * r + 1.0f; } else { Sg += expf(sk - Mg); }
     }
     for (int t = threadIdx.x; t < D; t += blockDim.x) {
         float a = 0.0f;
-        for (int s = 0; s < p.nsplit; s++) { const float m = w[s * (D + 2)]; if (m != -INFINITY) a += w[s * (D + 2) + 2 + t] * expf(m - Mx); }
-        fa_dst_row(p, iq1, iq2, iq3)[t] = St == 0.0f ? 0.0f : a * r / St;
+        for (int s = 0; s < p.nsplit; s++) { const float m = __ldcg(w + s * (D + 2)); if (m != -INFINITY) a += __ldcg(w + s * (D + 2) + 2 + t) * expf(m - Mg); }
+        fa_dst_row(p, iq1, iq2, iq3)[t] = Sg == 0.0f ? 0.0f : a * r / Sg;
     }
 }
 
@@ -378,10 +478,6 @@ bool nonneg(const b200_tensor * t) { return t->ne[0] >= 0 && t->ne[1] >= 0 && t-
     if (!(ctx)) return fail(B200_ERR_ARG, "null context");                                     \
     CU(cudaSetDevice((ctx)->device));                                                          \
     if (b200_status fst_ = b200_split_flush(ctx)) return fst_
-#define OPS_EPILOGUE(ctx)                                                                      \
-    CU(cudaGetLastError());                                                                    \
-    (ctx)->launches++;                                                                         \
-    return B200_OK
 
 } // namespace
 
@@ -393,14 +489,39 @@ int b200_rms_norm_supported(const b200_tensor * x, const b200_tensor * dst) {
            x->ne[1] * x->ne[2] * x->ne[3] < (1ll << 31);
 }
 
+int b200_rms_norm_mul_supported(const b200_tensor * x, const b200_tensor * w, const b200_tensor * dst) {
+    if (!b200_rms_norm_supported(x, dst) || !w || w->type != B200_TYPE_F32 || w->nb[0] != 4) return 0;
+    if (w->ne[0] != x->ne[0]) return 0;   // per-channel weights; rows, planes and batches broadcast
+    for (int i = 1; i < 4; i++) if (w->ne[i] <= 0 || x->ne[i] % w->ne[i]) return 0;
+    return 1;
+}
+
+static b200_status rms_norm_run(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * w, const b200_tensor * dst, float eps) {
+    const int64_t rows = x->ne[1] * x->ne[2] * x->ne[3], n = x->ne[0];
+    if (rows == 0 || n == 0) return B200_OK;
+    if (!x->data || !dst->data || (w && !w->data)) return fail(B200_ERR_ARG, "null argument");
+    NormP p;
+    p.s = t4(x); p.d = t4(dst); p.w = w ? t4(w) : T4{};
+    p.x = (const char *) x->data; p.y = (char *) dst->data; p.wd = w ? (const char *) w->data : nullptr;
+    p.eps = eps;
+    bool vec = n % 4 == 0 && n <= 16384 && (uintptr_t) x->data % 16 == 0 && (uintptr_t) dst->data % 16 == 0 && (!w || (uintptr_t) w->data % 16 == 0);
+    for (int i = 1; i < 4 && vec; i++) vec = x->nb[i] % 16 == 0 && dst->nb[i] % 16 == 0 && (!w || w->nb[i] % 16 == 0);
+    const int threads = (int) std::min<int64_t>(1024, std::max<int64_t>(32, ((vec ? n / 4 : n) + 31) / 32 * 32));
+    OPS_PROLOGUE(ctx);
+    CU(vec ? b200_launch(ctx, rms_norm_kernel<true>, dim3((unsigned) rows), dim3(threads), 0, p)
+           : b200_launch(ctx, rms_norm_kernel<false>, dim3((unsigned) rows), dim3(threads), 0, p));
+    ctx->launches++;
+    return B200_OK;
+}
+
 b200_status b200_rms_norm(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * dst, float eps) {
     if (!b200_rms_norm_supported(x, dst)) return fail(B200_ERR_UNSUPPORTED, "RMS_NORM: F32 rows, same shapes");
-    const int64_t rows = x->ne[1] * x->ne[2] * x->ne[3];
-    if (rows == 0 || x->ne[0] == 0) return B200_OK;
-    if (!x->data || !dst->data) return fail(B200_ERR_ARG, "null argument");
-    OPS_PROLOGUE(ctx);
-    rms_norm_kernel<<<(unsigned) rows, 256, 0, ctx->stream>>>((const char *) x->data, t4(x), (char *) dst->data, t4(dst), eps);
-    OPS_EPILOGUE(ctx);
+    return rms_norm_run(ctx, x, nullptr, dst, eps);
+}
+
+b200_status b200_rms_norm_mul(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * w, const b200_tensor * dst, float eps) {
+    if (!b200_rms_norm_mul_supported(x, w, dst)) return fail(B200_ERR_UNSUPPORTED, "RMS_NORM + MUL: F32 rows, per-channel weights broadcast over rows");
+    return rms_norm_run(ctx, x, w, dst, eps);
 }
 
 int b200_get_rows_supported(const b200_tensor * src0, const b200_tensor * ids, const b200_tensor * dst) {
@@ -424,10 +545,11 @@ b200_status b200_get_rows(b200_ctx * ctx, const b200_tensor * src0, const b200_t
     if (rows == 0 || src0->ne[0] == 0) return B200_OK;
     if (!src0->data || !ids->data || !dst->data) return fail(B200_ERR_ARG, "null argument");
     OPS_PROLOGUE(ctx);
-    get_rows_kernel<<<(unsigned) rows, 256, 0, ctx->stream>>>(src0->type, (const char *) src0->data, src0->ne[0], src0->ne[1], (int64_t) src0->nb[1],
-                                                              (int64_t) src0->nb[2], (int64_t) src0->nb[3], (const char *) ids->data, t4(ids),
-                                                              (char *) dst->data, (int64_t) dst->nb[1], (int64_t) dst->nb[2], (int64_t) dst->nb[3]);
-    OPS_EPILOGUE(ctx);
+    CU(b200_launch(ctx, get_rows_kernel, dim3((unsigned) rows), dim3(256), 0, (int) src0->type, (const char *) src0->data, src0->ne[0], src0->ne[1],
+                   (int64_t) src0->nb[1], (int64_t) src0->nb[2], (int64_t) src0->nb[3], (const char *) ids->data, t4(ids), (char *) dst->data,
+                   (int64_t) dst->nb[1], (int64_t) dst->nb[2], (int64_t) dst->nb[3]));
+    ctx->launches++;
+    return B200_OK;
 }
 
 int b200_rope_supported(const b200_tensor * x, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst, const b200_rope_params * rp) {
@@ -440,12 +562,7 @@ int b200_rope_supported(const b200_tensor * x, const b200_tensor * pos, const b2
     return x->ne[1] * x->ne[2] * x->ne[3] < (1ll << 31);
 }
 
-b200_status b200_rope(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst,
-                      const b200_rope_params * rp) {
-    if (!b200_rope_supported(x, pos, freq_factors, dst, rp)) return fail(B200_ERR_UNSUPPORTED, "ROPE: F32, normal or neox mode");
-    const int64_t rows = x->ne[1] * x->ne[2] * x->ne[3];
-    if (rows == 0 || x->ne[0] == 0) return B200_OK;
-    if (!x->data || !pos->data || !dst->data) return fail(B200_ERR_ARG, "null argument");
+static RopeP rope_consts(const b200_rope_params * rp) {
     // ggml_rope_yarn_corr_dims (ggml.c: ggml_rope_yarn_corr_dim): the channel range the YaRN ramp covers
     RopeP p;
     p.n_dims = rp->n_dims; p.neox = rp->mode == B200_ROPE_NEOX;
@@ -454,11 +571,29 @@ b200_status b200_rope(b200_ctx * ctx, const b200_tensor * x, const b200_tensor *
     auto corr_dim = [&](float n_rot) { return (float) rp->n_dims * logf((float) rp->n_ctx_orig / (n_rot * 2.0f * 3.14159265358979323846f)) / (2.0f * logf(rp->freq_base)); };
     p.corr0 = fmaxf(0.0f, floorf(corr_dim(rp->beta_fast)));
     p.corr1 = fminf((float) rp->n_dims - 1.0f, ceilf(corr_dim(rp->beta_slow)));
+    return p;
+}
+static RopeJob rope_job(const b200_tensor * x, const b200_tensor * pos, const b200_tensor * ff, const b200_tensor * dst) {
+    RopeJob j;
+    j.s = t4(x); j.d = t4(dst);
+    j.x = (const char *) x->data; j.y = (char *) dst->data;
+    j.pos = (const int32_t *) pos->data;
+    j.ff = ff ? (const float *) ff->data : nullptr;
+    j.st = RowStore{};
+    return j;
+}
+static int rope_threads(int64_t ne0) { return (int) std::min<int64_t>(256, std::max<int64_t>(32, (ne0 / 2 + 31) / 32 * 32)); }
+
+b200_status b200_rope(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst,
+                      const b200_rope_params * rp) {
+    if (!b200_rope_supported(x, pos, freq_factors, dst, rp)) return fail(B200_ERR_UNSUPPORTED, "ROPE: F32, normal or neox mode");
+    const int64_t rows = x->ne[1] * x->ne[2] * x->ne[3];
+    if (rows == 0 || x->ne[0] == 0) return B200_OK;
+    if (!x->data || !pos->data || !dst->data || (freq_factors && !freq_factors->data)) return fail(B200_ERR_ARG, "null argument");
     OPS_PROLOGUE(ctx);
-    const int threads = (int) std::min<int64_t>(256, std::max<int64_t>(32, (x->ne[0] / 2 + 31) / 32 * 32));
-    rope_kernel<<<(unsigned) rows, threads, 0, ctx->stream>>>((const char *) x->data, t4(x), (const int32_t *) pos->data,
-                                                              freq_factors ? (const float *) freq_factors->data : nullptr, (char *) dst->data, t4(dst), p);
-    OPS_EPILOGUE(ctx);
+    CU(b200_launch(ctx, rope_kernel, dim3((unsigned) rows), dim3(rope_threads(x->ne[0])), 0, rope_job(x, pos, freq_factors, dst), rope_consts(rp)));
+    ctx->launches++;
+    return B200_OK;
 }
 
 int b200_set_rows_supported(const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst) {
@@ -470,21 +605,58 @@ int b200_set_rows_supported(const b200_tensor * src, const b200_tensor * idx, co
     return src->ne[1] * src->ne[2] * src->ne[3] < (1ll << 31);
 }
 
+static SetRowsJob set_rows_job(const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst) {
+    SetRowsJob j;
+    j.s = t4(src); j.is = t4(idx); j.d = t4(dst);
+    j.src = (const char *) src->data; j.idx = (const char *) idx->data; j.dst = (char *) dst->data;
+    j.f16 = dst->type == B200_TYPE_F16; j.i64 = idx->type == B200_TYPE_I64;
+    return j;
+}
+
 b200_status b200_set_rows(b200_ctx * ctx, const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst) {
     if (!b200_set_rows_supported(src, idx, dst)) return fail(B200_ERR_UNSUPPORTED, "SET_ROWS: F32 rows into F32 / F16 by I64 / I32 index");
     const int64_t rows = src->ne[1] * src->ne[2] * src->ne[3];
     if (rows == 0 || src->ne[0] == 0) return B200_OK;
     if (!src->data || !idx->data || !dst->data) return fail(B200_ERR_ARG, "null argument");
     OPS_PROLOGUE(ctx);
-    const bool f16 = dst->type == B200_TYPE_F16, i64 = idx->type == B200_TYPE_I64;
-    const char * s = (const char *) src->data, * ix = (const char *) idx->data;
-    char * d = (char *) dst->data;
-    const unsigned g = (unsigned) rows;
-    if (f16 && i64)       set_rows_kernel<__half, int64_t><<<g, 256, 0, ctx->stream>>>(s, t4(src), ix, t4(idx), d, t4(dst));
-    else if (f16)         set_rows_kernel<__half, int32_t><<<g, 256, 0, ctx->stream>>>(s, t4(src), ix, t4(idx), d, t4(dst));
-    else if (i64)         set_rows_kernel<float, int64_t><<<g, 256, 0, ctx->stream>>>(s, t4(src), ix, t4(idx), d, t4(dst));
-    else                  set_rows_kernel<float, int32_t><<<g, 256, 0, ctx->stream>>>(s, t4(src), ix, t4(idx), d, t4(dst));
-    OPS_EPILOGUE(ctx);
+    CU(b200_launch(ctx, set_rows_kernel, dim3((unsigned) rows), dim3(256), 0, set_rows_job(src, idx, dst)));
+    ctx->launches++;
+    return B200_OK;
+}
+
+// ROPE(q), ROPE(k), SET_ROWS(k_cache <- rope(k) seen as [n_embd_k_gqa, n_tokens]) and SET_ROWS(v_cache <- v) as one launch
+int b200_attn_prep_supported(const b200_tensor * q, const b200_tensor * q_dst, const b200_tensor * k, const b200_tensor * k_dst, const b200_tensor * pos,
+                             const b200_tensor * freq_factors, const b200_rope_params * rp, const b200_tensor * k_idx, const b200_tensor * k_cache,
+                             const b200_tensor * v, const b200_tensor * v_idx, const b200_tensor * v_cache) {
+    if (!b200_rope_supported(q, pos, freq_factors, q_dst, rp) || !b200_rope_supported(k, pos, freq_factors, k_dst, rp)) return 0;
+    if (k->ne[3] != 1 || k_dst->nb[1] != (size_t) k->ne[0] * 4) return 0;   // the heads of a token are contiguous: one cache row
+    // the SET_ROWS of k: src = k_dst as [ne0 * ne1, ne2] rows
+    b200_tensor ks = *k_dst;
+    ks.ne[0] = k->ne[0] * k->ne[1]; ks.ne[1] = k->ne[2]; ks.ne[2] = 1; ks.ne[3] = 1;
+    ks.nb[1] = k_dst->nb[2]; ks.nb[2] = ks.nb[3] = ks.nb[1] * (size_t) ks.ne[1];
+    if (!b200_set_rows_supported(&ks, k_idx, k_cache) || k_idx->ne[1] != 1 || k_idx->ne[2] != 1 || k_cache->ne[2] != 1 || k_cache->ne[3] != 1) return 0;
+    if (!b200_set_rows_supported(v, v_idx, v_cache)) return 0;
+    return q->ne[1] * q->ne[2] * q->ne[3] + k->ne[1] * k->ne[2] + v->ne[1] * v->ne[2] * v->ne[3] < (1ll << 31);
+}
+
+b200_status b200_attn_prep(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * q_dst, const b200_tensor * k, const b200_tensor * k_dst,
+                           const b200_tensor * pos, const b200_tensor * freq_factors, const b200_rope_params * rp, const b200_tensor * k_idx,
+                           const b200_tensor * k_cache, const b200_tensor * v, const b200_tensor * v_idx, const b200_tensor * v_cache) {
+    if (!b200_attn_prep_supported(q, q_dst, k, k_dst, pos, freq_factors, rp, k_idx, k_cache, v, v_idx, v_cache))
+        return fail(B200_ERR_UNSUPPORTED, "attn_prep: ROPE(q), ROPE(k) + SET_ROWS(k), SET_ROWS(v) of one layer");
+    const int64_t nq = q->ne[1] * q->ne[2] * q->ne[3], nk = k->ne[1] * k->ne[2], nv = v->ne[1] * v->ne[2] * v->ne[3];
+    if (nq + nk + nv == 0 || q->ne[0] == 0) return B200_OK;
+    for (const b200_tensor * t : { q, q_dst, k, k_dst, pos, k_idx, k_cache, v, v_idx, v_cache }) if (!t->data) return fail(B200_ERR_ARG, "null argument");
+    if (freq_factors && !freq_factors->data) return fail(B200_ERR_ARG, "null argument");
+    RopeJob jq = rope_job(q, pos, freq_factors, q_dst), jk = rope_job(k, pos, freq_factors, k_dst);
+    jk.st.base = (char *) k_cache->data;
+    jk.st.idx = (const char *) k_idx->data; jk.st.idx_nb0 = (int64_t) k_idx->nb[0];
+    jk.st.row_nb = (int64_t) k_cache->nb[1]; jk.st.n_rows = k_cache->ne[1];
+    jk.st.f16 = k_cache->type == B200_TYPE_F16; jk.st.i64 = k_idx->type == B200_TYPE_I64;
+    OPS_PROLOGUE(ctx);
+    CU(b200_launch(ctx, attn_prep_kernel, dim3((unsigned) (nq + nk + nv)), dim3(256), 0, jq, jk, set_rows_job(v, v_idx, v_cache), rope_consts(rp), (int) nq, (int) nk));
+    ctx->launches++;
+    return B200_OK;
 }
 
 int b200_cpy_supported(const b200_tensor * src, const b200_tensor * dst) {
@@ -500,14 +672,15 @@ b200_status b200_cpy(b200_ctx * ctx, const b200_tensor * src, const b200_tensor 
     if (!src->data || !dst->data) return fail(B200_ERR_ARG, "null argument");
     OPS_PROLOGUE(ctx);
     const bool sf = src->type == B200_TYPE_F32, df = dst->type == B200_TYPE_F32;
-    const unsigned g = (unsigned) ((n + 255) / 256);
+    const dim3 g((unsigned) ((n + 255) / 256)), b(256);
     const char * s = (const char *) src->data;
     char * d = (char *) dst->data;
-    if (sf && df)       cpy_kernel<float, float><<<g, 256, 0, ctx->stream>>>(s, t4(src), d, t4(dst), n);
-    else if (sf)        cpy_kernel<float, __half><<<g, 256, 0, ctx->stream>>>(s, t4(src), d, t4(dst), n);
-    else if (df)        cpy_kernel<__half, float><<<g, 256, 0, ctx->stream>>>(s, t4(src), d, t4(dst), n);
-    else                cpy_kernel<__half, __half><<<g, 256, 0, ctx->stream>>>(s, t4(src), d, t4(dst), n);
-    OPS_EPILOGUE(ctx);
+    if (sf && df)       CU(b200_launch(ctx, cpy_kernel<float, float>, g, b, 0, s, t4(src), d, t4(dst), n));
+    else if (sf)        CU(b200_launch(ctx, cpy_kernel<float, __half>, g, b, 0, s, t4(src), d, t4(dst), n));
+    else if (df)        CU(b200_launch(ctx, cpy_kernel<__half, float>, g, b, 0, s, t4(src), d, t4(dst), n));
+    else                CU(b200_launch(ctx, cpy_kernel<__half, __half>, g, b, 0, s, t4(src), d, t4(dst), n));
+    ctx->launches++;
+    return B200_OK;
 }
 
 int b200_flash_attn_ext_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * sinks,
@@ -530,10 +703,13 @@ int b200_flash_attn_ext_supported(const b200_tensor * q, const b200_tensor * k, 
     return q->ne[1] * q->ne[2] * q->ne[3] < (1ll << 31);
 }
 
+constexpr size_t FA_CNT_BYTES = 4096;   // arrival counters at the head of the split workspace (splits only run with < 2 x SM-count rows)
+
 b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
                                 const b200_tensor * sinks, const b200_tensor * dst, float scale, float max_bias, float logit_softcap) {
     if (!b200_flash_attn_ext_supported(q, k, v, mask, sinks, dst))
         return fail(B200_ERR_UNSUPPORTED, "FLASH_ATTN_EXT: F32 q, F16 k / v of head size 64 / 128 / 256, F16 mask");
+    if (!ctx) return fail(B200_ERR_ARG, "null context");
     const int64_t rows = q->ne[1] * q->ne[2] * q->ne[3];
     if (rows == 0) return B200_OK;
     if (!q->data || !dst->data || (k->ne[1] > 0 && (!k->data || !v->data)) || (mask && !mask->data) || (sinks && !sinks->data)) return fail(B200_ERR_ARG, "null argument");
@@ -551,32 +727,32 @@ b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b20
     p.n_head_log2 = 1u << (uint32_t) floorf(log2f((float) n_head));
     p.m0 = powf(2.0f, -max_bias / (float) p.n_head_log2);
     p.m1 = powf(2.0f, -(max_bias / 2.0f) / (float) p.n_head_log2);
-    // KV splits: fill the SMs twice over, at least 256 positions per split
+    // KV splits (decode: a few dozen rows, one per head): about two CTAs per SM, no fewer than 32 positions (one round of the 8 warps)
+    // per split; the splits of a row are merged by the last of its CTAs to finish
     int nsplit = 1;
     const int64_t n_kv = k->ne[1];
-    if (rows < 2 * ctx->sm_count && n_kv >= 512) {
-        nsplit = (int) std::min<int64_t>(std::min<int64_t>((2 * (int64_t) ctx->sm_count + rows - 1) / rows, n_kv / 256), 32);
+    if (rows < 2 * ctx->sm_count && rows <= (int64_t) (FA_CNT_BYTES / 4) && n_kv >= 64) {
+        nsplit = (int) std::min<int64_t>(std::min<int64_t>((2 * (int64_t) ctx->sm_count + rows - 1) / rows, n_kv / 32), 64);
         if (nsplit < 1) nsplit = 1;
     }
-    p.nsplit = nsplit;
     p.chunk  = nsplit == 1 ? std::max<int64_t>(n_kv, 1) : ((n_kv + nsplit - 1) / nsplit + 31) / 32 * 32;
+    if (nsplit > 1) nsplit = (int) ((n_kv + p.chunk - 1) / p.chunk);   // no empty splits
+    p.nsplit = nsplit;
     p.ws     = nullptr;
+    p.cnt    = nullptr;
     OPS_PROLOGUE(ctx);
     if (nsplit > 1) {
-        if (b200_status st = b200_ensure(ctx, &ctx->fa_ws, &ctx->fa_ws_size, (size_t) rows * nsplit * (D + 2) * sizeof(float))) return st;
-        p.ws = (float *) ctx->fa_ws;
+        const void * before = ctx->fa_ws;
+        if (b200_status st = b200_ensure(ctx, &ctx->fa_ws, &ctx->fa_ws_size, FA_CNT_BYTES + (size_t) rows * nsplit * (D + 2) * sizeof(float))) return st;
+        if (ctx->fa_ws != before) CU(cudaMemsetAsync(ctx->fa_ws, 0, FA_CNT_BYTES, ctx->stream));   // (re)allocated: the counters start at zero
+        p.cnt = (unsigned *) ctx->fa_ws;
+        p.ws  = (float *) ((char *) ctx->fa_ws + FA_CNT_BYTES);
     }
-    const dim3 grid((unsigned) rows, (unsigned) nsplit);
-    if (D == 64)       fa_kernel<2><<<grid, FA_WARPS * 32, 0, ctx->stream>>>(p);
-    else if (D == 128) fa_kernel<4><<<grid, FA_WARPS * 32, 0, ctx->stream>>>(p);
-    else               fa_kernel<8><<<grid, FA_WARPS * 32, 0, ctx->stream>>>(p);
-    CU(cudaGetLastError());
+    const dim3 grid((unsigned) rows, (unsigned) nsplit), block(FA_WARPS * 32);
+    if (D == 64)       CU(b200_launch(ctx, fa_kernel<2>, grid, block, 0, p));
+    else if (D == 128) CU(b200_launch(ctx, fa_kernel<4>, grid, block, 0, p));
+    else               CU(b200_launch(ctx, fa_kernel<8>, grid, block, 0, p));
     ctx->launches++;
-    if (nsplit > 1) {
-        fa_combine_kernel<<<(unsigned) rows, std::min(D, 256), 0, ctx->stream>>>(p, D);
-        CU(cudaGetLastError());
-        ctx->launches++;
-    }
     return B200_OK;
 }
 

@@ -39,6 +39,47 @@ def test_rms_norm(ctx, shape, eps):
     assert float(out[..., : shape[-1]].abs().max()) == 0.0
 
 
+@pytest.mark.parametrize("shape", [(1, 1, 1, 4096), (1, 1, 7, 4096), (2, 3, 5, 100), (1, 1, 3, 20000)])
+def test_rms_norm_mul_is_the_two_nodes(ctx, shape):
+    """build_norm's RMS_NORM + MUL(norm weight) as one launch: bit-identical to running the two ops (vector and scalar paths)"""
+    import torch
+    g = torch.Generator(device="cuda").manual_seed(7)
+    x = torch.randn(shape, device="cuda", generator=g) * 2
+    w = torch.randn(shape[-1], device="cuda", generator=g)
+    fused = ctx.rms_norm_mul(x, w, 1e-5)
+    two = ctx.mul(ctx.rms_norm(x, 1e-5), w.reshape(1, 1, 1, -1))
+    assert torch.equal(fused, two)
+    x64 = x.double()
+    ref = x64 / torch.sqrt((x64 * x64).mean(-1, keepdim=True) + 1e-5) * w.double()
+    assert _nmse(ref.cpu().numpy(), fused.cpu().numpy()) < 1e-12
+
+
+@pytest.mark.parametrize("cache_dtype", ["float16", "float32"])
+@pytest.mark.parametrize("n_tok", [1, 5])
+def test_attn_prep_is_the_four_nodes(ctx, n_tok, cache_dtype):
+    """ROPE(q), ROPE(k), SET_ROWS(k cache), SET_ROWS(v cache) of one layer in one launch: bit-identical to the four ops"""
+    import torch
+    g = torch.Generator(device="cuda").manual_seed(8 + n_tok)
+    D, nh, nkv, n_ctx = 128, 32, 8, 96
+    q = torch.randn((1, n_tok, nh, D), device="cuda", generator=g)
+    k = torch.randn((1, n_tok, nkv, D), device="cuda", generator=g)
+    v = torch.randn((n_tok, nkv * D), device="cuda", generator=g)
+    pos = torch.arange(40, 40 + n_tok, device="cuda", dtype=torch.int32)
+    idx = (torch.arange(n_tok, device="cuda", dtype=torch.int64) * 3 + 11) % n_ctx
+    dt = getattr(torch, cache_dtype)
+    kc1, vc1 = torch.zeros((n_ctx, nkv * D), device="cuda", dtype=dt), torch.zeros((n_ctx, nkv * D), device="cuda", dtype=dt)
+    kc2, vc2 = torch.zeros_like(kc1), torch.zeros_like(vc1)
+    kw = dict(freq_base=500000.0, n_ctx_orig=8192)
+    qo, ko = ctx.attn_prep(q, k, pos, kc1, idx, v, vc1, idx, D, 0, **kw)
+    q_ref = ctx.rope(q, pos, D, 0, **kw)
+    k_ref = ctx.rope(k, pos, D, 0, **kw)
+    ctx.set_rows(kc2, k_ref.reshape(n_tok, nkv * D), idx)
+    ctx.set_rows(vc2, v, idx)
+    assert torch.equal(qo, q_ref) and torch.equal(ko, k_ref)
+    assert torch.equal(kc1, kc2) and torch.equal(vc1, vc2)
+    assert float(kc1.float().abs().sum()) > 0
+
+
 @pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q5_K, Q6_K])
 def test_get_rows_quantized_is_dequantize_row(pkg, ctx, refq, t):
     """token-embedding lookup from a quantized tok_embd: bit-identical to dequantize_row_<type> (ggml-quants.c) of the chosen rows"""

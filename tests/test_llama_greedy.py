@@ -209,7 +209,11 @@ def test_greedy_whole_graph_on_device(pkg, tmp_path, tname):
         report.update({"gen_s_ref_cuda": rc["gen_s"], "prompt_s_ref_cuda": rc["prompt_s"], "graph_splits_ref_cuda": rc["graph_splits"],
                        "noise_ref_cuda_vs_x64": noise(rc), "argmax_flips_ref_cuda": len(flips(rc))})
         n_ref = max(n_ref, noise(rc))
+    # the fused launches (RMS_NORM+MUL, hoisted q/k/v, ROPE+SET_ROWS) against the same graph node by node: not a bit may differ
+    unf = _decode(prefix, "file", [CPU_LIB, pkg.BACKEND_PATH], ngl=99, gen=n_gen, extra=["--fa", "--kqv", "--force", forced], env=_env(GGML_B200_DISABLE_F3_FUSION=1))
+    report.update({"gen_s_b200_node_by_node": unf["gen_s"], "fused_equals_node_by_node": unf["tokens"] == got["tokens"] and unf["margins"] == got["margins"]})
     _report(f"greedy_device_{tname}.json", report)
+    assert report["fused_equals_node_by_node"], report
     assert got["graph_splits"] < off["graph_splits"], report
     assert got["graph_splits"] <= 2, report
     assert noise(got) <= 2.0 * n_ref, report
