@@ -84,14 +84,15 @@ struct be_ctx {
     size_t     n_graphs    = 0;
     uint64_t   graph_clock = 0;
     uint64_t   graph_replays = 0, graph_captures = 0;
+    void *     blk_scratch = nullptr;              // try_fuse_attn_block: q / k / v projections of the layer in flight
+    size_t     blk_scratch_size = 0;
     std::vector<char> done;                        // run_nodes: nodes already executed ahead of their position (hoisted into a fused launch)
     bool       fuse_f3 = true;                     // GGML_B200_DISABLE_F3_FUSION=1: RMS_NORM+MUL, ROPE/SET_ROWS and the q/k/v hoist run node by node
     // GGML_B200_TIMING=1: where a graph_compute goes (printed when the backend is freed)
     bool       timing = false;
-    uint64_t   t_calls = 0, t_key_ns = 0, t_run_ns = 0, t_gpu_n = 0;
-    double     t_gpu_ms = 0;
+    struct tstat { uint64_t n = 0, key_ns = 0, run_ns = 0, gpu_n = 0; double gpu_ms = 0; } t_replay, t_direct;
     void *     t_ev0 = nullptr, * t_ev1 = nullptr;
-    bool       t_pending = false;
+    bool       t_pending = false, t_pending_replay = false;
 };
 
 ggml_backend_reg_t b200_reg();
@@ -407,15 +408,17 @@ void be_free(ggml_backend_t backend) {
         if (sp.event) b200_event_destroy(id, sp.event);
         b200_ctx_destroy(sp.ctx);
     }
+    if (c->blk_scratch) b200_free(c->device, c->blk_scratch);
     if (c->split_event) b200_event_destroy(c->device, c->split_event);
     if (c->copy_event) b200_event_destroy(c->device, c->copy_event);
     b200_ctx_synchronize(c->ctx);
     if (c->timing) {
         timing_collect(c);
-        fprintf(stderr, "ggml-b200 timing: %llu graph_compute calls; host per call: key %.1f us, launch %.1f us; device per call: %.1f us (%llu measured); "
-                "graph replays %llu, captures %llu\n", (unsigned long long) c->t_calls, c->t_calls ? c->t_key_ns / 1e3 / c->t_calls : 0.0,
-                c->t_calls ? c->t_run_ns / 1e3 / c->t_calls : 0.0, c->t_gpu_n ? c->t_gpu_ms * 1e3 / c->t_gpu_n : 0.0, (unsigned long long) c->t_gpu_n,
-                (unsigned long long) c->graph_replays, (unsigned long long) c->graph_captures);
+        for (const be_ctx::tstat * ts : { &c->t_replay, &c->t_direct }) {
+            fprintf(stderr, "ggml-b200 timing: %s: %llu graph_compute calls; host per call: key %.1f us, launch %.1f us; device per call: %.1f us\n",
+                    ts == &c->t_replay ? "graph replays" : "direct launches", (unsigned long long) ts->n, ts->n ? ts->key_ns / 1e3 / ts->n : 0.0,
+                    ts->n ? ts->run_ns / 1e3 / ts->n : 0.0, ts->gpu_n ? ts->gpu_ms * 1e3 / ts->gpu_n : 0.0);
+        }
         if (c->t_ev0) { b200_event_destroy(c->device, c->t_ev0); b200_event_destroy(c->device, c->t_ev1); }
     }
     for (auto & kv : c->graphs) for (auto & g : kv.second) b200_graph_destroy(g.exec);
@@ -813,6 +816,86 @@ bool try_fuse_attn_prep(be_ctx * c, ggml_cgraph * cgraph, int i) {
     return true;
 }
 
+int32_t use_count(const ggml_cgraph * cgraph, const ggml_tensor * t) {   // ggml_node_get_use_count by tensor
+    const size_t pos = ggml_hash_find(&cgraph->visited_hash_set, t);
+    return ggml_bitset_get(cgraph->visited_hash_set.used, pos) ? cgraph->use_counts[pos] : 0;
+}
+// t is `root` seen through reshapes / views that nobody else reads, same bytes, contiguous: what a kernel reading t would read from
+// any other contiguous copy of root's result
+bool sole_contiguous_view_of(const ggml_cgraph * cgraph, const ggml_tensor * t, const ggml_tensor * root) {
+    if (!t || t->data != root->data || !ggml_is_contiguous(t) || ggml_nelements(t) != ggml_nelements(root) || t->type != root->type) return false;
+    for (int depth = 0; t != root; depth++) {
+        if (depth > 4 || !(t->op == GGML_OP_RESHAPE || t->op == GGML_OP_VIEW) || !t->src[0] || use_count(cgraph, t) != 1 || (t->flags & GGML_TENSOR_FLAG_OUTPUT)) return false;
+        t = t->src[0];
+    }
+    return use_count(cgraph, root) == 1 && !(root->flags & GGML_TENSOR_FLAG_OUTPUT);
+}
+
+// The attention inputs of a layer as build_attn lays them out (src/models/llama.cpp:36-75, src/llama-graph.cpp:1593-1606):
+//   MUL_MAT(wq), ROPE(q), MUL_MAT(wv), MUL_MAT(wk), ROPE(k), SET_ROWS(k cache), SET_ROWS(v cache)      (reshapes / views in between)
+// run as TWO launches: the three projections of the shared activations into a scratch buffer of the backend, then b200_attn_prep
+// from there. The graph allocator gives Kcur the memory of Qcur (dead after ROPE(q)), so the projections cannot simply be hoisted
+// into one launch at their graph addresses; nothing but the two ROPEs / the V store reads them (checked), so they never need to exist
+// there. Returns true when the seven nodes have been run (the six followers are marked done).
+bool try_fuse_attn_block(be_ctx * c, ggml_cgraph * cgraph, int i) {
+    if (!c->fuse || !c->fuse_f3 || !f3_on() || exact_mode()) return false;
+    int j[7] = { i };
+    for (int k = 1; k < 7; k++) { j[k] = next_live(c, cgraph, j[k - 1] + 1); if (j[k] < 0) return false; }
+    ggml_tensor * mq = cgraph->nodes[j[0]], * rq = cgraph->nodes[j[1]], * ma = cgraph->nodes[j[2]], * mb = cgraph->nodes[j[3]], * rk = cgraph->nodes[j[4]],
+                * sk = cgraph->nodes[j[5]], * sv = cgraph->nodes[j[6]];
+    if (rq->op != GGML_OP_ROPE || ma->op != GGML_OP_MUL_MAT || mb->op != GGML_OP_MUL_MAT || rk->op != GGML_OP_ROPE || sk->op != GGML_OP_SET_ROWS ||
+        sv->op != GGML_OP_SET_ROWS) return false;
+    ggml_tensor * mk = rk->src[0] && rk->src[0]->data == ma->data ? ma : mb, * mv = mk == ma ? mb : ma;
+    ggml_tensor * mm[3] = { mq, mk, mv };
+    b200_mul_mat_desc d[3];
+    for (int k = 0; k < 3; k++) {
+        if (mm[k]->src[1] != mq->src[1] || mm[k]->src[0]->op != GGML_OP_NONE || !fill_mul_mat(mm[k], &d[k])) return false;
+        if (mm[k]->src[0]->buffer && buft_is_split(mm[k]->src[0]->buffer->buft)) return false;
+        if (d[k].type != d[0].type || d[k].ne00 != d[0].ne00 || d[k].ne02 != 1 || d[k].ne03 != 1 || d[k].ne12 != 1 || d[k].ne13 != 1 || !ggml_is_contiguous(mm[k])) return false;
+    }
+    if (!f3_ok(rq) || !f3_ok(rk) || !f3_ok(sk) || !f3_ok(sv)) return false;
+    if (memcmp(rq->op_params, rk->op_params, sizeof(rq->op_params)) != 0 || rq->src[1] != rk->src[1] || rq->src[2] != rk->src[2]) return false;
+    if (!sole_contiguous_view_of(cgraph, rq->src[0], mq) || !sole_contiguous_view_of(cgraph, rk->src[0], mk) || !sole_contiguous_view_of(cgraph, sv->src[0], mv)) return false;
+    const ggml_tensor * ks = sk->src[0];   // rope(k)'s output seen as [n_embd_k_gqa, n_tokens]
+    if (!ks || ks->data != rk->data || ks->type != GGML_TYPE_F32 || ks->ne[0] != rk->ne[0] * rk->ne[1] || ks->ne[1] != rk->ne[2] || ks->ne[2] != 1 ||
+        ks->ne[3] != 1 || ks->nb[1] != rk->nb[2] || rk->ne[3] != 1) return false;
+    // outputs that do land at their graph addresses: rope(q), rope(k), the cache rows. They are written at ROPE(q)'s position in the
+    // order, after every MUL_MAT of the block has completed: the block's inputs (src1, positions, indices) must not be among them
+    const ggml_tensor * outs[4] = { rq, rk, sk, sv };
+    const ggml_tensor * ins[6] = { mq->src[1], rq->src[1], rq->src[2], sk->src[1], sv->src[1], nullptr };
+    for (const ggml_tensor * o : outs) {
+        for (const ggml_tensor * in : ins) if (in && ranges_overlap(o, in)) return false;
+        for (const ggml_tensor * o2 : outs) if (o != o2 && ranges_overlap(o, o2)) return false;
+    }
+    const int64_t N = d[0].ne11;
+    size_t off[3], total = 0;
+    for (int k = 0; k < 3; k++) { off[k] = total; total += ((size_t) d[k].ne01 * N * sizeof(float) + 255) / 256 * 256; }
+    if (total > c->blk_scratch_size) {
+        if (c->capturing) return false;   // sized by the uncaptured first run
+        b200_ctx_synchronize(c->ctx);
+        if (!grow(c->device, &c->blk_scratch, &c->blk_scratch_size, total)) return false;
+    }
+    const void * w[3];
+    float *      o[3];
+    for (int k = 0; k < 3; k++) {
+        w[k] = mm[k]->src[0]->data;
+        o[k] = (float *) ((char *) c->blk_scratch + off[k]);
+        d[k].nb1 = (size_t) d[k].ne01 * sizeof(float); d[k].nb2 = d[k].nb3 = d[k].nb1 * (size_t) N;
+    }
+    // the descriptors b200_attn_prep would get node by node, with the three projections read from the scratch copies
+    b200_tensor q = as_b200(rq->src[0]), k = as_b200(rk->src[0]), v = as_b200(sv->src[0]);
+    q.data = o[0]; k.data = o[1]; v.data = o[2];
+    const b200_tensor qd = as_b200(rq), kd = as_b200(rk), pos = as_b200(rq->src[1]), ki = as_b200(sk->src[1]), kc = as_b200(sk), vi = as_b200(sv->src[1]), vc = as_b200(sv);
+    b200_tensor ff;
+    if (rq->src[2]) ff = as_b200(rq->src[2]);
+    const b200_rope_params rp = rope_params_of(rq);
+    if (!b200_attn_prep_supported(&q, &qd, &k, &kd, &pos, rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc)) return false;
+    CHECK_RUN(c, b200_mul_mat_shared_src1(c->ctx, 3, d, w, (const float *) mq->src[1]->data, o));
+    CHECK_RUN(c, b200_attn_prep(c->ctx, &q, &qd, &k, &kd, &pos, rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc));
+    for (int k2 = 1; k2 < 7; k2++) c->done[j[k2]] = 1;
+    return true;
+}
+
 ggml_status run_nodes(be_ctx * c, ggml_cgraph * cgraph) {
     c->done.assign((size_t) cgraph->n_nodes, 0);
     for (int i = 0; i < cgraph->n_nodes; i++) {
@@ -826,6 +909,7 @@ ggml_status run_nodes(be_ctx * c, ggml_cgraph * cgraph) {
                 continue;
             }
         }
+        if (node->op == GGML_OP_MUL_MAT && try_fuse_attn_block(c, cgraph, i)) continue;
         if (node->op == GGML_OP_MUL_MAT) {
             b200_mul_mat_desc descs[4];
             const void *      w[4];
@@ -971,7 +1055,8 @@ uint64_t now_ns() { return (uint64_t) std::chrono::duration_cast<std::chrono::na
 void timing_collect(be_ctx * c) {
     if (!c->t_pending) return;
     float ms = 0;
-    if (b200_event_synchronize(c->t_ev1) == B200_OK && b200_event_elapsed_ms(c->t_ev0, c->t_ev1, &ms) == B200_OK) { c->t_gpu_ms += ms; c->t_gpu_n++; }
+    be_ctx::tstat & ts = c->t_pending_replay ? c->t_replay : c->t_direct;
+    if (b200_event_synchronize(c->t_ev1) == B200_OK && b200_event_elapsed_ms(c->t_ev0, c->t_ev1, &ms) == B200_OK) { ts.gpu_ms += ms; ts.gpu_n++; }
     c->t_pending = false;
 }
 
@@ -983,12 +1068,15 @@ ggml_status be_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     const uint64_t t0 = now_ns();
     uint64_t key_ns = 0;
     CHECK(b200_event_record(c->ctx, c->t_ev0));
+    const uint64_t replays0 = c->graph_replays;
     const ggml_status st = be_graph_compute_impl(backend, cgraph, &key_ns);
     CHECK(b200_event_record(c->ctx, c->t_ev1));
     c->t_pending = true;
-    c->t_calls++;
-    c->t_key_ns += key_ns;
-    c->t_run_ns += now_ns() - t0 - key_ns;
+    c->t_pending_replay = c->graph_replays != replays0;
+    be_ctx::tstat & ts = c->t_pending_replay ? c->t_replay : c->t_direct;
+    ts.n++;
+    ts.key_ns += key_ns;
+    ts.run_ns += now_ns() - t0 - key_ns;
     return st;
 }
 

@@ -26,7 +26,11 @@ def run(args, env=None, timeout=1800):
     p = subprocess.run([str(HARNESS)] + [str(a) for a in args], capture_output=True, text=True, timeout=timeout, env=e)
     if p.returncode != 0:
         return {"error": (p.stderr or p.stdout)[-1500:]}
-    return json.loads(p.stdout.strip().splitlines()[-1])
+    r = json.loads(p.stdout.strip().splitlines()[-1])
+    t = [ln for ln in p.stderr.splitlines() if "ggml-b200 timing" in ln]   # GGML_B200_TIMING=1
+    if t:
+        r["backend_timing"] = t
+    return r
 
 
 def main():
@@ -67,9 +71,9 @@ def main():
         toks[name] = r["tokens"]
         res["runs"][name] = {"pp_tok_s": a.prompt / r["prompt_s"], "tg_tok_s": (a.gen - 1) / r["gen_s"], "ms_per_token": 1e3 * r["gen_s"] / (a.gen - 1),
                              "prompt_s": r["prompt_s"], "gen_s": r["gen_s"], "load_s": r["load_s"], "graph_splits": r["graph_splits"], "env": env}
+        if "backend_timing" in r:
+            res["runs"][name]["backend_timing"] = r["backend_timing"]
     if "b200" in toks and "reference_cuda" in toks:
-        same = next((i for i, (x, y) in enumerate(zip(toks["b200"], toks["reference_cuda"])) if x != y), len(toks["b200"]))
-        res["free_running_identical_prefix_b200_vs_reference_cuda"] = same
         b, c = res["runs"]["b200"], res["runs"]["reference_cuda"]
         res["tg_speedup_vs_reference_cuda"] = b["tg_tok_s"] / c["tg_tok_s"]
         res["pp_speedup_vs_reference_cuda"] = b["pp_tok_s"] / c["pp_tok_s"]
