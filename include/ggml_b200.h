@@ -378,6 +378,22 @@ B200_API b200_status  b200_rms_norm(b200_ctx * ctx, const b200_tensor * x, const
 B200_API int          b200_rms_norm_mul_supported(const b200_tensor * x, const b200_tensor * w, const b200_tensor * dst);
 B200_API b200_status  b200_rms_norm_mul(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * w, const b200_tensor * dst, float eps);
 
+/* RMS_NORM (+ MUL) folded into the MUL_MATs that read it (a decode step's attn_norm -> q/k/v and ffn_norm -> gate/up; the reference
+ * keeps them apart: norm.cu + quantize.cu + mmvq.cu). x is the UN-normalized src1; with one activation column on the TMA-staged
+ * mat-vec kernels the kernel normalizes the row in its own quantizer prologue, in the summation order of the stand-alone RMS_NORM
+ * kernel (same bits); otherwise the norm runs first, into y ([K, N] F32, rows y_nb1 bytes apart: the memory of the graph's MUL
+ * node), and the MUL_MATs read y. Either way the results are those of the nodes one after the other. w == NULL: no MUL. */
+typedef struct {
+    const float * w;      /* [K] per-channel norm weights (src of the MUL), 16-byte aligned, or NULL */
+    float         eps;
+    float *       y;      /* where RMS_NORM(x) * w goes when it has to be materialized */
+    size_t        y_nb1;
+} b200_norm;
+B200_API b200_status  b200_mul_mat_shared_src1_norm(b200_ctx * ctx, int n_ops, const b200_mul_mat_desc * descs, const void * const * src0s,
+                                                    const float * x, const b200_norm * norm, float * const * dsts);
+B200_API b200_status  b200_mul_mat_fused_norm(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * up, const void * gate, const float * x,
+                                              const b200_norm * norm, const b200_fusion * f, float * dst);
+
 /* GGML_OP_GET_ROWS (ggml-cpu/ops.cpp ggml_compute_forward_get_rows; ggml-cuda/getrows.cu): dst[:, i, j, k] = row ids[i, j, k] of
  * src0[:, :, j, k] as F32; src0 F32, F16 or one of the five quantized formats (dequantize_row_<type>, ggml-quants.c); ids I32 */
 B200_API int          b200_get_rows_supported(const b200_tensor * src0, const b200_tensor * ids, const b200_tensor * dst);

@@ -38,7 +38,8 @@ EXPORTS = [
     "b200_mul_mat_fused_supported", "b200_mul_mat_fused", "b200_mul_mat_id_fused_supported", "b200_mul_mat_id_fused",
     "b200_glu", "b200_add", "b200_mul", "b200_add_id",
     "b200_mul_mat_noalloc", "b200_mul_mat_noalloc_max_units",
-    "b200_rms_norm_supported", "b200_rms_norm", "b200_rms_norm_mul_supported", "b200_rms_norm_mul", "b200_attn_prep_supported", "b200_attn_prep", "b200_get_rows_supported", "b200_get_rows", "b200_rope_supported", "b200_rope",
+    "b200_rms_norm_supported", "b200_rms_norm", "b200_rms_norm_mul_supported", "b200_rms_norm_mul", "b200_attn_prep_supported", "b200_attn_prep",
+    "b200_mul_mat_shared_src1_norm", "b200_mul_mat_fused_norm", "b200_get_rows_supported", "b200_get_rows", "b200_rope_supported", "b200_rope",
     "b200_set_rows_supported", "b200_set_rows", "b200_cpy_supported", "b200_cpy", "b200_flash_attn_ext_supported", "b200_flash_attn_ext",
 ]
 
@@ -113,6 +114,11 @@ class Tensor(C.Structure):
         """a [K, M] weight matrix of ggml type `gtype` stored as bytes in `data` (torch uint8), rows contiguous"""
         rb = row_size(gtype, K)
         return cls(data.data_ptr(), gtype, (C.c_int64 * 4)(K, M, 1, 1), (C.c_size_t * 4)(BLOCK[gtype][1], rb, rb * M, rb * M))
+
+
+class Norm(C.Structure):
+    """b200_norm: the RMS_NORM (+ MUL) a b200_mul_mat_*_norm call applies to its src1"""
+    _fields_ = [("w", C.c_void_p), ("eps", C.c_float), ("y", C.c_void_p), ("y_nb1", C.c_size_t)]
 
 
 class RopeParams(C.Structure):
@@ -210,6 +216,8 @@ def lib() -> C.CDLL:
         L.b200_mul_mat_noalloc.argtypes = [vp, C.POINTER(MulMatDesc), vp, vp, vp]
         L.b200_mul_mat_noalloc_max_units.restype = sz
         L.b200_mul_mat_shared_src1.argtypes = [vp, ci, C.POINTER(MulMatDesc), C.POINTER(vp), vp, C.POINTER(vp)]
+        L.b200_mul_mat_shared_src1_norm.argtypes = [vp, ci, C.POINTER(MulMatDesc), C.POINTER(vp), vp, C.POINTER(Norm), C.POINTER(vp)]
+        L.b200_mul_mat_fused_norm.argtypes = [vp, C.POINTER(MulMatDesc), vp, vp, vp, C.POINTER(Norm), C.POINTER(Fusion), vp]
         L.b200_mul_mat_host.argtypes = [vp, C.POINTER(MulMatDesc), vp, ci, vp, vp]
         L.b200_mul_mat_id_supported.argtypes = [C.POINTER(MulMatIdDesc)]
         L.b200_mul_mat_id.argtypes = [vp, C.POINTER(MulMatIdDesc), vp, vp, vp, vp]
@@ -406,9 +414,10 @@ class Context:
         check(lib().b200_mul_mat(self.h, C.byref(desc), W.data_ptr(), X.data_ptr(), out.data_ptr()), "b200_mul_mat")
         return out
 
-    def mul_mat_shared(self, t: int, Ws, X, outs=None, dst_strides=None):
+    def mul_mat_shared(self, t: int, Ws, X, outs=None, dst_strides=None, norm_w=None, norm_eps=None):
         """several weight matrices against one X in one launch; dst_strides[i] = bytes between dst columns of output i
-        (default: contiguous [N, M_i])"""
+        (default: contiguous [N, M_i]). norm_eps: X is un-normalized, the call computes RMS_NORM(X) (* norm_w) first - inside the
+        mat-vec kernel where it can (b200_mul_mat_shared_src1_norm)"""
         torch = self.torch
         N, K = X.shape
         n = len(Ws)
@@ -425,6 +434,11 @@ class Context:
             outs = [torch.empty((N, M), dtype=torch.float32, device=X.device) for M in Ms]
         wp = (C.c_void_p * n)(*[W.data_ptr() for W in Ws])
         op = (C.c_void_p * n)(*[o.data_ptr() for o in outs])
+        if norm_eps is not None:
+            y = torch.empty_like(X)
+            nm = Norm(None if norm_w is None else norm_w.data_ptr(), norm_eps, y.data_ptr(), K * 4)
+            check(lib().b200_mul_mat_shared_src1_norm(self.h, n, descs, wp, X.data_ptr(), C.byref(nm), op), "b200_mul_mat_shared_src1_norm")
+            return outs
         check(lib().b200_mul_mat_shared_src1(self.h, n, descs, wp, X.data_ptr(), op), "b200_mul_mat_shared_src1")
         return outs
 
@@ -445,7 +459,8 @@ class Context:
         return out
 
     # ---- K7: fused epilogues and the stand-alone element-wise nodes
-    def mul_mat_fused(self, t: int, W_up, W_gate, X, up_bias=None, gate_bias=None, glu_op: int = GLU_NONE, alpha=1.702, limit=7.0, out=None):
+    def mul_mat_fused(self, t: int, W_up, W_gate, X, up_bias=None, gate_bias=None, glu_op: int = GLU_NONE, alpha=1.702, limit=7.0, out=None,
+                      norm_w=None, norm_eps=None):
         """one column: X float32 [1, K]; W_* uint8 [M, row_bytes]; biases float32 [M] -> float32 [1, M] in ONE launch"""
         torch = self.torch
         K = X.shape[-1]
@@ -455,6 +470,12 @@ class Context:
                    0, 4 * M, 4 * M)
         if out is None:
             out = torch.empty((1, M), dtype=torch.float32, device=X.device)
+        if norm_eps is not None:
+            y = torch.empty_like(X)
+            nm = Norm(None if norm_w is None else norm_w.data_ptr(), norm_eps, y.data_ptr(), K * 4)
+            check(lib().b200_mul_mat_fused_norm(self.h, C.byref(desc), W_up.data_ptr(), None if W_gate is None else W_gate.data_ptr(), X.data_ptr(),
+                                                C.byref(nm), C.byref(f), out.data_ptr()), "b200_mul_mat_fused_norm")
+            return out
         check(lib().b200_mul_mat_fused(self.h, C.byref(desc), W_up.data_ptr(), None if W_gate is None else W_gate.data_ptr(), X.data_ptr(),
                                        C.byref(f), out.data_ptr()), "b200_mul_mat_fused")
         return out

@@ -676,6 +676,12 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
                 p.act_main = act_main + (size_t) c0 * U * ACT_MAIN;
                 p.act_aux  = act_aux + (size_t) c0 * U * ACT_AUX;
             }
+            if (ctx->norm.on && x && ncols == 1 && !(ctx->dbg & 4) && p.x_vec && p.split.n_ranks <= 1 && (uintptr_t) ctx->norm.w % 16 == 0) {
+                // MvNorm: the row's RMS_NORM (+ MUL) in the K1 prologue - a GLU pair on the EPI kernel, or a plain launch on the lean kernel
+                const bool glu = ep && ep->glu >= 0, lean_run = !ep && lean && mv_lean_takes(type, 1, p, 1);
+                const int  nq  = lean_run ? std::min(MV_MAX_CONS, std::max(cfg.nw, U)) : cfg.nw;
+                if ((glu || lean_run) && U <= 4 * nq) { p.norm = ctx->norm; ctx->norm_used = true; }
+            }
             const int n_ctas = g < ctx->sm_count ? g : ctx->sm_count;
             if (ctx->prefetch_kb > 0) {
                 if (ctx->mem_gen != b200_mem_generation()) {  // an allocation went away: forget what was learned
@@ -947,6 +953,61 @@ b200_status b200_mul_mat_shared_src1(b200_ctx * ctx, int n_ops, const b200_mul_m
         if (all_empty) return split_empty_participant(ctx, n_ops, descs, dsts);
     }
     return mul_mat_impl(ctx, n_ops, descs, src0s, src1, dsts);
+}
+
+// RMS_NORM (+ MUL) in front of the MUL_MATs: the mat-vec kernel normalizes the one activation column in its own prologue (MvNorm);
+// whenever the call does not end up on such a kernel (more columns, another path) the norm runs as its own launch into norm->y first
+static b200_status norm_then(b200_ctx * ctx, const b200_mul_mat_desc & d, const float * x, const b200_norm * nm) {
+    b200_tensor tx = {}, tw = {}, ty = {};
+    tx.data = (void *) x; tx.type = B200_TYPE_F32;
+    tx.ne[0] = d.ne00; tx.ne[1] = d.ne11; tx.ne[2] = d.ne12; tx.ne[3] = d.ne13;
+    tx.nb[0] = 4; tx.nb[1] = d.nb11; tx.nb[2] = d.nb12; tx.nb[3] = d.nb13;
+    ty = tx; ty.data = nm->y;
+    ty.nb[1] = nm->y_nb1; ty.nb[2] = nm->y_nb1 * (size_t) d.ne11; ty.nb[3] = ty.nb[2] * (size_t) d.ne12;
+    if (!nm->w) return b200_rms_norm(ctx, &tx, &ty, nm->eps);
+    tw.data = (void *) nm->w; tw.type = B200_TYPE_F32;
+    tw.ne[0] = d.ne00; tw.ne[1] = tw.ne[2] = tw.ne[3] = 1;
+    tw.nb[0] = 4; tw.nb[1] = tw.nb[2] = tw.nb[3] = (size_t) d.ne00 * 4;
+    return b200_rms_norm_mul(ctx, &tx, &tw, &ty, nm->eps);
+}
+static bool norm_worth_trying(const b200_ctx * ctx, const b200_mul_mat_desc & d) {
+    return d.ne11 == 1 && d.ne12 == 1 && d.ne13 == 1 && d.ne00 % 256 == 0 && d.ne00 <= 16384 && ctx->force_path == B200_PATH_AUTO && !ctx->exact &&
+           ctx->split.n_ranks <= 1 && ctx->fuse_quant;
+}
+static b200_mul_mat_desc with_src1_rows(b200_mul_mat_desc d, size_t nb1) {
+    d.nb11 = nb1; d.nb12 = nb1 * (size_t) d.ne11; d.nb13 = d.nb12 * (size_t) d.ne12;
+    return d;
+}
+
+b200_status b200_mul_mat_shared_src1_norm(b200_ctx * ctx, int n_ops, const b200_mul_mat_desc * descs, const void * const * src0s, const float * x,
+                                          const b200_norm * nm, float * const * dsts) {
+    if (!ctx || !descs || !nm || !nm->y || n_ops < 1 || n_ops > 8 || nm->y_nb1 % 4) return fail(B200_ERR_ARG, "bad argument");
+    if (norm_worth_trying(ctx, descs[0])) {
+        ctx->norm = b200::MvNorm{ nm->w, nm->eps, 1 };
+        ctx->norm_used = false;
+        const b200_status st = b200_mul_mat_shared_src1(ctx, n_ops, descs, src0s, x, dsts);
+        ctx->norm.on = 0;
+        if (st != B200_OK || ctx->norm_used) return st;
+    }
+    if (b200_status st = norm_then(ctx, descs[0], x, nm)) return st;
+    b200_mul_mat_desc dn[8];
+    for (int i = 0; i < n_ops; i++) dn[i] = with_src1_rows(descs[i], nm->y_nb1);
+    return b200_mul_mat_shared_src1(ctx, n_ops, dn, src0s, nm->y, dsts);
+}
+
+b200_status b200_mul_mat_fused_norm(b200_ctx * ctx, const b200_mul_mat_desc * d, const void * up, const void * gate, const float * x, const b200_norm * nm,
+                                    const b200_fusion * f, float * dst) {
+    if (!ctx || !d || !nm || !nm->y || nm->y_nb1 % 4) return fail(B200_ERR_ARG, "bad argument");
+    if (norm_worth_trying(ctx, *d)) {
+        ctx->norm = b200::MvNorm{ nm->w, nm->eps, 1 };
+        ctx->norm_used = false;
+        const b200_status st = b200_mul_mat_fused(ctx, d, up, gate, x, f, dst);
+        ctx->norm.on = 0;
+        if (st != B200_OK || ctx->norm_used) return st;
+    }
+    if (b200_status st = norm_then(ctx, *d, x, nm)) return st;
+    const b200_mul_mat_desc dn = with_src1_rows(*d, nm->y_nb1);
+    return b200_mul_mat_fused(ctx, &dn, up, gate, nm->y, f, dst);
 }
 
 // ------------------------------------------------------------------------------------------------ K7: fused epilogues

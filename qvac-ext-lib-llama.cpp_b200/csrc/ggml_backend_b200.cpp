@@ -596,7 +596,14 @@ const ggml_tensor * bias_of(const ggml_tensor * add, const ggml_tensor * mm) {
 // K7 peephole (the reference's: ggml_cuda_can_fuse + ggml_cuda_should_fuse_mul_mat, ggml-cuda.cu:2020-2104, 3087-3115, 3404-3600):
 // node i is a one-column MUL_MAT / one-token MUL_MAT_ID. Recognises {mm, add, mm, add, GLU}, {mm, mm, GLU} and {mm, add} whose
 // intermediate results have no other consumer and runs them as ONE launch. Returns the number of nodes consumed (0: no fusion).
-int try_fuse_epilogue(be_ctx * c, ggml_cgraph * cgraph, int i) {
+// an RMS_NORM (+ MUL) whose only readers are the MUL_MATs about to be launched: they can take the un-normalized row and normalize it
+// themselves (b200_mul_mat_*_norm)
+struct norm_src {
+    const ggml_tensor * x0;   // the norm's input
+    b200_norm           n;
+};
+
+int try_fuse_epilogue(be_ctx * c, ggml_cgraph * cgraph, int i, const norm_src * nf = nullptr) {
     ggml_tensor * n0 = cgraph->nodes[i];
     const ggml_op mm = n0->op, bias_op = mm == GGML_OP_MUL_MAT ? GGML_OP_ADD : GGML_OP_ADD_ID;
     if (mm == GGML_OP_MUL_MAT ? n0->ne[1] != 1 : n0->ne[2] != 1) return 0;
@@ -658,13 +665,17 @@ int try_fuse_epilogue(be_ctx * c, ggml_cgraph * cgraph, int i) {
         d.nb1 = last->nb[1]; d.nb2 = last->nb[2]; d.nb3 = last->nb[3];
         if (bn) { f.bias_nb2 = bn->nb[2]; f.bias_nb3 = bn->nb[3]; }
         if (!b200_mul_mat_fused_supported(c->ctx, &d)) return 0;
+        if (nf) {
+            if (!glu || ranges_overlap(last, nf->x0)) return 0;
+            st = b200_mul_mat_fused_norm(c->ctx, &d, w->data, gate->src[0]->data, (const float *) nf->x0->data, &nf->n, &f, (float *) last->data);
+        } else
         st = b200_mul_mat_fused(c->ctx, &d, w->data, gate ? gate->src[0]->data : nullptr, (const float *) x->data, &f, (float *) last->data);
     } else {
         b200_mul_mat_id_desc d;
         if (!fill_mul_mat_id(up, &d)) return 0;
         d.nb1 = last->nb[1]; d.nb2 = last->nb[2];
         if (bn) f.bias_nb1 = bn->nb[1];
-        if (!b200_mul_mat_id_fused_supported(c->ctx, &d)) return 0;
+        if (nf || !b200_mul_mat_id_fused_supported(c->ctx, &d)) return 0;
         st = b200_mul_mat_id_fused(c->ctx, &d, w->data, gate ? gate->src[0]->data : nullptr, (const float *) x->data, (const int32_t *) up->src[2]->data, &f,
                                    (float *) last->data);
     }
@@ -773,19 +784,47 @@ int next_live(const be_ctx * c, const ggml_cgraph * cgraph, int from) {
     return -1;
 }
 
-// RMS_NORM at node i followed by MUL with a per-channel weight: one launch (build_norm's pair). Returns the number of nodes consumed.
-int try_fuse_norm_mul(be_ctx * c, ggml_cgraph * cgraph, int i) {
-    if (!c->fuse_f3 || i + 1 >= cgraph->n_nodes) return 0;
+bool try_fuse_attn_block(be_ctx * c, ggml_cgraph * cgraph, int i, const norm_src * nf = nullptr);
+int32_t use_count(const ggml_cgraph * cgraph, const ggml_tensor * t);
+
+// RMS_NORM at node i followed by MUL with a per-channel weight: one launch (build_norm's pair) - or none at all, when the only readers
+// of the result are the one-token MUL_MATs that follow (q/k/v of the attention block; the gate / up pair of a GLU FFN), which then
+// normalize the row themselves. Returns true when node i has been dealt with (the nodes consumed are marked done).
+bool try_fuse_norm_mul(be_ctx * c, ggml_cgraph * cgraph, int i) {
+    if (!c->fuse_f3 || i + 1 >= cgraph->n_nodes) return false;
     ggml_tensor * norm = cgraph->nodes[i], * mul = cgraph->nodes[i + 1];
-    if (mul->op != GGML_OP_MUL || c->done[i + 1] || !ggml_can_fuse(cgraph, i, { GGML_OP_RMS_NORM, GGML_OP_MUL })) return 0;
+    if (mul->op != GGML_OP_MUL || c->done[i + 1] || !ggml_can_fuse(cgraph, i, { GGML_OP_RMS_NORM, GGML_OP_MUL })) return false;
     const ggml_tensor * w = mul->src[0] == norm ? mul->src[1] : (mul->src[1] == norm ? mul->src[0] : nullptr);
-    if (!w || w == norm || !ggml_are_same_shape(mul, norm)) return 0;
+    if (!w || w == norm || !ggml_are_same_shape(mul, norm)) return false;
     const ggml_tensor * x = norm->src[0];
-    if (ranges_overlap(mul, w) || (ranges_overlap(mul, x) && mul->data != x->data)) return 0;
+    if (ranges_overlap(mul, w) || (ranges_overlap(mul, x) && mul->data != x->data)) return false;
     const b200_tensor bx = as_b200(x), bw = as_b200(w), bd = as_b200(mul);
-    if (!b200_rms_norm_mul_supported(&bx, &bw, &bd)) return 0;
+    if (!b200_rms_norm_mul_supported(&bx, &bw, &bd)) return false;
+    // the readers of the normalized row
+    const int jm = next_live(c, cgraph, i + 2);
+    if (jm >= 0 && c->fuse && cgraph->nodes[jm]->op == GGML_OP_MUL_MAT && cgraph->nodes[jm]->src[1] == mul && mul->ne[1] == 1 && ggml_is_contiguous(mul) &&
+        ggml_is_contiguous(x) && ggml_is_contiguous(w) && ggml_nelements(w) == mul->ne[0] && !(mul->flags & GGML_TENSOR_FLAG_OUTPUT) && mul->data != x->data) {
+        norm_src nf;
+        nf.x0 = x;
+        nf.n.w = (const float *) w->data; nf.n.eps = ggml_get_op_params_f32(norm, 0); nf.n.y = (float *) mul->data; nf.n.y_nb1 = mul->nb[1];
+        const int32_t uses = use_count(cgraph, mul);
+        if (uses == 3 && try_fuse_attn_block(c, cgraph, jm, &nf)) {
+            c->done[i + 1] = c->done[jm] = 1;
+            return true;
+        }
+        if (uses == 2 && c->fuse_epilogue) {
+            const int fused = try_fuse_epilogue(c, cgraph, jm, &nf);
+            if (fused > 0) {
+                g_fused_epilogues.fetch_add(1, std::memory_order_relaxed);
+                c->done[i + 1] = 1;
+                for (int k = 0; k < fused; k++) c->done[jm + k] = 1;
+                return true;
+            }
+        }
+    }
     CHECK_RUN(c, b200_rms_norm_mul(c->ctx, &bx, &bw, &bd, ggml_get_op_params_f32(norm, 0)));
-    return 2;
+    c->done[i + 1] = 1;
+    return true;
 }
 
 // ROPE(q) at node i, then - as the next nodes with work - ROPE(k), SET_ROWS(k cache <- rope(k)), SET_ROWS(v cache <- v): the attention
@@ -837,7 +876,7 @@ bool sole_contiguous_view_of(const ggml_cgraph * cgraph, const ggml_tensor * t, 
 // from there. The graph allocator gives Kcur the memory of Qcur (dead after ROPE(q)), so the projections cannot simply be hoisted
 // into one launch at their graph addresses; nothing but the two ROPEs / the V store reads them (checked), so they never need to exist
 // there. Returns true when the seven nodes have been run (the six followers are marked done).
-bool try_fuse_attn_block(be_ctx * c, ggml_cgraph * cgraph, int i) {
+bool try_fuse_attn_block(be_ctx * c, ggml_cgraph * cgraph, int i, const norm_src * nf) {
     if (!c->fuse || !c->fuse_f3 || !f3_on() || exact_mode()) return false;
     int j[7] = { i };
     for (int k = 1; k < 7; k++) { j[k] = next_live(c, cgraph, j[k - 1] + 1); if (j[k] < 0) return false; }
@@ -862,7 +901,7 @@ bool try_fuse_attn_block(be_ctx * c, ggml_cgraph * cgraph, int i) {
     // outputs that do land at their graph addresses: rope(q), rope(k), the cache rows. They are written at ROPE(q)'s position in the
     // order, after every MUL_MAT of the block has completed: the block's inputs (src1, positions, indices) must not be among them
     const ggml_tensor * outs[4] = { rq, rk, sk, sv };
-    const ggml_tensor * ins[6] = { mq->src[1], rq->src[1], rq->src[2], sk->src[1], sv->src[1], nullptr };
+    const ggml_tensor * ins[6] = { mq->src[1], rq->src[1], rq->src[2], sk->src[1], sv->src[1], nf ? nf->x0 : nullptr };
     for (const ggml_tensor * o : outs) {
         for (const ggml_tensor * in : ins) if (in && ranges_overlap(o, in)) return false;
         for (const ggml_tensor * o2 : outs) if (o != o2 && ranges_overlap(o, o2)) return false;
@@ -890,7 +929,8 @@ bool try_fuse_attn_block(be_ctx * c, ggml_cgraph * cgraph, int i) {
     if (rq->src[2]) ff = as_b200(rq->src[2]);
     const b200_rope_params rp = rope_params_of(rq);
     if (!b200_attn_prep_supported(&q, &qd, &k, &kd, &pos, rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc)) return false;
-    CHECK_RUN(c, b200_mul_mat_shared_src1(c->ctx, 3, d, w, (const float *) mq->src[1]->data, o));
+    if (nf) CHECK_RUN(c, b200_mul_mat_shared_src1_norm(c->ctx, 3, d, w, (const float *) nf->x0->data, &nf->n, o));
+    else    CHECK_RUN(c, b200_mul_mat_shared_src1(c->ctx, 3, d, w, (const float *) mq->src[1]->data, o));
     CHECK_RUN(c, b200_attn_prep(c->ctx, &q, &qd, &k, &kd, &pos, rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc));
     for (int k2 = 1; k2 < 7; k2++) c->done[j[k2]] = 1;
     return true;
@@ -977,8 +1017,7 @@ ggml_status run_nodes(be_ctx * c, ggml_cgraph * cgraph) {
             run_add_id(c, node);
         } else if (is_f3_op(node->op) && f3_ok(node)) {
             if (node->op == GGML_OP_RMS_NORM) {
-                const int fused = try_fuse_norm_mul(c, cgraph, i);
-                if (fused > 0) { i += fused - 1; continue; }
+                if (try_fuse_norm_mul(c, cgraph, i)) continue;
             } else if (node->op == GGML_OP_ROPE && try_fuse_attn_prep(c, cgraph, i)) {
                 continue;
             }

@@ -76,6 +76,8 @@ struct b200_ctx {
     int          tc_min_cols = 9, tc_max_cols = 16;
     uint32_t *   tc_turn = nullptr;            // per-tile turn counters of its split-K accumulation
     const void * tc_act_x = nullptr; size_t tc_act_rs = 0; int64_t tc_act_N = 0, tc_act_K = 0; const void * tc_act_buf = nullptr;
+    b200::MvNorm norm = {};                     // b200_mul_mat_*_norm: the RMS_NORM (+ MUL) the next one-column mat-vec launch applies to its src1
+    bool         norm_used = false;             // ... and whether a launch took it
     void *       fa_ws = nullptr; size_t fa_ws_size = 0;   // FLASH_ATTN_EXT: partial (max, sum, accumulator) of the KV splits (ops.cu)
     int          moe_tile_min  = 48;           // MUL_MAT_ID: one tile GEMM per expert from this many pairs per expert on average (GGML_B200_MOE_TILE_MIN; 0 = never)
     int          moe_group_min = 2;            // MUL_MAT_ID: group by expert (tensor-core mat-vec) from this many pairs per expert on

@@ -241,6 +241,15 @@ struct MvNext {
     int             glu;              // the predicted launch is a K7 gate / up pair: a group is rows of w[0] AND the same rows of w[1]
 };
 
+// RMS_NORM (+ MUL by per-channel weights) of the ONE activation column, done by the K1 prologue of the mat-vec kernel before it
+// quantizes: x is then the un-normalized row. Needs fuse_quant, one column, and every unit of the row in the prologue's single
+// round (U <= 4 x quantizing warps). Summation order: common.cuh unit_sumsq / rms_scale - the bits of rms_norm_units_kernel.
+struct MvNorm {
+    const float * w;    // nullptr: no MUL
+    float         eps;
+    int           on;
+};
+
 struct MvParams {
     MvMat           mat[MV_MAX_MATS];
     int             n_mats;
@@ -264,6 +273,7 @@ struct MvParams {
     SplitGeom       geom;     // split.ll: who owns which rows of mat[i]
     MvNext          next;
     MvEpi           epi;
+    MvNorm          norm;
     // debug timeline (b200_ctx_trace): 8 x u64 per CTA at trace + blockIdx.x*8: globaltimer ns of [0] CTA start, [1] first and
     // [2] last weight copy issued, [3] consumer warp 0 past griddepcontrol.wait, [4] activations quantized, [5] first stage
     // landed, [6] consumer warp 0 done, [7] SM id. nullptr = off.
@@ -273,6 +283,7 @@ struct MvParams {
 
 // one-column plain launches of these formats run on mv_lean_kernel, which consumes ring stages in pairs (wants 4 stages)
 bool mv_lean_type(int type);
+bool mv_lean_takes(int type, int ncols, const MvParams & p, int n_pairs);   // mv_fast_launch would run this launch on mv_lean_kernel
 constexpr int MV_LEAN_MAX_COLS = 4;
 // smem bytes needed by the fast kernel for a configuration
 size_t mv_fast_smem(int type, int U, int ncols, int n_cons, int n_stages);

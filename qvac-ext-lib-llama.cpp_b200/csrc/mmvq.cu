@@ -354,7 +354,7 @@ __device__ __forceinline__ void unit_dot(uint32_t w, uint32_t am, uint32_t ax, u
 //   [ring: NWC*NS*stage_bytes]
 // ------------------------------------------------------------------------------------------------
 
-constexpr int MV_HDR_BYTES = 64;
+constexpr int MV_HDR_BYTES = 64 + 256;   // act barrier | 64 unit sums of a fused RMS_NORM (MvNorm)
 
 __host__ __device__ inline size_t mv_align(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
@@ -372,6 +372,32 @@ size_t mv_fast_smem(int type, int U, int ncols, int n_cons, int n_stages) {
 
 __device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// MvNorm inside the fused K1 prologue: v[b] = unit t0 + b * stride of the row (valid while < n_units). Every quantizing warp calls it
+// exactly once (also a warp without a unit: the barrier counts it).
+__device__ __forceinline__ void norm_units(float (&v)[4][8], const MvNorm & nm, int t0, int stride, int n_units, int lane, float * part, int n_threads) {
+    float wv[4][8];
+#pragma unroll
+    for (int b = 0; b < 4; b++) {
+        const int t = t0 + b * stride;
+        if (t < n_units) {
+            const float sq = unit_sumsq(v[b]);
+            if (lane == 0) part[t] = sq;
+            if (nm.w) {
+                const float4 e = __ldg((const float4 *) nm.w + t * 64 + lane * 2), f = __ldg((const float4 *) nm.w + t * 64 + lane * 2 + 1);
+                wv[b][0] = e.x; wv[b][1] = e.y; wv[b][2] = e.z; wv[b][3] = e.w; wv[b][4] = f.x; wv[b][5] = f.y; wv[b][6] = f.z; wv[b][7] = f.w;
+            }
+        }
+    }
+    asm volatile("bar.sync 3, %0;" ::"r"(n_threads) : "memory");
+    const float scale = rms_scale(part, n_units, nm.eps);
+#pragma unroll
+    for (int b = 0; b < 4; b++) {
+        if (t0 + b * stride < n_units) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) { v[b][i] = v[b][i] * scale; if (nm.w) v[b][i] *= wv[b][i]; }
+        }
+    }
+}
 __device__ __forceinline__ void bar_sync_named(int id, int n_threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n_threads) : "memory"); }
 __device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok;
@@ -560,7 +586,8 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
         // fused K1: unit (c, u) of the activations, F32 global -> unit record in shared memory. Up to 4 units per warp are
         // loaded before the first is quantized, so the L2 round trips overlap instead of chaining
         const int n_tasks = NC * U;
-        for (int t0 = w; t0 < n_tasks; t0 += 4 * NWC) {
+        const bool norm_on = EPI && p.norm.on;   // one column, n_tasks <= 4 * NWC (the launcher's condition): a single round
+        for (int t0 = w; t0 < n_tasks || (norm_on && t0 == w); t0 += 4 * NWC) {
             float v[4][8];
 #pragma unroll
             for (int b = 0; b < 4; b++) {
@@ -583,6 +610,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
                 asm volatile("" : "+f"(v[0][0]), "+f"(v[0][7]));
                 MV_TRACE(7);
             }
+            if constexpr (EPI) { if (norm_on) norm_units(v, p.norm, t0, NWC, n_tasks, lane, (float *) (smem + 64), NWC * 32); }
 #pragma unroll
             for (int b = 0; b < 4; b++) {
                 const int t = t0 + b * NWC;
@@ -871,7 +899,8 @@ __device__ __forceinline__ void unit_dot2(uint32_t w0, uint32_t w1, uint32_t am,
 
 // LL: row split with the flagged-payload exchange (its own instantiation: the plain kernel keeps its registers). BIAS: the ADD of a
 // K7 epilogue without GLU (attn_output / ffn_down + residual in a decode graph): mat.bias[row] is added before the store
-template <int TYPE, int NC, bool LL, bool BIAS = false>
+// NORM: MvNorm - the RMS_NORM + MUL in front of the q/k/v projections happens in this kernel's K1 prologue
+template <int TYPE, int NC, bool LL, bool BIAS = false, bool NORM = false>
 __global__ void __launch_bounds__(32 * (MV_MAX_CONS + 1), 1)
 mv_lean_kernel(const __grid_constant__ MvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -992,7 +1021,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     if (p.fuse_quant) {
         constexpr int n_tasks_per_col = 0; (void) n_tasks_per_col;
         const int n_tasks = NC * U;   // task t = (column t / U, unit t % U); the records of column c start at c * U
-        for (int t0 = qw; t0 < n_tasks; t0 += 4 * NQ) {
+        for (int t0 = qw; t0 < n_tasks || (NORM && t0 == qw); t0 += 4 * NQ) {   // NORM: n_tasks <= 4 * NQ, every warp takes part once
             float v[4][8];
 #pragma unroll
             for (int b = 0; b < 4; b++) {
@@ -1015,6 +1044,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
                 asm volatile("" : "+f"(v[0][0]), "+f"(v[0][7]));
                 MV_TRACE(7);
             }
+            if constexpr (NORM) norm_units(v, p.norm, t0, NQ, n_tasks, lane, (float *) (smem + 64), NQ * 32);
 #pragma unroll
             for (int b = 0; b < 4; b++) {
                 const int t = t0 + b * NQ;
@@ -1115,7 +1145,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     }
 }
 
-template <int TYPE, int NC, bool LL, bool BIAS = false>
+template <int TYPE, int NC, bool LL, bool BIAS = false, bool NORM = false>
 static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t smem, cudaStream_t st) {
     MvParams p = p_in;
     p.n_helpers = 0;
@@ -1127,9 +1157,9 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS, NORM>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
@@ -1147,15 +1177,16 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
     }
     cfg.attrs    = attr;
     cfg.numAttrs = na;
-    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE, NC, LL, BIAS>, p);
+    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE, NC, LL, BIAS, NORM>, p);
 }
 
 // the launch can take the lean kernel: one column, plain MUL_MAT, no exchange, no epilogue, an even ring
 template <int TYPE>
 static cudaError_t mv_lean_launch_n(int nc, const MvParams & p, int n_ctas, size_t smem, cudaStream_t st) {
     for (int i = 0; i < p.n_mats; i++) {
-        if (p.mat[i].bias) return nc == 1 && p.split.n_ranks <= 1 ? mv_lean_launch_t<TYPE, 1, false, true>(p, n_ctas, smem, st) : cudaErrorInvalidValue;
+        if (p.mat[i].bias) return nc == 1 && p.split.n_ranks <= 1 && !p.norm.on ? mv_lean_launch_t<TYPE, 1, false, true>(p, n_ctas, smem, st) : cudaErrorInvalidValue;
     }
+    if (p.norm.on) return nc == 1 && p.split.n_ranks <= 1 && p.fuse_quant ? mv_lean_launch_t<TYPE, 1, false, false, true>(p, n_ctas, smem, st) : cudaErrorInvalidValue;
     if (p.split.n_ranks > 1) {
         switch (nc) {
             case 1: return mv_lean_launch_t<TYPE, 1, true>(p, n_ctas, smem, st);
@@ -1175,6 +1206,9 @@ static cudaError_t mv_lean_launch_n(int nc, const MvParams & p, int n_ctas, size
 }
 
 bool mv_lean_type(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0; }  // formats with a two-unit dot product
+
+static bool mv_lean_ok(int type, int ncols, const MvParams & p, int n_pairs);
+bool mv_lean_takes(int type, int ncols, const MvParams & p, int n_pairs) { return mv_lean_ok(type, ncols, p, n_pairs); }
 
 static bool mv_lean_ok(int type, int ncols, const MvParams & p, int n_pairs) {
     if (!mv_lean_type(type) || ncols < 1 || ncols > MV_LEAN_MAX_COLS || n_pairs != 1 || p.ids.ids || (p.split.n_ranks > 1 && !p.split.ll) || p.epi.glu || (p.n_stages & 1) || (p.dbg & 1)) return false;
@@ -1213,6 +1247,7 @@ template <int TYPE, int NC>
 static cudaError_t mv_fast_launch_t(const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
     bool epi = p.epi.glu != 0;
     for (int i = 0; i < p.n_mats; i++) epi = epi || p.mat[i].bias != nullptr;
+    if (p.norm.on && !epi) return cudaErrorInvalidValue;   // MvNorm: the lean kernel's NORM instantiation or an EPI one (api.cu decides)
     if (epi) {  // K7: one column; the wide CTA shape (or the 8-warp one for rows that leave less shared memory)
         if constexpr (NC == 1) {
             if (p.n_cons > 8) return mv_fast_launch_w<TYPE, 1, 1, true>(p, n_ctas, n_pairs, smem, st);

@@ -53,6 +53,48 @@ __device__ __forceinline__ float block_sum(float v, float * part) {   // all thr
     float t = (int) (threadIdx.x & 31) < nw ? part[threadIdx.x & 31] : 0.0f;
     return warp_sum(t);
 }
+// rows of 256 .. 16384 elements, a multiple of 256, 16-byte aligned (every transformer width): the canonical summation order of
+// common.cuh unit_sumsq / rms_scale, which the mat-vec kernels reproduce when they normalize their own activations (mmvq.cu MvNorm).
+// blockDim = 32 * min(32, units): a warp holds at most two units.
+__global__ void __launch_bounds__(1024) rms_norm_units_kernel(const NormP p) {
+    __shared__ float part[64];
+    pdl_prologue();
+    const int64_t row = blockIdx.x;
+    const int64_t i1 = row % p.s.ne[1], i2 = (row / p.s.ne[1]) % p.s.ne[2], i3 = row / (p.s.ne[1] * p.s.ne[2]);
+    const char * xr = p.x + i1 * p.s.nb[1] + i2 * p.s.nb[2] + i3 * p.s.nb[3];
+    char *       yr = p.y + i1 * p.d.nb[1] + i2 * p.d.nb[2] + i3 * p.d.nb[3];
+    const char * wr = p.wd ? p.wd + (i1 % p.w.ne[1]) * p.w.nb[1] + (i2 % p.w.ne[2]) * p.w.nb[2] + (i3 % p.w.ne[3]) * p.w.nb[3] : nullptr;
+    const int U = (int) (p.s.ne[0] >> 8), nw = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float v[2][8], wv[2][8];
+#pragma unroll
+    for (int b = 0; b < 2; b++) {
+        const int u = warp + b * nw;
+        if (u < U) {
+            const float4 a = ((const float4 *) xr)[u * 64 + lane * 2], c = ((const float4 *) xr)[u * 64 + lane * 2 + 1];
+            v[b][0] = a.x; v[b][1] = a.y; v[b][2] = a.z; v[b][3] = a.w; v[b][4] = c.x; v[b][5] = c.y; v[b][6] = c.z; v[b][7] = c.w;
+            if (wr) {
+                const float4 e = ((const float4 *) wr)[u * 64 + lane * 2], f = ((const float4 *) wr)[u * 64 + lane * 2 + 1];
+                wv[b][0] = e.x; wv[b][1] = e.y; wv[b][2] = e.z; wv[b][3] = e.w; wv[b][4] = f.x; wv[b][5] = f.y; wv[b][6] = f.z; wv[b][7] = f.w;
+            }
+            const float sq = unit_sumsq(v[b]);
+            if (lane == 0) part[u] = sq;
+        }
+    }
+    __syncthreads();
+    const float scale = rms_scale(part, U, p.eps);
+#pragma unroll
+    for (int b = 0; b < 2; b++) {
+        const int u = warp + b * nw;
+        if (u < U) {
+            float o[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) { o[i] = v[b][i] * scale; if (wr) o[i] *= wv[b][i]; }
+            ((float4 *) yr)[u * 64 + lane * 2]     = make_float4(o[0], o[1], o[2], o[3]);
+            ((float4 *) yr)[u * 64 + lane * 2 + 1] = make_float4(o[4], o[5], o[6], o[7]);
+        }
+    }
+}
+
 template <bool VEC>   // VEC: rows are 16-byte aligned, ne0 % 4 == 0 and a row fits the CTA's registers (4 float4 per thread)
 __global__ void __launch_bounds__(1024) rms_norm_kernel(const NormP p) {
     __shared__ float part[32];
@@ -308,22 +350,29 @@ struct FaP {
     float *  ws;       // partials of the KV splits: [row][split][2 + D] = running maximum, sum, accumulator
     unsigned * cnt;    // arrivals per row; the CTA that completes a row merges its splits and puts the counter back to 0
 };
-constexpr int FA_WARPS = 8, FA_U = 4;
+constexpr int FA_WARPS = 8, FA_U = 8;   // a warp keeps 8 KV positions in flight (K and V rows as packed halves: E registers per position)
 
+template <int E> struct HPack { uint32_t w[E / 2]; };
 template <int E>
-__device__ __forceinline__ void load_halfs(const char * p, float * out) {
+__device__ __forceinline__ HPack<E> load_pack(const char * p) {   // E halves, E * 2 bytes aligned
+    HPack<E> r;
     if constexpr (E == 2) {
-        const __half2 h = *(const __half2 *) p;
-        out[0] = __low2float(h); out[1] = __high2float(h);
+        r.w[0] = *(const uint32_t *) p;
     } else if constexpr (E == 4) {
         const uint2 u = *(const uint2 *) p;
-        const __half2 a = *(const __half2 *) &u.x, b = *(const __half2 *) &u.y;
-        out[0] = __low2float(a); out[1] = __high2float(a); out[2] = __low2float(b); out[3] = __high2float(b);
+        r.w[0] = u.x; r.w[1] = u.y;
     } else {
         const uint4 u = *(const uint4 *) p;
-        const __half2 a = *(const __half2 *) &u.x, b = *(const __half2 *) &u.y, c = *(const __half2 *) &u.z, d = *(const __half2 *) &u.w;
-        out[0] = __low2float(a); out[1] = __high2float(a); out[2] = __low2float(b); out[3] = __high2float(b);
-        out[4] = __low2float(c); out[5] = __high2float(c); out[6] = __low2float(d); out[7] = __high2float(d);
+        r.w[0] = u.x; r.w[1] = u.y; r.w[2] = u.z; r.w[3] = u.w;
+    }
+    return r;
+}
+template <int E>
+__device__ __forceinline__ void unpack(const HPack<E> & h, float * out) {
+#pragma unroll
+    for (int i = 0; i < E / 2; i++) {
+        const __half2 v = *(const __half2 *) &h.w[i];
+        out[2 * i] = __low2float(v); out[2 * i + 1] = __high2float(v);
     }
 }
 
@@ -364,7 +413,8 @@ __global__ void __launch_bounds__(FA_WARPS * 32) fa_kernel(const FaP p) {
 
     const int64_t c0 = (int64_t) blockIdx.y * p.chunk, c1 = min(c0 + p.chunk, p.k.ne[1]);
     for (int64_t base = c0 + warp * FA_U; base < c1; base += FA_WARPS * FA_U) {
-        float s[FA_U], mv[FA_U], kf[FA_U][E], vf[FA_U][E];
+        float s[FA_U], mv[FA_U];
+        HPack<E> kp[FA_U], vp[FA_U];
 #pragma unroll
         for (int u = 0; u < FA_U; u++) {
             const int64_t ic = base + u;
@@ -373,8 +423,8 @@ __global__ void __launch_bounds__(FA_WARPS * 32) fa_kernel(const FaP p) {
 #pragma unroll
         for (int u = 0; u < FA_U; u++) {
             if (mv[u] != -INFINITY) {   // warp-uniform
-                load_halfs<E>(kb + (base + u) * p.k.nb[1], kf[u]);
-                load_halfs<E>(vb + (base + u) * p.v.nb[1], vf[u]);
+                kp[u] = load_pack<E>(kb + (base + u) * p.k.nb[1]);
+                vp[u] = load_pack<E>(vb + (base + u) * p.v.nb[1]);
             }
         }
         float mx = -INFINITY;
@@ -382,12 +432,25 @@ __global__ void __launch_bounds__(FA_WARPS * 32) fa_kernel(const FaP p) {
         for (int u = 0; u < FA_U; u++) {
             s[u] = -INFINITY;
             if (mv[u] != -INFINITY) {
-                float t = 0.0f;
+                float kf[E], t = 0.0f;
+                unpack<E>(kp[u], kf);
 #pragma unroll
-                for (int e = 0; e < E; e++) t += qf[e] * kf[u][e];
-                t = warp_sum(t);
-                if (p.softcap != 0.0f) t = p.softcap * tanhf(t);
-                s[u] = t + mv[u];
+                for (int e = 0; e < E; e++) t += qf[e] * kf[e];
+                s[u] = t;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {   // the FA_U reductions side by side
+#pragma unroll
+            for (int u = 0; u < FA_U; u++) s[u] += __shfl_xor_sync(0xffffffffu, s[u], o);
+        }
+#pragma unroll
+        for (int u = 0; u < FA_U; u++) {
+            if (mv[u] != -INFINITY) {
+                if (p.softcap != 0.0f) s[u] = p.softcap * tanhf(s[u]);
+                s[u] += mv[u];
+            } else {
+                s[u] = -INFINITY;
             }
             mx = fmaxf(mx, s[u]);
         }
@@ -401,9 +464,11 @@ __global__ void __launch_bounds__(FA_WARPS * 32) fa_kernel(const FaP p) {
         for (int u = 0; u < FA_U; u++) {
             if (s[u] != -INFINITY) {
                 const float pr = expf(s[u] - Mn);
+                float vf[E];
+                unpack<E>(vp[u], vf);
                 S += pr;
 #pragma unroll
-                for (int e = 0; e < E; e++) acc[e] += pr * vf[u][e];
+                for (int e = 0; e < E; e++) acc[e] += pr * vf[e];
             }
         }
     }
@@ -508,6 +573,11 @@ static b200_status rms_norm_run(b200_ctx * ctx, const b200_tensor * x, const b20
     for (int i = 1; i < 4 && vec; i++) vec = x->nb[i] % 16 == 0 && dst->nb[i] % 16 == 0 && (!w || w->nb[i] % 16 == 0);
     const int threads = (int) std::min<int64_t>(1024, std::max<int64_t>(32, ((vec ? n / 4 : n) + 31) / 32 * 32));
     OPS_PROLOGUE(ctx);
+    if (vec && n % 256 == 0) {   // the canonical order (n <= 16384: at most 64 units)
+        CU(b200_launch(ctx, rms_norm_units_kernel, dim3((unsigned) rows), dim3(32 * (unsigned) std::min<int64_t>(32, n / 256)), 0, p));
+        ctx->launches++;
+        return B200_OK;
+    }
     CU(vec ? b200_launch(ctx, rms_norm_kernel<true>, dim3((unsigned) rows), dim3(threads), 0, p)
            : b200_launch(ctx, rms_norm_kernel<false>, dim3((unsigned) rows), dim3(threads), 0, p));
     ctx->launches++;
@@ -727,15 +797,15 @@ b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b20
     p.n_head_log2 = 1u << (uint32_t) floorf(log2f((float) n_head));
     p.m0 = powf(2.0f, -max_bias / (float) p.n_head_log2);
     p.m1 = powf(2.0f, -(max_bias / 2.0f) / (float) p.n_head_log2);
-    // KV splits (decode: a few dozen rows, one per head): about two CTAs per SM, no fewer than 32 positions (one round of the 8 warps)
-    // per split; the splits of a row are merged by the last of its CTAs to finish
+    // KV splits (decode: a few dozen rows, one per head): about two CTAs per SM, no fewer than 128 positions (two rounds of the 8 warps'
+    // 8 positions each) per split; the splits of a row are merged by the last of its CTAs to finish
     int nsplit = 1;
     const int64_t n_kv = k->ne[1];
-    if (rows < 2 * ctx->sm_count && rows <= (int64_t) (FA_CNT_BYTES / 4) && n_kv >= 64) {
-        nsplit = (int) std::min<int64_t>(std::min<int64_t>((2 * (int64_t) ctx->sm_count + rows - 1) / rows, n_kv / 32), 64);
+    if (rows < 2 * ctx->sm_count && rows <= (int64_t) (FA_CNT_BYTES / 4) && n_kv >= 256) {
+        nsplit = (int) std::min<int64_t>(std::min<int64_t>((2 * (int64_t) ctx->sm_count + rows - 1) / rows, (n_kv + 127) / 128), 64);
         if (nsplit < 1) nsplit = 1;
     }
-    p.chunk  = nsplit == 1 ? std::max<int64_t>(n_kv, 1) : ((n_kv + nsplit - 1) / nsplit + 31) / 32 * 32;
+    p.chunk  = nsplit == 1 ? std::max<int64_t>(n_kv, 1) : ((n_kv + nsplit - 1) / nsplit + 63) / 64 * 64;
     if (nsplit > 1) nsplit = (int) ((n_kv + p.chunk - 1) / p.chunk);   // no empty splits
     p.nsplit = nsplit;
     p.ws     = nullptr;

@@ -54,6 +54,33 @@ def test_rms_norm_mul_is_the_two_nodes(ctx, shape):
     assert _nmse(ref.cpu().numpy(), fused.cpu().numpy()) < 1e-12
 
 
+@pytest.mark.parametrize("t", [Q4_K, Q4_0, Q8_0, Q6_K])
+@pytest.mark.parametrize("K,N", [(4096, 1), (2048, 1), (4096, 3), (16384, 1)])
+def test_norm_folded_into_the_mat_vec_is_the_nodes(pkg, ctx, refq, t, K, N):
+    """attn_norm -> q/k/v and ffn_norm -> gate/up with the RMS_NORM + MUL inside the mat-vec kernel's quantizer prologue (one column,
+    formats of the lean / GLU kernels) or as its own launch in front (everything else): bit-identical to norm, mul, MUL_MAT(s), GLU
+    node by node - the kernels share one summation order (common.cuh unit_sumsq)"""
+    import torch
+    rng = np.random.default_rng(K + N + t)
+    Ms = [512, 128, 128]
+    Ws = [torch.from_numpy(refq.quantize_weights(t, rng.normal(0, 1, (M, K)).astype(np.float32) / 8)).cuda() for M in Ms]
+    x = torch.from_numpy(rng.normal(0, 2, (N, K)).astype(np.float32)).cuda()
+    w = torch.from_numpy(rng.normal(1, 0.2, K).astype(np.float32)).cuda()
+    xn = ctx.rms_norm_mul(x.reshape(1, 1, N, K), w, 1e-5).reshape(N, K)
+    n0 = ctx.launches()
+    fused = ctx.mul_mat_shared(t, Ws, x, norm_w=w, norm_eps=1e-5)
+    n_fused = ctx.launches() - n0
+    plain = ctx.mul_mat_shared(t, Ws, xn)
+    for a, b in zip(fused, plain):
+        assert torch.equal(a, b)
+    if N == 1 and t in (Q4_K, Q4_0, Q8_0) and K <= 16384:
+        assert n_fused == 1, n_fused          # the norm really ran inside the mat-vec launch
+    if N == 1:
+        g = ctx.mul_mat_fused(t, Ws[1], Ws[2], x, glu_op=pkg.GLU_SWIGLU, norm_w=w, norm_eps=1e-5)
+        g_ref = ctx.mul_mat_fused(t, Ws[1], Ws[2], xn, glu_op=pkg.GLU_SWIGLU)
+        assert torch.equal(g, g_ref)
+
+
 @pytest.mark.parametrize("cache_dtype", ["float16", "float32"])
 @pytest.mark.parametrize("n_tok", [1, 5])
 def test_attn_prep_is_the_four_nodes(ctx, n_tok, cache_dtype):
