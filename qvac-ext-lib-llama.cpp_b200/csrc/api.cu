@@ -118,6 +118,7 @@ b200_status b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     if (const char * s = getenv("GGML_B200_WEIGHT_CACHE")) c->weight_cache = atoi(s) != 0;
     if (const char * s = getenv("GGML_B200_FUSE_QUANT")) c->fuse_quant = atoi(s) != 0;
     if (const char * s = getenv("GGML_B200_PREFETCH_KB")) c->prefetch_kb = atoi(s);
+    if (const char * s = getenv("GGML_B200_FA_PREFETCH_KB")) c->fa_prefetch_kb = atoi(s);
     if (const char * s = getenv("GGML_B200_DBG")) c->dbg = atoi(s);
     if (const char * s = getenv("GGML_B200_MMA_MIN")) c->mma_min_cols = atoi(s);
     if (const char * s = getenv("GGML_B200_MMA_WARPS")) c->mma_warps = atoi(s);

@@ -82,6 +82,8 @@ struct be_ctx {
     };
     std::map<uint64_t, std::vector<cached_graph>> graphs;  // hash -> entries
     size_t     n_graphs    = 0;
+    uint64_t   last_hash   = 0;                    // bucket of the cgraph computed last
+    bool       last_hash_valid = false;
     uint64_t   graph_clock = 0;
     uint64_t   graph_replays = 0, graph_captures = 0;
     void *     blk_scratch = nullptr;              // try_fuse_attn_block: q / k / v projections of the layer in flight
@@ -1033,37 +1035,46 @@ ggml_status run_nodes(be_ctx * c, ggml_cgraph * cgraph) {
 // ---- CUDA-graph replay. The key of a cgraph is everything a launch depends on: per node the op, its parameters, shape, strides
 // and address, and shape, strides and address of every source (ggml_graph_node_properties, ggml-cuda.cu:2870-2935 does the same).
 // Weight CONTENTS are not part of it: kernels read them through the same pointers on every replay.
-void graph_key(const ggml_cgraph * cgraph, std::vector<uint64_t> & key, int * n_run, bool * capturable) {
+// (runs once per graph_compute, i.e. once per token: raw stores into a buffer that never shrinks, ~50 words per node)
+constexpr size_t KEY_WORDS_PER_NODE = 1 + 10 + GGML_MAX_OP_PARAMS / sizeof(uint64_t) + GGML_MAX_SRC * 10;
+size_t graph_key(const ggml_cgraph * cgraph, std::vector<uint64_t> & buf, int * n_run, bool * capturable) {
     *n_run = 0;
     *capturable = true;
-    key.clear();
+    const size_t need = (size_t) cgraph->n_nodes * KEY_WORDS_PER_NODE;
+    if (buf.size() < need) buf.resize(need);
+    uint64_t * o = buf.data();
     auto put_tensor = [&](const ggml_tensor * t) {
-        key.push_back((uint64_t) (uintptr_t) t->data);
-        key.push_back((uint64_t) t->type);
-        for (int d = 0; d < GGML_MAX_DIMS; d++) { key.push_back((uint64_t) t->ne[d]); key.push_back((uint64_t) t->nb[d]); }
+        *o++ = (uint64_t) (uintptr_t) t->data;
+        *o++ = (uint64_t) t->type;
+        memcpy(o, t->ne, sizeof(t->ne)); o += GGML_MAX_DIMS;
+        memcpy(o, t->nb, sizeof(t->nb)); o += GGML_MAX_DIMS;
     };
+    static_assert(sizeof(((ggml_tensor *) nullptr)->ne) == GGML_MAX_DIMS * 8 && sizeof(((ggml_tensor *) nullptr)->nb) == GGML_MAX_DIMS * 8, "ne / nb are 64-bit");
     for (int i = 0; i < cgraph->n_nodes; i++) {
         const ggml_tensor * n = cgraph->nodes[i];
         if (is_noop(n)) continue;
         (*n_run)++;
-        key.push_back((uint64_t) n->op | ((uint64_t) n->flags << 32));
+        *o++ = (uint64_t) n->op | ((uint64_t) n->flags << 32);
         put_tensor(n);
-        uint64_t w[GGML_MAX_OP_PARAMS / sizeof(uint64_t)];
-        memcpy(w, n->op_params, sizeof(w));
-        for (uint64_t v : w) key.push_back(v);
+        memcpy(o, n->op_params, GGML_MAX_OP_PARAMS); o += GGML_MAX_OP_PARAMS / sizeof(uint64_t);
         for (int k = 0; k < GGML_MAX_SRC; k++) {
             const ggml_tensor * s = n->src[k];
-            if (!s) { key.push_back(~(uint64_t) 0); continue; }
+            if (!s) { *o++ = ~(uint64_t) 0; continue; }
             put_tensor(s);
             if (s->buffer && buft_is_split(s->buffer->buft)) *capturable = false;  // several streams and devices: launched directly
         }
     }
+    return (size_t) (o - buf.data());
 }
 
-uint64_t hash_key(const std::vector<uint64_t> & key) {
-    uint64_t h = 0xcbf29ce484222325ull;
-    for (uint64_t v : key) { h ^= v; h *= 0x100000001b3ull; h ^= h >> 29; }
-    return h;
+uint64_t hash_key(const uint64_t * key, size_t n) {   // four independent lanes: the multiply chains overlap
+    uint64_t h[4] = { 0xcbf29ce484222325ull, 0x9e3779b97f4a7c15ull, 0xc2b2ae3d27d4eb4full, 0x165667b19e3779f9ull };
+    size_t i = 0;
+    for (; i + 4 <= n; i += 4) {
+        for (int l = 0; l < 4; l++) { h[l] ^= key[i + l]; h[l] *= 0x100000001b3ull; h[l] ^= h[l] >> 29; }
+    }
+    for (; i < n; i++) { h[0] ^= key[i]; h[0] *= 0x100000001b3ull; h[0] ^= h[0] >> 29; }
+    return (h[0] * 31 + h[1]) * 31 + (h[2] * 31 + h[3]) + n;
 }
 
 void evict_graphs(be_ctx * c) {  // bounded cache: drop the least recently used half
@@ -1126,22 +1137,33 @@ ggml_status be_graph_compute_impl(ggml_backend_t backend, ggml_cgraph * cgraph, 
     int  n_run = 0;
     bool capturable = true;
     const uint64_t tk0 = key_ns ? now_ns() : 0;
-    graph_key(cgraph, key, &n_run, &capturable);
+    const size_t n_key = graph_key(cgraph, key, &n_run, &capturable);
     if (!capturable || n_run < c->graph_min_nodes) return run_nodes(c, cgraph);
-    auto & bucket = c->graphs[hash_key(key)];
-    if (key_ns) *key_ns = now_ns() - tk0;
+    auto same = [&](const be_ctx::cached_graph & e) { return e.key.size() == n_key && memcmp(e.key.data(), key.data(), n_key * sizeof(uint64_t)) == 0; };
+    // decode repeats one cgraph token after token: the bucket that answered last time is compared first, and only a miss pays for the hash
     be_ctx::cached_graph * g = nullptr;
-    for (auto & e : bucket) if (e.key == key) { g = &e; break; }
-    if (!g) {
-        if (c->n_graphs >= 1024) {
-            evict_graphs(c);
-            return be_graph_compute_impl(backend, cgraph, key_ns);  // `bucket` may be gone
-        }
-        bucket.emplace_back();
-        g = &bucket.back();
-        g->key = key;
-        c->n_graphs++;
+    if (c->last_hash_valid) {
+        auto it = c->graphs.find(c->last_hash);
+        if (it != c->graphs.end()) for (auto & e : it->second) if (same(e)) { g = &e; break; }
     }
+    if (!g) {
+        const uint64_t h = hash_key(key.data(), n_key);
+        auto & bucket = c->graphs[h];
+        for (auto & e : bucket) if (same(e)) { g = &e; break; }
+        if (!g) {
+            if (c->n_graphs >= 1024) {
+                evict_graphs(c);
+                return be_graph_compute_impl(backend, cgraph, key_ns);  // `bucket` may be gone
+            }
+            bucket.emplace_back();
+            g = &bucket.back();
+            g->key.assign(key.begin(), key.begin() + (long) n_key);
+            c->n_graphs++;
+        }
+        c->last_hash = h;
+        c->last_hash_valid = true;
+    }
+    if (key_ns) *key_ns = now_ns() - tk0;
     g->stamp = ++c->graph_clock;
     g->seen++;
     if (g->exec) {

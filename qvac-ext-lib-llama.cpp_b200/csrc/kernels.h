@@ -250,6 +250,34 @@ struct MvNorm {
     int           on;
 };
 
+#ifdef __CUDACC__
+// L2 prefetch of the head (groups_per_cta row groups) of every CTA's range of the predicted launch nx, shared among `nb` warps of the
+// calling grid (this is warp b). Used by the mat-vec kernels' producer warps for the launch behind them, and by FLASH_ATTN_EXT - whose
+// own traffic is small and latency-bound - for the launch after that (the FFN's gate / up matrices), so that HBM keeps streaming
+// weights while the attention of a decode step runs.
+__device__ __forceinline__ void mv_prefetch_next(const MvNext & nx, int b, int nb, int lane) {
+    for (int c = b; c < nx.n_ctas; c += nb) {
+        const int g0 = (int) ((int64_t) nx.total_groups * c / nx.n_ctas);
+        const int g1 = min((int) ((int64_t) nx.total_groups * (c + 1) / nx.n_ctas), g0 + nx.groups_per_cta);
+        const int gs = nx.glu ? 2 : 1;  // a gate / up pair: lanes 2k and 2k + 1 take the two matrices of group k
+        for (int gl = gs * g0 + lane; gl < gs * g1; gl += 32) {
+            const int g = gl / gs;
+            int m = nx.glu ? gl - 2 * g : 0;
+#pragma unroll
+            for (int i = 1; i < MV_MAX_MATS; i++) if (!nx.glu && i < nx.n_mats && g >= nx.group0[i]) m = i;
+            const int row0 = (g - nx.group0[m]) * nx.rpg;
+            const int nrow = min(nx.rpg, nx.M[m] - row0);
+            const uint8_t * src = nx.w[m] + (int64_t) row0 * nx.nb01[m];
+            if (nx.nb01[m] == (int64_t) nx.row_bytes) {
+                bulk_prefetch_l2(src, (uint32_t) (nrow * nx.row_bytes));
+            } else {
+                for (int r = 0; r < nrow; r++) bulk_prefetch_l2(src + (int64_t) r * nx.nb01[m], (uint32_t) nx.row_bytes);
+            }
+        }
+    }
+}
+#endif
+
 struct MvParams {
     MvMat           mat[MV_MAX_MATS];
     int             n_mats;

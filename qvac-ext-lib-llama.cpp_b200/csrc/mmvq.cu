@@ -377,15 +377,19 @@ __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wa
 __device__ __forceinline__ void norm_units(float (&v)[4][8], const MvNorm & nm, int t0, int stride, int n_units, int lane, float * part, int n_threads) {
     float wv[4][8];
 #pragma unroll
+    for (int b = 0; b < 4; b++) {   // the norm weights are requested before the row's values are waited for
+        const int t = t0 + b * stride;
+        if (t < n_units && nm.w) {
+            const float4 e = __ldg((const float4 *) nm.w + t * 64 + lane * 2), f = __ldg((const float4 *) nm.w + t * 64 + lane * 2 + 1);
+            wv[b][0] = e.x; wv[b][1] = e.y; wv[b][2] = e.z; wv[b][3] = e.w; wv[b][4] = f.x; wv[b][5] = f.y; wv[b][6] = f.z; wv[b][7] = f.w;
+        }
+    }
+#pragma unroll
     for (int b = 0; b < 4; b++) {
         const int t = t0 + b * stride;
         if (t < n_units) {
             const float sq = unit_sumsq(v[b]);
             if (lane == 0) part[t] = sq;
-            if (nm.w) {
-                const float4 e = __ldg((const float4 *) nm.w + t * 64 + lane * 2), f = __ldg((const float4 *) nm.w + t * 64 + lane * 2 + 1);
-                wv[b][0] = e.x; wv[b][1] = e.y; wv[b][2] = e.z; wv[b][3] = e.w; wv[b][4] = f.x; wv[b][5] = f.y; wv[b][6] = f.z; wv[b][7] = f.w;
-            }
         }
     }
     asm volatile("bar.sync 3, %0;" ::"r"(n_threads) : "memory");
@@ -546,26 +550,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
         // every copy of this kernel is in flight: keep HBM busy across the kernel boundary with the head of the predicted
         // next kernel's weight stream (see MvNext)
         if (p.next.n_mats > 0) {
-            const MvNext & nx = p.next;
-            for (int b = blockIdx.x; b < nx.n_ctas; b += gridDim.x) {
-                const int nb = (int) ((int64_t) nx.total_groups * b / nx.n_ctas);
-                const int ne = min((int) ((int64_t) nx.total_groups * (b + 1) / nx.n_ctas), nb + nx.groups_per_cta);
-                const int gs = nx.glu ? 2 : 1;  // a gate / up pair: lanes 2k and 2k + 1 take the two matrices of group k
-                for (int gl = gs * nb + lane; gl < gs * ne; gl += 32) {
-                    const int g = gl / gs;
-                    int m = nx.glu ? gl - 2 * g : 0;
-#pragma unroll
-                    for (int i = 1; i < MV_MAX_MATS; i++) if (!nx.glu && i < nx.n_mats && g >= nx.group0[i]) m = i;
-                    const int row0 = (g - nx.group0[m]) * nx.rpg;
-                    const int nrow = min(nx.rpg, nx.M[m] - row0);
-                    const uint8_t * src = nx.w[m] + (int64_t) row0 * nx.nb01[m];
-                    if (nx.nb01[m] == (int64_t) nx.row_bytes) {
-                        bulk_prefetch_l2(src, (uint32_t) (nrow * nx.row_bytes));
-                    } else {
-                        for (int r = 0; r < nrow; r++) bulk_prefetch_l2(src + (int64_t) r * nx.nb01[m], (uint32_t) nx.row_bytes);
-                    }
-                }
-            }
+            mv_prefetch_next(p.next, (int) blockIdx.x, (int) gridDim.x, lane);
         }
         return;
     }
@@ -981,26 +966,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
             }
         }
         if (p.next.n_mats > 0) {  // head of the predicted next kernel's weight stream -> L2 (see MvNext)
-            const MvNext & nx = p.next;
-            for (int b = blockIdx.x; b < nx.n_ctas; b += gridDim.x) {
-                const int nb = (int) ((int64_t) nx.total_groups * b / nx.n_ctas);
-                const int ne = min((int) ((int64_t) nx.total_groups * (b + 1) / nx.n_ctas), nb + nx.groups_per_cta);
-                const int gs = nx.glu ? 2 : 1;
-                for (int gl = gs * nb + lane; gl < gs * ne; gl += 32) {
-                    const int g = gl / gs;
-                    int m = nx.glu ? gl - 2 * g : 0;
-#pragma unroll
-                    for (int i = 1; i < MV_MAX_MATS; i++) if (!nx.glu && i < nx.n_mats && g >= nx.group0[i]) m = i;
-                    const int row0 = (g - nx.group0[m]) * nx.rpg;
-                    const int nrow = min(nx.rpg, nx.M[m] - row0);
-                    const uint8_t * src = nx.w[m] + (int64_t) row0 * nx.nb01[m];
-                    if (nx.nb01[m] == (int64_t) nx.row_bytes) {
-                        bulk_prefetch_l2(src, (uint32_t) (nrow * nx.row_bytes));
-                    } else {
-                        for (int i = 0; i < nrow; i++) bulk_prefetch_l2(src + (int64_t) i * nx.nb01[m], (uint32_t) nx.row_bytes);
-                    }
-                }
-            }
+            mv_prefetch_next(p.next, (int) blockIdx.x, (int) gridDim.x, lane);
         }
         return;
     }

@@ -349,8 +349,11 @@ struct FaP {
     int64_t  chunk;
     float *  ws;       // partials of the KV splits: [row][split][2 + D] = running maximum, sum, accumulator
     unsigned * cnt;    // arrivals per row; the CTA that completes a row merges its splits and puts the counter back to 0
+    MvNext   next;     // n_mats > 0: weights to pull into L2 meanwhile (kernels.h mv_prefetch_next)
 };
-constexpr int FA_WARPS = 8, FA_U = 8;   // a warp keeps 8 KV positions in flight (K and V rows as packed halves: E registers per position)
+constexpr int FA_MAX_WARPS = 16;   // warps per CTA: 8 or 16 (launch parameter)
+// a warp keeps FA_U KV positions in flight, K and V rows as packed halves (E registers per position): one round of a CTA covers 8 x FA_U positions
+__host__ __device__ constexpr int fa_u(int E) { return 8; }   // measured on the 8B decode step: 8 beats 4 by 2 % and 16 (128 registers, spills) loses 13 %
 
 template <int E> struct HPack { uint32_t w[E / 2]; };
 template <int E>
@@ -386,9 +389,10 @@ __device__ __forceinline__ float * fa_dst_row(const FaP & p, int64_t iq1, int64_
     return (float *) (p.dd + (iq3 * p.d.ne[2] * p.d.ne[1] + iq2 + iq1 * p.d.ne[1]) * p.d.nb[1]);
 }
 
-template <int E>
-__global__ void __launch_bounds__(FA_WARPS * 32) fa_kernel(const FaP p) {
+template <int E, int FA_U>
+__global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
     constexpr int D = 32 * E;
+    const int FA_WARPS = blockDim.x >> 5;
     pdl_prologue();
     const int64_t row = blockIdx.x;
     const int64_t iq1 = row % p.q.ne[1], iq2 = (row / p.q.ne[1]) % p.q.ne[2], iq3 = row / (p.q.ne[1] * p.q.ne[2]);
@@ -396,59 +400,64 @@ __global__ void __launch_bounds__(FA_WARPS * 32) fa_kernel(const FaP p) {
     const int64_t iv2 = iq2 / (p.q.ne[2] / p.v.ne[2]), iv3 = iq3 / (p.q.ne[3] / p.v.ne[3]);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-    float qf[E];
-    {
-        const float * pq = (const float *) (p.qd + iq1 * p.q.nb[1] + iq2 * p.q.nb[2] + iq3 * p.q.nb[3]) + lane * E;
+    // everything the first round needs is requested before anything is used: q, the mask values and the K / V rows are independent
+    // loads (a masked position's rows are read anyway - they are valid cache memory - so that the K / V loads do not wait for the mask)
+    const float * pq = (const float *) (p.qd + iq1 * p.q.nb[1] + iq2 * p.q.nb[2] + iq3 * p.q.nb[3]) + lane * E;
+    float qraw[E];
 #pragma unroll
-        for (int e = 0; e < E; e++) qf[e] = __half2float(__float2half_rn(pq[e])) * p.scale;   // ggml-cpu converts q to the K type's vec_dot type: fp16
-    }
+    for (int e = 0; e < E; e++) qraw[e] = pq[e];
     const __half * mp = p.md ? (const __half *) (p.md + iq1 * p.m.nb[1] + (iq2 % p.m.ne[2]) * p.m.nb[2] + (iq3 % p.m.ne[3]) * p.m.nb[3]) : nullptr;
-    const float slope = fa_slope(p, (uint32_t) iq2);
     const char * kb = p.kd + ik2 * p.k.nb[2] + ik3 * p.k.nb[3] + lane * E * 2;
     const char * vb = p.vd + iv2 * p.v.nb[2] + iv3 * p.v.nb[3] + lane * E * 2;
+    const int64_t c0 = (int64_t) blockIdx.y * p.chunk, c1 = min(c0 + p.chunk, p.k.ne[1]);
 
-    float M = -INFINITY, S = 0.0f, acc[E];
+    if (p.next.n_mats > 0) mv_prefetch_next(p.next, (int) (blockIdx.y * gridDim.x + blockIdx.x) * FA_WARPS + warp, (int) (gridDim.x * gridDim.y) * FA_WARPS, lane);
+    float M = -INFINITY, S = 0.0f, acc[E], qf[E];
 #pragma unroll
     for (int e = 0; e < E; e++) acc[e] = 0.0f;
+    const float slope = fa_slope(p, (uint32_t) iq2);
+    bool q_ready = false;
 
-    const int64_t c0 = (int64_t) blockIdx.y * p.chunk, c1 = min(c0 + p.chunk, p.k.ne[1]);
     for (int64_t base = c0 + warp * FA_U; base < c1; base += FA_WARPS * FA_U) {
-        float s[FA_U], mv[FA_U];
+        float s[FA_U];
+        __half mh[FA_U];
         HPack<E> kp[FA_U], vp[FA_U];
 #pragma unroll
         for (int u = 0; u < FA_U; u++) {
-            const int64_t ic = base + u;
-            mv[u] = ic < c1 ? (mp ? slope * __half2float(mp[ic]) : 0.0f) : -INFINITY;
-        }
-#pragma unroll
-        for (int u = 0; u < FA_U; u++) {
-            if (mv[u] != -INFINITY) {   // warp-uniform
+            if (base + u < c1) {   // warp-uniform
+                if (mp) mh[u] = mp[base + u];
                 kp[u] = load_pack<E>(kb + (base + u) * p.k.nb[1]);
                 vp[u] = load_pack<E>(vb + (base + u) * p.v.nb[1]);
             }
         }
-        float mx = -INFINITY;
+        if (!q_ready) {
+#pragma unroll
+            for (int e = 0; e < E; e++) qf[e] = __half2float(__float2half_rn(qraw[e])) * p.scale;   // ggml-cpu converts q to the K type's vec_dot type: fp16
+            q_ready = true;
+        }
 #pragma unroll
         for (int u = 0; u < FA_U; u++) {
-            s[u] = -INFINITY;
-            if (mv[u] != -INFINITY) {
-                float kf[E], t = 0.0f;
+            float t = 0.0f;
+            if (base + u < c1) {
+                float kf[E];
                 unpack<E>(kp[u], kf);
 #pragma unroll
                 for (int e = 0; e < E; e++) t += qf[e] * kf[e];
-                s[u] = t;
             }
+            s[u] = t;
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {   // the FA_U reductions side by side
 #pragma unroll
             for (int u = 0; u < FA_U; u++) s[u] += __shfl_xor_sync(0xffffffffu, s[u], o);
         }
+        float mx = -INFINITY;
 #pragma unroll
         for (int u = 0; u < FA_U; u++) {
-            if (mv[u] != -INFINITY) {
+            const float mv = base + u < c1 ? (mp ? slope * __half2float(mh[u]) : 0.0f) : -INFINITY;
+            if (mv != -INFINITY) {
                 if (p.softcap != 0.0f) s[u] = p.softcap * tanhf(s[u]);
-                s[u] += mv[u];
+                s[u] += mv;
             } else {
                 s[u] = -INFINITY;
             }
@@ -473,23 +482,22 @@ __global__ void __launch_bounds__(FA_WARPS * 32) fa_kernel(const FaP p) {
         }
     }
 
-    __shared__ float sh_acc[FA_WARPS][D];
-    __shared__ float sh_m[FA_WARPS], sh_s[FA_WARPS];
+    __shared__ float sh_acc[FA_MAX_WARPS][D];
+    __shared__ float sh_m[FA_MAX_WARPS], sh_s[FA_MAX_WARPS];
 #pragma unroll
     for (int e = 0; e < E; e++) sh_acc[warp][lane * E + e] = acc[e];
     if (lane == 0) { sh_m[warp] = M; sh_s[warp] = S; }
     __syncthreads();
     float Mx = -INFINITY;
-#pragma unroll
     for (int w = 0; w < FA_WARPS; w++) Mx = fmaxf(Mx, sh_m[w]);
     float St = 0.0f;
-    float f[FA_WARPS];
+    float f[FA_MAX_WARPS];
 #pragma unroll
-    for (int w = 0; w < FA_WARPS; w++) { f[w] = sh_m[w] == -INFINITY ? 0.0f : expf(sh_m[w] - Mx); St += sh_s[w] * f[w]; }
+    for (int w = 0; w < FA_MAX_WARPS; w++) { f[w] = w >= FA_WARPS || sh_m[w] == -INFINITY ? 0.0f : expf(sh_m[w] - Mx); St += w < FA_WARPS ? sh_s[w] * f[w] : 0.0f; }
     for (int t = threadIdx.x; t < D; t += blockDim.x) {
         float a = 0.0f;
 #pragma unroll
-        for (int w = 0; w < FA_WARPS; w++) a += sh_acc[w][t] * f[w];
+        for (int w = 0; w < FA_MAX_WARPS; w++) a += w < FA_WARPS ? sh_acc[w][t] * f[w] : 0.0f;
         if (p.nsplit > 1) {
             p.ws[(row * p.nsplit + blockIdx.y) * (D + 2) + 2 + t] = a;
         } else {
@@ -797,15 +805,21 @@ b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b20
     p.n_head_log2 = 1u << (uint32_t) floorf(log2f((float) n_head));
     p.m0 = powf(2.0f, -max_bias / (float) p.n_head_log2);
     p.m1 = powf(2.0f, -(max_bias / 2.0f) / (float) p.n_head_log2);
-    // KV splits (decode: a few dozen rows, one per head): about two CTAs per SM, no fewer than 128 positions (two rounds of the 8 warps'
-    // 8 positions each) per split; the splits of a row are merged by the last of its CTAs to finish
+    // KV splits (decode: a few dozen rows, one per head): about two CTAs per SM, whole rounds (what the 8 warps of a CTA have in flight
+    // at a time: one memory round trip); the splits of a row are merged by the last of its CTAs to finish
     int nsplit = 1;
-    const int64_t n_kv = k->ne[1];
-    if (rows < 2 * ctx->sm_count && rows <= (int64_t) (FA_CNT_BYTES / 4) && n_kv >= 256) {
-        nsplit = (int) std::min<int64_t>(std::min<int64_t>((2 * (int64_t) ctx->sm_count + rows - 1) / rows, (n_kv + 127) / 128), 64);
+    static const int u_env = [] { const char * e = getenv("GGML_B200_FA_U"); return e ? atoi(e) : 0; }();   // experiments: 4 / 8 / 16 positions per warp in flight
+    const int U = (u_env == 4 || u_env == 8 || u_env == 16) && D <= 128 ? u_env : fa_u(D / 32);
+    static const int w_env = [] { const char * e = getenv("GGML_B200_FA_WARPS"); return e ? atoi(e) : 0; }();
+    const int FA_WARPS = w_env == 16 ? 16 : 8;
+    const int64_t n_kv = k->ne[1], round = FA_WARPS * U;   // positions one CTA has in flight at a time
+    if (rows < 2 * ctx->sm_count && rows <= (int64_t) (FA_CNT_BYTES / 4) && n_kv >= 2 * round) {
+        nsplit = (int) std::min<int64_t>(std::min<int64_t>((2 * (int64_t) ctx->sm_count + rows - 1) / rows, (n_kv + round - 1) / round), 64);
         if (nsplit < 1) nsplit = 1;
     }
-    p.chunk  = nsplit == 1 ? std::max<int64_t>(n_kv, 1) : ((n_kv + nsplit - 1) / nsplit + 63) / 64 * 64;
+    static const int max_split = [] { const char * e = getenv("GGML_B200_FA_MAX_SPLIT"); return e ? atoi(e) : 64; }();   // experiments
+    if (nsplit > max_split) nsplit = std::max(1, max_split);
+    p.chunk  = nsplit == 1 ? std::max<int64_t>(n_kv, 1) : ((n_kv + nsplit - 1) / nsplit + round - 1) / round * round;
     if (nsplit > 1) nsplit = (int) ((n_kv + p.chunk - 1) / p.chunk);   // no empty splits
     p.nsplit = nsplit;
     p.ws     = nullptr;
@@ -818,10 +832,23 @@ b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b20
         p.cnt = (unsigned *) ctx->fa_ws;
         p.ws  = (float *) ((char *) ctx->fa_ws + FA_CNT_BYTES);
     }
+    memset(&p.next, 0, sizeof(p.next));
+    if (ctx->fa_prefetch_kb > 0 && ctx->prefetch_kb > 0 && ctx->last_key && ctx->mem_gen == b200_mem_generation()) {
+        // the mat-vec launch behind this kernel has been staged by the one in front of it; this kernel's idle HBM time goes to the one after
+        auto it1 = ctx->next_of.find(ctx->last_key);
+        if (it1 != ctx->next_of.end() && it1->second.n_mats > 0) {
+            auto it2 = ctx->next_of.find(it1->second.w[0]);
+            if (it2 != ctx->next_of.end() && it2->second.n_mats > 0) {
+                p.next = it2->second;
+                const int64_t gb = (int64_t) p.next.rpg * p.next.row_bytes * (p.next.glu ? 2 : 1);
+                p.next.groups_per_cta = (int) (((int64_t) ctx->fa_prefetch_kb * 1024 + gb - 1) / gb);
+            }
+        }
+    }
     const dim3 grid((unsigned) rows, (unsigned) nsplit), block(FA_WARPS * 32);
-    if (D == 64)       CU(b200_launch(ctx, fa_kernel<2>, grid, block, 0, p));
-    else if (D == 128) CU(b200_launch(ctx, fa_kernel<4>, grid, block, 0, p));
-    else               CU(b200_launch(ctx, fa_kernel<8>, grid, block, 0, p));
+    if (D == 64)       CU(U == 4 ? b200_launch(ctx, fa_kernel<2, 4>, grid, block, 0, p) : U == 8 ? b200_launch(ctx, fa_kernel<2, 8>, grid, block, 0, p) : b200_launch(ctx, fa_kernel<2, 16>, grid, block, 0, p));
+    else if (D == 128) CU(U == 4 ? b200_launch(ctx, fa_kernel<4, 4>, grid, block, 0, p) : U == 8 ? b200_launch(ctx, fa_kernel<4, 8>, grid, block, 0, p) : b200_launch(ctx, fa_kernel<4, 16>, grid, block, 0, p));
+    else               CU(b200_launch(ctx, fa_kernel<8, 8>, grid, block, 0, p));
     ctx->launches++;
     return B200_OK;
 }

@@ -67,9 +67,9 @@ def test_norm_folded_into_the_mat_vec_is_the_nodes(pkg, ctx, refq, t, K, N):
     x = torch.from_numpy(rng.normal(0, 2, (N, K)).astype(np.float32)).cuda()
     w = torch.from_numpy(rng.normal(1, 0.2, K).astype(np.float32)).cuda()
     xn = ctx.rms_norm_mul(x.reshape(1, 1, N, K), w, 1e-5).reshape(N, K)
-    n0 = ctx.launches()
+    n0 = ctx.launches
     fused = ctx.mul_mat_shared(t, Ws, x, norm_w=w, norm_eps=1e-5)
-    n_fused = ctx.launches() - n0
+    n_fused = ctx.launches - n0
     plain = ctx.mul_mat_shared(t, Ws, xn)
     for a, b in zip(fused, plain):
         assert torch.equal(a, b)
