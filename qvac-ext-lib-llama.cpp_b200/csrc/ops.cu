@@ -352,6 +352,7 @@ struct FaP {
     MvNext   next;     // n_mats > 0: weights to pull into L2 meanwhile (kernels.h mv_prefetch_next)
 };
 constexpr int FA_MAX_WARPS = 16;   // warps per CTA: 8 or 16 (launch parameter)
+constexpr int FAQ_WARPS = 8, FAQ_U = 4;   // fa_rows_kernel: 8 warps, 4 KV positions per warp and round
 // a warp keeps FA_U KV positions in flight, K and V rows as packed halves (E registers per position): one round of a CTA covers 8 x FA_U positions
 __host__ __device__ constexpr int fa_u(int E) { return 8; }   // measured on the 8B decode step: 8 beats 4 by 2 % and 16 (128 registers, spills) loses 13 %
 
@@ -540,6 +541,154 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
         float a = 0.0f;
         for (int s = 0; s < p.nsplit; s++) { const float m = __ldcg(w + s * (D + 2)); if (m != -INFINITY) a += __ldcg(w + s * (D + 2) + 2 + t) * expf(m - Mg); }
         fa_dst_row(p, iq1, iq2, iq3)[t] = Sg == 0.0f ? 0.0f : a * r / Sg;
+    }
+}
+
+// Wide batches (prompt processing): a CTA takes NQ consecutive query rows of one head, so a K / V row is loaded once for all of them
+// (the decode kernel above would re-read the whole K / V per query row). Same arithmetic per (query, position) pair; a round whose
+// positions are masked for every row of the block - the upper triangle of a causal prompt - is skipped before its K / V loads.
+template <int E, int NQ>
+__global__ void __launch_bounds__(FAQ_WARPS * 32, 1) fa_rows_kernel(const FaP p) {
+    constexpr int D = 32 * E, U = FAQ_U;
+    pdl_prologue();
+    const int64_t nqb = (p.q.ne[1] + NQ - 1) / NQ;
+    const int64_t blk = blockIdx.x;
+    const int64_t iq1b = blk % nqb, iq2 = (blk / nqb) % p.q.ne[2], iq3 = blk / (nqb * p.q.ne[2]);
+    const int64_t q0 = iq1b * NQ;
+    const int     nq = (int) min((int64_t) NQ, p.q.ne[1] - q0);
+    const int64_t ik2 = iq2 / (p.q.ne[2] / p.k.ne[2]), ik3 = iq3 / (p.q.ne[3] / p.k.ne[3]);
+    const int64_t iv2 = iq2 / (p.q.ne[2] / p.v.ne[2]), iv3 = iq3 / (p.q.ne[3] / p.v.ne[3]);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t n_kv = p.k.ne[1];
+
+    float qf[NQ][E], acc[NQ][E], M[NQ], S[NQ];
+    const __half * mp[NQ];
+#pragma unroll
+    for (int r = 0; r < NQ; r++) {
+        const int64_t iq1 = q0 + min(r, nq - 1);   // rows past the end repeat the last one and are never stored
+        const float * pq = (const float *) (p.qd + iq1 * p.q.nb[1] + iq2 * p.q.nb[2] + iq3 * p.q.nb[3]) + lane * E;
+#pragma unroll
+        for (int e = 0; e < E; e++) { qf[r][e] = __half2float(__float2half_rn(pq[e])) * p.scale; acc[r][e] = 0.0f; }
+        mp[r] = p.md ? (const __half *) (p.md + iq1 * p.m.nb[1] + (iq2 % p.m.ne[2]) * p.m.nb[2] + (iq3 % p.m.ne[3]) * p.m.nb[3]) : nullptr;
+        M[r] = -INFINITY; S[r] = 0.0f;
+    }
+    const float slope = fa_slope(p, (uint32_t) iq2);
+    const char * kb = p.kd + ik2 * p.k.nb[2] + ik3 * p.k.nb[3] + lane * E * 2;
+    const char * vb = p.vd + iv2 * p.v.nb[2] + iv3 * p.v.nb[3] + lane * E * 2;
+
+    for (int64_t base = warp * U; base < n_kv; base += FAQ_WARPS * U) {
+        float s[NQ][U];
+        bool any = false;
+#pragma unroll
+        for (int r = 0; r < NQ; r++) {
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const float mv = r < nq && base + u < n_kv ? (mp[r] ? slope * __half2float(mp[r][base + u]) : 0.0f) : -INFINITY;
+                s[r][u] = mv;   // the mask value until the score replaces it
+                any = any || mv != -INFINITY;
+            }
+        }
+        if (!any) continue;   // warp-uniform: every lane reads the same mask values
+        HPack<E> kp[U], vp[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (base + u < n_kv) {
+                kp[u] = load_pack<E>(kb + (base + u) * p.k.nb[1]);
+                vp[u] = load_pack<E>(vb + (base + u) * p.v.nb[1]);
+            }
+        }
+        float d[NQ][U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            float kf[E];
+            if (base + u < n_kv) unpack<E>(kp[u], kf);
+#pragma unroll
+            for (int r = 0; r < NQ; r++) {
+                float t = 0.0f;
+                if (base + u < n_kv) {
+#pragma unroll
+                    for (int e = 0; e < E; e++) t += qf[r][e] * kf[e];
+                }
+                d[r][u] = t;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int r = 0; r < NQ; r++) {
+#pragma unroll
+                for (int u = 0; u < U; u++) d[r][u] += __shfl_xor_sync(0xffffffffu, d[r][u], o);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < NQ; r++) {
+            float mx = -INFINITY;
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                if (s[r][u] != -INFINITY) {
+                    float t = d[r][u];
+                    if (p.softcap != 0.0f) t = p.softcap * tanhf(t);
+                    s[r][u] += t;
+                }
+                mx = fmaxf(mx, s[r][u]);
+            }
+            if (mx == -INFINITY) {
+#pragma unroll
+                for (int u = 0; u < U; u++) s[r][u] = 0.0f;   // no weight for this row in this round
+                continue;
+            }
+            const float Mn = fmaxf(M[r], mx), ms = expf(M[r] - Mn);
+            M[r] = Mn;
+            S[r] *= ms;
+#pragma unroll
+            for (int e = 0; e < E; e++) acc[r][e] *= ms;
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const float pr = s[r][u] == -INFINITY ? 0.0f : expf(s[r][u] - Mn);
+                S[r] += pr;
+                s[r][u] = pr;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (base + u < n_kv) {
+                float vf[E];
+                unpack<E>(vp[u], vf);
+#pragma unroll
+                for (int r = 0; r < NQ; r++) {
+#pragma unroll
+                    for (int e = 0; e < E; e++) acc[r][e] += s[r][u] * vf[e];
+                }
+            }
+        }
+    }
+
+    __shared__ float sh_acc[FAQ_WARPS][NQ][D];
+    __shared__ float sh_m[FAQ_WARPS][NQ], sh_s[FAQ_WARPS][NQ];
+#pragma unroll
+    for (int r = 0; r < NQ; r++) {
+#pragma unroll
+        for (int e = 0; e < E; e++) sh_acc[warp][r][lane * E + e] = acc[r][e];
+        if (lane == 0) { sh_m[warp][r] = M[r]; sh_s[warp][r] = S[r]; }
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < nq * D; idx += blockDim.x) {
+        const int r = idx / D, t = idx - r * D;
+        float Mx = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < FAQ_WARPS; w++) Mx = fmaxf(Mx, sh_m[w][r]);
+        float St = 0.0f, a = 0.0f;
+#pragma unroll
+        for (int w = 0; w < FAQ_WARPS; w++) {
+            const float f = sh_m[w][r] == -INFINITY ? 0.0f : expf(sh_m[w][r] - Mx);
+            St += sh_s[w][r] * f;
+            a  += sh_acc[w][r][t] * f;
+        }
+        if (p.sinks) {
+            const float sk = p.sinks[iq2];
+            if (sk > Mx) { const float rr = expf(Mx - sk); a *= rr; St = St * rr + 1.0f; } else { St += expf(sk - Mx); }
+        }
+        fa_dst_row(p, q0 + r, iq2, iq3)[t] = St == 0.0f ? 0.0f : a / St;
     }
 }
 
@@ -844,6 +993,18 @@ b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b20
                 p.next.groups_per_cta = (int) (((int64_t) ctx->fa_prefetch_kb * 1024 + gb - 1) / gb);
             }
         }
+    }
+    if (q->ne[1] >= 4) {   // a batch: several query rows per CTA
+        const int NQ = D == 256 ? 4 : 8;
+        const int64_t blocks = (q->ne[1] + NQ - 1) / NQ * q->ne[2] * q->ne[3];
+        p.nsplit = 1;
+        p.chunk  = std::max<int64_t>(n_kv, 1);
+        const dim3 g((unsigned) blocks), b(FAQ_WARPS * 32);
+        if (D == 64)       CU(b200_launch(ctx, fa_rows_kernel<2, 8>, g, b, 0, p));
+        else if (D == 128) CU(b200_launch(ctx, fa_rows_kernel<4, 8>, g, b, 0, p));
+        else               CU(b200_launch(ctx, fa_rows_kernel<8, 4>, g, b, 0, p));
+        ctx->launches++;
+        return B200_OK;
     }
     const dim3 grid((unsigned) rows, (unsigned) nsplit), block(FA_WARPS * 32);
     if (D == 64)       CU(U == 4 ? b200_launch(ctx, fa_kernel<2, 4>, grid, block, 0, p) : U == 8 ? b200_launch(ctx, fa_kernel<2, 8>, grid, block, 0, p) : b200_launch(ctx, fa_kernel<2, 16>, grid, block, 0, p));
