@@ -14,7 +14,7 @@
 set -u
 O=gpurun_out; mkdir -p $O
 TAG=${TAG:-r02}
-LIGHT="--no-cpu --no-ref-cuda --no-plugin-e2e --no-scale-base"
+LIGHT="--no-cpu --no-ref-cuda --no-plugin-e2e --no-scale-base --no-token-step"
 for recipe in "$@"; do
   kind=${recipe%%:*}; rest=${recipe#*:}; [ "$rest" == "$recipe" ] && rest=""
   case $kind in
