@@ -692,6 +692,172 @@ __global__ void __launch_bounds__(FAQ_WARPS * 32, 1) fa_rows_kernel(const FaP p)
     }
 }
 
+// ------------------------------------------------------------------------------------------------ FLASH_ATTN_EXT, prompt batches
+// Tensor-core tiles (warp-level mma.sync m16n8k16, fp16 x fp16 -> fp32; tcgen05 would want 128-row tiles and TMEM round trips for the
+// softmax - at 64-row blocks the attention of a 512-token prompt is ~2 % of its MUL_MATs either way). A CTA of 4 warps takes 64
+// query rows of one head (16 per warp: Q lives in registers as A fragments, fp16 as ggml-cpu's own q conversion) and walks the KV
+// cache in tiles of 64 positions staged in shared memory (rows padded to D + 8 halves: the fragment loads are bank-conflict free):
+// S = Q K^T (fp32), scale / soft-cap / mask, online softmax in fp32, P rounded to fp16 as the A operand of O += P V (fp32).
+// A tile that is masked for all 64 rows (the upper triangle of a causal prompt) is skipped before it is loaded.
+constexpr int FT_BQ = 64, FT_BK = 64, FT_WARPS = 4;
+
+__device__ __forceinline__ void mma_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_half2(float lo, float hi) {
+    const __half2 h = __floats2half2_rn(lo, hi);
+    return *(const uint32_t *) &h;
+}
+
+template <int D>
+__global__ void __launch_bounds__(FT_WARPS * 32) fa_tile_kernel(const FaP p) {
+    constexpr int LD = D + 8, KS = D / 16, NTD = D / 8, NTS = FT_BK / 8;
+    __shared__ __align__(16) __half Ks[FT_BK][LD];
+    __shared__ __align__(16) __half Vs[FT_BK][LD];
+    pdl_prologue();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int64_t iq2 = blockIdx.y, iq3 = blockIdx.z;
+    const int64_t q0 = (int64_t) blockIdx.x * FT_BQ + warp * 16;
+    const int64_t n_q = p.q.ne[1], n_kv = p.k.ne[1];
+    const int64_t ik2 = iq2 / (p.q.ne[2] / p.k.ne[2]), ik3 = iq3 / (p.q.ne[3] / p.k.ne[3]);
+    const int64_t iv2 = iq2 / (p.q.ne[2] / p.v.ne[2]), iv3 = iq3 / (p.q.ne[3] / p.v.ne[3]);
+    const int64_t r0 = q0 + g, r1 = q0 + g + 8;   // this thread's two query rows
+    const bool ok0 = r0 < n_q, ok1 = r1 < n_q;
+
+    uint32_t qa[KS][4];   // A fragments of the warp's 16 x D block of Q
+    {
+        const char * qb = p.qd + iq2 * p.q.nb[2] + iq3 * p.q.nb[3];
+        const float * q0p = (const float *) (qb + (ok0 ? r0 : 0) * p.q.nb[1]), * q1p = (const float *) (qb + (ok1 ? r1 : 0) * p.q.nb[1]);
+#pragma unroll
+        for (int ks = 0; ks < KS; ks++) {
+            const int c = ks * 16 + 2 * t;
+            qa[ks][0] = ok0 ? pack_half2(q0p[c], q0p[c + 1]) : 0u;
+            qa[ks][1] = ok1 ? pack_half2(q1p[c], q1p[c + 1]) : 0u;
+            qa[ks][2] = ok0 ? pack_half2(q0p[c + 8], q0p[c + 9]) : 0u;
+            qa[ks][3] = ok1 ? pack_half2(q1p[c + 8], q1p[c + 9]) : 0u;
+        }
+    }
+    const char * mb = p.md ? p.md + (iq2 % p.m.ne[2]) * p.m.nb[2] + (iq3 % p.m.ne[3]) * p.m.nb[3] : nullptr;
+    const __half * m0p = mb && ok0 ? (const __half *) (mb + r0 * p.m.nb[1]) : nullptr, * m1p = mb && ok1 ? (const __half *) (mb + r1 * p.m.nb[1]) : nullptr;
+    const float slope = fa_slope(p, (uint32_t) iq2);
+    const char * kb = p.kd + ik2 * p.k.nb[2] + ik3 * p.k.nb[3];
+    const char * vb = p.vd + iv2 * p.v.nb[2] + iv3 * p.v.nb[3];
+
+    float o[NTD][4];
+#pragma unroll
+    for (int n = 0; n < NTD; n++) { o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.0f; }
+    float mrow[2] = { -INFINITY, -INFINITY }, lrow[2] = { 0.0f, 0.0f };
+
+    for (int64_t j0 = 0; j0 < n_kv; j0 += FT_BK) {
+        // mask values of this thread's (row, position) pairs; -inf: masked, out of range, or a row past the batch
+        float mv[NTS][4];
+        bool any = false;
+#pragma unroll
+        for (int n = 0; n < NTS; n++) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const int64_t pos = j0 + n * 8 + 2 * t + (i & 1);
+                const bool okr = i < 2 ? ok0 : ok1;
+                const __half * mp = i < 2 ? m0p : m1p;
+                float v = okr && pos < n_kv ? (mb ? slope * __half2float(mp[pos]) : 0.0f) : -INFINITY;
+                mv[n][i] = v;
+                any = any || v != -INFINITY;
+            }
+        }
+        if (!__syncthreads_or(any)) continue;   // also orders the previous tile's shared-memory reads before this tile's writes
+        for (int c = threadIdx.x; c < FT_BK * (D / 8); c += FT_WARPS * 32) {
+            const int row = c / (D / 8), col = (c % (D / 8)) * 8;
+            const int64_t pos = j0 + row;
+            uint4 kk = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
+            if (pos < n_kv) {
+                kk = *(const uint4 *) (kb + pos * p.k.nb[1] + col * 2);
+                vv = *(const uint4 *) (vb + pos * p.v.nb[1] + col * 2);
+            }
+            *(uint4 *) &Ks[row][col] = kk;
+            *(uint4 *) &Vs[row][col] = vv;
+        }
+        __syncthreads();
+
+        float sc[NTS][4];
+#pragma unroll
+        for (int n = 0; n < NTS; n++) {
+            sc[n][0] = sc[n][1] = sc[n][2] = sc[n][3] = 0.0f;
+#pragma unroll
+            for (int ks = 0; ks < KS; ks++) {
+                const uint32_t b0 = *(const uint32_t *) &Ks[n * 8 + g][ks * 16 + 2 * t], b1 = *(const uint32_t *) &Ks[n * 8 + g][ks * 16 + 2 * t + 8];
+                mma_16816(sc[n], qa[ks], b0, b1);
+            }
+        }
+        float mx[2] = { -INFINITY, -INFINITY };
+#pragma unroll
+        for (int n = 0; n < NTS; n++) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                float v = sc[n][i] * p.scale;
+                if (p.softcap != 0.0f) v = p.softcap * tanhf(v);
+                v = mv[n][i] == -INFINITY ? -INFINITY : v + mv[n][i];
+                sc[n][i] = v;
+                mx[i >> 1] = fmaxf(mx[i >> 1], v);
+            }
+        }
+        float alpha[2], msafe[2];
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 1));
+            mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 2));
+            const float mn = fmaxf(mrow[h], mx[h]);
+            msafe[h] = mn == -INFINITY ? 0.0f : mn;
+            alpha[h] = expf(mrow[h] - msafe[h]);   // mrow = -inf: 0
+            mrow[h]  = mn;
+            lrow[h] *= alpha[h];
+        }
+#pragma unroll
+        for (int n = 0; n < NTD; n++) { o[n][0] *= alpha[0]; o[n][1] *= alpha[0]; o[n][2] *= alpha[1]; o[n][3] *= alpha[1]; }
+        uint32_t pa[NTS / 2][4];   // P as A fragments: positions kk * 16 .. + 15
+#pragma unroll
+        for (int n = 0; n < NTS; n++) {
+            float e[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) { e[i] = expf(sc[n][i] - msafe[i >> 1]); lrow[i >> 1] += e[i]; }
+            pa[n >> 1][(n & 1) * 2 + 0] = pack_half2(e[0], e[1]);
+            pa[n >> 1][(n & 1) * 2 + 1] = pack_half2(e[2], e[3]);
+        }
+#pragma unroll
+        for (int n = 0; n < NTD; n++) {
+#pragma unroll
+            for (int kk = 0; kk < NTS / 2; kk++) {
+                const __half2 h0 = __halves2half2(Vs[kk * 16 + 2 * t][n * 8 + g], Vs[kk * 16 + 2 * t + 1][n * 8 + g]);
+                const __half2 h1 = __halves2half2(Vs[kk * 16 + 2 * t + 8][n * 8 + g], Vs[kk * 16 + 2 * t + 9][n * 8 + g]);
+                mma_16816(o[n], pa[kk], *(const uint32_t *) &h0, *(const uint32_t *) &h1);
+            }
+        }
+    }
+    // the row sums live spread over the four lanes of a quad
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        lrow[h] += __shfl_xor_sync(0xffffffffu, lrow[h], 1);
+        lrow[h] += __shfl_xor_sync(0xffffffffu, lrow[h], 2);
+    }
+    float rs[2] = { 1.0f, 1.0f };
+    if (p.sinks) {
+        const float sk = p.sinks[iq2];
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            if (sk > mrow[h]) { rs[h] = expf(mrow[h] - sk); lrow[h] = lrow[h] * rs[h] + 1.0f; } else { lrow[h] += expf(sk - mrow[h]); }
+        }
+    }
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int64_t r = h ? r1 : r0;
+        if (!(h ? ok1 : ok0)) continue;
+        float * dr = fa_dst_row(p, r, iq2, iq3);
+        const float inv = lrow[h] == 0.0f ? 0.0f : rs[h] / lrow[h];
+#pragma unroll
+        for (int n = 0; n < NTD; n++) *(float2 *) (dr + n * 8 + 2 * t) = make_float2(o[n][2 * h] * inv, o[n][2 * h + 1] * inv);
+    }
+}
+
 bool rows_ok(const b200_tensor * t, size_t elem) { return t && t->nb[0] == elem; }
 int64_t nelem(const b200_tensor * t) { return t->ne[0] * t->ne[1] * t->ne[2] * t->ne[3]; }
 bool nonneg(const b200_tensor * t) { return t->ne[0] >= 0 && t->ne[1] >= 0 && t->ne[2] >= 0 && t->ne[3] >= 0; }
@@ -993,6 +1159,19 @@ b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b20
                 p.next.groups_per_cta = (int) (((int64_t) ctx->fa_prefetch_kb * 1024 + gb - 1) / gb);
             }
         }
+    }
+    static const int tile_min = [] { const char * e = getenv("GGML_B200_FA_TILE_MIN"); return e ? atoi(e) : 16; }();   // 0: never
+    if (tile_min > 0 && q->ne[1] >= tile_min && D <= 128 && q->ne[2] <= 65535 && q->ne[3] <= 65535 && (uintptr_t) k->data % 16 == 0 &&
+        (uintptr_t) v->data % 16 == 0 && k->nb[1] % 16 == 0 && k->nb[2] % 16 == 0 && k->nb[3] % 16 == 0 && v->nb[1] % 16 == 0 && v->nb[2] % 16 == 0 &&
+        v->nb[3] % 16 == 0 && (uintptr_t) dst->data % 8 == 0) {
+        // a prompt batch on the tensor cores: 64 query rows of a head per CTA
+        p.nsplit = 1;
+        p.chunk  = std::max<int64_t>(n_kv, 1);
+        const dim3 g((unsigned) ((q->ne[1] + FT_BQ - 1) / FT_BQ), (unsigned) q->ne[2], (unsigned) q->ne[3]), b(FT_WARPS * 32);
+        if (D == 64) CU(b200_launch(ctx, fa_tile_kernel<64>, g, b, 0, p));
+        else         CU(b200_launch(ctx, fa_tile_kernel<128>, g, b, 0, p));
+        ctx->launches++;
+        return B200_OK;
     }
     if (q->ne[1] >= 4) {   // a batch: several query rows per CTA
         const int NQ = D == 256 ? 4 : 8;

@@ -256,7 +256,13 @@ def _fa_ref(q, k, v, mask, sinks, scale, max_bias, softcap):
 @pytest.mark.parametrize("D,nh,nkv_h,nq,n_kv,opts", [
     (128, 32, 8, 1, 256, {}),                 # Llama-3-8B decode, first cache page
     (128, 32, 8, 1, 4096, {}),                # ... a long context: KV splits + combine
-    (128, 32, 8, 64, 256, {}),                # the 64-token prompt of the greedy test
+    (128, 32, 8, 64, 256, {}),                # the 64-token prompt of the greedy test: tensor-core tiles
+    (128, 8, 2, 200, 456, {}),                # a ragged prompt batch on top of 256 cached positions (partial row block, partial KV tile)
+    (64, 4, 4, 33, 97, {"sinks": True}),
+    (128, 4, 1, 17, 130, {"softcap": 10.0}),
+    (128, 4, 2, 40, 300, {"max_bias": 8.0}),
+    (256, 4, 2, 20, 150, {}),                 # head size 256: the row-block kernel
+    (128, 4, 2, 9, 200, {}),                  # 4..15 rows: the row-block kernel
     (64, 4, 2, 3, 113, {"sinks": True}),
     (256, 8, 8, 2, 1024, {"softcap": 10.0}),
     (128, 8, 2, 5, 777, {"max_bias": 8.0}),
@@ -287,7 +293,9 @@ def test_flash_attn_ext(ctx, D, nh, nkv_h, nq, n_kv, opts):
     got = ctx.flash_attn_ext(q, k, v, mask, sinks, scale, opts.get("max_bias", 0.0), opts.get("softcap", 0.0))
     ref = _fa_ref(q, k, v, mask, sinks, scale, opts.get("max_bias", 0.0), opts.get("softcap", 0.0))
     assert got.shape == ref.shape
-    assert _nmse(ref.cpu().numpy(), got.cpu().numpy()) < 1e-10   # fp32 accumulation of exact fp16 products; test-backend-ops' bar is 5e-4
+    # decode / row-block kernels: fp32 accumulation of exact fp16 products. Tile kernel (16 rows and more, D <= 128): the softmax weights
+    # are rounded to fp16 for the tensor-core P V product (ggml-cpu rounds the whole accumulator to fp16). test-backend-ops' bar is 5e-4.
+    assert _nmse(ref.cpu().numpy(), got.cpu().numpy()) < (1e-10 if nq < 16 or D > 128 else 2e-6)
 
 
 def test_flash_attn_ext_all_masked_row_is_zero(ctx):
