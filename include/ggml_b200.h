@@ -429,6 +429,22 @@ B200_API b200_status  b200_attn_prep(b200_ctx * ctx, const b200_tensor * q, cons
                                      const b200_tensor * pos, const b200_tensor * freq_factors, const b200_rope_params * rp, const b200_tensor * k_idx,
                                      const b200_tensor * k_cache, const b200_tensor * v, const b200_tensor * v_idx, const b200_tensor * v_cache);
 
+/* One token (n_tokens == 1): the same four nodes AND the FLASH_ATTN_EXT behind them as ONE launch. Every CTA of the attention kernel
+ * rotates its own q head and the new K row of its KV head (rope_row's arithmetic), uses them and the new V row instead of the
+ * cache row they belong in, and the first CTA of each KV head writes that row (and q_dst / k_dst). fa_q / fa_k / fa_v: the operands of
+ * the FLASH_ATTN_EXT node (views of q_dst and of the caches); the views must address cache row r, head h where SET_ROWS writes it.
+ * Results equal to b200_attn_prep followed by b200_flash_attn_ext, bit for bit. */
+B200_API int          b200_attn_decode_supported(const b200_tensor * q, const b200_tensor * q_dst, const b200_tensor * k, const b200_tensor * k_dst,
+                                                 const b200_tensor * pos, const b200_tensor * freq_factors, const b200_rope_params * rp,
+                                                 const b200_tensor * k_idx, const b200_tensor * k_cache, const b200_tensor * v, const b200_tensor * v_idx,
+                                                 const b200_tensor * v_cache, const b200_tensor * fa_q, const b200_tensor * fa_k, const b200_tensor * fa_v,
+                                                 const b200_tensor * mask, const b200_tensor * sinks, const b200_tensor * dst);
+B200_API b200_status  b200_attn_decode(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * q_dst, const b200_tensor * k, const b200_tensor * k_dst,
+                                       const b200_tensor * pos, const b200_tensor * freq_factors, const b200_rope_params * rp, const b200_tensor * k_idx,
+                                       const b200_tensor * k_cache, const b200_tensor * v, const b200_tensor * v_idx, const b200_tensor * v_cache,
+                                       const b200_tensor * fa_q, const b200_tensor * fa_k, const b200_tensor * fa_v, const b200_tensor * mask,
+                                       const b200_tensor * sinks, const b200_tensor * dst, float scale, float max_bias, float logit_softcap);
+
 /* GGML_OP_CPY / CONT / DUP (ggml-cpu/ops.cpp ggml_compute_forward_dup; ggml-cuda/cpy.cu): element e of src (any strides) to
  * element e of dst (any strides, same number of elements), F32 / F16 in any combination (F32 -> F16 rounds to nearest even) */
 B200_API int          b200_cpy_supported(const b200_tensor * src, const b200_tensor * dst);

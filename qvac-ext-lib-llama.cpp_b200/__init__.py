@@ -38,7 +38,7 @@ EXPORTS = [
     "b200_mul_mat_fused_supported", "b200_mul_mat_fused", "b200_mul_mat_id_fused_supported", "b200_mul_mat_id_fused",
     "b200_glu", "b200_add", "b200_mul", "b200_add_id",
     "b200_mul_mat_noalloc", "b200_mul_mat_noalloc_max_units",
-    "b200_rms_norm_supported", "b200_rms_norm", "b200_rms_norm_mul_supported", "b200_rms_norm_mul", "b200_attn_prep_supported", "b200_attn_prep",
+    "b200_rms_norm_supported", "b200_rms_norm", "b200_rms_norm_mul_supported", "b200_rms_norm_mul", "b200_attn_prep_supported", "b200_attn_prep", "b200_attn_decode_supported", "b200_attn_decode",
     "b200_mul_mat_shared_src1_norm", "b200_mul_mat_fused_norm", "b200_get_rows_supported", "b200_get_rows", "b200_rope_supported", "b200_rope",
     "b200_set_rows_supported", "b200_set_rows", "b200_cpy_supported", "b200_cpy", "b200_flash_attn_ext_supported", "b200_flash_attn_ext",
 ]
@@ -201,6 +201,8 @@ def lib() -> C.CDLL:
         rpp = C.POINTER(RopeParams)
         L.b200_attn_prep_supported.argtypes = [tp, tp, tp, tp, tp, tp, rpp, tp, tp, tp, tp, tp]
         L.b200_attn_prep.argtypes = [vp, tp, tp, tp, tp, tp, tp, rpp, tp, tp, tp, tp, tp]
+        L.b200_attn_decode_supported.argtypes = [tp, tp, tp, tp, tp, tp, rpp, tp, tp, tp, tp, tp, tp, tp, tp, tp, tp, tp]
+        L.b200_attn_decode.argtypes = [vp, tp, tp, tp, tp, tp, tp, rpp, tp, tp, tp, tp, tp, tp, tp, tp, tp, tp, tp, C.c_float, C.c_float, C.c_float]
         L.b200_get_rows_supported.argtypes = [tp, tp, tp]
         L.b200_get_rows.argtypes = [vp, tp, tp, tp]
         L.b200_rope_supported.argtypes = [tp, tp, tp, tp, C.POINTER(RopeParams)]
@@ -541,6 +543,27 @@ class Context:
                                    None if freq_factors is None else Tensor.of(freq_factors), rp, Tensor.of(k_idx), Tensor.of(k_cache), Tensor.of(v),
                                    Tensor.of(v_idx), Tensor.of(v_cache)), "b200_attn_prep")
         return qo, ko
+
+    def attn_decode(self, q, k, pos, k_cache, k_idx, v, v_cache, v_idx, n_kv, mask, n_dims, mode=0, scale=1.0, freq_factors=None, sinks=None, **kw):
+        """one token: attn_prep + flash_attn_ext in ONE launch. q [1, 1, n_head, D], k [1, 1, n_head_kv, D], v [1, n_head_kv * D]; caches
+        [n_ctx, n_head_kv * D] float16; attention over cache rows [0, n_kv). Returns (attention [1, 1, n_head, D], rope(q), rope(k))"""
+        torch = self.torch
+        nh, D = q.shape[2], q.shape[3]
+        nkv = k.shape[2]
+        qo = torch.empty(q.shape, dtype=torch.float32, device=q.device)
+        ko = torch.empty(k.shape, dtype=torch.float32, device=k.device)
+        out = torch.empty((1, 1, nh, D), dtype=torch.float32, device=q.device)
+        rp = RopeParams(n_dims, mode, kw.get("n_ctx_orig", 0), kw.get("freq_base", 10000.0), kw.get("freq_scale", 1.0), kw.get("ext_factor", 0.0),
+                        kw.get("attn_factor", 1.0), kw.get("beta_fast", 32.0), kw.get("beta_slow", 1.0))
+        fa_q = qo.permute(0, 2, 1, 3)
+        fa_k = k_cache[:n_kv].view(1, n_kv, nkv, D).permute(0, 2, 1, 3)
+        fa_v = v_cache[:n_kv].view(1, n_kv, nkv, D).permute(0, 2, 1, 3)
+        check(lib().b200_attn_decode(self.h, Tensor.of(q), Tensor.of(qo), Tensor.of(k), Tensor.of(ko), Tensor.of(pos),
+                                     None if freq_factors is None else Tensor.of(freq_factors), rp, Tensor.of(k_idx), Tensor.of(k_cache), Tensor.of(v),
+                                     Tensor.of(v_idx), Tensor.of(v_cache), Tensor.of(fa_q), Tensor.of(fa_k), Tensor.of(fa_v),
+                                     None if mask is None else Tensor.of(mask), None if sinks is None else Tensor.of(sinks), Tensor.of(out), scale,
+                                     kw.get("max_bias", 0.0), kw.get("logit_softcap", 0.0)), "b200_attn_decode")
+        return out, qo, ko
 
     def get_rows(self, src0, ids, out=None):
         """GGML_OP_GET_ROWS: src0 a torch tensor [.., n_rows, K] (float32 / float16) or a Tensor (quantized); ids int32 [.., n_ids]"""

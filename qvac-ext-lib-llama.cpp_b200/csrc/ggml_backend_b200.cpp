@@ -931,9 +931,49 @@ bool try_fuse_attn_block(be_ctx * c, ggml_cgraph * cgraph, int i, const norm_src
     if (rq->src[2]) ff = as_b200(rq->src[2]);
     const b200_rope_params rp = rope_params_of(rq);
     if (!b200_attn_prep_supported(&q, &qd, &k, &kd, &pos, rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc)) return false;
+    // one token: the FLASH_ATTN_EXT that follows (behind, in the first layer, the CPY that casts the mask) joins the second launch
+    int j_cpy = -1, j_fa = -1;
+    b200_tensor fq, fk, fv, fm, fs, fd;
+    ggml_tensor * fa = nullptr;
+    // (opt-in, GGML_B200_ATTN_DECODE=1: measured 3 % SLOWER than attn_prep + FLASH_ATTN_EXT on the 8B step - every CTA of the attention
+    // kernel repeats the rotation, which costs more than the launch it saves)
+    static const bool attn_decode_on = [] { const char * e = getenv("GGML_B200_ATTN_DECODE"); return e && atoi(e) != 0; }();
+    if (N == 1 && attn_decode_on) {
+        int jn = next_live(c, cgraph, j[6] + 1);
+        if (jn >= 0 && (cgraph->nodes[jn]->op == GGML_OP_CPY || cgraph->nodes[jn]->op == GGML_OP_CONT) && f3_ok(cgraph->nodes[jn])) {
+            const ggml_tensor * cp = cgraph->nodes[jn];
+            bool indep = true;   // it must not read anything this block writes
+            for (const ggml_tensor * o2 : outs) indep = indep && !ranges_overlap(cp->src[0], o2) && !ranges_overlap(cp, o2);
+            for (int k2 = 0; k2 < 3; k2++) indep = indep && !ranges_overlap(cp->src[0], mm[k2]);
+            if (indep) { j_cpy = jn; jn = next_live(c, cgraph, jn + 1); }
+        }
+        if (jn >= 0 && cgraph->nodes[jn]->op == GGML_OP_FLASH_ATTN_EXT && f3_ok(cgraph->nodes[jn])) {
+            fa = cgraph->nodes[jn];
+            const ggml_tensor * aq = fa->src[0];
+            bool ok = aq && aq->data == rq->data && fa->src[1] && fa->src[2];
+            for (const ggml_tensor * o2 : outs) ok = ok && !ranges_overlap(fa, o2);
+            for (const ggml_tensor * in : ins) ok = ok && (!in || !ranges_overlap(fa, in));
+            for (int k2 = 3; k2 < 5; k2++) ok = ok && (!fa->src[k2] || !ranges_overlap(fa, fa->src[k2]));   // mask, sinks
+            if (ok) {
+                fq = as_b200(aq); fk = as_b200(fa->src[1]); fv = as_b200(fa->src[2]); fd = as_b200(fa);
+                if (fa->src[3]) fm = as_b200(fa->src[3]);
+                if (fa->src[4]) fs = as_b200(fa->src[4]);
+                if (b200_attn_decode_supported(&q, &qd, &k, &kd, &pos, rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc, &fq, &fk, &fv,
+                                               fa->src[3] ? &fm : nullptr, fa->src[4] ? &fs : nullptr, &fd)) j_fa = jn;
+            }
+        }
+    }
+    if (j_fa >= 0 && j_cpy >= 0) { run_f3(c, cgraph->nodes[j_cpy]); c->done[j_cpy] = 1; }
     if (nf) CHECK_RUN(c, b200_mul_mat_shared_src1_norm(c->ctx, 3, d, w, (const float *) nf->x0->data, &nf->n, o));
     else    CHECK_RUN(c, b200_mul_mat_shared_src1(c->ctx, 3, d, w, (const float *) mq->src[1]->data, o));
-    CHECK_RUN(c, b200_attn_prep(c->ctx, &q, &qd, &k, &kd, &pos, rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc));
+    if (j_fa >= 0) {
+        CHECK_RUN(c, b200_attn_decode(c->ctx, &q, &qd, &k, &kd, &pos, rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc, &fq, &fk, &fv,
+                                      fa->src[3] ? &fm : nullptr, fa->src[4] ? &fs : nullptr, &fd, ggml_get_op_params_f32(fa, 0),
+                                      ggml_get_op_params_f32(fa, 1), ggml_get_op_params_f32(fa, 2)));
+        c->done[j_fa] = 1;
+    } else {
+        CHECK_RUN(c, b200_attn_prep(c->ctx, &q, &qd, &k, &kd, &pos, rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc));
+    }
     for (int k2 = 1; k2 < 7; k2++) c->done[j[k2]] = 1;
     return true;
 }

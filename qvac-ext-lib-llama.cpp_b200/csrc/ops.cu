@@ -232,6 +232,26 @@ template <> __device__ __forceinline__ __half cvt_out<__half>(float v) { return 
 
 __device__ __forceinline__ int64_t load_idx(const char * p, int i64) { return i64 ? *(const int64_t *) p : (int64_t) *(const int32_t *) p; }
 
+// cos / sin (times the YaRN magnitude) of pair `ic` at position `base`. theta_base as ggml_rope_cache_init forms it (ops.cpp:5549-5563):
+// pos times theta_scale, ic times over, each product rounded - not powf, so that the angle is the reference's to the bit; then
+// rope_yarn (ops.cpp:5532-5547)
+__device__ __forceinline__ void rope_cs(const RopeP & p, const float * ff, float base, int ic, float & c, float & sn) {
+    float tb = base;
+    for (int k = 0; k < ic; k++) tb = __fmul_rn(tb, p.theta_scale);
+    const float theta_extrap = tb / (ff ? ff[ic] : 1.0f);
+    const float theta_interp = p.freq_scale * theta_extrap;
+    float theta = theta_interp, mscale = p.attn_factor;
+    if (p.ext_factor != 0.0f) {
+        const float yv = ((float) ic - p.corr0) / fmaxf(0.001f, p.corr1 - p.corr0);
+        const float ramp_mix = (1.0f - fminf(1.0f, fmaxf(0.0f, yv))) * p.ext_factor;
+        theta = theta_interp * (1.0f - ramp_mix) + theta_extrap * ramp_mix;
+        mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
+    }
+    c = cosf(theta) * mscale; sn = sinf(theta) * mscale;
+}
+__device__ __forceinline__ float rope_lo(float x0, float x1, float c, float sn) { return __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn)); }
+__device__ __forceinline__ float rope_hi(float x0, float x1, float c, float sn) { return __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c)); }
+
 // one CTA rotates row `row` (i1 = head, i2 = position, i3 = batch): one thread per pair, or per two pass-through channels beyond n_dims
 __device__ __forceinline__ void rope_row(const RopeJob & j, const RopeP & p, int64_t row) {
     const int64_t i1 = row % j.s.ne[1], i2 = (row / j.s.ne[1]) % j.s.ne[2], i3 = row / (j.s.ne[1] * j.s.ne[2]);
@@ -252,24 +272,12 @@ __device__ __forceinline__ void rope_row(const RopeJob & j, const RopeP & p, int
             put(i0, xr[i0]); put(i0 + 1, xr[i0 + 1]);
             continue;
         }
-        // theta_base of pair i0/2 as ggml_rope_cache_init forms it (ops.cpp:5549-5563): pos times theta_scale, i0/2 times over, each
-        // product rounded - not powf, so that the angle is the reference's to the bit; then rope_yarn (ops.cpp:5532-5547)
-        float tb = base;
-        for (int64_t k = 0; k < i0 / 2; k++) tb = __fmul_rn(tb, p.theta_scale);
-        const float theta_extrap = tb / (j.ff ? j.ff[i0 / 2] : 1.0f);
-        const float theta_interp = p.freq_scale * theta_extrap;
-        float theta = theta_interp, mscale = p.attn_factor;
-        if (p.ext_factor != 0.0f) {
-            const float yv = ((float) (i0 / 2) - p.corr0) / fmaxf(0.001f, p.corr1 - p.corr0);
-            const float ramp_mix = (1.0f - fminf(1.0f, fmaxf(0.0f, yv))) * p.ext_factor;
-            theta = theta_interp * (1.0f - ramp_mix) + theta_extrap * ramp_mix;
-            mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
-        }
-        const float c = cosf(theta) * mscale, sn = sinf(theta) * mscale;
+        float c, sn;
+        rope_cs(p, j.ff, base, (int) (i0 / 2), c, sn);
         const int64_t ia = p.neox ? i0 / 2 : i0, ib = p.neox ? i0 / 2 + p.n_dims / 2 : i0 + 1;
         const float x0 = xr[ia], x1 = xr[ib];
-        put(ia, x0 * c - x1 * sn);
-        put(ib, x0 * sn + x1 * c);
+        put(ia, rope_lo(x0, x1, c, sn));   // separately rounded products, as ggml-cpu's x86-64 baseline build (no FMA) computes them
+        put(ib, rope_hi(x0, x1, c, sn));
     }
 }
 __global__ void __launch_bounds__(256) rope_kernel(const RopeJob j, const RopeP p) {
@@ -338,6 +346,20 @@ __global__ void __launch_bounds__(256) cpy_kernel(const char * src, T4 s, char *
 // 64 E-byte read per warp. Online softmax per warp in fp32 (ggml-cpu keeps the F16-V accumulator in fp16: ops.cpp:8102-8123; this
 // one is the more accurate side), warps merged through shared memory, KV splits merged by whichever CTA of a row finishes last. The heads of one GQA
 // group read the same K/V rows out of L2. Decode-shaped: a wide prefill batch re-reads K/V per query row.
+// decode fusion (b200_attn_decode): the kernel rotates its q head and the new token's K row itself (the arithmetic of rope_row),
+// uses them - and the new V row - instead of the cache row they belong in, and the first CTA of a KV head writes that row
+struct FaDec {
+    int on;
+    const float * q_raw, * k_raw, * v_raw;   // the projections: [D * n_head], [D * n_head_kv], [D * n_head_kv]
+    const int32_t * pos;
+    const float * ff;
+    RopeP rp;
+    const char * k_idx, * v_idx;             // the cache slot of the token (I64 / I32)
+    int k_i64, v_i64;
+    char * kc, * vc;                          // row 0 of the K / V cache (F16 rows of kc_nb1 / vc_nb1 bytes)
+    int64_t kc_nb1, vc_nb1, kc_rows, vc_rows;
+    float * q_dst, * k_dst;                   // ROPE(q), ROPE(k) at their graph addresses
+};
 struct FaP {
     T4 q, k, v, m, d;
     const char * qd, * kd, * vd, * md;
@@ -350,6 +372,7 @@ struct FaP {
     float *  ws;       // partials of the KV splits: [row][split][2 + D] = running maximum, sum, accumulator
     unsigned * cnt;    // arrivals per row; the CTA that completes a row merges its splits and puts the counter back to 0
     MvNext   next;     // n_mats > 0: weights to pull into L2 meanwhile (kernels.h mv_prefetch_next)
+    FaDec    dec;
 };
 constexpr int FA_MAX_WARPS = 16;   // warps per CTA: 8 or 16 (launch parameter)
 constexpr int FAQ_WARPS = 8, FAQ_U = 4;   // fa_rows_kernel: 8 warps, 4 KV positions per warp and round
@@ -390,7 +413,57 @@ __device__ __forceinline__ float * fa_dst_row(const FaP & p, int64_t iq1, int64_
     return (float *) (p.dd + (iq3 * p.d.ne[2] * p.d.ne[1] + iq2 + iq1 * p.d.ne[1]) * p.d.nb[1]);
 }
 
-template <int E, int FA_U>
+// decode fusion: qraw / knew / vnew hold the raw projections of this lane's channels; on return the rotated q (F32), and the new K / V
+// rows as the cache will hold them (rounded to F16). Warp 0 of the row's first split writes what the graph's ROPE / SET_ROWS nodes would.
+template <int E>
+__device__ __forceinline__ void fa_dec_rotate(const FaP & p, float (&qraw)[E], float (&knew)[E], float (&vnew)[E], int64_t iq2, int64_t ik2, int64_t iv2,
+                                              int warp, int lane) {
+    constexpr int D = 32 * E;
+    const FaDec & dc = p.dec;
+    const float base = (float) dc.pos[0];
+    float qr[E], kr[E];
+    if (!dc.rp.neox) {   // pairs (2m, 2m + 1): both in this lane
+#pragma unroll
+        for (int m = 0; m < E / 2; m++) {
+            float c, sn;
+            rope_cs(dc.rp, dc.ff, base, lane * (E / 2) + m, c, sn);
+            qr[2 * m] = rope_lo(qraw[2 * m], qraw[2 * m + 1], c, sn); qr[2 * m + 1] = rope_hi(qraw[2 * m], qraw[2 * m + 1], c, sn);
+            kr[2 * m] = rope_lo(knew[2 * m], knew[2 * m + 1], c, sn); kr[2 * m + 1] = rope_hi(knew[2 * m], knew[2 * m + 1], c, sn);
+        }
+    } else {             // pairs (i, i + D/2): the partner is the same slot of lane ^ 16
+#pragma unroll
+        for (int e = 0; e < E; e++) {
+            float c, sn;
+            rope_cs(dc.rp, dc.ff, base, (lane & 15) * E + e, c, sn);
+            const float pq_ = __shfl_xor_sync(0xffffffffu, qraw[e], 16), pk_ = __shfl_xor_sync(0xffffffffu, knew[e], 16);
+            qr[e] = lane < 16 ? rope_lo(qraw[e], pq_, c, sn) : rope_hi(pq_, qraw[e], c, sn);
+            kr[e] = lane < 16 ? rope_lo(knew[e], pk_, c, sn) : rope_hi(pk_, knew[e], c, sn);
+        }
+    }
+    if (blockIdx.y == 0 && warp == 0) {
+        const int64_t slot = load_idx(dc.k_idx, dc.k_i64), slot_v = load_idx(dc.v_idx, dc.v_i64);
+#pragma unroll
+        for (int e = 0; e < E; e++) dc.q_dst[iq2 * D + lane * E + e] = qr[e];
+        if (iq2 % (p.q.ne[2] / p.k.ne[2]) == 0) {
+#pragma unroll
+            for (int e = 0; e < E; e++) dc.k_dst[ik2 * D + lane * E + e] = kr[e];
+            if (slot >= 0 && slot < dc.kc_rows) {
+                __half * o = (__half *) (dc.kc + slot * dc.kc_nb1) + ik2 * D + lane * E;
+#pragma unroll
+                for (int e = 0; e < E; e++) o[e] = __float2half_rn(kr[e]);
+            }
+        }
+        if (iq2 % (p.q.ne[2] / p.v.ne[2]) == 0 && slot_v >= 0 && slot_v < dc.vc_rows) {
+            __half * o = (__half *) (dc.vc + slot_v * dc.vc_nb1) + iv2 * D + lane * E;
+#pragma unroll
+            for (int e = 0; e < E; e++) o[e] = __float2half_rn(vnew[e]);
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < E; e++) { qraw[e] = qr[e]; knew[e] = __half2float(__float2half_rn(kr[e])); vnew[e] = __half2float(__float2half_rn(vnew[e])); }
+}
+
+template <int E, int FA_U, bool DEC = false>
 __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
     constexpr int D = 32 * E;
     const int FA_WARPS = blockDim.x >> 5;
@@ -403,10 +476,21 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
 
     // everything the first round needs is requested before anything is used: q, the mask values and the K / V rows are independent
     // loads (a masked position's rows are read anyway - they are valid cache memory - so that the K / V loads do not wait for the mask)
-    const float * pq = (const float *) (p.qd + iq1 * p.q.nb[1] + iq2 * p.q.nb[2] + iq3 * p.q.nb[3]) + lane * E;
-    float qraw[E];
+    float qraw[E], knew[E], vnew[E];
+    int64_t slot = -1;
+    if constexpr (DEC) {   // the projections of this lane's channels; rotated below, while the first round's K / V rows are on their way
 #pragma unroll
-    for (int e = 0; e < E; e++) qraw[e] = pq[e];
+        for (int e = 0; e < E; e++) {
+            qraw[e] = p.dec.q_raw[iq2 * D + lane * E + e];
+            knew[e] = p.dec.k_raw[ik2 * D + lane * E + e];
+            vnew[e] = p.dec.v_raw[iv2 * D + lane * E + e];
+        }
+        slot = load_idx(p.dec.k_idx, p.dec.k_i64);
+    } else {
+        const float * pq = (const float *) (p.qd + iq1 * p.q.nb[1] + iq2 * p.q.nb[2] + iq3 * p.q.nb[3]) + lane * E;
+#pragma unroll
+        for (int e = 0; e < E; e++) qraw[e] = pq[e];
+    }
     const __half * mp = p.md ? (const __half *) (p.md + iq1 * p.m.nb[1] + (iq2 % p.m.ne[2]) * p.m.nb[2] + (iq3 % p.m.ne[3]) * p.m.nb[3]) : nullptr;
     const char * kb = p.kd + ik2 * p.k.nb[2] + ik3 * p.k.nb[3] + lane * E * 2;
     const char * vb = p.vd + iv2 * p.v.nb[2] + iv3 * p.v.nb[3] + lane * E * 2;
@@ -432,6 +516,7 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
             }
         }
         if (!q_ready) {
+            if constexpr (DEC) fa_dec_rotate<E>(p, qraw, knew, vnew, iq2, ik2, iv2, warp, lane);
 #pragma unroll
             for (int e = 0; e < E; e++) qf[e] = __half2float(__float2half_rn(qraw[e])) * p.scale;   // ggml-cpu converts q to the K type's vec_dot type: fp16
             q_ready = true;
@@ -442,6 +527,10 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
             if (base + u < c1) {
                 float kf[E];
                 unpack<E>(kp[u], kf);
+                if (DEC && base + u == slot) {   // the token's own row is not in the cache yet (or is being written right now)
+#pragma unroll
+                    for (int e = 0; e < E; e++) kf[e] = knew[e];
+                }
 #pragma unroll
                 for (int e = 0; e < E; e++) t += qf[e] * kf[e];
             }
@@ -476,6 +565,10 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
                 const float pr = expf(s[u] - Mn);
                 float vf[E];
                 unpack<E>(vp[u], vf);
+                if (DEC && base + u == slot) {
+#pragma unroll
+                    for (int e = 0; e < E; e++) vf[e] = vnew[e];
+                }
                 S += pr;
 #pragma unroll
                 for (int e = 0; e < E; e++) acc[e] += pr * vf[e];
@@ -1098,14 +1191,14 @@ int b200_flash_attn_ext_supported(const b200_tensor * q, const b200_tensor * k, 
 
 constexpr size_t FA_CNT_BYTES = 4096;   // arrival counters at the head of the split workspace (splits only run with < 2 x SM-count rows)
 
-b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
-                                const b200_tensor * sinks, const b200_tensor * dst, float scale, float max_bias, float logit_softcap) {
+static b200_status fa_run(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
+                          const b200_tensor * sinks, const b200_tensor * dst, float scale, float max_bias, float logit_softcap, const FaDec * dec) {
     if (!b200_flash_attn_ext_supported(q, k, v, mask, sinks, dst))
         return fail(B200_ERR_UNSUPPORTED, "FLASH_ATTN_EXT: F32 q, F16 k / v of head size 64 / 128 / 256, F16 mask");
     if (!ctx) return fail(B200_ERR_ARG, "null context");
     const int64_t rows = q->ne[1] * q->ne[2] * q->ne[3];
     if (rows == 0) return B200_OK;
-    if (!q->data || !dst->data || (k->ne[1] > 0 && (!k->data || !v->data)) || (mask && !mask->data) || (sinks && !sinks->data)) return fail(B200_ERR_ARG, "null argument");
+    if ((!dec && !q->data) || !dst->data || (k->ne[1] > 0 && (!k->data || !v->data)) || (mask && !mask->data) || (sinks && !sinks->data)) return fail(B200_ERR_ARG, "null argument");
     const int D = (int) q->ne[0];
     if ((uintptr_t) k->data % (D / 16) || (uintptr_t) v->data % (D / 16)) return fail(B200_ERR_UNSUPPORTED, "FLASH_ATTN_EXT: K / V rows must be %d-byte aligned", D / 16);
     FaP p;
@@ -1124,7 +1217,7 @@ b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b20
     // at a time: one memory round trip); the splits of a row are merged by the last of its CTAs to finish
     int nsplit = 1;
     static const int u_env = [] { const char * e = getenv("GGML_B200_FA_U"); return e ? atoi(e) : 0; }();   // experiments: 4 / 8 / 16 positions per warp in flight
-    const int U = (u_env == 4 || u_env == 8 || u_env == 16) && D <= 128 ? u_env : fa_u(D / 32);
+    const int U = !dec && (u_env == 4 || u_env == 8 || u_env == 16) && D <= 128 ? u_env : fa_u(D / 32);
     static const int w_env = [] { const char * e = getenv("GGML_B200_FA_WARPS"); return e ? atoi(e) : 0; }();
     const int FA_WARPS = w_env == 16 ? 16 : 8;
     const int64_t n_kv = k->ne[1], round = FA_WARPS * U;   // positions one CTA has in flight at a time
@@ -1147,6 +1240,8 @@ b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b20
         p.cnt = (unsigned *) ctx->fa_ws;
         p.ws  = (float *) ((char *) ctx->fa_ws + FA_CNT_BYTES);
     }
+    memset(&p.dec, 0, sizeof(p.dec));
+    if (dec) p.dec = *dec;
     memset(&p.next, 0, sizeof(p.next));
     if (ctx->fa_prefetch_kb > 0 && ctx->prefetch_kb > 0 && ctx->last_key && ctx->mem_gen == b200_mem_generation()) {
         // the mat-vec launch behind this kernel has been staged by the one in front of it; this kernel's idle HBM time goes to the one after
@@ -1159,6 +1254,14 @@ b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b20
                 p.next.groups_per_cta = (int) (((int64_t) ctx->fa_prefetch_kb * 1024 + gb - 1) / gb);
             }
         }
+    }
+    if (dec) {   // one token: the decode kernel with the ROPEs and the cache rows folded in (8 positions per warp in flight)
+        const dim3 g((unsigned) rows, (unsigned) nsplit), b(FA_WARPS * 32);
+        if (D == 64)       CU(b200_launch(ctx, fa_kernel<2, 8, true>, g, b, 0, p));
+        else if (D == 128) CU(b200_launch(ctx, fa_kernel<4, 8, true>, g, b, 0, p));
+        else               CU(b200_launch(ctx, fa_kernel<8, 8, true>, g, b, 0, p));
+        ctx->launches++;
+        return B200_OK;
     }
     static const int tile_min = [] { const char * e = getenv("GGML_B200_FA_TILE_MIN"); return e ? atoi(e) : 16; }();   // 0: never
     if (tile_min > 0 && q->ne[1] >= tile_min && D <= 128 && q->ne[2] <= 65535 && q->ne[3] <= 65535 && (uintptr_t) k->data % 16 == 0 &&
@@ -1191,6 +1294,58 @@ b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b20
     else               CU(b200_launch(ctx, fa_kernel<8, 8>, grid, block, 0, p));
     ctx->launches++;
     return B200_OK;
+}
+
+b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
+                                const b200_tensor * sinks, const b200_tensor * dst, float scale, float max_bias, float logit_softcap) {
+    return fa_run(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap, nullptr);
+}
+
+// One token: ROPE(q), ROPE(k), SET_ROWS(k cache), SET_ROWS(v cache) and FLASH_ATTN_EXT of a layer as ONE launch. q / k / v are the
+// projections ([D, n_head, 1], [D, n_head_kv, 1], [D * n_head_kv, 1], contiguous F32); q_dst / k_dst the ROPE nodes' outputs; fa_q the
+// FLASH_ATTN_EXT node's q operand (a view of q_dst: shape only), fa_k / fa_v its views of the caches, which must address the row
+// k_idx / v_idx of k_cache / v_cache exactly where SET_ROWS puts it.
+int b200_attn_decode_supported(const b200_tensor * q, const b200_tensor * q_dst, const b200_tensor * k, const b200_tensor * k_dst, const b200_tensor * pos,
+                               const b200_tensor * freq_factors, const b200_rope_params * rp, const b200_tensor * k_idx, const b200_tensor * k_cache,
+                               const b200_tensor * v, const b200_tensor * v_idx, const b200_tensor * v_cache, const b200_tensor * fa_q,
+                               const b200_tensor * fa_k, const b200_tensor * fa_v, const b200_tensor * mask, const b200_tensor * sinks, const b200_tensor * dst) {
+    if (!b200_attn_prep_supported(q, q_dst, k, k_dst, pos, freq_factors, rp, k_idx, k_cache, v, v_idx, v_cache)) return 0;
+    if (!b200_flash_attn_ext_supported(fa_q, fa_k, fa_v, mask, sinks, dst)) return 0;
+    const int64_t D = q->ne[0], nh = q->ne[1], nkv = k->ne[1];
+    if (q->ne[2] != 1 || q->ne[3] != 1 || k->ne[2] != 1 || rp->n_dims != D || fa_q->ne[1] != 1 || fa_q->ne[2] != nh || fa_q->ne[3] != 1) return 0;
+    if (fa_k->ne[2] != nkv || fa_v->ne[2] != nkv || fa_k->ne[3] != 1 || fa_v->ne[3] != 1 || v->ne[0] != D * nkv || v->ne[1] != 1) return 0;
+    for (const b200_tensor * t : { q, q_dst, k, k_dst }) if (t->nb[1] != (size_t) D * 4) return 0;   // heads back to back
+    if (k_cache->type != B200_TYPE_F16 || v_cache->type != B200_TYPE_F16 || k_cache->ne[0] != D * nkv || v_cache->ne[0] != D * nkv) return 0;
+    // the FLASH_ATTN_EXT views see cache row r, head h at base + r * nb1 + h * D * 2: the address SET_ROWS writes
+    if (fa_k->data != k_cache->data || fa_k->nb[1] != k_cache->nb[1] || fa_k->nb[2] != (size_t) D * 2 || fa_k->ne[1] > k_cache->ne[1]) return 0;
+    if (fa_v->data != v_cache->data || fa_v->nb[1] != v_cache->nb[1] || fa_v->nb[2] != (size_t) D * 2 || fa_v->ne[1] > v_cache->ne[1]) return 0;
+    if (k_idx->ne[0] != 1 || v_idx->ne[0] != 1) return 0;
+    return 1;
+}
+
+b200_status b200_attn_decode(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * q_dst, const b200_tensor * k, const b200_tensor * k_dst,
+                             const b200_tensor * pos, const b200_tensor * freq_factors, const b200_rope_params * rp, const b200_tensor * k_idx,
+                             const b200_tensor * k_cache, const b200_tensor * v, const b200_tensor * v_idx, const b200_tensor * v_cache,
+                             const b200_tensor * fa_q, const b200_tensor * fa_k, const b200_tensor * fa_v, const b200_tensor * mask,
+                             const b200_tensor * sinks, const b200_tensor * dst, float scale, float max_bias, float logit_softcap) {
+    if (!b200_attn_decode_supported(q, q_dst, k, k_dst, pos, freq_factors, rp, k_idx, k_cache, v, v_idx, v_cache, fa_q, fa_k, fa_v, mask, sinks, dst))
+        return fail(B200_ERR_UNSUPPORTED, "attn_decode: one token, rope over the whole head, F16 caches seen by FLASH_ATTN_EXT where SET_ROWS writes them");
+    for (const b200_tensor * t : { q, q_dst, k, k_dst, pos, k_idx, k_cache, v, v_idx, v_cache }) if (!t->data) return fail(B200_ERR_ARG, "null argument");
+    if (freq_factors && !freq_factors->data) return fail(B200_ERR_ARG, "null argument");
+    FaDec dc;
+    memset(&dc, 0, sizeof(dc));
+    dc.on = 1;
+    dc.q_raw = (const float *) q->data; dc.k_raw = (const float *) k->data; dc.v_raw = (const float *) v->data;
+    dc.pos = (const int32_t *) pos->data;
+    dc.ff = freq_factors ? (const float *) freq_factors->data : nullptr;
+    dc.rp = rope_consts(rp);
+    dc.k_idx = (const char *) k_idx->data; dc.v_idx = (const char *) v_idx->data;
+    dc.k_i64 = k_idx->type == B200_TYPE_I64; dc.v_i64 = v_idx->type == B200_TYPE_I64;
+    dc.kc = (char *) k_cache->data; dc.vc = (char *) v_cache->data;
+    dc.kc_nb1 = (int64_t) k_cache->nb[1]; dc.vc_nb1 = (int64_t) v_cache->nb[1];
+    dc.kc_rows = k_cache->ne[1]; dc.vc_rows = v_cache->ne[1];
+    dc.q_dst = (float *) q_dst->data; dc.k_dst = (float *) k_dst->data;
+    return fa_run(ctx, fa_q, fa_k, fa_v, mask, sinks, dst, scale, max_bias, logit_softcap, &dc);
 }
 
 } // extern "C"

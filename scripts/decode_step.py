@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--skip", default="none")
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--prefetch-kb", type=int, default=64)
+    ap.add_argument("--one-launch-attn", action="store_true", help="b200_attn_decode instead of attn_prep + flash_attn_ext (measured slower)")
     ap.add_argument("--out", default="")
     a = ap.parse_args()
     import torch
@@ -70,14 +71,21 @@ def main():
                     else:
                         q, k, v = x0[:, :E], x0[:, :NKV * D], x0[:, NKV * D:2 * NKV * D]
                     q4, k4 = q.reshape(1, 1, NH, D), k.reshape(1, 1, NKV, D)
-                    if skip != "prep":
-                        q4, _ = ctx.attn_prep(q4, k4, pos, l["kc"], idx, v.reshape(1, NKV * D), l["vc"], idx, D, 0, freq_base=500000.0, n_ctx_orig=8192)
-                    if skip != "fa":
-                        kview = l["kc"][:a.n_kv].view(1, a.n_kv, NKV, D).permute(0, 2, 1, 3)
-                        vview = l["vc"][:a.n_kv].view(1, a.n_kv, NKV, D).permute(0, 2, 1, 3)
-                        att = ctx.flash_attn_ext(q4.permute(0, 2, 1, 3), kview, vview, mask, None, scale).reshape(1, E)
-                    else:
+                    if skip == "attn":
                         att = q4.reshape(1, E)
+                    elif skip not in ("prep", "fa") and a.one_launch_attn:   # ROPE + KV store + attention: one launch
+                        att, _, _ = ctx.attn_decode(q4, k4, pos, l["kc"], idx, v.reshape(1, NKV * D), l["vc"], idx, a.n_kv, mask, D, 0, scale=scale,
+                                                    freq_base=500000.0, n_ctx_orig=8192)
+                        att = att.reshape(1, E)
+                    else:
+                        if skip != "prep":
+                            q4, _ = ctx.attn_prep(q4, k4, pos, l["kc"], idx, v.reshape(1, NKV * D), l["vc"], idx, D, 0, freq_base=500000.0, n_ctx_orig=8192)
+                        if skip != "fa":
+                            kview = l["kc"][:a.n_kv].view(1, a.n_kv, NKV, D).permute(0, 2, 1, 3)
+                            vview = l["vc"][:a.n_kv].view(1, a.n_kv, NKV, D).permute(0, 2, 1, 3)
+                            att = ctx.flash_attn_ext(q4.permute(0, 2, 1, 3), kview, vview, mask, None, scale).reshape(1, E)
+                        else:
+                            att = q4.reshape(1, E)
                     x2 = ctx.mul_mat_fused(t, l["wo"], None, att, up_bias=x.reshape(-1)) if skip != "o" else x
                     if skip != "gateup":
                         if skip == "norm":

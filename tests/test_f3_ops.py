@@ -107,6 +107,39 @@ def test_attn_prep_is_the_four_nodes(ctx, n_tok, cache_dtype):
     assert float(kc1.float().abs().sum()) > 0
 
 
+@pytest.mark.parametrize("mode", [0, 2])
+@pytest.mark.parametrize("D,nh,nkv,n_kv,slot", [(128, 32, 8, 256, 70), (128, 32, 8, 1024, 1023), (64, 8, 2, 96, 0), (256, 4, 4, 640, 300), (128, 8, 1, 2048, 1500)])
+def test_attn_decode_is_prep_then_flash_attn(ctx, mode, D, nh, nkv, n_kv, slot):
+    """one token: ROPE(q), ROPE(k), the two KV-cache writes and FLASH_ATTN_EXT as ONE launch (the kernel rotates q and the new K row itself
+    and uses the new rows instead of the cache slot being written) - every output bit-identical to b200_attn_prep + b200_flash_attn_ext"""
+    import torch
+    g = torch.Generator(device="cuda").manual_seed(D + nh + n_kv + mode)
+    n_ctx = n_kv + 64
+    q = torch.randn((1, 1, nh, D), device="cuda", generator=g)
+    k = torch.randn((1, 1, nkv, D), device="cuda", generator=g)
+    v = torch.randn((1, nkv * D), device="cuda", generator=g)
+    kc = (torch.randn((n_ctx, nkv * D), device="cuda", generator=g) * 0.5).half()
+    vc = (torch.randn((n_ctx, nkv * D), device="cuda", generator=g) * 0.5).half()
+    pos = torch.tensor([slot + 5], device="cuda", dtype=torch.int32)
+    idx = torch.tensor([slot], device="cuda", dtype=torch.int64)
+    mask = torch.zeros((1, 1, 64, n_kv), device="cuda")
+    mask[0, 0, :, slot + 1:] = -math.inf      # cells behind the token's own are free (or another sequence's)
+    mask[0, 0, :, 2:5] = -math.inf
+    mask = mask.half()
+    scale = 1.0 / math.sqrt(D)
+    kw = dict(freq_base=500000.0, n_ctx_orig=8192)
+    kc1, vc1, kc2, vc2 = kc.clone(), vc.clone(), kc.clone(), vc.clone()
+    qo_ref, ko_ref = ctx.attn_prep(q, k, pos, kc1, idx, v, vc1, idx, D, mode, **kw)
+    kview = kc1[:n_kv].view(1, n_kv, nkv, D).permute(0, 2, 1, 3)
+    vview = vc1[:n_kv].view(1, n_kv, nkv, D).permute(0, 2, 1, 3)
+    ref = ctx.flash_attn_ext(qo_ref.permute(0, 2, 1, 3), kview, vview, mask, None, scale)
+    got, qo, ko = ctx.attn_decode(q, k, pos, kc2, idx, v, vc2, idx, n_kv, mask, D, mode, scale=scale, **kw)
+    assert torch.equal(qo, qo_ref) and torch.equal(ko, ko_ref)
+    assert torch.equal(kc2, kc1) and torch.equal(vc2, vc1)
+    assert torch.equal(got, ref)
+    assert float(got.abs().sum()) > 0
+
+
 @pytest.mark.parametrize("t", [Q4_0, Q8_0, Q4_K, Q5_K, Q6_K])
 def test_get_rows_quantized_is_dequantize_row(pkg, ctx, refq, t):
     """token-embedding lookup from a quantized tok_embd: bit-identical to dequantize_row_<type> (ggml-quants.c) of the chosen rows"""

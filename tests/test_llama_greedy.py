@@ -212,8 +212,12 @@ def test_greedy_whole_graph_on_device(pkg, tmp_path, tname):
     # the fused launches (RMS_NORM+MUL, hoisted q/k/v, ROPE+SET_ROWS) against the same graph node by node: not a bit may differ
     unf = _decode(prefix, "file", [CPU_LIB, pkg.BACKEND_PATH], ngl=99, gen=n_gen, extra=["--fa", "--kqv", "--force", forced], env=_env(GGML_B200_DISABLE_F3_FUSION=1))
     report.update({"gen_s_b200_node_by_node": unf["gen_s"], "fused_equals_node_by_node": unf["tokens"] == got["tokens"] and unf["margins"] == got["margins"]})
+    # ... and with the opt-in one-launch attention (ROPE + cache rows inside the attention kernel: b200_attn_decode)
+    one = _decode(prefix, "file", [CPU_LIB, pkg.BACKEND_PATH], ngl=99, gen=n_gen, extra=["--fa", "--kqv", "--force", forced], env=_env(GGML_B200_ATTN_DECODE=1))
+    report.update({"gen_s_b200_one_launch_attention": one["gen_s"], "one_launch_attention_equals_node_by_node": one["tokens"] == unf["tokens"] and one["margins"] == unf["margins"]})
     _report(f"greedy_device_{tname}.json", report)
     assert report["fused_equals_node_by_node"], report
+    assert report["one_launch_attention_equals_node_by_node"], report
     assert got["graph_splits"] < off["graph_splits"], report
     assert got["graph_splits"] <= 2, report
     assert noise(got) <= 2.0 * n_ref, report
