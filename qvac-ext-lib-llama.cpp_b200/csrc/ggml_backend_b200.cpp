@@ -1,7 +1,8 @@
 // ggml_backend_b200.cpp — the drop-in: a ggml backend ("B200") that implements the reference's five backend vtables
 // (/root/reference/ggml/src/ggml-backend-impl.h:16-204, API version 2) for GGML_OP_MUL_MAT and GGML_OP_MUL_MAT_ID on
-// q4_0 / q8_0 / q4_K / q5_K / q6_K weights x F32 activations, plus the element-wise nodes the fused mat-vec epilogue
-// absorbs (GLU, ADD, MUL, ADD_ID). All device work goes through the C-ABI of
+// q4_0 / q8_0 / q4_K / q5_K / q6_K weights x F32 activations, the element-wise nodes the fused mat-vec epilogue absorbs (GLU, ADD,
+// MUL, ADD_ID), and - SURVEY 8f rank 3, first slice - the ops between the matmuls of a Llama decode graph (GET_ROWS, RMS_NORM, ROPE,
+// SET_ROWS, CPY / CONT / DUP, FLASH_ATTN_EXT) with the planner that fuses them (run_nodes). All device work goes through the C-ABI of
 // include/ggml_b200.h (libb200mm.so); this file contains no CUDA and no CPU compute.
 //
 // Loaded out of tree: GGML_BACKEND_PATH=/path/libggml-b200.so (ggml-backend-reg.cpp:711-715) or ggml_backend_load();

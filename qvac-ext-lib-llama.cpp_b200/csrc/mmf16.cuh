@@ -694,7 +694,7 @@ int mmf_env(const char * name, int dflt) {
 
 template <int BN, int CL>
 b200_status mmf_launch(b200_ctx * ctx, const MmfMaps & maps, const CUtensorMap & map_b, MmfParams & p, int tiles) {
-    static bool attr_done[64] = {};
+    static std::atomic<bool> attr_done[64];
     if (ctx->device < 64 && !attr_done[ctx->device]) {
         CU(cudaFuncSetAttribute(mmf_kernel<BN, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, f_smem(BN, CL)));
         attr_done[ctx->device] = true;

@@ -967,7 +967,7 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
             !make_map(&map_da, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, sA, (uint64_t) N, (uint64_t) (K / 256), (uint64_t) Np * 4 * 8, 128, 1, false)) {
             return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed for the q8_K scale tiles (N=%lld K=%lld)", (long long) N, (long long) K);
         }
-        static bool kattr_done[64] = {};
+        static std::atomic<bool> kattr_done[64];
         if (ctx->device < 64 && !kattr_done[ctx->device]) {
             CU(cudaFuncSetAttribute(mmq_q4k_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KQ_SMEM));
             kattr_done[ctx->device] = true;
@@ -977,7 +977,7 @@ b200_status b200_mmq_run(b200_ctx * ctx, int type, const void * w, size_t nb01, 
         ctx->launches++;
         return B200_OK;
     }
-    static bool attr_done[2][64] = {};
+    static std::atomic<bool> attr_done[2][64];   // zero-initialised; several host threads may launch
     if (ctx->device < 64 && !attr_done[has_min][ctx->device]) {
         if (has_min) CU(cudaFuncSetAttribute(mmq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MMQ_SMEM));
         else         CU(cudaFuncSetAttribute(mmq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MMQ_SMEM));

@@ -20,6 +20,8 @@
 
 #include "quant_core.cuh"
 #include "kernels.h"
+
+#include <atomic>
 #include "epilogue.cuh"
 
 #include <type_traits>
@@ -1119,7 +1121,7 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
         const int room = MV_MAX_CONS - p.n_cons, want = NC * p.U - p.n_cons;
         p.n_helpers = want < 0 ? 0 : (want < room ? want : room);
     }
-    static bool attr_done[64] = {};
+    static std::atomic<bool> attr_done[64];
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_done[dev]) {
@@ -1184,7 +1186,7 @@ static bool mv_lean_ok(int type, int ncols, const MvParams & p, int n_pairs) {
 
 template <int TYPE, int NC, int WIDE, bool EPI = false>
 static cudaError_t mv_fast_launch_w(const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
-    static bool attr_done[64] = {};  // one attribute call per instantiation and device
+    static std::atomic<bool> attr_done[64];  // one attribute call per instantiation and device
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_done[dev]) {

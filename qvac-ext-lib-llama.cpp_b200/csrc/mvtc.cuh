@@ -308,7 +308,7 @@ mvtc_q4k_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant
 template <int BN, int NR>
 b200_status mvtc_launch(b200_ctx * ctx, const CUtensorMap & map_w, const CUtensorMap & map_b, const CUtensorMap & map_bs, const CUtensorMap & map_da,
                         const TcParams & p, int grid) {
-    static bool attr_done[64] = {};
+    static std::atomic<bool> attr_done[64];
     constexpr int SMEM = tc_smem(BN);
     if (ctx->device < 64 && !attr_done[ctx->device]) {
         CU(cudaFuncSetAttribute(mvtc_q4k_kernel<BN, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
