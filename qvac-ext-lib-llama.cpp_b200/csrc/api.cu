@@ -622,8 +622,8 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
             continue;
         }
         mv_cfg  cfg;
-        // the lean kernel takes a bias-only epilogue (MUL_MAT + ADD) on one device; GLU pairs stay on mv_fast_kernel's EPI instantiation
-        const bool lean = (!ep || (ep->glu < 0 && ctx->split.n_ranks <= 1 && nc == 1)) && (ctx->split.n_ranks <= 1 || (ctx->ll_on && !ctx->split_deferred)) && !(ctx->dbg & 1) && mv_lean_type(type);
+        // the lean kernel takes the K7 epilogues (bias rows, GLU pairs) of one device
+        const bool lean = (!ep || (ctx->split.n_ranks <= 1 && nc == 1)) && (ctx->split.n_ranks <= 1 || (ctx->ll_on && !ctx->split_deferred)) && !(ctx->dbg & 1) && mv_lean_type(type);
         while (nc >= 1 && !pick_mv_cfg(ctx, type, U, nc, &cfg, lean && nc <= MV_LEAN_MAX_COLS)) nc--;
         if (nc < 1) return fail(B200_ERR_UNSUPPORTED, "K=%lld: activations do not fit in shared memory", (long long) K);
         for (int o0 = 0; o0 < n_ops; o0 += MV_MAX_MATS) {
@@ -679,7 +679,7 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
             }
             if (ctx->norm.on && x && ncols == 1 && !(ctx->dbg & 4) && p.x_vec && p.split.n_ranks <= 1 && (uintptr_t) ctx->norm.w % 16 == 0) {
                 // MvNorm: the row's RMS_NORM (+ MUL) in the K1 prologue - a GLU pair on the EPI kernel, or a plain launch on the lean kernel
-                const bool glu = ep && ep->glu >= 0, lean_run = !ep && lean && mv_lean_takes(type, 1, p, 1);
+                const bool glu = ep && ep->glu >= 0, bias_only = ep && ep->glu < 0, lean_run = !bias_only && lean && mv_lean_takes(type, 1, p, 1);
                 const int  nq  = lean_run ? std::min(MV_MAX_CONS, std::max(cfg.nw, U)) : cfg.nw;
                 if ((glu || lean_run) && U <= 4 * nq) { p.norm = ctx->norm; ctx->norm_used = true; }
             }

@@ -886,8 +886,10 @@ __device__ __forceinline__ void unit_dot2(uint32_t w0, uint32_t w1, uint32_t am,
 
 // LL: row split with the flagged-payload exchange (its own instantiation: the plain kernel keeps its registers). BIAS: the ADD of a
 // K7 epilogue without GLU (attn_output / ffn_down + residual in a decode graph): mat.bias[row] is added before the store
-// NORM: MvNorm - the RMS_NORM + MUL in front of the q/k/v projections happens in this kernel's K1 prologue
-template <int TYPE, int NC, bool LL, bool BIAS = false, bool NORM = false>
+// NORM: MvNorm - the RMS_NORM + MUL in front of the q/k/v projections happens in this kernel's K1 prologue.
+// GLU: the K7 gate / up pair (MvEpi): the two stages of a pair are the gate rows and the up rows of ONE row group, and the pair's
+// two sums become glu(gate + bias, up + bias) in mat[0].dst - the stage pairs this kernel is built around are exactly that.
+template <int TYPE, int NC, bool LL, bool BIAS = false, bool NORM = false, bool GLU = false>
 __global__ void __launch_bounds__(32 * (MV_MAX_CONS + 1), 1)
 mv_lean_kernel(const __grid_constant__ MvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -934,7 +936,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
         const int w = lane;
         int cnt = 0;
         if (w < NWC && g_end - g_begin > w) cnt = (g_end - g_begin - w + NWC - 1) / NWC;
-        const int n_pair_stages = (cnt >> 1) * 2 * SL, my_total = cnt * SL;
+        const int n_pair_stages = GLU ? cnt * 2 * SL : (cnt >> 1) * 2 * SL, my_total = GLU ? cnt * 2 * SL : cnt * SL;
         int issued = 0, stage = 0, pg = 0, r = 0;  // r: position inside the pair (slice = r >> 1, which = r & 1)
         uint32_t phase = 1;
         while (__any_sync(0xffffffffu, issued < my_total)) {
@@ -942,10 +944,11 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
             if (can) can = mbar_test_wait(smem_u32(empty + w * NS + stage), phase);
             if (can) {
                 int j, slice;
-                if (issued < n_pair_stages) { j = 2 * pg + (r & 1); slice = r >> 1; }
-                else                        { j = cnt - 1; slice = issued - n_pair_stages; }
+                if (GLU)                         { j = pg; slice = r >> 1; }
+                else if (issued < n_pair_stages) { j = 2 * pg + (r & 1); slice = r >> 1; }
+                else                             { j = cnt - 1; slice = issued - n_pair_stages; }
                 const int     group = g_begin + w + j * NWC;
-                const MvMat & mat   = p.mat[mv_find_mat(p, group)];
+                const MvMat & mat   = p.mat[GLU ? (r & 1) : mv_find_mat(p, group)];
                 const int     row0  = (group - mat.group0) * p.rpg;
                 const int     nrow  = min(p.rpg, mat.M - row0);
                 const int     u0    = slice * 32;
@@ -1064,7 +1067,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
 
     int stage = 0;
     uint32_t phase = 0;
-    const int n_pairs = cnt >> 1;
+    const int n_pairs = GLU ? cnt : cnt >> 1;
     for (int pg = 0; pg < n_pairs; pg++) {
         float accA[NC], accB[NC];
 #pragma unroll
@@ -1083,11 +1086,26 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
             stage += 2;
             if (stage == NS) { stage = 0; phase ^= 1; }
         }
+        if constexpr (GLU) {   // one row group: accA = its gate rows, accB = its up rows
+            const int row = (g_begin + w + pg * NWC) * p.rpg + rr;
+            float vg = accA[0], vu = accB[0];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float tg = __shfl_xor_sync(0xffffffffu, vg, o), tu = __shfl_xor_sync(0xffffffffu, vu, o);
+                if (o < L) { vg += tg; vu += tu; }
+            }
+            if (sub == 0 && lane_on && row < p.mat[0].M) {
+                if (p.mat[0].bias) vg += p.mat[0].bias[row];
+                if (p.mat[1].bias) vu += p.mat[1].bias[row];
+                p.mat[0].dst[row] = glu_apply(p.epi.glu - 1, vg, vu, p.epi.alpha, p.epi.limit);
+            }
+            continue;
+        }
         const int groupA = g_begin + w + 2 * pg * NWC;
         reduce_store(accA, groupA);
         reduce_store(accB, groupA + NWC);
     }
-    if (cnt & 1) {  // the odd group at the end of the warp's list: one stage per slice
+    if (!GLU && (cnt & 1)) {  // the odd group at the end of the warp's list: one stage per slice
         float acc[NC];
 #pragma unroll
         for (int c = 0; c < NC; c++) acc[c] = 0.0f;
@@ -1113,7 +1131,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     }
 }
 
-template <int TYPE, int NC, bool LL, bool BIAS = false, bool NORM = false>
+template <int TYPE, int NC, bool LL, bool BIAS = false, bool NORM = false, bool GLU = false>
 static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t smem, cudaStream_t st) {
     MvParams p = p_in;
     p.n_helpers = 0;
@@ -1125,9 +1143,9 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS, NORM, GLU>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS, NORM>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS, NORM, GLU>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
@@ -1145,12 +1163,16 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
     }
     cfg.attrs    = attr;
     cfg.numAttrs = na;
-    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE, NC, LL, BIAS, NORM>, p);
+    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE, NC, LL, BIAS, NORM, GLU>, p);
 }
 
 // the launch can take the lean kernel: one column, plain MUL_MAT, no exchange, no epilogue, an even ring
 template <int TYPE>
 static cudaError_t mv_lean_launch_n(int nc, const MvParams & p, int n_ctas, size_t smem, cudaStream_t st) {
+    if (p.epi.glu) {   // the K7 pair (biases, if any, are looked at inside)
+        if (nc != 1 || p.split.n_ranks > 1 || p.n_mats != 2) return cudaErrorInvalidValue;
+        return p.norm.on ? mv_lean_launch_t<TYPE, 1, false, false, true, true>(p, n_ctas, smem, st) : mv_lean_launch_t<TYPE, 1, false, false, false, true>(p, n_ctas, smem, st);
+    }
     for (int i = 0; i < p.n_mats; i++) {
         if (p.mat[i].bias) return nc == 1 && p.split.n_ranks <= 1 && !p.norm.on ? mv_lean_launch_t<TYPE, 1, false, true>(p, n_ctas, smem, st) : cudaErrorInvalidValue;
     }
@@ -1179,7 +1201,8 @@ static bool mv_lean_ok(int type, int ncols, const MvParams & p, int n_pairs);
 bool mv_lean_takes(int type, int ncols, const MvParams & p, int n_pairs) { return mv_lean_ok(type, ncols, p, n_pairs); }
 
 static bool mv_lean_ok(int type, int ncols, const MvParams & p, int n_pairs) {
-    if (!mv_lean_type(type) || ncols < 1 || ncols > MV_LEAN_MAX_COLS || n_pairs != 1 || p.ids.ids || (p.split.n_ranks > 1 && !p.split.ll) || p.epi.glu || (p.n_stages & 1) || (p.dbg & 1)) return false;
+    if (!mv_lean_type(type) || ncols < 1 || ncols > MV_LEAN_MAX_COLS || n_pairs != 1 || p.ids.ids || (p.split.n_ranks > 1 && !p.split.ll) || (p.n_stages & 1) || (p.dbg & 1)) return false;
+    if (p.epi.glu && (ncols != 1 || p.split.n_ranks > 1 || p.n_mats != 2 || (p.dbg & 32))) return false;   // dbg 32: the K7 pair stays on mv_fast_kernel
     for (int i = 0; i < p.n_mats; i++) if (p.mat[i].bias && (ncols != 1 || p.split.n_ranks > 1)) return false;
     return true;
 }
