@@ -429,6 +429,16 @@ B200_API b200_status  b200_attn_prep(b200_ctx * ctx, const b200_tensor * q, cons
                                      const b200_tensor * pos, const b200_tensor * freq_factors, const b200_rope_params * rp, const b200_tensor * k_idx,
                                      const b200_tensor * k_cache, const b200_tensor * v, const b200_tensor * v_idx, const b200_tensor * v_cache);
 
+/* The three attention projections of a layer (src0s = wq, wk, wv against the shared activations x, optionally un-normalized: norm != NULL
+ * as in b200_mul_mat_shared_src1_norm) into dsts[0..2], followed by b200_attn_prep on them (q / k / v describe dsts[0..2] as the ROPE /
+ * SET_ROWS nodes see them). For one token on the lean mat-vec kernel (normal-mode rope over the whole head, F16 caches) the rotation
+ * and the cache stores happen in the kernel's own store - a row group is an even number of consecutive rows, i.e. whole rope pairs - and
+ * neither dsts[] nor a second launch are needed: the decode step's [norm + q/k/v + rope + KV store] is ONE launch. Same bits either way. */
+B200_API b200_status  b200_qkv_rope(b200_ctx * ctx, const b200_mul_mat_desc * descs, const void * const * src0s, const float * x, const b200_norm * norm,
+                                    float * const * dsts, const b200_tensor * q, const b200_tensor * q_dst, const b200_tensor * k, const b200_tensor * k_dst,
+                                    const b200_tensor * pos, const b200_tensor * freq_factors, const b200_rope_params * rp, const b200_tensor * k_idx,
+                                    const b200_tensor * k_cache, const b200_tensor * v, const b200_tensor * v_idx, const b200_tensor * v_cache);
+
 /* One token (n_tokens == 1): the same four nodes AND the FLASH_ATTN_EXT behind them as ONE launch. Every CTA of the attention kernel
  * rotates its own q head and the new K row of its KV head (rope_row's arithmetic), uses them and the new V row instead of the
  * cache row they belong in, and the first CTA of each KV head writes that row (and q_dst / k_dst). fa_q / fa_k / fa_v: the operands of

@@ -38,7 +38,7 @@ EXPORTS = [
     "b200_mul_mat_fused_supported", "b200_mul_mat_fused", "b200_mul_mat_id_fused_supported", "b200_mul_mat_id_fused",
     "b200_glu", "b200_add", "b200_mul", "b200_add_id",
     "b200_mul_mat_noalloc", "b200_mul_mat_noalloc_max_units",
-    "b200_rms_norm_supported", "b200_rms_norm", "b200_rms_norm_mul_supported", "b200_rms_norm_mul", "b200_attn_prep_supported", "b200_attn_prep", "b200_attn_decode_supported", "b200_attn_decode",
+    "b200_rms_norm_supported", "b200_rms_norm", "b200_rms_norm_mul_supported", "b200_rms_norm_mul", "b200_attn_prep_supported", "b200_attn_prep", "b200_attn_decode_supported", "b200_attn_decode", "b200_qkv_rope",
     "b200_mul_mat_shared_src1_norm", "b200_mul_mat_fused_norm", "b200_get_rows_supported", "b200_get_rows", "b200_rope_supported", "b200_rope",
     "b200_set_rows_supported", "b200_set_rows", "b200_cpy_supported", "b200_cpy", "b200_flash_attn_ext_supported", "b200_flash_attn_ext",
 ]
@@ -201,6 +201,7 @@ def lib() -> C.CDLL:
         rpp = C.POINTER(RopeParams)
         L.b200_attn_prep_supported.argtypes = [tp, tp, tp, tp, tp, tp, rpp, tp, tp, tp, tp, tp]
         L.b200_attn_prep.argtypes = [vp, tp, tp, tp, tp, tp, tp, rpp, tp, tp, tp, tp, tp]
+        L.b200_qkv_rope.argtypes = [vp, C.POINTER(MulMatDesc), C.POINTER(vp), vp, C.POINTER(Norm), C.POINTER(vp), tp, tp, tp, tp, tp, tp, rpp, tp, tp, tp, tp, tp]
         L.b200_attn_decode_supported.argtypes = [tp, tp, tp, tp, tp, tp, rpp, tp, tp, tp, tp, tp, tp, tp, tp, tp, tp, tp]
         L.b200_attn_decode.argtypes = [vp, tp, tp, tp, tp, tp, tp, rpp, tp, tp, tp, tp, tp, tp, tp, tp, tp, tp, tp, C.c_float, C.c_float, C.c_float]
         L.b200_get_rows_supported.argtypes = [tp, tp, tp]
@@ -542,6 +543,32 @@ class Context:
         check(lib().b200_attn_prep(self.h, Tensor.of(q), Tensor.of(qo), Tensor.of(k), Tensor.of(ko), Tensor.of(pos),
                                    None if freq_factors is None else Tensor.of(freq_factors), rp, Tensor.of(k_idx), Tensor.of(k_cache), Tensor.of(v),
                                    Tensor.of(v_idx), Tensor.of(v_cache)), "b200_attn_prep")
+        return qo, ko
+
+    def qkv_rope(self, t, Ws, x, pos, k_cache, k_idx, v_cache, v_idx, n_head, n_head_kv, n_dims, mode=0, norm_w=None, norm_eps=None, freq_factors=None, **kw):
+        """[RMS_NORM + MUL] + q/k/v projections + ROPE(q), ROPE(k) + the two KV-cache rows: x float32 [n_tok, K] -> (rope(q) [1, n_tok, n_head, D],
+        rope(k) [1, n_tok, n_head_kv, D]); one launch for one token (b200_qkv_rope)"""
+        torch = self.torch
+        N, K = x.shape
+        descs = (MulMatDesc * 3)()
+        Ms = [W.numel() // row_size(t, K) for W in Ws]
+        D = Ms[0] // n_head
+        for i in range(3):
+            descs[i] = MulMatDesc.contiguous(t, Ms[i], K, N)
+        raw = [torch.empty((N, M), dtype=torch.float32, device=x.device) for M in Ms]
+        wp = (C.c_void_p * 3)(*[W.data_ptr() for W in Ws])
+        op = (C.c_void_p * 3)(*[o.data_ptr() for o in raw])
+        q, k, v = raw[0].view(1, N, n_head, D), raw[1].view(1, N, n_head_kv, D), raw[2]
+        qo, ko = torch.empty_like(q), torch.empty_like(k)
+        nm = None
+        if norm_eps is not None:
+            y = torch.empty_like(x)
+            nm = C.byref(Norm(None if norm_w is None else norm_w.data_ptr(), norm_eps, y.data_ptr(), K * 4))
+        rp = RopeParams(n_dims, mode, kw.get("n_ctx_orig", 0), kw.get("freq_base", 10000.0), kw.get("freq_scale", 1.0), kw.get("ext_factor", 0.0),
+                        kw.get("attn_factor", 1.0), kw.get("beta_fast", 32.0), kw.get("beta_slow", 1.0))
+        check(lib().b200_qkv_rope(self.h, descs, wp, x.data_ptr(), nm, op, Tensor.of(q), Tensor.of(qo), Tensor.of(k), Tensor.of(ko), Tensor.of(pos),
+                                  None if freq_factors is None else Tensor.of(freq_factors), rp, Tensor.of(k_idx), Tensor.of(k_cache), Tensor.of(v),
+                                  Tensor.of(v_idx), Tensor.of(v_cache)), "b200_qkv_rope")
         return qo, ko
 
     def attn_decode(self, q, k, pos, k_cache, k_idx, v, v_cache, v_idx, n_kv, mask, n_dims, mode=0, scale=1.0, freq_factors=None, sinks=None, **kw):

@@ -683,6 +683,11 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
                 const int  nq  = lean_run ? std::min(MV_MAX_CONS, std::max(cfg.nw, U)) : cfg.nw;
                 if ((glu || lean_run) && U <= 4 * nq) { p.norm = ctx->norm; ctx->norm_used = true; }
             }
+            if (ctx->rope.on && x && ncols == 1 && n_ops == 3 && p.n_mats == 3 && !ep && !(p.rpg & 1) && p.split.n_ranks <= 1 && lean &&
+                mv_lean_takes(type, 1, p, 1)) {
+                p.rope = ctx->rope;   // MvRope: the rows leave the kernel rotated / as KV-cache rows
+                ctx->rope_used = true;
+            }
             const int n_ctas = g < ctx->sm_count ? g : ctx->sm_count;
             if (ctx->prefetch_kb > 0) {
                 if (ctx->mem_gen != b200_mem_generation()) {  // an allocation went away: forget what was learned
@@ -1009,6 +1014,43 @@ b200_status b200_mul_mat_fused_norm(b200_ctx * ctx, const b200_mul_mat_desc * d,
     if (b200_status st = norm_then(ctx, *d, x, nm)) return st;
     const b200_mul_mat_desc dn = with_src1_rows(*d, nm->y_nb1);
     return b200_mul_mat_fused(ctx, &dn, up, gate, nm->y, f, dst);
+}
+
+// q / k / v of one token with ROPE(q), ROPE(k), SET_ROWS(k cache), SET_ROWS(v cache) folded into the mat-vec launch (MvRope). When
+// the launch cannot take them (another kernel, another layout) the projections go to dsts[] as usual and b200_attn_prep follows.
+b200_status b200_qkv_rope(b200_ctx * ctx, const b200_mul_mat_desc * descs, const void * const * src0s, const float * x, const b200_norm * nm,
+                          float * const * dsts, const b200_tensor * q, const b200_tensor * q_dst, const b200_tensor * k, const b200_tensor * k_dst,
+                          const b200_tensor * pos, const b200_tensor * freq_factors, const b200_rope_params * rp, const b200_tensor * k_idx,
+                          const b200_tensor * k_cache, const b200_tensor * v, const b200_tensor * v_idx, const b200_tensor * v_cache) {
+    if (!ctx || !descs || !src0s || !x || !dsts) return fail(B200_ERR_ARG, "null argument");
+    if (!b200_attn_prep_supported(q, q_dst, k, k_dst, pos, freq_factors, rp, k_idx, k_cache, v, v_idx, v_cache))
+        return fail(B200_ERR_UNSUPPORTED, "qkv_rope: the ROPE / SET_ROWS nodes of one layer (see b200_attn_prep)");
+    const int64_t D = q->ne[0];
+    const bool one_token = descs[0].ne11 == 1 && q->ne[2] == 1 && q->ne[3] == 1 && k->ne[2] == 1 && v->ne[1] == 1 && v->ne[2] == 1 && v->ne[3] == 1;
+    const bool fold = one_token && rp->mode == B200_ROPE_NORMAL && rp->n_dims == D && k_cache->type == B200_TYPE_F16 && v_cache->type == B200_TYPE_F16 &&
+                      q_dst->nb[1] == (size_t) D * 4 && k_dst->nb[1] == (size_t) D * 4 && descs[0].ne01 == D * q->ne[1] && descs[1].ne01 == D * k->ne[1] &&
+                      descs[2].ne01 == v->ne[0] && k_cache->ne[0] == descs[1].ne01 && v_cache->ne[0] == descs[2].ne01 && k_idx->ne[0] == 1 && v_idx->ne[0] == 1 &&
+                      q->data == dsts[0] && k->data == dsts[1] && v->data == dsts[2];
+    if (fold) {
+        b200::MvRope r;
+        memset(&r, 0, sizeof(r));
+        r.on = 1; r.head_dim = (int) D;
+        r.rp = b200_rope_consts(rp);
+        r.pos = (const int32_t *) pos->data; r.ff = freq_factors ? (const float *) freq_factors->data : nullptr;
+        r.q_dst = (float *) q_dst->data; r.k_dst = (float *) k_dst->data;
+        r.k_idx = (const char *) k_idx->data; r.v_idx = (const char *) v_idx->data;
+        r.k_i64 = k_idx->type == B200_TYPE_I64; r.v_i64 = v_idx->type == B200_TYPE_I64;
+        r.kc = (char *) k_cache->data; r.vc = (char *) v_cache->data;
+        r.kc_nb1 = (int64_t) k_cache->nb[1]; r.vc_nb1 = (int64_t) v_cache->nb[1];
+        r.kc_rows = k_cache->ne[1]; r.vc_rows = v_cache->ne[1];
+        ctx->rope = r;
+        ctx->rope_used = false;
+    }
+    const b200_status st = nm ? b200_mul_mat_shared_src1_norm(ctx, 3, descs, src0s, x, nm, dsts) : b200_mul_mat_shared_src1(ctx, 3, descs, src0s, x, dsts);
+    ctx->rope.on = 0;
+    if (st != B200_OK) return st;
+    if (fold && ctx->rope_used) return B200_OK;
+    return b200_attn_prep(ctx, q, q_dst, k, k_dst, pos, freq_factors, rp, k_idx, k_cache, v, v_idx, v_cache);
 }
 
 // ------------------------------------------------------------------------------------------------ K7: fused epilogues

@@ -965,6 +965,14 @@ bool try_fuse_attn_block(be_ctx * c, ggml_cgraph * cgraph, int i, const norm_src
         }
     }
     if (j_fa >= 0 && j_cpy >= 0) { run_f3(c, cgraph->nodes[j_cpy]); c->done[j_cpy] = 1; }
+    if (j_fa < 0) {
+        // projections + ROPEs + cache rows: one launch for one token where the mat-vec kernel can fold them into its store (b200_qkv_rope),
+        // the projections followed by b200_attn_prep otherwise
+        CHECK_RUN(c, b200_qkv_rope(c->ctx, d, w, (const float *) (nf ? nf->x0->data : mq->src[1]->data), nf ? &nf->n : nullptr, o, &q, &qd, &k, &kd, &pos,
+                                   rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc));
+        for (int k2 = 1; k2 < 7; k2++) c->done[j[k2]] = 1;
+        return true;
+    }
     if (nf) CHECK_RUN(c, b200_mul_mat_shared_src1_norm(c->ctx, 3, d, w, (const float *) nf->x0->data, &nf->n, o));
     else    CHECK_RUN(c, b200_mul_mat_shared_src1(c->ctx, 3, d, w, (const float *) mq->src[1]->data, o));
     if (j_fa >= 0) {

@@ -79,6 +79,8 @@ struct b200_ctx {
     const void * tc_act_x = nullptr; size_t tc_act_rs = 0; int64_t tc_act_N = 0, tc_act_K = 0; const void * tc_act_buf = nullptr;
     b200::MvNorm norm = {};                     // b200_mul_mat_*_norm: the RMS_NORM (+ MUL) the next one-column mat-vec launch applies to its src1
     bool         norm_used = false;             // ... and whether a launch took it
+    b200::MvRope rope = {};                     // b200_qkv_rope: the ROPE / KV-cache stores the next q/k/v mat-vec launch applies to its rows
+    bool         rope_used = false;
     int          fa_prefetch_kb = 0;            // FLASH_ATTN_EXT pulls this much per CTA of the mat-vec launch AFTER the next one into L2 (GGML_B200_FA_PREFETCH_KB)
     void *       fa_ws = nullptr; size_t fa_ws_size = 0;   // FLASH_ATTN_EXT: partial (max, sum, accumulator) of the KV splits (ops.cu)
     int          moe_tile_min  = 48;           // MUL_MAT_ID: one tile GEMM per expert from this many pairs per expert on average (GGML_B200_MOE_TILE_MIN; 0 = never)
@@ -102,6 +104,8 @@ inline cudaError_t b200_launch(const b200_ctx * ctx, void (*kernel)(KArgs...), d
     cfg.numAttrs = ctx->pdl ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
+
+b200::RopeP b200_rope_consts(const b200_rope_params * rp);   // ops.cu: theta_scale and the YaRN ramp range of a ROPE node
 
 // bumped whenever device memory the library may hold predictions / caches for is freed or rewritten
 uint64_t b200_mem_generation();

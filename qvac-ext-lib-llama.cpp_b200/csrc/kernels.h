@@ -250,6 +250,36 @@ struct MvNorm {
     int           on;
 };
 
+// ROPE constants of a node (ops.cu rope_consts) and the rotation itself, shared by the stand-alone ROPE kernels (ops.cu) and the mat-vec
+// kernel that rotates its q / k rows in its epilogue (MvRope): one set of functions, one set of bits
+struct RopeP {
+    int   n_dims, neox;
+    float theta_scale, freq_scale, ext_factor, attn_factor, corr0, corr1;
+};
+#ifdef __CUDACC__
+__device__ __forceinline__ int64_t load_idx(const char * p, int i64) { return i64 ? *(const int64_t *) p : (int64_t) *(const int32_t *) p; }
+
+// cos / sin (times the YaRN magnitude) of pair `ic` at position `base`. theta_base as ggml_rope_cache_init forms it (ops.cpp:5549-5563):
+// pos times theta_scale, ic times over, each product rounded - not powf, so that the angle is the reference's to the bit; then
+// rope_yarn (ops.cpp:5532-5547)
+__device__ __forceinline__ void rope_cs(const RopeP & p, const float * ff, float base, int ic, float & c, float & sn) {
+    float tb = base;
+    for (int k = 0; k < ic; k++) tb = __fmul_rn(tb, p.theta_scale);
+    const float theta_extrap = tb / (ff ? ff[ic] : 1.0f);
+    const float theta_interp = p.freq_scale * theta_extrap;
+    float theta = theta_interp, mscale = p.attn_factor;
+    if (p.ext_factor != 0.0f) {
+        const float yv = ((float) ic - p.corr0) / fmaxf(0.001f, p.corr1 - p.corr0);
+        const float ramp_mix = (1.0f - fminf(1.0f, fmaxf(0.0f, yv))) * p.ext_factor;
+        theta = theta_interp * (1.0f - ramp_mix) + theta_extrap * ramp_mix;
+        mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
+    }
+    c = cosf(theta) * mscale; sn = sinf(theta) * mscale;
+}
+__device__ __forceinline__ float rope_lo(float x0, float x1, float c, float sn) { return __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn)); }
+__device__ __forceinline__ float rope_hi(float x0, float x1, float c, float sn) { return __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c)); }
+#endif
+
 #ifdef __CUDACC__
 // L2 prefetch of the head (groups_per_cta row groups) of every CTA's range of the predicted launch nx, shared among `nb` warps of the
 // calling grid (this is warp b). Used by the mat-vec kernels' producer warps for the launch behind them, and by FLASH_ATTN_EXT - whose
@@ -278,6 +308,23 @@ __device__ __forceinline__ void mv_prefetch_next(const MvNext & nx, int b, int n
 }
 #endif
 
+// The q / k / v projections of ONE token with what build_attn does to them next folded into the store of the lean mat-vec kernel:
+// mat[0] = wq, mat[1] = wk, mat[2] = wv; a row group holds an even number of consecutive rows, i.e. whole ROPE pairs (normal mode,
+// n_dims = head size). q rows go rotated to q_dst, k rows rotated to k_dst and - as F16 - into row k_idx[0] of the K cache, v rows as
+// F16 into row v_idx[0] of the V cache: ROPE(q), ROPE(k), SET_ROWS(k), SET_ROWS(v) without a launch of their own.
+struct MvRope {
+    int             on;
+    int             head_dim;
+    RopeP           rp;
+    const int32_t * pos;
+    const float *   ff;
+    float *         q_dst, * k_dst;
+    const char *    k_idx, * v_idx;
+    int             k_i64, v_i64;
+    char *          kc, * vc;
+    int64_t         kc_nb1, vc_nb1, kc_rows, vc_rows;
+};
+
 struct MvParams {
     MvMat           mat[MV_MAX_MATS];
     int             n_mats;
@@ -302,6 +349,7 @@ struct MvParams {
     MvNext          next;
     MvEpi           epi;
     MvNorm          norm;
+    MvRope          rope;
     // debug timeline (b200_ctx_trace): 8 x u64 per CTA at trace + blockIdx.x*8: globaltimer ns of [0] CTA start, [1] first and
     // [2] last weight copy issued, [3] consumer warp 0 past griddepcontrol.wait, [4] activations quantized, [5] first stage
     // landed, [6] consumer warp 0 done, [7] SM id. nullptr = off.

@@ -889,7 +889,8 @@ __device__ __forceinline__ void unit_dot2(uint32_t w0, uint32_t w1, uint32_t am,
 // NORM: MvNorm - the RMS_NORM + MUL in front of the q/k/v projections happens in this kernel's K1 prologue.
 // GLU: the K7 gate / up pair (MvEpi): the two stages of a pair are the gate rows and the up rows of ONE row group, and the pair's
 // two sums become glu(gate + bias, up + bias) in mat[0].dst - the stage pairs this kernel is built around are exactly that.
-template <int TYPE, int NC, bool LL, bool BIAS = false, bool NORM = false, bool GLU = false>
+// ROPE: MvRope - the launch is q / k / v of one token; the rows leave the kernel rotated / as KV-cache rows.
+template <int TYPE, int NC, bool LL, bool BIAS = false, bool NORM = false, bool GLU = false, bool ROPE = false>
 __global__ void __launch_bounds__(32 * (MV_MAX_CONS + 1), 1)
 mv_lean_kernel(const __grid_constant__ MvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -1056,6 +1057,29 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
                 const float t = __shfl_xor_sync(0xffffffffu, v, o);
                 if (o < L) v += t;
             }
+            if constexpr (ROPE) {   // rows 2m and 2m + 1 of a head sit in neighbouring row slots of this group: lanes rr * L and (rr ^ 1) * L
+                const float other = __shfl_xor_sync(0xffffffffu, v, L);
+                if (sub == 0 && lane_on && row < mat.M) {
+                    const MvRope & r = p.rope;
+                    const int m = (int) (&mat - p.mat);
+                    if (m < 2) {
+                        float cs, sn;
+                        rope_cs(r.rp, r.ff, (float) r.pos[0], (row % r.head_dim) >> 1, cs, sn);
+                        const float y = (row & 1) ? rope_hi(other, v, cs, sn) : rope_lo(v, other, cs, sn);
+                        if (m == 0) {
+                            r.q_dst[row] = y;
+                        } else {
+                            r.k_dst[row] = y;
+                            const int64_t slot = load_idx(r.k_idx, r.k_i64);
+                            if (slot >= 0 && slot < r.kc_rows) ((__half *) (r.kc + slot * r.kc_nb1))[row] = __float2half_rn(y);
+                        }
+                    } else {
+                        const int64_t slot = load_idx(r.v_idx, r.v_i64);
+                        if (slot >= 0 && slot < r.vc_rows) ((__half *) (r.vc + slot * r.vc_nb1))[row] = __float2half_rn(v);
+                    }
+                }
+                continue;
+            }
             if (sub == 0 && lane_on && row < mat.M) {
                 float * a = mat.dst + (int64_t) c * mat.dst_cs + row;
                 if constexpr (BIAS) { if (mat.bias) v += mat.bias[row]; }
@@ -1131,7 +1155,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     }
 }
 
-template <int TYPE, int NC, bool LL, bool BIAS = false, bool NORM = false, bool GLU = false>
+template <int TYPE, int NC, bool LL, bool BIAS = false, bool NORM = false, bool GLU = false, bool ROPE = false>
 static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t smem, cudaStream_t st) {
     MvParams p = p_in;
     p.n_helpers = 0;
@@ -1143,9 +1167,9 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS, NORM, GLU>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS, NORM, GLU, ROPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS, NORM, GLU>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        e = cudaFuncSetAttribute(mv_lean_kernel<TYPE, NC, LL, BIAS, NORM, GLU, ROPE>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
@@ -1163,7 +1187,7 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
     }
     cfg.attrs    = attr;
     cfg.numAttrs = na;
-    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE, NC, LL, BIAS, NORM, GLU>, p);
+    return cudaLaunchKernelEx(&cfg, mv_lean_kernel<TYPE, NC, LL, BIAS, NORM, GLU, ROPE>, p);
 }
 
 // the launch can take the lean kernel: one column, plain MUL_MAT, no exchange, no epilogue, an even ring
@@ -1175,6 +1199,10 @@ static cudaError_t mv_lean_launch_n(int nc, const MvParams & p, int n_ctas, size
     }
     for (int i = 0; i < p.n_mats; i++) {
         if (p.mat[i].bias) return nc == 1 && p.split.n_ranks <= 1 && !p.norm.on ? mv_lean_launch_t<TYPE, 1, false, true>(p, n_ctas, smem, st) : cudaErrorInvalidValue;
+    }
+    if (p.rope.on) {   // q / k / v of one token: rows leave rotated / as cache rows
+        if (nc != 1 || p.split.n_ranks > 1 || p.n_mats != 3 || (p.rpg & 1)) return cudaErrorInvalidValue;
+        return p.norm.on ? mv_lean_launch_t<TYPE, 1, false, false, true, false, true>(p, n_ctas, smem, st) : mv_lean_launch_t<TYPE, 1, false, false, false, false, true>(p, n_ctas, smem, st);
     }
     if (p.norm.on) return nc == 1 && p.split.n_ranks <= 1 && p.fuse_quant ? mv_lean_launch_t<TYPE, 1, false, false, true>(p, n_ctas, smem, st) : cudaErrorInvalidValue;
     if (p.split.n_ranks > 1) {
@@ -1236,6 +1264,7 @@ static cudaError_t mv_fast_launch_w(const MvParams & p, int n_ctas, int n_pairs,
 
 template <int TYPE, int NC>
 static cudaError_t mv_fast_launch_t(const MvParams & p, int n_ctas, int n_pairs, size_t smem, cudaStream_t st) {
+    if (p.rope.on) return cudaErrorInvalidValue;   // MvRope: the lean kernel only (api.cu decides)
     bool epi = p.epi.glu != 0;
     for (int i = 0; i < p.n_mats; i++) epi = epi || p.mat[i].bias != nullptr;
     if (p.norm.on && !epi) return cudaErrorInvalidValue;   // MvNorm: the lean kernel's NORM instantiation or an EPI one (api.cu decides)

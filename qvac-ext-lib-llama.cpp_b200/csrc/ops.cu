@@ -205,10 +205,6 @@ __global__ void __launch_bounds__(256) get_rows_kernel(int type, const char * sr
 }
 
 // ------------------------------------------------------------------------------------------------ ROPE (normal and neox pairs)
-struct RopeP {
-    int   n_dims, neox;
-    float theta_scale, freq_scale, ext_factor, attn_factor, corr0, corr1;
-};
 // where a rotated K row also goes (attn_prep_kernel): row idx[token] of the KV cache, at this head's channels, as F16 or F32 -
 // the SET_ROWS that follows ROPE(k) in build_attn (src/llama-graph.cpp:1604, llama_kv_cache::cpy_k)
 struct RowStore {
@@ -229,28 +225,6 @@ template <typename OUT>
 __device__ __forceinline__ OUT cvt_out(float v);
 template <> __device__ __forceinline__ float cvt_out<float>(float v) { return v; }
 template <> __device__ __forceinline__ __half cvt_out<__half>(float v) { return __float2half_rn(v); }
-
-__device__ __forceinline__ int64_t load_idx(const char * p, int i64) { return i64 ? *(const int64_t *) p : (int64_t) *(const int32_t *) p; }
-
-// cos / sin (times the YaRN magnitude) of pair `ic` at position `base`. theta_base as ggml_rope_cache_init forms it (ops.cpp:5549-5563):
-// pos times theta_scale, ic times over, each product rounded - not powf, so that the angle is the reference's to the bit; then
-// rope_yarn (ops.cpp:5532-5547)
-__device__ __forceinline__ void rope_cs(const RopeP & p, const float * ff, float base, int ic, float & c, float & sn) {
-    float tb = base;
-    for (int k = 0; k < ic; k++) tb = __fmul_rn(tb, p.theta_scale);
-    const float theta_extrap = tb / (ff ? ff[ic] : 1.0f);
-    const float theta_interp = p.freq_scale * theta_extrap;
-    float theta = theta_interp, mscale = p.attn_factor;
-    if (p.ext_factor != 0.0f) {
-        const float yv = ((float) ic - p.corr0) / fmaxf(0.001f, p.corr1 - p.corr0);
-        const float ramp_mix = (1.0f - fminf(1.0f, fmaxf(0.0f, yv))) * p.ext_factor;
-        theta = theta_interp * (1.0f - ramp_mix) + theta_extrap * ramp_mix;
-        mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
-    }
-    c = cosf(theta) * mscale; sn = sinf(theta) * mscale;
-}
-__device__ __forceinline__ float rope_lo(float x0, float x1, float c, float sn) { return __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn)); }
-__device__ __forceinline__ float rope_hi(float x0, float x1, float c, float sn) { return __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c)); }
 
 // one CTA rotates row `row` (i1 = head, i2 = position, i3 = batch): one thread per pair, or per two pass-through channels beyond n_dims
 __device__ __forceinline__ void rope_row(const RopeJob & j, const RopeP & p, int64_t row) {
@@ -1048,7 +1022,9 @@ int b200_rope_supported(const b200_tensor * x, const b200_tensor * pos, const b2
     return x->ne[1] * x->ne[2] * x->ne[3] < (1ll << 31);
 }
 
-static RopeP rope_consts(const b200_rope_params * rp) {
+static RopeP rope_consts(const b200_rope_params * rp) { return b200_rope_consts(rp); }
+} // extern "C"
+b200::RopeP b200_rope_consts(const b200_rope_params * rp) {
     // ggml_rope_yarn_corr_dims (ggml.c: ggml_rope_yarn_corr_dim): the channel range the YaRN ramp covers
     RopeP p;
     p.n_dims = rp->n_dims; p.neox = rp->mode == B200_ROPE_NEOX;
@@ -1059,6 +1035,7 @@ static RopeP rope_consts(const b200_rope_params * rp) {
     p.corr1 = fminf((float) rp->n_dims - 1.0f, ceilf(corr_dim(rp->beta_slow)));
     return p;
 }
+extern "C" {
 static RopeJob rope_job(const b200_tensor * x, const b200_tensor * pos, const b200_tensor * ff, const b200_tensor * dst) {
     RopeJob j;
     j.s = t4(x); j.d = t4(dst);

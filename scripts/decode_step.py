@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """decode_step.py — one WHOLE Llama-3-8B token step through the C-ABI (what libggml-b200.so launches for a decode cgraph once its
-planner has fused it: per layer [RMS_NORM+MUL+q/k/v], [ROPE q,k + KV-cache rows], [FLASH_ATTN_EXT], [attn_output+residual],
+planner has fused it: per layer [RMS_NORM+MUL+q/k/v+ROPE q,k+KV-cache rows], [FLASH_ATTN_EXT], [attn_output+residual],
 [RMS_NORM+MUL+gate/up+SWIGLU], [ffn_down+residual]; then the output norm and lm_head), replayed as a CUDA graph. Prints ms per token
 and, with --skip, the same step without one class of launches: the marginal in-graph cost of each kernel (a dependent chain cannot
 be timed kernel by kernel any other way without a profiler serialising it). Weights: tests/golden slabs gathered at random, like bench.py.
@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--prefetch-kb", type=int, default=64)
     ap.add_argument("--one-launch-attn", action="store_true", help="b200_attn_decode instead of attn_prep + flash_attn_ext (measured slower)")
+    ap.add_argument("--no-qkv-rope", action="store_true", help="q/k/v and attn_prep as two launches instead of b200_qkv_rope's one")
     ap.add_argument("--out", default="")
     a = ap.parse_args()
     import torch
@@ -63,15 +64,26 @@ def main():
             def step():
                 x = x0
                 for l in L:
-                    if skip != "qkv":
+                    folded = False
+                    if skip not in ("qkv", "prep", "attn", "norm") and not a.no_qkv_rope and not a.one_launch_attn:
+                        # norm + q/k/v + ROPE + KV-cache rows: ONE launch
+                        q4, _ = ctx.qkv_rope(t, [l["wq"], l["wk"], l["wv"]], x, pos, l["kc"], idx, l["vc"], idx, NH, NKV, D, 0, norm_w=l["an"], norm_eps=1e-5,
+                                             freq_base=500000.0, n_ctx_orig=8192)
+                        folded = True
+                    elif skip != "qkv":
                         if skip == "norm":
                             q, k, v = ctx.mul_mat_shared(t, [l["wq"], l["wk"], l["wv"]], x)
                         else:
                             q, k, v = ctx.mul_mat_shared(t, [l["wq"], l["wk"], l["wv"]], x, norm_w=l["an"], norm_eps=1e-5)
                     else:
                         q, k, v = x0[:, :E], x0[:, :NKV * D], x0[:, NKV * D:2 * NKV * D]
-                    q4, k4 = q.reshape(1, 1, NH, D), k.reshape(1, 1, NKV, D)
-                    if skip == "attn":
+                    if not folded:
+                        q4, k4 = q.reshape(1, 1, NH, D), k.reshape(1, 1, NKV, D)
+                    if folded:
+                        kview = l["kc"][:a.n_kv].view(1, a.n_kv, NKV, D).permute(0, 2, 1, 3)
+                        vview = l["vc"][:a.n_kv].view(1, a.n_kv, NKV, D).permute(0, 2, 1, 3)
+                        att = ctx.flash_attn_ext(q4.permute(0, 2, 1, 3), kview, vview, mask, None, scale).reshape(1, E) if skip != "fa" else q4.reshape(1, E)
+                    elif skip == "attn":
                         att = q4.reshape(1, E)
                     elif skip not in ("prep", "fa") and a.one_launch_attn:   # ROPE + KV store + attention: one launch
                         att, _, _ = ctx.attn_decode(q4, k4, pos, l["kc"], idx, v.reshape(1, NKV * D), l["vc"], idx, a.n_kv, mask, D, 0, scale=scale,

@@ -107,6 +107,37 @@ def test_attn_prep_is_the_four_nodes(ctx, n_tok, cache_dtype):
     assert float(kc1.float().abs().sum()) > 0
 
 
+@pytest.mark.parametrize("t", [Q4_K, Q4_0, Q8_0, Q6_K])
+@pytest.mark.parametrize("K,D,nh,nkv,N,mode,norm", [(4096, 128, 32, 8, 1, 0, True), (4096, 128, 32, 8, 1, 0, False), (2048, 64, 8, 2, 1, 0, True),
+                                                    (4096, 128, 32, 8, 1, 2, True), (4096, 128, 32, 8, 3, 0, True), (8192, 128, 8, 8, 1, 0, True)])
+def test_qkv_rope_is_the_nodes(pkg, ctx, refq, t, K, D, nh, nkv, N, mode, norm):
+    """[RMS_NORM + MUL] + the three attention projections + ROPE(q), ROPE(k) + the KV-cache rows through b200_qkv_rope: ONE launch for one
+    token on the lean mat-vec kernel (normal-mode rope: a row group is whole rope pairs), projections + attn_prep otherwise - the rotated
+    q / k and both caches bit-identical to norm, MUL_MATs, ROPE, ROPE, SET_ROWS, SET_ROWS node by node"""
+    import torch
+    rng = np.random.default_rng(K + D + N + t + mode)
+    Ws = [torch.from_numpy(refq.quantize_weights(t, rng.normal(0, 1, (M, K)).astype(np.float32) / 8)).cuda() for M in (nh * D, nkv * D, nkv * D)]
+    x = torch.from_numpy(rng.normal(0, 2, (N, K)).astype(np.float32)).cuda()
+    w = torch.from_numpy(rng.normal(1, 0.2, K).astype(np.float32)).cuda()
+    n_ctx = 64
+    pos = torch.arange(17, 17 + N, device="cuda", dtype=torch.int32)
+    idx = torch.arange(20, 20 + N, device="cuda", dtype=torch.int64)
+    kc1 = (torch.randn((n_ctx, nkv * D), device="cuda") * 0.5).half()
+    vc1 = (torch.randn((n_ctx, nkv * D), device="cuda") * 0.5).half()
+    kc2, vc2 = kc1.clone(), vc1.clone()
+    kw = dict(freq_base=500000.0, n_ctx_orig=8192)
+    xn = ctx.rms_norm_mul(x.reshape(1, 1, N, K), w, 1e-5).reshape(N, K) if norm else x
+    q, k, v = ctx.mul_mat_shared(t, Ws, xn)
+    qo_ref, ko_ref = ctx.attn_prep(q.view(1, N, nh, D), k.view(1, N, nkv, D), pos, kc1, idx, v, vc1, idx, D, mode, **kw)
+    n0 = ctx.launches
+    qo, ko = ctx.qkv_rope(t, Ws, x, pos, kc2, idx, vc2, idx, nh, nkv, D, mode, norm_w=w if norm else None, norm_eps=1e-5 if norm else None, **kw)
+    n_launch = ctx.launches - n0
+    assert torch.equal(kc2, kc1) and torch.equal(vc2, vc1)
+    assert torch.equal(qo, qo_ref) and torch.equal(ko, ko_ref)
+    if N == 1 and mode == 0 and t in (Q4_K, Q4_0, Q8_0) and K <= 4096:
+        assert n_launch == 1, n_launch      # everything really happened in the mat-vec launch
+
+
 @pytest.mark.parametrize("mode", [0, 2])
 @pytest.mark.parametrize("D,nh,nkv,n_kv,slot", [(128, 32, 8, 256, 70), (128, 32, 8, 1024, 1023), (64, 8, 2, 96, 0), (256, 4, 4, 640, 300), (128, 8, 1, 2048, 1500)])
 def test_attn_decode_is_prep_then_flash_attn(ctx, mode, D, nh, nkv, n_kv, slot):
