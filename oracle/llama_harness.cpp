@@ -349,7 +349,7 @@ int cmd_run(int argc, char ** argv) {
     }
     const double gen_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
 
-    printf("{\"loader\": \"%s\", \"ngl\": %d, \"n_prompt\": %d, \"load_s\": %.3f, \"prompt_s\": %.3f, \"gen_s\": %.3f, \"graph_splits\": %d, \"tokens\": [", loader.c_str(), ngl,
+    printf("{\"loader\": \"%s\", \"ngl\": %d, \"n_prompt\": %d, \"load_s\": %.3f, \"prompt_s\": %.6f, \"gen_s\": %.6f, \"graph_splits\": %d, \"tokens\": [", loader.c_str(), ngl,
            n_prompt, load_s, prompt_s, gen_s, g_graph_splits);
     for (size_t i = 0; i < out.size(); i++) printf("%s%d", i ? ", " : "", out[i]);
     printf("], \"margins\": [");
