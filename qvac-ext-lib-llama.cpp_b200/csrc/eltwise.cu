@@ -19,6 +19,25 @@ __global__ void __launch_bounds__(256) glu_kernel(int op, float alpha, float lim
     }
 }
 
+// the shapes a prompt batch produces in bulk: all three tensors contiguous and 16-byte aligned, src1 either the same shape (residual
+// add) or one row repeated (norm weight, bias): float4 per thread, no index arithmetic (the general kernel divides 64-bit indices per element)
+template <bool MUL>
+__global__ void __launch_bounds__(256) add_flat_kernel(const float4 * a, const float4 * b, float4 * dst, int64_t n4, int64_t period4) {
+    pdl_prologue();
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t) gridDim.x * blockDim.x) {
+        const float4 x = a[i], y = b[period4 ? i % period4 : i];
+        dst[i] = MUL ? make_float4(x.x * y.x, x.y * y.y, x.z * y.z, x.w * y.w) : make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
+    }
+}
+__global__ void __launch_bounds__(256) glu_flat_kernel(int op, float alpha, float limit, const float4 * x, const float4 * g, float4 * dst, int64_t n4) {
+    pdl_prologue();
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t) gridDim.x * blockDim.x) {
+        const float4 a = x[i], b = g[i];
+        dst[i] = make_float4(glu_apply(op, a.x, b.x, alpha, limit), glu_apply(op, a.y, b.y, alpha, limit), glu_apply(op, a.z, b.z, alpha, limit),
+                             glu_apply(op, a.w, b.w, alpha, limit));
+    }
+}
+
 struct AddParams {
     int64_t ne[4];                // dst / src0 extents
     int64_t ne1[4];               // src1 extents (each divides ne[i])
@@ -80,6 +99,14 @@ b200_status b200_glu(b200_ctx * ctx, int glu_op, float alpha, float limit, const
     if (e != cudaSuccess) return FAIL_CUDA(e);
     const int64_t total = nc * nrows;
     if (b200_status fst = b200_split_flush(ctx)) return fst;  // the inputs may be a dst whose remote slices are still in flight
+    if (nc % 4 == 0 && gate_nb1 == (size_t) nc * 4 && up_nb1 == (size_t) nc * 4 && dst_nb1 == (size_t) nc * 4 &&
+        ((uintptr_t) gate | (uintptr_t) up | (uintptr_t) dst) % 16 == 0) {
+        e = b200_launch(ctx, glu_flat_kernel, dim3(grid_for(ctx, total / 4)), dim3(256), 0, glu_op, alpha, limit, (const float4 *) gate, (const float4 *) up,
+                        (float4 *) dst, total / 4);
+        if (e != cudaSuccess) return FAIL_CUDA(e);
+        ctx->launches++;
+        return B200_OK;
+    }
     e = b200_launch(ctx, glu_kernel, dim3(grid_for(ctx, total)), dim3(256), 0, glu_op, alpha, limit, gate, (int64_t) (gate_nb1 / 4), up, (int64_t) (up_nb1 / 4), dst,
                     (int64_t) (dst_nb1 / 4), nc, total);
     if (e != cudaSuccess) return FAIL_CUDA(e);
@@ -105,6 +132,24 @@ static b200_status binary_bcast(b200_ctx * ctx, bool mul, const int64_t * ne, co
     cudaError_t e = cudaSetDevice(ctx->device);
     if (e != cudaSuccess) return FAIL_CUDA(e);
     if (b200_status fst = b200_split_flush(ctx)) return fst;
+    {
+        auto contiguous = [](const int64_t * n, const size_t * nb) {
+            size_t want = 4;
+            for (int i = 0; i < 4; i++) { if (n[i] != 1 && nb[i] != want) return false; want *= (size_t) n[i]; }
+            return true;
+        };
+        const bool same = ne_b[0] == ne[0] && ne_b[1] == ne[1] && ne_b[2] == ne[2] && ne_b[3] == ne[3];
+        const bool row  = ne_b[0] == ne[0] && ne_b[1] == 1 && ne_b[2] == 1 && ne_b[3] == 1;
+        if ((same || row) && ne[0] % 4 == 0 && total >= 4096 && contiguous(ne, nb_a) && contiguous(ne, nb_d) && contiguous(ne_b, nb_b) &&
+            ((uintptr_t) a | (uintptr_t) b | (uintptr_t) dst) % 16 == 0) {
+            const int64_t n4 = total / 4, per = same ? 0 : ne[0] / 4;
+            e = mul ? b200_launch(ctx, add_flat_kernel<true>, dim3(grid_for(ctx, n4)), dim3(256), 0, (const float4 *) a, (const float4 *) b, (float4 *) dst, n4, per)
+                    : b200_launch(ctx, add_flat_kernel<false>, dim3(grid_for(ctx, n4)), dim3(256), 0, (const float4 *) a, (const float4 *) b, (float4 *) dst, n4, per);
+            if (e != cudaSuccess) return FAIL_CUDA(e);
+            ctx->launches++;
+            return B200_OK;
+        }
+    }
     e = mul ? b200_launch(ctx, add_kernel<true>, dim3(grid_for(ctx, total)), dim3(256), 0, p, a, b, dst, total)
             : b200_launch(ctx, add_kernel<false>, dim3(grid_for(ctx, total)), dim3(256), 0, p, a, b, dst, total);
     if (e != cudaSuccess) return FAIL_CUDA(e);

@@ -291,6 +291,43 @@ __global__ void __launch_bounds__(256) attn_prep_kernel(const RopeJob q, const R
     else set_rows_row(v, b - nq - nk);
 }
 
+// The same for a batch of tokens: one CTA per token computes the cos / sin of its position once (the chain of rounded products and
+// the sinf / cosf are per pair, not per head) and applies them to every q and k head of the token; then its v row.
+__device__ __forceinline__ void rope_heads_tab(const RopeJob & j, const RopeP & p, int64_t i2, const float * cs, const float * sn) {
+    const int64_t half = j.s.ne[0] / 2, n = j.s.ne[1] * half;
+    char * srow = nullptr;
+    if (j.st.base) {
+        const int64_t r = load_idx(j.st.idx + i2 * j.st.idx_nb0, j.st.i64);
+        if (r >= 0 && r < j.st.n_rows) srow = j.st.base + r * j.st.row_nb;
+    }
+    for (int64_t t = threadIdx.x; t < n; t += blockDim.x) {
+        const int64_t i1 = t / half, pr = t - i1 * half, i0 = 2 * pr;
+        const float * xr = (const float *) (j.x + i1 * j.s.nb[1] + i2 * j.s.nb[2]);
+        float *       yr = (float *) (j.y + i1 * j.d.nb[1] + i2 * j.d.nb[2]);
+        char * sr = srow ? srow + i1 * j.s.ne[0] * (j.st.f16 ? 2 : 4) : nullptr;
+        auto put = [&](int64_t i, float v) {
+            yr[i] = v;
+            if (sr) { if (j.st.f16) ((__half *) sr)[i] = __float2half_rn(v); else ((float *) sr)[i] = v; }
+        };
+        if (i0 >= p.n_dims) { put(i0, xr[i0]); put(i0 + 1, xr[i0 + 1]); continue; }
+        const int64_t ia = p.neox ? pr : i0, ib = p.neox ? pr + p.n_dims / 2 : i0 + 1;
+        const float x0 = xr[ia], x1 = xr[ib];
+        put(ia, rope_lo(x0, x1, cs[pr], sn[pr]));
+        put(ib, rope_hi(x0, x1, cs[pr], sn[pr]));
+    }
+}
+__global__ void __launch_bounds__(256) attn_prep_tok_kernel(const RopeJob q, const RopeJob k, const SetRowsJob v, const RopeP p) {
+    __shared__ float cs[256], sn[256];
+    pdl_prologue();
+    const int64_t tok = blockIdx.x;
+    const float base = (float) q.pos[tok];
+    for (int ic = threadIdx.x; ic < p.n_dims / 2; ic += blockDim.x) rope_cs(p, q.ff, base, ic, cs[ic], sn[ic]);
+    __syncthreads();
+    rope_heads_tab(q, p, tok, cs, sn);
+    rope_heads_tab(k, p, tok, cs, sn);
+    set_rows_row(v, tok);
+}
+
 // ------------------------------------------------------------------------------------------------ CPY / CONT / DUP
 // element e (in the order of the SOURCE's logical index) goes to the same linear index of the destination's shape
 template <typename IN> __device__ __forceinline__ float cvt_in(IN v);
@@ -1117,6 +1154,13 @@ b200_status b200_attn_prep(b200_ctx * ctx, const b200_tensor * q, const b200_ten
     jk.st.row_nb = (int64_t) k_cache->nb[1]; jk.st.n_rows = k_cache->ne[1];
     jk.st.f16 = k_cache->type == B200_TYPE_F16; jk.st.i64 = k_idx->type == B200_TYPE_I64;
     OPS_PROLOGUE(ctx);
+    const int64_t n_tok = q->ne[2];
+    if (n_tok >= 8 && q->ne[3] == 1 && k->ne[2] == n_tok && v->ne[1] == n_tok && v->ne[2] == 1 && v->ne[3] == 1 && rp->n_dims <= 512) {
+        // a batch: one CTA per token, the cos / sin of the token's position computed once for all its heads
+        CU(b200_launch(ctx, attn_prep_tok_kernel, dim3((unsigned) n_tok), dim3(256), 0, jq, jk, set_rows_job(v, v_idx, v_cache), rope_consts(rp)));
+        ctx->launches++;
+        return B200_OK;
+    }
     CU(b200_launch(ctx, attn_prep_kernel, dim3((unsigned) (nq + nk + nv)), dim3(256), 0, jq, jk, set_rows_job(v, v_idx, v_cache), rope_consts(rp), (int) nq, (int) nk));
     ctx->launches++;
     return B200_OK;

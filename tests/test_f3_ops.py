@@ -82,12 +82,12 @@ def test_norm_folded_into_the_mat_vec_is_the_nodes(pkg, ctx, refq, t, K, N):
 
 
 @pytest.mark.parametrize("cache_dtype", ["float16", "float32"])
-@pytest.mark.parametrize("n_tok", [1, 5])
+@pytest.mark.parametrize("n_tok", [1, 5, 37])
 def test_attn_prep_is_the_four_nodes(ctx, n_tok, cache_dtype):
     """ROPE(q), ROPE(k), SET_ROWS(k cache), SET_ROWS(v cache) of one layer in one launch: bit-identical to the four ops"""
     import torch
     g = torch.Generator(device="cuda").manual_seed(8 + n_tok)
-    D, nh, nkv, n_ctx = 128, 32, 8, 96
+    D, nh, nkv, n_ctx = 128, 32, 8, 128
     q = torch.randn((1, n_tok, nh, D), device="cuda", generator=g)
     k = torch.randn((1, n_tok, nkv, D), device="cuda", generator=g)
     v = torch.randn((n_tok, nkv * D), device="cuda", generator=g)
