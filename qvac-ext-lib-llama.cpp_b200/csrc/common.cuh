@@ -51,7 +51,7 @@ __device__ __forceinline__ void pdl_prologue() {
 }
 // The canonical sum of squares of a row whose length is a multiple of 256 (RMS_NORM): per 256-element unit, lane l adds the squares
 // of its 8 consecutive values by fmaf in order, the 32 lane sums go through an xor-shuffle tree (every lane gets the unit's sum), and
-// the unit sums are added in unit order. rms_norm_kernel (ops.cu) and the mat-vec kernels that normalize their activations themselves
+// the unit sums are added by a second xor-shuffle tree (lane u holds units u and u + 32). rms_norm_kernel (ops.cu) and the mat-vec kernels that normalize their activations themselves
 // (mmvq.cu, MvNorm) both follow it, so a fused launch gives the bits of the stand-alone node.
 __device__ __forceinline__ float unit_sumsq(const float (&v)[8]) {
     float s = 0.0f;
@@ -61,10 +61,17 @@ __device__ __forceinline__ float unit_sumsq(const float (&v)[8]) {
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     return s;
 }
-__device__ __forceinline__ float rms_scale(const float * unit_sums, int n_units, float eps) {
-    float tot = 0.0f;
-    for (int u = 0; u < n_units; u++) tot += unit_sums[u];
+__device__ __forceinline__ float rms_scale(const float * unit_sums, int n_units, float eps) {   // whole warps call this (n_units <= 64)
+    const int lane = threadIdx.x & 31;
+    float tot = (lane < n_units ? unit_sums[lane] : 0.0f) + (lane + 32 < n_units ? unit_sums[lane + 32] : 0.0f);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
     return 1.0f / sqrtf(tot / (float) (n_units * 256) + eps);
+}
+__device__ __forceinline__ unsigned long long global_ns_c() {   // %globaltimer, for the debug timelines (b200_ctx_trace)
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
 }
 __device__ __forceinline__ float half_bits_to_float(uint16_t h) { return __half2float(__ushort_as_half(h)); }
 

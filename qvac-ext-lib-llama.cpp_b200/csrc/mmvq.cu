@@ -376,16 +376,23 @@ __device__ __forceinline__ void griddep_launch_dependents() { asm volatile("grid
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 // MvNorm inside the fused K1 prologue: v[b] = unit t0 + b * stride of the row (valid while < n_units). Every quantizing warp calls it
 // exactly once (also a warp without a unit: the barrier counts it).
-__device__ __forceinline__ void norm_units(float (&v)[4][8], const MvNorm & nm, int t0, int stride, int n_units, int lane, float * part, int n_threads) {
-    float wv[4][8];
+// this warp's share of the norm weights (they do not depend on the previous kernel: the lean kernel requests them before its
+// griddepcontrol.wait - measured on the device timeline, the norm prologue took 2.2 - 3.2 us against 1.0 us without a norm, the
+// difference being these loads queueing behind the weight stream)
+__device__ __forceinline__ void norm_load_w(float (&wv)[4][8], const MvNorm & nm, int t0, int stride, int n_units, int lane) {
 #pragma unroll
-    for (int b = 0; b < 4; b++) {   // the norm weights are requested before the row's values are waited for
+    for (int b = 0; b < 4; b++) {
         const int t = t0 + b * stride;
         if (t < n_units && nm.w) {
             const float4 e = __ldg((const float4 *) nm.w + t * 64 + lane * 2), f = __ldg((const float4 *) nm.w + t * 64 + lane * 2 + 1);
             wv[b][0] = e.x; wv[b][1] = e.y; wv[b][2] = e.z; wv[b][3] = e.w; wv[b][4] = f.x; wv[b][5] = f.y; wv[b][6] = f.z; wv[b][7] = f.w;
         }
     }
+}
+template <bool PRE = false>
+__device__ __forceinline__ void norm_units(float (&v)[4][8], const MvNorm & nm, int t0, int stride, int n_units, int lane, float * part, int n_threads,
+                                           float (&wv)[4][8]) {
+    if (!PRE) norm_load_w(wv, nm, t0, stride, n_units, lane);   // requested before the row's values are waited for
 #pragma unroll
     for (int b = 0; b < 4; b++) {
         const int t = t0 + b * stride;
@@ -597,7 +604,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
                 asm volatile("" : "+f"(v[0][0]), "+f"(v[0][7]));
                 MV_TRACE(7);
             }
-            if constexpr (EPI) { if (norm_on) norm_units(v, p.norm, t0, NWC, n_tasks, lane, (float *) (smem + 64), NWC * 32); }
+            if constexpr (EPI) { if (norm_on) { float wv[4][8]; norm_units<false>(v, p.norm, t0, NWC, n_tasks, lane, (float *) (smem + 64), NWC * 32, wv); } }
 #pragma unroll
             for (int b = 0; b < 4; b++) {
                 const int t = t0 + b * NWC;
@@ -984,6 +991,8 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     int cnt = 0;
     if (w < NWC && g_end - g_begin > w) cnt = (g_end - g_begin - w + NWC - 1) / NWC;
 
+    float nwv[NORM ? 4 : 1][8];
+    if constexpr (NORM) norm_load_w(nwv, p.norm, qw, NQ, NC * U, lane);   // ahead of the stream dependency: weights never depend on it
     griddep_wait();
     if (w == 0) MV_TRACE(3);
     // row split, flagged-payload exchange (kernels.h ll_store / ll_receive): this launch's epoch is final once the stream dependency is
@@ -1016,7 +1025,7 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
                 asm volatile("" : "+f"(v[0][0]), "+f"(v[0][7]));
                 MV_TRACE(7);
             }
-            if constexpr (NORM) norm_units(v, p.norm, t0, NQ, n_tasks, lane, (float *) (smem + 64), NQ * 32);
+            if constexpr (NORM) norm_units<true>(v, p.norm, t0, NQ, n_tasks, lane, (float *) (smem + 64), NQ * 32, nwv);
 #pragma unroll
             for (int b = 0; b < 4; b++) {
                 const int t = t0 + b * NQ;

@@ -382,7 +382,10 @@ struct FaP {
     int64_t  chunk;
     float *  ws;       // partials of the KV splits: [row][split][2 + D] = running maximum, sum, accumulator
     unsigned * cnt;    // arrivals per row; the CTA that completes a row merges its splits and puts the counter back to 0
+    int      cluster;  // the nsplit CTAs of a row are one thread-block cluster: partials merged through distributed shared memory
     MvNext   next;     // n_mats > 0: weights to pull into L2 meanwhile (kernels.h mv_prefetch_next)
+    unsigned long long * trace;   // b200_ctx_trace slot of this launch (8 x u64 per CTA): [0] CTA start, [3] past the stream dependency, [4] first
+                                  // round's rows used, [5] rounds done, [6] done, [1] warps merged, [2] partial published / arrival counted
     FaDec    dec;
 };
 constexpr int FA_MAX_WARPS = 16;   // warps per CTA: 8 or 16 (launch parameter)
@@ -474,11 +477,13 @@ __device__ __forceinline__ void fa_dec_rotate(const FaP & p, float (&qraw)[E], f
     for (int e = 0; e < E; e++) { qraw[e] = qr[e]; knew[e] = __half2float(__float2half_rn(kr[e])); vnew[e] = __half2float(__float2half_rn(vnew[e])); }
 }
 
+#define FA_TRACE(i) do { if (p.trace && threadIdx.x == 0) atomicMax(p.trace + (size_t) ((blockIdx.y * gridDim.x + blockIdx.x) % 148) * 8 + (i), global_ns_c()); } while (0)   // CTAs beyond 148 share slots: the latest stamp wins
 template <int E, int FA_U, bool DEC = false>
 __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
     constexpr int D = 32 * E;
     const int FA_WARPS = blockDim.x >> 5;
-    pdl_prologue();
+    FA_TRACE(0);
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int64_t row = blockIdx.x;
     const int64_t iq1 = row % p.q.ne[1], iq2 = (row / p.q.ne[1]) % p.q.ne[2], iq3 = row / (p.q.ne[1] * p.q.ne[2]);
     const int64_t ik2 = iq2 / (p.q.ne[2] / p.k.ne[2]), ik3 = iq3 / (p.q.ne[3] / p.k.ne[3]);
@@ -487,6 +492,13 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
 
     // everything the first round needs is requested before anything is used: q, the mask values and the K / V rows are independent
     // loads (a masked position's rows are read anyway - they are valid cache memory - so that the K / V loads do not wait for the mask)
+    const __half * mp = p.md ? (const __half *) (p.md + iq1 * p.m.nb[1] + (iq2 % p.m.ne[2]) * p.m.nb[2] + (iq3 % p.m.ne[3]) * p.m.nb[3]) : nullptr;
+    const char * kb = p.kd + ik2 * p.k.nb[2] + ik3 * p.k.nb[3] + lane * E * 2;
+    const char * vb = p.vd + iv2 * p.v.nb[2] + iv3 * p.v.nb[3] + lane * E * 2;
+    const int64_t c0 = (int64_t) blockIdx.y * p.chunk, c1 = min(c0 + p.chunk, p.k.ne[1]);
+
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    FA_TRACE(3);
     float qraw[E], knew[E], vnew[E];
     int64_t slot = -1;
     if constexpr (DEC) {   // the projections of this lane's channels; rotated below, while the first round's K / V rows are on their way
@@ -502,11 +514,6 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
 #pragma unroll
         for (int e = 0; e < E; e++) qraw[e] = pq[e];
     }
-    const __half * mp = p.md ? (const __half *) (p.md + iq1 * p.m.nb[1] + (iq2 % p.m.ne[2]) * p.m.nb[2] + (iq3 % p.m.ne[3]) * p.m.nb[3]) : nullptr;
-    const char * kb = p.kd + ik2 * p.k.nb[2] + ik3 * p.k.nb[3] + lane * E * 2;
-    const char * vb = p.vd + iv2 * p.v.nb[2] + iv3 * p.v.nb[3] + lane * E * 2;
-    const int64_t c0 = (int64_t) blockIdx.y * p.chunk, c1 = min(c0 + p.chunk, p.k.ne[1]);
-
     if (p.next.n_mats > 0) mv_prefetch_next(p.next, (int) (blockIdx.y * gridDim.x + blockIdx.x) * FA_WARPS + warp, (int) (gridDim.x * gridDim.y) * FA_WARPS, lane);
     float M = -INFINITY, S = 0.0f, acc[E], qf[E];
 #pragma unroll
@@ -531,6 +538,7 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
 #pragma unroll
             for (int e = 0; e < E; e++) qf[e] = __half2float(__float2half_rn(qraw[e])) * p.scale;   // ggml-cpu converts q to the K type's vec_dot type: fp16
             q_ready = true;
+            if (p.trace) { asm volatile("" : "+f"(qf[0])); FA_TRACE(4); }
         }
 #pragma unroll
         for (int u = 0; u < FA_U; u++) {
@@ -587,18 +595,63 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
         }
     }
 
+    if (p.trace) { asm volatile("" : "+f"(acc[0])); FA_TRACE(5); }
     __shared__ float sh_acc[FA_MAX_WARPS][D];
     __shared__ float sh_m[FA_MAX_WARPS], sh_s[FA_MAX_WARPS];
 #pragma unroll
     for (int e = 0; e < E; e++) sh_acc[warp][lane * E + e] = acc[e];
     if (lane == 0) { sh_m[warp] = M; sh_s[warp] = S; }
     __syncthreads();
+    FA_TRACE(1);
     float Mx = -INFINITY;
     for (int w = 0; w < FA_WARPS; w++) Mx = fmaxf(Mx, sh_m[w]);
     float St = 0.0f;
     float f[FA_MAX_WARPS];
 #pragma unroll
     for (int w = 0; w < FA_MAX_WARPS; w++) { f[w] = w >= FA_WARPS || sh_m[w] == -INFINITY ? 0.0f : expf(sh_m[w] - Mx); St += w < FA_WARPS ? sh_s[w] * f[w] : 0.0f; }
+    // KV splits of a row as one cluster (nsplit <= 8): every CTA stores its (max, sum, accumulator) into the shared memory of the
+    // cluster's first CTA, one cluster barrier, and that CTA merges them in split order - no global round trips (partials, fence,
+    // atomic, reload: 4 - 5 us on the device timeline)
+    __shared__ float cl_acc[8][D];
+    __shared__ float cl_m[8], cl_s[8];
+    if (p.cluster) {
+        const uint32_t rank = blockIdx.y;   // cluster dims (1, nsplit, 1): the rank is the split index
+        for (int t = threadIdx.x; t < D; t += blockDim.x) {
+            float a = 0.0f;
+#pragma unroll
+            for (int w = 0; w < FA_MAX_WARPS; w++) a += w < FA_WARPS ? sh_acc[w][t] * f[w] : 0.0f;
+            uint32_t dst;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(dst) : "r"((uint32_t) __cvta_generic_to_shared(&cl_acc[rank][t])), "r"(0u));
+            asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dst), "f"(a) : "memory");
+        }
+        if (threadIdx.x == 0) {
+            uint32_t dm, ds;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(dm) : "r"((uint32_t) __cvta_generic_to_shared(&cl_m[rank])), "r"(0u));
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ds) : "r"((uint32_t) __cvta_generic_to_shared(&cl_s[rank])), "r"(0u));
+            asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dm), "f"(Mx) : "memory");
+            asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(ds), "f"(St) : "memory");
+        }
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+        FA_TRACE(2);
+        if (rank != 0) { FA_TRACE(6); return; }
+        float Mg = -INFINITY;
+        for (int s = 0; s < p.nsplit; s++) Mg = fmaxf(Mg, cl_m[s]);
+        float Sg = 0.0f;
+        for (int s = 0; s < p.nsplit; s++) Sg += cl_m[s] == -INFINITY ? 0.0f : cl_s[s] * expf(cl_m[s] - Mg);
+        float r = 1.0f;
+        if (p.sinks) {
+            const float sk = p.sinks[iq2];
+            if (sk > Mg) { r = expf(Mg - sk); Sg = Sg * r + 1.0f; } else { Sg += expf(sk - Mg); }
+        }
+        for (int t = threadIdx.x; t < D; t += blockDim.x) {
+            float a = 0.0f;
+            for (int s = 0; s < p.nsplit; s++) { if (cl_m[s] != -INFINITY) a += cl_acc[s][t] * expf(cl_m[s] - Mg); }
+            fa_dst_row(p, iq1, iq2, iq3)[t] = Sg == 0.0f ? 0.0f : a * r / Sg;
+        }
+        FA_TRACE(6);
+        return;
+    }
     for (int t = threadIdx.x; t < D; t += blockDim.x) {
         float a = 0.0f;
 #pragma unroll
@@ -614,28 +667,44 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
             fa_dst_row(p, iq1, iq2, iq3)[t] = Sf == 0.0f ? 0.0f : af / Sf;
         }
     }
-    if (p.nsplit == 1) return;
+    if (p.nsplit == 1) { FA_TRACE(6); return; }
     if (threadIdx.x == 0) {
         float * w = p.ws + (row * p.nsplit + blockIdx.y) * (D + 2);
         w[0] = Mx; w[1] = St;
     }
-    // the last CTA of this row to get here merges the splits (threadfence reduction: partials are published before the arrival)
+    // the last CTA of this row to get here merges the splits. Publication: the CTA's partials are ordered before the barrier, thread 0's
+    // fence is cumulative over what it has observed through the barrier, then it counts the arrival (the grid-sync pattern: one fence
+    // per CTA, not one per thread)
     __shared__ unsigned last;
-    __threadfence();
+    __shared__ float cm[64], cs[64];
     __syncthreads();
     if (threadIdx.x == 0) {
+        __threadfence();
         const unsigned n = atomicAdd(p.cnt + row, 1u);
         last = n == (unsigned) p.nsplit - 1;
-        if (last) p.cnt[row] = 0;
+        if (last) { p.cnt[row] = 0; __threadfence(); }   // acquire: the other CTAs' partials, for the whole CTA through the barrier below
     }
     __syncthreads();
-    if (!last) return;
-    __threadfence();
+    FA_TRACE(2);
+    if (!last) { FA_TRACE(6); return; }
     const float * w = p.ws + row * p.nsplit * (D + 2);
+    // every load of the merge is issued before any is used: maxima and sums by one thread per split, and the first eight splits'
+    // accumulators of this thread's channel - one L2 round trip
+    float v0[8];
+    {
+        const int t = threadIdx.x < D ? threadIdx.x : 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) v0[j] = j < p.nsplit ? __ldcg(w + j * (D + 2) + 2 + t) : 0.0f;
+    }
+    if ((int) threadIdx.x < p.nsplit) {
+        cm[threadIdx.x] = __ldcg(w + threadIdx.x * (D + 2));
+        cs[threadIdx.x] = __ldcg(w + threadIdx.x * (D + 2) + 1);
+    }
+    __syncthreads();
     float Mg = -INFINITY;
-    for (int s = 0; s < p.nsplit; s++) Mg = fmaxf(Mg, __ldcg(w + s * (D + 2)));
+    for (int s = 0; s < p.nsplit; s++) Mg = fmaxf(Mg, cm[s]);
     float Sg = 0.0f;
-    for (int s = 0; s < p.nsplit; s++) { const float m = __ldcg(w + s * (D + 2)); Sg += m == -INFINITY ? 0.0f : __ldcg(w + s * (D + 2) + 1) * expf(m - Mg); }
+    for (int s = 0; s < p.nsplit; s++) Sg += cm[s] == -INFINITY ? 0.0f : cs[s] * expf(cm[s] - Mg);
     float r = 1.0f;
     if (p.sinks) {
         const float sk = p.sinks[iq2];
@@ -643,9 +712,18 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
     }
     for (int t = threadIdx.x; t < D; t += blockDim.x) {
         float a = 0.0f;
-        for (int s = 0; s < p.nsplit; s++) { const float m = __ldcg(w + s * (D + 2)); if (m != -INFINITY) a += __ldcg(w + s * (D + 2) + 2 + t) * expf(m - Mg); }
+        for (int s0 = 0; s0 < p.nsplit; s0 += 8) {
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[j] = s0 == 0 && t == (int) threadIdx.x ? v0[j] : (s0 + j < p.nsplit ? __ldcg(w + (s0 + j) * (D + 2) + 2 + t) : 0.0f);
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                if (s0 + j < p.nsplit && cm[s0 + j] != -INFINITY) a += v[j] * expf(cm[s0 + j] - Mg);
+            }
+        }
         fa_dst_row(p, iq1, iq2, iq3)[t] = Sg == 0.0f ? 0.0f : a * r / Sg;
     }
+    FA_TRACE(6);
 }
 
 // Wide batches (prompt processing): a CTA takes NQ consecutive query rows of one head, so a K / V row is loaded once for all of them
@@ -971,6 +1049,20 @@ bool nonneg(const b200_tensor * t) { return t->ne[0] >= 0 && t->ne[1] >= 0 && t-
     CU(cudaSetDevice((ctx)->device));                                                          \
     if (b200_status fst_ = b200_split_flush(ctx)) return fst_
 
+// the decode attention kernel: programmatic dependent launch, and - when the KV splits of a row merge through distributed shared
+// memory - the nsplit CTAs of a row as one cluster
+template <typename K>
+static cudaError_t fa_launch(const b200_ctx * ctx, K kernel, dim3 grid, dim3 block, const FaP & p) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (ctx->pdl) { attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization; attr[na].val.programmaticStreamSerializationAllowed = 1; na++; }
+    if (p.cluster) { attr[na].id = cudaLaunchAttributeClusterDimension; attr[na].val.clusterDim.x = 1; attr[na].val.clusterDim.y = (unsigned) p.nsplit; attr[na].val.clusterDim.z = 1; na++; }
+    cfg.attrs = attr; cfg.numAttrs = na;
+    return cudaLaunchKernelEx(&cfg, kernel, p);
+}
+
 } // namespace
 
 extern "C" {
@@ -1248,19 +1340,23 @@ static b200_status fa_run(b200_ctx * ctx, const b200_tensor * q, const b200_tens
     }
     static const int max_split = [] { const char * e = getenv("GGML_B200_FA_MAX_SPLIT"); return e ? atoi(e) : 64; }();   // experiments
     if (nsplit > max_split) nsplit = std::max(1, max_split);
+    static const bool cluster_on = [] { const char * e = getenv("GGML_B200_FA_CLUSTER"); return !(e && atoi(e) == 0); }();
+    if (cluster_on && nsplit > 8) nsplit = 8;   // the splits of a row form one thread-block cluster (portable size: 8)
     p.chunk  = nsplit == 1 ? std::max<int64_t>(n_kv, 1) : ((n_kv + nsplit - 1) / nsplit + round - 1) / round * round;
     if (nsplit > 1) nsplit = (int) ((n_kv + p.chunk - 1) / p.chunk);   // no empty splits
-    p.nsplit = nsplit;
-    p.ws     = nullptr;
-    p.cnt    = nullptr;
+    p.nsplit  = nsplit;
+    p.cluster = cluster_on && nsplit > 1 && nsplit <= 8;
+    p.ws      = nullptr;
+    p.cnt     = nullptr;
     OPS_PROLOGUE(ctx);
-    if (nsplit > 1) {
+    if (nsplit > 1 && !p.cluster) {
         const void * before = ctx->fa_ws;
         if (b200_status st = b200_ensure(ctx, &ctx->fa_ws, &ctx->fa_ws_size, FA_CNT_BYTES + (size_t) rows * nsplit * (D + 2) * sizeof(float))) return st;
         if (ctx->fa_ws != before) CU(cudaMemsetAsync(ctx->fa_ws, 0, FA_CNT_BYTES, ctx->stream));   // (re)allocated: the counters start at zero
         p.cnt = (unsigned *) ctx->fa_ws;
         p.ws  = (float *) ((char *) ctx->fa_ws + FA_CNT_BYTES);
     }
+    p.trace = nullptr;
     memset(&p.dec, 0, sizeof(p.dec));
     if (dec) p.dec = *dec;
     memset(&p.next, 0, sizeof(p.next));
@@ -1278,9 +1374,9 @@ static b200_status fa_run(b200_ctx * ctx, const b200_tensor * q, const b200_tens
     }
     if (dec) {   // one token: the decode kernel with the ROPEs and the cache rows folded in (8 positions per warp in flight)
         const dim3 g((unsigned) rows, (unsigned) nsplit), b(FA_WARPS * 32);
-        if (D == 64)       CU(b200_launch(ctx, fa_kernel<2, 8, true>, g, b, 0, p));
-        else if (D == 128) CU(b200_launch(ctx, fa_kernel<4, 8, true>, g, b, 0, p));
-        else               CU(b200_launch(ctx, fa_kernel<8, 8, true>, g, b, 0, p));
+        if (D == 64)       CU(fa_launch(ctx, fa_kernel<2, 8, true>, g, b, p));
+        else if (D == 128) CU(fa_launch(ctx, fa_kernel<4, 8, true>, g, b, p));
+        else               CU(fa_launch(ctx, fa_kernel<8, 8, true>, g, b, p));
         ctx->launches++;
         return B200_OK;
     }
@@ -1309,10 +1405,11 @@ static b200_status fa_run(b200_ctx * ctx, const b200_tensor * q, const b200_tens
         ctx->launches++;
         return B200_OK;
     }
+    if (ctx->trace && ctx->sm_count >= 148) p.trace = ctx->trace + (size_t) (ctx->launches % ctx->trace_slots) * ctx->sm_count * 8;
     const dim3 grid((unsigned) rows, (unsigned) nsplit), block(FA_WARPS * 32);
-    if (D == 64)       CU(U == 4 ? b200_launch(ctx, fa_kernel<2, 4>, grid, block, 0, p) : U == 8 ? b200_launch(ctx, fa_kernel<2, 8>, grid, block, 0, p) : b200_launch(ctx, fa_kernel<2, 16>, grid, block, 0, p));
-    else if (D == 128) CU(U == 4 ? b200_launch(ctx, fa_kernel<4, 4>, grid, block, 0, p) : U == 8 ? b200_launch(ctx, fa_kernel<4, 8>, grid, block, 0, p) : b200_launch(ctx, fa_kernel<4, 16>, grid, block, 0, p));
-    else               CU(b200_launch(ctx, fa_kernel<8, 8>, grid, block, 0, p));
+    if (D == 64)       CU(U == 4 ? fa_launch(ctx, fa_kernel<2, 4>, grid, block, p) : U == 8 ? fa_launch(ctx, fa_kernel<2, 8>, grid, block, p) : fa_launch(ctx, fa_kernel<2, 16>, grid, block, p));
+    else if (D == 128) CU(U == 4 ? fa_launch(ctx, fa_kernel<4, 4>, grid, block, p) : U == 8 ? fa_launch(ctx, fa_kernel<4, 8>, grid, block, p) : fa_launch(ctx, fa_kernel<4, 16>, grid, block, p));
+    else               CU(fa_launch(ctx, fa_kernel<8, 8>, grid, block, p));
     ctx->launches++;
     return B200_OK;
 }
