@@ -372,6 +372,15 @@ typedef struct {
 B200_API int          b200_rms_norm_supported(const b200_tensor * x, const b200_tensor * dst);
 B200_API b200_status  b200_rms_norm(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * dst, float eps);
 
+/* FLASH_ATTN_EXT of one token right behind the layer's own KV-cache write. written_idx (I64 / I32, one element): the caller guarantees
+ * that the only rows of k / v which launches still in flight on the context's stream may write are rows written_idx[0] - what a
+ * decode graph does (SET_ROWS(k), SET_ROWS(v) by the token's slot, then the attention; the previous token's launches completed
+ * long ago). The kernel then requests the other K / V rows of its first round before the stream dependency resolves (it is resident
+ * while the q/k/v launch still runs) and reads row written_idx[0] again afterwards. Same results as b200_flash_attn_ext. */
+B200_API b200_status  b200_flash_attn_ext_decode(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
+                                                 const b200_tensor * mask, const b200_tensor * sinks, const b200_tensor * dst, float scale,
+                                                 float max_bias, float logit_softcap, const b200_tensor * written_idx);
+
 /* RMS_NORM followed by the MUL with the norm weight (build_norm, src/llama-graph.cpp; ggml-cuda fuses the same pair:
  * ggml_cuda_op_rms_norm_fused, ggml-cuda.cu:3360-3380): dst = (x * scale) * w, both products rounded as the two nodes would;
  * w F32 with w->ne[0] == x->ne[0], its other dimensions broadcast */

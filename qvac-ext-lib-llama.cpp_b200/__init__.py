@@ -38,7 +38,7 @@ EXPORTS = [
     "b200_mul_mat_fused_supported", "b200_mul_mat_fused", "b200_mul_mat_id_fused_supported", "b200_mul_mat_id_fused",
     "b200_glu", "b200_add", "b200_mul", "b200_add_id",
     "b200_mul_mat_noalloc", "b200_mul_mat_noalloc_max_units",
-    "b200_rms_norm_supported", "b200_rms_norm", "b200_rms_norm_mul_supported", "b200_rms_norm_mul", "b200_attn_prep_supported", "b200_attn_prep", "b200_attn_decode_supported", "b200_attn_decode", "b200_qkv_rope",
+    "b200_rms_norm_supported", "b200_rms_norm", "b200_rms_norm_mul_supported", "b200_rms_norm_mul", "b200_attn_prep_supported", "b200_attn_prep", "b200_attn_decode_supported", "b200_attn_decode", "b200_qkv_rope", "b200_flash_attn_ext_decode",
     "b200_mul_mat_shared_src1_norm", "b200_mul_mat_fused_norm", "b200_get_rows_supported", "b200_get_rows", "b200_rope_supported", "b200_rope",
     "b200_set_rows_supported", "b200_set_rows", "b200_cpy_supported", "b200_cpy", "b200_flash_attn_ext_supported", "b200_flash_attn_ext",
 ]
@@ -214,6 +214,7 @@ def lib() -> C.CDLL:
         L.b200_cpy.argtypes = [vp, tp, tp]
         L.b200_flash_attn_ext_supported.argtypes = [tp, tp, tp, tp, tp, tp]
         L.b200_flash_attn_ext.argtypes = [vp, tp, tp, tp, tp, tp, tp, C.c_float, C.c_float, C.c_float]
+        L.b200_flash_attn_ext_decode.argtypes = [vp, tp, tp, tp, tp, tp, tp, C.c_float, C.c_float, C.c_float, tp]
         L.b200_mul_mat_supported.argtypes = [C.POINTER(MulMatDesc)]
         L.b200_mul_mat.argtypes = [vp, C.POINTER(MulMatDesc), vp, vp, vp]
         L.b200_mul_mat_noalloc.argtypes = [vp, C.POINTER(MulMatDesc), vp, vp, vp]
@@ -619,11 +620,16 @@ class Context:
         check(lib().b200_cpy(self.h, Tensor.of(src), Tensor.of(dst)), "b200_cpy")
         return dst
 
-    def flash_attn_ext(self, q, k, v, mask=None, sinks=None, scale=1.0, max_bias=0.0, logit_softcap=0.0):
+    def flash_attn_ext(self, q, k, v, mask=None, sinks=None, scale=1.0, max_bias=0.0, logit_softcap=0.0, written_idx=None):
         """GGML_OP_FLASH_ATTN_EXT: q float32 [n_batch, n_head, n_q, D]; k, v float16 [n_batch, n_head_kv, n_kv, D]; mask float16
         [1 | n_batch, 1 | n_head, >= n_q, n_kv]; returns float32 [n_batch, n_q, n_head, D]"""
         nb_, nh, nq, D = q.shape
         out = self.torch.empty((nb_, nq, nh, D), dtype=self.torch.float32, device=q.device)
+        if written_idx is not None:   # one token behind its own KV-cache write: b200_flash_attn_ext_decode
+            check(lib().b200_flash_attn_ext_decode(self.h, Tensor.of(q), Tensor.of(k), Tensor.of(v), None if mask is None else Tensor.of(mask),
+                                                   None if sinks is None else Tensor.of(sinks), Tensor.of(out), scale, max_bias, logit_softcap,
+                                                   Tensor.of(written_idx)), "b200_flash_attn_ext_decode")
+            return out
         check(lib().b200_flash_attn_ext(self.h, Tensor.of(q), Tensor.of(k), Tensor.of(v), None if mask is None else Tensor.of(mask),
                                         None if sinks is None else Tensor.of(sinks), Tensor.of(out), scale, max_bias, logit_softcap), "b200_flash_attn_ext")
         return out

@@ -87,6 +87,10 @@ struct be_ctx {
     bool       last_hash_valid = false;
     uint64_t   graph_clock = 0;
     uint64_t   graph_replays = 0, graph_captures = 0;
+    // try_fuse_attn_block -> the FLASH_ATTN_EXT right behind it: the only KV-cache rows in flight are the token's slot (b200_flash_attn_ext_decode)
+    int        kv_hint_node = -1;
+    const void * kv_hint_k = nullptr, * kv_hint_v = nullptr;
+    const ggml_tensor * kv_hint_idx = nullptr;
     void *     blk_scratch = nullptr;              // try_fuse_attn_block: q / k / v projections of the layer in flight
     size_t     blk_scratch_size = 0;
     std::vector<char> done;                        // run_nodes: nodes already executed ahead of their position (hoisted into a fused launch)
@@ -748,7 +752,7 @@ bool is_f3_op(ggml_op op) {
     return op == GGML_OP_RMS_NORM || op == GGML_OP_GET_ROWS || op == GGML_OP_ROPE || op == GGML_OP_SET_ROWS || op == GGML_OP_CPY || op == GGML_OP_CONT ||
            op == GGML_OP_DUP || op == GGML_OP_FLASH_ATTN_EXT;
 }
-void run_f3(be_ctx * c, ggml_tensor * op) {
+void run_f3(be_ctx * c, ggml_tensor * op, const ggml_tensor * hint_idx = nullptr) {
     const b200_tensor d = as_b200(op);
     b200_tensor s[5];
     for (int i = 0; i < 5; i++) if (op->src[i]) s[i] = as_b200(op->src[i]);
@@ -773,6 +777,12 @@ void run_f3(be_ctx * c, ggml_tensor * op) {
             CHECK_RUN(c, b200_cpy(c->ctx, &s[0], &d));
             break;
         case GGML_OP_FLASH_ATTN_EXT:
+            if (hint_idx) {
+                const b200_tensor hi = as_b200(hint_idx);
+                CHECK_RUN(c, b200_flash_attn_ext_decode(c->ctx, &s[0], &s[1], &s[2], op->src[3] ? &s[3] : nullptr, op->src[4] ? &s[4] : nullptr, &d,
+                                                        ggml_get_op_params_f32(op, 0), ggml_get_op_params_f32(op, 1), ggml_get_op_params_f32(op, 2), &hi));
+                break;
+            }
             CHECK_RUN(c, b200_flash_attn_ext(c->ctx, &s[0], &s[1], &s[2], op->src[3] ? &s[3] : nullptr, op->src[4] ? &s[4] : nullptr, &d,
                                              ggml_get_op_params_f32(op, 0), ggml_get_op_params_f32(op, 1), ggml_get_op_params_f32(op, 2)));
             break;
@@ -971,6 +981,10 @@ bool try_fuse_attn_block(be_ctx * c, ggml_cgraph * cgraph, int i, const norm_src
         CHECK_RUN(c, b200_qkv_rope(c->ctx, d, w, (const float *) (nf ? nf->x0->data : mq->src[1]->data), nf ? &nf->n : nullptr, o, &q, &qd, &k, &kd, &pos,
                                    rq->src[2] ? &ff : nullptr, &rp, &ki, &kc, &v, &vi, &vc));
         for (int k2 = 1; k2 < 7; k2++) c->done[j[k2]] = 1;
+        if (N == 1 && sk->src[1] == sv->src[1]) {   // one token, one slot index for both caches: the attention directly behind may read the rest early
+            c->kv_hint_node = next_live(c, cgraph, j[6] + 1);
+            c->kv_hint_k = sk->data; c->kv_hint_v = sv->data; c->kv_hint_idx = sk->src[1];
+        }
         return true;
     }
     if (nf) CHECK_RUN(c, b200_mul_mat_shared_src1_norm(c->ctx, 3, d, w, (const float *) nf->x0->data, &nf->n, o));
@@ -989,6 +1003,7 @@ bool try_fuse_attn_block(be_ctx * c, ggml_cgraph * cgraph, int i, const norm_src
 
 ggml_status run_nodes(be_ctx * c, ggml_cgraph * cgraph) {
     c->done.assign((size_t) cgraph->n_nodes, 0);
+    c->kv_hint_node = -1;
     for (int i = 0; i < cgraph->n_nodes; i++) {
         ggml_tensor * node = cgraph->nodes[i];
         if (is_noop(node) || c->done[i]) continue;  // as ggml-cuda.cu:3333-3335; done: ran ahead of its position in a fused launch
@@ -1072,7 +1087,10 @@ ggml_status run_nodes(be_ctx * c, ggml_cgraph * cgraph) {
             } else if (node->op == GGML_OP_ROPE && try_fuse_attn_prep(c, cgraph, i)) {
                 continue;
             }
-            run_f3(c, node);
+            const ggml_tensor * hint = nullptr;
+            if (node->op == GGML_OP_FLASH_ATTN_EXT && c->kv_hint_node == i && node->src[1]->data == c->kv_hint_k && node->src[2]->data == c->kv_hint_v &&
+                node->src[0]->ne[1] == 1) hint = c->kv_hint_idx;
+            run_f3(c, node, hint);
         } else {
             GGML_LOG_ERROR("ggml-b200: op %s is not implemented by this backend (%s)\n", ggml_op_name(node->op), node->name);
             return GGML_STATUS_FAILED;

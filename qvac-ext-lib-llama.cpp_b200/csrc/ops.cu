@@ -382,6 +382,8 @@ struct FaP {
     int64_t  chunk;
     float *  ws;       // partials of the KV splits: [row][split][2 + D] = running maximum, sum, accumulator
     unsigned * cnt;    // arrivals per row; the CTA that completes a row merges its splits and puts the counter back to 0
+    const char * early_idx;   // != nullptr: the only rows of k / v that launches still in flight on the stream may write are rows
+    int      early_i64;       // early_idx[0] (the token's cache slot): every other row may be read before the stream dependency resolves
     int      cluster;  // the nsplit CTAs of a row are one thread-block cluster: partials merged through distributed shared memory
     MvNext   next;     // n_mats > 0: weights to pull into L2 meanwhile (kernels.h mv_prefetch_next)
     unsigned long long * trace;   // b200_ctx_trace slot of this launch (8 x u64 per CTA): [0] CTA start, [3] past the stream dependency, [4] first
@@ -497,10 +499,28 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
     const char * vb = p.vd + iv2 * p.v.nb[2] + iv3 * p.v.nb[3] + lane * E * 2;
     const int64_t c0 = (int64_t) blockIdx.y * p.chunk, c1 = min(c0 + p.chunk, p.k.ne[1]);
 
+    // Decode behind the layer's own KV-cache write (early_idx): the K / V rows of the first round are requested BEFORE the stream dependency
+    // resolves - this CTA is resident while the q/k/v launch is still running, and the only row that launch writes is the token's own
+    // slot, which is read again afterwards. The device timeline showed these rows arriving 1.7 us after q otherwise: they come from HBM
+    // at the moment the next mat-vec launch starts streaming its weights.
+    __half mh[FA_U];
+    HPack<E> kp[FA_U], vp[FA_U];
+    const int64_t base0 = c0 + warp * FA_U;
+    const bool early = !DEC && p.early_idx != nullptr && base0 < c1;
+    if (early) {
+#pragma unroll
+        for (int u = 0; u < FA_U; u++) {
+            if (base0 + u < c1) {
+                kp[u] = load_pack<E>(kb + (base0 + u) * p.k.nb[1]);
+                vp[u] = load_pack<E>(vb + (base0 + u) * p.v.nb[1]);
+            }
+        }
+    }
     asm volatile("griddepcontrol.wait;" ::: "memory");
     FA_TRACE(3);
     float qraw[E], knew[E], vnew[E];
     int64_t slot = -1;
+    if (early) slot = load_idx(p.early_idx, p.early_i64);
     if constexpr (DEC) {   // the projections of this lane's channels; rotated below, while the first round's K / V rows are on their way
 #pragma unroll
         for (int e = 0; e < E; e++) {
@@ -523,14 +543,15 @@ __global__ void __launch_bounds__(FA_MAX_WARPS * 32, 1) fa_kernel(const FaP p) {
 
     for (int64_t base = c0 + warp * FA_U; base < c1; base += FA_WARPS * FA_U) {
         float s[FA_U];
-        __half mh[FA_U];
-        HPack<E> kp[FA_U], vp[FA_U];
+        const bool have = early && base == base0;   // this round's rows were requested ahead of the dependency
 #pragma unroll
         for (int u = 0; u < FA_U; u++) {
             if (base + u < c1) {   // warp-uniform
                 if (mp) mh[u] = mp[base + u];
-                kp[u] = load_pack<E>(kb + (base + u) * p.k.nb[1]);
-                vp[u] = load_pack<E>(vb + (base + u) * p.v.nb[1]);
+                if (!have || base + u == slot) {
+                    kp[u] = load_pack<E>(kb + (base + u) * p.k.nb[1]);
+                    vp[u] = load_pack<E>(vb + (base + u) * p.v.nb[1]);
+                }
             }
         }
         if (!q_ready) {
@@ -1305,7 +1326,8 @@ int b200_flash_attn_ext_supported(const b200_tensor * q, const b200_tensor * k, 
 constexpr size_t FA_CNT_BYTES = 4096;   // arrival counters at the head of the split workspace (splits only run with < 2 x SM-count rows)
 
 static b200_status fa_run(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
-                          const b200_tensor * sinks, const b200_tensor * dst, float scale, float max_bias, float logit_softcap, const FaDec * dec) {
+                          const b200_tensor * sinks, const b200_tensor * dst, float scale, float max_bias, float logit_softcap, const FaDec * dec,
+                          const b200_tensor * written_idx = nullptr) {
     if (!b200_flash_attn_ext_supported(q, k, v, mask, sinks, dst))
         return fail(B200_ERR_UNSUPPORTED, "FLASH_ATTN_EXT: F32 q, F16 k / v of head size 64 / 128 / 256, F16 mask");
     if (!ctx) return fail(B200_ERR_ARG, "null context");
@@ -1357,6 +1379,14 @@ static b200_status fa_run(b200_ctx * ctx, const b200_tensor * q, const b200_tens
         p.ws  = (float *) ((char *) ctx->fa_ws + FA_CNT_BYTES);
     }
     p.trace = nullptr;
+    // opt-in (GGML_B200_FA_EARLY=1): measured no faster at 512 cached positions and 10 % slower at 4096 - memory operations issued ahead of
+    // griddepcontrol.wait delay the wait itself (device timeline: the dependency resolves 0.7 us after the previous kernel without
+    // them, 0.7 - 3.5 us with them)
+    static const bool early_on = [] { const char * e = getenv("GGML_B200_FA_EARLY"); return e && atoi(e) != 0; }();
+    const bool early = early_on && written_idx && written_idx->data && written_idx->ne[0] == 1 && q->ne[1] == 1 &&
+                       (written_idx->type == B200_TYPE_I64 || written_idx->type == B200_TYPE_I32);
+    p.early_idx = early ? (const char *) written_idx->data : nullptr;
+    p.early_i64 = early && written_idx->type == B200_TYPE_I64;
     memset(&p.dec, 0, sizeof(p.dec));
     if (dec) p.dec = *dec;
     memset(&p.next, 0, sizeof(p.next));
@@ -1417,6 +1447,12 @@ static b200_status fa_run(b200_ctx * ctx, const b200_tensor * q, const b200_tens
 b200_status b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
                                 const b200_tensor * sinks, const b200_tensor * dst, float scale, float max_bias, float logit_softcap) {
     return fa_run(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap, nullptr);
+}
+
+b200_status b200_flash_attn_ext_decode(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
+                                       const b200_tensor * sinks, const b200_tensor * dst, float scale, float max_bias, float logit_softcap,
+                                       const b200_tensor * written_idx) {
+    return fa_run(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap, nullptr, written_idx);
 }
 
 // One token: ROPE(q), ROPE(k), SET_ROWS(k cache), SET_ROWS(v cache) and FLASH_ATTN_EXT of a layer as ONE launch. q / k / v are the

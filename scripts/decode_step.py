@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--prefetch-kb", type=int, default=64)
     ap.add_argument("--one-launch-attn", action="store_true", help="b200_attn_decode instead of attn_prep + flash_attn_ext (measured slower)")
+    ap.add_argument("--no-early-kv", action="store_true", help="plain b200_flash_attn_ext instead of b200_flash_attn_ext_decode")
     ap.add_argument("--no-qkv-rope", action="store_true", help="q/k/v and attn_prep as two launches instead of b200_qkv_rope's one")
     ap.add_argument("--out", default="")
     a = ap.parse_args()
@@ -82,7 +83,7 @@ def main():
                     if folded:
                         kview = l["kc"][:a.n_kv].view(1, a.n_kv, NKV, D).permute(0, 2, 1, 3)
                         vview = l["vc"][:a.n_kv].view(1, a.n_kv, NKV, D).permute(0, 2, 1, 3)
-                        att = ctx.flash_attn_ext(q4.permute(0, 2, 1, 3), kview, vview, mask, None, scale).reshape(1, E) if skip != "fa" else q4.reshape(1, E)
+                        att = ctx.flash_attn_ext(q4.permute(0, 2, 1, 3), kview, vview, mask, None, scale, written_idx=None if a.no_early_kv else idx).reshape(1, E) if skip != "fa" else q4.reshape(1, E)
                     elif skip == "attn":
                         att = q4.reshape(1, E)
                     elif skip not in ("prep", "fa") and a.one_launch_attn:   # ROPE + KV store + attention: one launch

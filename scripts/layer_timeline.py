@@ -59,7 +59,7 @@ def main():
                                      freq_base=500000.0, n_ctx_orig=8192)
                 kview = l["kc"][:a.n_kv].view(1, a.n_kv, NKV, D).permute(0, 2, 1, 3)
                 vview = l["vc"][:a.n_kv].view(1, a.n_kv, NKV, D).permute(0, 2, 1, 3)
-                att = ctx.flash_attn_ext(q4.permute(0, 2, 1, 3), kview, vview, mask, None, scale).reshape(1, E)
+                att = ctx.flash_attn_ext(q4.permute(0, 2, 1, 3), kview, vview, mask, None, scale, written_idx=idx).reshape(1, E)
                 x2 = ctx.mul_mat_fused(t, l["wo"], None, att, up_bias=x.reshape(-1))
                 h = ctx.mul_mat_fused(t, l["wu"], l["wg"], x2, glu_op=pkg.GLU_SWIGLU, norm_w=l["fn"], norm_eps=1e-5)
                 x = ctx.mul_mat_fused(t, l["wd"], None, h, up_bias=x2.reshape(-1))

@@ -164,6 +164,12 @@ def test_attn_decode_is_prep_then_flash_attn(ctx, mode, D, nh, nkv, n_kv, slot):
     kview = kc1[:n_kv].view(1, n_kv, nkv, D).permute(0, 2, 1, 3)
     vview = vc1[:n_kv].view(1, n_kv, nkv, D).permute(0, 2, 1, 3)
     ref = ctx.flash_attn_ext(qo_ref.permute(0, 2, 1, 3), kview, vview, mask, None, scale)
+    # the attention behind the cache write, told which row is in flight (with GGML_B200_FA_EARLY=1 it reads the rest ahead of the stream dependency)
+    kc3, vc3 = kc.clone(), vc.clone()
+    qo3, _ = ctx.attn_prep(q, k, pos, kc3, idx, v, vc3, idx, D, mode, **kw)
+    early = ctx.flash_attn_ext(qo3.permute(0, 2, 1, 3), kc3[:n_kv].view(1, n_kv, nkv, D).permute(0, 2, 1, 3), vc3[:n_kv].view(1, n_kv, nkv, D).permute(0, 2, 1, 3),
+                               mask, None, scale, written_idx=idx)
+    assert torch.equal(early, ref)
     got, qo, ko = ctx.attn_decode(q, k, pos, kc2, idx, v, vc2, idx, n_kv, mask, D, mode, scale=scale, **kw)
     assert torch.equal(qo, qo_ref) and torch.equal(ko, ko_ref)
     assert torch.equal(kc2, kc1) and torch.equal(vc2, vc1)
