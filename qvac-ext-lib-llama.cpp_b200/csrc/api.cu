@@ -681,7 +681,7 @@ static b200_status mv_fast_run(b200_ctx * ctx, int type, int64_t K, int n_ops, c
                 // MvNorm: the row's RMS_NORM (+ MUL) in the K1 prologue - a GLU pair on the EPI kernel, or a plain launch on the lean kernel
                 const bool glu = ep && ep->glu >= 0, bias_only = ep && ep->glu < 0, lean_run = !bias_only && lean && mv_lean_takes(type, 1, p, 1);
                 const int  nq  = lean_run ? std::min(MV_MAX_CONS, std::max(cfg.nw, U)) : cfg.nw;
-                if ((glu || lean_run) && U <= 4 * nq) { p.norm = ctx->norm; ctx->norm_used = true; }
+                if ((glu || lean_run) && U <= (lean_run ? 2 : 4) * nq) { p.norm = ctx->norm; ctx->norm_used = true; }   // units a warp holds: mmvq.cu NB
             }
             if (ctx->rope.on && x && ncols == 1 && n_ops == 3 && p.n_mats == 3 && !ep && !(p.rpg & 1) && p.split.n_ranks <= 1 && lean &&
                 mv_lean_takes(type, 1, p, 1)) {

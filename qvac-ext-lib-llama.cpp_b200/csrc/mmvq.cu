@@ -379,9 +379,10 @@ __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wa
 // this warp's share of the norm weights (they do not depend on the previous kernel: the lean kernel requests them before its
 // griddepcontrol.wait - measured on the device timeline, the norm prologue took 2.2 - 3.2 us against 1.0 us without a norm, the
 // difference being these loads queueing behind the weight stream)
-__device__ __forceinline__ void norm_load_w(float (&wv)[4][8], const MvNorm & nm, int t0, int stride, int n_units, int lane) {
+template <int NB>
+__device__ __forceinline__ void norm_load_w(float (&wv)[NB][8], const MvNorm & nm, int t0, int stride, int n_units, int lane) {
 #pragma unroll
-    for (int b = 0; b < 4; b++) {
+    for (int b = 0; b < NB; b++) {
         const int t = t0 + b * stride;
         if (t < n_units && nm.w) {
             const float4 e = __ldg((const float4 *) nm.w + t * 64 + lane * 2), f = __ldg((const float4 *) nm.w + t * 64 + lane * 2 + 1);
@@ -389,12 +390,12 @@ __device__ __forceinline__ void norm_load_w(float (&wv)[4][8], const MvNorm & nm
         }
     }
 }
-template <bool PRE = false>
-__device__ __forceinline__ void norm_units(float (&v)[4][8], const MvNorm & nm, int t0, int stride, int n_units, int lane, float * part, int n_threads,
-                                           float (&wv)[4][8]) {
-    if (!PRE) norm_load_w(wv, nm, t0, stride, n_units, lane);   // requested before the row's values are waited for
+template <bool PRE, int NB>
+__device__ __forceinline__ void norm_units(float (&v)[NB][8], const MvNorm & nm, int t0, int stride, int n_units, int lane, float * part, int n_threads,
+                                           float (&wv)[NB][8]) {
+    if (!PRE) norm_load_w<NB>(wv, nm, t0, stride, n_units, lane);   // requested before the row's values are waited for
 #pragma unroll
-    for (int b = 0; b < 4; b++) {
+    for (int b = 0; b < NB; b++) {
         const int t = t0 + b * stride;
         if (t < n_units) {
             const float sq = unit_sumsq(v[b]);
@@ -404,7 +405,7 @@ __device__ __forceinline__ void norm_units(float (&v)[4][8], const MvNorm & nm, 
     asm volatile("bar.sync 3, %0;" ::"r"(n_threads) : "memory");
     const float scale = rms_scale(part, n_units, nm.eps);
 #pragma unroll
-    for (int b = 0; b < 4; b++) {
+    for (int b = 0; b < NB; b++) {
         if (t0 + b * stride < n_units) {
 #pragma unroll
             for (int i = 0; i < 8; i++) { v[b][i] = v[b][i] * scale; if (nm.w) v[b][i] *= wv[b][i]; }
@@ -604,7 +605,7 @@ mv_fast_kernel(const __grid_constant__ MvParams p) {
                 asm volatile("" : "+f"(v[0][0]), "+f"(v[0][7]));
                 MV_TRACE(7);
             }
-            if constexpr (EPI) { if (norm_on) { float wv[4][8]; norm_units<false>(v, p.norm, t0, NWC, n_tasks, lane, (float *) (smem + 64), NWC * 32, wv); } }
+            if constexpr (EPI) { if (norm_on) { float wv[4][8]; norm_units<false, 4>(v, p.norm, t0, NWC, n_tasks, lane, (float *) (smem + 64), NWC * 32, wv); } }
 #pragma unroll
             for (int b = 0; b < 4; b++) {
                 const int t = t0 + b * NWC;
@@ -991,8 +992,11 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     int cnt = 0;
     if (w < NWC && g_end - g_begin > w) cnt = (g_end - g_begin - w + NWC - 1) / NWC;
 
-    float nwv[NORM ? 4 : 1][8];
-    if constexpr (NORM) norm_load_w(nwv, p.norm, qw, NQ, NC * U, lane);   // ahead of the stream dependency: weights never depend on it
+    // units a quantizing warp holds at a time: a NORM launch keeps the norm weights of its units in registers as well, and two units
+    // (rows up to 2 x 16 x 256 = 8192 elements) keep that free of spills - the launcher sends longer rows to the stand-alone norm
+    constexpr int NB = NORM ? 2 : 4;
+    float nwv[NORM ? NB : 1][8];
+    if constexpr (NORM) norm_load_w<NB>(nwv, p.norm, qw, NQ, NC * U, lane);   // ahead of the stream dependency: weights never depend on it
     griddep_wait();
     if (w == 0) MV_TRACE(3);
     // row split, flagged-payload exchange (kernels.h ll_store / ll_receive): this launch's epoch is final once the stream dependency is
@@ -1002,10 +1006,10 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
     if (p.fuse_quant) {
         constexpr int n_tasks_per_col = 0; (void) n_tasks_per_col;
         const int n_tasks = NC * U;   // task t = (column t / U, unit t % U); the records of column c start at c * U
-        for (int t0 = qw; t0 < n_tasks || (NORM && t0 == qw); t0 += 4 * NQ) {   // NORM: n_tasks <= 4 * NQ, every warp takes part once
-            float v[4][8];
+        for (int t0 = qw; t0 < n_tasks || (NORM && t0 == qw); t0 += NB * NQ) {   // NORM: n_tasks <= NB * NQ, every warp takes part once
+            float v[NB][8];
 #pragma unroll
-            for (int b = 0; b < 4; b++) {
+            for (int b = 0; b < NB; b++) {
                 const int t = t0 + b * NQ;
                 if (t < n_tasks) {
                     const int c = NC == 1 ? 0 : t / U, u = t - c * U;
@@ -1025,9 +1029,9 @@ mv_lean_kernel(const __grid_constant__ MvParams p) {
                 asm volatile("" : "+f"(v[0][0]), "+f"(v[0][7]));
                 MV_TRACE(7);
             }
-            if constexpr (NORM) norm_units<true>(v, p.norm, t0, NQ, n_tasks, lane, (float *) (smem + 64), NQ * 32, nwv);
+            if constexpr (NORM) norm_units<true, NB>(v, p.norm, t0, NQ, n_tasks, lane, (float *) (smem + 64), NQ * 32, nwv);
 #pragma unroll
-            for (int b = 0; b < 4; b++) {
+            for (int b = 0; b < NB; b++) {
                 const int t = t0 + b * NQ;
                 if (t < n_tasks) quant_unit_store<KIND>(v[b], lane, act_m + (size_t) t * ACT_MAIN, act_x + (size_t) t * ACT_AUX);
             }
