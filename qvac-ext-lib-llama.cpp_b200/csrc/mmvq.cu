@@ -898,8 +898,11 @@ __device__ __forceinline__ void unit_dot2(uint32_t w0, uint32_t w1, uint32_t am,
 // GLU: the K7 gate / up pair (MvEpi): the two stages of a pair are the gate rows and the up rows of ONE row group, and the pair's
 // two sums become glu(gate + bias, up + bias) in mat[0].dst - the stage pairs this kernel is built around are exactly that.
 // ROPE: MvRope - the launch is q / k / v of one token; the rows leave the kernel rotated / as KV-cache rows.
+// warps a CTA of the lean kernel may have: 16 quantizing warps + the producer for one column; 12 + producer from two columns on - ptxas
+// sizes registers for the bound (96 at 17 warps: the two- to four-column dot products spilled up to 136 bytes; 168 at 13 warps)
+constexpr int mv_lean_max_cons(int nc) { return nc == 1 ? MV_MAX_CONS : 12; }
 template <int TYPE, int NC, bool LL, bool BIAS = false, bool NORM = false, bool GLU = false, bool ROPE = false>
-__global__ void __launch_bounds__(32 * (MV_MAX_CONS + 1), 1)
+__global__ void __launch_bounds__(32 * (mv_lean_max_cons(NC) + 1), 1)
 mv_lean_kernel(const __grid_constant__ MvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int UB    = unit_bytes(TYPE);
@@ -1173,7 +1176,7 @@ static cudaError_t mv_lean_launch_t(const MvParams & p_in, int n_ctas, size_t sm
     MvParams p = p_in;
     p.n_helpers = 0;
     if (p.fuse_quant && !(p.dbg & 4)) {   // as many quantizing warps as src1 has units, up to the 16 + 1 warps the kernel is compiled for
-        const int room = MV_MAX_CONS - p.n_cons, want = NC * p.U - p.n_cons;
+        const int room = mv_lean_max_cons(NC) - p.n_cons, want = NC * p.U - p.n_cons;
         p.n_helpers = want < 0 ? 0 : (want < room ? want : room);
     }
     static std::atomic<bool> attr_done[64];
