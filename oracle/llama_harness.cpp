@@ -324,8 +324,15 @@ int cmd_run(int argc, char ** argv) {
         if (!forced.empty()) deficits.push_back(b1 - lg[forced[margins.size() - 1]]);
         return (llama_token) best;
     };
+    auto decode_prompt = [&]() {   // in pieces of n_batch, as llama-bench feeds a prompt (llama_context::decode asserts n_tokens <= n_batch)
+        for (size_t i0 = 0; i0 < toks.size(); i0 += (size_t) n_batch) {
+            const int32_t n = (int32_t) std::min(toks.size() - i0, (size_t) n_batch);
+            if (llama_decode(ctx, llama_batch_get_one(toks.data() + i0, n)) != 0) return false;
+        }
+        return true;
+    };
     if (n_warm > 0) {
-        if (llama_decode(ctx, llama_batch_get_one(toks.data(), (int32_t) toks.size())) != 0) { fprintf(stderr, "llama_decode(warmup prompt) failed\n"); return 1; }
+        if (!decode_prompt()) { fprintf(stderr, "llama_decode(warmup prompt) failed\n"); return 1; }
         llama_token w = toks[0];
         for (int i = 0; i < n_warm; i++) {
             if (llama_decode(ctx, llama_batch_get_one(&w, 1)) != 0) { fprintf(stderr, "llama_decode(warmup token) failed\n"); return 1; }
@@ -334,7 +341,7 @@ int cmd_run(int argc, char ** argv) {
         llama_memory_clear(llama_get_memory(ctx), true);
     }
     const auto t0 = std::chrono::steady_clock::now();
-    if (llama_decode(ctx, llama_batch_get_one(toks.data(), (int32_t) toks.size())) != 0) { fprintf(stderr, "llama_decode(prompt) failed\n"); return 1; }
+    if (!decode_prompt()) { fprintf(stderr, "llama_decode(prompt) failed\n"); return 1; }
     llama_synchronize(ctx);   // device backends return from llama_decode before the work is done
     const double prompt_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     llama_token cur = pick();
